@@ -1,0 +1,303 @@
+// common.cuh -- device context, constants, Philox stream, vector helpers.
+//
+// Everything under artis_b200/csrc/device is written as `ARTIS_DEV` inline functions over a `const Ctx &`
+// (the three C-ABI table structs with their pointers replaced by device addresses, plus derived index tables).
+// The kernels in transport.cu include these headers; tests/hostsim compiles the same headers for the host as a
+// debugging aid (never shipped, never imported by the package).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#include "artis_gpu.h"
+
+#ifdef __CUDACC__
+#define ARTIS_DEV __device__ __forceinline__
+#define ARTIS_DEV_NOINLINE __device__ __noinline__
+#else
+#define ARTIS_DEV inline
+#define ARTIS_DEV_NOINLINE inline
+#endif
+
+namespace artis {
+
+// ---- physical constants, values exactly as the reference's constants.h:3-37 ------------------------------
+constexpr double CLIGHT = 2.99792458e+10;
+constexpr double CLIGHT_PROP = CLIGHT;
+constexpr double H = 6.6260755e-27;
+constexpr double MH = 1.67352e-24;
+constexpr double ME = 9.1093897e-28;
+constexpr double PI = 3.1415926535987;  // sic (constants.h:12)
+constexpr double EV = 1.6021772e-12;
+constexpr double MEV = 1.6021772e-6;
+constexpr double SIGMA_T = 6.6524e-25;
+constexpr double THOMSON_LIMIT = 1e-2;
+constexpr double KB = 1.38064852e-16;
+constexpr double SAHACONST = 2.0706659e-16;
+constexpr double CLIGHTSQUARED = 8.9875518e+20;
+constexpr double TWOHOVERCLIGHTSQUARED = 1.4745007e-47;
+constexpr double CLIGHTSQUAREDOVERTWOH = 6.7819570e+46;
+constexpr double ONEOVERH = 1.509188961e+26;
+constexpr double HOVERKB = 4.799243681748932e-11;
+constexpr double HCLIGHTOVERFOURPI = 1.580764662876770e-17;
+constexpr double H_ionpot = 13.5979996 * EV;
+constexpr double C_0 = 5.465e-11;
+constexpr double DBL_MAX_ = 1.7976931348623157e+308;
+
+constexpr int COOLINGTYPE_FF = 880, COOLINGTYPE_FB = 881, COOLINGTYPE_COLLEXC = 882, COOLINGTYPE_COLLION = 883;
+enum { MA_RADDEEXC = 0, MA_COLDEEXC, MA_RADRECOMB, MA_COLRECOMB, MA_INTERNALDOWNSAME, MA_INTERNALDOWNLOWER,
+       MA_INTERNALUPSAME, MA_INTERNALUPHIGHER, MA_INTERNALUPHIGHERNT, MA_ACTION_COUNT };
+enum { RPKT_EVENTTYPE_NONE = -1, RPKT_EVENTTYPE_BB = 550, RPKT_EVENTTYPE_CONT = 551 };
+
+// ---- device context -----------------------------------------------------------------------------------------
+struct Ctx {
+  ArtisStaticTables st;   // pointers are device addresses
+  ArtisCellState cs;      // 〃
+  ArtisEstimators es;     // 〃 (non-const: accumulated with atomics)
+  // derived at init on the host (transport.cu: build_derived)
+  const int *line_upper_g;   // global level index of the line's upper level   [nlines]
+  const int *line_lower_g;   // 〃 lower level
+  const int *line_uion;      // unique ion index of the line                   [nlines]
+  const int *cont_level_g;   // global level index of allcont[i] lower level   [nbfcontinua]
+  const int *cont_upper_g;   // global level index of allcont[i] upper-ion level
+  const int *cont_uion;      // unique ion index of allcont[i] lower ion
+  const int *gcont_uion;     // unique ion index of groundcont[i]
+  unsigned long long seed;
+  int rank;
+  int nts;                   // timestep being transported
+  double t2;                 // ts + tw of that timestep
+  double ts_width;
+  double t_mid;
+  int *error_flag;           // set non-zero by a packet that hits a reference abort() branch
+};
+
+// ---- Philox4x32-10 counter-based stream (Salmon et al. 2011), one stream per packet -----------------------
+// key = (seed, rank, packet.number); counter = per-packet draw index, kept in the two padding words of the
+// packet record so that it survives across timesteps. Interval conventions of SURVEY Q17.
+struct Rng {
+  uint32_t k0, k1;
+  uint64_t ctr;
+};
+ARTIS_DEV uint32_t mulhi32(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * (uint64_t)b) >> 32); }
+ARTIS_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    const uint32_t hi0 = mulhi32(M0, c0), lo0 = M0 * c0;
+    const uint32_t hi1 = mulhi32(M1, c2), lo1 = M1 * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0;
+    c1 = n1;
+    c2 = n2;
+    c3 = n3;
+    k0 += W0;
+    k1 += W1;
+  }
+  out[0] = c0;
+  out[1] = c1;
+  out[2] = c2;
+  out[3] = c3;
+}
+ARTIS_DEV Rng rng_init(const Ctx &c, const ArtisPacket &p) {
+  Rng r;
+  r.k0 = (uint32_t)(c.seed & 0xffffffffu) ^ (uint32_t)p.number;
+  r.k1 = (uint32_t)(c.seed >> 32) ^ (0x9E3779B9u * (uint32_t)(c.rank + 1));
+  r.ctr = ((uint64_t)(uint32_t)p._pad1 << 32) | (uint64_t)(uint32_t)p._pad0;
+  return r;
+}
+ARTIS_DEV void rng_store(const Rng &r, ArtisPacket &p) {
+  p._pad0 = (int32_t)(uint32_t)(r.ctr & 0xffffffffu);
+  p._pad1 = (int32_t)(uint32_t)(r.ctr >> 32);
+}
+// [0,1) like gsl_rng_uniform
+ARTIS_DEV double rng_uniform(Rng &r) {
+  uint32_t o[4];
+  philox4x32_10((uint32_t)(r.ctr & 0xffffffffu), (uint32_t)(r.ctr >> 32), 0x41525449u, 0u, r.k0, r.k1, o);
+  r.ctr++;
+  const uint64_t bits = (((uint64_t)o[0] << 32) | (uint64_t)o[1]) >> 11;
+  return (double)bits * (1.0 / 9007199254740992.0);
+}
+// (0,1) like gsl_rng_uniform_pos
+ARTIS_DEV double rng_uniform_pos(Rng &r) {
+  double x;
+  do {
+    x = rng_uniform(r);
+  } while (x == 0.);
+  return x;
+}
+
+// ---- vectors.h:15-144 -------------------------------------------------------------------------------------------
+ARTIS_DEV double vec_len(const double x[3]) { return sqrt((x[0] * x[0]) + (x[1] * x[1]) + (x[2] * x[2])); }
+ARTIS_DEV double dot3(const double x[3], const double y[3]) { return (x[0] * y[0]) + (x[1] * y[1]) + (x[2] * y[2]); }
+ARTIS_DEV void vec_norm(const double in[3], double out[3]) {
+  const double m = vec_len(in);
+  out[0] = in[0] / m;
+  out[1] = in[1] / m;
+  out[2] = in[2] / m;
+}
+ARTIS_DEV void get_velocity(const double x[3], double y[3], const double t) {
+  y[0] = x[0] / t;
+  y[1] = x[1] / t;
+  y[2] = x[2] / t;
+}
+ARTIS_DEV void cross_prod(const double a[3], const double b[3], double o[3]) {
+  o[0] = (a[1] * b[2]) - (b[1] * a[2]);
+  o[1] = (a[2] * b[0]) - (b[2] * a[0]);
+  o[2] = (a[0] * b[1]) - (b[0] * a[1]);
+}
+ARTIS_DEV void vec_scale(double v[3], const double f) {
+  v[0] *= f;
+  v[1] *= f;
+  v[2] *= f;
+}
+// aberration of angles (vectors.h:63-79)
+ARTIS_DEV void angle_ab(const double dir1[3], const double vel[3], double dir2[3]) {
+  const double vsqr = dot3(vel, vel) / CLIGHTSQUARED;
+  const double gamma_rel = 1. / sqrt(1 - vsqr);
+  const double ndotv = dot3(dir1, vel);
+  const double fact1 = gamma_rel * (1 - (ndotv / CLIGHT));
+  const double fact2 = (gamma_rel - (gamma_rel * gamma_rel * ndotv / (gamma_rel + 1) / CLIGHT)) / CLIGHT;
+  for (int d = 0; d < 3; d++) dir2[d] = (dir1[d] - (vel[d] * fact2)) / fact1;
+}
+// vectors.h:81-106
+ARTIS_DEV double doppler_nucmf_on_nurf(const Ctx &c, const double dir_rf[3], const double vel_rf[3]) {
+  const double ndotv = dot3(dir_rf, vel_rf);
+  double dopplerfactor = 1. - (ndotv / CLIGHT);
+  if (c.st.opt_relativistic_doppler) {
+    const double betasq = dot3(vel_rf, vel_rf) / CLIGHTSQUARED;
+    dopplerfactor = dopplerfactor / sqrt(1 - betasq);
+  }
+  return dopplerfactor;
+}
+ARTIS_DEV double doppler_packet(const Ctx &c, const double pos[3], const double dir[3], const double prop_time) {
+  double v[3];
+  get_velocity(pos, v, prop_time);
+  return doppler_nucmf_on_nurf(c, dir, v);
+}
+template <class P>
+ARTIS_DEV double doppler_packet(const Ctx &c, const P &p) { return doppler_packet(c, p.pos, p.dir, p.prop_time); }
+// the subset of struct packet that a dummy ("ray") packet needs in get_event (rpkt.cc:83-90)
+struct Ray {
+  double pos[3], dir[3], prop_time, nu_cmf, nu_rf, e_cmf, e_rf;
+  int next_trans;
+};
+template <class P>
+ARTIS_DEV Ray ray_of(const P &p) {
+  Ray r;
+  for (int d = 0; d < 3; d++) {
+    r.pos[d] = p.pos[d];
+    r.dir[d] = p.dir[d];
+  }
+  r.prop_time = p.prop_time;
+  r.nu_cmf = p.nu_cmf;
+  r.nu_rf = p.nu_rf;
+  r.e_cmf = p.e_cmf;
+  r.e_rf = p.e_rf;
+  r.next_trans = p.next_trans;
+  return r;
+}
+// vectors.h:115-144
+template <class P>
+ARTIS_DEV void move_pkt(const Ctx &c, P &p, const double distance) {
+  p.pos[0] += (p.dir[0] * distance);
+  p.pos[1] += (p.dir[1] * distance);
+  p.pos[2] += (p.dir[2] * distance);
+  const double dopplerfactor = doppler_packet(c, p);
+  p.nu_cmf = p.nu_rf * dopplerfactor;
+  p.e_cmf = p.e_rf * dopplerfactor;
+}
+template <class P>
+ARTIS_DEV void move_pkt_withtime(const Ctx &c, P &p, const double distance) {
+  const double nu_cmf_old = p.nu_cmf;
+  p.prop_time += distance / CLIGHT_PROP;
+  move_pkt(c, p, distance);
+  if (p.nu_cmf > nu_cmf_old) p.nu_cmf = nu_cmf_old;
+}
+// vectors.cc:46-62
+ARTIS_DEV void get_rand_isotropic_unitvec(Rng &r, double v[3]) {
+  const double zrand = rng_uniform(r);
+  const double zrand2 = rng_uniform(r);
+  const double mu = -1 + (2. * zrand);
+  const double phi = zrand2 * 2 * PI;
+  const double sintheta = sqrt(1. - (mu * mu));
+  v[0] = sintheta * cos(phi);
+  v[1] = sintheta * sin(phi);
+  v[2] = mu;
+}
+// vectors.cc:10-44
+ARTIS_DEV void scatter_dir(Rng &r, const double dir_in[3], const double cos_theta, double dir_out[3]) {
+  const double zrand = rng_uniform(r);
+  const double phi = zrand * 2 * PI;
+  const double sin_theta_sq = 1. - (cos_theta * cos_theta);
+  const double sin_theta = sqrt(sin_theta_sq);
+  const double zprime = cos_theta;
+  const double xprime = sin_theta * cos(phi);
+  const double yprime = sin_theta * sin(phi);
+  const double norm1 = 1. / sqrt((dir_in[0] * dir_in[0]) + (dir_in[1] * dir_in[1]));
+  const double norm2 = 1. / sqrt((dir_in[0] * dir_in[0]) + (dir_in[1] * dir_in[1]) + (dir_in[2] * dir_in[2]));
+  const double r11 = dir_in[1] * norm1, r12 = -1 * dir_in[0] * norm1, r13 = 0.0;
+  const double r21 = dir_in[0] * dir_in[2] * norm1 * norm2, r22 = dir_in[1] * dir_in[2] * norm1 * norm2;
+  const double r23 = -1 * norm2 / norm1;
+  const double r31 = dir_in[0] * norm2, r32 = dir_in[1] * norm2, r33 = dir_in[2] * norm2;
+  dir_out[0] = (r11 * xprime) + (r21 * yprime) + (r31 * zprime);
+  dir_out[1] = (r12 * xprime) + (r22 * yprime) + (r32 * zprime);
+  dir_out[2] = (r13 * xprime) + (r23 * yprime) + (r33 * zprime);
+}
+
+// ---- estimator / counter accumulation ------------------------------------------------------------------------
+#ifdef __CUDACC__
+ARTIS_DEV void est_add(double *addr, double v) { atomicAdd(addr, v); }
+ARTIS_DEV void ctr_add(long long *addr, long long v) { atomicAdd((unsigned long long *)addr, (unsigned long long)v); }
+ARTIS_DEV void int_add(int *addr, int v) { atomicAdd(addr, v); }
+#else
+ARTIS_DEV void est_add(double *addr, double v) { *addr += v; }
+ARTIS_DEV void ctr_add(long long *addr, long long v) { *addr += v; }
+ARTIS_DEV void int_add(int *addr, int v) { *addr += v; }
+#endif
+
+// per-thread work counters, flushed once per thread at the end of a pass (keeps atomics off the hot loops)
+struct Work {
+  long long stats[34];  // stats::eventcounters increments are rare enough to go straight to global; unused here
+};
+struct Tally {
+  int rpkt_steps, lines_scanned, lines_tau, bf_evaluated, estim_atomics, gamma_steps, ma_jumps, ma_trans_scanned,
+      kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates;
+};
+ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
+  long long *k = c.es.counters;
+  if (t.rpkt_steps) ctr_add(&k[ARTIS_CTR_RPKT_STEPS], t.rpkt_steps);
+  if (t.lines_scanned) ctr_add(&k[ARTIS_CTR_LINES_SCANNED], t.lines_scanned);
+  if (t.lines_tau) ctr_add(&k[ARTIS_CTR_LINES_TAU], t.lines_tau);
+  if (t.bf_evaluated) ctr_add(&k[ARTIS_CTR_BF_EVALUATED], t.bf_evaluated);
+  if (t.estim_atomics) ctr_add(&k[ARTIS_CTR_ESTIM_ATOMICS], t.estim_atomics);
+  if (t.gamma_steps) ctr_add(&k[ARTIS_CTR_GAMMA_STEPS], t.gamma_steps);
+  if (t.ma_jumps) ctr_add(&k[ARTIS_CTR_MA_JUMPS], t.ma_jumps);
+  if (t.ma_trans_scanned) ctr_add(&k[ARTIS_CTR_MA_TRANS_SCANNED], t.ma_trans_scanned);
+  if (t.kpkt_events) ctr_add(&k[ARTIS_CTR_KPKT_EVENTS], t.kpkt_events);
+  if (t.cool_scanned) ctr_add(&k[ARTIS_CTR_COOL_SCANNED], t.cool_scanned);
+  if (t.interactions) ctr_add(&k[ARTIS_CTR_INTERACTIONS], t.interactions);
+  if (t.soft_repairs) ctr_add(&k[ARTIS_CTR_SOFT_REPAIRS], t.soft_repairs);
+  if (t.kappa_evals) ctr_add(&k[ARTIS_CTR_KAPPA_EVALS], t.kappa_evals);
+  if (t.packet_updates) ctr_add(&k[ARTIS_CTR_PACKET_UPDATES], t.packet_updates);
+}
+ARTIS_DEV void stat_inc(const Ctx &c, int counter) { ctr_add(&c.es.counters[counter], 1); }
+ARTIS_DEV void fatal(const Ctx &c, int code) {
+  if (c.error_flag) *c.error_flag = code;
+}
+
+// stats::eventcounters (stats.h:48-84)
+enum {
+  COUNTER_MA_STAT_ACTIVATION_COLLEXC = 0, COUNTER_MA_STAT_ACTIVATION_COLLION = 1,
+  COUNTER_MA_STAT_ACTIVATION_NTCOLLEXC = 2, COUNTER_MA_STAT_ACTIVATION_NTCOLLION = 3,
+  COUNTER_MA_STAT_ACTIVATION_BB = 4, COUNTER_MA_STAT_ACTIVATION_BF = 5, COUNTER_MA_STAT_ACTIVATION_FB = 6,
+  COUNTER_MA_STAT_DEACTIVATION_COLLDEEXC = 7, COUNTER_MA_STAT_DEACTIVATION_COLLRECOMB = 8,
+  COUNTER_MA_STAT_DEACTIVATION_BB = 9, COUNTER_MA_STAT_DEACTIVATION_FB = 10, COUNTER_MA_STAT_INTERNALUPHIGHER = 11,
+  COUNTER_MA_STAT_INTERNALUPHIGHERNT = 12, COUNTER_MA_STAT_INTERNALDOWNLOWER = 13, COUNTER_K_STAT_TO_MA_COLLEXC = 14,
+  COUNTER_K_STAT_TO_MA_COLLION = 15, COUNTER_K_STAT_TO_R_FF = 16, COUNTER_K_STAT_TO_R_FB = 17,
+  COUNTER_K_STAT_TO_R_BB = 18, COUNTER_K_STAT_FROM_FF = 19, COUNTER_K_STAT_FROM_BF = 20,
+  COUNTER_NT_STAT_FROM_GAMMA = 21, COUNTER_NT_STAT_TO_IONIZATION = 22, COUNTER_NT_STAT_TO_EXCITATION = 23,
+  COUNTER_NT_STAT_TO_KPKT = 24, COUNTER_K_STAT_FROM_EARLIERDECAY = 25, COUNTER_ESCOUNTER = 26,
+  COUNTER_RESONANCESCATTERINGS = 27, COUNTER_CELLCROSSINGS = 28, COUNTER_UPSCATTER = 29, COUNTER_DOWNSCATTER = 30,
+  COUNTER_UPDATECELL = 31, COUNTER_COOLINGRATECALCCOUNTER = 32, COUNTER_NESC = 33
+};
+
+}  // namespace artis

@@ -1,0 +1,392 @@
+// rpkt.cuh -- r-packet propagation: boundary crossing, continuum opacity, Sobolev line
+// sweep, event handlers, estimators. Mirrors rpkt.cc / boundary.cc / polarization.cc of the reference;
+// each function cites the lines it follows.
+#pragma once
+#include "atomicdata.cuh"
+
+namespace artis {
+
+constexpr int MAX_GROUNDCONT = 96;  // per-thread scratch for groundcont_gamma_contr (checked at init)
+
+// per-thread continuum-opacity cache == globals::kappa_rpkt_cont[tid] + phixslist[tid].groundcont_gamma_contr
+// (globals.h:162-172, 72-80). Lives for one pass of one packet (reuse if same cell and |dnu/nu|<1e-4).
+struct KappaCache {
+  double nu, total, es, ff, bf, ffheating;
+  int mgi;
+  bool valid;
+  double gamma_contr[MAX_GROUNDCONT];
+};
+
+// ---- grid geometry (grid.cc:76-200, 2086) -----------------------------------------------------------------------
+ARTIS_DEV int cell_mgi(const Ctx &c, int cellindex) { return c.st.cell_mgi[cellindex]; }
+ARTIS_DEV int ncoordgrid(const Ctx &c, int d) { return d == 0 ? c.st.ncoordgrid_x : (d == 1 ? c.st.ncoordgrid_y : c.st.ncoordgrid_z); }
+ARTIS_DEV double coordmax(const Ctx &c, int d) { return d == 0 ? c.st.coordmax_x : (d == 1 ? c.st.coordmax_y : c.st.coordmax_z); }
+ARTIS_DEV int cellcoordpointnum(const Ctx &c, int cellindex, int d) {
+  if (d == 0) return cellindex % c.st.ncoordgrid_x;
+  if (d == 1) return (cellindex / c.st.ncoordgrid_x) % c.st.ncoordgrid_y;
+  return (cellindex / (c.st.ncoordgrid_x * c.st.ncoordgrid_y)) % c.st.ncoordgrid_z;
+}
+ARTIS_DEV int coordcellindexincrement(const Ctx &c, int d) {
+  return d == 0 ? 1 : (d == 1 ? c.st.ncoordgrid_x : c.st.ncoordgrid_x * c.st.ncoordgrid_y);
+}
+// grid.cc:2086: pos_min = -coordmax + (2 * n * coordmax / ncoordgrid), evaluated in the same order
+ARTIS_DEV double cellcoordmin(const Ctx &c, int cellindex, int d) {
+  const int n = cellcoordpointnum(c, cellindex, d);
+  return -coordmax(c, d) + (2 * n * coordmax(c, d) / ncoordgrid(c, d));
+}
+ARTIS_DEV double wid_init(const Ctx &c) { return 2 * c.st.coordmax_x / c.st.ncoordgrid_x; }
+
+// ---- boundary.cc:101-330 boundary_cross (GRID_UNIFORM) ----------------------------------------------------------
+template <class P>
+ARTIS_DEV double boundary_cross(const Ctx &c, P &p, int *snext) {
+  const double tstart = p.prop_time;
+  const int cellindex = p.where;
+  const double tmin = c.st.tmin;
+  double initpos[3], cmin[3], cmax[3], vel[3];
+  const double wid = wid_init(c);
+  for (int d = 0; d < 3; d++) {
+    initpos[d] = p.pos[d];
+    cmin[d] = cellcoordmin(c, cellindex, d);
+    cmax[d] = cmin[d] + wid;
+    vel[d] = p.dir[d] * CLIGHT_PROP;
+  }
+  int last_cross = p.last_cross;
+  const int negdirections[3] = {ARTIS_NEG_X, ARTIS_NEG_Y, ARTIS_NEG_Z};
+  const int posdirections[3] = {ARTIS_POS_X, ARTIS_POS_Y, ARTIS_POS_Z};
+
+  // 10 cm tolerance repair path (boundary.cc:160-222)
+  for (int d = 0; d < 3; d++) {
+    for (int flip = 0; flip < 2; flip++) {
+      const int direction = flip ? posdirections[d] : negdirections[d];
+      const int invdirection = !flip ? posdirections[d] : negdirections[d];
+      const int stride = flip ? -coordcellindexincrement(c, d) : coordcellindexincrement(c, d);
+      bool isoutside;
+      if (flip) {
+        isoutside = initpos[d] < (cmin[d] / tmin * tstart - 10.);
+      } else {
+        isoutside = initpos[d] > (cmax[d] / tmin * tstart + 10.);
+      }
+      if (isoutside && (last_cross != direction)) {
+        if ((vel[d] - (initpos[d] / tstart)) > 0) {
+          const int pn = cellcoordpointnum(c, cellindex, d);
+          if ((pn == (ncoordgrid(c, d) - 1) && stride > 0) || (pn == 0 && stride < 0)) {
+            *snext = -99;
+            return 0;
+          }
+          *snext = p.where + stride;
+          p.last_cross = invdirection;
+          return 0;
+        }
+        last_cross = direction;
+      }
+    }
+  }
+
+  double t_max[3], t_min[3];
+  for (int d = 0; d < 3; d++) {
+    t_max[d] = ((initpos[d] - (vel[d] * tstart)) / ((cmax[d]) - (vel[d] * tmin)) * tmin) - tstart;
+    t_min[d] = ((initpos[d] - (vel[d] * tstart)) / ((cmin[d]) - (vel[d] * tmin)) * tmin) - tstart;
+  }
+  int choice = 0;
+  double time = 1.e99;
+  for (int d = 0; d < 3; d++) {
+    if ((t_max[d] > 0) && (t_max[d] < time) && (last_cross != negdirections[d])) {
+      choice = posdirections[d];
+      time = t_max[d];
+      if (cellcoordpointnum(c, cellindex, d) == (ncoordgrid(c, d) - 1)) {
+        *snext = -99;
+      } else {
+        *snext = p.where + coordcellindexincrement(c, d);
+        p.last_cross = posdirections[d];
+      }
+    }
+    if ((t_min[d] > 0) && (t_min[d] < time) && (last_cross != posdirections[d])) {
+      choice = negdirections[d];
+      time = t_min[d];
+      if (cellcoordpointnum(c, cellindex, d) == 0) {
+        *snext = -99;
+      } else {
+        *snext = p.where - coordcellindexincrement(c, d);
+        p.last_cross = negdirections[d];
+      }
+    }
+  }
+  (void)choice;  // choice == 0 ("didn't find anything") yields 1e99*c and is caught by the maxsdist check
+  return CLIGHT_PROP * time;
+}
+
+// boundary.cc:332-357 change_cell
+ARTIS_DEV void change_cell(const Ctx &c, ArtisPacket &p, int snext) {
+  if (snext == -99) {
+    p.escape_type = p.type;
+    p.escape_time = (int)p.prop_time;  // int field
+    p.type = ARTIS_TYPE_ESCAPE;
+    stat_inc(c, COUNTER_NESC);
+  } else {
+    p.where = snext;
+    stat_inc(c, COUNTER_CELLCROSSINGS);
+  }
+}
+
+// ---- rpkt.cc:26-65 closest_transition -----------------------------------------------------------------------------
+// first index i in [lo, nlines) with line_nu[i] <= nu_cmf (list sorted by decreasing nu): std::lower_bound with
+// the comparator of rpkt.cc:24
+ARTIS_DEV int linelist_lower_bound(const Ctx &c, int lo, double nu_cmf) {
+  int hi = c.st.nlines;
+  while (lo < hi) {
+    const int mid = lo + ((hi - lo) >> 1);
+    if (!(c.st.line_nu[mid] <= nu_cmf))
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  return lo;
+}
+ARTIS_DEV int closest_transition(const Ctx &c, const double nu_cmf, const int next_trans) {
+  const int left = next_trans;
+  const int right = c.st.nlines - 1;
+  if (nu_cmf < c.st.line_nu[right]) return -1;
+  if (left > right) return -1;
+  if (left > 0) return left;  // index-driven
+  if (nu_cmf >= c.st.line_nu[0]) return 0;
+  return linelist_lower_bound(c, next_trans, nu_cmf);
+}
+// rpkt.cc:511-555 closest_transition_empty. Where the reference reads past the end of the line list
+// (left > right) or calls lower_bound on an inverted range, every outcome means "no more lines"; nlines+1 is
+// what the reference stores in those cases.
+ARTIS_DEV void closest_transition_empty(const Ctx &c, ArtisPacket &p) {
+  const int left = p.next_trans;
+  const int right = c.st.nlines - 1;
+  if (left > right) {
+    p.next_trans = c.st.nlines + 1;
+  } else if (p.nu_cmf >= c.st.line_nu[left]) {
+    p.next_trans = left;
+  } else if (p.nu_cmf < c.st.line_nu[right]) {
+    p.next_trans = c.st.nlines + 1;
+  } else {
+    p.next_trans = linelist_lower_bound(c, left, p.nu_cmf);
+  }
+}
+
+// ---- rpkt.cc:1027-1073 calculate_kappa_ff -------------------------------------------------------------------------
+ARTIS_DEV double calculate_kappa_ff(const Ctx &c, const int mgi, const double nu) {
+  const float nne = c.cs.nne[mgi];
+  const float T_e = c.cs.Te[mgi];
+  double kappa_ff = 0.;
+  int ui = 0;
+  for (int element = 0; element < c.st.nelements; element++) {
+    const int nions = c.st.el_nions[element];
+    for (int ion = 0; ion < nions; ion++, ui++) {
+      const int Z = c.st.ion_ionstage[ui] - 1;
+      if (Z > 0) {
+        const double nnion = ionstagepop_ui(c, mgi, element, ui);
+        kappa_ff += Z * Z * 1 * nnion;
+      }
+    }
+  }
+  // sqrt(T_e) is evaluated in float in the reference (float argument, rpkt.cc:1064)
+  kappa_ff *= 3.69255e8 / sqrtf(T_e) * pow(nu, -3) * nne * (1 - exp(-HOVERKB * nu / T_e));
+  return kappa_ff;
+}
+
+// ---- rpkt.cc:1075-1207 calculate_kappa_bf_gammacontr ---------------------------------------------------------------
+// One term of the sum: returns kappa_bf_contr of continuum i at frequency nu (0 if skipped); *gcontr receives
+// sigma_bf*probability*corrfactor (the gamma_contr of rpkt.cc:1158-1166) or 0. `*stop` is set when nu < nu_edge
+// (list sorted by nu_edge: nothing further contributes).
+ARTIS_DEV double kappa_bf_term(const Ctx &c, const int mgi, const int i, const double nu, const double T_e, const double nne,
+                               const double nnetot, double *gcontr, bool *stop) {
+  *gcontr = 0.;
+  const int element = c.st.cont_element[i];
+  const int level = c.st.cont_level[i];
+  const int ui = c.cont_uion[i];
+  bool present;
+  if (c.st.opt_detailed_bf_estimators) {
+    present = elem_abundance(c, mgi, element) > 0;
+  } else {
+    present = (level == 0) || (ionstagepop_ui(c, mgi, element, ui) / nnetot > 1.e-6);
+  }
+  if (!present) return 0.;
+  const double nu_edge = c.st.cont_nu_edge[i];
+  const int gl = c.cont_level_g[i];
+  const double nnlevel = levelpop_g(c, mgi, element, ui, gl);
+  const double nu_max_phixs = nu_edge * c.st.last_phixs_nuovernuedge;
+  if (nu < nu_edge) {
+    *stop = true;
+    return 0.;
+  }
+  if (!(nu <= nu_max_phixs && nnlevel > 0)) return 0.;
+  const double sigma_bf = phixs_fromtable(c, c.st.cont_phixstable[i], nu_edge, nu);
+  const double probability = c.st.cont_probability[i];
+  // departure ratio (rpkt.cc:1136-1145); the reference caches it per thread and cell, the value is the same
+  const int glu = c.cont_upper_g[i];
+  const double nnupperionlevel = levelpop_g(c, mgi, element, ui + 1, glu);
+  const double sf = calculate_sahafact_g(c, gl, glu, T_e, H * nu_edge);
+  const double departure_ratio = nnupperionlevel / nnlevel * nne * sf;
+  const double stimfactor = departure_ratio * exp(-HOVERKB * nu / T_e);
+  double corrfactor = 1 - stimfactor;
+  if (corrfactor < 0) corrfactor = 0.;
+  *gcontr = sigma_bf * probability * corrfactor;
+  return nnlevel * sigma_bf * probability * corrfactor;
+}
+
+ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, const double nu, KappaCache &k, Tally &tl) {
+  double kappa_bf_sum = 0.;
+  const int ng = c.st.nbfcontinua_ground;
+  for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
+  const double T_e = (double)c.cs.Te[mgi];
+  const double nne = (double)c.cs.nne[mgi];
+  const double nnetot = (double)c.cs.nnetot[mgi];
+  const int nbf = c.st.nbfcontinua;
+  for (int i = 0; i < nbf; i++) {
+    bool stop = false;
+    double gcontr;
+    const double contr = kappa_bf_term(c, mgi, i, nu, T_e, nne, nnetot, &gcontr, &stop);
+    if (stop) break;
+    tl.bf_evaluated++;
+    if (gcontr != 0. || contr != 0.) {
+      if (c.st.cont_level[i] == 0 && ng > 0) k.gamma_contr[c.st.cont_index_in_groundphixslist[i]] += gcontr;
+      kappa_bf_sum += contr;
+    }
+  }
+  return kappa_bf_sum;
+}
+
+// rpkt.cc:1209-1309 calculate_kappa_rpkt_cont
+template <class P>
+ARTIS_DEV void calculate_kappa_rpkt_cont(const Ctx &c, const P &p, const int mgi, KappaCache &k, Tally &tl) {
+  const double nu_cmf = p.nu_cmf;
+  if (k.valid && (mgi == k.mgi) && (fabs(k.nu / nu_cmf - 1.0) < 1e-4)) return;
+  tl.kappa_evals++;
+  const float nne = c.cs.nne[mgi];
+  double sigma = 0.0, kappa_ff = 0., kappa_bf = 0., kappa_ffheating = 0.;
+  if (c.st.do_r_lc) {
+    if (c.st.opacity_case == 4) {
+      sigma = SIGMA_T * nne;
+      kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
+      kappa_ffheating = kappa_ff;
+      kappa_bf = calculate_kappa_bf_gammacontr(c, mgi, nu_cmf, k, tl);
+    } else {
+      sigma = 0.;
+      kappa_ff = 1e5 * calculate_kappa_ff(c, mgi, nu_cmf);
+      kappa_bf = 0.;
+    }
+  }
+  k.nu = nu_cmf;
+  k.mgi = mgi;
+  k.valid = true;
+  k.total = sigma + kappa_bf + kappa_ff;
+  k.es = sigma;
+  k.ff = kappa_ff;
+  k.bf = kappa_bf;
+  k.ffheating = kappa_ffheating;
+  if (!isfinite(k.total)) {  // rpkt.cc:1280-1294 soft fallback
+    if (isfinite(k.es)) {
+      k.ff = 0.;
+      k.bf = 0.;
+      k.total = k.es;
+      tl.soft_repairs++;
+    } else {
+      fatal(c, 101);
+    }
+  }
+}
+
+// ---- rpkt.cc:67-328 get_event ---------------------------------------------------------------------------------------
+// `p` is only modified where the reference modifies pkt_ptr: next_trans and mastate.
+ARTIS_DEV double get_event(const Ctx &c, const int mgi, ArtisPacket &p, int *rpkt_eventtype, const double tau_rnd,
+                           const double abort_dist, KappaCache &k, Tally &tl) {
+  double tau = 0., dist = 0., edist = 0.;
+  Ray abortray = ray_of(p);
+  move_pkt_withtime(c, abortray, abort_dist / 2.);
+  move_pkt_withtime(c, abortray, abort_dist / 2.);
+  const double nu_cmf_abort = abortray.nu_cmf;
+  Ray d = ray_of(p);
+  calculate_kappa_rpkt_cont(c, p, mgi, k, tl);
+  const double kap_cont = k.total * doppler_packet(c, p);
+  const double t_unused = 0.;
+  (void)t_unused;
+  while (true) {
+    const int lineindex = closest_transition(c, d.nu_cmf, d.next_trans);
+    if (lineindex >= 0) {
+      tl.lines_scanned++;
+      const double nu_trans = c.st.line_nu[lineindex];
+      d.next_trans = lineindex + 1;
+      double ldist;
+      if (d.nu_cmf <= nu_trans) {
+        ldist = 0;
+      } else if (!c.st.opt_relativistic_doppler) {
+        ldist = CLIGHT * d.prop_time * (d.nu_cmf / nu_trans - 1);
+      } else {
+        const double nu_r = nu_trans / d.nu_rf;
+        const double ct = CLIGHT * d.prop_time;
+        const double r = vec_len(d.pos);
+        const double mu = dot3(d.dir, d.pos) / r;
+        ldist = -mu * r + (ct - nu_r * nu_r * sqrt(ct * ct - (1 + r * r * (1 - mu * mu) * (1 + pow(nu_r, -2))))) /
+                              (1 + nu_r * nu_r);
+      }
+      if (ldist < 0.) {
+        if (!(ldist >= -100.)) fatal(c, 102);
+        ldist = 0.;
+        tl.soft_repairs++;
+      }
+      const double tau_cont = kap_cont * ldist;
+      if (tau_rnd - tau > tau_cont) {
+        if (nu_trans < nu_cmf_abort) {
+          d.next_trans -= 1;
+          p.next_trans = d.next_trans;
+          return DBL_MAX_;
+        }
+        tl.lines_tau++;
+        const int ui = c.line_uion[lineindex];
+        const int element = c.st.line_element[lineindex];
+        const int glu = c.line_upper_g[lineindex];
+        const int gll = c.line_lower_g[lineindex];
+        const double A_ul = (double)c.st.line_einstein_A[lineindex];
+        const double B_ul = CLIGHTSQUAREDOVERTWOH / pow(nu_trans, 3) * A_ul;
+        const double B_lu = (double)c.st.lev_statweight[glu] / (double)c.st.lev_statweight[gll] * B_ul;
+        const double n_u = levelpop_g(c, mgi, element, ui, glu);
+        const double n_l = levelpop_g(c, mgi, element, ui, gll);
+        double tau_line = (B_lu * n_l - B_ul * n_u) * HCLIGHTOVERFOURPI * d.prop_time;
+        if (tau_line < 0) tau_line = 0.;
+        if (tau_rnd - tau > tau_cont + tau_line) {
+          dist = dist + ldist;
+          tau += tau_cont + tau_line;
+          move_pkt_withtime(c, d, ldist);
+          // radfield::update_lineestimator: DETAILED_LINE_ESTIMATORS_ON is false in every shipped header
+        } else {
+          p.ma_element = element;
+          p.ma_ion = c.st.line_ion[lineindex];
+          p.ma_level = c.st.line_upper[lineindex];
+          p.ma_activatingline = lineindex;
+          edist = dist + ldist;
+          if (edist >= abort_dist) {  // rpkt.cc:249-262
+            edist = abort_dist * (1 - 2e-8);
+            tl.soft_repairs++;
+          }
+          *rpkt_eventtype = RPKT_EVENTTYPE_BB;
+          p.next_trans = d.next_trans;
+          return edist;
+        }
+      } else {
+        edist = dist + (tau_rnd - tau) / kap_cont;
+        d.next_trans -= 1;
+        *rpkt_eventtype = RPKT_EVENTTYPE_CONT;
+        p.next_trans = d.next_trans;
+        return edist;
+      }
+    } else {
+      d.next_trans = c.st.nlines + 1;
+      const double tau_cont = kap_cont * (abort_dist - dist);
+      if (tau_rnd - tau > tau_cont) {
+        edist = DBL_MAX_;
+      } else {
+        edist = dist + (tau_rnd - tau) / kap_cont;
+        *rpkt_eventtype = RPKT_EVENTTYPE_CONT;
+      }
+      p.next_trans = d.next_trans;
+      return edist;
+    }
+  }
+}
+
+}  // namespace artis

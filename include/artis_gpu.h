@@ -1,0 +1,209 @@
+/* artis_gpu.h -- C ABI of the B200-native ARTIS packet-transport path.
+ *
+ * This is the whole drop-in boundary: the entry points below replace exactly
+ *     update_packets(my_rank, nts, packets)          (update_packets.h; call site sn3d.cc:574)
+ *     mpi_reduce_estimators(my_rank, nts)            (sn3d.cc:316-384; call site sn3d.cc:582)
+ *     radfield::reduce_estimators()                  (radfield.cc:1502-1563)
+ * of the reference and nothing else. Plain pointers and sizes only; no C++ or torch types.
+ * The reference keeps every input/output of update_packets in process globals, so the host glue
+ * (oracle/refglue/flatten.h is a working example) flattens those globals into the three
+ * table structs declared here and passes them across.
+ *
+ * All functions return 0 on success and a non-zero code otherwise; artis_gpu_last_error() gives the text.
+ * The reference aborts on failure (sn3d.h:50-62): the glue is expected to printout()+abort() on non-zero.
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with ARTIS_ERR_NODEVICE.
+ */
+#ifndef ARTIS_GPU_H
+#define ARTIS_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "artis_gpu_fields.def"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ARTIS_GPU_ABI_VERSION 3
+
+enum artis_gpu_error {
+  ARTIS_OK = 0,
+  ARTIS_ERR_NODEVICE = 1,   /* no CUDA device / driver */
+  ARTIS_ERR_CUDA = 2,       /* a CUDA runtime call failed */
+  ARTIS_ERR_ABI = 3,        /* abi_version mismatch or inconsistent table sizes */
+  ARTIS_ERR_STATE = 4,      /* call order violated (e.g. transport before upload_cellstate) */
+  ARTIS_ERR_TRANSPORT = 5,  /* a packet hit one of the reference's fatal branches (abort() in the reference) */
+  ARTIS_ERR_UNSUPPORTED = 6,/* option combination not implemented yet */
+  ARTIS_ERR_NCCL = 7
+};
+
+/* ---- A1: struct packet (packet.h:28-73), byte-identical 304-byte AoS layout -------------------------- */
+/* packet_type (packet.h:6-17) */
+enum {
+  ARTIS_TYPE_ESCAPE = 32,
+  ARTIS_TYPE_RADIOACTIVE_PELLET = 100,
+  ARTIS_TYPE_GAMMA = 10,
+  ARTIS_TYPE_RPKT = 11,
+  ARTIS_TYPE_KPKT = 12,
+  ARTIS_TYPE_MA = 13,
+  ARTIS_TYPE_NTLEPTON = 20,
+  ARTIS_TYPE_NONTHERMAL_PREDEPOSIT = 21,
+  ARTIS_TYPE_PRE_KPKT = 120,
+  ARTIS_TYPE_GAMMA_KPKT = 121
+};
+/* cell_boundary (boundary.h:4-12) */
+enum { ARTIS_NEG_X = 101, ARTIS_POS_X = 102, ARTIS_NEG_Y = 103, ARTIS_POS_Y = 104, ARTIS_NEG_Z = 105,
+       ARTIS_POS_Z = 106, ARTIS_CROSS_NONE = 107 };
+/* decay::decaytypes used on the path (decay.h) */
+enum { ARTIS_DECAYTYPE_ALPHA = 0, ARTIS_DECAYTYPE_ELECTRONCAPTURE = 1, ARTIS_DECAYTYPE_BETAPLUS = 2,
+       ARTIS_DECAYTYPE_BETAMINUS = 3, ARTIS_DECAYTYPE_NONE = 4 };
+
+typedef struct ArtisPacket {
+  int32_t where;
+  int32_t type;
+  int32_t last_cross;
+  int32_t interactions;
+  int32_t nscatterings;
+  int32_t last_event;
+  double pos[3];
+  double dir[3];
+  double e_cmf;
+  double e_rf;
+  double nu_cmf;
+  double nu_rf;
+  int32_t next_trans;
+  int32_t emissiontype;
+  double em_pos[3];
+  int32_t em_time;
+  int32_t _pad0;
+  double prop_time;
+  int32_t absorptiontype;
+  int32_t trueemissiontype;
+  int32_t trueem_time;
+  int32_t _pad1;
+  double absorptionfreq;
+  double absorptiondir[3];
+  double stokes[3];
+  double pol_dir[3];
+  double tdecay;
+  int32_t escape_type;
+  int32_t escape_time;
+  int32_t scat_count;
+  int32_t number;
+  uint8_t originated_from_particlenotgamma;
+  uint8_t _pad2[3];
+  int32_t pellet_decaytype;
+  int32_t pellet_nucindex;
+  float trueemissionvelocity;
+  int32_t ma_element;       /* mastate.element */
+  int32_t ma_ion;           /* mastate.ion */
+  int32_t ma_level;         /* mastate.level */
+  int32_t ma_activatingline;/* mastate.activatingline */
+} ArtisPacket;
+
+/* ---- the three table structs, generated from artis_gpu_fields.def ------------------------------------ */
+#define ARTIS_DECL_S(type, name) type name;
+#define ARTIS_DECL_A(type, name, count) const type *name;
+#define ARTIS_DECL_AOUT(type, name, count) type *name;
+typedef struct ArtisStaticTables { ARTIS_STATIC_FIELDS(ARTIS_DECL_S, ARTIS_DECL_A) } ArtisStaticTables;
+typedef struct ArtisCellState { ARTIS_CELL_FIELDS(ARTIS_DECL_S, ARTIS_DECL_A) } ArtisCellState;
+typedef struct ArtisEstimators { ARTIS_ESTIM_FIELDS(ARTIS_DECL_S, ARTIS_DECL_AOUT) } ArtisEstimators;
+
+/* indices into ArtisEstimators.ts_scalars: members of globals::time_step[nts] written by the path
+ * (globals.h:20-40; update_packets.cc:53-60,88-118,152-163; nonthermal.cc do_ntlepton) */
+enum {
+  ARTIS_TS_GAMMA_DEP = 0, ARTIS_TS_POSITRON_DEP = 1, ARTIS_TS_ELECTRON_DEP = 2, ARTIS_TS_ELECTRON_EMISSION = 3,
+  ARTIS_TS_ALPHA_DEP = 4, ARTIS_TS_ALPHA_EMISSION = 5, ARTIS_TS_GAMMA_EMISSION = 6, ARTIS_TS_CMF_LUM = 7,
+  ARTIS_TS_NT_ENERGY_DEPOSITED = 8, /* nonthermal::nt_energy_deposited */
+  ARTIS_TS_COUNT = 9
+};
+/* indices into ArtisEstimators.counters: [0,34) = stats::eventcounters (stats.h:48-84); then device counters */
+enum {
+  ARTIS_CTR_NESC = 33,            /* COUNTER_NESC / globals::nesc */
+  ARTIS_CTR_PELLET_DECAYS = 34,   /* time_step[nts].pellet_decays */
+  ARTIS_CTR_RPKT_STEPS = 35,      /* iterations of do_rpkt_step (rpkt.cc:623): the roofline unit */
+  ARTIS_CTR_LINES_SCANNED = 36,   /* n_scan: line frequencies examined in get_event */
+  ARTIS_CTR_LINES_TAU = 37,       /* n_tau : Sobolev optical depths evaluated */
+  ARTIS_CTR_BF_EVALUATED = 38,    /* n_bf  : bf continua evaluated in calculate_kappa_bf */
+  ARTIS_CTR_ESTIM_ATOMICS = 39,   /* n_est : estimator atomics issued (after warp aggregation) */
+  ARTIS_CTR_GAMMA_STEPS = 40,     /* do_gamma calls */
+  ARTIS_CTR_MA_JUMPS = 41,        /* macro-atom loop iterations */
+  ARTIS_CTR_MA_TRANS_SCANNED = 42,/* transitions scanned while building/sampling macro-atom rates */
+  ARTIS_CTR_KPKT_EVENTS = 43,     /* do_kpkt / do_kpkt_bb calls */
+  ARTIS_CTR_COOL_SCANNED = 44,    /* cooling terms evaluated */
+  ARTIS_CTR_INTERACTIONS = 45,    /* sum of pkt.interactions increments (stats.cc:172-178) */
+  ARTIS_CTR_PASSES = 46,          /* bucket+transport passes in the last update_packets */
+  ARTIS_CTR_SOFT_REPAIRS = 47,    /* clamps of SURVEY Q6 applied */
+  ARTIS_CTR_KAPPA_EVALS = 48,     /* calculate_kappa_rpkt_cont recomputes (cache misses) */
+  ARTIS_CTR_PACKET_UPDATES = 49,  /* do_packet calls */
+  ARTIS_CTR_COUNT = 64
+};
+
+/* ---- life cycle --------------------------------------------------------------------------------------- */
+/* Once, after input()/ratecoefficients_init()/grid_init(). `rank`/`nranks` are the shard ("MPI rank") numbers:
+ * the Philox key of every packet is (seed, rank, packet.number) like the per-rank seeding at input.cc:1908. */
+int artis_gpu_init(const ArtisStaticTables *tables, int device, int rank, int nranks, unsigned long long seed);
+int artis_gpu_finalize(void);
+/* Text of the last error on this thread-less (single host thread per shard) library. */
+int artis_gpu_last_error(char *buf, size_t buflen);
+
+/* After update_grid + broadcast (sn3d.cc:543-551). Also runs the per-cell device precompute. */
+int artis_gpu_upload_cellstate(const ArtisCellState *state);
+/* emissivities.cc:138 zero_estimators() equivalent for the device-resident E-list. */
+int artis_gpu_zero_estimators(void);
+
+/* ---- the hot path ------------------------------------------------------------------------------------- */
+/* Drop-in for update_packets(my_rank, nts, packets) (update_packets.cc:234): H2D of the AoS packet array,
+ * all passes of the transport, D2H of the packets. Postconditions as update_packets.cc:309:
+ * every packet has type ESCAPE or prop_time == ts+tw. Packets come back in input order. */
+int artis_gpu_update_packets(int my_rank, int nts, ArtisPacket *host_packets, int npkts);
+/* The same in three steps, so that a driver can keep the packets resident between timesteps
+ *  and so that the device-resident rate can be measured separately from the copies. */
+int artis_gpu_packets_upload(const ArtisPacket *host_packets, int npkts);
+int artis_gpu_transport_resident(int nts);
+int artis_gpu_packets_download(ArtisPacket *host_packets, int npkts);
+/* milliseconds spent in the kernels of the last transport_resident call (CUDA events on the library's stream):
+ * [0] total, [1] bucketing, [2] transport kernels; returns number of values written */
+int artis_gpu_last_timings(double *ms, int n);
+/* Tunables (0 keeps the default): events a thread may process before it yields its packet for re-bucketing;
+ * threads per block. */
+int artis_gpu_set_tuning(int max_events_per_pass, int block_threads);
+
+/* ---- estimators --------------------------------------------------------------------------------------- */
+/* Replaces mpi_reduce_estimators + radfield::reduce_estimators: ONE sum all-reduce over the contiguous FP64
+ * estimator block and one over the integer block, on the transport stream (NCCL over NVLink). No-op for 1 rank. */
+int artis_gpu_comm_unique_id(char id_out[128]);                 /* rank 0 creates the NCCL id */
+int artis_gpu_comm_init(const char id[128], int rank, int nranks); /* every rank joins */
+int artis_gpu_reduce_estimators(int nts);
+int artis_gpu_download_estimators(ArtisEstimators *est);
+/* Device address and length (in doubles) of the contiguous FP64 estimator block, for callers that run their own
+ * collective on it (e.g. torch.distributed). */
+int artis_gpu_estimator_block(void **dev_ptr, size_t *ndoubles);
+
+/* ---- K10: deterministic probes (test entry points for SURVEY 8a A4-A8, A11, A12, A14) ------------------ */
+/* Each probe runs the corresponding device function for n independent packet states on the GPU. */
+/* boundary_cross (boundary.cc:101): out sdist[n], snext[n], last_cross_out[n] */
+int artis_gpu_probe_boundary_cross(const ArtisPacket *pkts, int n, double *sdist, int *snext, int *last_cross_out);
+/* calculate_kappa_rpkt_cont (rpkt.cc:1209): out kappa[n*5] = total, es, ff, bf, ffheating */
+int artis_gpu_probe_kappa_cont(const ArtisPacket *pkts, int n, double *kappa);
+/* closest_transition (rpkt.cc:26): out lineindex[n] */
+int artis_gpu_probe_closest_transition(const double *nu_cmf, const int *next_trans, int n, int *lineindex);
+/* get_event (rpkt.cc:67) with injected tau_rnd and abort_dist: out edist[n], eventtype[n] (-1 none, 1 bb, 2 cont),
+ * next_trans_out[n], mastate_out[n*4] */
+int artis_gpu_probe_get_event(const ArtisPacket *pkts, int n, const double *tau_rnd, const double *abort_dist,
+                              double *edist, int *eventtype, int *next_trans_out, int *mastate_out);
+/* calculate_macroatom_transitionrates (macroatom.cc:57) for (mgi, element, ion, level): out rates[n*9] */
+int artis_gpu_probe_macroatom_rates(const int *mgi, const int *element, const int *ion, const int *level, int n,
+                                    int nts, double *rates);
+/* calculate_kpkt_rates_ion totals (kpkt.cc:167): cumulative cooling of one ion: out contrib_total[n] */
+int artis_gpu_probe_cooling_ion(const int *mgi, const int *element, const int *ion, int n, double *contrib_total);
+/* gamma opacities (gammapkt.cc:335, photo_electric.cc:10,51): out kap[n*3] = compton, photoelectric, pair */
+int artis_gpu_probe_gamma_kappa(const ArtisPacket *pkts, int n, double *kap);
+/* get_levelpop (ltepop.cc:432): out pop[n] */
+int artis_gpu_probe_levelpop(const int *mgi, const int *element, const int *ion, const int *level, int n, double *pop);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ARTIS_GPU_H */

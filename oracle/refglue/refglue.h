@@ -1,0 +1,15 @@
+// refglue.h -- accessors for the reference's file-static state (TEST INFRASTRUCTURE / integration example).
+// Each accessor is defined in a wrapper TU (wrap_<file>.cc) that #includes the reference's <file>.cc unmodified
+// and appends the accessor, so no reference source is edited or copied.
+#ifndef REFGLUE_H
+#define REFGLUE_H
+namespace refglue {
+double *radfield_J(void);    // radfield.cc:100
+double *radfield_nuJ(void);  // radfield.cc:108
+void coolinglist_entry(int i, int *type, int *level, int *upperlevel);  // kpkt.cc:27-35
+int gamma_nlines(int nucindex);                                         // gammapkt.cc:24-31
+void gamma_line(int nucindex, int k, double *energy, double *probability);
+}  // namespace refglue
+// the reference's own transport entry point, renamed at compile time in wrap_update_packets.cc
+void ref_update_packets(const int my_rank, const int nts, struct packet *packets);
+#endif

@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Set up a run directory for the shim-built reference (TEST INFRASTRUCTURE; needs /root/reference).
+
+  python oracle/tools/make_run.py classic1d oracle/_ref/runs/s1 [--ftstep 20] [--nlevels 100] ...
+
+Mirrors what the reference's tests/setup_classicmode.sh does (rsync the input files, cp ../data/*), with the
+network-hosted atomic data replaced by oracle/tools/gen_atomic_data.py. Everything is written under oracle/_ref/
+(git-ignored); nothing from the reference is committed to this repository.
+"""
+import argparse
+import os
+import shutil
+import sys
+
+sys.path.insert(0, os.path.dirname(__file__))
+import gen_atomic_data  # noqa: E402
+
+REF = os.environ.get("ARTIS_REF", "/root/reference")
+
+
+def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax=None, model_type=None):
+    lines = open(template).read().splitlines()
+    out = []
+    k = 0
+    for line in lines:
+        if line.strip().startswith("#") or not line.strip():
+            out.append(line)
+            continue
+        body, _, comment = line.partition("#")
+        if k == 1 and ntstep is not None:
+            body = f"{ntstep}".ljust(25)
+        if k == 2:
+            body = f"{itstep:03d} {ftstep:03d}".ljust(25)
+        if k == 3 and tmin is not None:
+            body = f"{tmin} {tmax}".ljust(25)
+        if k == 7 and model_type is not None:
+            body = f"{model_type}".ljust(25)
+        out.append(body + ("#" + comment if comment else ""))
+        k += 1
+    open(path, "w").write("\n".join(out) + "\n")
+
+
+def setup_classic1d(rundir, args):
+    src = os.path.join(REF, "tests", "classicmode_inputfiles")
+    os.makedirs(rundir, exist_ok=True)
+    for f in ("model.txt", "abundances.txt"):
+        shutil.copy(os.path.join(src, f), rundir)
+    for f in os.listdir(os.path.join(REF, "data")):
+        shutil.copy(os.path.join(REF, "data", f), rundir)
+    write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep)
+    n = gen_atomic_data.generate(rundir, tuple(int(z) for z in args.elements.split(",")), args.nions, args.nlevels,
+                                 args.dense_levels, args.sparsity, args.seed)
+    print(f"run dir {rundir}: {n} lines")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("kind", choices=["classic1d"])
+    ap.add_argument("rundir")
+    ap.add_argument("--itstep", type=int, default=0)
+    ap.add_argument("--ftstep", type=int, default=36)
+    ap.add_argument("--elements", default="14,16,20,26,27,28")
+    ap.add_argument("--nions", type=int, default=5)
+    ap.add_argument("--nlevels", type=int, default=60)
+    ap.add_argument("--dense-levels", type=int, default=15)
+    ap.add_argument("--sparsity", type=float, default=0.15)
+    ap.add_argument("--seed", type=int, default=20240607)
+    args = ap.parse_args()
+    if args.kind == "classic1d":
+        setup_classic1d(args.rundir, args)
+
+
+if __name__ == "__main__":
+    main()
