@@ -32,6 +32,8 @@ PACKET_DTYPE = np.dtype({
     "itemsize": 304,
 })
 
+ABI_VERSION = int(re.search(r"#define ARTIS_GPU_ABI_VERSION (\d+)", open(os.path.join(INCLUDE, "artis_gpu.h")).read()).group(1))
+
 TYPE_ESCAPE, TYPE_PELLET, TYPE_GAMMA, TYPE_RPKT, TYPE_KPKT, TYPE_MA = 32, 100, 10, 11, 12, 13
 TYPE_NTLEPTON, TYPE_NT_PREDEPOSIT, TYPE_PRE_KPKT, TYPE_GAMMA_KPKT = 20, 21, 120, 121
 
@@ -172,5 +174,5 @@ EXPORTED_SYMBOLS = [
     "artis_gpu_download_estimators", "artis_gpu_estimator_block", "artis_gpu_probe_boundary_cross",
     "artis_gpu_probe_kappa_cont", "artis_gpu_probe_closest_transition", "artis_gpu_probe_get_event",
     "artis_gpu_probe_macroatom_rates", "artis_gpu_probe_cooling_ion", "artis_gpu_probe_gamma_kappa",
-    "artis_gpu_probe_levelpop",
+    "artis_gpu_probe_levelpop", "artis_gpu_launch_count", "artis_gpu_table_bytes",
 ]

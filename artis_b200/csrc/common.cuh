@@ -49,6 +49,23 @@ enum { MA_RADDEEXC = 0, MA_COLDEEXC, MA_RADRECOMB, MA_COLRECOMB, MA_INTERNALDOWN
 enum { RPKT_EVENTTYPE_NONE = -1, RPKT_EVENTTYPE_BB = 550, RPKT_EVENTTYPE_CONT = 551 };
 
 // ---- device context -----------------------------------------------------------------------------------------
+// Per-cell tables filled by the cell_precompute kernels after every upload_cellstate (celltables.cuh). They replace
+// the reference's per-thread `cellhistory` (globals.h:174-208): one row per non-empty model cell (index nonemptymgi)
+// instead of one cached cell per host thread. Prefix sums are accumulated in the reference's own summation order, so
+// a binary search over a row selects exactly what the reference's linear scans select.
+struct CellTables {
+  int ncells;                // nonempty_npts_model
+  double *levelpop;          // [ncells][nlevels_total]        calculate_levelpop (ltepop.cc:417)
+  double *bf_nnlevel;        // [ncells][nbfcontinua]          level pop of allcont[i], -1 if the continuum is skipped
+  double *bf_depratio;       // [ncells][nbfcontinua]          ch_allcont_departureratios (rpkt.cc:1136-1145)
+  double *ma_rates;          // [ncells][nlevels_total][9]     chlevels.processrates (macroatom.cc:57-159)
+  double *ma_cum_raddeexc;   // [ncells][ndowntrans_total]     running sum of individ_rad_deexc
+  double *ma_cum_intdown;    // [ncells][ndowntrans_total]     running sum of individ_internal_down_same
+  double *ma_cum_intup;      // [ncells][nuptrans_total]       running sum of individ_internal_up_same
+  double *cool_cum;          // [ncells][ncoolingterms]        cellhistory.cooling_contrib (kpkt.cc:167-308)
+  double *collexc_cum;       // [ncells][nuptrans_total]       running `contrib` inside a COLLEXC term (kpkt.cc:706-724)
+};
+
 struct Ctx {
   ArtisStaticTables st;   // pointers are device addresses
   ArtisCellState cs;      // 〃
@@ -61,6 +78,10 @@ struct Ctx {
   const int *cont_upper_g;   // global level index of allcont[i] upper-ion level
   const int *cont_uion;      // unique ion index of allcont[i] lower ion
   const int *gcont_uion;     // unique ion index of groundcont[i]
+  const int *lev_uion;       // unique ion index of a global level index      [nlevels_total]
+  const int *uion_element;   // element index of a unique ion index           [includedions]
+  const int *mgi_of_tabcell; // model grid index of a CellTables row           [tb.ncells]
+  CellTables tb;
   unsigned long long seed;
   int rank;
   int nts;                   // timestep being transported
@@ -70,14 +91,22 @@ struct Ctx {
   int *error_flag;           // set non-zero by a packet that hits a reference abort() branch
 };
 
-// ---- Philox4x32-10 counter-based stream (Salmon et al. 2011), one stream per packet -----------------------
-// key = (seed, rank, packet.number); counter = per-packet draw index, kept in the two padding words of the
-// packet record so that it survives across timesteps. Interval conventions of SURVEY Q17.
+// ---- Philox4x32-10 counter-based stream (Salmon et al. 2011), one stream per packet and timestep -------------
+// key = (seed_lo ^ packet.number, seed_hi); counter = (draw index lo, draw index hi, nts, rank). The draw index
+// restarts at 0 every timestep and is kept in a device array between the passes of one timestep, so nothing has to
+// survive in the host's struct packet. Interval conventions of SURVEY Q17. One Philox call yields two doubles.
 struct Rng {
-  uint32_t k0, k1;
-  uint64_t ctr;
+  uint32_t k0, k1, c2, c3;
+  uint64_t ctr;      // number of doubles drawn so far
+  double spare;      // second double of the last block
 };
-ARTIS_DEV uint32_t mulhi32(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * (uint64_t)b) >> 32); }
+ARTIS_DEV uint32_t mulhi32(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __umulhi(a, b);
+#else
+  return (uint32_t)(((uint64_t)a * (uint64_t)b) >> 32);
+#endif
+}
 ARTIS_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
@@ -97,24 +126,35 @@ ARTIS_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
   out[2] = c2;
   out[3] = c3;
 }
-ARTIS_DEV Rng rng_init(const Ctx &c, const ArtisPacket &p) {
+ARTIS_DEV Rng rng_init(const Ctx &c, const int number, const uint64_t ctr) {
   Rng r;
-  r.k0 = (uint32_t)(c.seed & 0xffffffffu) ^ (uint32_t)p.number;
-  r.k1 = (uint32_t)(c.seed >> 32) ^ (0x9E3779B9u * (uint32_t)(c.rank + 1));
-  r.ctr = ((uint64_t)(uint32_t)p._pad1 << 32) | (uint64_t)(uint32_t)p._pad0;
+  r.k0 = (uint32_t)(c.seed & 0xffffffffu) ^ (uint32_t)number;
+  r.k1 = (uint32_t)(c.seed >> 32);
+  r.c2 = (uint32_t)c.nts;
+  r.c3 = (uint32_t)c.rank;
+  r.ctr = ctr;
+  r.spare = -1.;
   return r;
 }
-ARTIS_DEV void rng_store(const Rng &r, ArtisPacket &p) {
-  p._pad0 = (int32_t)(uint32_t)(r.ctr & 0xffffffffu);
-  p._pad1 = (int32_t)(uint32_t)(r.ctr >> 32);
-}
-// [0,1) like gsl_rng_uniform
-ARTIS_DEV double rng_uniform(Rng &r) {
-  uint32_t o[4];
-  philox4x32_10((uint32_t)(r.ctr & 0xffffffffu), (uint32_t)(r.ctr >> 32), 0x41525449u, 0u, r.k0, r.k1, o);
-  r.ctr++;
-  const uint64_t bits = (((uint64_t)o[0] << 32) | (uint64_t)o[1]) >> 11;
+ARTIS_DEV double bits_to_unit(uint32_t hi, uint32_t lo) {
+  const uint64_t bits = (((uint64_t)hi << 32) | (uint64_t)lo) >> 11;
   return (double)bits * (1.0 / 9007199254740992.0);
+}
+// [0,1) like gsl_rng_uniform. Draw 2n and 2n+1 come from Philox block n.
+ARTIS_DEV double rng_uniform(Rng &r) {
+  const uint64_t blk = r.ctr >> 1;
+  const bool odd = (r.ctr & 1) != 0;
+  r.ctr++;
+  if (odd && r.spare >= 0.) {
+    const double x = r.spare;
+    r.spare = -1.;
+    return x;
+  }
+  uint32_t o[4];
+  philox4x32_10((uint32_t)(blk & 0xffffffffu), (uint32_t)(blk >> 32), r.c2, r.c3, r.k0, r.k1, o);
+  if (odd) return bits_to_unit(o[2], o[3]);  // stream resumed on an odd draw (spare was lost between passes)
+  r.spare = bits_to_unit(o[2], o[3]);
+  return bits_to_unit(o[0], o[1]);
 }
 // (0,1) like gsl_rng_uniform_pos
 ARTIS_DEV double rng_uniform_pos(Rng &r) {

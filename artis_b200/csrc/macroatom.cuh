@@ -1,0 +1,346 @@
+// macroatom.cuh -- macro-atom state machine: macroatom.cc:174-901 and select_continuum_nu
+// (ratecoeff.cc:628-684). Process rates and their running sums come from the per-cell tables (celltables.cuh); the
+// reference's linear scans `rate += x[i]; if (zrand * total < rate) break;` become a binary search for the first
+// prefix sum greater than zrand * total, which picks the same index because the prefix sums are the same FP64
+// running sums.
+#pragma once
+#include "rpkt_events.cuh"
+
+namespace artis {
+
+// first index i in [0, n) with cum[i] > target, n if none
+ARTIS_DEV int first_greater(const double *cum, const int n, const double target) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cum[mid] > target)
+      hi = mid;
+    else
+      lo = mid + 1;
+  }
+  return lo;
+}
+
+// ratecoeff.cc:264-280 alpha_sp_E_integrand_gsl
+ARTIS_DEV double alpha_sp_E_integrand(const Ctx &c, const int tablerow, const double nu_edge, const float T, const double nu) {
+  const float sigma_bf = (float)phixs_fromtable(c, tablerow, nu_edge, nu);
+  return 2. / CLIGHTSQUARED * sigma_bf * pow(nu, 3) / nu_edge * exp(-HOVERKB * nu / T);
+}
+// 8-point Gauss-Legendre on [a, b]
+ARTIS_DEV double gl8(const Ctx &c, const int tablerow, const double nu_edge, const float T, const double a, const double b) {
+  const double x[4] = {0.1834346424956498, 0.5255324099163290, 0.7966664774136267, 0.9602898564975363};
+  const double w[4] = {0.3626837833783620, 0.3137066458778873, 0.2223810344533745, 0.1012285362903763};
+  const double h = 0.5 * (b - a), m = 0.5 * (a + b);
+  double s = 0.;
+  for (int i = 0; i < 4; i++)
+    s += w[i] * (alpha_sp_E_integrand(c, tablerow, nu_edge, T, m - h * x[i]) +
+                 alpha_sp_E_integrand(c, tablerow, nu_edge, T, m + h * x[i]));
+  return s * h;
+}
+// ratecoeff.cc:628-684 select_continuum_nu. The reference evaluates up to NPHIXSPOINTS adaptive GK31 integrals of the
+// tail [xlow_i, nu_max] to CONTINUUM_NU_INTEGRAL_ACCURACY (1e-2 classic / 1e-3 nebular); here the NPHIXSPOINTS piece
+// integrals are evaluated once with a fixed 8-point rule per smooth sub-interval (pieces are split at the knots of
+// the cross-section table) and the tails are their suffix sums. Selection rule and interpolation are the
+// reference's, including the extrapolation when no piece is selected. Tolerance: |dnu/nu| <= 1e-3 (tests).
+ARTIS_DEV double select_continuum_nu(const Ctx &c, const int ui_lower, const int gl_lower, const int upperionlevel, const float T_e,
+                                     Rng &rng) {
+  const int t = phixstargetindex_of(c, gl_lower, upperionlevel);
+  if (t < 0) {
+    fatal(c, 210);
+    return 1e15;
+  }
+  const double E_threshold = phixs_threshold(c, ui_lower, gl_lower, t);
+  const double nu_threshold = ONEOVERH * E_threshold;
+  const double nu_max_phixs = nu_threshold * c.st.last_phixs_nuovernuedge;
+  const int npieces = c.st.nphixspoints;
+  const int tablerow = c.st.lev_phixstable[gl_lower];
+  const double zrand = 1. - rng_uniform(rng);  // (0, 1]
+  const double deltanu = (nu_max_phixs - nu_threshold) / npieces;
+  const double knotstep = nu_threshold * c.st.nphixsnuincrement;
+  // pass 1: total; pass 2: walk the tails from the blue end of the reference's loop
+  double total = 0.;
+  for (int pass = 0; pass < 2; pass++) {
+    double done = 0.;  // integral over [nu_threshold, xlow_i)
+    double alpha_sp_old = total, alpha_sp = total;
+    int i = 1;
+    for (int j = 0; j < npieces; j++) {
+      const double a = nu_threshold + j * deltanu;
+      const double b = (j == npieces - 1) ? nu_max_phixs : nu_threshold + (j + 1) * deltanu;
+      // split [a, b] at table knots
+      double piece = 0.;
+      double lo = a;
+      int kn = (int)floor((a - nu_threshold) / knotstep) + 1;
+      while (true) {
+        const double knot = nu_threshold + kn * knotstep;
+        if (knot > lo && knot < b) {
+          piece += gl8(c, tablerow, nu_threshold, T_e, lo, knot);
+          lo = knot;
+          kn++;
+        } else if (knot <= lo) {
+          kn++;
+        } else {
+          break;
+        }
+      }
+      piece += gl8(c, tablerow, nu_threshold, T_e, lo, b);
+      done += piece;
+      if (pass == 1 && j + 1 < npieces) {
+        i = j + 1;
+        alpha_sp_old = alpha_sp;
+        alpha_sp = total - done;
+        if (alpha_sp < 0.) alpha_sp = 0.;
+        if (zrand >= alpha_sp / total) {
+          const double nuoffset = (total * zrand - alpha_sp_old) / (alpha_sp - alpha_sp_old) * deltanu;
+          return nu_threshold + (i - 1) * deltanu + nuoffset;
+        }
+      }
+    }
+    if (pass == 0) {
+      total = done;
+    } else {
+      // no break: i == npieces in the reference, alpha_sp(_old) hold the last two tails (ratecoeff.cc:676-677)
+      const double nuoffset = (total * zrand - alpha_sp_old) / (alpha_sp - alpha_sp_old) * deltanu;
+      return nu_threshold + (npieces - 1) * deltanu + nuoffset;
+    }
+  }
+  return nu_threshold;
+}
+
+// common tail of every r-packet emission from a macro-atom / k-packet
+ARTIS_DEV void mark_emission(ArtisPacket &p) {
+  p.em_pos[0] = p.pos[0];
+  p.em_pos[1] = p.pos[1];
+  p.em_pos[2] = p.pos[2];
+  p.em_time = (int)p.prop_time;
+  p.nscatterings = 0;
+}
+
+// macroatom.cc:416-901 do_macroatom
+ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+  const int mgi = cell_mgi(c, p.where);
+  const int tc = tabcell(c, mgi);
+  const float T_e = c.cs.Te[mgi];
+  const float nne = c.cs.nne[mgi];
+  if (c.cs.thick[mgi] == 1 || tc < 0) {
+    fatal(c, 220);
+    p.type = ARTIS_TYPE_KPKT;
+    return;
+  }
+  const int element = p.ma_element;
+  int ui = uion_of(c, element, p.ma_ion);
+  int gl = c.st.ion_leveloffset[ui] + p.ma_level;
+  const int activatingline = p.ma_activatingline;
+
+  bool end_packet = false;
+  while (!end_packet) {
+    tl.ma_jumps++;
+    const double epsilon_current = c.st.lev_epsilon[gl];
+    const double *processrates = tab_ma_rates(c, tc, gl);
+    double pr[MA_ACTION_COUNT];
+    double total_transitions = 0.;
+    for (int a = 0; a < MA_ACTION_COUNT; a++) {
+      pr[a] = processrates[a];
+      total_transitions += pr[a];
+    }
+    const double randomrate = rng_uniform(rng) * total_transitions;
+    double rate = 0.;
+    int selected_action = MA_ACTION_COUNT;
+    for (int a = 0; a < MA_ACTION_COUNT; a++) {
+      rate += pr[a];
+      if (rate > randomrate) {
+        selected_action = a;
+        break;
+      }
+    }
+    if (selected_action == MA_ACTION_COUNT) {  // reference: "[fatal] do_ma: problem with random numbers" + abort
+      fatal(c, 221);
+      p.type = ARTIS_TYPE_KPKT;
+      return;
+    }
+    const int level = gl - c.st.ion_leveloffset[ui];
+    switch (selected_action) {
+      case MA_RADDEEXC: {  // macroatom.cc:222-296
+        const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
+        const double zrand = rng_uniform(rng);
+        const int i = first_greater(c.tb.ma_cum_raddeexc + (size_t)tc * c.st.ndowntrans_total + doff, ndown,
+                                    zrand * pr[MA_RADDEEXC]);
+        tl.ma_trans_scanned += ndown;
+        if (i >= ndown) {
+          fatal(c, 222);
+          p.type = ARTIS_TYPE_KPKT;
+          return;
+        }
+        const int linelistindex = c.st.downtrans_lineindex[doff + i];
+        if (c.st.opt_record_linestat) int_add(&c.es.ecounter[linelistindex], 1);
+        const int gll = c.line_lower_g[linelistindex];
+        const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gll];
+        const double oldnucmf = p.nu_cmf;
+        p.nu_cmf = epsilon_trans / H;
+        if (p.last_event == 1) stat_inc(c, oldnucmf < p.nu_cmf ? COUNTER_UPSCATTER : COUNTER_DOWNSCATTER);
+        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_BB);
+        p.interactions += 1;
+        tl.interactions++;
+        p.last_event = 0;
+        emitt_rpkt(c, p, rng);
+        if (linelistindex == activatingline) stat_inc(c, COUNTER_RESONANCESCATTERINGS);
+        p.next_trans = linelistindex + 1;
+        p.emissiontype = linelistindex;
+        mark_emission(p);
+        end_packet = true;
+        break;
+      }
+      case MA_COLDEEXC: {
+        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_COLLDEEXC);
+        p.interactions += 1;
+        tl.interactions++;
+        p.last_event = 10;
+        p.type = ARTIS_TYPE_KPKT;
+        end_packet = true;
+        est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
+        tl.estim_atomics++;
+        break;
+      }
+      case MA_INTERNALDOWNSAME: {  // macroatom.cc:174-220
+        p.interactions += 1;
+        tl.interactions++;
+        const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
+        const double zrand = rng_uniform(rng);
+        const int i = first_greater(c.tb.ma_cum_intdown + (size_t)tc * c.st.ndowntrans_total + doff, ndown,
+                                    zrand * pr[MA_INTERNALDOWNSAME]);
+        tl.ma_trans_scanned += ndown;
+        if (i >= ndown) {
+          fatal(c, 223);
+          p.type = ARTIS_TYPE_KPKT;
+          return;
+        }
+        gl = c.line_lower_g[c.st.downtrans_lineindex[doff + i]];
+        break;
+      }
+      case MA_RADRECOMB: {  // macroatom.cc:298-380
+        const int gl0_lower = c.st.ion_leveloffset[ui - 1];
+        const int nlevels = c.st.ion_ionisinglevels[ui - 1];
+        const double zrand = rng_uniform(rng);
+        double rrate = 0.;
+        int lower;
+        for (lower = 0; lower < nlevels; lower++) {
+          const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gl0_lower + lower];
+          const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
+          rrate += R * epsilon_trans;
+          if (zrand * pr[MA_RADRECOMB] < rrate) break;
+        }
+        tl.ma_trans_scanned += nlevels;
+        if (zrand * pr[MA_RADRECOMB] >= rrate) {
+          fatal(c, 224);
+          p.type = ARTIS_TYPE_KPKT;
+          return;
+        }
+        const int gl_lower = gl0_lower + lower;
+        p.nu_cmf = select_continuum_nu(c, ui - 1, gl_lower, level, T_e, rng);
+        if (!isfinite(p.nu_cmf)) fatal(c, 225);
+        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_FB);
+        p.interactions += 1;
+        tl.interactions++;
+        p.last_event = 2;
+        emitt_rpkt(c, p, rng);
+        p.next_trans = 0;
+        p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, level);
+        mark_emission(p);
+        ui -= 1;
+        gl = gl_lower;
+        end_packet = true;
+        break;
+      }
+      case MA_COLRECOMB: {
+        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_COLLRECOMB);
+        p.interactions += 1;
+        tl.interactions++;
+        p.last_event = 11;
+        p.type = ARTIS_TYPE_KPKT;
+        end_packet = true;
+        est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
+        tl.estim_atomics++;
+        break;
+      }
+      case MA_INTERNALDOWNLOWER: {  // macroatom.cc:766-813
+        p.interactions += 1;
+        tl.interactions++;
+        stat_inc(c, COUNTER_MA_STAT_INTERNALDOWNLOWER);
+        const double zrand = rng_uniform(rng);
+        const int gl0_lower = c.st.ion_leveloffset[ui - 1];
+        const int nlevels = c.st.ion_ionisinglevels[ui - 1];
+        double rrate = 0.;
+        int lower;
+        for (lower = 0; lower < nlevels; lower++) {
+          const double epsilon_target = c.st.lev_epsilon[gl0_lower + lower];
+          const double epsilon_trans = epsilon_current - epsilon_target;
+          const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
+          const double C = col_recombination_ratecoeff(c, mgi, ui, gl, gl0_lower + lower, epsilon_trans);
+          rrate += (R + C) * epsilon_target;
+          if (zrand * pr[MA_INTERNALDOWNLOWER] < rrate) break;
+        }
+        tl.ma_trans_scanned += nlevels;
+        if (lower >= nlevels) {
+          fatal(c, 226);
+          p.type = ARTIS_TYPE_KPKT;
+          return;
+        }
+        ui -= 1;
+        gl = gl0_lower + lower;
+        break;
+      }
+      case MA_INTERNALUPSAME: {  // macroatom.cc:815-835
+        p.interactions += 1;
+        tl.interactions++;
+        const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
+        const double zrand = rng_uniform(rng);
+        const int i = first_greater(c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + uoff, nup,
+                                    zrand * pr[MA_INTERNALUPSAME]);
+        tl.ma_trans_scanned += nup;
+        if (i >= nup) {
+          fatal(c, 227);
+          p.type = ARTIS_TYPE_KPKT;
+          return;
+        }
+        gl = c.line_upper_g[c.st.uptrans_lineindex[uoff + i]];
+        break;
+      }
+      case MA_INTERNALUPHIGHER: {  // macroatom.cc:382-414 do_macroatom_ionisation
+        p.interactions += 1;
+        tl.interactions++;
+        stat_inc(c, COUNTER_MA_STAT_INTERNALUPHIGHER);
+        const double zrand = rng_uniform(rng);
+        const int ntargets = c.st.lev_nphixstargets[gl];
+        double rrate = 0.;
+        int upper = -1;
+        for (int t = 0; t < ntargets; t++) {
+          upper = c.st.phixstarget_level[c.st.lev_phixstargetoffset[gl] + t];
+          const double epsilon_trans = phixs_threshold(c, ui, gl, t);
+          const double R = get_corrphotoioncoeff(c, mgi, gl, t);
+          const double C = col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans);
+          rrate += (R + C) * epsilon_current;
+          if (zrand * pr[MA_INTERNALUPHIGHER] < rrate) break;
+        }
+        if (zrand * pr[MA_INTERNALUPHIGHER] >= rrate || upper < 0) {
+          fatal(c, 228);
+          p.type = ARTIS_TYPE_KPKT;
+          return;
+        }
+        ui += 1;
+        gl = c.st.ion_leveloffset[ui] + upper;
+        break;
+      }
+      default:  // MA_INTERNALUPHIGHERNT: rate is zero unless NT_ON (not built yet)
+        fatal(c, 229);
+        p.type = ARTIS_TYPE_KPKT;
+        return;
+    }
+  }
+  if (p.trueemissiontype < 0) {  // macroatom.cc:894-898
+    p.trueemissiontype = p.emissiontype;
+    double ep[3] = {p.em_pos[0], p.em_pos[1], p.em_pos[2]};
+    p.trueemissionvelocity = (float)(vec_len(ep) / p.em_time);
+    p.trueem_time = p.em_time;
+  }
+}
+
+}  // namespace artis

@@ -2,7 +2,7 @@
 // sweep, event handlers, estimators. Mirrors rpkt.cc / boundary.cc / polarization.cc of the reference;
 // each function cites the lines it follows.
 #pragma once
-#include "atomicdata.cuh"
+#include "celltables.cuh"
 
 namespace artis {
 
@@ -193,36 +193,21 @@ ARTIS_DEV double calculate_kappa_ff(const Ctx &c, const int mgi, const double nu
 // One term of the sum: returns kappa_bf_contr of continuum i at frequency nu (0 if skipped); *gcontr receives
 // sigma_bf*probability*corrfactor (the gamma_contr of rpkt.cc:1158-1166) or 0. `*stop` is set when nu < nu_edge
 // (list sorted by nu_edge: nothing further contributes).
-ARTIS_DEV double kappa_bf_term(const Ctx &c, const int mgi, const int i, const double nu, const double T_e, const double nne,
-                               const double nnetot, double *gcontr, bool *stop) {
+ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr,
+                               bool *stop) {
   *gcontr = 0.;
-  const int element = c.st.cont_element[i];
-  const int level = c.st.cont_level[i];
-  const int ui = c.cont_uion[i];
-  bool present;
-  if (c.st.opt_detailed_bf_estimators) {
-    present = elem_abundance(c, mgi, element) > 0;
-  } else {
-    present = (level == 0) || (ionstagepop_ui(c, mgi, element, ui) / nnetot > 1.e-6);
-  }
-  if (!present) return 0.;
+  const double nnlevel = c.tb.bf_nnlevel[(size_t)tc * c.st.nbfcontinua + i];
+  if (nnlevel < 0.) return 0.;  // element absent / unimportant ion (rpkt.cc:1101-1104): skipped without the nu test
   const double nu_edge = c.st.cont_nu_edge[i];
-  const int gl = c.cont_level_g[i];
-  const double nnlevel = levelpop_g(c, mgi, element, ui, gl);
-  const double nu_max_phixs = nu_edge * c.st.last_phixs_nuovernuedge;
   if (nu < nu_edge) {
     *stop = true;
     return 0.;
   }
+  const double nu_max_phixs = nu_edge * c.st.last_phixs_nuovernuedge;
   if (!(nu <= nu_max_phixs && nnlevel > 0)) return 0.;
   const double sigma_bf = phixs_fromtable(c, c.st.cont_phixstable[i], nu_edge, nu);
   const double probability = c.st.cont_probability[i];
-  // departure ratio (rpkt.cc:1136-1145); the reference caches it per thread and cell, the value is the same
-  const int glu = c.cont_upper_g[i];
-  const double nnupperionlevel = levelpop_g(c, mgi, element, ui + 1, glu);
-  const double sf = calculate_sahafact_g(c, gl, glu, T_e, H * nu_edge);
-  const double departure_ratio = nnupperionlevel / nnlevel * nne * sf;
-  const double stimfactor = departure_ratio * exp(-HOVERKB * nu / T_e);
+  const double stimfactor = c.tb.bf_depratio[(size_t)tc * c.st.nbfcontinua + i] * expfac;  // expfac = exp(-h nu / k T_e)
   double corrfactor = 1 - stimfactor;
   if (corrfactor < 0) corrfactor = 0.;
   *gcontr = sigma_bf * probability * corrfactor;
@@ -233,14 +218,13 @@ ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, cons
   double kappa_bf_sum = 0.;
   const int ng = c.st.nbfcontinua_ground;
   for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
-  const double T_e = (double)c.cs.Te[mgi];
-  const double nne = (double)c.cs.nne[mgi];
-  const double nnetot = (double)c.cs.nnetot[mgi];
+  const int tc = tabcell(c, mgi);
+  const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[mgi]);
   const int nbf = c.st.nbfcontinua;
   for (int i = 0; i < nbf; i++) {
     bool stop = false;
     double gcontr;
-    const double contr = kappa_bf_term(c, mgi, i, nu, T_e, nne, nnetot, &gcontr, &stop);
+    const double contr = kappa_bf_term(c, tc, i, nu, expfac, &gcontr, &stop);
     if (stop) break;
     tl.bf_evaluated++;
     if (gcontr != 0. || contr != 0.) {
@@ -303,8 +287,7 @@ ARTIS_DEV double get_event(const Ctx &c, const int mgi, ArtisPacket &p, int *rpk
   Ray d = ray_of(p);
   calculate_kappa_rpkt_cont(c, p, mgi, k, tl);
   const double kap_cont = k.total * doppler_packet(c, p);
-  const double t_unused = 0.;
-  (void)t_unused;
+  const int tc = tabcell(c, mgi);
   while (true) {
     const int lineindex = closest_transition(c, d.nu_cmf, d.next_trans);
     if (lineindex >= 0) {
@@ -337,15 +320,14 @@ ARTIS_DEV double get_event(const Ctx &c, const int mgi, ArtisPacket &p, int *rpk
           return DBL_MAX_;
         }
         tl.lines_tau++;
-        const int ui = c.line_uion[lineindex];
         const int element = c.st.line_element[lineindex];
         const int glu = c.line_upper_g[lineindex];
         const int gll = c.line_lower_g[lineindex];
         const double A_ul = (double)c.st.line_einstein_A[lineindex];
         const double B_ul = CLIGHTSQUAREDOVERTWOH / pow(nu_trans, 3) * A_ul;
         const double B_lu = (double)c.st.lev_statweight[glu] / (double)c.st.lev_statweight[gll] * B_ul;
-        const double n_u = levelpop_g(c, mgi, element, ui, glu);
-        const double n_l = levelpop_g(c, mgi, element, ui, gll);
+        const double n_u = tab_levelpop(c, tc, glu);
+        const double n_l = tab_levelpop(c, tc, gll);
         double tau_line = (B_lu * n_l - B_ul * n_u) * HCLIGHTOVERFOURPI * d.prop_time;
         if (tau_line < 0) tau_line = 0.;
         if (tau_rnd - tau > tau_cont + tau_line) {

@@ -288,7 +288,8 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
     const double kappa_bf_rand = zrand2 * kappa_bf_inrest;
     // std::lower_bound over kappa_bf_sum[0 .. nbf-1): the prefix sum is re-accumulated in index order at
     // the frequency of the cached opacity, so the values are those the reference stored in its per-thread scratch
-    const double T_e = (double)c.cs.Te[mgi], nne = (double)c.cs.nne[mgi], nnetot = (double)c.cs.nnetot[mgi];
+    const int tc = tabcell(c, mgi);
+    const double expfac = exp(-HOVERKB * k.nu / (double)c.cs.Te[mgi]);
     const int nbf = c.st.nbfcontinua;
     int allcontindex = nbf - 1;
     double sum = 0.;
@@ -297,7 +298,7 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
       if (!stopped) {
         bool stop = false;
         double gcontr;
-        const double contr = kappa_bf_term(c, mgi, i, k.nu, T_e, nne, nnetot, &gcontr, &stop);
+        const double contr = kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr, &stop);
         if (stop)
           stopped = true;
         else

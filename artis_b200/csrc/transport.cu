@@ -1,0 +1,258 @@
+// transport.cu -- CUDA backend of the ARTIS packet-transport C ABI (include/artis_gpu.h), sm_100a.
+//
+// Builds libartis_gpu.so (see __graft_entry__.build()). Kernel bodies live in kernels.cuh; this file holds the
+// __global__ wrappers, the launch geometry and the CUDA implementations of the backend primitives that engine.inc
+// (the host side of the ABI) is written against. There is no CPU path: every entry point fails with
+// ARTIS_ERR_NODEVICE when no CUDA device is present.
+//
+// Launch geometry: B200 has 148 SMs. Transport threads carry a whole packet (304 B) plus the continuum-opacity
+// scratch in registers/local memory, so blocks are small (128 threads) and the grid is a grid-stride loop sized to a
+// multiple of 148 * resident blocks per SM; the table kernels are plain one-thread-per-entry grids.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <string>
+
+#include "kernels.cuh"
+
+namespace {
+
+__constant__ artis::Ctx d_ctx;
+
+constexpr int SM_COUNT_B200 = 148;
+
+__global__ void k_levelpop(long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_levelpop(d_ctx, i);
+}
+__global__ void k_bf(long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_bf(d_ctx, i);
+}
+__global__ void k_ma(long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_ma(d_ctx, i);
+}
+__global__ void k_cool(long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_cool(d_ctx, i);
+}
+__global__ void __launch_bounds__(128) k_transport(ArtisPacket *pkts, unsigned long long *rngctr, int n, int pass,
+                                                   long long max_events, int *unfinished) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    artis::body_transport(d_ctx, pkts, rngctr, i, pass, max_events, unfinished);
+}
+__global__ void k_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_boundary(d_ctx, p, i, a, b, c);
+}
+__global__ void k_probe_kappa(const ArtisPacket *p, int n, double *k) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_kappa(d_ctx, p, i, k);
+}
+__global__ void k_probe_closest(const double *nu, const int *nt, int n, int *o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_closest(d_ctx, nu, nt, i, o);
+}
+__global__ void k_probe_get_event(const ArtisPacket *p, int n, const double *t, const double *ad, double *e, int *et, int *nt,
+                                  int *ma) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_get_event(d_ctx, p, i, t, ad, e, et, nt, ma);
+}
+__global__ void k_probe_ma_rates(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_ma_rates(d_ctx, a, b, c, d, i, o);
+}
+__global__ void k_probe_cooling(const int *a, const int *b, const int *c, int n, double *o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_cooling(d_ctx, a, b, c, i, o);
+}
+__global__ void k_probe_gamma_kappa(const ArtisPacket *p, int n, double *o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_gamma_kappa(d_ctx, p, i, o);
+}
+__global__ void k_probe_levelpop(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_levelpop(d_ctx, a, b, c, d, i, o);
+}
+
+cudaStream_t g_stream = nullptr;
+cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
+int g_sms = SM_COUNT_B200;
+std::string g_async_err;
+
+void note(cudaError_t e, const char *what) {
+  if (e != cudaSuccess && g_async_err.empty()) g_async_err = std::string(what) + ": " + cudaGetErrorString(e);
+}
+
+bool be_available(std::string *why) {
+  int n = 0;
+  const cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    *why = (e != cudaSuccess) ? cudaGetErrorString(e) : "cudaGetDeviceCount returned 0 devices";
+    return false;
+  }
+  return true;
+}
+bool be_select_device(int device, std::string *why) {
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) {
+    *why = std::string("cudaSetDevice: ") + cudaGetErrorString(e);
+    return false;
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) g_sms = prop.multiProcessorCount;
+  if (g_stream == nullptr) {
+    note(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    note(cudaEventCreate(&g_ev0), "cudaEventCreate");
+    note(cudaEventCreate(&g_ev1), "cudaEventCreate");
+  }
+  g_async_err.clear();
+  return true;
+}
+void *be_alloc(size_t n) {
+  void *p = nullptr;
+  if (cudaMalloc(&p, n ? n : 1) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+void be_free(void *p) { cudaFree(p); }
+void be_h2d(void *d, const void *s, size_t n) {
+  note(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g_stream), "H2D copy");
+  note(cudaStreamSynchronize(g_stream), "H2D sync");  // the caller's buffer may be pageable / reused right away
+}
+void be_d2h(void *d, const void *s, size_t n) {
+  note(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, g_stream), "D2H copy");
+  note(cudaStreamSynchronize(g_stream), "D2H sync");
+}
+void be_zero(void *p, size_t n) { note(cudaMemsetAsync(p, 0, n, g_stream), "memset"); }
+void be_set_ctx(const artis::Ctx &c) {
+  note(cudaMemcpyToSymbolAsync(d_ctx, &c, sizeof(c), 0, cudaMemcpyHostToDevice, g_stream), "ctx upload");
+  note(cudaStreamSynchronize(g_stream), "ctx sync");
+}
+int be_sync(std::string *why) {
+  note(cudaStreamSynchronize(g_stream), "stream sync");
+  note(cudaGetLastError(), "kernel launch");
+  if (!g_async_err.empty()) {
+    *why = g_async_err;
+    g_async_err.clear();
+    return 1;
+  }
+  return 0;
+}
+void be_timer_begin() { note(cudaEventRecord(g_ev0, g_stream), "event record"); }
+double be_timer_end_ms() {
+  float ms = 0.f;
+  note(cudaEventRecord(g_ev1, g_stream), "event record");
+  note(cudaEventSynchronize(g_ev1), "event sync");
+  note(cudaEventElapsedTime(&ms, g_ev0, g_ev1), "event elapsed");
+  return ms;
+}
+int grid_for(long long n, int block, int blocks_per_sm) {
+  long long g = (n + block - 1) / block;
+  const long long cap = (long long)g_sms * blocks_per_sm;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
+void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
+void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
+void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
+void be_run_transport(ArtisPacket *p, unsigned long long *r, int n, int pass, long long maxev, int *unf, int block) {
+  if (n <= 0) return;
+  if (block > 128) block = 128;  // __launch_bounds__
+  k_transport<<<grid_for(n, block, 16), block, 0, g_stream>>>(p, r, n, pass, maxev, unf);
+}
+#define PROBE_GRID(n) ((n) + 127) / 128, 128, 0, g_stream
+void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) { k_probe_boundary<<<PROBE_GRID(n)>>>(p, n, a, b, c); }
+void be_run_probe_kappa(const ArtisPacket *p, int n, double *k) { k_probe_kappa<<<PROBE_GRID(n)>>>(p, n, k); }
+void be_run_probe_closest(const double *nu, const int *nt, int n, int *o) { k_probe_closest<<<PROBE_GRID(n)>>>(nu, nt, n, o); }
+void be_run_probe_get_event(const ArtisPacket *p, int n, const double *t, const double *ad, double *e, int *et, int *nt, int *ma) {
+  k_probe_get_event<<<PROBE_GRID(n)>>>(p, n, t, ad, e, et, nt, ma);
+}
+void be_run_probe_ma_rates(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
+  k_probe_ma_rates<<<PROBE_GRID(n)>>>(a, b, c, d, n, o);
+}
+void be_run_probe_cooling(const int *a, const int *b, const int *c, int n, double *o) { k_probe_cooling<<<PROBE_GRID(n)>>>(a, b, c, n, o); }
+void be_run_probe_gamma_kappa(const ArtisPacket *p, int n, double *o) { k_probe_gamma_kappa<<<PROBE_GRID(n)>>>(p, n, o); }
+void be_run_probe_levelpop(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
+  k_probe_levelpop<<<PROBE_GRID(n)>>>(a, b, c, d, n, o);
+}
+
+// ---- NCCL (loaded at run time so that single-GPU use needs no libnccl) ---------------------------------------------------
+struct Nccl {
+  void *h = nullptr;
+  void *comm = nullptr;
+  int nranks = 1;
+  int (*GetUniqueId)(void *) = nullptr;
+  int (*CommInitRank)(void **, int, char[128], int) = nullptr;  // ncclUniqueId is a 128-byte struct passed by value
+  int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+} g_nccl;
+struct NcclId {
+  char b[128];
+};
+bool nccl_load(std::string *err) {
+  if (g_nccl.h) return true;
+  const char *names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char *nm : names) {
+    g_nccl.h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+    if (g_nccl.h) break;
+  }
+  if (!g_nccl.h) {
+    *err = "cannot dlopen libnccl.so.2";
+    return false;
+  }
+  g_nccl.GetUniqueId = (int (*)(void *))dlsym(g_nccl.h, "ncclGetUniqueId");
+  g_nccl.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(g_nccl.h, "ncclAllReduce");
+  g_nccl.GetErrorString = (const char *(*)(int))dlsym(g_nccl.h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.AllReduce || !dlsym(g_nccl.h, "ncclCommInitRank")) {
+    *err = "libnccl lacks the expected symbols";
+    return false;
+  }
+  return true;
+}
+int be_comm_unique_id(char *id_out, std::string *err) {
+  if (!nccl_load(err)) return ARTIS_ERR_NCCL;
+  const int rc = g_nccl.GetUniqueId(id_out);
+  if (rc != 0) {
+    *err = std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(rc);
+    return ARTIS_ERR_NCCL;
+  }
+  return ARTIS_OK;
+}
+int be_comm_init(const char *id, int rank, int nranks, std::string *err) {
+  if (!nccl_load(err)) return ARTIS_ERR_NCCL;
+  NcclId nid;
+  memcpy(nid.b, id, 128);
+  auto init = (int (*)(void **, int, NcclId, int))dlsym(g_nccl.h, "ncclCommInitRank");
+  const int rc = init(&g_nccl.comm, nranks, nid, rank);
+  if (rc != 0) {
+    *err = std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(rc);
+    return ARTIS_ERR_NCCL;
+  }
+  g_nccl.nranks = nranks;
+  return ARTIS_OK;
+}
+// one sum all-reduce over the FP64 estimator block, one over the int64 counters and one over the int32 line
+// counters, issued on the transport stream right behind the last transport kernel
+int be_comm_allreduce(double *d, size_t nd, long long *l, size_t nl, int *i, size_t ni, std::string *err) {
+  if (g_nccl.comm == nullptr || g_nccl.nranks <= 1) return ARTIS_OK;  // single shard: nothing to reduce
+  const int ncclSum = 0, ncclInt32 = 2, ncclInt64 = 4, ncclFloat64 = 8;
+  int rc = g_nccl.AllReduce(d, d, nd, ncclFloat64, ncclSum, g_nccl.comm, g_stream);
+  if (rc == 0) rc = g_nccl.AllReduce(l, l, nl, ncclInt64, ncclSum, g_nccl.comm, g_stream);
+  if (rc == 0 && ni > 0) rc = g_nccl.AllReduce(i, i, ni, ncclInt32, ncclSum, g_nccl.comm, g_stream);
+  if (rc != 0) {
+    *err = std::string("ncclAllReduce: ") + g_nccl.GetErrorString(rc);
+    return ARTIS_ERR_NCCL;
+  }
+  note(cudaStreamSynchronize(g_stream), "allreduce sync");
+  return ARTIS_OK;
+}
+
+}  // namespace
+
+#include "engine.inc"

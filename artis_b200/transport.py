@@ -1,0 +1,187 @@
+"""Thin ctypes binding of the C ABI (include/artis_gpu.h) -- plumbing for tests/ and bench.py.
+
+The product is the shared library `artis_b200/libartis_gpu.so` (built from artis_b200/csrc/transport.cu by
+`__graft_entry__.build()`); the reference-side caller is the C++ glue of INTEGRATION.md. This module only moves
+numpy arrays across the same boundary and mirrors the reference's call order around `update_packets`
+(sn3d.cc:543-582): upload_cellstate -> zero_estimators -> update_packets -> reduce/download estimators.
+There is no fallback: if the library is missing or no CUDA device is present, construction / init raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_LIB = os.path.join(HERE, "libartis_gpu.so")
+
+
+class ArtisGpuError(RuntimeError):
+    pass
+
+
+class Transport:
+    def __init__(self, libpath=None):
+        path = libpath or DEFAULT_LIB
+        if not os.path.exists(path):
+            raise ArtisGpuError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                                "(there is no CPU fallback)")
+        self.lib = C.CDLL(path)
+        abi.declare(self.lib)
+        self.lib.artis_gpu_launch_count.restype = C.c_longlong
+        self.lib.artis_gpu_table_bytes.restype = C.c_size_t
+        self._keep = []
+        self.static = None
+        self.npkts = 0
+
+    # ---- helpers
+    def _check(self, rc, what):
+        if rc != 0:
+            buf = C.create_string_buffer(1024)
+            self.lib.artis_gpu_last_error(buf, 1024)
+            raise ArtisGpuError(f"{what} failed with code {rc}: {buf.value.decode()}")
+
+    # ---- life cycle
+    def init(self, static, device=0, rank=0, nranks=1, seed=1281360349):
+        static = dict(static)
+        static["abi_version"] = abi.ABI_VERSION
+        st, keep = abi.build_struct(abi.ArtisStaticTables, abi.STATIC_FIELDS, static)
+        self._keep.append(keep)
+        self.static = static
+        self._check(self.lib.artis_gpu_init(C.byref(st), device, rank, nranks, C.c_ulonglong(seed)), "artis_gpu_init")
+
+    def finalize(self):
+        self.lib.artis_gpu_finalize()
+
+    def upload_cellstate(self, cell):
+        cs, keep = abi.build_struct(abi.ArtisCellState, abi.CELL_FIELDS, dict(cell))
+        self._check(self.lib.artis_gpu_upload_cellstate(C.byref(cs)), "artis_gpu_upload_cellstate")
+        self.nts = int(cell["nts"])
+
+    def zero_estimators(self):
+        self._check(self.lib.artis_gpu_zero_estimators(), "artis_gpu_zero_estimators")
+
+    # ---- the hot path
+    def update_packets(self, packets, nts=None, rank=0):
+        """Drop-in for update_packets(my_rank, nts, packets): host array in, host array out (modified in place)."""
+        assert packets.dtype == abi.PACKET_DTYPE and packets.flags.c_contiguous
+        nts = self.nts if nts is None else nts
+        self._check(self.lib.artis_gpu_update_packets(rank, nts, packets.ctypes.data_as(C.c_void_p), packets.size),
+                    "artis_gpu_update_packets")
+        return packets
+
+    def packets_upload(self, packets):
+        assert packets.dtype == abi.PACKET_DTYPE and packets.flags.c_contiguous
+        self._check(self.lib.artis_gpu_packets_upload(packets.ctypes.data_as(C.c_void_p), packets.size),
+                    "artis_gpu_packets_upload")
+        self.npkts = packets.size
+
+    def transport_resident(self, nts=None):
+        self._check(self.lib.artis_gpu_transport_resident(self.nts if nts is None else nts),
+                    "artis_gpu_transport_resident")
+
+    def packets_download(self, out=None):
+        if out is None:
+            out = np.zeros(self.npkts, dtype=abi.PACKET_DTYPE)
+        self._check(self.lib.artis_gpu_packets_download(out.ctypes.data_as(C.c_void_p), out.size),
+                    "artis_gpu_packets_download")
+        return out
+
+    def last_timings(self):
+        ms = (C.c_double * 4)()
+        n = self.lib.artis_gpu_last_timings(ms, 4)
+        return [ms[i] for i in range(n)]
+
+    def set_tuning(self, max_events_per_pass=0, block_threads=0):
+        self.lib.artis_gpu_set_tuning(max_events_per_pass, block_threads)
+
+    def launch_count(self):
+        return int(self.lib.artis_gpu_launch_count())
+
+    def table_bytes(self):
+        return int(self.lib.artis_gpu_table_bytes())
+
+    # ---- estimators
+    def reduce_estimators(self, nts=None):
+        self._check(self.lib.artis_gpu_reduce_estimators(self.nts if nts is None else nts), "artis_gpu_reduce_estimators")
+
+    def download_estimators(self):
+        s = self.static
+        d = abi.empty_estimators(s["npts_model"], s["nelements"], s["max_nions"], s["nlines"])
+        est, keep = abi.build_struct(abi.ArtisEstimators, abi.ESTIM_FIELDS, d, writable=True)
+        self._check(self.lib.artis_gpu_download_estimators(C.byref(est)), "artis_gpu_download_estimators")
+        return d
+
+    def estimator_block(self):
+        ptr = C.c_void_p()
+        n = C.c_size_t()
+        self._check(self.lib.artis_gpu_estimator_block(C.byref(ptr), C.byref(n)), "artis_gpu_estimator_block")
+        return ptr.value, n.value
+
+    # ---- deterministic probes (K10)
+    def probe_boundary_cross(self, pkts):
+        n = pkts.size
+        sd, sn, lc = np.zeros(n), np.zeros(n, np.int32), np.zeros(n, np.int32)
+        self._check(self.lib.artis_gpu_probe_boundary_cross(pkts.ctypes.data_as(C.c_void_p), n, _pd(sd), _pi(sn), _pi(lc)),
+                    "probe_boundary_cross")
+        return sd, sn, lc
+
+    def probe_kappa_cont(self, pkts):
+        n = pkts.size
+        k = np.zeros((n, 5))
+        self._check(self.lib.artis_gpu_probe_kappa_cont(pkts.ctypes.data_as(C.c_void_p), n, _pd(k)), "probe_kappa_cont")
+        return k
+
+    def probe_closest_transition(self, nu_cmf, next_trans):
+        nu = np.ascontiguousarray(nu_cmf, np.float64)
+        nt = np.ascontiguousarray(next_trans, np.int32)
+        out = np.zeros(nu.size, np.int32)
+        self._check(self.lib.artis_gpu_probe_closest_transition(_pd(nu), _pi(nt), nu.size, _pi(out)), "probe_closest")
+        return out
+
+    def probe_get_event(self, pkts, tau_rnd, abort_dist):
+        n = pkts.size
+        t = np.ascontiguousarray(tau_rnd, np.float64)
+        a = np.ascontiguousarray(abort_dist, np.float64)
+        ed, et, nt, ma = np.zeros(n), np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros((n, 4), np.int32)
+        self._check(self.lib.artis_gpu_probe_get_event(pkts.ctypes.data_as(C.c_void_p), n, _pd(t), _pd(a), _pd(ed), _pi(et),
+                                                       _pi(nt), _pi(ma)), "probe_get_event")
+        return ed, et, nt, ma
+
+    def probe_macroatom_rates(self, mgi, element, ion, level):
+        a = [np.ascontiguousarray(x, np.int32) for x in (mgi, element, ion, level)]
+        n = a[0].size
+        out = np.zeros((n, 9))
+        self._check(self.lib.artis_gpu_probe_macroatom_rates(_pi(a[0]), _pi(a[1]), _pi(a[2]), _pi(a[3]), n, self.nts,
+                                                             _pd(out)), "probe_macroatom_rates")
+        return out
+
+    def probe_cooling_ion(self, mgi, element, ion):
+        a = [np.ascontiguousarray(x, np.int32) for x in (mgi, element, ion)]
+        n = a[0].size
+        out = np.zeros(n)
+        self._check(self.lib.artis_gpu_probe_cooling_ion(_pi(a[0]), _pi(a[1]), _pi(a[2]), n, _pd(out)), "probe_cooling_ion")
+        return out
+
+    def probe_gamma_kappa(self, pkts):
+        n = pkts.size
+        out = np.zeros((n, 3))
+        self._check(self.lib.artis_gpu_probe_gamma_kappa(pkts.ctypes.data_as(C.c_void_p), n, _pd(out)), "probe_gamma_kappa")
+        return out
+
+    def probe_levelpop(self, mgi, element, ion, level):
+        a = [np.ascontiguousarray(x, np.int32) for x in (mgi, element, ion, level)]
+        n = a[0].size
+        out = np.zeros(n)
+        self._check(self.lib.artis_gpu_probe_levelpop(_pi(a[0]), _pi(a[1]), _pi(a[2]), _pi(a[3]), n, _pd(out)),
+                    "probe_levelpop")
+        return out
+
+
+def _pd(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _pi(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int))

@@ -164,8 +164,12 @@ int artis_gpu_packets_upload(const ArtisPacket *host_packets, int npkts);
 int artis_gpu_transport_resident(int nts);
 int artis_gpu_packets_download(ArtisPacket *host_packets, int npkts);
 /* milliseconds spent in the kernels of the last transport_resident call (CUDA events on the library's stream):
- * [0] total, [1] bucketing, [2] transport kernels; returns number of values written */
+ * [0] total, [1] bucketing, [2] transport kernels, [3] cell_precompute of the last upload_cellstate; returns number of values written */
 int artis_gpu_last_timings(double *ms, int n);
+/* Introspection for the measurement harness: kernels launched by the library since init, and bytes held by the
+ * per-cell tables that replace the reference's cellhistory cache. */
+long long artis_gpu_launch_count(void);
+size_t artis_gpu_table_bytes(void);
 /* Tunables (0 keeps the default): events a thread may process before it yields its packet for re-bucketing;
  * threads per block. */
 int artis_gpu_set_tuning(int max_events_per_pass, int block_threads);

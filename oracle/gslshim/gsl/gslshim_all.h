@@ -10,9 +10,9 @@
 #ifndef GSLSHIM_ALL_H
 #define GSLSHIM_ALL_H
 
-#include <cmath>
-#include <cstddef>
-#include <cstdlib>
+#include <math.h>   // like the real gsl_math.h: in C++ this brings the float overloads of sqrt/exp/... into the global namespace
+#include <stddef.h>
+#include <stdlib.h>
 
 #ifdef __cplusplus
 extern "C" {

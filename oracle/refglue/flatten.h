@@ -489,6 +489,7 @@ inline void flatten_estimators(ArtisEstimators *E, Storage *st, const int nts) {
   const size_t NG = (size_t)NM * e.nelements * e.max_nions;
   double *ga = st->D(NG), *bf = st->D(NG);
   for (int m = 0; m < e.npts_model; m++) {
+    if (grid::get_numassociatedcells(m) <= 0) continue;  // the reference never zeroes the slots of empty cells
     J[m] = refglue::radfield_J()[m];
     nuJ[m] = refglue::radfield_nuJ()[m];
     ff[m] = globals::ffheatingestimator[m];

@@ -59,10 +59,12 @@ def generate(outdir, elements=(26, 27, 28), nions=5, nlevels=100, dense_levels=2
                     dense = up < dense_levels
                     if dense or rng.random() < sparsity:
                         forbidden = 1 if (rng.random() < 0.3 or up <= nlow) else 0
-                        if forbidden:
-                            A = 10 ** rng.uniform(-2.0, 1.5)
-                        else:
-                            A = 10 ** rng.uniform(4.0, 8.5)
+                        # A-values follow from an oscillator strength and the transition energy, so that close-lying
+                        # levels get small A (A ~ nu^2 f): A_ul = 6.6702e15 g_l/g_u f / lambda[Angstrom]^2.
+                        # Forbidden lines: f ~ 1e-9..1e-6.
+                        lam = 12398.42 / max(energies[up] - energies[lo], 1e-6)
+                        f = 10 ** (rng.uniform(-9.0, -6.0) if forbidden else rng.uniform(-3.5, -0.3))
+                        A = 6.6702e15 * g[lo] / g[up] * f / lam ** 2
                         tl.append((lo + 1, up + 1, A, -1.0, forbidden))
             ntr = np.zeros(nlev, dtype=int)
             for lo, up, *_ in tl:

@@ -1,0 +1,62 @@
+// hostsim.cc -- TEST INFRASTRUCTURE / DEBUGGING AID. Never shipped, never imported by artis_b200.
+//
+// Compiles the device headers of artis_b200/csrc as plain host C++ and runs every kernel body in a serial loop, behind
+// the same C ABI. This exists because the development container has no GPU: it lets the physics restatement be
+// debugged against the reference's snapshots with gdb/ASan before GPU time is spent. The product library
+// (artis_b200/csrc/transport.cu -> libartis_gpu.so) has no CPU path: without a CUDA device every entry point fails.
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "../../artis_b200/csrc/kernels.cuh"
+
+namespace {
+artis::Ctx g_ctx;
+std::chrono::steady_clock::time_point g_t0;
+bool be_available(std::string *) { return true; }
+bool be_select_device(int, std::string *) { return true; }
+void *be_alloc(size_t n) { return calloc(1, n ? n : 1); }
+void be_free(void *p) { free(p); }
+void be_h2d(void *d, const void *s, size_t n) { memcpy(d, s, n); }
+void be_d2h(void *d, const void *s, size_t n) { memcpy(d, s, n); }
+void be_zero(void *p, size_t n) { memset(p, 0, n); }
+void be_set_ctx(const artis::Ctx &c) { g_ctx = c; }
+int be_sync(std::string *) { return 0; }
+void be_timer_begin() { g_t0 = std::chrono::steady_clock::now(); }
+double be_timer_end_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_t0).count(); }
+void be_run_levelpop(long long n) { for (long long i = 0; i < n; i++) artis::body_levelpop(g_ctx, i); }
+void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g_ctx, i); }
+void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
+void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
+void be_run_transport(ArtisPacket *p, unsigned long long *r, int n, int pass, long long maxev, int *unf, int) {
+  for (int i = 0; i < n; i++) artis::body_transport(g_ctx, p, r, i, pass, maxev, unf);
+}
+void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
+  for (int i = 0; i < n; i++) artis::body_probe_boundary(g_ctx, p, i, a, b, c);
+}
+void be_run_probe_kappa(const ArtisPacket *p, int n, double *k) { for (int i = 0; i < n; i++) artis::body_probe_kappa(g_ctx, p, i, k); }
+void be_run_probe_closest(const double *nu, const int *nt, int n, int *o) {
+  for (int i = 0; i < n; i++) artis::body_probe_closest(g_ctx, nu, nt, i, o);
+}
+void be_run_probe_get_event(const ArtisPacket *p, int n, const double *t, const double *ad, double *e, int *et, int *nt, int *ma) {
+  for (int i = 0; i < n; i++) artis::body_probe_get_event(g_ctx, p, i, t, ad, e, et, nt, ma);
+}
+void be_run_probe_ma_rates(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
+  for (int i = 0; i < n; i++) artis::body_probe_ma_rates(g_ctx, a, b, c, d, i, o);
+}
+void be_run_probe_cooling(const int *a, const int *b, const int *c, int n, double *o) {
+  for (int i = 0; i < n; i++) artis::body_probe_cooling(g_ctx, a, b, c, i, o);
+}
+void be_run_probe_gamma_kappa(const ArtisPacket *p, int n, double *o) {
+  for (int i = 0; i < n; i++) artis::body_probe_gamma_kappa(g_ctx, p, i, o);
+}
+void be_run_probe_levelpop(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
+  for (int i = 0; i < n; i++) artis::body_probe_levelpop(g_ctx, a, b, c, d, i, o);
+}
+int be_comm_unique_id(char *, std::string *) { return ARTIS_ERR_NCCL; }
+int be_comm_init(const char *, int, int, std::string *) { return ARTIS_ERR_NCCL; }
+int be_comm_allreduce(double *, size_t, long long *, size_t, int *, size_t, std::string *) { return ARTIS_OK; }
+}  // namespace
+
+#include "../../artis_b200/csrc/engine.inc"

@@ -1,0 +1,103 @@
+"""Summary statistics of one update_packets call, shared by the golden-fixture generator
+(oracle/tools/ref_ensemble.py, which runs the reference) and the parity tests (which run the CUDA path).
+
+A Monte Carlo transport step cannot be compared packet by packet (the reference consumes one GSL ran3
+stream in packet-visit order, the device draws from per-packet Philox streams), so parity of the full step is
+statistical: an ensemble of K reference runs of the SAME timestep from the SAME start state with K seeds is compared
+with an ensemble of device runs. For every scalar below the test is a two-sample z-test with both ensemble variances.
+"""
+import numpy as np
+
+TYPES = (10, 11, 12, 13, 20, 21, 32, 100, 120)
+NSPEC = 12
+
+
+def good_cells(static, cell):
+    """non-empty, non-grey model cells: the only ones whose estimators mean something in the reference (in grey cells
+    the reference adds whatever opacity scratch its host thread last computed for some other cell)."""
+    n = int(static["npts_model"])
+    return (np.asarray(static["nonemptymgi_of_mgi"][:n]) >= 0) & (np.asarray(cell["thick"][:n]) != 1)
+
+
+def nonempty_cells(static):
+    n = int(static["npts_model"])
+    return np.asarray(static["nonemptymgi_of_mgi"][:n]) >= 0
+
+
+def summary(static, cell, est, post, pre):
+    """dict name -> float for one transported timestep."""
+    n = int(static["npts_model"])
+    ng = int(static["nelements"]) * int(static["max_nions"])
+    good = good_cells(static, cell)
+    ne = nonempty_cells(static)
+    d = {}
+    # radiation-field estimators: totals over non-grey cells and three radial groups of them
+    idx = np.nonzero(good)[0]
+    groups = np.array_split(idx, 3) if idx.size >= 3 else [idx]
+    for key, short in (("J", "J"), ("nuJ", "nuJ"), ("ffheatingestimator", "ff"), ("colheatingestimator", "col")):
+        a = np.asarray(est[key][:n])
+        d[short + "_tot"] = a[good].sum()
+        for g, ii in enumerate(groups):
+            d[f"{short}_g{g}"] = a[ii].sum()
+    a = np.asarray(est["rpkt_emiss"][:n])
+    d["rpkt_emiss_tot"] = a[ne].sum()
+    for key, short in (("gammaestimator", "gamma"), ("bfheatingestimator", "bfheat")):
+        a = np.asarray(est[key][: n * ng]).reshape(n, ng)
+        d[short + "_tot"] = a[good].sum()
+    ts = np.asarray(est["ts_scalars"])
+    for i, nm in enumerate(("gamma_dep", "positron_dep", "electron_dep", "electron_emission", "alpha_dep",
+                            "alpha_emission", "gamma_emission", "cmf_lum", "nt_energy_deposited")):
+        d["ts_" + nm] = ts[i]
+    ctr = np.asarray(est["counters"])
+    for i in range(31):  # stats::eventcounters except UPDATECELL / COOLINGRATECALC / NESC (scheduler-specific)
+        d[f"ctr{i:02d}"] = float(ctr[i])
+    d["acounter_sum"] = float(np.asarray(est["acounter"]).sum())
+    d["ecounter_sum"] = float(np.asarray(est["ecounter"]).sum())
+    # packets
+    d["interactions"] = float(post["interactions"].sum())
+    for t in TYPES:
+        d[f"ntype{t}"] = float((post["type"] == t).sum())
+    newesc = (post["type"] == 32) & _was_active(post, pre)
+    d["n_newly_escaped"] = float(newesc.sum())
+    d["e_rf_newly_escaped_r"] = post["e_rf"][newesc & (post["escape_type"] == 11)].sum()
+    d["e_rf_newly_escaped_gamma"] = post["e_rf"][newesc & (post["escape_type"] == 10)].sum()
+    r = post["type"] == 11
+    d["rpkt_e_cmf"] = post["e_cmf"][r].sum()
+    d["rpkt_mean_lognu"] = np.log(post["nu_cmf"][r]).mean() if r.any() else 0.0
+    d["rpkt_mean_radius"] = np.sqrt((post["pos"][r] ** 2).sum(1)).mean() if r.any() else 0.0
+    d["rpkt_mean_mu"] = ((post["pos"][r] * post["dir"][r]).sum(1) / np.sqrt((post["pos"][r] ** 2).sum(1))).mean() if r.any() else 0.0
+    d["rpkt_mean_nscat"] = post["nscatterings"][r].mean() if r.any() else 0.0
+    # coarse emergent spectrum of the packets that escaped in this step (spectrum.cc:339 bins nu_rf logarithmically)
+    er = newesc & (post["escape_type"] == 11)
+    edges = np.logspace(np.log10(float(static["nu_min_r"])), np.log10(float(static["nu_max_r"])), NSPEC + 1)
+    h, _ = np.histogram(post["nu_rf"][er], bins=edges, weights=post["e_rf"][er])
+    for i in range(NSPEC):
+        d[f"spec{i:02d}"] = h[i]
+    return d
+
+
+def _was_active(post, pre):
+    """mask over `post` of packets that were not yet escaped in `pre` (matched by packet.number: the reference
+    re-orders the array, update_packets.cc:256)."""
+    esc_before = np.zeros(int(max(pre["number"].max(), post["number"].max())) + 1, dtype=bool)
+    esc_before[pre["number"][pre["type"] == 32]] = True
+    return ~esc_before[post["number"]]
+
+
+def ztest(ref_rows, dev_rows, names):
+    """two-sample z for every quantity; returns list of (name, ref_mean, dev_mean, z)."""
+    out = []
+    ra, da = np.asarray(ref_rows, float), np.asarray(dev_rows, float)
+    for j, nm in enumerate(names):
+        r, d = ra[:, j], da[:, j]
+        se = np.sqrt(r.var(ddof=1) / r.size + d.var(ddof=1) / d.size)
+        diff = d.mean() - r.mean()
+        scale = max(abs(r.mean()), abs(d.mean()))
+        if scale == 0 or abs(diff) <= 1e-9 * scale:  # identical up to summation order (deterministic quantities)
+            z = 0.0
+        elif se == 0:
+            z = np.inf
+        else:
+            z = diff / se
+        out.append((nm, r.mean(), d.mean(), z))
+    return out
