@@ -85,7 +85,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
   const int ihigh = ilow + c.st.ion_ncoolingterms[ui] - 1;
   const double *cool = c.tb.cool_cum + (size_t)tc * c.st.ncoolingterms;
   int i = lower_bound_idx(cool, ilow, ihigh, rndcool);
-  tl.cool_scanned++;
+  tl.cool_scanned += bsearch_probes(ihigh - ilow + 1) + ui + 1;  // list probes + ion totals scanned
   if (i > ihigh) {  // assert_always(i <= ihigh) in the reference
     fatal(c, 303);
     p.prop_time = t2;

@@ -8,6 +8,15 @@
 
 namespace artis {
 
+// number of table entries a binary search over n entries reads (the work counters feed the roofline)
+ARTIS_DEV int bsearch_probes(int n) {
+  int k = 0;
+  while (n > 0) {
+    k++;
+    n >>= 1;
+  }
+  return k;
+}
 // first index i in [0, n) with cum[i] > target, n if none
 ARTIS_DEV int first_greater(const double *cum, const int n, const double target) {
   int lo = 0, hi = n;
@@ -164,7 +173,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         const double zrand = rng_uniform(rng);
         const int i = first_greater(c.tb.ma_cum_raddeexc + (size_t)tc * c.st.ndowntrans_total + doff, ndown,
                                     zrand * pr[MA_RADDEEXC]);
-        tl.ma_trans_scanned += ndown;
+        tl.ma_trans_scanned += bsearch_probes(ndown);
         if (i >= ndown) {
           fatal(c, 222);
           p.type = ARTIS_TYPE_KPKT;
@@ -207,7 +216,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         const double zrand = rng_uniform(rng);
         const int i = first_greater(c.tb.ma_cum_intdown + (size_t)tc * c.st.ndowntrans_total + doff, ndown,
                                     zrand * pr[MA_INTERNALDOWNSAME]);
-        tl.ma_trans_scanned += ndown;
+        tl.ma_trans_scanned += bsearch_probes(ndown);
         if (i >= ndown) {
           fatal(c, 223);
           p.type = ARTIS_TYPE_KPKT;
@@ -228,7 +237,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
           rrate += R * epsilon_trans;
           if (zrand * pr[MA_RADRECOMB] < rrate) break;
         }
-        tl.ma_trans_scanned += nlevels;
+        tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
         if (zrand * pr[MA_RADRECOMB] >= rrate) {
           fatal(c, 224);
           p.type = ARTIS_TYPE_KPKT;
@@ -278,7 +287,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
           rrate += (R + C) * epsilon_target;
           if (zrand * pr[MA_INTERNALDOWNLOWER] < rrate) break;
         }
-        tl.ma_trans_scanned += nlevels;
+        tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
         if (lower >= nlevels) {
           fatal(c, 226);
           p.type = ARTIS_TYPE_KPKT;
@@ -295,7 +304,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         const double zrand = rng_uniform(rng);
         const int i = first_greater(c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + uoff, nup,
                                     zrand * pr[MA_INTERNALUPSAME]);
-        tl.ma_trans_scanned += nup;
+        tl.ma_trans_scanned += bsearch_probes(nup);
         if (i >= nup) {
           fatal(c, 227);
           p.type = ARTIS_TYPE_KPKT;

@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the ARTIS update_packets hot path on B200, next to the reference on the host cores.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--packets P] [--impl reference]
+
+A "step" is one pass of the hot path (one update_packets call, update_packets.cc:234) over one batch of packets of
+the workload timestep. The workload is a snapshot of the inputs of that call, taken from a run of the unmodified
+reference (oracle/refglue/hook.cc) on the repo's classic-mode test model with synthetic atomic data, and replicated
+to P statistically identical packets per GPU (weak scaling: packets are sharded, grid and atomic data replicated,
+one estimator all-reduce per step -- SURVEY 8e).
+
+  value      interactions/s, whole job, packets resident in HBM when the timed region starts (device time, CUDA events
+             inside the library on the stream the kernels run on, max over ranks; + the NCCL all-reduce for N > 1)
+  e2e        the same through artis_gpu_update_packets with HOST packet buffers: H2D of the 304-byte packets, all
+             passes, D2H of the packets and of the estimator block inside the timed region
+  roofline   algorithmic bytes (SURVEY 8d formula over the library's device work counters) / transport-kernel time
+  cpu_baseline / --impl reference : the reference's own update_packets on the host cores (oracle/_ref)
+"""
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+METRIC = "rpkt_interactions_per_s"
+UNIT = "interactions/s"
+BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_base")
+BENCH_TS = 25
+REF_EXE = os.path.join(REPO, "oracle", "_ref", "classic", "sn3d_ref")
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def load_workload():
+    """(static, cell, packets_pre, name). The bench snapshot lives under oracle/_ref (git-ignored, travels to the GPU
+    box); if it is missing the committed golden fixture is used and the workload name says so."""
+    from artis_b200 import snapshot
+    snap = os.path.join(BENCH_RUN, f"snap_ts{BENCH_TS}.bin")
+    if os.path.exists(snap):
+        s = snapshot.load(snap)
+        st, cs = snapshot.static_tables(s), snapshot.cell_state(s)
+        name = (f"classicmode W7-like 1D model (tests/classicmode_inputfiles, artisoptions_classic.h, 100^3 grid), "
+                f"synthetic atomic data {st['nlines']} lines / {st['nbfcontinua']} bf continua / {st['nlevels_total']} "
+                f"levels, timestep {BENCH_TS}")
+        return st, cs, s["packets.pre"].copy(), name
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    import goldenlib
+    fx = goldenlib.load_fixture("classic_nogrey_ts12.npz")
+    return fx["static"], fx["cell"], fx["pre"], "FALLBACK golden fixture classic_nogrey_ts12 (bench snapshot missing)"
+
+
+def replicate(pre, P, rank, step):
+    """P statistically identical packets: the snapshot's packets tiled, each copy with its own packet.number (its
+    Philox stream) and with energies scaled so that the total energy is that of the snapshot (packet.cc:106-108)."""
+    reps = -(-P // pre.size)
+    out = np.tile(pre, reps)[:P].copy()
+    scale = pre.size / float(P)
+    for f in ("e_cmf", "e_rf"):
+        out[f] *= scale
+    base = (step * 8 + rank) * P
+    out["number"] = (np.arange(P, dtype=np.int64) + base).astype(np.int32)
+    return out
+
+
+def algorithmic_bytes(ctr):
+    """B = 208 n_rpkt_step + 8 n_scan + 64 n_tau + 80 n_bf + 16 n_est + (72 n_ma_jump + 8 n_ma_probe)
+    + (72 n_kpkt + 8 n_cool_probe) + 240 n_gamma_step, all exact device counters of the timed steps."""
+    return (208 * ctr[35] + 8 * ctr[36] + 64 * ctr[37] + 80 * ctr[38] + 16 * ctr[39] + 240 * ctr[40] + 72 * ctr[41] +
+            8 * ctr[42] + 72 * ctr[43] + 8 * ctr[44])
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.rows, self.stop_flag = device, [], False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.device)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def run_reference(nproc, steps, warmup):
+    """Times the UNMODIFIED reference (oracle/_ref/classic/sn3d_ref: the reference's own sources built against the
+    GSL shim) on the host cores: `nproc` independent single-thread processes (= MPI ranks of the reference: packets
+    sharded, everything else replicated; MPI itself is not in the image) each transporting the workload timestep from
+    the same checkpoint with its own seed. Returns (interactions, seconds, sample description)."""
+    if not (os.path.exists(REF_EXE) and os.path.exists(os.path.join(BENCH_RUN, f"gridsave_ts{BENCH_TS}.tmp"))):
+        return None
+    keep = ("adata.txt", "transitiondata.txt", "phixsdata_v2.txt", "compositiondata.txt", "model.txt", "abundances.txt",
+            "input.txt", "ratecoeff.dat", "bflist.dat", f"gridsave_ts{BENCH_TS}.tmp", f"packets_0000_ts{BENCH_TS}.tmp")
+    tot_inter, tot_sec = 0.0, 0.0
+    npk = 0
+    with tempfile.TemporaryDirectory(prefix="artis_ref_") as tmp:
+        dirs = []
+        for r in range(nproc):
+            d = os.path.join(tmp, f"rank{r}")
+            os.makedirs(d)
+            for f in os.listdir(BENCH_RUN):
+                if f in keep or f.endswith("_lines.txt") or f.endswith("decays.txt") or f.startswith(("auger", "collion",
+                                                                                                       "binding")):
+                    shutil.copy(os.path.join(BENCH_RUN, f), d)
+            dirs.append(d)
+        for it in range(warmup + steps):
+            procs = []
+            for r, d in enumerate(dirs):
+                lines = open(os.path.join(d, "input.txt")).read().splitlines()
+                for i, line in enumerate(lines):
+                    if line.strip() and not line.strip().startswith("#"):
+                        lines[i] = f"{900001 + 7919 * (it * nproc + r)}".ljust(25) + "# pre_zseed"
+                        break
+                open(os.path.join(d, "input.txt"), "w").write("\n".join(lines) + "\n")
+                if os.path.exists(os.path.join(d, "hook_timing.txt")):
+                    os.remove(os.path.join(d, "hook_timing.txt"))
+                env = dict(os.environ, ARTIS_HOOK_DIR=".", ARTIS_HOOK_STOP_AFTER_TS=str(BENCH_TS))
+                procs.append(subprocess.Popen([REF_EXE], cwd=d, env=env, stdout=subprocess.DEVNULL,
+                                              stderr=subprocess.DEVNULL))
+            for p in procs:
+                p.wait()
+            inter, sec = 0.0, 0.0
+            for d in dirs:
+                row = open(os.path.join(d, "hook_timing.txt")).read().split()
+                npk = int(row[1])
+                inter += float(row[3])
+                sec = max(sec, float(row[2]))  # the ranks run concurrently: the step takes as long as the slowest
+            if it >= warmup:
+                tot_inter += inter
+                tot_sec += sec
+    sample = (f"{nproc} concurrent single-thread sn3d_ref processes x {npk} packets, timestep {BENCH_TS} of the workload "
+              f"run, update_packets call only (std::chrono in oracle/refglue/hook.cc), {steps} step(s)")
+    return tot_inter, tot_sec, sample
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--packets", type=int, default=1000000, help="packets per GPU")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-baseline", default="auto", choices=["auto", "off"])
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        st, cs, pre, wname = load_workload()
+        cores = host_cores()
+        res = run_reference(cores, max(1, a.steps), min(a.warmup, 1))
+        if res is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/classic/sn3d_ref or its checkpoint is "
+                              "missing (built from /root/reference by `make -C oracle ref`)"}))
+            return 0
+        inter, sec, sample = res
+        v = inter / sec
+        line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": 1e3 * sec / max(1, a.steps), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
+                "config": {"workload": wname, "packets_per_rank": int(pre.size), "ranks": cores},
+                "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+                "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from artis_b200.transport import Transport
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    st, cs, pre, wname = load_workload()
+    P = a.packets
+    T = Transport()
+    T.init(st, device=local_rank, rank=rank, nranks=world)
+    T.upload_cellstate(cs)
+    precompute_ms = T.last_timings()[3]
+    # the contiguous FP64 estimator block as a torch tensor (for the NCCL all-reduce that replaces
+    # mpi_reduce_estimators, sn3d.cc:316-384)
+    ptr, ndoubles = T.estimator_block()
+
+    class _Blk:
+        __cuda_array_interface__ = {"shape": (ndoubles,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+    est_t = torch.as_tensor(_Blk(), device=torch.device("cuda", local_rank))
+    # pinned host staging for the end-to-end leg
+    nbytes = P * 304
+    pinned = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    from artis_b200 import abi
+    host_pk = pinned.numpy().view(abi.PACKET_DTYPE)
+    est_host = torch.empty(ndoubles, dtype=torch.float64, pin_memory=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step(step, timed):
+        """device-resident step: returns (device ms of transport [+ all-reduce], interactions of this rank)"""
+        pk = replicate(pre, P, rank, step)
+        T.packets_upload(pk)  # untimed: inputs are resident in HBM when the timed region starts
+        T.zero_estimators()
+        barrier()
+        T.transport_resident()
+        ms = T.last_timings()[0]
+        if world > 1:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            dist.all_reduce(est_t)
+            e1.record()
+            e1.synchronize()
+            ms += e0.elapsed_time(e1)
+        return ms
+
+    for w in range(a.warmup):
+        one_step(1000 + w, False)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = T.launch_count()
+    tot_ms = 0.0
+    ctr_sum = np.zeros(64, dtype=np.int64)
+    kernel_ms = 0.0
+    for s in range(a.steps):
+        ms = one_step(s, True)
+        kernel_ms += T.last_timings()[2]
+        c = T.download_estimators()["counters"]
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        tot_ms += ms
+        ctr_sum += c
+    launches = T.launch_count() - launches0
+    inter_rank = float(ctr_sum[45])
+    alg_bytes = float(algorithmic_bytes(ctr_sum))
+    if world > 1:
+        t = torch.tensor([inter_rank], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        inter_all = float(t.item())
+    else:
+        inter_all = inter_rank
+    value = inter_all / (tot_ms * 1e-3)
+
+    # end-to-end through the C ABI with host buffers
+    e2e_sec, e2e_inter = 0.0, 0.0
+    for s in range(max(1, min(a.steps, 3)) + 1):
+        host_pk[:] = replicate(pre, P, rank, 2000 + s)
+        T.zero_estimators()
+        barrier()
+        t0 = time.perf_counter()
+        T.update_packets(host_pk)                      # H2D packets, all passes, D2H packets
+        if world > 1:
+            dist.all_reduce(est_t)
+        est_host.copy_(est_t, non_blocking=False)      # D2H of the step's result (the estimator block)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        if s > 0:  # first one is warm-up of the pinned path
+            e2e_sec += dt
+            e2e_inter += float(host_pk["interactions"].sum())
+    if world > 1:
+        t = torch.tensor([e2e_inter], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        e2e_inter = float(t.item())
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6537.6))
+        achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": tot_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": wname, "packets_per_gpu": P, "parallelism": f"packets sharded x{world}, grid and "
+                           "atomic data replicated, one estimator all-reduce per step",
+                           "l2": "per-step working set (304 B x packets + per-cell tables) exceeds the 126 MB L2",
+                           "s_per_timestep": tot_ms / a.steps * 1e-3, "cell_precompute_ms": precompute_ms,
+                           "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps,
+                           "events_per_s": float(ctr_sum[49]) * world / (tot_ms * 1e-3)},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": None,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6537.6",
+                             "kernel": "k_transport", "algorithmic_bytes_per_step": alg_bytes / a.steps},
+                "e2e": {"value": e2e_inter / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+                        "d2h_bytes_per_step": nbytes + ndoubles * 8},
+                "gpu_launches": int(launches), "clocks": sampler.summary()}
+        if world == 1 and a.cpu_baseline != "off":
+            res = run_reference(1, 1, 0)
+            if res is not None:
+                inter, sec, sample = res
+                line["cpu_baseline"] = {"value": inter / sec, "unit": UNIT, "cores": 1, "kind": "reference",
+                                        "sample": sample}
+            else:
+                line["cpu_baseline"] = cpu_port_baseline(st, cs, pre)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def cpu_port_baseline(st, cs, pre):
+    """fallback when oracle/_ref did not travel: the oracle's CPU restatement on one core"""
+    from artis_b200.transport import Transport
+    lib = os.path.join(REPO, "oracle", "libartis_oracle.so")
+    if not os.path.exists(lib):
+        subprocess.run(["make", "-C", os.path.join(REPO, "oracle"), "restatement"], check=True,
+                       stdout=subprocess.DEVNULL)
+    O = Transport(lib)
+    O.init(st)
+    O.upload_cellstate(cs)
+    O.zero_estimators()
+    pk = pre.copy()
+    t0 = time.perf_counter()
+    O.update_packets(pk)
+    dt = time.perf_counter() - t0
+    return {"value": float(pk["interactions"].sum()) / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"oracle restatement, {pk.size} packets, one step"}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -6,6 +6,7 @@
 //                                  before and after the reference transport, the reference's estimators)
 //   ARTIS_HOOK_DIR=<dir>           where to write (default ".")
 //   ARTIS_HOOK_STOP_AFTER_TS=N     exit(0) after timestep N's transport (bounds the run)
+//   ARTIS_HOOK_PROBES=N            with snapshots: also store N deterministic probes (inputs + reference outputs)
 //   ARTIS_HOOK_SKIP_POST=1         with snapshots: do not store the (large) post-transport packet array
 // Always appends one line per timestep to <dir>/hook_timing.txt:
 //   nts npkts seconds interactions cellcrossings escounter nesc threads
@@ -20,6 +21,13 @@
 #include "flatten.h"
 #include "packet.h"
 #include "update_packets.h"
+#include "boundary.h"
+#include "ltepop.h"
+#include "photo_electric.h"
+#include "rpkt.h"
+#include "update_grid.h"
+#include "vectors.h"
+#include <vector>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -83,6 +91,166 @@ std::set<int> parse_list(const char *env) {
   return out;
 }
 
+
+// ---- deterministic probes: the reference's own functions called on packet states built
+// from packets.pre; inputs and outputs go into the snapshot so that the CUDA probes (artis_gpu_probe_*) can be
+// compared entry by entry. Runs before the reference transport; touches only the per-thread caches.
+double hash01(unsigned long long x) {
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdULL;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ULL;
+  x ^= x >> 33;
+  return (double)(x >> 11) * (1.0 / 9007199254740992.0);
+}
+
+void write_probes(FILE *f, const struct packet *packets, const int npkts, const int nts, const int nprobe_max) {
+  std::vector<struct packet> q;
+  std::vector<struct packet> gq;
+  const double t2 = globals::time_step[nts].start + globals::time_step[nts].width;
+  const int stride = (nprobe_max > 0 && npkts > nprobe_max) ? (npkts + nprobe_max - 1) / nprobe_max : 1;  // sample every cell
+  for (int n = 0; n < npkts && (int)q.size() < nprobe_max; n += stride) {
+    struct packet p = packets[n];
+    if (p.type == TYPE_ESCAPE || !(p.prop_time < t2)) continue;
+    const unsigned long long h = 1000003ULL * (unsigned long long)p.number + 17ULL * nts;
+    if (p.type != TYPE_RPKT) {
+      // pellet / gamma / k-packet position re-used for a synthetic r-packet
+      const double mu = -1 + 2 * hash01(h + 1), phi = 2 * 3.141592653589793 * hash01(h + 2);
+      const double st = sqrt(1 - mu * mu);
+      p.dir[0] = st * cos(phi);
+      p.dir[1] = st * sin(phi);
+      p.dir[2] = mu;
+      p.nu_rf = globals::nu_min_r * pow(globals::nu_max_r / globals::nu_min_r, hash01(h + 3));
+      p.e_rf = p.e_cmf;
+      p.type = TYPE_RPKT;
+      p.last_cross = NONE;
+      p.next_trans = 0;
+      const double dopplerfactor = doppler_packet_nucmf_on_nurf(&p);
+      p.nu_cmf = p.nu_rf * dopplerfactor;
+      p.e_cmf = p.e_rf * dopplerfactor;
+      // the same position as a gamma packet of 0.05 - 3 MeV
+      struct packet g = p;
+      g.type = TYPE_GAMMA;
+      g.nu_rf = (0.05 * pow(60., hash01(h + 4))) * MEV / H;
+      g.nu_cmf = g.nu_rf * dopplerfactor;
+      gq.push_back(g);
+    }
+    q.push_back(p);
+  }
+  const int N = q.size();
+  std::vector<double> sdist(N), kappa(5 * (size_t)N, 0.), tau(N), abortd(N), edist(N, 0.);
+  std::vector<int> snext(N), lcross(N), closest(N), closest0(N), valid(N, 0), etype(N, -1), ntout(N, 0), ma(4 * (size_t)N, 0);
+  for (int i = 0; i < N; i++) {
+    struct packet p = q[i];
+    int sn = 0;
+    sdist[i] = boundary_cross(&p, &sn);
+    snext[i] = sn;
+    lcross[i] = p.last_cross;
+    closest[i] = closest_transition(q[i].nu_cmf, q[i].next_trans);
+    closest0[i] = closest_transition(q[i].nu_cmf, 0);
+    const int mgi = grid::get_cell_modelgridindex(q[i].where);
+    tau[i] = -log(1. - hash01(7919ULL * i + 3));
+    const double tdist = (t2 - q[i].prop_time) * CLIGHT_PROP;
+    abortd[i] = (sdist[i] > 0 && sdist[i] < tdist) ? sdist[i] : tdist;
+    if (mgi != grid::get_npts_model() && grid::modelgrid[mgi].thick != 1) {
+      valid[i] = 1;
+      cellhistory_reset(mgi, false);
+      globals::kappa_rpkt_cont[tid].recalculate_required = true;
+      struct packet p2 = q[i];
+      calculate_kappa_rpkt_cont(&p2, &globals::kappa_rpkt_cont[tid]);
+      kappa[5 * i + 0] = globals::kappa_rpkt_cont[tid].total;
+      kappa[5 * i + 1] = globals::kappa_rpkt_cont[tid].es;
+      kappa[5 * i + 2] = globals::kappa_rpkt_cont[tid].ff;
+      kappa[5 * i + 3] = globals::kappa_rpkt_cont[tid].bf;
+      kappa[5 * i + 4] = globals::kappa_rpkt_cont[tid].ffheating;
+      struct packet p3 = q[i];
+      int et = -1;
+      edist[i] = refglue::probe_get_event(mgi, &p3, &et, tau[i], abortd[i]);
+      etype[i] = (et == RPKT_EVENTTYPE_BB) ? 1 : (et == RPKT_EVENTTYPE_CONT ? 2 : -1);
+      ntout[i] = p3.next_trans;
+      if (etype[i] == 1) {
+        ma[4 * i + 0] = p3.mastate.element;
+        ma[4 * i + 1] = p3.mastate.ion;
+        ma[4 * i + 2] = p3.mastate.level;
+        ma[4 * i + 3] = p3.mastate.activatingline;
+      }
+    }
+  }
+  write_record(f, "probe.packets", "pkt", q.data(), N, sizeof(struct packet));
+  write_record(f, "probe.sdist", "f8", sdist.data(), N, 8);
+  write_record(f, "probe.snext", "i4", snext.data(), N, 4);
+  write_record(f, "probe.last_cross", "i4", lcross.data(), N, 4);
+  write_record(f, "probe.closest", "i4", closest.data(), N, 4);
+  write_record(f, "probe.closest0", "i4", closest0.data(), N, 4);
+  write_record(f, "probe.valid", "i4", valid.data(), N, 4);
+  write_record(f, "probe.kappa", "f8", kappa.data(), 5 * (size_t)N, 8);
+  write_record(f, "probe.tau_rnd", "f8", tau.data(), N, 8);
+  write_record(f, "probe.abort_dist", "f8", abortd.data(), N, 8);
+  write_record(f, "probe.edist", "f8", edist.data(), N, 8);
+  write_record(f, "probe.eventtype", "i4", etype.data(), N, 4);
+  write_record(f, "probe.next_trans_out", "i4", ntout.data(), N, 4);
+  write_record(f, "probe.mastate", "i4", ma.data(), 4 * (size_t)N, 4);
+  // gamma opacities
+  const int G = gq.size();
+  std::vector<double> gk(3 * (size_t)G);
+  for (int i = 0; i < G; i++) {
+    gk[3 * i + 0] = refglue::probe_sig_comp(&gq[i]);
+    gk[3 * i + 1] = sig_photo_electric(&gq[i]);
+    gk[3 * i + 2] = sig_pair_prod(&gq[i]);
+  }
+  write_record(f, "probe.gpackets", "pkt", gq.data(), G, sizeof(struct packet));
+  write_record(f, "probe.gkappa", "f8", gk.data(), 3 * (size_t)G, 8);
+  // level populations, macro-atom process rates and per-ion cooling sums for every level / ion of a few cells
+  std::vector<int> cells;
+  for (int m = 0; m < grid::get_npts_model() && cells.size() < 4; m++)
+    if (grid::get_numassociatedcells(m) > 0 && grid::modelgrid[m].thick != 1) cells.push_back(m);
+  {
+    int last = -1;
+    for (int m = grid::get_npts_model() - 1; m >= 0; m--)
+      if (grid::get_numassociatedcells(m) > 0 && grid::modelgrid[m].thick != 1) {
+        last = m;
+        break;
+      }
+    if (last >= 0 && (cells.empty() || cells.back() != last)) cells.push_back(last);
+  }
+  std::vector<int> lm, le, li, ll, cm, ce, ci;
+  std::vector<double> pop, rates, cool;
+  const double t_mid = globals::time_step[nts].mid;
+  for (int m : cells) {
+    cellhistory_reset(m, true);
+    for (int el = 0; el < get_nelements(); el++)
+      for (int ion = 0; ion < get_nions(el); ion++) {
+        cm.push_back(m);
+        ce.push_back(el);
+        ci.push_back(ion);
+        cool.push_back(refglue::probe_cooling_ion(m, el, ion));
+        for (int lev = 0; lev < get_nlevels(el, ion); lev++) {
+          lm.push_back(m);
+          le.push_back(el);
+          li.push_back(ion);
+          ll.push_back(lev);
+          pop.push_back(get_levelpop(m, el, ion, lev));
+          double r9[9];
+          refglue::probe_macroatom_rates(m, el, ion, lev, t_mid, r9);
+          rates.insert(rates.end(), r9, r9 + 9);
+        }
+      }
+  }
+  write_record(f, "probe.lev_mgi", "i4", lm.data(), lm.size(), 4);
+  write_record(f, "probe.lev_element", "i4", le.data(), le.size(), 4);
+  write_record(f, "probe.lev_ion", "i4", li.data(), li.size(), 4);
+  write_record(f, "probe.lev_level", "i4", ll.data(), ll.size(), 4);
+  write_record(f, "probe.levelpop", "f8", pop.data(), pop.size(), 8);
+  write_record(f, "probe.ma_rates", "f8", rates.data(), rates.size(), 8);
+  write_record(f, "probe.cool_mgi", "i4", cm.data(), cm.size(), 4);
+  write_record(f, "probe.cool_element", "i4", ce.data(), ce.size(), 4);
+  write_record(f, "probe.cool_ion", "i4", ci.data(), ci.size(), 4);
+  write_record(f, "probe.cool_total", "f8", cool.data(), cool.size(), 8);
+  // leave the per-thread caches as update_packets expects to find them
+  globals::cellhistory[tid].cellnumber = -99;
+  globals::kappa_rpkt_cont[tid].recalculate_required = true;
+}
+
 }  // namespace
 
 void update_packets(const int my_rank, const int nts, struct packet *packets) {
@@ -110,6 +278,7 @@ void update_packets(const int my_rank, const int nts, struct packet *packets) {
     const int meta[4] = {my_rank, globals::nprocs, nts, npkts};
     write_record(f, "meta.rank_nprocs_nts_npkts", "i4", meta, 4, sizeof(int));
     write_record(f, "packets.pre", "pkt", packets, npkts, sizeof(struct packet));
+    if (getenv("ARTIS_HOOK_PROBES")) write_probes(f, packets, npkts, nts, atoi(getenv("ARTIS_HOOK_PROBES")));
   }
 
   const long long cross0 = stats::get_counter(stats::COUNTER_CELLCROSSINGS);

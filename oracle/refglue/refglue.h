@@ -9,6 +9,11 @@ double *radfield_nuJ(void);  // radfield.cc:108
 void coolinglist_entry(int i, int *type, int *level, int *upperlevel);  // kpkt.cc:27-35
 int gamma_nlines(int nucindex);                                         // gammapkt.cc:24-31
 void gamma_line(int nucindex, int k, double *energy, double *probability);
+// probes of file-static functions on the path (wrap_rpkt.cc, wrap_macroatom.cc, wrap_kpkt.cc, wrap_gammapkt.cc)
+double probe_get_event(int modelgridindex, struct packet *pkt_ptr, int *rpkt_eventtype, double tau_rnd, double abort_dist);
+void probe_macroatom_rates(int modelgridindex, int element, int ion, int level, double t_mid, double *rates9);
+double probe_cooling_ion(int modelgridindex, int element, int ion);
+double probe_sig_comp(const struct packet *pkt_ptr);
 }  // namespace refglue
 // the reference's own transport entry point, renamed at compile time in wrap_update_packets.cc
 void ref_update_packets(const int my_rank, const int nts, struct packet *packets);

@@ -8,3 +8,6 @@ void gamma_line(int nucindex, int k, double *energy, double *probability) {
   *probability = gammapkt::gamma_spectra[nucindex].probability[k];
 }
 }  // namespace refglue
+namespace refglue {
+double probe_sig_comp(const struct packet *pkt_ptr) { return gammapkt::sig_comp(pkt_ptr); }  // gammapkt.cc:335
+}  // namespace refglue

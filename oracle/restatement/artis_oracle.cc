@@ -1,9 +1,20 @@
-// hostsim.cc -- TEST INFRASTRUCTURE / DEBUGGING AID. Never shipped, never imported by artis_b200.
+// artis_oracle.cc -- THE ORACLE'S CPU RESTATEMENT. TEST INFRASTRUCTURE: never shipped, never imported by artis_b200.
 //
-// Compiles the device headers of artis_b200/csrc as plain host C++ and runs every kernel body in a serial loop, behind
-// the same C ABI. This exists because the development container has no GPU: it lets the physics restatement be
-// debugged against the reference's snapshots with gdb/ASan before GPU time is spent. The product library
-// (artis_b200/csrc/transport.cu -> libartis_gpu.so) has no CPU path: without a CUDA device every entry point fails.
+// Builds oracle/libartis_oracle.so (`make -C oracle restatement`): the restatement of the reference's update_packets
+// path (artis_b200/csrc/*.cuh -- every function there cites the reference file:line it follows) compiled as plain
+// host C++ and run one packet after another, behind the same C ABI as the product. Only tests/, bench.py's
+// cpu_baseline leg and __graft_entry__.smoke() load it, and only as the checker.
+//
+// Pinning: compiled with the flags of the reference build (oracle/Makefile: -O3 -march=x86-64-v3) this restatement
+// reproduces the outputs of the reference's own boundary_cross, closest_transition, calculate_kappa_rpkt_cont,
+// get_event, get_levelpop, calculate_macroatom_transitionrates, calculate_kpkt_rates_ion, sig_comp,
+// sig_photo_electric and sig_pair_prod BIT FOR BIT (<= 4e-16 relative for the macro-atom rates) on the probe sets
+// stored in tests/golden/*.npz, which were produced by the unmodified reference sources built against the GSL shim
+// (oracle/_ref, oracle/refglue/hook.cc). The full Monte Carlo step is pinned statistically against ensembles of
+// reference runs (tests/statlib.py). See tests/test_oracle.py.
+//
+// The product library (artis_b200/csrc/transport.cu -> artis_b200/libartis_gpu.so) has no CPU path: without a CUDA
+// device every entry point fails with ARTIS_ERR_NODEVICE.
 #include <chrono>
 #include <cstdlib>
 #include <cstring>

@@ -41,12 +41,15 @@ def main():
     ap.add_argument("out")
     ap.add_argument("--seeds", type=int, default=24)
     ap.add_argument("--mode", default="classic_small")
+    ap.add_argument("--probes", type=int, default=1500)
     a = ap.parse_args()
     exe = os.path.join(REPO, "oracle", "_ref", a.mode, "sn3d_ref")
     rows, names, inputs = [], None, None
     for k in range(a.seeds):
         set_seed(a.rundir, 700001 + 7919 * k)
         env = dict(os.environ, ARTIS_HOOK_SNAPSHOT_TS=str(a.nts), ARTIS_HOOK_DIR=".", ARTIS_HOOK_STOP_AFTER_TS=str(a.nts))
+        if k == 0:
+            env["ARTIS_HOOK_PROBES"] = str(a.probes)  # deterministic sub-kernel probes: inputs + the reference's outputs
         subprocess.run([exe], cwd=a.rundir, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=True)
         s = snapshot.load(os.path.join(a.rundir, f"snap_ts{a.nts}.bin"))
         st, cs, est = snapshot.static_tables(s), snapshot.cell_state(s), snapshot.estimators(s)
@@ -54,13 +57,14 @@ def main():
         if names is None:
             names = list(d)
             inputs = {k2: np.array(v) for k2, v in s.items()
-                      if k2.startswith(("static.", "cell.", "meta.")) or k2 == "packets.pre"}
+                      if k2.startswith(("static.", "cell.", "meta.", "probe.")) or k2 == "packets.pre"}
         else:
             assert np.array_equal(inputs["packets.pre"], s["packets.pre"]), "restart did not reproduce the start state"
         rows.append([d[nm] for nm in names])
         print(k, "interactions", d["interactions"], flush=True)
     # packets.pre is a structured array: store its raw bytes
-    inputs["packets.pre"] = np.frombuffer(inputs["packets.pre"].tobytes(), dtype=np.uint8)
+    for key in ("packets.pre", "probe.packets", "probe.gpackets"):
+        inputs[key] = np.frombuffer(inputs[key].tobytes(), dtype=np.uint8)
     np.savez_compressed(a.out, ref_rows=np.array(rows), ref_names=np.array(names), nts=a.nts, **inputs)
     print("wrote", a.out, os.path.getsize(a.out) / 1e6, "MB")
 

@@ -21,10 +21,14 @@ def load_fixture(name):
         if k.startswith(("static.", "cell.", "meta.")):
             snap[k] = z[k]
     snap["packets.pre"] = np.frombuffer(z["packets.pre"].tobytes(), dtype=abi.PACKET_DTYPE).copy()
+    probe = {k[6:]: z[k] for k in z.files if k.startswith("probe.")}
+    for key in ("packets", "gpackets"):
+        if key in probe:
+            probe[key] = np.frombuffer(probe[key].tobytes(), dtype=abi.PACKET_DTYPE).copy()
     static = {f[2]: (snap["static." + f[2]][0].item() if f[0] == "S" else snap["static." + f[2]]) for f in abi.STATIC_FIELDS}
     cell = {f[2]: (snap["cell." + f[2]][0].item() if f[0] == "S" else snap["cell." + f[2]]) for f in abi.CELL_FIELDS}
     return {"static": static, "cell": cell, "pre": snap["packets.pre"], "ref_rows": z["ref_rows"],
-            "names": [str(x) for x in z["ref_names"]], "nts": int(z["nts"])}
+            "names": [str(x) for x in z["ref_names"]], "nts": int(z["nts"]), "probe": probe}
 
 
 def run_ensemble(T, fx, nseeds, seed0=424242):
