@@ -288,19 +288,23 @@ ARTIS_DEV void scatter_dir(Rng &r, const double dir_in[3], const double cos_thet
 ARTIS_DEV void est_add(double *addr, double v) { atomicAdd(addr, v); }
 ARTIS_DEV void ctr_add(long long *addr, long long v) { atomicAdd((unsigned long long *)addr, (unsigned long long)v); }
 ARTIS_DEV void int_add(int *addr, int v) { atomicAdd(addr, v); }
+ARTIS_DEV int int_fetch_add(int *addr, int v) { return atomicAdd(addr, v); }
 #else
 ARTIS_DEV void est_add(double *addr, double v) { *addr += v; }
 ARTIS_DEV void ctr_add(long long *addr, long long v) { *addr += v; }
 ARTIS_DEV void int_add(int *addr, int v) { *addr += v; }
+ARTIS_DEV int int_fetch_add(int *addr, int v) {
+  const int old = *addr;
+  *addr += v;
+  return old;
+}
 #endif
 
 // per-thread work counters, flushed once per thread at the end of a pass (keeps atomics off the hot loops)
-struct Work {
-  long long stats[34];  // stats::eventcounters increments are rare enough to go straight to global; unused here
-};
 struct Tally {
   int rpkt_steps, lines_scanned, lines_tau, bf_evaluated, estim_atomics, gamma_steps, ma_jumps, ma_trans_scanned,
       kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates;
+  int stats[34];  // stats::eventcounters increments of this thread (stats.h:48-84), flushed once per thread and pass
 };
 ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   long long *k = c.es.counters;
@@ -318,8 +322,11 @@ ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   if (t.soft_repairs) ctr_add(&k[ARTIS_CTR_SOFT_REPAIRS], t.soft_repairs);
   if (t.kappa_evals) ctr_add(&k[ARTIS_CTR_KAPPA_EVALS], t.kappa_evals);
   if (t.packet_updates) ctr_add(&k[ARTIS_CTR_PACKET_UPDATES], t.packet_updates);
+  for (int i = 0; i < 34; i++)
+    if (t.stats[i]) ctr_add(&k[i], t.stats[i]);
 }
-ARTIS_DEV void stat_inc(const Ctx &c, int counter) { ctr_add(&c.es.counters[counter], 1); }
+// stats::increment (stats.cc:151): per-thread tally instead of one global atomic per event
+ARTIS_DEV void stat_inc(Tally &t, int counter) { t.stats[counter]++; }
 ARTIS_DEV void fatal(const Ctx &c, int code) {
   if (c.error_flag) *c.error_flag = code;
 }

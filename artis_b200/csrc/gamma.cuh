@@ -120,7 +120,7 @@ ARTIS_DEV double thomson_angle(const Ctx &c, Rng &rng) {
   return mu;
 }
 // gammapkt.cc:421-531
-ARTIS_DEV void compton_scatter(const Ctx &c, ArtisPacket &p, Rng &rng) {
+ARTIS_DEV void compton_scatter(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   double f;
   const double xx = H * p.nu_cmf / ME / CLIGHT / CLIGHT;
   bool stay_gamma;
@@ -164,18 +164,18 @@ ARTIS_DEV void compton_scatter(const Ctx &c, ArtisPacket &p, Rng &rng) {
   } else {
     p.type = ARTIS_TYPE_NTLEPTON;
     p.absorptiontype = -3;
-    stat_inc(c, COUNTER_NT_STAT_FROM_GAMMA);
+    stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
   }
 }
 // photo_electric.cc:116-164
-ARTIS_DEV void pair_prod(const Ctx &c, ArtisPacket &p, Rng &rng) {
+ARTIS_DEV void pair_prod(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   const double prob_gamma = 1.022 * MEV / (H * p.nu_cmf);
   if (prob_gamma < 0) fatal(c, 405);
   const double zrand = rng_uniform(rng);
   if (zrand > prob_gamma) {
     p.type = ARTIS_TYPE_NTLEPTON;
     p.absorptiontype = -5;
-    stat_inc(c, COUNTER_NT_STAT_FROM_GAMMA);
+    stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
   } else {
     p.nu_cmf = 0.511 * MEV / H;
     double dir_cmf[3];
@@ -234,7 +234,7 @@ ARTIS_DEV void do_gamma(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng,
     if (est) rlc_emiss_gamma(c, p, mgi, sdist, tl);
     p.prop_time += sdist / 2. / CLIGHT_PROP;
     move_pkt(c, p, sdist / 2.);
-    if (snext != p.where) change_cell(c, p, snext);
+    if (snext != p.where) change_cell(c, p, snext, tl);
   } else if ((tdist < sdist) && (tdist < edist)) {
     p.prop_time += tdist / 2. / CLIGHT_PROP;
     move_pkt(c, p, tdist / 2.);
@@ -249,13 +249,13 @@ ARTIS_DEV void do_gamma(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng,
     move_pkt(c, p, edist / 2.);
     const double zrand = rng_uniform(rng);
     if (kap_compton > (zrand * kap_tot)) {
-      compton_scatter(c, p, rng);
+      compton_scatter(c, p, rng, tl);
     } else if ((kap_compton + kap_photo_electric) > (zrand * kap_tot)) {
       p.type = ARTIS_TYPE_NTLEPTON;
       p.absorptiontype = -4;
-      stat_inc(c, COUNTER_NT_STAT_FROM_GAMMA);
+      stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
     } else if ((kap_compton + kap_photo_electric + kap_pair_prod) > (zrand * kap_tot)) {
-      pair_prod(c, p, rng);
+      pair_prod(c, p, rng, tl);
     } else {
       fatal(c, 413);
       p.type = ARTIS_TYPE_ESCAPE;
@@ -309,7 +309,7 @@ ARTIS_DEV void pellet_gamma_decay(const Ctx &c, ArtisPacket &p, Rng &rng) {
 }
 
 // update_packets.cc:71-135 update_pellet
-ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng) {
+ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, Tally &tl) {
   const double ts = p.prop_time;
   const double tdecay = p.tdecay;
   double *tsc = c.es.ts_scalars;
@@ -344,7 +344,7 @@ ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng 
     p.e_cmf *= tdecay / c.st.tmin;
     p.type = ARTIS_TYPE_PRE_KPKT;
     p.absorptiontype = -7;
-    stat_inc(c, COUNTER_K_STAT_FROM_EARLIERDECAY);
+    stat_inc(tl, COUNTER_K_STAT_FROM_EARLIERDECAY);
     p.prop_time = c.st.tmin;
   } else {
     fatal(c, 430);
@@ -391,7 +391,7 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
   tl.packet_updates++;
   switch (p.type) {
     case ARTIS_TYPE_RADIOACTIVE_PELLET:
-      update_pellet(c, p, t2, rng);
+      update_pellet(c, p, t2, rng, tl);
       break;
     case ARTIS_TYPE_GAMMA:
       do_gamma(c, p, t2, rng, tl);
@@ -405,7 +405,7 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
       do_nonthermal_predeposit(c, p, t2, rng);
       break;
     case ARTIS_TYPE_NTLEPTON:
-      do_ntlepton(c, p);
+      do_ntlepton(c, p, tl);
       break;
     case ARTIS_TYPE_KPKT:
     case ARTIS_TYPE_PRE_KPKT:

@@ -28,34 +28,103 @@ ARTIS_DEV void body_cool(const Ctx &c, const long long idx) {
   if (cell_uses_tables(c, mgi)) build_cooling_ion(c, mgi, (int)(idx % c.st.includedions));
 }
 
-// ---- transport: one thread follows one packet (first correct path) -------------------------------
-// Runs do_packet until the packet escapes, reaches t2, or has used `max_events` calls in this pass; packets that stop
-// for the last reason are counted in *unfinished and picked up by the next pass (update_packets.cc:249-311).
-ARTIS_DEV void body_transport(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const int idx, const int pass,
-                              const long long max_events, int *unfinished) {
-  ArtisPacket p = pkts[idx];
-  if (pass == 0) {  // update_packets.cc:282-285
+// ---- K0 bucket_packets: replaces the std::sort of update_packets.cc:204-256 --------------------------------
+// Counting sort of the ACTIVE packets by (model cell, packet kind). Dense inner cells come first, like the reference's
+// comparator (density descending == model cell ascending for the 1D models; for 3D it is only a locality key), so the
+// longest histories start first; packets that are escaped or already at t2 are left out of the queue.
+ARTIS_DEV int bucket_key(const Ctx &c, const ArtisPacket &p) {
+  int kind;
+  switch (p.type) {
+    case ARTIS_TYPE_KPKT:
+    case ARTIS_TYPE_MA:
+    case ARTIS_TYPE_NTLEPTON:
+    case ARTIS_TYPE_PRE_KPKT:
+    case ARTIS_TYPE_GAMMA_KPKT:
+      kind = 0;
+      break;
+    case ARTIS_TYPE_RPKT:
+      kind = 1;
+      break;
+    case ARTIS_TYPE_GAMMA:
+      kind = 2;
+      break;
+    default:
+      kind = 3;
+  }
+  return cell_mgi(c, p.where) * 4 + kind;
+}
+ARTIS_DEV bool packet_active(const Ctx &c, const ArtisPacket &p) { return p.type != ARTIS_TYPE_ESCAPE && p.prop_time < c.t2; }
+ARTIS_DEV void body_bucket_hist(const Ctx &c, ArtisPacket *pkts, const int idx, const int pass, int *counts) {
+  ArtisPacket &p = pkts[idx];
+  if (pass == 0) {  // update_packets.cc:282-285, for every packet including the escaped ones
     p.interactions = 0;
     p.scat_count = 0;
   }
-  const double t2 = c.t2;
-  if (p.type == ARTIS_TYPE_ESCAPE || !(p.prop_time < t2)) {
-    if (pass == 0) pkts[idx] = p;
-    return;
+  if (packet_active(c, p)) int_add(&counts[bucket_key(c, p)], 1);
+}
+ARTIS_DEV void body_bucket_scatter(const Ctx &c, const ArtisPacket *pkts, const int idx, int *offsets, int *order) {
+  const ArtisPacket &p = pkts[idx];
+  if (packet_active(c, p)) order[int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
+}
+// exclusive prefix sum over the bucket counts (one thread; the bucket count is small next to the packet count)
+ARTIS_DEV void body_bucket_scan(int *counts, const int nbuckets, int *n_active) {
+  int run = 0;
+  for (int b = 0; b < nbuckets; b++) {
+    const int cnt = counts[b];
+    counts[b] = run;
+    run += cnt;
   }
-  Rng rng = rng_init(c, p.number, pass == 0 ? 0ull : rngctr[idx]);
+  *n_active = run;
+}
+
+// ---- transport ------------------------------------------------------------------------------
+// Persistent threads: every lane pulls the next packet from a global queue (`order`, packets bucketed by model cell;
+// queue head = one atomic counter) as soon as its current packet has escaped, reached t2 or used up `max_events`
+// events in this pass. One loop iteration = one event of one packet (do_packet: one r-packet step, one macro-atom
+// jump, one k-packet / gamma / pellet event), so lanes holding the same kind of packet execute it in lock step and
+// no lane idles while another works through a long history. Packets that stop on `max_events` are counted in
+// *unfinished and picked up by the next pass (the passes of update_packets.cc:249-311).
+ARTIS_DEV void body_transport(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const int *order, const int n,
+                              int *queue_head, const int pass, const long long max_events, int *unfinished) {
+  const double t2 = c.t2;
+  Tally tl = {};
   KappaCache k;
   k.valid = false;
-  Tally tl = {};
+  ArtisPacket p;
+  Rng rng = {};
+  int idx = -1;
   long long events = 0;
-  while (p.type != ARTIS_TYPE_ESCAPE && p.prop_time < t2 && events < max_events) {
+  bool have = false;
+  while (true) {
+    if (!have) {
+      const int q = int_fetch_add(queue_head, 1);
+      if (q >= n) break;
+      idx = order ? order[q] : q;
+      p = pkts[idx];
+      if (pass == 0) {  // update_packets.cc:282-285
+        p.interactions = 0;
+        p.scat_count = 0;
+      }
+      if (p.type == ARTIS_TYPE_ESCAPE || !(p.prop_time < t2)) {
+        if (pass == 0) pkts[idx] = p;
+        continue;
+      }
+      rng = rng_init(c, p.number, pass == 0 ? 0ull : rngctr[idx]);
+      k.valid = false;
+      events = 0;
+      have = true;
+    }
     do_packet(c, p, t2, k, rng, tl);
     events++;
+    const bool finished = (p.type == ARTIS_TYPE_ESCAPE) || !(p.prop_time < t2);
+    if (finished || events >= max_events) {
+      rngctr[idx] = rng.ctr;
+      pkts[idx] = p;
+      if (!finished) int_add(unfinished, 1);
+      have = false;
+    }
   }
-  rngctr[idx] = rng.ctr;
-  pkts[idx] = p;
   tally_flush(c, tl);
-  if (p.type != ARTIS_TYPE_ESCAPE && p.prop_time < t2) int_add(unfinished, 1);
 }
 
 // ---- K10 deterministic probes --------------------------------------------------------------------------------

@@ -27,7 +27,7 @@ ARTIS_DEV void do_kpkt_bb(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   if (!isfinite(p.nu_cmf)) fatal(c, 301);
   emitt_rpkt(c, p, rng);
   p.next_trans = 0;
-  stat_inc(c, COUNTER_K_STAT_TO_R_BB);
+  stat_inc(tl, COUNTER_K_STAT_TO_R_BB);
   p.interactions++;
   tl.interactions++;
   p.last_event = 6;
@@ -100,7 +100,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     if (!isfinite(p.nu_cmf)) fatal(c, 304);
     emitt_rpkt(c, p, rng);
     p.next_trans = 0;
-    stat_inc(c, COUNTER_K_STAT_TO_R_FF);
+    stat_inc(tl, COUNTER_K_STAT_TO_R_FF);
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 6;
@@ -113,7 +113,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.nu_cmf = select_continuum_nu(c, ui, gl_lower, upper, T_e, rng);
     emitt_rpkt(c, p, rng);
     p.next_trans = 0;
-    stat_inc(c, COUNTER_K_STAT_TO_R_FB);
+    stat_inc(tl, COUNTER_K_STAT_TO_R_FB);
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 7;
@@ -140,8 +140,8 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.ma_level = c.st.line_upper[lineindex];
     p.ma_activatingline = -99;
     p.type = ARTIS_TYPE_MA;
-    stat_inc(c, COUNTER_MA_STAT_ACTIVATION_COLLEXC);
-    stat_inc(c, COUNTER_K_STAT_TO_MA_COLLEXC);
+    stat_inc(tl, COUNTER_MA_STAT_ACTIVATION_COLLEXC);
+    stat_inc(tl, COUNTER_K_STAT_TO_MA_COLLEXC);
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 8;
@@ -153,8 +153,8 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.ma_level = c.st.cool_upperlevel[i];
     p.ma_activatingline = -99;
     p.type = ARTIS_TYPE_MA;
-    stat_inc(c, COUNTER_MA_STAT_ACTIVATION_COLLION);
-    stat_inc(c, COUNTER_K_STAT_TO_MA_COLLION);
+    stat_inc(tl, COUNTER_MA_STAT_ACTIVATION_COLLION);
+    stat_inc(tl, COUNTER_K_STAT_TO_MA_COLLION);
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 9;
@@ -168,11 +168,11 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
 
 // nonthermal.cc:1877-1978 do_ntlepton with NT_ON && NT_SOLVE_SPENCERFANO false (classic, kilonova_lte): every
 // non-thermal lepton thermalises into a k-packet
-ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p) {
+ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p, Tally &tl) {
   est_add(&c.es.ts_scalars[ARTIS_TS_NT_ENERGY_DEPOSITED], p.e_cmf);
   p.last_event = 22;
   p.type = ARTIS_TYPE_KPKT;
-  stat_inc(c, COUNTER_NT_STAT_TO_KPKT);
+  stat_inc(tl, COUNTER_NT_STAT_TO_KPKT);
 }
 
 }  // namespace artis

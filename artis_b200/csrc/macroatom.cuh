@@ -124,7 +124,10 @@ ARTIS_DEV void mark_emission(ArtisPacket &p) {
   p.nscatterings = 0;
 }
 
-// macroatom.cc:416-901 do_macroatom
+// macroatom.cc:416-901 do_macroatom, ONE iteration of its `while (!end_packet)` loop per call: the macro-atom state
+// (ion, level) lives in the packet's mastate between calls, so that all lanes of a warp that hold an activated
+// macro-atom take their jumps in lock step and the scheduler can interleave packet kinds (the reference keeps the
+// state in locals and never reads mastate again after the chain has started, so nothing observable changes).
 ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   const int mgi = cell_mgi(c, p.where);
   const int tc = tabcell(c, mgi);
@@ -141,7 +144,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   const int activatingline = p.ma_activatingline;
 
   bool end_packet = false;
-  while (!end_packet) {
+  {
     tl.ma_jumps++;
     const double epsilon_current = c.st.lev_epsilon[gl];
     const double *processrates = tab_ma_rates(c, tc, gl);
@@ -185,13 +188,13 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gll];
         const double oldnucmf = p.nu_cmf;
         p.nu_cmf = epsilon_trans / H;
-        if (p.last_event == 1) stat_inc(c, oldnucmf < p.nu_cmf ? COUNTER_UPSCATTER : COUNTER_DOWNSCATTER);
-        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_BB);
+        if (p.last_event == 1) stat_inc(tl, oldnucmf < p.nu_cmf ? COUNTER_UPSCATTER : COUNTER_DOWNSCATTER);
+        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_BB);
         p.interactions += 1;
         tl.interactions++;
         p.last_event = 0;
         emitt_rpkt(c, p, rng);
-        if (linelistindex == activatingline) stat_inc(c, COUNTER_RESONANCESCATTERINGS);
+        if (linelistindex == activatingline) stat_inc(tl, COUNTER_RESONANCESCATTERINGS);
         p.next_trans = linelistindex + 1;
         p.emissiontype = linelistindex;
         mark_emission(p);
@@ -199,7 +202,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         break;
       }
       case MA_COLDEEXC: {
-        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_COLLDEEXC);
+        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_COLLDEEXC);
         p.interactions += 1;
         tl.interactions++;
         p.last_event = 10;
@@ -246,7 +249,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         const int gl_lower = gl0_lower + lower;
         p.nu_cmf = select_continuum_nu(c, ui - 1, gl_lower, level, T_e, rng);
         if (!isfinite(p.nu_cmf)) fatal(c, 225);
-        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_FB);
+        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_FB);
         p.interactions += 1;
         tl.interactions++;
         p.last_event = 2;
@@ -260,7 +263,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         break;
       }
       case MA_COLRECOMB: {
-        stat_inc(c, COUNTER_MA_STAT_DEACTIVATION_COLLRECOMB);
+        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_COLLRECOMB);
         p.interactions += 1;
         tl.interactions++;
         p.last_event = 11;
@@ -273,7 +276,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       case MA_INTERNALDOWNLOWER: {  // macroatom.cc:766-813
         p.interactions += 1;
         tl.interactions++;
-        stat_inc(c, COUNTER_MA_STAT_INTERNALDOWNLOWER);
+        stat_inc(tl, COUNTER_MA_STAT_INTERNALDOWNLOWER);
         const double zrand = rng_uniform(rng);
         const int gl0_lower = c.st.ion_leveloffset[ui - 1];
         const int nlevels = c.st.ion_ionisinglevels[ui - 1];
@@ -316,7 +319,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       case MA_INTERNALUPHIGHER: {  // macroatom.cc:382-414 do_macroatom_ionisation
         p.interactions += 1;
         tl.interactions++;
-        stat_inc(c, COUNTER_MA_STAT_INTERNALUPHIGHER);
+        stat_inc(tl, COUNTER_MA_STAT_INTERNALUPHIGHER);
         const double zrand = rng_uniform(rng);
         const int ntargets = c.st.lev_nphixstargets[gl];
         double rrate = 0.;
@@ -343,6 +346,11 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         p.type = ARTIS_TYPE_KPKT;
         return;
     }
+  }
+  if (!end_packet) {  // internal jump: remember where the macro-atom is
+    p.ma_ion = ui - c.st.el_ionoffset[element];
+    p.ma_level = gl - c.st.ion_leveloffset[ui];
+    return;
   }
   if (p.trueemissiontype < 0) {  // macroatom.cc:894-898
     p.trueemissiontype = p.emissiontype;

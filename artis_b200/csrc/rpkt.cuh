@@ -116,15 +116,15 @@ ARTIS_DEV double boundary_cross(const Ctx &c, P &p, int *snext) {
 }
 
 // boundary.cc:332-357 change_cell
-ARTIS_DEV void change_cell(const Ctx &c, ArtisPacket &p, int snext) {
+ARTIS_DEV void change_cell(const Ctx &c, ArtisPacket &p, int snext, Tally &tl) {
   if (snext == -99) {
     p.escape_type = p.type;
     p.escape_time = (int)p.prop_time;  // int field
     p.type = ARTIS_TYPE_ESCAPE;
-    stat_inc(c, COUNTER_NESC);
+    stat_inc(tl, COUNTER_NESC);
   } else {
     p.where = snext;
-    stat_inc(c, COUNTER_CELLCROSSINGS);
+    stat_inc(tl, COUNTER_CELLCROSSINGS);
   }
 }
 

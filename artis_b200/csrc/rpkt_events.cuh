@@ -268,14 +268,14 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
     tl.interactions++;
     p.nscatterings += 1;
     p.last_event = 12;
-    stat_inc(c, COUNTER_ESCOUNTER);
+    stat_inc(tl, COUNTER_ESCOUNTER);
     escat_rpkt(c, p, rng);
     p.em_pos[0] = p.pos[0];
     p.em_pos[1] = p.pos[1];
     p.em_pos[2] = p.pos[2];
     p.em_time = (int)p.prop_time;
   } else if (zrand * kappa_cont < sigma + kappa_ff) {
-    stat_inc(c, COUNTER_K_STAT_FROM_FF);
+    stat_inc(tl, COUNTER_K_STAT_FROM_FF);
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 5;
@@ -318,7 +318,7 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
     const int ion = c.st.cont_ion[allcontindex];
     const double zrand3 = rng_uniform(rng);
     if (zrand3 < nu_edge / nu) {
-      stat_inc(c, COUNTER_MA_STAT_ACTIVATION_BF);
+      stat_inc(tl, COUNTER_MA_STAT_ACTIVATION_BF);
       p.interactions += 1;
       tl.interactions++;
       p.last_event = 3;
@@ -328,7 +328,7 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
       p.ma_level = c.st.cont_upperlevel[allcontindex];  // == get_phixsupperlevel(element, ion, level, target)
       p.ma_activatingline = -99;
     } else {
-      stat_inc(c, COUNTER_K_STAT_FROM_BF);
+      stat_inc(tl, COUNTER_K_STAT_FROM_BF);
       p.interactions += 1;
       tl.interactions++;
       p.last_event = 4;
@@ -341,7 +341,7 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
 
 // rpkt.cc:449-489
 ARTIS_DEV void rpkt_event_boundbound(const Ctx &c, ArtisPacket &p, Tally &tl) {
-  stat_inc(c, COUNTER_MA_STAT_ACTIVATION_BB);
+  stat_inc(tl, COUNTER_MA_STAT_ACTIVATION_BB);
   p.interactions += 1;
   tl.interactions++;
   p.last_event = 1;
@@ -359,7 +359,7 @@ ARTIS_DEV void rpkt_event_thickcell(const Ctx &c, ArtisPacket &p, Rng &rng, Tall
   tl.interactions++;
   p.nscatterings += 1;
   p.last_event = 12;
-  stat_inc(c, COUNTER_ESCOUNTER);
+  stat_inc(tl, COUNTER_ESCOUNTER);
   emitt_rpkt(c, p, rng);
   p.em_pos[0] = p.pos[0];
   p.em_pos[1] = p.pos[1];
@@ -378,7 +378,7 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
   int snext = 0;
   double sdist = boundary_cross(c, p, &snext);
   if (sdist == 0) {
-    change_cell(c, p, snext);
+    change_cell(c, p, snext, tl);
     return p.type == ARTIS_TYPE_RPKT;
   }
   const double maxsdist = c.st.rmax * p.prop_time / c.st.tmin;
@@ -418,7 +418,7 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
     if (do_rlc) rlc_emiss_rpkt(c, p, sdist, tl);
     move_pkt_withtime(c, p, sdist / 2.);
     if (snext != p.where) {
-      change_cell(c, p, snext);
+      change_cell(c, p, snext, tl);
       mgi = cell_mgi(c, p.where);
     }
     p.scat_count = 0;

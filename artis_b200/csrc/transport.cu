@@ -37,10 +37,18 @@ __global__ void k_cool(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_cool(d_ctx, i);
 }
-__global__ void __launch_bounds__(128) k_transport(ArtisPacket *pkts, unsigned long long *rngctr, int n, int pass,
-                                                   long long max_events, int *unfinished) {
+__global__ void __launch_bounds__(128) k_transport(ArtisPacket *pkts, unsigned long long *rngctr, const int *order, int n,
+                                                   int *queue_head, int pass, long long max_events, int *unfinished) {
+  artis::body_transport(d_ctx, pkts, rngctr, order, n, queue_head, pass, max_events, unfinished);
+}
+__global__ void k_bucket_hist(ArtisPacket *pkts, int n, int pass, int *counts) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    artis::body_transport(d_ctx, pkts, rngctr, i, pass, max_events, unfinished);
+    artis::body_bucket_hist(d_ctx, pkts, i, pass, counts);
+}
+__global__ void k_bucket_scan(int *counts, int nbuckets, int *n_active) { artis::body_bucket_scan(counts, nbuckets, n_active); }
+__global__ void k_bucket_scatter(const ArtisPacket *pkts, int n, int *offsets, int *order) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    artis::body_bucket_scatter(d_ctx, pkts, i, offsets, order);
 }
 __global__ void k_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -79,6 +87,7 @@ __global__ void k_probe_levelpop(const int *a, const int *b, const int *c, const
 cudaStream_t g_stream = nullptr;
 cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 int g_sms = SM_COUNT_B200;
+int g_transport_blocks_per_sm = 4;
 std::string g_async_err;
 
 void note(cudaError_t e, const char *what) {
@@ -102,6 +111,9 @@ bool be_select_device(int device, std::string *why) {
   }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) g_sms = prop.multiProcessorCount;
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport, 128, 0) == cudaSuccess && nb > 0)
+    g_transport_blocks_per_sm = nb;
   if (g_stream == nullptr) {
     note(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking), "cudaStreamCreate");
     note(cudaEventCreate(&g_ev0), "cudaEventCreate");
@@ -161,10 +173,17 @@ void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8),
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
-void be_run_transport(ArtisPacket *p, unsigned long long *r, int n, int pass, long long maxev, int *unf, int block) {
+void be_run_transport(ArtisPacket *p, unsigned long long *r, const int *order, int n, int *qh, int pass, long long maxev,
+                      int *unf, int block) {
   if (n <= 0) return;
   if (block > 128) block = 128;  // __launch_bounds__
-  k_transport<<<grid_for(n, block, 16), block, 0, g_stream>>>(p, r, n, pass, maxev, unf);
+  // persistent grid: every SM gets its full complement of resident blocks (register-limited), the queue does the rest
+  k_transport<<<grid_for(n, block, g_transport_blocks_per_sm), block, 0, g_stream>>>(p, r, order, n, qh, pass, maxev, unf);
+}
+void be_run_bucket(ArtisPacket *p, int n, int pass, int *buckets, int nbuckets, int *order, int *n_active) {
+  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, pass, buckets);
+  k_bucket_scan<<<1, 1, 0, g_stream>>>(buckets, nbuckets, n_active);
+  k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, buckets, order);
 }
 #define PROBE_GRID(n) ((n) + 127) / 128, 128, 0, g_stream
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) { k_probe_boundary<<<PROBE_GRID(n)>>>(p, n, a, b, c); }
