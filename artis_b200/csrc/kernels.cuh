@@ -28,100 +28,98 @@ ARTIS_DEV void body_cool(const Ctx &c, const long long idx) {
   if (cell_uses_tables(c, mgi)) build_cooling_ion(c, mgi, (int)(idx % c.st.includedions));
 }
 
-// ---- K0 bucket_packets: replaces the std::sort of update_packets.cc:204-256 --------------------------------
-// Counting sort of the ACTIVE packets by (model cell, packet kind). Dense inner cells come first, like the reference's
-// comparator (density descending == model cell ascending for the 1D models; for 3D it is only a locality key), so the
-// longest histories start first; packets that are escaped or already at t2 are left out of the queue.
-ARTIS_DEV int bucket_key(const Ctx &c, const ArtisPacket &p) {
-  int kind;
-  switch (p.type) {
+// ---- event-kind wavefront -------------------------------------------------------------
+// Packets are grouped by the KIND of event they need next; each kind has its own queue of packet indices and its own
+// kernel launch, so that a warp only ever executes one kind of event: the cheap table-driven macro-atom / k-packet
+// events are never serialised behind a lane that is doing an r-packet step with a continuum-opacity evaluation and
+// a line sweep (measured on v1/v2: ~1.8 active lanes per instruction, profiles/r1_v1_*, r1_v2_*).
+//   kind 0  macro-atom jumps, k-packets, non-thermal leptons        (macroatom.cc, kpkt.cc, nonthermal.cc:1877)
+//   kind 1  r-packet steps                                          (rpkt.cc:623)
+//   kind 2  gamma-packet steps                                      (gammapkt.cc:533)
+//   kind 3  pellets and non-thermal pre-deposition                  (update_packets.cc:16,71)
+// A lane pulls the next index from its kind's queue, runs do_packet while the packet stays of that kind, then writes
+// it back and appends its index to the queue of the kind it has become (or drops it when it escaped / reached t2).
+constexpr int NKIND = 4;
+ARTIS_DEV int kind_of(const int type) {
+  switch (type) {
     case ARTIS_TYPE_KPKT:
     case ARTIS_TYPE_MA:
     case ARTIS_TYPE_NTLEPTON:
     case ARTIS_TYPE_PRE_KPKT:
     case ARTIS_TYPE_GAMMA_KPKT:
-      kind = 0;
-      break;
+      return 0;
     case ARTIS_TYPE_RPKT:
-      kind = 1;
-      break;
+      return 1;
     case ARTIS_TYPE_GAMMA:
-      kind = 2;
-      break;
+      return 2;
     default:
-      kind = 3;
+      return 3;
   }
-  return cell_mgi(c, p.where) * 4 + kind;
 }
 ARTIS_DEV bool packet_active(const Ctx &c, const ArtisPacket &p) { return p.type != ARTIS_TYPE_ESCAPE && p.prop_time < c.t2; }
-ARTIS_DEV void body_bucket_hist(const Ctx &c, ArtisPacket *pkts, const int idx, const int pass, int *counts) {
+
+struct QueueView {
+  const int *in;        // indices to consume
+  const int *n_in;      // how many
+  int *head;            // consumption cursor (zeroed before the launch)
+  int *out[NKIND];      // queues being produced, one per kind
+  int *n_out[NKIND];    // their sizes
+};
+
+// K0 bucket_packets: counting sort of the active packets by (kind, model cell) into the initial queues; replaces the
+// std::sort of update_packets.cc:204-256 (dense inner cells first, like the reference's comparator for 1D models).
+ARTIS_DEV int bucket_key(const Ctx &c, const ArtisPacket &p) { return kind_of(p.type) * (c.st.npts_model + 1) + cell_mgi(c, p.where); }
+ARTIS_DEV void body_bucket_hist(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const int idx, int *counts) {
   ArtisPacket &p = pkts[idx];
-  if (pass == 0) {  // update_packets.cc:282-285, for every packet including the escaped ones
-    p.interactions = 0;
-    p.scat_count = 0;
-  }
+  p.interactions = 0;  // update_packets.cc:282-285, for every packet including the escaped ones
+  p.scat_count = 0;
+  rngctr[idx] = 0ull;  // each packet's Philox stream restarts with the timestep
   if (packet_active(c, p)) int_add(&counts[bucket_key(c, p)], 1);
 }
-ARTIS_DEV void body_bucket_scatter(const Ctx &c, const ArtisPacket *pkts, const int idx, int *offsets, int *order) {
-  const ArtisPacket &p = pkts[idx];
-  if (packet_active(c, p)) order[int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
-}
-// exclusive prefix sum over the bucket counts (one thread; the bucket count is small next to the packet count)
-ARTIS_DEV void body_bucket_scan(int *counts, const int nbuckets, int *n_active) {
-  int run = 0;
-  for (int b = 0; b < nbuckets; b++) {
-    const int cnt = counts[b];
-    counts[b] = run;
-    run += cnt;
+// exclusive prefix sum over the (kind, cell) counts, one thread; also the size of each kind's queue
+ARTIS_DEV void body_bucket_scan(const Ctx &c, int *counts, int *kind_sizes) {
+  const int per = c.st.npts_model + 1;
+  for (int k = 0; k < NKIND; k++) {
+    int run = 0;
+    for (int b = 0; b < per; b++) {
+      const int cnt = counts[k * per + b];
+      counts[k * per + b] = run;
+      run += cnt;
+    }
+    kind_sizes[k] = run;
   }
-  *n_active = run;
+}
+ARTIS_DEV void body_bucket_scatter(const Ctx &c, const ArtisPacket *pkts, const int idx, int *offsets, int *const *queues) {
+  const ArtisPacket &p = pkts[idx];
+  if (packet_active(c, p)) queues[kind_of(p.type)][int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
 }
 
-// ---- transport ------------------------------------------------------------------------------
-// Persistent threads: every lane pulls the next packet from a global queue (`order`, packets bucketed by model cell;
-// queue head = one atomic counter) as soon as its current packet has escaped, reached t2 or used up `max_events`
-// events in this pass. One loop iteration = one event of one packet (do_packet: one r-packet step, one macro-atom
-// jump, one k-packet / gamma / pellet event), so lanes holding the same kind of packet execute it in lock step and
-// no lane idles while another works through a long history. Packets that stop on `max_events` are counted in
-// *unfinished and picked up by the next pass (the passes of update_packets.cc:249-311).
-ARTIS_DEV void body_transport(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const int *order, const int n,
-                              int *queue_head, const int pass, const long long max_events, int *unfinished) {
+ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const QueueView &qv, const int kind,
+                              const long long max_events) {
   const double t2 = c.t2;
+  const int n = *qv.n_in;
   Tally tl = {};
   KappaCache k;
   k.valid = false;
-  ArtisPacket p;
-  Rng rng = {};
-  int idx = -1;
-  long long events = 0;
-  bool have = false;
   while (true) {
-    if (!have) {
-      const int q = int_fetch_add(queue_head, 1);
-      if (q >= n) break;
-      idx = order ? order[q] : q;
-      p = pkts[idx];
-      if (pass == 0) {  // update_packets.cc:282-285
-        p.interactions = 0;
-        p.scat_count = 0;
-      }
-      if (p.type == ARTIS_TYPE_ESCAPE || !(p.prop_time < t2)) {
-        if (pass == 0) pkts[idx] = p;
-        continue;
-      }
-      rng = rng_init(c, p.number, pass == 0 ? 0ull : rngctr[idx]);
-      k.valid = false;
-      events = 0;
-      have = true;
-    }
-    do_packet(c, p, t2, k, rng, tl);
-    events++;
-    const bool finished = (p.type == ARTIS_TYPE_ESCAPE) || !(p.prop_time < t2);
-    if (finished || events >= max_events) {
-      rngctr[idx] = rng.ctr;
-      pkts[idx] = p;
-      if (!finished) int_add(unfinished, 1);
-      have = false;
+    const int q = int_fetch_add(qv.head, 1);
+    if (q >= n) break;
+    const int idx = qv.in[q];
+    ArtisPacket p = pkts[idx];
+    Rng rng = rng_init(c, p.number, rngctr[idx]);
+    k.valid = false;
+    long long events = 0;
+    bool active = true;
+    do {
+      do_packet(c, p, t2, k, rng, tl);
+      events++;
+      active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
+    } while (active && kind_of(p.type) == kind && events < max_events);
+    rngctr[idx] = rng.ctr;
+    pkts[idx] = p;
+    if (active) {
+      const int k2 = kind_of(p.type);
+      qv.out[k2][int_fetch_add(qv.n_out[k2], 1)] = idx;
     }
   }
   tally_flush(c, tl);

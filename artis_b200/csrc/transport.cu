@@ -37,18 +37,20 @@ __global__ void k_cool(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_cool(d_ctx, i);
 }
-__global__ void __launch_bounds__(128) k_transport(ArtisPacket *pkts, unsigned long long *rngctr, const int *order, int n,
-                                                   int *queue_head, int pass, long long max_events, int *unfinished) {
-  artis::body_transport(d_ctx, pkts, rngctr, order, n, queue_head, pass, max_events, unfinished);
+// one kernel per event kind (template parameter only to give each kind its own name in profiles)
+template <int KIND>
+__global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned long long *rngctr, artis::QueueView qv,
+                                                   long long max_events) {
+  artis::body_wavefront(d_ctx, pkts, rngctr, qv, KIND, max_events);
 }
-__global__ void k_bucket_hist(ArtisPacket *pkts, int n, int pass, int *counts) {
+__global__ void k_bucket_hist(ArtisPacket *pkts, unsigned long long *rngctr, int n, int *counts) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    artis::body_bucket_hist(d_ctx, pkts, i, pass, counts);
+    artis::body_bucket_hist(d_ctx, pkts, rngctr, i, counts);
 }
-__global__ void k_bucket_scan(int *counts, int nbuckets, int *n_active) { artis::body_bucket_scan(counts, nbuckets, n_active); }
-__global__ void k_bucket_scatter(const ArtisPacket *pkts, int n, int *offsets, int *order) {
+__global__ void k_bucket_scan(int *counts, int *kind_sizes) { artis::body_bucket_scan(d_ctx, counts, kind_sizes); }
+__global__ void k_bucket_scatter(const ArtisPacket *pkts, int n, int *offsets, int *const *queues) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    artis::body_bucket_scatter(d_ctx, pkts, i, offsets, order);
+    artis::body_bucket_scatter(d_ctx, pkts, i, offsets, queues);
 }
 __global__ void k_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -112,7 +114,7 @@ bool be_select_device(int device, std::string *why) {
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) g_sms = prop.multiProcessorCount;
   int nb = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport, 128, 0) == cudaSuccess && nb > 0)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_wavefront<1>, 128, 0) == cudaSuccess && nb > 0)
     g_transport_blocks_per_sm = nb;
   if (g_stream == nullptr) {
     note(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -173,17 +175,21 @@ void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8),
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
-void be_run_transport(ArtisPacket *p, unsigned long long *r, const int *order, int n, int *qh, int pass, long long maxev,
-                      int *unf, int block) {
-  if (n <= 0) return;
-  if (block > 128) block = 128;  // __launch_bounds__
-  // persistent grid: every SM gets its full complement of resident blocks (register-limited), the queue does the rest
-  k_transport<<<grid_for(n, block, g_transport_blocks_per_sm), block, 0, g_stream>>>(p, r, order, n, qh, pass, maxev, unf);
+void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
+  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, r, n, buckets);
+  k_bucket_scan<<<1, 1, 0, g_stream>>>(buckets, kind_sizes);
+  k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, buckets, queues);
 }
-void be_run_bucket(ArtisPacket *p, int n, int pass, int *buckets, int nbuckets, int *order, int *n_active) {
-  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, pass, buckets);
-  k_bucket_scan<<<1, 1, 0, g_stream>>>(buckets, nbuckets, n_active);
-  k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, buckets, order);
+void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueView &qv, int kind, long long maxev, int block) {
+  if (block > 128) block = 128;  // __launch_bounds__
+  // persistent grid: every SM gets its full complement of resident blocks; the queue size is read on the device
+  const int grid = g_sms * g_transport_blocks_per_sm;
+  switch (kind) {
+    case 0: k_wavefront<0><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
+    case 1: k_wavefront<1><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
+    case 2: k_wavefront<2><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
+    default: k_wavefront<3><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
+  }
 }
 #define PROBE_GRID(n) ((n) + 127) / 128, 128, 0, g_stream
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) { k_probe_boundary<<<PROBE_GRID(n)>>>(p, n, a, b, c); }

@@ -174,6 +174,7 @@ def main():
     ap.add_argument("--packets", type=int, default=1000000, help="packets per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-baseline", default="auto", choices=["auto", "off"])
+    ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -214,6 +215,8 @@ def main():
     T = Transport()
     T.init(st, device=local_rank, rank=rank, nranks=world)
     T.upload_cellstate(cs)
+    if a.max_events:
+        T.set_tuning(max_events_per_pass=a.max_events)
     precompute_ms = T.last_timings()[3]
     # the contiguous FP64 estimator block as a torch tensor (for the NCCL all-reduce that replaces
     # mpi_reduce_estimators, sn3d.cc:316-384)

@@ -40,14 +40,13 @@ void be_run_levelpop(long long n) { for (long long i = 0; i < n; i++) artis::bod
 void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g_ctx, i); }
 void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
 void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
-void be_run_transport(ArtisPacket *p, unsigned long long *r, const int *order, int n, int *qh, int pass, long long maxev,
-                      int *unf, int) {
-  artis::body_transport(g_ctx, p, r, order, n, qh, pass, maxev, unf);  // one "thread" drains the whole queue
+void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
+  for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, p, r, i, buckets);
+  artis::body_bucket_scan(g_ctx, buckets, kind_sizes);
+  for (int i = 0; i < n; i++) artis::body_bucket_scatter(g_ctx, p, i, buckets, queues);
 }
-void be_run_bucket(ArtisPacket *p, int n, int pass, int *buckets, int nbuckets, int *order, int *n_active) {
-  for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, p, i, pass, buckets);
-  artis::body_bucket_scan(buckets, nbuckets, n_active);
-  for (int i = 0; i < n; i++) artis::body_bucket_scatter(g_ctx, p, i, buckets, order);
+void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueView &qv, int kind, long long maxev, int) {
+  artis::body_wavefront(g_ctx, p, r, qv, kind, maxev);  // one "thread" drains the whole queue
 }
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   for (int i = 0; i < n; i++) artis::body_probe_boundary(g_ctx, p, i, a, b, c);
