@@ -430,4 +430,38 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
   }
 }
 
+// do_packet restricted to the packet types of one scheduler kind (kernels.cuh kind_of): each wavefront kernel only
+// carries the code and registers of the physics it can meet.
+template <int KIND>
+ARTIS_DEV void do_packet_kind(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
+  if constexpr (KIND == 1) {
+    tl.packet_updates++;
+    do_rpkt_step(c, p, t2, k, rng, tl);
+    if (p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
+  } else if constexpr (KIND == 2) {
+    tl.packet_updates++;
+    do_gamma(c, p, t2, rng, tl);
+    if (p.type != ARTIS_TYPE_GAMMA && p.type != ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_GAMMA_DEP], p.e_cmf);
+  } else if constexpr (KIND == 0) {
+    tl.packet_updates++;
+    if (p.type == ARTIS_TYPE_MA) {
+      do_macroatom(c, p, rng, tl);
+    } else if (p.type == ARTIS_TYPE_NTLEPTON) {
+      do_ntlepton(c, p, tl);
+    } else {
+      const int mgi = cell_mgi(c, p.where);
+      if (p.type == ARTIS_TYPE_PRE_KPKT || c.cs.thick[mgi] == 1) {
+        do_kpkt_bb(c, p, rng, tl);
+      } else if (p.type == ARTIS_TYPE_KPKT) {
+        do_kpkt(c, p, t2, rng, tl);
+      } else {
+        fatal(c, 440);
+        p.prop_time = t2;
+      }
+    }
+  } else {
+    do_packet(c, p, t2, k, rng, tl);
+  }
+}
+
 }  // namespace artis

@@ -94,32 +94,45 @@ ARTIS_DEV void body_bucket_scatter(const Ctx &c, const ArtisPacket *pkts, const 
   if (packet_active(c, p)) queues[kind_of(p.type)][int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
 }
 
-ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const QueueView &qv, const int kind,
+template <int KIND>
+ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const QueueView &qv,
                               const long long max_events) {
+  constexpr int kind = KIND;
   const double t2 = c.t2;
   const int n = *qv.n_in;
   Tally tl = {};
   KappaCache k;
   k.valid = false;
+  // One flat loop: a lane either holds a packet and advances it by one event, or fetches the next queue entry. There is
+  // deliberately no inner per-packet loop, because lanes leaving an inner loop wait at its convergence barrier for the
+  // slowest lane of the warp; here every lane reaches the event code again on the next iteration.
+  bool have = false;
+  int idx = 0;
+  long long events = 0;
+  ArtisPacket p;
+  Rng rng;
   while (true) {
-    const int q = int_fetch_add(qv.head, 1);
-    if (q >= n) break;
-    const int idx = qv.in[q];
-    ArtisPacket p = pkts[idx];
-    Rng rng = rng_init(c, p.number, rngctr[idx]);
-    k.valid = false;
-    long long events = 0;
-    bool active = true;
-    do {
-      do_packet(c, p, t2, k, rng, tl);
-      events++;
-      active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
-    } while (active && kind_of(p.type) == kind && events < max_events);
-    rngctr[idx] = rng.ctr;
-    pkts[idx] = p;
-    if (active) {
-      const int k2 = kind_of(p.type);
-      qv.out[k2][int_fetch_add(qv.n_out[k2], 1)] = idx;
+    if (!have) {
+      const int q = int_fetch_add(qv.head, 1);
+      if (q >= n) break;
+      idx = qv.in[q];
+      p = pkts[idx];
+      rng = rng_init(c, p.number, rngctr[idx]);
+      k.valid = false;
+      events = 0;
+      have = true;
+    }
+    do_packet_kind<KIND>(c, p, t2, k, rng, tl);
+    events++;
+    const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
+    if (!(active && kind_of(p.type) == kind && events < max_events)) {
+      rngctr[idx] = rng.ctr;
+      pkts[idx] = p;
+      if (active) {
+        const int k2 = kind_of(p.type);
+        qv.out[k2][int_fetch_add(qv.n_out[k2], 1)] = idx;
+      }
+      have = false;
     }
   }
   tally_flush(c, tl);

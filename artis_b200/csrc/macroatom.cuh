@@ -155,13 +155,13 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       total_transitions += pr[a];
     }
     const double randomrate = rng_uniform(rng) * total_transitions;
-    double rate = 0.;
+    double rate = 0., pr_sel = 0.;
     int selected_action = MA_ACTION_COUNT;
-    for (int a = 0; a < MA_ACTION_COUNT; a++) {
+    for (int a = 0; a < MA_ACTION_COUNT; a++) {  // first action whose running sum exceeds the draw (macroatom.cc:470-478)
       rate += pr[a];
-      if (rate > randomrate) {
+      if (selected_action == MA_ACTION_COUNT && rate > randomrate) {
         selected_action = a;
-        break;
+        pr_sel = pr[a];
       }
     }
     if (selected_action == MA_ACTION_COUNT) {  // reference: "[fatal] do_ma: problem with random numbers" + abort
@@ -169,20 +169,38 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       p.type = ARTIS_TYPE_KPKT;
       return;
     }
-    const int level = gl - c.st.ion_leveloffset[ui];
-    switch (selected_action) {
-      case MA_RADDEEXC: {  // macroatom.cc:222-296
-        const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
+    // The three list-driven actions (radiative de-excitation, internal jump down / up within the ion) share one draw and
+    // one search over a per-cell prefix-sum row; doing it here, before the per-action switch, keeps the lanes of a warp
+    // converged through the expensive part of a jump whatever action each of them selected.
+    int sel = -1, toff = 0;
+    {
+      const double *cum = nullptr;
+      int ntrans = 0;
+      if (selected_action == MA_RADDEEXC || selected_action == MA_INTERNALDOWNSAME) {
+        ntrans = c.st.lev_ndowntrans[gl];
+        toff = c.st.lev_downoffset[gl];
+        cum = (selected_action == MA_RADDEEXC ? c.tb.ma_cum_raddeexc : c.tb.ma_cum_intdown) +
+              (size_t)tc * c.st.ndowntrans_total + toff;
+      } else if (selected_action == MA_INTERNALUPSAME) {
+        ntrans = c.st.lev_nuptrans[gl];
+        toff = c.st.lev_upoffset[gl];
+        cum = c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + toff;
+      }
+      if (cum != nullptr) {
         const double zrand = rng_uniform(rng);
-        const int i = first_greater(c.tb.ma_cum_raddeexc + (size_t)tc * c.st.ndowntrans_total + doff, ndown,
-                                    zrand * pr[MA_RADDEEXC]);
-        tl.ma_trans_scanned += bsearch_probes(ndown);
-        if (i >= ndown) {
-          fatal(c, 222);
+        sel = first_greater(cum, ntrans, zrand * pr_sel);
+        tl.ma_trans_scanned += bsearch_probes(ntrans);
+        if (sel >= ntrans) {
+          fatal(c, selected_action == MA_RADDEEXC ? 222 : (selected_action == MA_INTERNALDOWNSAME ? 223 : 227));
           p.type = ARTIS_TYPE_KPKT;
           return;
         }
-        const int linelistindex = c.st.downtrans_lineindex[doff + i];
+      }
+    }
+    const int level = gl - c.st.ion_leveloffset[ui];
+    switch (selected_action) {
+      case MA_RADDEEXC: {  // macroatom.cc:222-296
+        const int linelistindex = c.st.downtrans_lineindex[toff + sel];
         if (c.st.opt_record_linestat) int_add(&c.es.ecounter[linelistindex], 1);
         const int gll = c.line_lower_g[linelistindex];
         const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gll];
@@ -215,17 +233,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       case MA_INTERNALDOWNSAME: {  // macroatom.cc:174-220
         p.interactions += 1;
         tl.interactions++;
-        const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
-        const double zrand = rng_uniform(rng);
-        const int i = first_greater(c.tb.ma_cum_intdown + (size_t)tc * c.st.ndowntrans_total + doff, ndown,
-                                    zrand * pr[MA_INTERNALDOWNSAME]);
-        tl.ma_trans_scanned += bsearch_probes(ndown);
-        if (i >= ndown) {
-          fatal(c, 223);
-          p.type = ARTIS_TYPE_KPKT;
-          return;
-        }
-        gl = c.line_lower_g[c.st.downtrans_lineindex[doff + i]];
+        gl = c.line_lower_g[c.st.downtrans_lineindex[toff + sel]];
         break;
       }
       case MA_RADRECOMB: {  // macroatom.cc:298-380
@@ -238,10 +246,10 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
           const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gl0_lower + lower];
           const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
           rrate += R * epsilon_trans;
-          if (zrand * pr[MA_RADRECOMB] < rrate) break;
+          if (zrand * pr_sel < rrate) break;
         }
         tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
-        if (zrand * pr[MA_RADRECOMB] >= rrate) {
+        if (zrand * pr_sel >= rrate) {
           fatal(c, 224);
           p.type = ARTIS_TYPE_KPKT;
           return;
@@ -288,7 +296,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
           const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
           const double C = col_recombination_ratecoeff(c, mgi, ui, gl, gl0_lower + lower, epsilon_trans);
           rrate += (R + C) * epsilon_target;
-          if (zrand * pr[MA_INTERNALDOWNLOWER] < rrate) break;
+          if (zrand * pr_sel < rrate) break;
         }
         tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
         if (lower >= nlevels) {
@@ -303,17 +311,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       case MA_INTERNALUPSAME: {  // macroatom.cc:815-835
         p.interactions += 1;
         tl.interactions++;
-        const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
-        const double zrand = rng_uniform(rng);
-        const int i = first_greater(c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + uoff, nup,
-                                    zrand * pr[MA_INTERNALUPSAME]);
-        tl.ma_trans_scanned += bsearch_probes(nup);
-        if (i >= nup) {
-          fatal(c, 227);
-          p.type = ARTIS_TYPE_KPKT;
-          return;
-        }
-        gl = c.line_upper_g[c.st.uptrans_lineindex[uoff + i]];
+        gl = c.line_upper_g[c.st.uptrans_lineindex[toff + sel]];
         break;
       }
       case MA_INTERNALUPHIGHER: {  // macroatom.cc:382-414 do_macroatom_ionisation
@@ -330,9 +328,9 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
           const double R = get_corrphotoioncoeff(c, mgi, gl, t);
           const double C = col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans);
           rrate += (R + C) * epsilon_current;
-          if (zrand * pr[MA_INTERNALUPHIGHER] < rrate) break;
+          if (zrand * pr_sel < rrate) break;
         }
-        if (zrand * pr[MA_INTERNALUPHIGHER] >= rrate || upper < 0) {
+        if (zrand * pr_sel >= rrate || upper < 0) {
           fatal(c, 228);
           p.type = ARTIS_TYPE_KPKT;
           return;

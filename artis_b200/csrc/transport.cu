@@ -37,12 +37,192 @@ __global__ void k_cool(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_cool(d_ctx, i);
 }
-// one kernel per event kind (template parameter only to give each kind its own name in profiles)
+// one kernel per event kind, each compiled with only that kind's physics
 template <int KIND>
 __global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned long long *rngctr, artis::QueueView qv,
                                                    long long max_events) {
-  artis::body_wavefront(d_ctx, pkts, rngctr, qv, KIND, max_events);
+  artis::body_wavefront<KIND>(d_ctx, pkts, rngctr, qv, max_events);
 }
+// ---- barrier-free scheduler ------------------------------------------------------------------------------------------
+// One persistent kernel, one ring of packet indices per event kind, warps specialised by kind. A warp that has no
+// packet left picks the kind with the longest backlog and keeps that role until it runs dry; its lanes claim ring
+// entries (warp-aggregated), advance their packet by events of that kind only and, when the packet changes kind, write
+// it back and push its index on the ring of the new kind. Nothing waits for the slowest packet of a round: the step
+// ends when the longest single packet history ends, and a warp never executes two kinds' code in one iteration.
+//
+// Ring protocol (capacity >= number of packets, so at most `cap` entries are ever outstanding): a slot holds -1 when
+// empty. Producers take a ticket from tail (atomicAdd) and CAS their index into slot ticket % cap; consumers CAS head
+// forward only over tickets below the tail they observed and then exchange the slot back to -1, spinning for the few
+// cycles a producer may still need to fill it. Packet state written before the push is made visible with
+// __threadfence() and read with ld.global.cg on the consumer side (L1 is not coherent across SMs).
+struct PersistView {
+  int *ring[artis::NKIND];
+  unsigned long long *head;  // [NKIND]
+  unsigned long long *tail;  // [NKIND]
+  int *n_active;             // packets that have not finished the timestep
+  int cap;
+};
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
+  return *reinterpret_cast<const volatile unsigned long long *>(p);
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+static_assert(sizeof(ArtisPacket) % 8 == 0, "packet copied as 8-byte words");
+__device__ __forceinline__ void packet_load_cg(ArtisPacket &p, const ArtisPacket *src) {
+  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(src);
+  unsigned long long *d = reinterpret_cast<unsigned long long *>(&p);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) d[i] = __ldcg(s + i);
+}
+__device__ __forceinline__ void packet_store_cg(ArtisPacket *dst, const ArtisPacket &p) {
+  unsigned long long *d = reinterpret_cast<unsigned long long *>(dst);
+  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(&p);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) __stcg(d + i, s[i]);
+}
+
+__global__ void __launch_bounds__(128, 2) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
+                                                                 long long max_events, unsigned long long idle_timeout_ns) {
+  using namespace artis;
+  const Ctx &c = d_ctx;
+  const double t2 = c.t2;
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  Tally tl = {};
+  KappaCache k;
+  k.valid = false;
+  bool have = false;
+  int idx = 0, role = 0;
+  long long events = 0;
+  ArtisPacket p;
+  Rng rng;
+  unsigned long long idle_since = 0ull;
+  while (true) {
+    __syncwarp(full);
+    const unsigned need = __ballot_sync(full, !have);
+    if (need != 0u) {
+      if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
+        long long backlog = 0;
+        if (lane < NKIND) {
+          const unsigned long long h = ld_volatile_u64(pv.head + lane), t = ld_volatile_u64(pv.tail + lane);
+          backlog = t > h ? (long long)(t - h) : 0;
+        }
+        long long best = backlog;
+        int best_kind = lane;
+#pragma unroll
+        for (int off = 2; off >= 1; off >>= 1) {
+          const long long ob = __shfl_down_sync(full, best, off);
+          const int ok = __shfl_down_sync(full, best_kind, off);
+          if (ob > best) {
+            best = ob;
+            best_kind = ok;
+          }
+        }
+        best = __shfl_sync(full, best, 0);
+        best_kind = __shfl_sync(full, best_kind, 0);
+        if (best <= 0) {
+          int left = 0;
+          if (lane == 0) left = *reinterpret_cast<volatile int *>(pv.n_active);
+          left = __shfl_sync(full, left, 0);
+          if (left <= 0) break;  // every packet has reached the end of the timestep
+          unsigned long long now = 0ull;
+          if (lane == 0) now = global_ns();
+          now = __shfl_sync(full, now, 0);
+          if (idle_since == 0ull) idle_since = now;
+          if (now - idle_since > idle_timeout_ns) {  // a lost packet would otherwise hang the device
+            if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
+            break;
+          }
+          __nanosleep(1000);
+          continue;
+        }
+        role = best_kind;
+        idle_since = 0ull;
+      }
+      int take = 0;
+      unsigned long long base = 0ull;
+      if (lane == 0) {
+        const int want = __popc(need);
+        for (int tries = 0; tries < 4; tries++) {
+          const unsigned long long h = ld_volatile_u64(pv.head + role), t = ld_volatile_u64(pv.tail + role);
+          const long long avail = t > h ? (long long)(t - h) : 0;
+          take = avail < want ? (int)avail : want;
+          if (take == 0) break;
+          if (atomicCAS(pv.head + role, h, h + (unsigned long long)take) == h) {
+            base = h;
+            break;
+          }
+          take = 0;
+        }
+      }
+      take = __shfl_sync(full, take, 0);
+      base = __shfl_sync(full, base, 0);
+      const int rank = __popc(need & lt_mask);
+      if (!have && rank < take) {
+        int *slot = pv.ring[role] + (size_t)((base + (unsigned long long)rank) % (unsigned long long)pv.cap);
+        int v;
+        while ((v = atomicExch(slot, -1)) < 0) {
+        }
+        __threadfence();
+        idx = v;
+        packet_load_cg(p, pkts + idx);
+        rng = rng_init(c, p.number, __ldcg(rngctr + idx));
+        k.valid = false;
+        events = 0;
+        have = true;
+      }
+      if (need == full && take == 0) continue;  // lost the race for the last entries
+    }
+    __syncwarp(full);
+    bool done = false;
+    int k2 = -1;
+    if (have) {
+      switch (role) {  // warp-uniform
+        case 0: do_packet_kind<0>(c, p, t2, k, rng, tl); break;
+        case 1: do_packet_kind<1>(c, p, t2, k, rng, tl); break;
+        case 2: do_packet_kind<2>(c, p, t2, k, rng, tl); break;
+        default: do_packet_kind<3>(c, p, t2, k, rng, tl); break;
+      }
+      events++;
+      const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
+      if (!(active && kind_of(p.type) == role && events < max_events)) {
+        __stcg(rngctr + idx, (unsigned long long)rng.ctr);
+        packet_store_cg(pkts + idx, p);
+        __threadfence();
+        done = true;
+        k2 = active ? kind_of(p.type) : -1;
+        have = false;
+      }
+    }
+    __syncwarp(full);
+    if (__ballot_sync(full, done) != 0u) {
+#pragma unroll
+      for (int kk = 0; kk < NKIND; kk++) {
+        const unsigned m = __ballot_sync(full, done && k2 == kk);
+        if (m != 0u) {
+          const int leader = __ffs(m) - 1;
+          unsigned long long b = 0ull;
+          if (lane == leader) b = atomicAdd(pv.tail + kk, (unsigned long long)__popc(m));
+          b = __shfl_sync(full, b, leader);
+          if (done && k2 == kk) {
+            int *slot = pv.ring[kk] + (size_t)((b + (unsigned long long)__popc(m & lt_mask)) % (unsigned long long)pv.cap);
+            while (atomicCAS(slot, -1, idx) != -1) {
+            }
+          }
+        }
+      }
+      const unsigned fin = __ballot_sync(full, done && k2 < 0);
+      if (fin != 0u && lane == __ffs(fin) - 1) atomicSub(pv.n_active, __popc(fin));
+    }
+  }
+  tally_flush(c, tl);
+}
+
 __global__ void k_bucket_hist(ArtisPacket *pkts, unsigned long long *rngctr, int n, int *counts) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     artis::body_bucket_hist(d_ctx, pkts, rngctr, i, counts);
@@ -90,6 +270,7 @@ cudaStream_t g_stream = nullptr;
 cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 int g_sms = SM_COUNT_B200;
 int g_transport_blocks_per_sm = 4;
+int g_persistent_blocks_per_sm = 2;
 std::string g_async_err;
 
 void note(cudaError_t e, const char *what) {
@@ -116,6 +297,8 @@ bool be_select_device(int device, std::string *why) {
   int nb = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_wavefront<1>, 128, 0) == cudaSuccess && nb > 0)
     g_transport_blocks_per_sm = nb;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent, 128, 0) == cudaSuccess && nb > 0)
+    g_persistent_blocks_per_sm = nb;  // the whole grid must be resident: idle warps wait for the others' packets
   if (g_stream == nullptr) {
     note(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking), "cudaStreamCreate");
     note(cudaEventCreate(&g_ev0), "cudaEventCreate");
@@ -191,6 +374,20 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
     default: k_wavefront<3><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
   }
 }
+// barrier-free scheduler: rings = NKIND rings of `cap` ints (initial entries written by be_run_bucket, -1 elsewhere),
+// pmeta = head[NKIND], tail[NKIND], n_active (int)
+bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int cap, unsigned long long *pmeta, long long maxev) {
+  PersistView pv;
+  for (int k = 0; k < artis::NKIND; k++) pv.ring[k] = rings + (size_t)k * cap;
+  pv.head = pmeta;
+  pv.tail = pmeta + artis::NKIND;
+  pv.n_active = reinterpret_cast<int *>(pmeta + 2 * artis::NKIND);
+  pv.cap = cap;
+  const int grid = g_sms * g_persistent_blocks_per_sm;
+  k_transport_persistent<<<grid, 128, 0, g_stream>>>(p, r, pv, maxev, 20ull * 1000000000ull);
+  return true;
+}
+void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }
 #define PROBE_GRID(n) ((n) + 127) / 128, 128, 0, g_stream
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) { k_probe_boundary<<<PROBE_GRID(n)>>>(p, n, a, b, c); }
 void be_run_probe_kappa(const ArtisPacket *p, int n, double *k) { k_probe_kappa<<<PROBE_GRID(n)>>>(p, n, k); }

@@ -46,8 +46,16 @@ void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, i
   for (int i = 0; i < n; i++) artis::body_bucket_scatter(g_ctx, p, i, buckets, queues);
 }
 void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueView &qv, int kind, long long maxev, int) {
-  artis::body_wavefront(g_ctx, p, r, qv, kind, maxev);  // one "thread" drains the whole queue
+  switch (kind) {  // one "thread" drains the whole queue
+    case 0: artis::body_wavefront<0>(g_ctx, p, r, qv, maxev); break;
+    case 1: artis::body_wavefront<1>(g_ctx, p, r, qv, maxev); break;
+    case 2: artis::body_wavefront<2>(g_ctx, p, r, qv, maxev); break;
+    default: artis::body_wavefront<3>(g_ctx, p, r, qv, maxev); break;
+  }
 }
+// the barrier-free scheduler is a device-only construct; the host backend runs the same visits as kernel rounds
+bool be_run_persistent(ArtisPacket *, unsigned long long *, int *, int, unsigned long long *, long long) { return false; }
+void be_fill_bytes(void *p, int byte, size_t n) { memset(p, byte, n); }
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   for (int i = 0; i < n; i++) artis::body_probe_boundary(g_ctx, p, i, a, b, c);
 }
