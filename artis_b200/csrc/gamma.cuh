@@ -434,9 +434,9 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
 // carries the code and registers of the physics it can meet.
 template <int KIND>
 ARTIS_DEV void do_packet_kind(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
-  if constexpr (KIND == 1) {
+  if constexpr (KIND == 1 || KIND == 4) {
     tl.packet_updates++;
-    do_rpkt_step(c, p, t2, k, rng, tl);
+    do_rpkt_step<(KIND == 1 ? 1 : 2)>(c, p, t2, k, rng, tl);
     if (p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
   } else if constexpr (KIND == 2) {
     tl.packet_updates++;

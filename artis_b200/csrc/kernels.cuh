@@ -39,21 +39,27 @@ ARTIS_DEV void body_cool(const Ctx &c, const long long idx) {
 //   kind 3  pellets and non-thermal pre-deposition                  (update_packets.cc:16,71)
 // A lane pulls the next index from its kind's queue, runs do_packet while the packet stays of that kind, then writes
 // it back and appends its index to the queue of the kind it has become (or drops it when it escaped / reached t2).
-constexpr int NKIND = 4;
-ARTIS_DEV int kind_of(const int type) {
-  switch (type) {
+constexpr int NKIND = 5;
+enum { KIND_MAK = 0, KIND_RPKT_THIN = 1, KIND_GAMMA = 2, KIND_OTHER = 3, KIND_RPKT_GREY = 4 };
+// r-packets are two kinds: in a non-grey cell a step evaluates the continuum opacity and sweeps lines (expensive), in a
+// grey or empty cell it is a boundary distance and a Thomson-like scattering (cheap); mixed in one warp the cheap lanes
+// would idle through the others' opacity loops.
+ARTIS_DEV int kind_of(const Ctx &c, const ArtisPacket &p) {
+  switch (p.type) {
     case ARTIS_TYPE_KPKT:
     case ARTIS_TYPE_MA:
     case ARTIS_TYPE_NTLEPTON:
     case ARTIS_TYPE_PRE_KPKT:
     case ARTIS_TYPE_GAMMA_KPKT:
-      return 0;
-    case ARTIS_TYPE_RPKT:
-      return 1;
+      return KIND_MAK;
+    case ARTIS_TYPE_RPKT: {
+      const int mgi = cell_mgi(c, p.where);
+      return (mgi == c.st.npts_model || c.cs.thick[mgi] == 1) ? KIND_RPKT_GREY : KIND_RPKT_THIN;
+    }
     case ARTIS_TYPE_GAMMA:
-      return 2;
+      return KIND_GAMMA;
     default:
-      return 3;
+      return KIND_OTHER;
   }
 }
 ARTIS_DEV bool packet_active(const Ctx &c, const ArtisPacket &p) { return p.type != ARTIS_TYPE_ESCAPE && p.prop_time < c.t2; }
@@ -68,7 +74,7 @@ struct QueueView {
 
 // K0 bucket_packets: counting sort of the active packets by (kind, model cell) into the initial queues; replaces the
 // std::sort of update_packets.cc:204-256 (dense inner cells first, like the reference's comparator for 1D models).
-ARTIS_DEV int bucket_key(const Ctx &c, const ArtisPacket &p) { return kind_of(p.type) * (c.st.npts_model + 1) + cell_mgi(c, p.where); }
+ARTIS_DEV int bucket_key(const Ctx &c, const ArtisPacket &p) { return kind_of(c, p) * (c.st.npts_model + 1) + cell_mgi(c, p.where); }
 ARTIS_DEV void body_bucket_hist(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const int idx, int *counts) {
   ArtisPacket &p = pkts[idx];
   p.interactions = 0;  // update_packets.cc:282-285, for every packet including the escaped ones
@@ -91,7 +97,7 @@ ARTIS_DEV void body_bucket_scan(const Ctx &c, int *counts, int *kind_sizes) {
 }
 ARTIS_DEV void body_bucket_scatter(const Ctx &c, const ArtisPacket *pkts, const int idx, int *offsets, int *const *queues) {
   const ArtisPacket &p = pkts[idx];
-  if (packet_active(c, p)) queues[kind_of(p.type)][int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
+  if (packet_active(c, p)) queues[kind_of(c, p)][int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
 }
 
 template <int KIND>
@@ -125,11 +131,11 @@ ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long lon
     do_packet_kind<KIND>(c, p, t2, k, rng, tl);
     events++;
     const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
-    if (!(active && kind_of(p.type) == kind && events < max_events)) {
+    if (!(active && kind_of(c, p) == kind && events < max_events)) {
       rngctr[idx] = rng.ctr;
       pkts[idx] = p;
       if (active) {
-        const int k2 = kind_of(p.type);
+        const int k2 = kind_of(c, p);
         qv.out[k2][int_fetch_add(qv.n_out[k2], 1)] = idx;
       }
       have = false;

@@ -370,6 +370,9 @@ ARTIS_DEV void rpkt_event_thickcell(const Ctx &c, ArtisPacket &p, Rng &rng, Tall
 // ---- rpkt.cc:623-813 do_rpkt_step ----------------------------------------------------------------------------------------
 // returns true while the packet is still an r-packet inside its time step (the reference additionally stops at a
 // model-cell change because of its cellhistory cache; the wavefront scheduler decides that)
+// MODE 0: any cell; 1: the caller guarantees a non-grey, non-empty cell; 2: the caller guarantees a grey or empty cell
+// (the scheduler's two r-packet kinds, kernels.cuh) -- only prunes code, the arithmetic is the same.
+template <int MODE = 0>
 ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
   tl.rpkt_steps++;
   int mgi = cell_mgi(c, p.where);
@@ -400,8 +403,8 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
   double edist;
   int rpkt_eventtype = RPKT_EVENTTYPE_NONE;
   bool find_nextline = false;
-  const bool thick = (mgi != c.st.npts_model) && (c.cs.thick[mgi] == 1);
-  if (mgi == c.st.npts_model) {
+  const bool thick = (MODE != 1) && (mgi != c.st.npts_model) && (c.cs.thick[mgi] == 1);
+  if (MODE != 1 && mgi == c.st.npts_model) {
     edist = DBL_MAX_;
     find_nextline = true;
   } else if (thick) {
@@ -409,7 +412,13 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
     edist = (tau_next - 0.0) / kappa;
     find_nextline = true;
   } else {
-    edist = get_event(c, mgi, p, &rpkt_eventtype, tau_next, fmin(tdist, sdist), k, tl);
+    if constexpr (MODE == 2) {
+      fatal(c, 107);
+      p.type = ARTIS_TYPE_ESCAPE;
+      return false;
+    } else {
+      edist = get_event(c, mgi, p, &rpkt_eventtype, tau_next, fmin(tdist, sdist), k, tl);
+    }
   }
   const bool do_rlc = (c.cs.do_rlc_est != 0 && c.cs.do_rlc_est != 3);
   if ((sdist < tdist) && (sdist < edist)) {

@@ -85,7 +85,10 @@ __device__ __forceinline__ void packet_store_cg(ArtisPacket *dst, const ArtisPac
   for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) __stcg(d + i, s[i]);
 }
 
-__global__ void __launch_bounds__(128, 2) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
+#ifndef ARTIS_PERSIST_MINBLOCKS
+#define ARTIS_PERSIST_MINBLOCKS 2
+#endif
+__global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
                                                                  long long max_events, unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;
@@ -115,7 +118,7 @@ __global__ void __launch_bounds__(128, 2) k_transport_persistent(ArtisPacket *pk
         long long best = backlog;
         int best_kind = lane;
 #pragma unroll
-        for (int off = 2; off >= 1; off >>= 1) {
+        for (int off = 4; off >= 1; off >>= 1) {
           const long long ob = __shfl_down_sync(full, best, off);
           const int ok = __shfl_down_sync(full, best_kind, off);
           if (ob > best) {
@@ -186,16 +189,17 @@ __global__ void __launch_bounds__(128, 2) k_transport_persistent(ArtisPacket *pk
         case 0: do_packet_kind<0>(c, p, t2, k, rng, tl); break;
         case 1: do_packet_kind<1>(c, p, t2, k, rng, tl); break;
         case 2: do_packet_kind<2>(c, p, t2, k, rng, tl); break;
+        case 4: do_packet_kind<4>(c, p, t2, k, rng, tl); break;
         default: do_packet_kind<3>(c, p, t2, k, rng, tl); break;
       }
       events++;
       const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
-      if (!(active && kind_of(p.type) == role && events < max_events)) {
+      if (!(active && kind_of(c, p) == role && events < max_events)) {
         __stcg(rngctr + idx, (unsigned long long)rng.ctr);
         packet_store_cg(pkts + idx, p);
         __threadfence();
         done = true;
-        k2 = active ? kind_of(p.type) : -1;
+        k2 = active ? kind_of(c, p) : -1;
         have = false;
       }
     }
@@ -371,6 +375,7 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
     case 0: k_wavefront<0><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
     case 1: k_wavefront<1><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
     case 2: k_wavefront<2><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
+    case 4: k_wavefront<4><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
     default: k_wavefront<3><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
   }
 }

@@ -14,7 +14,7 @@ import numpy as np
 from . import abi
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-DEFAULT_LIB = os.path.join(HERE, "libartis_gpu.so")
+DEFAULT_LIB = os.environ.get("ARTIS_GPU_LIB", os.path.join(HERE, "libartis_gpu.so"))  # override: kernel tuning experiments
 
 
 class ArtisGpuError(RuntimeError):

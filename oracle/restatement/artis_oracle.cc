@@ -50,6 +50,7 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
     case 0: artis::body_wavefront<0>(g_ctx, p, r, qv, maxev); break;
     case 1: artis::body_wavefront<1>(g_ctx, p, r, qv, maxev); break;
     case 2: artis::body_wavefront<2>(g_ctx, p, r, qv, maxev); break;
+    case 4: artis::body_wavefront<4>(g_ctx, p, r, qv, maxev); break;
     default: artis::body_wavefront<3>(g_ctx, p, r, qv, maxev); break;
   }
 }
