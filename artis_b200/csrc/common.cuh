@@ -303,7 +303,7 @@ ARTIS_DEV int int_fetch_add(int *addr, int v) {
 // per-thread work counters, flushed once per thread at the end of a pass (keeps atomics off the hot loops)
 struct Tally {
   int rpkt_steps, lines_scanned, lines_tau, bf_evaluated, estim_atomics, gamma_steps, ma_jumps, ma_trans_scanned,
-      kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates;
+      kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates, handoffs;
   int stats[34];  // stats::eventcounters increments of this thread (stats.h:48-84), flushed once per thread and pass
 };
 ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
@@ -322,6 +322,7 @@ ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   if (t.soft_repairs) ctr_add(&k[ARTIS_CTR_SOFT_REPAIRS], t.soft_repairs);
   if (t.kappa_evals) ctr_add(&k[ARTIS_CTR_KAPPA_EVALS], t.kappa_evals);
   if (t.packet_updates) ctr_add(&k[ARTIS_CTR_PACKET_UPDATES], t.packet_updates);
+  if (t.handoffs) ctr_add(&k[ARTIS_CTR_HANDOFFS], t.handoffs);
   for (int i = 0; i < 34; i++)
     if (t.stats[i]) ctr_add(&k[i], t.stats[i]);
 }

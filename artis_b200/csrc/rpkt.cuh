@@ -190,71 +190,89 @@ ARTIS_DEV double calculate_kappa_ff(const Ctx &c, const int mgi, const double nu
 }
 
 // ---- rpkt.cc:1075-1207 calculate_kappa_bf_gammacontr ---------------------------------------------------------------
-// One term of the sum: returns kappa_bf_contr of continuum i at frequency nu (0 if skipped); *gcontr receives
-// sigma_bf*probability*corrfactor (the gamma_contr of rpkt.cc:1158-1166) or 0. `*stop` is set when nu < nu_edge
-// (list sorted by nu_edge: nothing further contributes).
-ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr,
-                               bool *stop) {
-  *gcontr = 0.;
-  const double nnlevel = c.tb.bf_nnlevel[(size_t)tc * c.st.nbfcontinua + i];
-  if (nnlevel < 0.) return 0.;  // element absent / unimportant ion (rpkt.cc:1101-1104): skipped without the nu test
-  const double nu_edge = c.st.cont_nu_edge[i];
-  if (nu < nu_edge) {
-    *stop = true;
-    return 0.;
+// The reference walks the continua in order of nu_edge, skips those of absent elements / unimportant ions before looking
+// at the frequency, and stops at the first remaining one with nu < nu_edge. Because the list is sorted, every term at or
+// beyond i0 = (first i with nu < nu_edge[i]) is either skipped or stops the loop, so the sum is exactly the sum over
+// i < i0; that bound comes from a binary search here and the terms become independent.
+ARTIS_DEV int bf_stop_index(const Ctx &c, const double nu) {
+  int lo = 0, hi = c.st.nbfcontinua;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (nu < c.st.cont_nu_edge[mid]) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
   }
-  const double nu_max_phixs = nu_edge * c.st.last_phixs_nuovernuedge;
-  if (!(nu <= nu_max_phixs && nnlevel > 0)) return 0.;
-  const double sigma_bf = phixs_fromtable(c, c.st.cont_phixstable[i], nu_edge, nu);
+  return lo;
+}
+// One term of the sum for a continuum with nu >= nu_edge: returns kappa_bf_contr at frequency nu (0 if skipped);
+// *gcontr receives sigma_bf*probability*corrfactor (the gamma_contr of rpkt.cc:1158-1166) or 0.
+ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr) {
+  // every load is issued before the first use, and sigma_bf is interpolated even for a term that ends up skipped: the
+  // dependent nnlevel -> branch -> table row -> cross-section chain was the latency of the whole sum
+  const size_t ci = (size_t)tc * c.st.nbfcontinua + i;
+  const double nnlevel = c.tb.bf_nnlevel[ci];
+  const double depratio = c.tb.bf_depratio[ci];
+  const double nu_edge = c.st.cont_nu_edge[i];
+  const int tablerow = c.st.cont_phixstable[i];
   const double probability = c.st.cont_probability[i];
-  const double stimfactor = c.tb.bf_depratio[(size_t)tc * c.st.nbfcontinua + i] * expfac;  // expfac = exp(-h nu / k T_e)
+  const double sigma_bf = phixs_fromtable(c, tablerow, nu_edge, nu);
+  const double nu_max_phixs = nu_edge * c.st.last_phixs_nuovernuedge;
+  // nnlevel < 0: element absent / unimportant ion (rpkt.cc:1101-1104); otherwise rpkt.cc:1128
+  const bool counts = (nnlevel > 0.) && (nu <= nu_max_phixs);
+  const double stimfactor = depratio * expfac;  // expfac = exp(-h nu / k T_e)
   double corrfactor = 1 - stimfactor;
   if (corrfactor < 0) corrfactor = 0.;
-  *gcontr = sigma_bf * probability * corrfactor;
-  return nnlevel * sigma_bf * probability * corrfactor;
+  *gcontr = counts ? sigma_bf * probability * corrfactor : 0.;
+  return counts ? nnlevel * sigma_bf * probability * corrfactor : 0.;
+}
+// ground-continuum slot that term i feeds (rpkt.cc:1158), or -1
+ARTIS_DEV int kappa_bf_ground_slot(const Ctx &c, const int i) {
+  return (c.st.cont_level[i] == 0 && c.st.nbfcontinua_ground > 0) ? c.st.cont_index_in_groundphixslist[i] : -1;
 }
 
+// Summation order: the terms are added in tiles of BF_TILE consecutive continua, each tile reduced as a binary tree
+// (t[j] += t[j + off], off = 16, 8, 4, 2, 1) and the tile sums accumulated in order. This is the order a warp produces
+// with shuffle-xor reductions (transport.cu coop_kappa_warm); the host restatement uses the same order so that both
+// give the same bits. It differs from the reference's strictly serial sum by rounding only (~1e-16 relative, far
+// inside the 1e-10 tolerance on kappa_cont; checked against the reference probes in tests/).
+constexpr int BF_TILE = 32;
 ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, const double nu, KappaCache &k, Tally &tl) {
   double kappa_bf_sum = 0.;
   const int ng = c.st.nbfcontinua_ground;
   for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
   const int tc = tabcell(c, mgi);
   const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[mgi]);
-  const int nbf = c.st.nbfcontinua;
-  for (int i = 0; i < nbf; i++) {
-    bool stop = false;
-    double gcontr;
-    const double contr = kappa_bf_term(c, tc, i, nu, expfac, &gcontr, &stop);
-    if (stop) break;
-    tl.bf_evaluated++;
-    if (gcontr != 0. || contr != 0.) {
-      if (c.st.cont_level[i] == 0 && ng > 0) k.gamma_contr[c.st.cont_index_in_groundphixslist[i]] += gcontr;
-      kappa_bf_sum += contr;
+  const int i0 = bf_stop_index(c, nu);
+  tl.bf_evaluated += i0;
+  for (int base = 0; base < i0; base += BF_TILE) {
+    double t[BF_TILE];
+    for (int j = 0; j < BF_TILE; j++) {
+      const int i = base + j;
+      t[j] = 0.;
+      if (i < i0) {
+        double gcontr;
+        t[j] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr);
+        if (gcontr != 0.) {
+          const int slot = kappa_bf_ground_slot(c, i);
+          if (slot >= 0) k.gamma_contr[slot] += gcontr;
+        }
+      }
     }
+    for (int off = BF_TILE / 2; off >= 1; off >>= 1)
+      for (int j = 0; j < off; j++) t[j] += t[j + off];
+    kappa_bf_sum += t[0];
   }
   return kappa_bf_sum;
 }
 
-// rpkt.cc:1209-1309 calculate_kappa_rpkt_cont
-template <class P>
-ARTIS_DEV void calculate_kappa_rpkt_cont(const Ctx &c, const P &p, const int mgi, KappaCache &k, Tally &tl) {
-  const double nu_cmf = p.nu_cmf;
-  if (k.valid && (mgi == k.mgi) && (fabs(k.nu / nu_cmf - 1.0) < 1e-4)) return;
-  tl.kappa_evals++;
-  const float nne = c.cs.nne[mgi];
-  double sigma = 0.0, kappa_ff = 0., kappa_bf = 0., kappa_ffheating = 0.;
-  if (c.st.do_r_lc) {
-    if (c.st.opacity_case == 4) {
-      sigma = SIGMA_T * nne;
-      kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
-      kappa_ffheating = kappa_ff;
-      kappa_bf = calculate_kappa_bf_gammacontr(c, mgi, nu_cmf, k, tl);
-    } else {
-      sigma = 0.;
-      kappa_ff = 1e5 * calculate_kappa_ff(c, mgi, nu_cmf);
-      kappa_bf = 0.;
-    }
-  }
+// rpkt.cc:1209-1309 calculate_kappa_rpkt_cont, in pieces: cache test, the cheap terms, the bf sum, the bookkeeping
+ARTIS_DEV bool kappa_cache_hit(const KappaCache &k, const int mgi, const double nu_cmf) {
+  return k.valid && (mgi == k.mgi) && (fabs(k.nu / nu_cmf - 1.0) < 1e-4);
+}
+ARTIS_DEV void kappa_store(const Ctx &c, KappaCache &k, const int mgi, const double nu_cmf, const double sigma, const double kappa_ff,
+                           const double kappa_bf, const double kappa_ffheating, Tally &tl) {
   k.nu = nu_cmf;
   k.mgi = mgi;
   k.valid = true;
@@ -273,6 +291,27 @@ ARTIS_DEV void calculate_kappa_rpkt_cont(const Ctx &c, const P &p, const int mgi
       fatal(c, 101);
     }
   }
+}
+template <class P>
+ARTIS_DEV void calculate_kappa_rpkt_cont(const Ctx &c, const P &p, const int mgi, KappaCache &k, Tally &tl) {
+  const double nu_cmf = p.nu_cmf;
+  if (kappa_cache_hit(k, mgi, nu_cmf)) return;
+  tl.kappa_evals++;
+  const float nne = c.cs.nne[mgi];
+  double sigma = 0.0, kappa_ff = 0., kappa_bf = 0., kappa_ffheating = 0.;
+  if (c.st.do_r_lc) {
+    if (c.st.opacity_case == 4) {
+      sigma = SIGMA_T * nne;
+      kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
+      kappa_ffheating = kappa_ff;
+      kappa_bf = calculate_kappa_bf_gammacontr(c, mgi, nu_cmf, k, tl);
+    } else {
+      sigma = 0.;
+      kappa_ff = 1e5 * calculate_kappa_ff(c, mgi, nu_cmf);
+      kappa_bf = 0.;
+    }
+  }
+  kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ffheating, tl);
 }
 
 // ---- rpkt.cc:67-328 get_event ---------------------------------------------------------------------------------------

@@ -19,7 +19,8 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
   const bool kv = k.valid && (k.mgi == mgi);
   est_add(&c.es.ffheatingestimator[mgi], distance_e_cmf * (kv ? k.ffheating : 0.));
   tl.estim_atomics += 3;
-  if (!c.st.opt_no_lut_photoion || !c.st.opt_no_lut_bfheating) {
+  // without a valid opacity scratch for this cell every contribution below is +0.0: nothing to add (grey cells)
+  if (kv && (!c.st.opt_no_lut_photoion || !c.st.opt_no_lut_bfheating)) {
     const int nelements = c.st.nelements, max_nions = c.st.max_nions;
     const double distance_e_cmf_over_nu = distance_e_cmf / nu;
     const int ng = c.st.nbfcontinua_ground;
@@ -30,7 +31,8 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
         if (elem_abundance(c, mgi, element) > 0) {
           const int ion = c.st.gcont_ion[i];
           const int ionestimindex = mgi * nelements * max_nions + element * max_nions + ion;
-          const double contr = kv ? k.gamma_contr[i] : 0.;
+          const double contr = k.gamma_contr[i];
+          if (contr == 0.) continue;  // adds +0.0 to both estimators
           if (!c.st.opt_no_lut_photoion) {
             est_add(&c.es.gammaestimator[ionestimindex], contr * distance_e_cmf_over_nu);
             tl.estim_atomics++;
@@ -293,23 +295,16 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
     const int nbf = c.st.nbfcontinua;
     int allcontindex = nbf - 1;
     double sum = 0.;
-    bool stopped = false;
-    for (int i = 0; i < nbf - 1; i++) {
-      if (!stopped) {
-        bool stop = false;
-        double gcontr;
-        const double contr = kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr, &stop);
-        if (stop)
-          stopped = true;
-        else
-          sum += contr;
-      }
+    // entries at and beyond the stop index all equal the last sum (rpkt.cc:1117-1125), so only i < i0 can be selected
+    // before lower_bound runs off the end -- except that an all-zero list with a zero draw selects entry 0
+    const int i0 = bf_stop_index(c, k.nu);
+    const int lim = i0 < nbf - 1 ? i0 : nbf - 1;
+    if (lim == 0 && nbf > 1 && !(sum < kappa_bf_rand)) allcontindex = 0;
+    for (int i = 0; i < lim; i++) {
+      double gcontr;
+      sum += kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr);
       if (!(sum < kappa_bf_rand)) {
         allcontindex = i;
-        break;
-      }
-      if (stopped) {  // remaining entries all equal `sum` < kappa_bf_rand: lower_bound returns the end pointer
-        allcontindex = nbf - 1;
         break;
       }
     }
@@ -370,19 +365,24 @@ ARTIS_DEV void rpkt_event_thickcell(const Ctx &c, ArtisPacket &p, Rng &rng, Tall
 // ---- rpkt.cc:623-813 do_rpkt_step ----------------------------------------------------------------------------------------
 // returns true while the packet is still an r-packet inside its time step (the reference additionally stops at a
 // model-cell change because of its cellhistory cache; the wavefront scheduler decides that)
-// MODE 0: any cell; 1: the caller guarantees a non-grey, non-empty cell; 2: the caller guarantees a grey or empty cell
-// (the scheduler's two r-packet kinds, kernels.cuh) -- only prunes code, the arithmetic is the same.
+// The step is written in two halves so that a scheduler can evaluate the continuum opacity between them with a whole
+// warp (transport.cu coop_kappa_warm): rpkt_step_begin runs up to the point where get_event needs kappa and returns
+// false when the step is already over (cell change at zero distance, fatal geometry); rpkt_step_finish is the rest.
+struct RpktStepState {
+  int mgi, snext;
+  double tau_next, sdist;
+};
 template <int MODE = 0>
-ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
+ARTIS_DEV bool rpkt_step_begin(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl, RpktStepState &st) {
   tl.rpkt_steps++;
-  int mgi = cell_mgi(c, p.where);
+  st.mgi = cell_mgi(c, p.where);
   const double zrand = rng_uniform_pos(rng);
-  const double tau_next = -1. * log(zrand);
+  st.tau_next = -1. * log(zrand);
   int snext = 0;
   double sdist = boundary_cross(c, p, &snext);
   if (sdist == 0) {
     change_cell(c, p, snext, tl);
-    return p.type == ARTIS_TYPE_RPKT;
+    return false;
   }
   const double maxsdist = c.st.rmax * p.prop_time / c.st.tmin;
   if (sdist > maxsdist) {
@@ -399,6 +399,17 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
     sdist = c.cs.max_path_step;
     snext = p.where;
   }
+  st.sdist = sdist;
+  st.snext = snext;
+  return true;
+}
+template <int MODE = 0>
+ARTIS_DEV bool rpkt_step_finish(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl,
+                                const RpktStepState &st) {
+  int mgi = st.mgi;
+  const double tau_next = st.tau_next;
+  const double sdist = st.sdist;
+  const int snext = st.snext;
   const double tdist = (t2 - p.prop_time) * CLIGHT_PROP;
   double edist;
   int rpkt_eventtype = RPKT_EVENTTYPE_NONE;
@@ -421,11 +432,35 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
     }
   }
   const bool do_rlc = (c.cs.do_rlc_est != 0 && c.cs.do_rlc_est != 3);
+  // rpkt.cc:700-810: the three outcomes (cell boundary, event, end of the time step) all begin with the same half move,
+  // estimator update and second half move over the shortest of the three distances; it is written once here so that the
+  // lanes of a warp stay converged through it whatever their outcome is.
+  int outcome;  // 0 boundary, 1 event, 2 end of time step
+  double dist;
   if ((sdist < tdist) && (sdist < edist)) {
-    move_pkt_withtime(c, p, sdist / 2.);
-    update_estimators(c, p, sdist, k, tl);
-    if (do_rlc) rlc_emiss_rpkt(c, p, sdist, tl);
-    move_pkt_withtime(c, p, sdist / 2.);
+    outcome = 0;
+    dist = sdist;
+  } else if ((edist < sdist) && (edist < tdist)) {
+    outcome = 1;
+    dist = edist;
+  } else if ((tdist < sdist) && (tdist < edist)) {
+    outcome = 2;
+    dist = tdist;
+  } else {
+    fatal(c, 107);  // exact tie: the reference aborts
+    p.type = ARTIS_TYPE_ESCAPE;
+    return false;
+  }
+  move_pkt_withtime(c, p, dist / 2.);
+  update_estimators(c, p, dist, k, tl);
+  if (do_rlc) rlc_emiss_rpkt(c, p, dist, tl);
+  if (outcome == 2) {
+    p.prop_time = t2;
+    move_pkt(c, p, dist / 2.);
+  } else {
+    move_pkt_withtime(c, p, dist / 2.);
+  }
+  if (outcome == 0) {
     if (snext != p.where) {
       change_cell(c, p, snext, tl);
       mgi = cell_mgi(c, p.where);
@@ -436,11 +471,8 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
       if (p.type == ARTIS_TYPE_RPKT && mgi != c.st.npts_model && c.cs.thick[mgi] != 1) closest_transition_empty(c, p);
     }
     return p.type == ARTIS_TYPE_RPKT;
-  } else if ((edist < sdist) && (edist < tdist)) {
-    move_pkt_withtime(c, p, edist / 2.);
-    update_estimators(c, p, edist, k, tl);
-    if (do_rlc) rlc_emiss_rpkt(c, p, edist, tl);
-    move_pkt_withtime(c, p, edist / 2.);
+  }
+  if (outcome == 1) {
     if (thick) {
       rpkt_event_thickcell(c, p, rng, tl);
     } else if (rpkt_eventtype == RPKT_EVENTTYPE_BB) {
@@ -451,19 +483,18 @@ ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, Kappa
       fatal(c, 106);
     }
     return p.type == ARTIS_TYPE_RPKT;
-  } else if ((tdist < sdist) && (tdist < edist)) {
-    move_pkt_withtime(c, p, tdist / 2.);
-    update_estimators(c, p, tdist, k, tl);
-    if (do_rlc) rlc_emiss_rpkt(c, p, tdist, tl);
-    p.prop_time = t2;
-    move_pkt(c, p, tdist / 2.);
-    p.last_event = p.last_event + 1000;
-    if (find_nextline) closest_transition_empty(c, p);
-    return false;
   }
-  fatal(c, 107);  // exact tie: the reference aborts
-  p.type = ARTIS_TYPE_ESCAPE;
+  p.last_event = p.last_event + 1000;
+  if (find_nextline) closest_transition_empty(c, p);
   return false;
+}
+// MODE 0: any cell; 1: the caller guarantees a non-grey, non-empty cell; 2: the caller guarantees a grey or empty cell
+// (the scheduler's two r-packet kinds, kernels.cuh) -- only prunes code, the arithmetic is the same.
+template <int MODE = 0>
+ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
+  RpktStepState st;
+  if (!rpkt_step_begin<MODE>(c, p, rng, tl, st)) return p.type == ARTIS_TYPE_RPKT;
+  return rpkt_step_finish<MODE>(c, p, t2, k, rng, tl, st);
 }
 
 }  // namespace artis

@@ -21,6 +21,7 @@ __constant__ artis::Ctx d_ctx;
 
 constexpr int SM_COUNT_B200 = 148;
 
+
 __global__ void k_levelpop(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_levelpop(d_ctx, i);
@@ -61,7 +62,17 @@ struct PersistView {
   unsigned long long *tail;  // [NKIND]
   int *n_active;             // packets that have not finished the timestep
   int cap;
+  double *kcache;            // [cap][kstride] continuum-opacity cache of a packet handed over in mid-visit
+  int *kflag;                // [cap] 1 when kcache holds that packet's cache
+  int kstride;
 };
+// A warp whose ring has run dry and that is left with at most this many busy lanes hands those packets back to the ring
+// (to be absorbed by the idle lanes of other warps of the same kind) and takes up a kind that has work for all 32 lanes.
+#ifndef ARTIS_CONSOLIDATE_MAX_BUSY
+#define ARTIS_CONSOLIDATE_MAX_BUSY -1  /* off: measured no gain on the bench workload (profiles/r1_notes.md) */
+#endif
+constexpr int CONSOLIDATE_MAX_BUSY = ARTIS_CONSOLIDATE_MAX_BUSY;
+constexpr long long CONSOLIDATE_MIN_BACKLOG = 64;
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
   return *reinterpret_cast<const volatile unsigned long long *>(p);
@@ -85,10 +96,98 @@ __device__ __forceinline__ void packet_store_cg(ArtisPacket *dst, const ArtisPac
   for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) __stcg(d + i, s[i]);
 }
 
-#ifndef ARTIS_PERSIST_MINBLOCKS
-#define ARTIS_PERSIST_MINBLOCKS 2
+// Warp-cooperative continuum opacity (K2): every lane that is about to need kappa_cont for its own packet and misses its
+// cache ("owner") gets its bound-free sum evaluated by all 32 lanes, a tile of 32 consecutive continua at a time --
+// coalesced reads of the per-cell table rows, no dependence between tiles, and the step's latency no longer grows with
+// the number of continua below the packet's frequency (up to all 3204 for a UV packet, on one lane before). The result
+// is left in the owner's cache exactly as calculate_kappa_rpkt_cont would leave it, so the unchanged get_event that
+// follows finds a hit. Summation order = rpkt.cuh BF_TILE trees, the same as the host restatement.
+static_assert(artis::BF_TILE == 32, "one continuum per lane");
+constexpr int COOP_UNROLL = 4;
+#ifndef ARTIS_COOP_MAX_OWNERS
+#define ARTIS_COOP_MAX_OWNERS 8
 #endif
-__global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
+constexpr int COOP_MAX_OWNERS = ARTIS_COOP_MAX_OWNERS;
+__device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool wants, const int mgi, const double nu_cmf,
+                                                artis::KappaCache &k, artis::Tally &tl) {
+  using namespace artis;
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const bool need = wants && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, mgi, nu_cmf);
+  unsigned owners = __ballot_sync(full, need);
+  // With many owners the per-lane evaluation inside get_event has the better throughput (32 sums advance at once);
+  // the cooperative form is for sparsely filled warps, where it cuts the latency of the step (the tail of a timestep).
+  if (owners == 0u || __popc(owners) > COOP_MAX_OWNERS) return;
+  double sigma = 0., kappa_ff = 0., kappa_bf = 0.;
+  if (need) {
+    tl.kappa_evals++;
+    sigma = SIGMA_T * c.cs.nne[mgi];
+    kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
+    const int ng = c.st.nbfcontinua_ground;
+    for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
+  }
+  const int nbf = c.st.nbfcontinua;
+  while (owners != 0u) {
+    const int owner = __ffs(owners) - 1;
+    owners &= owners - 1u;
+    const double nu = __shfl_sync(full, nu_cmf, owner);
+    const int omgi = __shfl_sync(full, mgi, owner);
+    const int tc = tabcell(c, omgi);
+    const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[omgi]);
+    const int i0 = bf_stop_index(c, nu);
+    double sum = 0.;
+    for (int base = 0; base < i0; base += BF_TILE * COOP_UNROLL) {
+      // COOP_UNROLL tiles in flight per lane: their loads overlap, their trees interleave; tile sums are still added
+      // in tile order
+      double t[COOP_UNROLL], gcontr[COOP_UNROLL];
+      int slot[COOP_UNROLL];
+#pragma unroll
+      for (int u = 0; u < COOP_UNROLL; u++) {
+        const int i = base + u * BF_TILE + lane;
+        t[u] = 0.;
+        gcontr[u] = 0.;
+        slot[u] = -1;
+        if (i < i0) t[u] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < COOP_UNROLL; u++) {
+        const int i = base + u * BF_TILE + lane;
+        if (gcontr[u] != 0.) slot[u] = kappa_bf_ground_slot(c, i);
+      }
+#pragma unroll
+      for (int off = BF_TILE / 2; off >= 1; off >>= 1) {
+#pragma unroll
+        for (int u = 0; u < COOP_UNROLL; u++) t[u] += __shfl_down_sync(full, t[u], off);
+      }
+#pragma unroll
+      for (int u = 0; u < COOP_UNROLL; u++) {
+        sum += t[u];  // lane 0 holds each tile sum in tree order; only lane 0's running sum is used
+        unsigned g = __ballot_sync(full, slot[u] >= 0);
+        while (g != 0u) {  // ground-continuum contributions, in index order like the serial loop
+          const int src = __ffs(g) - 1;
+          g &= g - 1u;
+          const double v = __shfl_sync(full, gcontr[u], src);
+          const int sl = __shfl_sync(full, slot[u], src);
+          if (lane == owner) k.gamma_contr[sl] += v;
+        }
+      }
+    }
+    sum = __shfl_sync(full, sum, 0);
+    if (lane == owner) {
+      kappa_bf = sum;
+      tl.bf_evaluated += i0;
+    }
+  }
+  (void)nbf;
+  if (need) kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ff, tl);
+}
+
+#ifndef ARTIS_ROLE_AFFINITY
+#define ARTIS_ROLE_AFFINITY 0
+#endif
+// about 250 registers per thread: 8 warps per SM, as two blocks of 4 or (with role affinity) one block of 8
+constexpr int PERSIST_THREADS = ARTIS_ROLE_AFFINITY ? 256 : 128;
+__global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
                                                                  long long max_events, unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;
@@ -105,8 +204,17 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
   ArtisPacket p;
   Rng rng;
   unsigned long long idle_since = 0ull;
+#if ARTIS_ROLE_AFFINITY
+  __shared__ int s_role;
+  if (threadIdx.x == 0) s_role = -1;
+  __syncthreads();
+#endif
+  long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
   while (true) {
     __syncwarp(full);
+#ifdef ARTIS_ROLE_CYCLES
+    const long long tr0 = clock64();
+#endif
     const unsigned need = __ballot_sync(full, !have);
     if (need != 0u) {
       if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
@@ -128,6 +236,20 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
         }
         best = __shfl_sync(full, best, 0);
         best_kind = __shfl_sync(full, best_kind, 0);
+        // Soft role affinity: the warps of a block (one block per SM) prefer the kind their neighbours are running as
+        // long as its ring has at least a warp's worth of work, so that an SM's instruction caches hold one kind's code.
+#if ARTIS_ROLE_AFFINITY
+        {
+          const int pref = *reinterpret_cast<volatile int *>(&s_role);
+          const long long pref_backlog = __shfl_sync(full, backlog, pref >= 0 ? pref : 0);
+          if (pref >= 0 && pref_backlog >= 32 && best > 0) {
+            best_kind = pref;
+            best = pref_backlog;
+          } else if (best > 0 && lane == 0) {
+            *reinterpret_cast<volatile int *>(&s_role) = best_kind;
+          }
+        }
+#endif
         if (best <= 0) {
           int left = 0;
           if (lane == 0) left = *reinterpret_cast<volatile int *>(pv.n_active);
@@ -141,7 +263,13 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
             if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
             break;
           }
+#ifdef ARTIS_ROLE_CYCLES
+          const long long ti0 = clock64();
+#endif
           __nanosleep(1000);
+#ifdef ARTIS_ROLE_CYCLES
+          (void)ti0;
+#endif
           continue;
         }
         role = best_kind;
@@ -176,15 +304,104 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
         packet_load_cg(p, pkts + idx);
         rng = rng_init(c, p.number, __ldcg(rngctr + idx));
         k.valid = false;
+        if (CONSOLIDATE_MAX_BUSY >= 0 && role == KIND_RPKT_THIN && __ldcg(pv.kflag + idx) != 0) {  // handed over in mid-visit: its cache comes along
+          const double *kc = pv.kcache + (size_t)idx * pv.kstride;
+          k.nu = __ldcg(kc + 0);
+          k.total = __ldcg(kc + 1);
+          k.es = __ldcg(kc + 2);
+          k.ff = __ldcg(kc + 3);
+          k.bf = __ldcg(kc + 4);
+          k.ffheating = __ldcg(kc + 5);
+          k.mgi = (int)__ldcg(kc + 6);
+          k.valid = true;
+          const int ng = c.st.nbfcontinua_ground;
+          for (int g = 0; g < ng; g++) k.gamma_contr[g] = __ldcg(kc + 8 + g);
+          __stcg(pv.kflag + idx, 0);
+        }
         events = 0;
         have = true;
       }
       if (need == full && take == 0) continue;  // lost the race for the last entries
+      if (CONSOLIDATE_MAX_BUSY >= 0 && take == 0 && __popc(~need) <= CONSOLIDATE_MAX_BUSY) {
+        long long other = 0;
+        if (lane < NKIND && lane != role) {
+          const unsigned long long h = ld_volatile_u64(pv.head + lane), t = ld_volatile_u64(pv.tail + lane);
+          other = t > h ? (long long)(t - h) : 0;
+        }
+#pragma unroll
+        for (int off = 4; off >= 1; off >>= 1) {
+          const long long o = __shfl_down_sync(full, other, off);
+          other = o > other ? o : other;
+        }
+        other = __shfl_sync(full, other, 0);
+        if (other >= CONSOLIDATE_MIN_BACKLOG) {
+          if (have) {
+            __stcg(rngctr + idx, (unsigned long long)rng.ctr);
+            packet_store_cg(pkts + idx, p);
+            if (role == KIND_RPKT_THIN && k.valid) {
+              double *kc = pv.kcache + (size_t)idx * pv.kstride;
+              __stcg(kc + 0, k.nu);
+              __stcg(kc + 1, k.total);
+              __stcg(kc + 2, k.es);
+              __stcg(kc + 3, k.ff);
+              __stcg(kc + 4, k.bf);
+              __stcg(kc + 5, k.ffheating);
+              __stcg(kc + 6, (double)k.mgi);
+              const int ng = c.st.nbfcontinua_ground;
+              for (int g = 0; g < ng; g++) __stcg(kc + 8 + g, k.gamma_contr[g]);
+              __stcg(pv.kflag + idx, 1);
+            }
+            __threadfence();
+          }
+          const unsigned m = __ballot_sync(full, have);
+          unsigned long long b = 0ull;
+          if (lane == 0) b = atomicAdd(pv.tail + role, (unsigned long long)__popc(m));
+          b = __shfl_sync(full, b, 0);
+          if (have) {
+            int *slot = pv.ring[role] + (size_t)((b + (unsigned long long)__popc(m & lt_mask)) % (unsigned long long)pv.cap);
+            while (atomicCAS(slot, -1, idx) != -1) {
+            }
+            have = false;
+            tl.handoffs++;
+          }
+          continue;  // the warp is idle now and picks the kind with the longest backlog
+        }
+      }
     }
     __syncwarp(full);
     bool done = false;
     int k2 = -1;
-    if (have) {
+    {
+      const unsigned busy = __ballot_sync(full, have);
+      if (lane == role) {  // lane k keeps the occupancy statistics of kind k
+        fill_iters++;
+#ifndef ARTIS_ROLE_CYCLES
+        fill_lanes += __popc(busy);
+#endif
+      }
+    }
+#ifdef ARTIS_ROLE_CYCLES
+    const long long tc0 = clock64();
+    if (lane == 3) {  // experiment: kind-3 slots hold the scheduling overhead (refill + previous push)
+      fill_lanes += tc0 - tr0;
+      fill_iters++;
+    }
+#endif
+#ifndef ARTIS_COOP_KAPPA
+#define ARTIS_COOP_KAPPA 1
+#endif
+    if (ARTIS_COOP_KAPPA && role == KIND_RPKT_THIN) {  // warp-uniform: the step in two halves around the cooperative opacity evaluation
+      RpktStepState st;
+      st.mgi = 0;
+      bool proceed = false;
+      if (have) {
+        tl.packet_updates++;
+        proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
+      }
+      coop_kappa_warm(c, proceed, st.mgi, p.nu_cmf, k, tl);
+      if (proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
+      if (have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
+    } else if (have) {
       switch (role) {  // warp-uniform
         case 0: do_packet_kind<0>(c, p, t2, k, rng, tl); break;
         case 1: do_packet_kind<1>(c, p, t2, k, rng, tl); break;
@@ -192,6 +409,8 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
         case 4: do_packet_kind<4>(c, p, t2, k, rng, tl); break;
         default: do_packet_kind<3>(c, p, t2, k, rng, tl); break;
       }
+    }
+    if (have) {
       events++;
       const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
       if (!(active && kind_of(c, p) == role && events < max_events)) {
@@ -204,6 +423,10 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
       }
     }
     __syncwarp(full);
+#ifdef ARTIS_ROLE_CYCLES
+    if (lane == role) fill_lanes += clock64() - tc0 - 27;  // experiment: slots 56.. hold cycles instead of busy lanes
+    const long long tp0 = clock64();
+#endif
     if (__ballot_sync(full, done) != 0u) {
 #pragma unroll
       for (int kk = 0; kk < NKIND; kk++) {
@@ -223,8 +446,18 @@ __global__ void __launch_bounds__(128, ARTIS_PERSIST_MINBLOCKS) k_transport_pers
       const unsigned fin = __ballot_sync(full, done && k2 < 0);
       if (fin != 0u && lane == __ffs(fin) - 1) atomicSub(pv.n_active, __popc(fin));
     }
+#ifdef ARTIS_ROLE_CYCLES
+    if (lane == 2) {  // experiment: kind-2 slots hold the push section
+      fill_lanes += clock64() - tp0;
+      fill_iters++;
+    }
+#endif
   }
   tally_flush(c, tl);
+  if (lane < NKIND && fill_iters > 0) {
+    ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + lane], fill_iters);
+    ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + lane], fill_lanes);
+  }
 }
 
 __global__ void k_bucket_hist(ArtisPacket *pkts, unsigned long long *rngctr, int n, int *counts) {
@@ -275,6 +508,10 @@ cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 int g_sms = SM_COUNT_B200;
 int g_transport_blocks_per_sm = 4;
 int g_persistent_blocks_per_sm = 2;
+int g_nbfcontinua_ground = 0;
+double *g_kcache = nullptr;
+int *g_kflag = nullptr;
+size_t g_kcache_doubles = 0;
 std::string g_async_err;
 
 void note(cudaError_t e, const char *what) {
@@ -301,7 +538,7 @@ bool be_select_device(int device, std::string *why) {
   int nb = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_wavefront<1>, 128, 0) == cudaSuccess && nb > 0)
     g_transport_blocks_per_sm = nb;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent, 128, 0) == cudaSuccess && nb > 0)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent, PERSIST_THREADS, 0) == cudaSuccess && nb > 0)
     g_persistent_blocks_per_sm = nb;  // the whole grid must be resident: idle warps wait for the others' packets
   if (g_stream == nullptr) {
     note(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -330,6 +567,7 @@ void be_d2h(void *d, const void *s, size_t n) {
 }
 void be_zero(void *p, size_t n) { note(cudaMemsetAsync(p, 0, n, g_stream), "memset"); }
 void be_set_ctx(const artis::Ctx &c) {
+  g_nbfcontinua_ground = c.st.nbfcontinua_ground;
   note(cudaMemcpyToSymbolAsync(d_ctx, &c, sizeof(c), 0, cudaMemcpyHostToDevice, g_stream), "ctx upload");
   note(cudaStreamSynchronize(g_stream), "ctx sync");
 }
@@ -388,8 +626,26 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
   pv.tail = pmeta + artis::NKIND;
   pv.n_active = reinterpret_cast<int *>(pmeta + 2 * artis::NKIND);
   pv.cap = cap;
+  const int kstride = 8 + g_nbfcontinua_ground;
+  if (CONSOLIDATE_MAX_BUSY >= 0 && (size_t)cap * kstride > g_kcache_doubles) {
+    if (g_kcache) cudaFree(g_kcache);
+    if (g_kflag) cudaFree(g_kflag);
+    g_kcache = nullptr;
+    g_kflag = nullptr;
+    g_kcache_doubles = 0;
+    if (cudaMalloc(&g_kcache, (size_t)cap * kstride * sizeof(double)) != cudaSuccess ||
+        cudaMalloc(&g_kflag, (size_t)cap * sizeof(int)) != cudaSuccess) {
+      note(cudaGetLastError(), "cudaMalloc (opacity cache side buffer)");
+      return true;  // be_sync reports the error
+    }
+    g_kcache_doubles = (size_t)cap * kstride;
+  }
+  if (g_kflag) note(cudaMemsetAsync(g_kflag, 0, (size_t)cap * sizeof(int), g_stream), "memset");
+  pv.kcache = g_kcache;
+  pv.kflag = g_kflag;
+  pv.kstride = kstride;
   const int grid = g_sms * g_persistent_blocks_per_sm;
-  k_transport_persistent<<<grid, 128, 0, g_stream>>>(p, r, pv, maxev, 20ull * 1000000000ull);
+  k_transport_persistent<<<grid, PERSIST_THREADS, 0, g_stream>>>(p, r, pv, maxev, 20ull * 1000000000ull);
   return true;
 }
 void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }

@@ -326,7 +326,9 @@ def main():
                            "atomic data replicated, one estimator all-reduce per step",
                            "l2": "per-step working set (304 B x packets + per-cell tables) exceeds the 126 MB L2",
                            "s_per_timestep": tot_ms / a.steps * 1e-3, "cell_precompute_ms": precompute_ms,
-                           "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps,
+                           "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps, "handoffs_per_step": float(ctr_sum[50]) / a.steps,
+                           "warp_iters_by_kind": [float(x) / a.steps for x in ctr_sum[51:56]],
+                           "mean_busy_lanes_by_kind": [round(float(ctr_sum[56 + i]) / max(float(ctr_sum[51 + i]), 1.0), 2) for i in range(5)],
                            "events_per_s": float(ctr_sum[49]) * world / (tot_ms * 1e-3)},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": None,

@@ -137,6 +137,9 @@ enum {
   ARTIS_CTR_SOFT_REPAIRS = 47,    /* clamps of SURVEY Q6 applied */
   ARTIS_CTR_KAPPA_EVALS = 48,     /* calculate_kappa_rpkt_cont recomputes (cache misses) */
   ARTIS_CTR_PACKET_UPDATES = 49,  /* do_packet calls */
+  ARTIS_CTR_HANDOFFS = 50,        /* packets handed back to their ring in mid-visit by a consolidating warp */
+  ARTIS_CTR_WARP_ITERS0 = 51,     /* [51,56): scheduler iterations a warp ran in kind 0..4 */
+  ARTIS_CTR_BUSY_LANES0 = 56,     /* [56,61): lanes holding a packet, summed over those iterations */
   ARTIS_CTR_COUNT = 64
 };
 

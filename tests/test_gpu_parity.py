@@ -118,3 +118,4 @@ def test_cuda_edge_cases_and_scale(gpu_lib):
     t2 = st["ts_start"][fx["nts"]] + st["ts_width"][fx["nts"]]
     assert ((big["type"] == abi.TYPE_ESCAPE) | (big["prop_time"] == t2)).all()
     T.finalize()
+
