@@ -103,9 +103,11 @@ ARTIS_DEV double calculate_sahafact_g(const Ctx &c, int gl_lower, int gl_upper, 
 }
 
 // atomic.cc:87-137 photoionization_crosssection_fromtable (phixsdata_v2 branch)
-ARTIS_DEV double phixs_fromtable(const Ctx &c, int tablerow, double nu_edge, double nu) {
+// inv_nu_edge: RN(1/nu_edge) when that gives an exact quotient (ContRec), or 0 for the plain division
+ARTIS_DEV double phixs_fromtable(const Ctx &c, int tablerow, double nu_edge, double nu, double inv_nu_edge = 0.) {
   const float *xs = c.st.phixs_tables + (size_t)tablerow * c.st.nphixspoints;
-  const double ireal = (nu / nu_edge - 1.0) / c.st.nphixsnuincrement;
+  const double ireal = div_by_known(div_by_known(nu, nu_edge, inv_nu_edge) - 1.0, c.st.nphixsnuincrement,
+                                    inv_nu_edge != 0. ? c.inv_nphixsnuincrement : 0.);
   const int i = (int)floor(ireal);
   float sigma_bf;
   if (i < 0) {

@@ -213,8 +213,8 @@ ARTIS_DEV void build_bf(const Ctx &c, const int mgi, const int i) {
       dep = nnupperionlevel / nnlevel * (double)c.cs.nne[mgi] * sf;
     }
   }
-  c.tb.bf_nnlevel[(size_t)tc * c.st.nbfcontinua + i] = nnlevel;
-  c.tb.bf_depratio[(size_t)tc * c.st.nbfcontinua + i] = dep;
+  c.tb.bf_cell[2 * ((size_t)tc * c.st.nbfcontinua + i)] = nnlevel;
+  c.tb.bf_cell[2 * ((size_t)tc * c.st.nbfcontinua + i) + 1] = dep;
 }
 
 // macroatom.cc:57-159 calculate_macroatom_transitionrates for one (cell, level)

@@ -53,11 +53,35 @@ enum { RPKT_EVENTTYPE_NONE = -1, RPKT_EVENTTYPE_BB = 550, RPKT_EVENTTYPE_CONT = 
 // the reference's per-thread `cellhistory` (globals.h:174-208): one row per non-empty model cell (index nonemptymgi)
 // instead of one cached cell per host thread. Prefix sums are accumulated in the reference's own summation order, so
 // a binary search over a row selects exactly what the reference's linear scans select.
+// Static data of one bound-free continuum as the opacity sum reads it: one 32-byte record instead of five arrays.
+// inv_nu_edge = RN(1/nu_edge) (an IEEE division on the host): with it nu/nu_edge is evaluated as
+//   q = nu * inv; r = fma(-nu_edge, q, nu); q' = fma(r, inv, q)
+// which is the correctly rounded quotient (Markstein's theorem: the reciprocal is correctly rounded and nu_edge's
+// significand is not all ones -- checked at init, the plain division is used otherwise), i.e. the same bits as
+// nu / nu_edge at a fifth of the instructions (no reciprocal seed, no Newton iterations).
+struct ContRec {
+  double nu_edge;
+  double inv_nu_edge;   // 0 when the fast quotient is not provably exact for this divisor
+  double probability;
+  int tablerow;
+  int ground_slot;      // index in the ground-continuum list if this is a ground-level continuum, else -1
+};
+// a / b given inv = RN(1/b), or the plain division when inv == 0
+ARTIS_DEV double div_by_known(const double a, const double b, const double inv) {
+  if (inv != 0.) {
+    const double q = a * inv;
+    const double r = fma(-b, q, a);
+    return fma(r, inv, q);
+  }
+  return a / b;
+}
+
 struct CellTables {
   int ncells;                // nonempty_npts_model
   double *levelpop;          // [ncells][nlevels_total]        calculate_levelpop (ltepop.cc:417)
-  double *bf_nnlevel;        // [ncells][nbfcontinua]          level pop of allcont[i], -1 if the continuum is skipped
-  double *bf_depratio;       // [ncells][nbfcontinua]          ch_allcont_departureratios (rpkt.cc:1136-1145)
+  // [ncells][nbfcontinua][2]: level pop of allcont[i] (-1 if the continuum is skipped) and its departure ratio
+  // (ch_allcont_departureratios, rpkt.cc:1136-1145), interleaved so that one 16-byte load brings both
+  double *bf_cell;
   double *ma_rates;          // [ncells][nlevels_total][9]     chlevels.processrates (macroatom.cc:57-159)
   double *ma_cum_raddeexc;   // [ncells][ndowntrans_total]     running sum of individ_rad_deexc
   double *ma_cum_intdown;    // [ncells][ndowntrans_total]     running sum of individ_internal_down_same
@@ -78,6 +102,10 @@ struct Ctx {
   const int *cont_upper_g;   // global level index of allcont[i] upper-ion level
   const int *cont_uion;      // unique ion index of allcont[i] lower ion
   const int *gcont_uion;     // unique ion index of groundcont[i]
+  const ContRec *cont_rec;   // packed static data of a bf continuum          [nbfcontinua]
+  double inv_nphixsnuincrement;  // RN(1 / NPHIXSNUINCREMENT), see ContRec
+  const int *downtrans_target_g;  // global level index a downward transition ends in   [ndowntrans_total]
+  const int *uptrans_target_g;    // global level index an upward transition ends in    [nuptrans_total]
   const int *lev_uion;       // unique ion index of a global level index      [nlevels_total]
   const int *uion_element;   // element index of a unique ion index           [includedions]
   const int *mgi_of_tabcell; // model grid index of a CellTables row           [tb.ncells]
@@ -285,7 +313,45 @@ ARTIS_DEV void scatter_dir(Rng &r, const double dir_in[3], const double cos_thet
 
 // ---- estimator / counter accumulation ------------------------------------------------------------------------
 #ifdef __CUDACC__
-ARTIS_DEV void est_add(double *addr, double v) { atomicAdd(addr, v); }
+// Block-private estimators. With a 1D model every packet of the timestep adds to the same ~100 cells' J / nuJ /
+// heating sums: hundreds of millions of FP64 atomics on a few hundred addresses, which serialise in L2 and back up the
+// load path behind them (profiles/r1_final: 47% of all long-scoreboard stalls sat behind them). A kernel that opts in
+// (est_private_begin) accumulates into a copy of the estimator block in its dynamic shared memory and adds that copy
+// to the global block once, at its end (est_private_flush). The copy is used only when the whole block fits.
+extern __shared__ double artis_est_smem[];
+__shared__ double *artis_est_global;   // global estimator block this copy shadows, nullptr = no private copy
+__shared__ unsigned artis_est_count;   // its length in doubles
+ARTIS_DEV void est_add(double *addr, double v) {
+  double *const base = artis_est_global;
+  if (base != nullptr) {
+    const unsigned long long off = (unsigned long long)(addr - base);
+    if (off < (unsigned long long)artis_est_count) {
+      atomicAdd(&artis_est_smem[off], v);
+      return;
+    }
+  }
+  atomicAdd(addr, v);
+}
+// all threads of the block call these; ndoubles == 0 selects plain global atomics
+ARTIS_DEV void est_private_begin(double *global_block, unsigned ndoubles) {
+  if (threadIdx.x == 0) {
+    artis_est_global = ndoubles > 0 ? global_block : nullptr;
+    artis_est_count = ndoubles;
+  }
+  for (unsigned i = threadIdx.x; i < ndoubles; i += blockDim.x) artis_est_smem[i] = 0.;
+  __syncthreads();
+}
+ARTIS_DEV void est_private_flush() {
+  __syncthreads();
+  double *const base = artis_est_global;
+  const unsigned n = artis_est_count;
+  if (base != nullptr) {
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
+      const double v = artis_est_smem[i];
+      if (v != 0.) atomicAdd(base + i, v);
+    }
+  }
+}
 ARTIS_DEV void ctr_add(long long *addr, long long v) { atomicAdd((unsigned long long *)addr, (unsigned long long)v); }
 ARTIS_DEV void int_add(int *addr, int v) { atomicAdd(addr, v); }
 ARTIS_DEV int int_fetch_add(int *addr, int v) { return atomicAdd(addr, v); }

@@ -18,16 +18,28 @@ ARTIS_DEV int bsearch_probes(int n) {
   return k;
 }
 // first index i in [0, n) with cum[i] > target, n if none
+// `cum` is a prefix sum of non-negative rates (non-decreasing), so the answer is unique and the search may probe in any
+// pattern. Eight-way: each round issues seven independent loads and keeps an eighth of the range, i.e. log8(n) round
+// trips to L2 instead of log2(n) dependent ones -- a macro-atom jump is a chain of such round trips and nothing else.
 ARTIS_DEV int first_greater(const double *cum, const int n, const double target) {
-  int lo = 0, hi = n;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (cum[mid] > target)
-      hi = mid;
-    else
-      lo = mid + 1;
+  int lo = 0, hi = n;  // the answer lies in [lo, hi]
+  while (hi - lo > 7) {
+    const int step = (hi - lo) >> 3;
+    int below = 0;  // pivots lo + j*step - 1, j = 1..7, that are <= target: a prefix of them
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+    for (int j = 1; j <= 7; j++) below += (cum[lo + j * step - 1] <= target) ? 1 : 0;
+    if (below < 7) hi = lo + (below + 1) * step - 1;
+    lo += below * step;
   }
-  return lo;
+  int below = 0;
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+  for (int j = 0; j < 7; j++)
+    if (lo + j < hi) below += (cum[lo + j] <= target) ? 1 : 0;
+  return lo + below;
 }
 
 // ratecoeff.cc:264-280 alpha_sp_E_integrand_gsl
@@ -233,7 +245,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       case MA_INTERNALDOWNSAME: {  // macroatom.cc:174-220
         p.interactions += 1;
         tl.interactions++;
-        gl = c.line_lower_g[c.st.downtrans_lineindex[toff + sel]];
+        gl = c.downtrans_target_g[toff + sel];
         break;
       }
       case MA_RADRECOMB: {  // macroatom.cc:298-380
@@ -311,7 +323,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       case MA_INTERNALUPSAME: {  // macroatom.cc:815-835
         p.interactions += 1;
         tl.interactions++;
-        gl = c.line_upper_g[c.st.uptrans_lineindex[toff + sel]];
+        gl = c.uptrans_target_g[toff + sel];
         break;
       }
       case MA_INTERNALUPHIGHER: {  // macroatom.cc:382-414 do_macroatom_ionisation

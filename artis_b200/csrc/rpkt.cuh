@@ -208,28 +208,41 @@ ARTIS_DEV int bf_stop_index(const Ctx &c, const double nu) {
 }
 // One term of the sum for a continuum with nu >= nu_edge: returns kappa_bf_contr at frequency nu (0 if skipped);
 // *gcontr receives sigma_bf*probability*corrfactor (the gamma_contr of rpkt.cc:1158-1166) or 0.
-ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr) {
+ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr,
+                               int *ground_slot = nullptr) {
   // every load is issued before the first use, and sigma_bf is interpolated even for a term that ends up skipped: the
   // dependent nnlevel -> branch -> table row -> cross-section chain was the latency of the whole sum
-  const size_t ci = (size_t)tc * c.st.nbfcontinua + i;
-  const double nnlevel = c.tb.bf_nnlevel[ci];
-  const double depratio = c.tb.bf_depratio[ci];
-  const double nu_edge = c.st.cont_nu_edge[i];
-  const int tablerow = c.st.cont_phixstable[i];
-  const double probability = c.st.cont_probability[i];
-  const double sigma_bf = phixs_fromtable(c, tablerow, nu_edge, nu);
-  const double nu_max_phixs = nu_edge * c.st.last_phixs_nuovernuedge;
+  const double *cell = c.tb.bf_cell + 2 * ((size_t)tc * c.st.nbfcontinua + i);
+  const double nnlevel = cell[0];
+  const double depratio = cell[1];
+  const ContRec r = c.cont_rec[i];
+  const double sigma_bf = phixs_fromtable(c, r.tablerow, r.nu_edge, nu, r.inv_nu_edge);
+  const double nu_max_phixs = r.nu_edge * c.st.last_phixs_nuovernuedge;
   // nnlevel < 0: element absent / unimportant ion (rpkt.cc:1101-1104); otherwise rpkt.cc:1128
   const bool counts = (nnlevel > 0.) && (nu <= nu_max_phixs);
   const double stimfactor = depratio * expfac;  // expfac = exp(-h nu / k T_e)
   double corrfactor = 1 - stimfactor;
   if (corrfactor < 0) corrfactor = 0.;
-  *gcontr = counts ? sigma_bf * probability * corrfactor : 0.;
-  return counts ? nnlevel * sigma_bf * probability * corrfactor : 0.;
+  *gcontr = counts ? sigma_bf * r.probability * corrfactor : 0.;
+  if (ground_slot != nullptr) *ground_slot = r.ground_slot;
+  return counts ? nnlevel * sigma_bf * r.probability * corrfactor : 0.;
 }
 // ground-continuum slot that term i feeds (rpkt.cc:1158), or -1
-ARTIS_DEV int kappa_bf_ground_slot(const Ctx &c, const int i) {
-  return (c.st.cont_level[i] == 0 && c.st.nbfcontinua_ground > 0) ? c.st.cont_index_in_groundphixslist[i] : -1;
+ARTIS_DEV int kappa_bf_ground_slot(const Ctx &c, const int i) { return c.cont_rec[i].ground_slot; }
+// A continuum also contributes nothing above the end of its cross-section table, nu > nu_edge * last_phixs_nuovernuedge
+// (rpkt.cc:1128): first index whose table still reaches nu. Everything below it is an exact zero and is not visited.
+ARTIS_DEV int bf_start_index(const Ctx &c, const double nu, const int i0) {
+  int lo = 0, hi = i0;
+  const double reach = c.st.last_phixs_nuovernuedge;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (nu <= c.st.cont_nu_edge[mid] * reach) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
+  }
+  return lo;
 }
 
 // Summation order: the terms are added in tiles of BF_TILE consecutive continua, each tile reduced as a binary tree
@@ -245,19 +258,22 @@ ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, cons
   const int tc = tabcell(c, mgi);
   const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[mgi]);
   const int i0 = bf_stop_index(c, nu);
-  tl.bf_evaluated += i0;
-  for (int base = 0; base < i0; base += BF_TILE) {
+  const int ilo = bf_start_index(c, nu, i0);
+  tl.bf_evaluated += i0 - ilo;
+  for (int base = ilo; base < i0; base += BF_TILE) {
     double t[BF_TILE];
+    // the terms of a tile are independent: four in flight per lane so that their table loads overlap
+#ifdef __CUDA_ARCH__
+#pragma unroll 4
+#endif
     for (int j = 0; j < BF_TILE; j++) {
       const int i = base + j;
       t[j] = 0.;
       if (i < i0) {
         double gcontr;
-        t[j] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr);
-        if (gcontr != 0.) {
-          const int slot = kappa_bf_ground_slot(c, i);
-          if (slot >= 0) k.gamma_contr[slot] += gcontr;
-        }
+        int slot;
+        t[j] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr, &slot);
+        if (gcontr != 0. && slot >= 0) k.gamma_contr[slot] += gcontr;
       }
     }
     for (int off = BF_TILE / 2; off >= 1; off >>= 1)

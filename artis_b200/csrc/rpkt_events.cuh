@@ -299,13 +299,17 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
     // before lower_bound runs off the end -- except that an all-zero list with a zero draw selects entry 0
     const int i0 = bf_stop_index(c, k.nu);
     const int lim = i0 < nbf - 1 ? i0 : nbf - 1;
-    if (lim == 0 && nbf > 1 && !(sum < kappa_bf_rand)) allcontindex = 0;
-    for (int i = 0; i < lim; i++) {
-      double gcontr;
-      sum += kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr);
-      if (!(sum < kappa_bf_rand)) {
-        allcontindex = i;
-        break;
+    if (nbf > 1 && !(sum < kappa_bf_rand)) {
+      allcontindex = 0;  // a zero draw selects the first entry whatever it holds
+    } else {
+      // entries below the table-reach window are exact zeros (bf_start_index): the running sum starts there
+      for (int i = bf_start_index(c, k.nu, i0); i < lim; i++) {
+        double gcontr;
+        sum += kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr);
+        if (!(sum < kappa_bf_rand)) {
+          allcontindex = i;
+          break;
+        }
       }
     }
     const double nu_edge = c.st.cont_nu_edge[allcontindex];

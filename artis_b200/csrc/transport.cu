@@ -42,6 +42,7 @@ __global__ void k_cool(long long n) {
 template <int KIND>
 __global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned long long *rngctr, artis::QueueView qv,
                                                    long long max_events) {
+  artis::est_private_begin(nullptr, 0u);
   artis::body_wavefront<KIND>(d_ctx, pkts, rngctr, qv, max_events);
 }
 // ---- barrier-free scheduler ------------------------------------------------------------------------------------------
@@ -61,10 +62,14 @@ struct PersistView {
   unsigned long long *head;  // [NKIND]
   unsigned long long *tail;  // [NKIND]
   int *n_active;             // packets that have not finished the timestep
+  int n_initial;             // its value at launch
+  unsigned long long *t_start;  // globaltimer at launch (written by thread 0 of block 0)
   int cap;
   double *kcache;            // [cap][kstride] continuum-opacity cache of a packet handed over in mid-visit
   int *kflag;                // [cap] 1 when kcache holds that packet's cache
   int kstride;
+  double *est_block;         // global estimator block and the length of its block-private copy (0 = none)
+  unsigned est_private_doubles;
 };
 // A warp whose ring has run dry and that is left with at most this many busy lanes hands those packets back to the ring
 // (to be absorbed by the idle lanes of other warps of the same kind) and takes up a kind that has work for all 32 lanes.
@@ -135,8 +140,9 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
     const int tc = tabcell(c, omgi);
     const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[omgi]);
     const int i0 = bf_stop_index(c, nu);
+    const int ilo = bf_start_index(c, nu, i0);
     double sum = 0.;
-    for (int base = 0; base < i0; base += BF_TILE * COOP_UNROLL) {
+    for (int base = ilo; base < i0; base += BF_TILE * COOP_UNROLL) {
       // COOP_UNROLL tiles in flight per lane: their loads overlap, their trees interleave; tile sums are still added
       // in tile order
       double t[COOP_UNROLL], gcontr[COOP_UNROLL];
@@ -147,12 +153,11 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
         t[u] = 0.;
         gcontr[u] = 0.;
         slot[u] = -1;
-        if (i < i0) t[u] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr[u]);
-      }
-#pragma unroll
-      for (int u = 0; u < COOP_UNROLL; u++) {
-        const int i = base + u * BF_TILE + lane;
-        if (gcontr[u] != 0.) slot[u] = kappa_bf_ground_slot(c, i);
+        if (i < i0) {
+          int sl;
+          t[u] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr[u], &sl);
+          if (gcontr[u] != 0.) slot[u] = sl;
+        }
       }
 #pragma unroll
       for (int off = BF_TILE / 2; off >= 1; off >>= 1) {
@@ -175,7 +180,7 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
     sum = __shfl_sync(full, sum, 0);
     if (lane == owner) {
       kappa_bf = sum;
-      tl.bf_evaluated += i0;
+      tl.bf_evaluated += i0 - ilo;
     }
   }
   (void)nbf;
@@ -204,6 +209,8 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) 
   ArtisPacket p;
   Rng rng;
   unsigned long long idle_since = 0ull;
+  est_private_begin(pv.est_block, pv.est_private_doubles);
+  if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
 #if ARTIS_ROLE_AFFINITY
   __shared__ int s_role;
   if (threadIdx.x == 0) s_role = -1;
@@ -382,6 +389,8 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) 
     }
 #ifdef ARTIS_ROLE_CYCLES
     const long long tc0 = clock64();
+#endif
+#if defined(ARTIS_ROLE_CYCLES) && !defined(ARTIS_ROLE_CYCLES2)
     if (lane == 3) {  // experiment: kind-3 slots hold the scheduling overhead (refill + previous push)
       fill_lanes += tc0 - tr0;
       fill_iters++;
@@ -398,7 +407,25 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) 
         tl.packet_updates++;
         proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
       }
+#ifdef ARTIS_ROLE_CYCLES2
+      const long long tb1 = clock64();
+#endif
       coop_kappa_warm(c, proceed, st.mgi, p.nu_cmf, k, tl);
+#ifdef ARTIS_ROLE_CYCLES2
+      const long long tb2 = clock64();
+      if (proceed) calculate_kappa_rpkt_cont(c, p, st.mgi, k, tl);  // what get_event would do first
+      __syncwarp(full);
+      const long long tb3 = clock64();
+      if (lane == 2) {  // kind-2 slots: begin + coop; kind-3 slots: per-lane kappa
+        fill_lanes += tb2 - tc0;
+        fill_iters++;
+      }
+      if (lane == 3) {
+        fill_lanes += tb3 - tb2;
+        fill_iters++;
+      }
+      (void)tb1;
+#endif
       if (proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
       if (have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
     } else if (have) {
@@ -444,9 +471,18 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) 
         }
       }
       const unsigned fin = __ballot_sync(full, done && k2 < 0);
-      if (fin != 0u && lane == __ffs(fin) - 1) atomicSub(pv.n_active, __popc(fin));
+      if (fin != 0u && lane == __ffs(fin) - 1) {
+        const int nfin = __popc(fin);
+        const int before = atomicSub(pv.n_active, nfin), after = before - nfin;
+        // drain profile: when the active count falls through 10%, 1% and 0 of its initial value (ns since launch)
+        const int n0 = pv.n_initial;
+        const long long now = (long long)(global_ns() - *reinterpret_cast<volatile unsigned long long *>(pv.t_start));
+        if (before > n0 / 10 && after <= n0 / 10) c.es.counters[ARTIS_CTR_DRAIN_NS_10PCT] = now;
+        if (before > n0 / 100 && after <= n0 / 100) c.es.counters[ARTIS_CTR_DRAIN_NS_1PCT] = now;
+        if (after <= 0) c.es.counters[ARTIS_CTR_DRAIN_NS_DONE] = now;
+      }
     }
-#ifdef ARTIS_ROLE_CYCLES
+#if defined(ARTIS_ROLE_CYCLES) && !defined(ARTIS_ROLE_CYCLES2)
     if (lane == 2) {  // experiment: kind-2 slots hold the push section
       fill_lanes += clock64() - tp0;
       fill_iters++;
@@ -454,6 +490,7 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) 
 #endif
   }
   tally_flush(c, tl);
+  est_private_flush();
   if (lane < NKIND && fill_iters > 0) {
     ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + lane], fill_iters);
     ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + lane], fill_lanes);
@@ -509,6 +546,9 @@ int g_sms = SM_COUNT_B200;
 int g_transport_blocks_per_sm = 4;
 int g_persistent_blocks_per_sm = 2;
 int g_nbfcontinua_ground = 0;
+double *g_est_block = nullptr;
+size_t g_est_ndoubles = 0, g_persistent_smem_bytes = 0;
+constexpr size_t g_est_private_max_bytes = 100 * 1024;
 double *g_kcache = nullptr;
 int *g_kflag = nullptr;
 size_t g_kcache_doubles = 0;
@@ -619,12 +659,15 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
 }
 // barrier-free scheduler: rings = NKIND rings of `cap` ints (initial entries written by be_run_bucket, -1 elsewhere),
 // pmeta = head[NKIND], tail[NKIND], n_active (int)
-bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int cap, unsigned long long *pmeta, long long maxev) {
+bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int cap, unsigned long long *pmeta, int n_initial,
+                       long long maxev) {
   PersistView pv;
   for (int k = 0; k < artis::NKIND; k++) pv.ring[k] = rings + (size_t)k * cap;
   pv.head = pmeta;
   pv.tail = pmeta + artis::NKIND;
   pv.n_active = reinterpret_cast<int *>(pmeta + 2 * artis::NKIND);
+  pv.n_initial = n_initial;
+  pv.t_start = pmeta + 2 * artis::NKIND + 1;
   pv.cap = cap;
   const int kstride = 8 + g_nbfcontinua_ground;
   if (CONSOLIDATE_MAX_BUSY >= 0 && (size_t)cap * kstride > g_kcache_doubles) {
@@ -644,11 +687,29 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
   pv.kcache = g_kcache;
   pv.kflag = g_kflag;
   pv.kstride = kstride;
+  // block-private estimators when the block fits next to a second resident CTA (227 KB per SM, 1 KB reserved each)
+  size_t est_bytes = g_est_ndoubles * sizeof(double);
+  if (est_bytes > g_est_private_max_bytes) est_bytes = 0;
+  pv.est_block = g_est_block;
+  pv.est_private_doubles = (unsigned)(est_bytes / sizeof(double));
+  if (est_bytes != g_persistent_smem_bytes) {
+    note(cudaFuncSetAttribute(k_transport_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)est_bytes),
+         "cudaFuncSetAttribute");
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent, PERSIST_THREADS, est_bytes) ==
+            cudaSuccess && nb > 0)
+      g_persistent_blocks_per_sm = nb;
+    g_persistent_smem_bytes = est_bytes;
+  }
   const int grid = g_sms * g_persistent_blocks_per_sm;
-  k_transport_persistent<<<grid, PERSIST_THREADS, 0, g_stream>>>(p, r, pv, maxev, 20ull * 1000000000ull);
+  k_transport_persistent<<<grid, PERSIST_THREADS, est_bytes, g_stream>>>(p, r, pv, maxev, 20ull * 1000000000ull);
   return true;
 }
 void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }
+void be_set_estimator_block(double *block, size_t ndoubles) {
+  g_est_block = block;
+  g_est_ndoubles = ndoubles;
+}
 #define PROBE_GRID(n) ((n) + 127) / 128, 128, 0, g_stream
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) { k_probe_boundary<<<PROBE_GRID(n)>>>(p, n, a, b, c); }
 void be_run_probe_kappa(const ArtisPacket *p, int n, double *k) { k_probe_kappa<<<PROBE_GRID(n)>>>(p, n, k); }

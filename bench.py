@@ -70,6 +70,16 @@ def replicate(pre, P, rank, step):
     return out
 
 
+def measured_traffic(packets):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one transport launch from the committed ncu capture, when that
+    capture was taken at this packet count; None otherwise (the number is not measured under this run)"""
+    try:
+        t = json.load(open(os.path.join(REPO, "profiles", "r1_final_traffic.json")))
+        return float(t["dram_bytes_per_launch"]) if int(t["packets_per_gpu"]) == int(packets) else None
+    except Exception:
+        return None
+
+
 def algorithmic_bytes(ctr):
     """B = 208 n_rpkt_step + 8 n_scan + 64 n_tau + 80 n_bf + 16 n_est + (72 n_ma_jump + 8 n_ma_probe)
     + (72 n_kpkt + 8 n_cool_probe) + 240 n_gamma_step, all exact device counters of the timed steps."""
@@ -327,13 +337,17 @@ def main():
                            "l2": "per-step working set (304 B x packets + per-cell tables) exceeds the 126 MB L2",
                            "s_per_timestep": tot_ms / a.steps * 1e-3, "cell_precompute_ms": precompute_ms,
                            "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps, "handoffs_per_step": float(ctr_sum[50]) / a.steps,
+                           "drain_ms_to_10pct_1pct_done": [round(float(c[61 + i]) * 1e-6, 1) for i in range(3)],
                            "warp_iters_by_kind": [float(x) / a.steps for x in ctr_sum[51:56]],
                            "mean_busy_lanes_by_kind": [round(float(ctr_sum[56 + i]) / max(float(ctr_sum[51 + i]), 1.0), 2) for i in range(5)],
                            "events_per_s": float(ctr_sum[49]) * world / (tot_ms * 1e-3)},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None,
+                             "frac": achieved / peak, "traffic": measured_traffic(P),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6537.6",
-                             "kernel": "k_transport", "algorithmic_bytes_per_step": alg_bytes / a.steps},
+                             "kernel": "k_transport_persistent", "launches_per_step": 1,
+                             "algorithmic_bytes_per_launch": alg_bytes / a.steps,
+                             "traffic_source": "profiles/r1_final_traffic.json (ncu dram bytes per launch at this packet "
+                                               "count; null at other counts)"},
                 "e2e": {"value": e2e_inter / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                         "d2h_bytes_per_step": nbytes + ndoubles * 8},
                 "gpu_launches": int(launches), "clocks": sampler.summary()}

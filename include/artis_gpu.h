@@ -140,6 +140,9 @@ enum {
   ARTIS_CTR_HANDOFFS = 50,        /* packets handed back to their ring in mid-visit by a consolidating warp */
   ARTIS_CTR_WARP_ITERS0 = 51,     /* [51,56): scheduler iterations a warp ran in kind 0..4 */
   ARTIS_CTR_BUSY_LANES0 = 56,     /* [56,61): lanes holding a packet, summed over those iterations */
+  ARTIS_CTR_DRAIN_NS_10PCT = 61,  /* ns from the transport launch until 10% / 1% / none of the packets are still active */
+  ARTIS_CTR_DRAIN_NS_1PCT = 62,
+  ARTIS_CTR_DRAIN_NS_DONE = 63,
   ARTIS_CTR_COUNT = 64
 };
 

@@ -152,3 +152,15 @@ def test_product_does_not_reference_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inc", ".h")):
                 text = open(os.path.join(root, f)).read()
                 assert "libartis_oracle" not in text and "oracle/restatement" not in text, f
+
+
+def test_known_reciprocal_quotient_is_exact(tmp_path):
+    """common.cuh div_by_known (used for nu/nu_edge in the bound-free opacity sum) must give the bits of a true division:
+    12 million random and hard (near-tie) cases on the host FPU"""
+    import subprocess
+    exe = tmp_path / "divcheck"
+    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "divcheck.c")
+    subprocess.run(["gcc", "-O2", "-march=x86-64-v3", "-ffp-contract=off", src, "-o", str(exe), "-lm"], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout
+    assert "mismatches 0" in out.stdout
