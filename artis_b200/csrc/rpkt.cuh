@@ -245,12 +245,47 @@ ARTIS_DEV int bf_start_index(const Ctx &c, const double nu, const int i0) {
   return lo;
 }
 
-// Summation order: the terms are added in tiles of BF_TILE consecutive continua, each tile reduced as a binary tree
-// (t[j] += t[j + off], off = 16, 8, 4, 2, 1) and the tile sums accumulated in order. This is the order a warp produces
-// with shuffle-xor reductions (transport.cu coop_kappa_warm); the host restatement uses the same order so that both
-// give the same bits. It differs from the reference's strictly serial sum by rounding only (~1e-16 relative, far
-// inside the 1e-10 tolerance on kappa_cont; checked against the reference probes in tests/).
+// Summation order: the terms are added in tiles of BF_TILE consecutive continua (counted from the first visited one),
+// each tile reduced as a balanced binary tree over adjacent pairs ((t0+t1)+(t2+t3))+..., and the tile sums accumulated
+// in order. A warp produces exactly this tree with shuffle-down reductions of offsets 1, 2, 4, 8, 16
+// (transport.cu coop_kappa_warm); a single thread produces it with a binary counter of partial sums (PairTree below:
+// five doubles in registers instead of a 32-entry scratch array in local memory, which was a quarter of the hot
+// per-thread stack). Host and device use the same code, so both give the same bits; the result differs from the
+// reference's strictly serial sum by rounding only (~1e-16 relative, far inside the 1e-10 tolerance on kappa_cont;
+// checked against the reference probes in tests/).
 constexpr int BF_TILE = 32;
+struct PairTree {
+  double s0, s1, s2, s3, s4;  // pending partial sums of 1, 2, 4, 8, 16 consecutive terms
+  // add term number j (0-based within the tile); returns true when the tile is complete, with its sum in *tile_sum
+  ARTIS_DEV bool push(const int j, double v, double *tile_sum) {
+    if ((j & 1) == 0) {
+      s0 = v;
+      return false;
+    }
+    v = s0 + v;
+    if ((j & 2) == 0) {
+      s1 = v;
+      return false;
+    }
+    v = s1 + v;
+    if ((j & 4) == 0) {
+      s2 = v;
+      return false;
+    }
+    v = s2 + v;
+    if ((j & 8) == 0) {
+      s3 = v;
+      return false;
+    }
+    v = s3 + v;
+    if ((j & 16) == 0) {
+      s4 = v;
+      return false;
+    }
+    *tile_sum = s4 + v;
+    return true;
+  }
+};
 ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, const double nu, KappaCache &k, Tally &tl) {
   double kappa_bf_sum = 0.;
   const int ng = c.st.nbfcontinua_ground;
@@ -260,25 +295,32 @@ ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, cons
   const int i0 = bf_stop_index(c, nu);
   const int ilo = bf_start_index(c, nu, i0);
   tl.bf_evaluated += i0 - ilo;
-  for (int base = ilo; base < i0; base += BF_TILE) {
-    double t[BF_TILE];
-    // the terms of a tile are independent: four in flight per lane so that their table loads overlap
+  // whole tiles: the last one is padded with zero terms, exactly like the idle lanes of a warp
+  const int iend = ilo + ((i0 - ilo + BF_TILE - 1) / BF_TILE) * BF_TILE;
+  PairTree tree;
+  // the terms are independent: four in flight per thread so that their table loads overlap
+  for (int base = ilo; base < iend; base += 4) {
+    double t[4];
 #ifdef __CUDA_ARCH__
-#pragma unroll 4
+#pragma unroll
 #endif
-    for (int j = 0; j < BF_TILE; j++) {
-      const int i = base + j;
-      t[j] = 0.;
+    for (int u = 0; u < 4; u++) {
+      const int i = base + u;
+      t[u] = 0.;
       if (i < i0) {
         double gcontr;
         int slot;
-        t[j] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr, &slot);
+        t[u] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr, &slot);
         if (gcontr != 0. && slot >= 0) k.gamma_contr[slot] += gcontr;
       }
     }
-    for (int off = BF_TILE / 2; off >= 1; off >>= 1)
-      for (int j = 0; j < off; j++) t[j] += t[j + off];
-    kappa_bf_sum += t[0];
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+    for (int u = 0; u < 4; u++) {
+      double tile_sum;
+      if (tree.push((base + u - ilo) & (BF_TILE - 1), t[u], &tile_sum)) kappa_bf_sum += tile_sum;
+    }
   }
   return kappa_bf_sum;
 }

@@ -160,7 +160,7 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
         }
       }
 #pragma unroll
-      for (int off = BF_TILE / 2; off >= 1; off >>= 1) {
+      for (int off = 1; off < BF_TILE; off <<= 1) {  // adjacent pairs first: the tree of rpkt.cuh PairTree
 #pragma unroll
         for (int u = 0; u < COOP_UNROLL; u++) t[u] += __shfl_down_sync(full, t[u], off);
       }
@@ -190,9 +190,15 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
 #ifndef ARTIS_ROLE_AFFINITY
 #define ARTIS_ROLE_AFFINITY 0
 #endif
+#ifndef ARTIS_PERSIST_MINBLOCKS
+#define ARTIS_PERSIST_MINBLOCKS 2
+#endif
+#ifndef ARTIS_EST_PRIVATE_MAX_KB
+#define ARTIS_EST_PRIVATE_MAX_KB 0  /* off: the shared-memory copy costs more L1 than the atomics it saves (profiles/r1_notes.md) */
+#endif
 // about 250 registers per thread: 8 warps per SM, as two blocks of 4 or (with role affinity) one block of 8
 constexpr int PERSIST_THREADS = ARTIS_ROLE_AFFINITY ? 256 : 128;
-__global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : 2) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
+__global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : ARTIS_PERSIST_MINBLOCKS) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
                                                                  long long max_events, unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;
@@ -548,7 +554,7 @@ int g_persistent_blocks_per_sm = 2;
 int g_nbfcontinua_ground = 0;
 double *g_est_block = nullptr;
 size_t g_est_ndoubles = 0, g_persistent_smem_bytes = 0;
-constexpr size_t g_est_private_max_bytes = 100 * 1024;
+constexpr size_t g_est_private_max_bytes = (size_t)ARTIS_EST_PRIVATE_MAX_KB * 1024;
 double *g_kcache = nullptr;
 int *g_kflag = nullptr;
 size_t g_kcache_doubles = 0;
