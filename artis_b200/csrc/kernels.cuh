@@ -62,6 +62,12 @@ ARTIS_DEV int kind_of(const Ctx &c, const ArtisPacket &p) {
       return KIND_OTHER;
   }
 }
+// Scheduler-internal kinds of the barrier-free scheduler (transport.cu), on top of kind_of(): a thin-cell r-packet whose
+// step has begun and that waits for its continuum opacity (KIND_KAPPA), and one whose opacity has been delivered
+// (KIND_THIN_RESUME, consumed by the thin role together with KIND_RPKT_THIN). One ring of packet indices per entry.
+constexpr int KIND_KAPPA = NKIND;
+constexpr int KIND_THIN_RESUME = NKIND + 1;
+constexpr int NRING = NKIND + 2;
 ARTIS_DEV bool packet_active(const Ctx &c, const ArtisPacket &p) { return p.type != ARTIS_TYPE_ESCAPE && p.prop_time < c.t2; }
 
 struct QueueView {

@@ -57,50 +57,6 @@ __global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned l
 // forward only over tickets below the tail they observed and then exchange the slot back to -1, spinning for the few
 // cycles a producer may still need to fill it. Packet state written before the push is made visible with
 // __threadfence() and read with ld.global.cg on the consumer side (L1 is not coherent across SMs).
-struct PersistView {
-  int *ring[artis::NKIND];
-  unsigned long long *head;  // [NKIND]
-  unsigned long long *tail;  // [NKIND]
-  int *n_active;             // packets that have not finished the timestep
-  int n_initial;             // its value at launch
-  unsigned long long *t_start;  // globaltimer at launch (written by thread 0 of block 0)
-  int cap;
-  double *kcache;            // [cap][kstride] continuum-opacity cache of a packet handed over in mid-visit
-  int *kflag;                // [cap] 1 when kcache holds that packet's cache
-  int kstride;
-  double *est_block;         // global estimator block and the length of its block-private copy (0 = none)
-  unsigned est_private_doubles;
-};
-// A warp whose ring has run dry and that is left with at most this many busy lanes hands those packets back to the ring
-// (to be absorbed by the idle lanes of other warps of the same kind) and takes up a kind that has work for all 32 lanes.
-#ifndef ARTIS_CONSOLIDATE_MAX_BUSY
-#define ARTIS_CONSOLIDATE_MAX_BUSY -1  /* off: measured no gain on the bench workload (profiles/r1_notes.md) */
-#endif
-constexpr int CONSOLIDATE_MAX_BUSY = ARTIS_CONSOLIDATE_MAX_BUSY;
-constexpr long long CONSOLIDATE_MIN_BACKLOG = 64;
-
-__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
-  return *reinterpret_cast<const volatile unsigned long long *>(p);
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-static_assert(sizeof(ArtisPacket) % 8 == 0, "packet copied as 8-byte words");
-__device__ __forceinline__ void packet_load_cg(ArtisPacket &p, const ArtisPacket *src) {
-  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(src);
-  unsigned long long *d = reinterpret_cast<unsigned long long *>(&p);
-#pragma unroll
-  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) d[i] = __ldcg(s + i);
-}
-__device__ __forceinline__ void packet_store_cg(ArtisPacket *dst, const ArtisPacket &p) {
-  unsigned long long *d = reinterpret_cast<unsigned long long *>(dst);
-  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(&p);
-#pragma unroll
-  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) __stcg(d + i, s[i]);
-}
-
 // Warp-cooperative continuum opacity (K2): every lane that is about to need kappa_cont for its own packet and misses its
 // cache ("owner") gets its bound-free sum evaluated by all 32 lanes, a tile of 32 consecutive continua at a time --
 // coalesced reads of the per-cell table rows, no dependence between tiles, and the step's latency no longer grows with
@@ -187,54 +143,158 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
   if (need) kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ff, tl);
 }
 
-#ifndef ARTIS_ROLE_AFFINITY
-#define ARTIS_ROLE_AFFINITY 0
+using artis::KIND_KAPPA;
+using artis::KIND_THIN_RESUME;
+using artis::NRING;
+constexpr unsigned ROLES_ALL = (1u << artis::KIND_MAK) | (1u << artis::KIND_RPKT_THIN) | (1u << artis::KIND_GAMMA) |
+                               (1u << artis::KIND_OTHER) | (1u << artis::KIND_RPKT_GREY);
+// Two co-resident persistent kernels: the "light" one runs the roles that are chains of dependent table
+// loads with little live state (macro-atom / k-packet jumps, and continuum-opacity sums on request) at a small
+// register budget and therefore many resident warps; the "heavy" one runs the r-packet / gamma / pellet steps.
+#ifndef ARTIS_LIGHT_HAS_MAK
+#define ARTIS_LIGHT_HAS_MAK 1
 #endif
-#ifndef ARTIS_PERSIST_MINBLOCKS
-#define ARTIS_PERSIST_MINBLOCKS 2
+#ifndef ARTIS_HEAVY_MINBLOCKS
+#define ARTIS_HEAVY_MINBLOCKS 1
 #endif
-#ifndef ARTIS_EST_PRIVATE_MAX_KB
-#define ARTIS_EST_PRIVATE_MAX_KB 0  /* off: the shared-memory copy costs more L1 than the atomics it saves (profiles/r1_notes.md) */
+constexpr unsigned ROLES_LIGHT = (ARTIS_LIGHT_HAS_MAK ? (1u << artis::KIND_MAK) : 0u) | (1u << KIND_KAPPA);
+constexpr unsigned ROLES_HEAVY = ROLES_ALL & ~(ARTIS_LIGHT_HAS_MAK ? (1u << artis::KIND_MAK) : 0u);
+constexpr int HEAVY_MINBLOCKS = ARTIS_HEAVY_MINBLOCKS;
+#ifndef ARTIS_LIGHT_MINBLOCKS
+#define ARTIS_LIGHT_MINBLOCKS 6
 #endif
-// about 250 registers per thread: 8 warps per SM, as two blocks of 4 or (with role affinity) one block of 8
-constexpr int PERSIST_THREADS = ARTIS_ROLE_AFFINITY ? 256 : 128;
-__global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : ARTIS_PERSIST_MINBLOCKS) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr, PersistView pv,
-                                                                 long long max_events, unsigned long long idle_timeout_ns) {
+constexpr int LIGHT_MINBLOCKS = ARTIS_LIGHT_MINBLOCKS;  // register cap of the light kernel: 65536 / (128 x this)
+
+struct PersistView {
+  int *ring[NRING];
+  unsigned long long *head;  // [NRING]
+  unsigned long long *tail;  // [NRING]
+  int *n_active;             // packets that have not finished the timestep
+  int n_initial;             // its value at launch
+  unsigned long long *t_start;  // globaltimer at launch
+  int cap;
+  double *kcache;            // [cap][kstride] continuum opacity delivered for a packet (KappaCache scalars + gamma_contr)
+  double *stepstate;         // [cap][3] RpktStepState of a step that waits for its opacity
+  int kstride;
+  int offload_kappa;         // 1: the thin role hands opacity evaluations to the KIND_KAPPA role of the light kernel
+};
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
+  return *reinterpret_cast<const volatile unsigned long long *>(p);
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+static_assert(sizeof(ArtisPacket) % 8 == 0, "packet copied as 8-byte words");
+__device__ __forceinline__ void packet_load_cg(ArtisPacket &p, const ArtisPacket *src) {
+  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(src);
+  unsigned long long *d = reinterpret_cast<unsigned long long *>(&p);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) d[i] = __ldcg(s + i);
+}
+__device__ __forceinline__ void packet_store_cg(ArtisPacket *dst, const ArtisPacket &p) {
+  unsigned long long *d = reinterpret_cast<unsigned long long *>(dst);
+  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(&p);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) __stcg(d + i, s[i]);
+}
+__device__ __forceinline__ void kcache_store(double *kc, const artis::KappaCache &k, const int ng) {
+  __stcg(kc + 0, k.nu);
+  __stcg(kc + 1, k.total);
+  __stcg(kc + 2, k.es);
+  __stcg(kc + 3, k.ff);
+  __stcg(kc + 4, k.bf);
+  __stcg(kc + 5, k.ffheating);
+  __stcg(kc + 6, (double)k.mgi);
+  for (int g = 0; g < ng; g++) __stcg(kc + 8 + g, k.gamma_contr[g]);
+}
+__device__ __forceinline__ void kcache_load(artis::KappaCache &k, const double *kc, const int ng) {
+  k.nu = __ldcg(kc + 0);
+  k.total = __ldcg(kc + 1);
+  k.es = __ldcg(kc + 2);
+  k.ff = __ldcg(kc + 3);
+  k.bf = __ldcg(kc + 4);
+  k.ffheating = __ldcg(kc + 5);
+  k.mgi = (int)__ldcg(kc + 6);
+  k.valid = true;
+  for (int g = 0; g < ng; g++) k.gamma_contr[g] = __ldcg(kc + 8 + g);
+}
+// ring primitives (protocol in the comment above)
+__device__ __forceinline__ long long ring_backlog(const PersistView &pv, const int r) {
+  const unsigned long long h = ld_volatile_u64(pv.head + r), t = ld_volatile_u64(pv.tail + r);
+  return t > h ? (long long)(t - h) : 0;
+}
+// lane 0: claim up to `want` entries of ring r; returns the count and the first ticket
+__device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, const int want, unsigned long long *base) {
+  for (int tries = 0; tries < 4; tries++) {
+    const unsigned long long h = ld_volatile_u64(pv.head + r), t = ld_volatile_u64(pv.tail + r);
+    const long long avail = t > h ? (long long)(t - h) : 0;
+    const int take = avail < want ? (int)avail : want;
+    if (take == 0) return 0;
+    if (atomicCAS(pv.head + r, h, h + (unsigned long long)take) == h) {
+      *base = h;
+      return take;
+    }
+  }
+  return 0;
+}
+__device__ __forceinline__ int ring_take(const PersistView &pv, const int r, const unsigned long long ticket) {
+  int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);
+  int v;
+  while ((v = atomicExch(slot, -1)) < 0) {
+  }
+  __threadfence();
+  return v;
+}
+__device__ __forceinline__ void ring_put(const PersistView &pv, const int r, const unsigned long long ticket, const int idx) {
+  int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);
+  while (atomicCAS(slot, -1, idx) != -1) {
+  }
+}
+
+// ROLES: bit mask of the kinds the warps of this kernel may take up
+template <unsigned ROLES, int MINBLOCKS>
+__global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr,
+                                                                         PersistView pv, long long max_events,
+                                                                         unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;
   const double t2 = c.t2;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
+  const int ng = c.st.nbfcontinua_ground;
+  constexpr bool HAS_THIN = (ROLES & (1u << KIND_RPKT_THIN)) != 0;
+  constexpr bool HAS_KAPPA = (ROLES & (1u << KIND_KAPPA)) != 0;
   Tally tl = {};
   KappaCache k;
   k.valid = false;
-  bool have = false;
+  bool have = false, resumed = false;
   int idx = 0, role = 0;
   long long events = 0;
   ArtisPacket p;
   Rng rng;
+  RpktStepState st;
+  st.mgi = 0;
   unsigned long long idle_since = 0ull;
-  est_private_begin(pv.est_block, pv.est_private_doubles);
-  if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
-#if ARTIS_ROLE_AFFINITY
-  __shared__ int s_role;
-  if (threadIdx.x == 0) s_role = -1;
-  __syncthreads();
-#endif
+  est_private_begin(nullptr, 0u);
+  if ((ROLES & (1u << KIND_RPKT_GREY)) != 0 && blockIdx.x == 0 && threadIdx.x == 0)
+    *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
   long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
   while (true) {
     __syncwarp(full);
-#ifdef ARTIS_ROLE_CYCLES
-    const long long tr0 = clock64();
-#endif
     const unsigned need = __ballot_sync(full, !have);
     if (need != 0u) {
       if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
         long long backlog = 0;
-        if (lane < NKIND) {
-          const unsigned long long h = ld_volatile_u64(pv.head + lane), t = ld_volatile_u64(pv.tail + lane);
-          backlog = t > h ? (long long)(t - h) : 0;
+        if (lane < NRING && ((ROLES >> lane) & 1u) != 0) backlog = ring_backlog(pv, lane);
+        if (HAS_THIN && lane == KIND_THIN_RESUME) backlog = ring_backlog(pv, lane);
+        if (HAS_THIN) {  // the thin role drains two rings
+          const long long extra = __shfl_sync(full, backlog, KIND_THIN_RESUME);
+          if (lane == KIND_RPKT_THIN) backlog += extra;
+          if (lane == KIND_THIN_RESUME) backlog = 0;
         }
         long long best = backlog;
         int best_kind = lane;
@@ -249,20 +309,6 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : ART
         }
         best = __shfl_sync(full, best, 0);
         best_kind = __shfl_sync(full, best_kind, 0);
-        // Soft role affinity: the warps of a block (one block per SM) prefer the kind their neighbours are running as
-        // long as its ring has at least a warp's worth of work, so that an SM's instruction caches hold one kind's code.
-#if ARTIS_ROLE_AFFINITY
-        {
-          const int pref = *reinterpret_cast<volatile int *>(&s_role);
-          const long long pref_backlog = __shfl_sync(full, backlog, pref >= 0 ? pref : 0);
-          if (pref >= 0 && pref_backlog >= 32 && best > 0) {
-            best_kind = pref;
-            best = pref_backlog;
-          } else if (best > 0 && lane == 0) {
-            *reinterpret_cast<volatile int *>(&s_role) = best_kind;
-          }
-        }
-#endif
         if (best <= 0) {
           int left = 0;
           if (lane == 0) left = *reinterpret_cast<volatile int *>(pv.n_active);
@@ -276,174 +322,126 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : ART
             if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
             break;
           }
-#ifdef ARTIS_ROLE_CYCLES
-          const long long ti0 = clock64();
-#endif
           __nanosleep(1000);
-#ifdef ARTIS_ROLE_CYCLES
-          (void)ti0;
-#endif
           continue;
         }
         role = best_kind;
         idle_since = 0ull;
       }
-      int take = 0;
-      unsigned long long base = 0ull;
+      // refill the idle lanes from the role's ring(s); for the thin role the resumed steps come first
+      const int want = __popc(need);
+      int take_a = 0, take_b = 0;
+      unsigned long long base_a = 0ull, base_b = 0ull;
       if (lane == 0) {
-        const int want = __popc(need);
-        for (int tries = 0; tries < 4; tries++) {
-          const unsigned long long h = ld_volatile_u64(pv.head + role), t = ld_volatile_u64(pv.tail + role);
-          const long long avail = t > h ? (long long)(t - h) : 0;
-          take = avail < want ? (int)avail : want;
-          if (take == 0) break;
-          if (atomicCAS(pv.head + role, h, h + (unsigned long long)take) == h) {
-            base = h;
-            break;
-          }
-          take = 0;
-        }
+        if (HAS_THIN && role == KIND_RPKT_THIN) take_a = ring_claim(pv, KIND_THIN_RESUME, want, &base_a);
+        if (take_a < want) take_b = ring_claim(pv, role, want - take_a, &base_b);
       }
-      take = __shfl_sync(full, take, 0);
-      base = __shfl_sync(full, base, 0);
+      take_a = __shfl_sync(full, take_a, 0);
+      take_b = __shfl_sync(full, take_b, 0);
+      base_a = __shfl_sync(full, base_a, 0);
+      base_b = __shfl_sync(full, base_b, 0);
       const int rank = __popc(need & lt_mask);
-      if (!have && rank < take) {
-        int *slot = pv.ring[role] + (size_t)((base + (unsigned long long)rank) % (unsigned long long)pv.cap);
-        int v;
-        while ((v = atomicExch(slot, -1)) < 0) {
+      if (!have && rank < take_a + take_b) {
+        const bool from_resume = rank < take_a;
+        idx = from_resume ? ring_take(pv, KIND_THIN_RESUME, base_a + (unsigned long long)rank)
+                          : ring_take(pv, role, base_b + (unsigned long long)(rank - take_a));
+        if (HAS_KAPPA && role == KIND_KAPPA) {
+          // only the two fields the opacity depends on
+          p.nu_cmf = __ldcg(&pkts[idx].nu_cmf);
+          p.where = __ldcg(&pkts[idx].where);
+        } else {
+          packet_load_cg(p, pkts + idx);
+          rng = rng_init(c, p.number, __ldcg(rngctr + idx));
         }
-        __threadfence();
-        idx = v;
-        packet_load_cg(p, pkts + idx);
-        rng = rng_init(c, p.number, __ldcg(rngctr + idx));
         k.valid = false;
-        if (CONSOLIDATE_MAX_BUSY >= 0 && role == KIND_RPKT_THIN && __ldcg(pv.kflag + idx) != 0) {  // handed over in mid-visit: its cache comes along
-          const double *kc = pv.kcache + (size_t)idx * pv.kstride;
-          k.nu = __ldcg(kc + 0);
-          k.total = __ldcg(kc + 1);
-          k.es = __ldcg(kc + 2);
-          k.ff = __ldcg(kc + 3);
-          k.bf = __ldcg(kc + 4);
-          k.ffheating = __ldcg(kc + 5);
-          k.mgi = (int)__ldcg(kc + 6);
-          k.valid = true;
-          const int ng = c.st.nbfcontinua_ground;
-          for (int g = 0; g < ng; g++) k.gamma_contr[g] = __ldcg(kc + 8 + g);
-          __stcg(pv.kflag + idx, 0);
+        resumed = false;
+        if (HAS_THIN && from_resume) {
+          kcache_load(k, pv.kcache + (size_t)idx * pv.kstride, ng);
+          const double *ss = pv.stepstate + (size_t)idx * 3;
+          st.tau_next = __ldcg(ss + 0);
+          st.sdist = __ldcg(ss + 1);
+          const long long packed = __double_as_longlong(__ldcg(ss + 2));
+          st.snext = (int)(packed >> 32);
+          st.mgi = (int)(packed & 0xffffffffll);
+          resumed = true;
         }
         events = 0;
         have = true;
       }
-      if (need == full && take == 0) continue;  // lost the race for the last entries
-      if (CONSOLIDATE_MAX_BUSY >= 0 && take == 0 && __popc(~need) <= CONSOLIDATE_MAX_BUSY) {
-        long long other = 0;
-        if (lane < NKIND && lane != role) {
-          const unsigned long long h = ld_volatile_u64(pv.head + lane), t = ld_volatile_u64(pv.tail + lane);
-          other = t > h ? (long long)(t - h) : 0;
-        }
-#pragma unroll
-        for (int off = 4; off >= 1; off >>= 1) {
-          const long long o = __shfl_down_sync(full, other, off);
-          other = o > other ? o : other;
-        }
-        other = __shfl_sync(full, other, 0);
-        if (other >= CONSOLIDATE_MIN_BACKLOG) {
-          if (have) {
-            __stcg(rngctr + idx, (unsigned long long)rng.ctr);
-            packet_store_cg(pkts + idx, p);
-            if (role == KIND_RPKT_THIN && k.valid) {
-              double *kc = pv.kcache + (size_t)idx * pv.kstride;
-              __stcg(kc + 0, k.nu);
-              __stcg(kc + 1, k.total);
-              __stcg(kc + 2, k.es);
-              __stcg(kc + 3, k.ff);
-              __stcg(kc + 4, k.bf);
-              __stcg(kc + 5, k.ffheating);
-              __stcg(kc + 6, (double)k.mgi);
-              const int ng = c.st.nbfcontinua_ground;
-              for (int g = 0; g < ng; g++) __stcg(kc + 8 + g, k.gamma_contr[g]);
-              __stcg(pv.kflag + idx, 1);
-            }
-            __threadfence();
-          }
-          const unsigned m = __ballot_sync(full, have);
-          unsigned long long b = 0ull;
-          if (lane == 0) b = atomicAdd(pv.tail + role, (unsigned long long)__popc(m));
-          b = __shfl_sync(full, b, 0);
-          if (have) {
-            int *slot = pv.ring[role] + (size_t)((b + (unsigned long long)__popc(m & lt_mask)) % (unsigned long long)pv.cap);
-            while (atomicCAS(slot, -1, idx) != -1) {
-            }
-            have = false;
-            tl.handoffs++;
-          }
-          continue;  // the warp is idle now and picks the kind with the longest backlog
-        }
-      }
+      if (need == full && take_a + take_b == 0) continue;  // lost the race for the last entries
     }
     __syncwarp(full);
     bool done = false;
     int k2 = -1;
     {
       const unsigned busy = __ballot_sync(full, have);
-      if (lane == role) {  // lane k keeps the occupancy statistics of kind k
+      if (lane == role && lane < NKIND) {  // lane k keeps the occupancy statistics of kind k
         fill_iters++;
-#ifndef ARTIS_ROLE_CYCLES
         fill_lanes += __popc(busy);
-#endif
       }
     }
-#ifdef ARTIS_ROLE_CYCLES
-    const long long tc0 = clock64();
-#endif
-#if defined(ARTIS_ROLE_CYCLES) && !defined(ARTIS_ROLE_CYCLES2)
-    if (lane == 3) {  // experiment: kind-3 slots hold the scheduling overhead (refill + previous push)
-      fill_lanes += tc0 - tr0;
-      fill_iters++;
-    }
-#endif
-#ifndef ARTIS_COOP_KAPPA
-#define ARTIS_COOP_KAPPA 1
-#endif
-    if (ARTIS_COOP_KAPPA && role == KIND_RPKT_THIN) {  // warp-uniform: the step in two halves around the cooperative opacity evaluation
-      RpktStepState st;
-      st.mgi = 0;
+    bool stepped = have;  // false for a lane that hands its step over instead of finishing it
+    if (HAS_THIN && role == KIND_RPKT_THIN) {  // warp-uniform: the step in two halves around the opacity evaluation
       bool proceed = false;
       if (have) {
-        tl.packet_updates++;
-        proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
+        if (resumed) {
+          proceed = true;
+        } else {
+          tl.packet_updates++;
+          proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
+        }
       }
-#ifdef ARTIS_ROLE_CYCLES2
-      const long long tb1 = clock64();
-#endif
-      coop_kappa_warm(c, proceed, st.mgi, p.nu_cmf, k, tl);
-#ifdef ARTIS_ROLE_CYCLES2
-      const long long tb2 = clock64();
-      if (proceed) calculate_kappa_rpkt_cont(c, p, st.mgi, k, tl);  // what get_event would do first
-      __syncwarp(full);
-      const long long tb3 = clock64();
-      if (lane == 2) {  // kind-2 slots: begin + coop; kind-3 slots: per-lane kappa
-        fill_lanes += tb2 - tc0;
-        fill_iters++;
+      const bool wants = proceed && !resumed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
+      const unsigned owners = __ballot_sync(full, wants);
+      if (pv.offload_kappa != 0 && __popc(owners) > COOP_MAX_OWNERS) {
+        if (wants) {  // hand the evaluation to the light kernel; the step resumes in whichever thin warp picks it up
+          double *ss = pv.stepstate + (size_t)idx * 3;
+          __stcg(ss + 0, st.tau_next);
+          __stcg(ss + 1, st.sdist);
+          __stcg(ss + 2, __longlong_as_double(((long long)st.snext << 32) | (long long)(unsigned)st.mgi));
+          stepped = false;
+        }
+      } else {
+        coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl);
       }
-      if (lane == 3) {
-        fill_lanes += tb3 - tb2;
-        fill_iters++;
+      if (stepped && proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
+      resumed = false;
+      if (stepped && have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
+    } else if (HAS_KAPPA && role == KIND_KAPPA) {
+      if (have) {
+        const int mgi = cell_mgi(c, p.where);
+        calculate_kappa_rpkt_cont(c, p, mgi, k, tl);
+        kcache_store(pv.kcache + (size_t)idx * pv.kstride, k, ng);
+        __threadfence();
+        done = true;
+        k2 = KIND_THIN_RESUME;
+        have = false;
+        stepped = false;
       }
-      (void)tb1;
-#endif
-      if (proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
-      if (have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
     } else if (have) {
       switch (role) {  // warp-uniform
-        case 0: do_packet_kind<0>(c, p, t2, k, rng, tl); break;
-        case 1: do_packet_kind<1>(c, p, t2, k, rng, tl); break;
-        case 2: do_packet_kind<2>(c, p, t2, k, rng, tl); break;
-        case 4: do_packet_kind<4>(c, p, t2, k, rng, tl); break;
-        default: do_packet_kind<3>(c, p, t2, k, rng, tl); break;
+        case KIND_MAK:
+          if constexpr ((ROLES & (1u << KIND_MAK)) != 0) do_packet_kind<KIND_MAK>(c, p, t2, k, rng, tl);
+          break;
+        case KIND_GAMMA:
+          if constexpr ((ROLES & (1u << KIND_GAMMA)) != 0) do_packet_kind<KIND_GAMMA>(c, p, t2, k, rng, tl);
+          break;
+        case KIND_RPKT_GREY:
+          if constexpr ((ROLES & (1u << KIND_RPKT_GREY)) != 0) do_packet_kind<KIND_RPKT_GREY>(c, p, t2, k, rng, tl);
+          break;
+        default:
+          if constexpr ((ROLES & (1u << KIND_OTHER)) != 0) do_packet_kind<KIND_OTHER>(c, p, t2, k, rng, tl);
+          break;
       }
     }
-    if (have) {
+    if (have && !stepped) {  // thin lane that handed its opacity evaluation over
+      __stcg(rngctr + idx, (unsigned long long)rng.ctr);
+      packet_store_cg(pkts + idx, p);
+      __threadfence();
+      done = true;
+      k2 = KIND_KAPPA;
+      have = false;
+    } else if (have) {
       events++;
       const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
       if (!(active && kind_of(c, p) == role && events < max_events)) {
@@ -456,24 +454,16 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : ART
       }
     }
     __syncwarp(full);
-#ifdef ARTIS_ROLE_CYCLES
-    if (lane == role) fill_lanes += clock64() - tc0 - 27;  // experiment: slots 56.. hold cycles instead of busy lanes
-    const long long tp0 = clock64();
-#endif
     if (__ballot_sync(full, done) != 0u) {
 #pragma unroll
-      for (int kk = 0; kk < NKIND; kk++) {
+      for (int kk = 0; kk < NRING; kk++) {
         const unsigned m = __ballot_sync(full, done && k2 == kk);
         if (m != 0u) {
           const int leader = __ffs(m) - 1;
           unsigned long long b = 0ull;
           if (lane == leader) b = atomicAdd(pv.tail + kk, (unsigned long long)__popc(m));
           b = __shfl_sync(full, b, leader);
-          if (done && k2 == kk) {
-            int *slot = pv.ring[kk] + (size_t)((b + (unsigned long long)__popc(m & lt_mask)) % (unsigned long long)pv.cap);
-            while (atomicCAS(slot, -1, idx) != -1) {
-            }
-          }
+          if (done && k2 == kk) ring_put(pv, kk, b + (unsigned long long)__popc(m & lt_mask), idx);
         }
       }
       const unsigned fin = __ballot_sync(full, done && k2 < 0);
@@ -488,15 +478,8 @@ __global__ void __launch_bounds__(PERSIST_THREADS, ARTIS_ROLE_AFFINITY ? 1 : ART
         if (after <= 0) c.es.counters[ARTIS_CTR_DRAIN_NS_DONE] = now;
       }
     }
-#if defined(ARTIS_ROLE_CYCLES) && !defined(ARTIS_ROLE_CYCLES2)
-    if (lane == 2) {  // experiment: kind-2 slots hold the push section
-      fill_lanes += clock64() - tp0;
-      fill_iters++;
-    }
-#endif
   }
   tally_flush(c, tl);
-  est_private_flush();
   if (lane < NKIND && fill_iters > 0) {
     ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + lane], fill_iters);
     ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + lane], fill_lanes);
@@ -550,13 +533,16 @@ cudaStream_t g_stream = nullptr;
 cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 int g_sms = SM_COUNT_B200;
 int g_transport_blocks_per_sm = 4;
-int g_persistent_blocks_per_sm = 2;
+int g_blocks_all = 2, g_blocks_heavy = 1, g_blocks_light = 3;
+int g_scheduler_kernels = 1;  // 2 = light + heavy kernels side by side: correct but slower on every split tried (profiles/r1_notes.md)
+cudaStream_t g_stream2 = nullptr;
+cudaEvent_t g_ev_fork = nullptr, g_ev_join = nullptr;
+double *g_stepstate = nullptr;
+bool g_persistent_warmed = false;
 int g_nbfcontinua_ground = 0;
 double *g_est_block = nullptr;
-size_t g_est_ndoubles = 0, g_persistent_smem_bytes = 0;
-constexpr size_t g_est_private_max_bytes = (size_t)ARTIS_EST_PRIVATE_MAX_KB * 1024;
+size_t g_est_ndoubles = 0;
 double *g_kcache = nullptr;
-int *g_kflag = nullptr;
 size_t g_kcache_doubles = 0;
 std::string g_async_err;
 
@@ -584,12 +570,33 @@ bool be_select_device(int device, std::string *why) {
   int nb = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_wavefront<1>, 128, 0) == cudaSuccess && nb > 0)
     g_transport_blocks_per_sm = nb;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent, PERSIST_THREADS, 0) == cudaSuccess && nb > 0)
-    g_persistent_blocks_per_sm = nb;  // the whole grid must be resident: idle warps wait for the others' packets
+  // every block of the persistent grids must be resident (idle warps wait for the others' packets): size the grids
+  // from the occupancy of each kernel alone, and in two-kernel mode from the registers the heavy kernel leaves free
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent<ROLES_ALL, 2>, 128, 0) == cudaSuccess && nb > 0)
+    g_blocks_all = nb;
+  {
+    cudaFuncAttributes ah{}, al{};
+    int regs_per_sm = 65536;
+    cudaDeviceGetAttribute(&regs_per_sm, cudaDevAttrMaxRegistersPerMultiprocessor, device);
+    if (cudaFuncGetAttributes(&ah, k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS>) == cudaSuccess &&
+        cudaFuncGetAttributes(&al, k_transport_persistent<ROLES_LIGHT, LIGHT_MINBLOCKS>) == cudaSuccess && al.numRegs > 0) {
+      // registers are allocated per warp in units of 512 (256-register granularity x 2 is a safe upper bound)
+      const int heavy = ((ah.numRegs * 32 + 511) / 512) * 512 * 4, light = ((al.numRegs * 32 + 511) / 512) * 512 * 4;
+      g_blocks_heavy = HEAVY_MINBLOCKS >= 3 ? 2 : 1;
+      g_blocks_light = (regs_per_sm - g_blocks_heavy * heavy) / light;
+      if (g_blocks_light > 8) g_blocks_light = 8;
+      if (g_blocks_light < 1) g_scheduler_kernels = 1;  // no room next to the heavy kernel: one kernel with all roles
+    } else {
+      g_scheduler_kernels = 1;
+    }
+  }
   if (g_stream == nullptr) {
     note(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    note(cudaStreamCreateWithFlags(&g_stream2, cudaStreamNonBlocking), "cudaStreamCreate");
     note(cudaEventCreate(&g_ev0), "cudaEventCreate");
     note(cudaEventCreate(&g_ev1), "cudaEventCreate");
+    note(cudaEventCreateWithFlags(&g_ev_fork, cudaEventDisableTiming), "cudaEventCreate");
+    note(cudaEventCreateWithFlags(&g_ev_join, cudaEventDisableTiming), "cudaEventCreate");
   }
   g_async_err.clear();
   return true;
@@ -663,55 +670,80 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
     default: k_wavefront<3><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
   }
 }
-// barrier-free scheduler: rings = NKIND rings of `cap` ints (initial entries written by be_run_bucket, -1 elsewhere),
-// pmeta = head[NKIND], tail[NKIND], n_active (int)
+// barrier-free scheduler: rings = NRING rings of `cap` ints (initial entries written by be_run_bucket, -1 elsewhere),
+// pmeta = head[NRING], tail[NRING], n_active (int), t_start.
+// g_scheduler_kernels == 2: the light kernel (macro-atom/k-packet and opacity-on-request roles, <= 80 registers, 3 blocks
+// per SM) and the heavy kernel (everything else, 1 block per SM) run side by side on two streams and exchange packets
+// through the rings; 1: one kernel with every role (2 blocks per SM of ~250 registers).
 bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int cap, unsigned long long *pmeta, int n_initial,
                        long long maxev) {
   PersistView pv;
-  for (int k = 0; k < artis::NKIND; k++) pv.ring[k] = rings + (size_t)k * cap;
+  for (int k = 0; k < NRING; k++) pv.ring[k] = rings + (size_t)k * cap;
   pv.head = pmeta;
-  pv.tail = pmeta + artis::NKIND;
-  pv.n_active = reinterpret_cast<int *>(pmeta + 2 * artis::NKIND);
+  pv.tail = pmeta + NRING;
+  pv.n_active = reinterpret_cast<int *>(pmeta + 2 * NRING);
   pv.n_initial = n_initial;
-  pv.t_start = pmeta + 2 * artis::NKIND + 1;
+  pv.t_start = pmeta + 2 * NRING + 1;
   pv.cap = cap;
   const int kstride = 8 + g_nbfcontinua_ground;
-  if (CONSOLIDATE_MAX_BUSY >= 0 && (size_t)cap * kstride > g_kcache_doubles) {
+  const bool two = g_scheduler_kernels == 2;
+  if (two && (size_t)cap * kstride > g_kcache_doubles) {
     if (g_kcache) cudaFree(g_kcache);
-    if (g_kflag) cudaFree(g_kflag);
+    if (g_stepstate) cudaFree(g_stepstate);
     g_kcache = nullptr;
-    g_kflag = nullptr;
+    g_stepstate = nullptr;
     g_kcache_doubles = 0;
     if (cudaMalloc(&g_kcache, (size_t)cap * kstride * sizeof(double)) != cudaSuccess ||
-        cudaMalloc(&g_kflag, (size_t)cap * sizeof(int)) != cudaSuccess) {
-      note(cudaGetLastError(), "cudaMalloc (opacity cache side buffer)");
+        cudaMalloc(&g_stepstate, (size_t)cap * 3 * sizeof(double)) != cudaSuccess) {
+      note(cudaGetLastError(), "cudaMalloc (opacity hand-over buffers)");
       return true;  // be_sync reports the error
     }
     g_kcache_doubles = (size_t)cap * kstride;
   }
-  if (g_kflag) note(cudaMemsetAsync(g_kflag, 0, (size_t)cap * sizeof(int), g_stream), "memset");
   pv.kcache = g_kcache;
-  pv.kflag = g_kflag;
+  pv.stepstate = g_stepstate;
   pv.kstride = kstride;
-  // block-private estimators when the block fits next to a second resident CTA (227 KB per SM, 1 KB reserved each)
-  size_t est_bytes = g_est_ndoubles * sizeof(double);
-  if (est_bytes > g_est_private_max_bytes) est_bytes = 0;
-  pv.est_block = g_est_block;
-  pv.est_private_doubles = (unsigned)(est_bytes / sizeof(double));
-  if (est_bytes != g_persistent_smem_bytes) {
-    note(cudaFuncSetAttribute(k_transport_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)est_bytes),
-         "cudaFuncSetAttribute");
-    int nb = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent, PERSIST_THREADS, est_bytes) ==
-            cudaSuccess && nb > 0)
-      g_persistent_blocks_per_sm = nb;
-    g_persistent_smem_bytes = est_bytes;
+  pv.offload_kappa = two ? 1 : 0;
+  const unsigned long long timeout = 20ull * 1000000000ull;
+  if (!g_persistent_warmed) {
+    // First launch of each persistent kernel with nothing to do (n_active == 0: every warp leaves at once). A first
+    // launch can make the driver grow the local-memory pool, which waits for running kernels -- with the other
+    // persistent kernel already spinning that would never end.
+    unsigned long long *scratch = nullptr;
+    if (cudaMalloc(&scratch, 16 * sizeof(unsigned long long)) == cudaSuccess) {
+      note(cudaMemsetAsync(scratch, 0, 16 * sizeof(unsigned long long), g_stream), "memset");
+      PersistView w = pv;
+      w.head = scratch;
+      w.tail = scratch + NRING;
+      w.n_active = reinterpret_cast<int *>(scratch + 2 * NRING);
+      w.t_start = scratch + 2 * NRING + 1;
+      w.n_initial = 0;
+      k_transport_persistent<ROLES_ALL, 2><<<1, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
+      k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS><<<1, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
+      k_transport_persistent<ROLES_LIGHT, LIGHT_MINBLOCKS><<<g_sms * g_blocks_light, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
+      note(cudaStreamSynchronize(g_stream), "warm-up sync");
+      cudaFree(scratch);
+    }
+    g_persistent_warmed = true;
   }
-  const int grid = g_sms * g_persistent_blocks_per_sm;
-  k_transport_persistent<<<grid, PERSIST_THREADS, est_bytes, g_stream>>>(p, r, pv, maxev, 20ull * 1000000000ull);
+  if (!two) {
+    k_transport_persistent<ROLES_ALL, 2><<<g_sms * g_blocks_all, 128, 0, g_stream>>>(p, r, pv, maxev, timeout);
+    return true;
+  }
+  // the heavy kernel goes first (its blocks are the big ones), the light kernel fills the rest of every SM; the side
+  // stream waits for what is queued on the main stream (ring setup) and the main stream waits for the side kernel
+  note(cudaEventRecord(g_ev_fork, g_stream), "event record");
+  note(cudaStreamWaitEvent(g_stream2, g_ev_fork, 0), "stream wait");
+  k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS><<<g_sms * g_blocks_heavy, 128, 0, g_stream>>>(p, r, pv, maxev, timeout);
+  k_transport_persistent<ROLES_LIGHT, LIGHT_MINBLOCKS><<<g_sms * g_blocks_light, 128, 0, g_stream2>>>(p, r, pv, maxev, timeout);
+  note(cudaEventRecord(g_ev_join, g_stream2), "event record");
+  note(cudaStreamWaitEvent(g_stream, g_ev_join, 0), "stream wait");
   return true;
 }
 void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }
+void be_set_scheduler_kernels(int n) {
+  if (n == 1 || (n == 2 && g_blocks_light >= 1)) g_scheduler_kernels = n;
+}
 void be_set_estimator_block(double *block, size_t ndoubles) {
   g_est_block = block;
   g_est_ndoubles = ndoubles;

@@ -185,6 +185,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-baseline", default="auto", choices=["auto", "off"])
     ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
+    ap.add_argument("--scheduler-kernels", type=int, default=0, choices=(0, 1, 2),
+                    help="1: one persistent kernel with every role, 2: light + heavy kernels side by side (0: library default)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -227,6 +229,8 @@ def main():
     T.upload_cellstate(cs)
     if a.max_events:
         T.set_tuning(max_events_per_pass=a.max_events)
+    if a.scheduler_kernels:
+        T.set_tuning(block_threads=-3 if a.scheduler_kernels == 1 else -4)
     precompute_ms = T.last_timings()[3]
     # the contiguous FP64 estimator block as a torch tensor (for the NCCL all-reduce that replaces
     # mpi_reduce_estimators, sn3d.cc:316-384)

@@ -58,6 +58,7 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
 bool be_run_persistent(ArtisPacket *, unsigned long long *, int *, int, unsigned long long *, int, long long) { return false; }
 void be_fill_bytes(void *p, int byte, size_t n) { memset(p, byte, n); }
 void be_set_estimator_block(double *, size_t) {}
+void be_set_scheduler_kernels(int) {}
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   for (int i = 0; i < n; i++) artis::body_probe_boundary(g_ctx, p, i, a, b, c);
 }

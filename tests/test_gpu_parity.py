@@ -119,3 +119,30 @@ def test_cuda_edge_cases_and_scale(gpu_lib):
     assert ((big["type"] == abi.TYPE_ESCAPE) | (big["prop_time"] == t2)).all()
     T.finalize()
 
+
+
+def test_scheduler_variants_give_identical_packets(gpu_lib):
+    """scheduling must not change physics: one persistent kernel with every role, the light + heavy kernel pair (opacity
+    evaluations handed over between kernels), and the kernel-rounds scheduler all produce the same packets bit for bit
+    (every packet owns its Philox stream and its draw counter travels with it)"""
+    fx = goldenlib.load_fixture("classic_nogrey_ts12.npz")
+    outs = []
+    for mode in (-3, -4, -1):
+        T = _ready(gpu_lib, fx, seed=99)
+        T.set_tuning(block_threads=-2)   # barrier-free scheduler ...
+        T.set_tuning(block_threads=mode)  # ... with one kernel (-3), two kernels (-4); -1: kernel rounds per kind
+        pk = fx["pre"].copy()
+        T.update_packets(pk)
+        outs.append(pk)
+        T.set_tuning(block_threads=-2)  # back to the defaults for whatever runs next in this process
+        T.set_tuning(block_threads=-3)
+        T.finalize()
+    for name in outs[0].dtype.names:
+        assert np.array_equal(outs[0][name], outs[1][name], equal_nan=True), ("two-kernel", name)
+    # the kernel-rounds scheduler never takes the warp-cooperative opacity path, whose FMA contraction differs in the
+    # last bit: same histories, positions and frequencies equal to rounding
+    a, b = outs[0], outs[2]
+    for name in ("type", "where", "interactions", "next_trans", "emissiontype", "escape_type"):
+        assert np.array_equal(a[name], b[name]), ("rounds", name)
+    for name in ("pos", "nu_cmf", "e_cmf", "prop_time"):
+        assert np.allclose(a[name], b[name], rtol=1e-9, atol=0, equal_nan=True), ("rounds", name)
