@@ -32,17 +32,26 @@ MASS = {14: 28.09, 16: 32.06, 20: 40.08, 26: 55.85, 27: 58.93, 28: 58.69}
 
 
 def generate(outdir, elements=(26, 27, 28), nions=5, nlevels=100, dense_levels=20, sparsity=0.1, seed=20240607,
-             nphixspoints=100, nphixsnuincrement=0.1, multitarget_every=7):
+             nphixspoints=100, nphixsnuincrement=0.1, multitarget_every=7, ion_ranges=None, abundance_only=(),
+             single_level_top_ion=True):
+    """ion_ranges: optional {Z: (lowermost_ionstage, uppermost_ionstage)} (default 1..nions for every element);
+    abundance_only: [(Z, mass_amu)] elements without ions (compositiondata rows with nions = 0, as in
+    tests/kilonova_inputfiles/compositiondata.txt); single_level_top_ion as in artisoptions_*.h."""
     rng = np.random.default_rng(seed)
     os.makedirs(outdir, exist_ok=True)
-    comp = [f"{len(elements)}", "0", "0"]
+    rows = {}
     adata, trans, phixs = [], [], [f"{nphixspoints}", f"{nphixsnuincrement}"]
     nlines_total = 0
+    for Z, mass in abundance_only:
+        rows[Z] = f"{Z} 0 0 0 1 0.0 {mass}"
+    nions_default = nions
     for Z in elements:
-        comp.append(f"{Z} {nions} 1 {nions} {nlevels} 0.0 {MASS[Z]}")
+        lowest, highest = (ion_ranges or {}).get(Z, (1, nions_default))
+        nions = highest - lowest + 1
+        rows[Z] = f"{Z} {nions} {lowest} {highest} {nlevels} 0.0 {MASS[Z]}"
         ion_levels = []
         for ion in range(nions):
-            ionpot = IONPOT[Z][ion]
+            ionpot = IONPOT[Z][lowest - 1 + ion]
             nlev = nlevels
             # level energies: ground at 0, a few low-lying metastable levels, the rest spread below 0.95*ionpot
             nlow = min(6, nlev - 1)
@@ -69,13 +78,13 @@ def generate(outdir, elements=(26, 27, 28), nions=5, nlevels=100, dense_levels=2
             ntr = np.zeros(nlev, dtype=int)
             for lo, up, *_ in tl:
                 ntr[up - 1] += 1
-            adata.append(f"{Z} {ion + 1} {nlev} {ionpot:.6f}")
+            adata.append(f"{Z} {lowest + ion} {nlev} {ionpot:.6f}")
             for i in range(nlev):
                 adata.append(f"{i + 1} {energies[i]:.8f} {g[i]:.1f} {ntr[i]}")
             adata.append("")
             # transitiondata sorted by lower then upper (input.cc:429-470 expects grouped by lower level)
             tl.sort(key=lambda x: (x[0], x[1]))
-            trans.append(f"{Z} {ion + 1} {len(tl)}")
+            trans.append(f"{Z} {lowest + ion} {len(tl)}")
             for lo, up, A, cs, fb in tl:
                 trans.append(f"{lo} {up} {A:.6e} {cs:.1f} {fb}")
             trans.append("")
@@ -85,8 +94,8 @@ def generate(outdir, elements=(26, 27, 28), nions=5, nlevels=100, dense_levels=2
         for ion in range(nions - 1):
             energies, g = ion_levels[ion]
             up_energies, _ = ion_levels[ion + 1]
-            ionpot = IONPOT[Z][ion]
-            top_is_next = (ion + 1 == nions - 1)  # single_level_top_ion: only level 0 exists there
+            ionpot = IONPOT[Z][lowest - 1 + ion]
+            top_is_next = single_level_top_ion and (ion + 1 == nions - 1)  # then only level 0 exists there
             for lev in range(len(energies)):
                 sigma0 = 10 ** rng.uniform(-1.0, 1.0)
                 x = 1.0 + nphixsnuincrement * np.arange(nphixspoints)
@@ -94,14 +103,15 @@ def generate(outdir, elements=(26, 27, 28), nions=5, nlevels=100, dense_levels=2
                 multi = (not top_is_next) and (lev % multitarget_every == 0)
                 if multi:
                     thr = ionpot + up_energies[0] - energies[lev]
-                    phixs.append(f"{Z} {ion + 2} -1 {ion + 1} {lev + 1} {thr:.8f}")
+                    phixs.append(f"{Z} {lowest + ion + 1} -1 {lowest + ion} {lev + 1} {thr:.8f}")
                     phixs.append("2")
                     phixs.append("1 0.7")
                     phixs.append("2 0.3")
                 else:
                     thr = ionpot - energies[lev]
-                    phixs.append(f"{Z} {ion + 2} 1 {ion + 1} {lev + 1} {thr:.8f}")
+                    phixs.append(f"{Z} {lowest + ion + 1} 1 {lowest + ion} {lev + 1} {thr:.8f}")
                 phixs.extend(f"{s:.6e}" for s in sig)
+    comp = [f"{len(rows)}", "0", "0"] + [rows[Z] for Z in sorted(rows)]
     open(os.path.join(outdir, "compositiondata.txt"), "w").write("\n".join(comp) + "\n")
     open(os.path.join(outdir, "adata.txt"), "w").write("\n".join(adata) + "\n")
     open(os.path.join(outdir, "transitiondata.txt"), "w").write("\n".join(trans) + "\n")

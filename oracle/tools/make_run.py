@@ -18,7 +18,7 @@ import gen_atomic_data  # noqa: E402
 REF = os.environ.get("ARTIS_REF", "/root/reference")
 
 
-def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax=None, model_type=None):
+def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax=None, model_type=None, ngrey=None):
     lines = open(template).read().splitlines()
     out = []
     k = 0
@@ -35,6 +35,8 @@ def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax
             body = f"{tmin} {tmax}".ljust(25)
         if k == 7 and model_type is not None:
             body = f"{model_type}".ljust(25)
+        if k == 19 and ngrey is not None:  # cell_is_optically_thick num_grey_timesteps
+            body = f"{body.split()[0]} {ngrey}".ljust(25)
         out.append(body + ("#" + comment if comment else ""))
         k += 1
     open(path, "w").write("\n".join(out) + "\n")
@@ -53,9 +55,29 @@ def setup_classic1d(rundir, args):
     print(f"run dir {rundir}: {n} lines")
 
 
+def setup_kilonova1d(rundir, args):
+    """tests/setup_kilonova.sh: the 1D kilonova model with the composition of tests/kilonova_inputfiles (Fe I-V,
+    Co II-IV, Ni II-V with levels and lines, seven abundance-only elements), synthetic atomic data"""
+    import lzma
+    src = os.path.join(REF, "tests", "kilonova_inputfiles")
+    os.makedirs(rundir, exist_ok=True)
+    shutil.copy(os.path.join(src, "abundances.txt"), rundir)
+    for f in ("model.txt", "gridcontributions.txt"):
+        open(os.path.join(rundir, f), "wb").write(lzma.open(os.path.join(src, f + ".xz")).read())
+    for f in os.listdir(os.path.join(REF, "data")):
+        shutil.copy(os.path.join(REF, "data", f), rundir)
+    write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep,
+                    ngrey=args.ngrey)
+    n = gen_atomic_data.generate(rundir, (26, 27, 28), 5, args.nlevels, args.dense_levels, args.sparsity, args.seed,
+                                 ion_ranges={26: (1, 5), 27: (2, 4), 28: (2, 5)},
+                                 abundance_only=[(2, 4), (24, 60), (38, 95), (58, 145), (60, 150), (88, 220), (92, 230)],
+                                 single_level_top_ion=False)
+    print(f"run dir {rundir}: {n} lines")
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("kind", choices=["classic1d"])
+    ap.add_argument("kind", choices=["classic1d", "kilonova1d"])
     ap.add_argument("rundir")
     ap.add_argument("--itstep", type=int, default=0)
     ap.add_argument("--ftstep", type=int, default=36)
@@ -65,9 +87,12 @@ def main():
     ap.add_argument("--dense-levels", type=int, default=15)
     ap.add_argument("--sparsity", type=float, default=0.15)
     ap.add_argument("--seed", type=int, default=20240607)
+    ap.add_argument("--ngrey", type=int, default=None, help="kilonova1d: override num_grey_timesteps of input.txt")
     args = ap.parse_args()
     if args.kind == "classic1d":
         setup_classic1d(args.rundir, args)
+    else:
+        setup_kilonova1d(args.rundir, args)
 
 
 if __name__ == "__main__":
