@@ -68,10 +68,12 @@ ARTIS_DEV double levelpop_g(const Ctx &c, int mgi, int element, int ui, int gl) 
     } else {
       const double superlevelpop_over_rho = pops[c.st.ion_first_nlte[ui] + nlev_nlte];
       if (superlevelpop_over_rho >= -0.9) {
-        // superlevel_boltzmann (ltepop.cc): g * exp(-(E-E0)/kT_exc) relative partition handled on host
+        // nltepop.cc:1543-1554 superlevel_boltzmann: relative to the first level of the superlevel
+        const int gls = gl0 + nlev_nlte + 1;
         const double T_exc = T_exc_of(c, mgi);
-        return superlevelpop_over_rho * (double)c.cs.rho[mgi] * (double)c.st.lev_statweight[gl] *
-               exp(-(c.st.lev_epsilon[gl] - c.st.lev_epsilon[gl0]) / KB / T_exc);
+        return superlevelpop_over_rho * (double)c.cs.rho[mgi] *
+               ((double)c.st.lev_statweight[gl] / (double)c.st.lev_statweight[gls] *
+                exp(-(c.st.lev_epsilon[gl] - c.st.lev_epsilon[gls]) / KB / T_exc));
       }
       nn = levelpop_lte_g(c, mgi, element, ui, gl0, gl);
     }
@@ -149,8 +151,35 @@ ARTIS_DEV double lut_interp(const Ctx &c, const double *table, int gl, int phixs
 
 // radfield.h:44 dbb with float T, W as passed by radfield::radfield (radfield.cc:930-934)
 ARTIS_DEV double dbb(double nu, float T, float W) { return W * TWOHOVERCLIGHTSQUARED * pow(nu, 3) / expm1(HOVERKB * nu / T); }
-// radfield.cc:898-935 (full-spectrum fit; the multi-bin branch is the nebular mode, not built in round 1)
-ARTIS_DEV double radfield_J(const Ctx &c, double nu, int mgi) { return dbb(nu, c.cs.TR[mgi], c.cs.W[mgi]); }
+// radfield.cc:596-610 select_bin: -2 below the first bin, -1 above the last one, else the first bin whose upper
+// boundary is greater than nu (std::upper_bound)
+ARTIS_DEV int radfield_select_bin(const Ctx &c, const double nu) {
+  if (nu < c.st.radfield_nu_lower_first) return -2;
+  int lo = 0, hi = c.st.opt_radfieldbincount;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (nu < c.st.radfieldbin_nu_upper[mid]) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
+  }
+  return lo >= c.st.opt_radfieldbincount ? -1 : lo;
+}
+// radfield.cc:898-943 radfield(): the bin's dilute black body from FIRST_NLTE_RADFIELD_TIMESTEP on when
+// MULTIBIN_RADFIELD_MODEL_ON (zero outside the bins and in bins without a fit), else the full-spectrum fit
+ARTIS_DEV double radfield_J(const Ctx &c, double nu, int mgi) {
+  if (c.st.opt_multibin_radfield && c.nts >= c.st.opt_first_nlte_radfield_timestep) {
+    const int binindex = radfield_select_bin(c, nu);
+    if (binindex >= 0) {
+      const size_t mgibinindex = (size_t)c.st.nonemptymgi_of_mgi[mgi] * c.st.opt_radfieldbincount + binindex;
+      const float W = c.cs.radfieldbin_W[mgibinindex];
+      if (W >= 0.f) return dbb(nu, c.cs.radfieldbin_TR[mgibinindex], W);
+    }
+    return 0.;
+  }
+  return dbb(nu, c.cs.TR[mgi], c.cs.W[mgi]);
+}
 
 // atomic.cc:437-454
 ARTIS_DEV double get_phixs_threshold_g(const Ctx &c, int gl_lower, int gl_upperion_ground, int t) {

@@ -40,6 +40,7 @@ constexpr double ONEOVERH = 1.509188961e+26;
 constexpr double HOVERKB = 4.799243681748932e-11;
 constexpr double HCLIGHTOVERFOURPI = 1.580764662876770e-17;
 constexpr double H_ionpot = 13.5979996 * EV;
+constexpr double FOURPI = 1.256637061600000e+01;
 constexpr double C_0 = 5.465e-11;
 constexpr double DBL_MAX_ = 1.7976931348623157e+308;
 
@@ -88,6 +89,9 @@ struct CellTables {
   double *ma_cum_intup;      // [ncells][nuptrans_total]       running sum of individ_internal_up_same
   double *cool_cum;          // [ncells][ncoolingterms]        cellhistory.cooling_contrib (kpkt.cc:167-308)
   double *collexc_cum;       // [ncells][nuptrans_total]       running `contrib` inside a COLLEXC term (kpkt.cc:706-724)
+  // [ncells][nbfcontinua], NO_LUT_PHOTOION builds only: get_corrphotoioncoeff (ratecoeff.cc:1247) of allcont[i], i.e.
+  // the bf-rate estimator of the previous timestep or the integral over the radiation field model
+  double *corrphoto;
 };
 
 struct Ctx {
@@ -109,6 +113,7 @@ struct Ctx {
   const int *lev_uion;       // unique ion index of a global level index      [nlevels_total]
   const int *uion_element;   // element index of a unique ion index           [includedions]
   const int *mgi_of_tabcell; // model grid index of a CellTables row           [tb.ncells]
+  const int *allcont_of_lut; // allcont index of LUT continuum index (-1 - cont_index + phixstargetindex) [nbfcontinua]
   CellTables tb;
   unsigned long long seed;
   int rank;

@@ -405,7 +405,7 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
       do_nonthermal_predeposit(c, p, t2, rng);
       break;
     case ARTIS_TYPE_NTLEPTON:
-      do_ntlepton(c, p, tl);
+      do_ntlepton(c, p, rng, tl);
       break;
     case ARTIS_TYPE_KPKT:
     case ARTIS_TYPE_PRE_KPKT:
@@ -447,7 +447,7 @@ ARTIS_DEV void do_packet_kind(const Ctx &c, ArtisPacket &p, const double t2, Kap
     if (p.type == ARTIS_TYPE_MA) {
       do_macroatom(c, p, rng, tl);
     } else if (p.type == ARTIS_TYPE_NTLEPTON) {
-      do_ntlepton(c, p, tl);
+      do_ntlepton(c, p, rng, tl);
     } else {
       const int mgi = cell_mgi(c, p.where);
       if (p.type == ARTIS_TYPE_PRE_KPKT || c.cs.thick[mgi] == 1) {

@@ -17,6 +17,11 @@ ARTIS_DEV void body_bf(const Ctx &c, const long long idx) {
   const int mgi = c.mgi_of_tabcell[tc];
   if (cell_uses_tables(c, mgi)) build_bf(c, mgi, (int)(idx % c.st.nbfcontinua));
 }
+ARTIS_DEV void body_corrphoto(const Ctx &c, const long long idx) {
+  const int tc = (int)(idx / c.st.nbfcontinua);
+  const int mgi = c.mgi_of_tabcell[tc];
+  if (cell_uses_tables(c, mgi)) build_corrphoto(c, mgi, (int)(idx % c.st.nbfcontinua));
+}
 ARTIS_DEV void body_ma(const Ctx &c, const long long idx) {
   const int tc = (int)(idx / c.st.nlevels_total);
   const int mgi = c.mgi_of_tabcell[tc];

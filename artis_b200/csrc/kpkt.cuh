@@ -166,10 +166,60 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
   }
 }
 
-// nonthermal.cc:1877-1978 do_ntlepton with NT_ON && NT_SOLVE_SPENCERFANO false (classic, kilonova_lte): every
-// non-thermal lepton thermalises into a k-packet
-ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p, Tally &tl) {
+// nonthermal.cc:1877-1978 do_ntlepton. Without the Spencer-Fano solution (classic, kilonova_lte) every non-thermal
+// lepton thermalises into a k-packet; with it (nebular NLTE) a fraction get_ntion_energyrate / deposition_rate_density
+// activates a macro-atom by non-thermal ionisation (select_nt_ionization2, nonthermal.cc:1858-1875). NT_EXCITATION_ON
+// is false in every shipped options header (frac_excitation = 0., nonthermal.cc:1898).
+ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   est_add(&c.es.ts_scalars[ARTIS_TS_NT_ENERGY_DEPOSITED], p.e_cmf);
+  const int mgi = cell_mgi(c, p.where);
+  if (c.st.opt_nt_on && c.st.opt_nt_solve_spencerfano && c.cs.thick[mgi] != 1) {
+    const double zrand = rng_uniform(rng);
+    // get_ntion_energyrate (nonthermal.cc:1847-1856): the same sum serves frac_ionization and select_nt_ionization2
+    double ratetotal = 0.;
+    for (int el = 0; el < c.st.nelements; el++) {
+      const int nions = c.st.el_nions[el];
+      for (int ion = 0; ion < nions - 1; ion++)
+        ratetotal += ion_ntion_energyrate(c, mgi, el, c.st.el_ionoffset[el] + ion, nions, ion);
+    }
+    const double frac_ionization = ratetotal / c.cs.nt_deposition_rate_density[mgi];
+    if (zrand < frac_ionization) {
+      const double zrand2 = rng_uniform(rng);
+      double ratesum = 0.;
+      int element = -1, lowerion = -1;
+      for (int el = 0; el < c.st.nelements && element < 0; el++) {
+        const int nions = c.st.el_nions[el];
+        for (int ion = 0; ion < nions - 1; ion++) {
+          ratesum += ion_ntion_energyrate(c, mgi, el, c.st.el_ionoffset[el] + ion, nions, ion);
+          if (ratesum >= zrand2 * ratetotal) {
+            element = el;
+            lowerion = ion;
+            break;
+          }
+        }
+      }
+      if (element < 0) {  // assert_always(false) in the reference
+        fatal(c, 263);
+        p.type = ARTIS_TYPE_KPKT;
+        return;
+      }
+      const int upperion = lowerion + nt_random_upperion(c, mgi, c.st.el_ionoffset[element] + lowerion,
+                                                         c.st.el_nions[element], lowerion, true, rng);
+      p.ma_element = element;
+      p.ma_ion = upperion;
+      p.ma_level = 0;
+      p.ma_activatingline = -99;
+      p.type = ARTIS_TYPE_MA;
+      stat_inc(tl, COUNTER_MA_STAT_ACTIVATION_NTCOLLION);
+      p.interactions += 1;
+      tl.interactions++;
+      p.last_event = 20;
+      p.trueemissiontype = -1;
+      p.trueemissionvelocity = -1;
+      stat_inc(tl, COUNTER_NT_STAT_TO_IONIZATION);
+      return;
+    }
+  }
   p.last_event = 22;
   p.type = ARTIS_TYPE_KPKT;
   stat_inc(tl, COUNTER_NT_STAT_TO_KPKT);

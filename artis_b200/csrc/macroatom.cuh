@@ -351,7 +351,16 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         gl = c.st.ion_leveloffset[ui] + upper;
         break;
       }
-      default:  // MA_INTERNALUPHIGHERNT: rate is zero unless NT_ON (not built yet)
+      case MA_INTERNALUPHIGHERNT: {  // macroatom.cc:856-876: non-thermal ionisation to the ground level of a higher ion
+        p.interactions += 1;
+        tl.interactions++;
+        const int ion = ui - c.st.el_ionoffset[element];
+        ui += nt_random_upperion(c, mgi, ui, c.st.el_nions[element], ion, false, rng);
+        gl = c.st.ion_leveloffset[ui];
+        stat_inc(tl, COUNTER_MA_STAT_INTERNALUPHIGHERNT);
+        break;
+      }
+      default:
         fatal(c, 229);
         p.type = ARTIS_TYPE_KPKT;
         return;

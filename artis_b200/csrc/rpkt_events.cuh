@@ -19,6 +19,39 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
   const bool kv = k.valid && (k.mgi == mgi);
   est_add(&c.es.ffheatingestimator[mgi], distance_e_cmf * (kv ? k.ffheating : 0.));
   tl.estim_atomics += 3;
+  // radfield.cc:764-829 update_bfestimators (DETAILED_BF_ESTIMATORS_ON): every continuum whose cross-section table
+  // covers nu gets gamma_contr[i] * distance_e_cmf / nu * doppler, where gamma_contr is the per-continuum scratch of the
+  // last opacity evaluation (at k.nu). The reference keeps that scratch as an nbfcontinua-long array per host
+  // thread; here the term is re-evaluated at k.nu from the per-cell table -- same function, same inputs, same bits.
+  if (c.st.opt_detailed_bf_estimators && kv && distance_e_cmf != 0) {
+    const int tc = tabcell(c, mgi);
+    const double distance_e_cmf_over_nu = distance_e_cmf / nu * doppler_packet(c, p);
+    const int i0k = bf_stop_index(c, k.nu);
+    int i0 = bf_stop_index(c, nu);
+    if (i0k < i0) i0 = i0k;  // gamma_contr[i] is zero from the first continuum with k.nu < nu_edge on
+    const int ilo = bf_start_index(c, nu, i0);
+    const double expfac = exp(-HOVERKB * k.nu / (double)c.cs.Te[mgi]);
+    double *row = c.es.bfrate_raw + (size_t)tc * c.st.nbfcontinua;
+    for (int i = ilo; i < i0; i++) {
+      double gcontr;
+      kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr);
+      if (gcontr != 0.) {
+        est_add(&row[i], gcontr * distance_e_cmf_over_nu);
+        tl.estim_atomics++;
+      }
+    }
+  }
+  // radfield.cc:843-874: frequency-binned J and nuJ of the multi-bin radiation field model
+  if (c.st.opt_multibin_radfield) {
+    const int binindex = radfield_select_bin(c, nu);
+    if (binindex >= 0) {
+      const size_t mgibinindex = (size_t)tabcell(c, mgi) * c.st.opt_radfieldbincount + binindex;
+      est_add(&c.es.radfieldbin_J_raw[mgibinindex], distance_e_cmf);
+      est_add(&c.es.radfieldbin_nuJ_raw[mgibinindex], distance_e_cmf * nu);
+      int_add(&c.es.radfieldbin_contribcount[mgibinindex], 1);
+      tl.estim_atomics += 3;
+    }
+  }
   // without a valid opacity scratch for this cell every contribution below is +0.0: nothing to add (grey cells)
   if (kv && (!c.st.opt_no_lut_photoion || !c.st.opt_no_lut_bfheating)) {
     const int nelements = c.st.nelements, max_nions = c.st.max_nions;

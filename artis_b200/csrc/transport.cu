@@ -30,6 +30,10 @@ __global__ void k_bf(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_bf(d_ctx, i);
 }
+__global__ void k_corrphoto(long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_corrphoto(d_ctx, i);
+}
 __global__ void k_ma(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_ma(d_ctx, i);
@@ -651,6 +655,7 @@ int grid_for(long long n, int block, int blocks_per_sm) {
 }
 void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
+void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {

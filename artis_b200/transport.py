@@ -108,7 +108,10 @@ class Transport:
 
     def download_estimators(self):
         s = self.static
-        d = abi.empty_estimators(s["npts_model"], s["nelements"], s["max_nions"], s["nlines"])
+        nonempty = int(s["nonempty_npts_model"])
+        nbins = nonempty * int(s["opt_radfieldbincount"]) if s.get("opt_multibin_radfield") else 0
+        nbfrate = nonempty * int(s["nbfcontinua"]) if s.get("opt_detailed_bf_estimators") else 0
+        d = abi.empty_estimators(s["npts_model"], s["nelements"], s["max_nions"], s["nlines"], nbins, nbfrate)
         est, keep = abi.build_struct(abi.ArtisEstimators, abi.ESTIM_FIELDS, d, writable=True)
         self._check(self.lib.artis_gpu_download_estimators(C.byref(est)), "artis_gpu_download_estimators")
         return d

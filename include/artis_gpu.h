@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define ARTIS_GPU_ABI_VERSION 3
+#define ARTIS_GPU_ABI_VERSION 4
 
 enum artis_gpu_error {
   ARTIS_OK = 0,

@@ -88,6 +88,7 @@ inline void flatten_static(ArtisStaticTables *T, Storage *st) {
   t.opt_detailed_bf_usefromtimestep = DETAILED_BF_ESTIMATORS_USEFROMTIMESTEP;
   t.opt_nt_on = NT_ON;
   t.opt_nt_solve_spencerfano = NT_SOLVE_SPENCERFANO;
+  t.opt_nt_max_auger_electrons = NT_MAX_AUGER_ELECTRONS;
   t.opt_relativistic_doppler = USE_RELATIVISTIC_DOPPLER_SHIFT;
   t.opt_instant_particle_deposition = INSTANT_PARTICLE_DEPOSITION;
 #ifdef RECORD_LINESTAT
@@ -393,6 +394,14 @@ inline void flatten_static(ArtisStaticTables *T, Storage *st) {
     t.gam_prob = pr;
     t.nuc_decayenergygamma = eg;
   }
+  // ---- multi-bin radiation field model (radfield.cc:43, artisoptions nu_lower_first_initial)
+  t.radfield_nu_lower_first = nu_lower_first_initial;
+  {
+    const int nb = MULTIBIN_RADFIELD_MODEL_ON ? RADFIELDBINCOUNT : 0;
+    double *up = st->D(nb);
+    for (int b = 0; b < nb; b++) up[b] = refglue::radfieldbin_nu_upper(b);
+    t.radfieldbin_nu_upper = up;
+  }
 }
 
 inline void flatten_cellstate(ArtisCellState *C, Storage *st, const int nts) {
@@ -474,6 +483,55 @@ inline void flatten_cellstate(ArtisCellState *C, Storage *st, const int nts) {
                  sizeof(double) * c.total_nlte_levels);
     c.nlte_pops = p;
   }
+  // ---- radiation-field bin solutions and bf-rate estimators of the previous timestep (radfield.cc:30-45,73)
+  const int nonempty = grid::get_nonempty_npts_model();
+  c.nradfieldbins = MULTIBIN_RADFIELD_MODEL_ON ? nonempty * RADFIELDBINCOUNT : 0;
+  {
+    float *bw = st->F(c.nradfieldbins), *bt = st->F(c.nradfieldbins);
+    for (int i = 0; i < c.nradfieldbins; i++) refglue::radfieldbin_solution(i, &bw[i], &bt[i]);
+    c.radfieldbin_W = bw;
+    c.radfieldbin_TR = bt;
+  }
+  c.nprevbfrate = DETAILED_BF_ESTIMATORS_ON ? nonempty * globals::nbfcontinua : 0;
+  {
+    float *pb = st->F(c.nprevbfrate);
+    for (int i = 0; i < c.nprevbfrate; i++) pb[i] = refglue::prev_bfrate_normed(i);
+    c.prev_bfrate_normed = pb;
+  }
+  // ---- Spencer-Fano solution (nonthermal.cc:95-151); only the numbers the transport path reads
+  const bool sf = NT_ON && NT_SOLVE_SPENCERFANO;
+  c.nt_nions = NT_ON ? NM * NI : 0;
+  c.nt_nauger = NT_MAX_AUGER_ELECTRONS + 1;
+  {
+    float *ep = st->F(c.nt_nions), *pa = st->F((size_t)c.nt_nions * c.nt_nauger),
+          *ea = st->F((size_t)c.nt_nions * c.nt_nauger);
+    double *wf = st->D(c.nt_nions), *dep = st->D(NT_ON ? NM : 0), *ntot = st->D(NT_ON ? NM : 0);
+    if (NT_ON) {
+      for (int m = 0; m < c.npts_model; m++) {
+        if (grid::get_numassociatedcells(m) <= 0) continue;
+        dep[m] = refglue::nt_deposition_rate_density_raw(m);
+        ntot[m] = get_nntot(m);
+        for (int el = 0; el < NE; el++)
+          for (int ion = 0; ion < get_nions(el); ion++) {
+            const int ui = get_uniqueionindex(el, ion);
+            const size_t k = (size_t)m * NI + ui;
+            if (ion < get_nions(el) - 1) wf[k] = refglue::nt_ratecoeff_wfapprox(m, el, ion);
+            if (!sf) continue;
+            ep[k] = refglue::nt_eff_ionpot(m, ui);
+            for (int a = 0; a < c.nt_nauger; a++) {
+              pa[k * c.nt_nauger + a] = refglue::nt_prob_num_auger(m, ui * c.nt_nauger + a, false);
+              ea[k * c.nt_nauger + a] = refglue::nt_prob_num_auger(m, ui * c.nt_nauger + a, true);
+            }
+          }
+      }
+    }
+    c.nt_eff_ionpot = ep;
+    c.nt_ratecoeff_wfapprox = wf;
+    c.nt_prob_num_auger = pa;
+    c.nt_ionenfrac_num_auger = ea;
+    c.nt_deposition_rate_density = dep;
+    c.nntot = ntot;
+  }
 }
 
 // Copies the reference's estimator globals (after the reference's own update_packets) into the E-list struct.
@@ -522,6 +580,18 @@ inline void flatten_estimators(ArtisEstimators *E, Storage *st, const int nts) {
   memcpy(ec, globals::ecounter, sizeof(int) * e.nlines);
   memcpy(ac, globals::acounter, sizeof(int) * e.nlines);
 #endif
+  e.nradfieldbins = MULTIBIN_RADFIELD_MODEL_ON ? grid::get_nonempty_npts_model() * RADFIELDBINCOUNT : 0;
+  e.nbfrate = DETAILED_BF_ESTIMATORS_ON ? grid::get_nonempty_npts_model() * globals::nbfcontinua : 0;
+  {
+    double *bj = st->D(e.nradfieldbins), *bn = st->D(e.nradfieldbins), *br = st->D(e.nbfrate);
+    int *bc = st->I(e.nradfieldbins);
+    for (int i = 0; i < e.nradfieldbins; i++) refglue::radfieldbin_raw(i, &bj[i], &bn[i], &bc[i]);
+    for (int i = 0; i < e.nbfrate; i++) br[i] = refglue::bfrate_raw(i);
+    e.radfieldbin_J_raw = bj;
+    e.radfieldbin_nuJ_raw = bn;
+    e.radfieldbin_contribcount = bc;
+    e.bfrate_raw = br;
+  }
   e.J = J;
   e.nuJ = nuJ;
   e.ffheatingestimator = ff;

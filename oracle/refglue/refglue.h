@@ -6,6 +6,17 @@
 namespace refglue {
 double *radfield_J(void);    // radfield.cc:100
 double *radfield_nuJ(void);  // radfield.cc:108
+// multi-bin radiation field and detailed bf estimators (radfield.cc:30-45,73-74), flat index nonemptymgi * N + i
+double radfieldbin_nu_upper(int binindex);
+void radfieldbin_solution(int mgibinindex, float *W, float *T_R);
+void radfieldbin_raw(int mgibinindex, double *J_raw, double *nuJ_raw, int *contribcount);
+float prev_bfrate_normed(int index);
+double bfrate_raw(int index);
+// Spencer-Fano solution of the host solver (nonthermal.cc:95-151) and the work-function fallback (:1362)
+float nt_eff_ionpot(int modelgridindex, int uniqueionindex);
+float nt_prob_num_auger(int modelgridindex, int index, bool energyweighted);
+double nt_ratecoeff_wfapprox(int modelgridindex, int element, int ion);
+double nt_deposition_rate_density_raw(int modelgridindex);
 void coolinglist_entry(int i, int *type, int *level, int *upperlevel);  // kpkt.cc:27-35
 int gamma_nlines(int nucindex);                                         // gammapkt.cc:24-31
 void gamma_line(int nucindex, int k, double *energy, double *probability);

@@ -38,6 +38,7 @@ void be_timer_begin() { g_t0 = std::chrono::steady_clock::now(); }
 double be_timer_end_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_t0).count(); }
 void be_run_levelpop(long long n) { for (long long i = 0; i < n; i++) artis::body_levelpop(g_ctx, i); }
 void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g_ctx, i); }
+void be_run_corrphoto(long long n) { for (long long i = 0; i < n; i++) artis::body_corrphoto(g_ctx, i); }
 void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
 void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {

@@ -18,7 +18,8 @@ import gen_atomic_data  # noqa: E402
 REF = os.environ.get("ARTIS_REF", "/root/reference")
 
 
-def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax=None, model_type=None, ngrey=None):
+def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax=None, model_type=None, ngrey=None,
+                    resume=False):
     lines = open(template).read().splitlines()
     out = []
     k = 0
@@ -35,6 +36,8 @@ def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax
             body = f"{tmin} {tmax}".ljust(25)
         if k == 7 and model_type is not None:
             body = f"{model_type}".ljust(25)
+        if k == 16 and resume:  # simulation_continued_from_saved
+            body = "1".ljust(25)
         if k == 19 and ngrey is not None:  # cell_is_optically_thick num_grey_timesteps
             body = f"{body.split()[0]} {ngrey}".ljust(25)
         out.append(body + ("#" + comment if comment else ""))
@@ -75,9 +78,25 @@ def setup_kilonova1d(rundir, args):
     print(f"run dir {rundir}: {n} lines")
 
 
+def setup_nebular1zone(rundir, args):
+    """tests/setup_nebularonezone.sh: the one-zone nebular model (model.txt, abundances.txt, recombrates.txt,
+    input-newrun.txt of tests/nebularonezone_inputfiles verbatim) with synthetic Fe/Co/Ni atomic data"""
+    src = os.path.join(REF, "tests", "nebularonezone_inputfiles")
+    os.makedirs(rundir, exist_ok=True)
+    for f in ("model.txt", "abundances.txt", "recombrates.txt"):
+        shutil.copy(os.path.join(src, f), rundir)
+    for f in os.listdir(os.path.join(REF, "data")):
+        shutil.copy(os.path.join(REF, "data", f), rundir)
+    write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep,
+                    resume=args.resume)
+    n = gen_atomic_data.generate(rundir, (26, 27, 28), args.nions, args.nlevels, args.dense_levels, args.sparsity,
+                                 args.seed, single_level_top_ion=False)
+    print(f"run dir {rundir}: {n} lines")
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("kind", choices=["classic1d", "kilonova1d"])
+    ap.add_argument("kind", choices=["classic1d", "kilonova1d", "nebular1zone"])
     ap.add_argument("rundir")
     ap.add_argument("--itstep", type=int, default=0)
     ap.add_argument("--ftstep", type=int, default=36)
@@ -88,11 +107,15 @@ def main():
     ap.add_argument("--sparsity", type=float, default=0.15)
     ap.add_argument("--seed", type=int, default=20240607)
     ap.add_argument("--ngrey", type=int, default=None, help="kilonova1d: override num_grey_timesteps of input.txt")
+    ap.add_argument("--resume", action="store_true",
+                    help="nebular1zone: write input.txt to continue from the gridsave/packets files of timestep itstep-1")
     args = ap.parse_args()
     if args.kind == "classic1d":
         setup_classic1d(args.rundir, args)
-    else:
+    elif args.kind == "kilonova1d":
         setup_kilonova1d(args.rundir, args)
+    else:
+        setup_nebular1zone(args.rundir, args)
 
 
 if __name__ == "__main__":

@@ -32,6 +32,7 @@ def gpu_lib():
     return GPU_LIB
 
 
-@pytest.fixture(scope="session", params=["classic_nogrey_ts12.npz", "classic_grey_ts8.npz", "kilonova_lte_ts1.npz"])
+@pytest.fixture(scope="session", params=["classic_nogrey_ts12.npz", "classic_grey_ts8.npz", "kilonova_lte_ts1.npz",
+                                        "nebular_nlte_ts8.npz"])
 def fixture_name(request):
     return request.param

@@ -14,6 +14,19 @@ import statlib  # noqa: E402
 GOLDEN = os.path.join(HERE, "golden")
 
 
+def _section(snap, prefix, fields):
+    """Fields that a fixture written before an ABI extension does not hold are zero / empty: every extension is a
+    switch that is off (0 entries) in the older option sets."""
+    d = {}
+    for kind, _, fname, _ in fields:
+        key = prefix + fname
+        if key in snap:
+            d[fname] = snap[key][0].item() if kind == "S" else snap[key]
+        elif kind == "S":
+            d[fname] = 0
+    return d
+
+
 def load_fixture(name):
     z = np.load(os.path.join(GOLDEN, name), allow_pickle=False)
     snap = {}
@@ -25,8 +38,8 @@ def load_fixture(name):
     for key in ("packets", "gpackets"):
         if key in probe:
             probe[key] = np.frombuffer(probe[key].tobytes(), dtype=abi.PACKET_DTYPE).copy()
-    static = {f[2]: (snap["static." + f[2]][0].item() if f[0] == "S" else snap["static." + f[2]]) for f in abi.STATIC_FIELDS}
-    cell = {f[2]: (snap["cell." + f[2]][0].item() if f[0] == "S" else snap["cell." + f[2]]) for f in abi.CELL_FIELDS}
+    static = _section(snap, "static.", abi.STATIC_FIELDS)
+    cell = _section(snap, "cell.", abi.CELL_FIELDS)
     return {"static": static, "cell": cell, "pre": snap["packets.pre"], "ref_rows": z["ref_rows"],
             "names": [str(x) for x in z["ref_names"]], "nts": int(z["nts"]), "probe": probe}
 

@@ -44,6 +44,22 @@ def summary(static, cell, est, post, pre):
     for key, short in (("gammaestimator", "gamma"), ("bfheatingestimator", "bfheat")):
         a = np.asarray(est[key][: n * ng]).reshape(n, ng)
         d[short + "_tot"] = a[good].sum()
+    # multi-bin radiation field and detailed bf-rate estimators (nebular NLTE option set; radfield.cc:764-874): totals and
+    # four contiguous groups of bins / continua, summed over the non-empty cells
+    nb = int(est.get("nradfieldbins", 0) or 0)
+    if nb > 0:
+        for key, short in (("radfieldbin_J_raw", "binJ"), ("radfieldbin_nuJ_raw", "binnuJ"),
+                           ("radfieldbin_contribcount", "bincount")):
+            a = np.asarray(est[key][:nb], dtype=float).reshape(-1, int(static["opt_radfieldbincount"])).sum(0)
+            d[short + "_tot"] = a.sum()
+            for g, part in enumerate(np.array_split(a, 4)):
+                d[f"{short}_q{g}"] = part.sum()
+    nr = int(est.get("nbfrate", 0) or 0)
+    if nr > 0:
+        a = np.asarray(est["bfrate_raw"][:nr]).reshape(-1, int(static["nbfcontinua"])).sum(0)
+        d["bfrate_tot"] = a.sum()
+        for g, part in enumerate(np.array_split(a, 4)):
+            d[f"bfrate_q{g}"] = part.sum()
     ts = np.asarray(est["ts_scalars"])
     for i, nm in enumerate(("gamma_dep", "positron_dep", "electron_dep", "electron_emission", "alpha_dep",
                             "alpha_emission", "gamma_emission", "cmf_lum", "nt_energy_deposited")):
@@ -91,6 +107,12 @@ def ztest(ref_rows, dev_rows, names):
     for j, nm in enumerate(names):
         r, d = ra[:, j], da[:, j]
         se = np.sqrt(r.var(ddof=1) / r.size + d.var(ddof=1) / d.size)
+        # rare-event quantities (e.g. a spectrum bin hit by a packet in a few runs out of hundreds): a small ensemble
+        # that happens to hold no event has zero sample variance and the unpooled error is meaningless; under the
+        # null hypothesis both ensembles share one distribution, so use its pooled variance
+        if min((r != 0).mean(), (d != 0).mean()) < 0.2:
+            both = np.concatenate([r, d])
+            se = np.sqrt(both.var(ddof=1) * (1.0 / r.size + 1.0 / d.size))
         diff = d.mean() - r.mean()
         scale = max(abs(r.mean()), abs(d.mean()))
         if scale == 0 or abs(diff) <= 1e-9 * scale:  # identical up to summation order (deterministic quantities)
