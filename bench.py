@@ -36,6 +36,24 @@ UNIT = "interactions/s"
 BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_base")
 BENCH_TS = 25
 REF_EXE = os.path.join(REPO, "oracle", "_ref", "classic", "sn3d_ref")
+WORKLOAD_NAME = ("classicmode W7-like 1D model (tests/classicmode_inputfiles, artisoptions_classic.h, 100^3 grid), "
+                 "synthetic atomic data {nlines} lines / {nbf} bf continua / {nlev} levels, timestep {ts}")
+FALLBACK_FIXTURE = "classic_nogrey_ts12.npz"
+
+
+def select_workload(name):
+    """--workload nebular: BASELINE.json config 2, the one-zone nebular NLTE model (tests/nebularonezone_inputfiles,
+    artisoptions_nltenebular.h with the overrides of tests/setup_nebularonezone.sh, 50^3 grid) at timestep 8; the
+    default stays the classic-mode model, whose timestep is the interaction-rich one the metric is about."""
+    global BENCH_RUN, BENCH_TS, REF_EXE, WORKLOAD_NAME, FALLBACK_FIXTURE
+    if name == "nebular":
+        BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_neb")
+        BENCH_TS = 8
+        REF_EXE = os.path.join(REPO, "oracle", "_ref", "nebular", "sn3d_ref")
+        WORKLOAD_NAME = ("nebular one-zone NLTE model (tests/nebularonezone_inputfiles, artisoptions_nltenebular.h with the "
+                         "overrides of tests/setup_nebularonezone.sh, 50^3 grid), synthetic atomic data {nlines} lines / "
+                         "{nbf} bf continua / {nlev} levels, timestep {ts}")
+        FALLBACK_FIXTURE = "nebular_nlte_ts8.npz"
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -47,14 +65,12 @@ def load_workload():
     if os.path.exists(snap):
         s = snapshot.load(snap)
         st, cs = snapshot.static_tables(s), snapshot.cell_state(s)
-        name = (f"classicmode W7-like 1D model (tests/classicmode_inputfiles, artisoptions_classic.h, 100^3 grid), "
-                f"synthetic atomic data {st['nlines']} lines / {st['nbfcontinua']} bf continua / {st['nlevels_total']} "
-                f"levels, timestep {BENCH_TS}")
+        name = WORKLOAD_NAME.format(nlines=st["nlines"], nbf=st["nbfcontinua"], nlev=st["nlevels_total"], ts=BENCH_TS)
         return st, cs, s["packets.pre"].copy(), name
     sys.path.insert(0, os.path.join(REPO, "tests"))
     import goldenlib
-    fx = goldenlib.load_fixture("classic_nogrey_ts12.npz")
-    return fx["static"], fx["cell"], fx["pre"], "FALLBACK golden fixture classic_nogrey_ts12 (bench snapshot missing)"
+    fx = goldenlib.load_fixture(FALLBACK_FIXTURE)
+    return fx["static"], fx["cell"], fx["pre"], f"FALLBACK golden fixture {FALLBACK_FIXTURE} (bench snapshot missing)"
 
 
 def replicate(pre, P, rank, step):
@@ -126,7 +142,8 @@ def run_reference(nproc, steps, warmup):
     if not (os.path.exists(REF_EXE) and os.path.exists(os.path.join(BENCH_RUN, f"gridsave_ts{BENCH_TS}.tmp"))):
         return None
     keep = ("adata.txt", "transitiondata.txt", "phixsdata_v2.txt", "compositiondata.txt", "model.txt", "abundances.txt",
-            "input.txt", "ratecoeff.dat", "bflist.dat", f"gridsave_ts{BENCH_TS}.tmp", f"packets_0000_ts{BENCH_TS}.tmp")
+            "input.txt", "ratecoeff.dat", "bflist.dat", "recombrates.txt", f"gridsave_ts{BENCH_TS}.tmp",
+            f"packets_0000_ts{BENCH_TS}.tmp")
     tot_inter, tot_sec = 0.0, 0.0
     npk = 0
     with tempfile.TemporaryDirectory(prefix="artis_ref_") as tmp:
@@ -187,7 +204,9 @@ def main():
     ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
     ap.add_argument("--scheduler-kernels", type=int, default=0, choices=(0, 1, 2),
                     help="1: one persistent kernel with every role, 2: light + heavy kernels side by side (0: library default)")
+    ap.add_argument("--workload", default="classic", choices=["classic", "nebular"])
     a = ap.parse_args()
+    select_workload(a.workload)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -52,7 +52,8 @@ def setup_classic1d(rundir, args):
         shutil.copy(os.path.join(src, f), rundir)
     for f in os.listdir(os.path.join(REF, "data")):
         shutil.copy(os.path.join(REF, "data", f), rundir)
-    write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep)
+    write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep,
+                    resume=args.resume)
     n = gen_atomic_data.generate(rundir, tuple(int(z) for z in args.elements.split(",")), args.nions, args.nlevels,
                                  args.dense_levels, args.sparsity, args.seed)
     print(f"run dir {rundir}: {n} lines")
@@ -108,7 +109,7 @@ def main():
     ap.add_argument("--seed", type=int, default=20240607)
     ap.add_argument("--ngrey", type=int, default=None, help="kilonova1d: override num_grey_timesteps of input.txt")
     ap.add_argument("--resume", action="store_true",
-                    help="nebular1zone: write input.txt to continue from the gridsave/packets files of timestep itstep-1")
+                    help="write input.txt to continue from the gridsave/packets files of timestep itstep-1")
     args = ap.parse_args()
     if args.kind == "classic1d":
         setup_classic1d(args.rundir, args)
