@@ -313,7 +313,10 @@ ARTIS_DEV double corrphoto_integrand(const Ctx &c, const int mgi, const int tabl
 // the boundaries of the radiation-field bins and jumps at the latter, so here every such piece gets a fixed 8-point
 // Gauss-Legendre rule: deterministic, and closer to the exact integral than the reference's own tolerance.
 // Stated tolerance against the reference: 5e-3 relative (tests/probelib.py, macro-atom rate probe).
-ARTIS_DEV double corrphotoioncoeff_integral(const Ctx &c, const int mgi, const int tc, const int ui, const int gl, const int t) {
+// Returns the sum over the knot intervals first, first + stride, ... (a single thread passes 0, 1; the lanes of a warp
+// pass lane, 32 and add their parts, transport.cu k_corrphoto); the caller multiplies by FOURPI * phixsprobability.
+ARTIS_DEV double corrphotoioncoeff_integral(const Ctx &c, const int mgi, const int tc, const int ui, const int gl, const int t,
+                                            const int first = 0, const int stride = 1) {
   const double x8[4] = {0.1834346424956498, 0.5255324099163290, 0.7966664774136267, 0.9602898564975363};
   const double w8[4] = {0.3626837833783620, 0.3137066458778873, 0.2223810344533745, 0.1012285362903763};
   const double E_threshold = phixs_threshold(c, ui, gl, t);
@@ -331,7 +334,7 @@ ARTIS_DEV double corrphotoioncoeff_integral(const Ctx &c, const int mgi, const i
   const bool binned = c.st.opt_multibin_radfield && c.nts >= c.st.opt_first_nlte_radfield_timestep;
   const int nknots = c.st.nphixspoints;
   double total = 0.;
-  for (int k = 0; k + 1 < nknots; k++) {
+  for (int k = first; k + 1 < nknots; k += stride) {
     double lo = nu_threshold * (1. + k * c.st.nphixsnuincrement);
     const double hi = (k + 2 == nknots) ? nu_max_phixs : nu_threshold * (1. + (k + 1) * c.st.nphixsnuincrement);
     int bin = binned ? radfield_select_bin(c, lo) : -1;
@@ -364,19 +367,33 @@ ARTIS_DEV double corrphotoioncoeff_integral(const Ctx &c, const int mgi, const i
       lo = b;
     }
   }
-  return total * FOURPI * get_phixsprobability_g(c, gl, t);
+  return total;
 }
 // ratecoeff.cc:1247-1310 with NO_LUT_PHOTOION, for allcont[i] of one cell: the bf-rate estimator of the previous
 // timestep where DETAILED_BF_ESTIMATORS_ON has one (radfield.cc:1440-1457), else the integral above
-ARTIS_DEV void build_corrphoto(const Ctx &c, const int mgi, const int i) {
+// `first`/`stride` as in corrphotoioncoeff_integral; *needs_sum is set when the returned value is a partial integral
+// that the caller has to add up over its threads and scale with corrphoto_scale()
+ARTIS_DEV double build_corrphoto_part(const Ctx &c, const int mgi, const int i, const int first, const int stride,
+                                      bool *needs_sum) {
   const int tc = tabcell(c, mgi);
   double gammacorr = -1.;
   if (c.st.opt_detailed_bf_estimators && c.nts >= c.st.opt_detailed_bf_usefromtimestep)
     gammacorr = (double)c.cs.prev_bfrate_normed[(size_t)tc * c.st.nbfcontinua + i];
+  *needs_sum = !(gammacorr > 0);
   if (!(gammacorr > 0)) {
-    gammacorr = corrphotoioncoeff_integral(c, mgi, tc, c.cont_uion[i], c.cont_level_g[i], c.st.cont_phixstargetindex[i]);
+    gammacorr = corrphotoioncoeff_integral(c, mgi, tc, c.cont_uion[i], c.cont_level_g[i], c.st.cont_phixstargetindex[i],
+                                           first, stride);
   }
-  c.tb.corrphoto[(size_t)tc * c.st.nbfcontinua + i] = gammacorr;
+  return gammacorr;
+}
+ARTIS_DEV double corrphoto_scale(const Ctx &c, const int i) {
+  return FOURPI * get_phixsprobability_g(c, c.cont_level_g[i], c.st.cont_phixstargetindex[i]);
+}
+ARTIS_DEV void build_corrphoto(const Ctx &c, const int mgi, const int i) {
+  bool needs_sum;
+  double gammacorr = build_corrphoto_part(c, mgi, i, 0, 1, &needs_sum);
+  if (needs_sum) gammacorr *= corrphoto_scale(c, i);
+  c.tb.corrphoto[(size_t)tabcell(c, mgi) * c.st.nbfcontinua + i] = gammacorr;
 }
 
 // macroatom.cc:57-159 calculate_macroatom_transitionrates for one (cell, level)

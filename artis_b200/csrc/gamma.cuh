@@ -198,7 +198,7 @@ ARTIS_DEV void do_gamma(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng,
   const double tau_next = -1. * log(zrand0);
   int snext = 0;
   double sdist = boundary_cross(c, p, &snext);
-  const double maxsdist = c.st.rmax * p.prop_time / c.st.tmin;
+  const double maxsdist = max_sdist(c, p, sdist);
   if (sdist > maxsdist) {
     fatal(c, 410);
     p.type = ARTIS_TYPE_ESCAPE;

@@ -14,6 +14,12 @@ struct KappaCache {
   double nu, total, es, ff, bf, ffheating;
   int mgi;
   bool valid;
+  // DETAILED_BF_ESTIMATORS_ON: a scheduler that sets defer_bfest gets the bf-rate estimator sweep of update_estimators
+  // (radfield.cc:764-829) left pending here -- frequency of the step's midpoint, distance_e_cmf / nu * doppler, cell row --
+  // and runs it with a whole warp right after the step (transport.cu coop_bfest_flush); bfest_factor == 0: nothing pending
+  bool defer_bfest = false;
+  int bfest_tc = 0;
+  double bfest_nu = 0., bfest_factor = 0.;
   double gamma_contr[MAX_GROUNDCONT];
 };
 
@@ -36,9 +42,121 @@ ARTIS_DEV double cellcoordmin(const Ctx &c, int cellindex, int d) {
 }
 ARTIS_DEV double wid_init(const Ctx &c) { return 2 * c.st.coordmax_x / c.st.ncoordgrid_x; }
 
-// ---- boundary.cc:101-330 boundary_cross (GRID_UNIFORM) ----------------------------------------------------------
+// ---- boundary.cc:14-99 get_shellcrossdist: closest forward distance to an expanding spherical shell, -1 if none ----
+ARTIS_DEV double get_shellcrossdist(const Ctx &c, const double pos[3], const double dir[3], const double shellradius,
+                                    const bool isinnerboundary, const double tstart) {
+  const double speed = vec_len(dir) * CLIGHT_PROP;
+  const double q = shellradius / tstart / speed;
+  const double a = dot3(dir, dir) - q * q;                                       // pow(x, 2) in the reference
+  const double b = 2 * (dot3(dir, pos) - shellradius * shellradius / tstart / speed);
+  const double cc = dot3(pos, pos) - shellradius * shellradius;
+  const double discriminant = b * b - 4 * a * cc;
+  if (discriminant < 0) {
+    if (!(shellradius < vec_len(pos))) fatal(c, 110);  // assert_always in the reference
+    return -1;
+  } else if (discriminant > 0) {
+    double d1 = (-b + sqrt(discriminant)) / 2 / a;
+    double d2 = (-b - sqrt(discriminant)) / 2 / a;
+    double posfinal1[3], posfinal2[3];
+    for (int d = 0; d < 3; d++) {
+      posfinal1[d] = pos[d] + d1 * dir[d];
+      posfinal2[d] = pos[d] + d2 * dir[d];
+    }
+    const double shellradiusfinal1 = shellradius / tstart * (tstart + d1 / speed);
+    const double shellradiusfinal2 = shellradius / tstart * (tstart + d2 / speed);
+    if (!(fabs(vec_len(posfinal1) / shellradiusfinal1 - 1.) < 1e-3) || !(fabs(vec_len(posfinal2) / shellradiusfinal2 - 1.) < 1e-3))
+      fatal(c, 111);  // assert_always in the reference
+    // a solution that enters the boundary from the wrong radial direction is not a crossing
+    if (isinnerboundary) {
+      if (dot3(posfinal1, dir) > 0.) d1 = -1;
+      if (dot3(posfinal2, dir) > 0.) d2 = -1;
+    } else {
+      if (dot3(posfinal1, dir) < 0.) d1 = -1;
+      if (dot3(posfinal2, dir) < 0.) d2 = -1;
+    }
+    if (d1 < 0 && d2 < 0) return -1;
+    if (d2 < 0) return d1;
+    if (d1 < 0) return d2;
+    return fmin(d1, d2);
+  }
+  if (!(shellradius <= vec_len(pos))) fatal(c, 112);
+  return -1.;
+}
+// grid.cc:76-95 wid_init and :131-139 get_cellcoordmax for GRID_SPHERICAL1D (cellindex == shell number)
+ARTIS_DEV double wid_init_1d(const Ctx &c, const int cellindex) {
+  const int mgi = c.st.cell_mgi[cellindex];
+  const double v_inner = mgi > 0 ? c.st.vout_model[mgi - 1] : 0.;
+  return (c.st.vout_model[mgi] - v_inner) * c.st.tmin;
+}
+// ---- boundary.cc:101-330 boundary_cross, GRID_SPHERICAL1D branch: one radial coordinate, inner and outer shell ------
+template <class P>
+ARTIS_DEV double boundary_cross_1d(const Ctx &c, P &p, int *snext) {
+  const double tstart = p.prop_time;
+  const int cellindex = p.where;
+  const double tmin = c.st.tmin;
+  const double initpos = vec_len(p.pos);
+  const double cmin = c.st.cell_posmin_x[cellindex];
+  const double cmax = cmin + wid_init_1d(c, cellindex);
+  const double vel = dot3(p.pos, p.dir) / vec_len(p.pos) * CLIGHT_PROP;
+  const int ncoord = c.st.ncoordgrid_x;
+  // 10 cm tolerance repair path (boundary.cc:165-222) on the radial coordinate
+  for (int flip = 0; flip < 2; flip++) {
+    const int direction = flip ? ARTIS_POS_X : ARTIS_NEG_X;
+    const int invdirection = !flip ? ARTIS_POS_X : ARTIS_NEG_X;
+    const int stride = flip ? -1 : 1;
+    const bool isoutside = flip ? (initpos < (cmin / tmin * tstart - 10.)) : (initpos > (cmax / tmin * tstart + 10.));
+    if (isoutside && (p.last_cross != direction)) {
+      if ((vel - (initpos / tstart)) > 0) {
+        if ((cellindex == (ncoord - 1) && stride > 0) || (cellindex == 0 && stride < 0)) {
+          *snext = -99;
+          return 0;
+        }
+        *snext = p.where + stride;
+        p.last_cross = invdirection;
+        return 0;
+      }
+      // "pretending last_cross is direction" has no effect here: boundary.cc:235 resets last_cross for this grid
+    }
+  }
+  // invalid directions are handled by negative distances (boundary.cc:235-245)
+  const double r_inner = cmin * tstart / tmin;
+  const double d_inner = (r_inner > 0.) ? get_shellcrossdist(c, p.pos, p.dir, r_inner, true, tstart) : -1.;
+  const double t_min = d_inner / CLIGHT_PROP;
+  const double r_outer = cmax * tstart / tmin;
+  const double d_outer = get_shellcrossdist(c, p.pos, p.dir, r_outer, false, tstart);
+  const double t_max = d_outer / CLIGHT_PROP;
+  double time = 1.e99;
+  if ((t_max > 0) && (t_max < time)) {
+    time = t_max;
+    if (cellindex == (ncoord - 1)) {
+      *snext = -99;
+    } else {
+      *snext = p.where + 1;
+      p.last_cross = ARTIS_POS_X;
+    }
+  }
+  if ((t_min > 0) && (t_min < time)) {
+    time = t_min;
+    if (cellindex == 0) {
+      *snext = -99;
+    } else {
+      *snext = p.where - 1;
+      p.last_cross = ARTIS_NEG_X;
+    }
+  }
+  return CLIGHT_PROP * time;
+}
+// rpkt.cc:659-661 / gammapkt.cc:551-553: the largest credible distance to a cell boundary
+template <class P>
+ARTIS_DEV double max_sdist(const Ctx &c, const P &p, const double sdist) {
+  return c.st.opt_grid_type == 1 ? 2 * c.st.rmax * (p.prop_time + sdist / CLIGHT_PROP) / c.st.tmin
+                                 : c.st.rmax * p.prop_time / c.st.tmin;
+}
+
+// ---- boundary.cc:101-330 boundary_cross ----------------------------------------------------------------------------
 template <class P>
 ARTIS_DEV double boundary_cross(const Ctx &c, P &p, int *snext) {
+  if (c.st.opt_grid_type == 1) return boundary_cross_1d(c, p, snext);
   const double tstart = p.prop_time;
   const int cellindex = p.where;
   const double tmin = c.st.tmin;

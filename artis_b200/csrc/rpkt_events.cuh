@@ -6,7 +6,27 @@
 namespace artis {
 
 // ---- rpkt.cc:557-621 update_estimators + radfield.cc:831-860 + grey_emissivities.cc:79-106 ---------------------
-ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const double distance, const KappaCache &k, Tally &tl) {
+// The sweep of radfield.cc:764-829 for one r-packet step: continua first, first + stride, ... of those whose table
+// covers nu (a single thread passes first = 0, stride = 1; a warp passes lane, 32). gamma_contr[i] is zero from the first
+// continuum with knu < nu_edge on, and for a continuum whose table does not reach knu.
+ARTIS_DEV void bfest_sweep(const Ctx &c, const int tc, const int mgi, const double knu, const double nu, const double factor,
+                           const int first, const int stride, Tally &tl) {
+  const int i0k = bf_stop_index(c, knu);
+  int i0 = bf_stop_index(c, nu);
+  if (i0k < i0) i0 = i0k;
+  const int ilo = bf_start_index(c, nu, i0);
+  const double expfac = exp(-HOVERKB * knu / (double)c.cs.Te[mgi]);
+  double *row = c.es.bfrate_raw + (size_t)tc * c.st.nbfcontinua;
+  for (int i = ilo + first; i < i0; i += stride) {
+    double gcontr;
+    kappa_bf_term(c, tc, i, knu, expfac, &gcontr);
+    if (gcontr != 0.) {
+      est_add(&row[i], gcontr * factor);
+      tl.estim_atomics++;
+    }
+  }
+}
+ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const double distance, KappaCache &k, Tally &tl) {
   const int mgi = cell_mgi(c, p.where);
   if (mgi == c.st.npts_model) return;
   const double distance_e_cmf = distance * p.e_cmf;
@@ -26,19 +46,12 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
   if (c.st.opt_detailed_bf_estimators && kv && distance_e_cmf != 0) {
     const int tc = tabcell(c, mgi);
     const double distance_e_cmf_over_nu = distance_e_cmf / nu * doppler_packet(c, p);
-    const int i0k = bf_stop_index(c, k.nu);
-    int i0 = bf_stop_index(c, nu);
-    if (i0k < i0) i0 = i0k;  // gamma_contr[i] is zero from the first continuum with k.nu < nu_edge on
-    const int ilo = bf_start_index(c, nu, i0);
-    const double expfac = exp(-HOVERKB * k.nu / (double)c.cs.Te[mgi]);
-    double *row = c.es.bfrate_raw + (size_t)tc * c.st.nbfcontinua;
-    for (int i = ilo; i < i0; i++) {
-      double gcontr;
-      kappa_bf_term(c, tc, i, k.nu, expfac, &gcontr);
-      if (gcontr != 0.) {
-        est_add(&row[i], gcontr * distance_e_cmf_over_nu);
-        tl.estim_atomics++;
-      }
+    if (k.defer_bfest) {  // the warp runs the sweep right after the step (same terms, same factor)
+      k.bfest_tc = tc;
+      k.bfest_nu = nu;
+      k.bfest_factor = distance_e_cmf_over_nu;
+    } else {
+      bfest_sweep(c, tc, mgi, k.nu, nu, distance_e_cmf_over_nu, 0, 1, tl);
     }
   }
   // radfield.cc:843-874: frequency-binned J and nuJ of the multi-bin radiation field model
@@ -421,7 +434,7 @@ ARTIS_DEV bool rpkt_step_begin(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl
     change_cell(c, p, snext, tl);
     return false;
   }
-  const double maxsdist = c.st.rmax * p.prop_time / c.st.tmin;
+  const double maxsdist = max_sdist(c, p, sdist);
   if (sdist > maxsdist) {
     fatal(c, 104);
     p.type = ARTIS_TYPE_ESCAPE;  // park the packet; the run is reported as failed

@@ -30,9 +30,27 @@ __global__ void k_bf(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_bf(d_ctx, i);
 }
+// one warp per (cell, continuum): the lanes split the knot intervals of the photoionisation integral
 __global__ void k_corrphoto(long long n) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    artis::body_corrphoto(d_ctx, i);
+  using namespace artis;
+  const Ctx &c = d_ctx;
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long idx = warp; idx < n; idx += nwarps) {
+    const int tc = (int)(idx / c.st.nbfcontinua);
+    const int i = (int)(idx % c.st.nbfcontinua);
+    const int mgi = c.mgi_of_tabcell[tc];
+    if (!cell_uses_tables(c, mgi)) continue;
+    bool needs_sum;
+    double v = build_corrphoto_part(c, mgi, i, lane, 32, &needs_sum);  // warp-uniform branch inside
+    if (needs_sum) {
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+      v *= corrphoto_scale(c, i);
+    }
+    if (lane == 0) c.tb.corrphoto[(size_t)tc * c.st.nbfcontinua + i] = v;
+  }
 }
 __global__ void k_ma(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
@@ -145,6 +163,30 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
   }
   (void)nbf;
   if (need) kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ff, tl);
+}
+
+// Warp-cooperative bf-rate estimator sweep (DETAILED_BF_ESTIMATORS_ON, radfield.cc:764-829): an r-packet step in a
+// non-grey cell adds gamma_contr[i] * distance_e_cmf / nu to the estimator of EVERY continuum whose table covers nu --
+// about a thousand dependent table reads and FP64 atomics on one lane, in a role whose warps are sparsely filled in the
+// optically thin nebular models (2-6 busy lanes). update_estimators leaves the request in the lane's KappaCache and the
+// whole warp serves the requests one after another, lane l taking continua l, l + 32, ...: the same terms and products,
+// so the estimator sums differ from the serial sweep by the (already unordered) order of the atomics only.
+__device__ __forceinline__ void coop_bfest_flush(const artis::Ctx &c, artis::KappaCache &k, artis::Tally &tl) {
+  using namespace artis;
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  unsigned owners = __ballot_sync(full, k.bfest_factor != 0.);
+  while (owners != 0u) {
+    const int owner = __ffs(owners) - 1;
+    owners &= owners - 1u;
+    const double knu = __shfl_sync(full, k.nu, owner);
+    const double nu = __shfl_sync(full, k.bfest_nu, owner);
+    const double factor = __shfl_sync(full, k.bfest_factor, owner);
+    const int tc = __shfl_sync(full, k.bfest_tc, owner);
+    const int mgi = __shfl_sync(full, k.mgi, owner);
+    bfest_sweep(c, tc, mgi, knu, nu, factor, lane, 32, tl);
+  }
+  k.bfest_factor = 0.;
 }
 
 using artis::KIND_KAPPA;
@@ -275,6 +317,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
   Tally tl = {};
   KappaCache k;
   k.valid = false;
+  k.defer_bfest = HAS_THIN && c.st.opt_detailed_bf_estimators != 0;
   bool have = false, resumed = false;
   int idx = 0, role = 0;
   long long events = 0;
@@ -409,6 +452,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
         coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl);
       }
       if (stepped && proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
+      if (k.defer_bfest) coop_bfest_flush(c, k, tl);  // warp-uniform: the flag is an option of the build mode
       resumed = false;
       if (stepped && have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
     } else if (HAS_KAPPA && role == KIND_KAPPA) {
@@ -655,7 +699,7 @@ int grid_for(long long n, int block, int blocks_per_sm) {
 }
 void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
-void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
+void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {

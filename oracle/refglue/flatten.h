@@ -25,6 +25,7 @@
 
 namespace grid {
 extern __managed__ struct gridcell *cell;  // grid.cc:47 (non-static, not declared in grid.h)
+extern __managed__ double *vout_model;     // grid.cc:37 (non-static, not declared in grid.h)
 }
 namespace nonthermal {
 extern __managed__ double nt_energy_deposited;  // nonthermal.cc:115 (non-static, not declared in nonthermal.h)
@@ -129,6 +130,10 @@ inline void flatten_static(ArtisStaticTables *T, Storage *st) {
     }
     t.cell_mgi = cm;
     t.cell_posmin_x = px;
+    const int nv = (GRID_TYPE == GRID_SPHERICAL1D) ? grid::get_npts_model() : 0;
+    double *vo = st->D(nv);
+    for (int m = 0; m < nv; m++) vo[m] = grid::vout_model[m];
+    t.vout_model = vo;
     int *ne = st->I(t.npts_model + 1);
     for (int m = 0; m < t.npts_model; m++)
       ne[m] = (grid::get_numassociatedcells(m) > 0) ? grid::get_modelcell_nonemptymgi(m) : -1;

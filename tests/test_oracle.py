@@ -106,6 +106,14 @@ def test_edge_cases(oracle_lib):
     T.finalize()
 
 
+def test_fields_def_is_fully_mirrored():
+    """every S(...) / A(...) entry of include/artis_gpu_fields.def reaches the ctypes mirror (an entry the line parser of
+    artis_b200/abi.py skipped would shift every later struct member)"""
+    text = open(os.path.join(REPO, "include", "artis_gpu_fields.def")).read()
+    n_src = len(re.findall(r"^\s*[SA]\(", text, re.M))
+    assert n_src == len(abi.STATIC_FIELDS) + len(abi.CELL_FIELDS) + len(abi.ESTIM_FIELDS)
+
+
 def test_abi_version_is_checked(oracle_lib):
     fx = goldenlib.load_fixture("classic_nogrey_ts12.npz")
     T = Transport(oracle_lib)
