@@ -121,9 +121,9 @@ def build_struct(cls, fields, data, writable=False):
     return st, keep
 
 
-def empty_estimators(npts_model, nelements, max_nions, nlines, nradfieldbins=0, nbfrate=0):
+def empty_estimators(npts_model, nelements, max_nions, nlines, nradfieldbins=0, nbfrate=0, nvstokes=0, nvgrid=0):
     d = {"npts_model": npts_model, "nelements": nelements, "max_nions": max_nions, "nlines": nlines,
-         "nradfieldbins": nradfieldbins, "nbfrate": nbfrate}
+         "nradfieldbins": nradfieldbins, "nbfrate": nbfrate, "nvstokes": nvstokes, "nvgrid": nvgrid}
     for kind, ctype, fname, expr in ESTIM_FIELDS:
         if kind == "A":
             d[fname] = np.zeros(max(count_of(expr, d), 1), dtype=_CT[ctype][1])

@@ -106,6 +106,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.last_event = 6;
     p.emissiontype = -9999999;
     mark_emission(p);
+    if (c.st.opt_vpkt_on) vpkt_call_estimators(c, p, p.prop_time, 2);  // kpkt.cc:631-634 (t_current == prop_time)
   } else if (type == COOLINGTYPE_FB) {
     const int level = c.st.cool_level[i];
     const int upper = c.st.cool_upperlevel[i];
@@ -120,6 +121,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, upper);
     p.trueemissiontype = p.emissiontype;
     mark_emission(p);
+    if (c.st.opt_vpkt_on) vpkt_call_estimators(c, p, p.prop_time, 2);  // kpkt.cc:691-694
   } else if (type == COOLINGTYPE_COLLEXC) {
     // kpkt.cc:695-759: walk the level's upward transitions until the running contribution reaches rndcool; the
     // running values are CellTables.collexc_cum (same arithmetic, same order), so this is a search for the first

@@ -303,7 +303,11 @@ ARTIS_DEV void escat_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
 }
 
 // ---- rpkt.cc:330-447 rpkt_event_continuum --------------------------------------------------------------------------
-ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
+}  // namespace artis
+#include "vpkt.cuh"
+namespace artis {
+
+ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
   const double nu = p.nu_cmf;
   const double dopplerfactor = doppler_packet(c, p);
   const double kappa_cont = k.total * dopplerfactor;
@@ -317,6 +321,10 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
     p.nscatterings += 1;
     p.last_event = 12;
     stat_inc(tl, COUNTER_ESCOUNTER);
+    if (c.st.opt_vpkt_on) {  // rpkt.cc:359-363: virtual packets see the packet as it arrives at the scattering
+      p.last_cross = ARTIS_CROSS_NONE;
+      if (vpkt_call_estimators(c, p, p.prop_time, 1)) k.valid = false;
+    }
     escat_rpkt(c, p, rng);
     p.em_pos[0] = p.pos[0];
     p.em_pos[1] = p.pos[1];

@@ -111,7 +111,13 @@ class Transport:
         nonempty = int(s["nonempty_npts_model"])
         nbins = nonempty * int(s["opt_radfieldbincount"]) if s.get("opt_multibin_radfield") else 0
         nbfrate = nonempty * int(s["nbfcontinua"]) if s.get("opt_detailed_bf_estimators") else 0
-        d = abi.empty_estimators(s["npts_model"], s["nelements"], s["max_nions"], s["nlines"], nbins, nbfrate)
+        nvstokes = nvgrid = 0
+        if s.get("opt_vpkt_on"):
+            nvstokes = 3 * int(s["vpkt_vmtbins"]) * int(s["vpkt_nspectra"]) * int(s["vpkt_nobs"]) * int(s["vpkt_vmnubins"])
+            if int(s["vpkt_vgrid_flag"]) == 1:
+                nvgrid = 3 * int(s["vpkt_ny_vgrid"]) * int(s["vpkt_nz_vgrid"]) * int(s["vpkt_nrange_grid"]) * int(s["vpkt_nobs"])
+        d = abi.empty_estimators(s["npts_model"], s["nelements"], s["max_nions"], s["nlines"], nbins, nbfrate, nvstokes,
+                                 nvgrid)
         est, keep = abi.build_struct(abi.ArtisEstimators, abi.ESTIM_FIELDS, d, writable=True)
         self._check(self.lib.artis_gpu_download_estimators(C.byref(est)), "artis_gpu_download_estimators")
         return d

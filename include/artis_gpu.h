@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define ARTIS_GPU_ABI_VERSION 4
+#define ARTIS_GPU_ABI_VERSION 5
 
 enum artis_gpu_error {
   ARTIS_OK = 0,
@@ -116,7 +116,10 @@ enum {
   ARTIS_TS_GAMMA_DEP = 0, ARTIS_TS_POSITRON_DEP = 1, ARTIS_TS_ELECTRON_DEP = 2, ARTIS_TS_ELECTRON_EMISSION = 3,
   ARTIS_TS_ALPHA_DEP = 4, ARTIS_TS_ALPHA_EMISSION = 5, ARTIS_TS_GAMMA_EMISSION = 6, ARTIS_TS_CMF_LUM = 7,
   ARTIS_TS_NT_ENERGY_DEPOSITED = 8, /* nonthermal::nt_energy_deposited */
-  ARTIS_TS_COUNT = 9
+  /* virtual-packet counts of the timestep (vpkt.cc:69-74), whole numbers kept in the FP64 block so that they ride the
+   * same all-reduce: nvpkt, nvpkt_esc1 (electron scattering), nvpkt_esc2 (k-packet), nvpkt_esc3 (macro-atom) */
+  ARTIS_TS_NVPKT = 9, ARTIS_TS_NVPKT_ESC1 = 10, ARTIS_TS_NVPKT_ESC2 = 11, ARTIS_TS_NVPKT_ESC3 = 12,
+  ARTIS_TS_COUNT = 13
 };
 /* indices into ArtisEstimators.counters: [0,34) = stats::eventcounters (stats.h:48-84); then device counters */
 enum {

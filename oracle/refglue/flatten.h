@@ -22,6 +22,7 @@
 #include "refglue.h"
 #include "sn3d.h"
 #include "stats.h"
+#include "vpkt.h"
 
 namespace grid {
 extern __managed__ struct gridcell *cell;  // grid.cc:47 (non-static, not declared in grid.h)
@@ -399,6 +400,55 @@ inline void flatten_static(ArtisStaticTables *T, Storage *st) {
     t.gam_prob = pr;
     t.nuc_decayenergygamma = eg;
   }
+  // ---- virtual packets (vpkt.cc:15-74, vpkt.h:27-47)
+  t.nprocs = globals::nprocs;
+#ifdef VPKT_ON
+  {
+    VpktParams vp;
+    vpkt_params(&vp);
+    t.vpkt_nobs = vp.nobs;
+    t.vpkt_nspectra = vp.nspectra;
+    t.vpkt_nrange = vp.nrange;
+    t.vpkt_nrange_grid = vp.vgrid_flag == 1 ? vp.nrange_grid : 0;
+    t.vpkt_vgrid_flag = vp.vgrid_flag;
+    t.vpkt_vmtbins = VMTBINS;
+    t.vpkt_vmnubins = VMNUBINS;
+    t.vpkt_ny_vgrid = NY_VGRID;
+    t.vpkt_nz_vgrid = NZ_VGRID;
+    t.vpkt_tmin_input = vp.tmin_input;
+    t.vpkt_tmax_input = vp.tmax_input;
+    t.vpkt_tau_max = vp.tau_max;
+    t.vpkt_tmin_grid = vp.tmin_grid;
+    t.vpkt_tmax_grid = vp.tmax_grid;
+    t.vpkt_tmin_vspec = tmin_vspec;
+    t.vpkt_tmax_vspec = tmax_vspec;
+    t.vpkt_numin_vspec = numin_vspec;
+    t.vpkt_numax_vspec = numax_vspec;
+    t.vpkt_dlogt = vp.dlogt;
+    t.vpkt_dlognu = vp.dlognu;
+    auto copyd = [&](const double *src, int n) {
+      double *d = st->D(n);
+      for (int i = 0; i < n; i++) d[i] = src[i];
+      return d;
+    };
+    t.vpkt_nz_obs = copyd(vp.nz_obs, vp.nobs);
+    t.vpkt_phiobs = copyd(vp.phiobs, vp.nobs);
+    t.vpkt_exclude = copyd(vp.exclude, vp.nspectra);
+    t.vpkt_numin_input = copyd(vp.numin_input, vp.nrange);
+    t.vpkt_numax_input = copyd(vp.numax_input, vp.nrange);
+    t.vpkt_nu_grid_min = copyd(vp.nu_grid_min, t.vpkt_nrange_grid);
+    t.vpkt_nu_grid_max = copyd(vp.nu_grid_max, t.vpkt_nrange_grid);
+    float *dt = st->F(VMTBINS), *df = st->F(VMNUBINS);
+    for (int n = 0; n < VMTBINS; n++) dt[n] = vpkt_delta_t(n);
+    for (int m = 0; m < VMNUBINS; m++) df[m] = vp.delta_freq[m];
+    t.vpkt_delta_t = dt;
+    t.vpkt_delta_freq = df;
+  }
+#else
+  t.vpkt_nz_obs = t.vpkt_phiobs = t.vpkt_exclude = t.vpkt_numin_input = t.vpkt_numax_input = t.vpkt_nu_grid_min =
+      t.vpkt_nu_grid_max = st->D(0);
+  t.vpkt_delta_t = t.vpkt_delta_freq = st->F(0);
+#endif
   // ---- multi-bin radiation field model (radfield.cc:43, artisoptions nu_lower_first_initial)
   t.radfield_nu_lower_first = nu_lower_first_initial;
   {
@@ -597,6 +647,39 @@ inline void flatten_estimators(ArtisEstimators *E, Storage *st, const int nts) {
     e.radfieldbin_contribcount = bc;
     e.bfrate_raw = br;
   }
+#ifdef VPKT_ON
+  {
+    VpktParams vp;
+    vpkt_params(&vp);
+    const int ncomb = vp.nspectra * vp.nobs;
+    e.nvstokes = 3 * VMTBINS * ncomb * VMNUBINS;
+    e.nvgrid = vp.vgrid_flag == 1 ? 3 * NY_VGRID * NZ_VGRID * vp.nrange_grid * vp.nobs : 0;
+    double *vs = st->D(e.nvstokes), *vg = st->D(e.nvgrid);
+    size_t at = 0;
+    for (int s3 = 0; s3 < 3; s3++)
+      for (int nt = 0; nt < VMTBINS; nt++)
+        for (int ic = 0; ic < ncomb; ic++)
+          for (int m = 0; m < VMNUBINS; m++) vs[at++] = vpkt_vstokes(s3, nt, ic, m);
+    at = 0;
+    if (e.nvgrid > 0)
+      for (int s3 = 0; s3 < 3; s3++)
+        for (int n = 0; n < NY_VGRID; n++)
+          for (int m = 0; m < NZ_VGRID; m++)
+            for (int r = 0; r < vp.nrange_grid; r++)
+              for (int b = 0; b < vp.nobs; b++) vg[at++] = vpkt_vgrid(s3, n, m, r, b);
+    e.vstokes = vs;
+    e.vgrid = vg;
+    int cnt[4];
+    vpkt_counts(cnt);
+    ts[ARTIS_TS_NVPKT] = cnt[0];
+    ts[ARTIS_TS_NVPKT_ESC1] = cnt[1];
+    ts[ARTIS_TS_NVPKT_ESC2] = cnt[2];
+    ts[ARTIS_TS_NVPKT_ESC3] = cnt[3];
+  }
+#else
+  e.vstokes = st->D(0);
+  e.vgrid = st->D(0);
+#endif
   e.J = J;
   e.nuJ = nuJ;
   e.ffheatingestimator = ff;

@@ -281,6 +281,9 @@ void update_packets(const int my_rank, const int nts, struct packet *packets) {
     if (getenv("ARTIS_HOOK_PROBES")) write_probes(f, packets, npkts, nts, atoi(getenv("ARTIS_HOOK_PROBES")));
   }
 
+#ifdef VPKT_ON
+  if (snap) refglue::vpkt_zero_accumulators();  // the run-long virtual-packet sums: dump this step's contribution only
+#endif
   const long long cross0 = stats::get_counter(stats::COUNTER_CELLCROSSINGS);
   const long long es0 = stats::get_counter(stats::COUNTER_ESCOUNTER);
   const auto t0 = std::chrono::steady_clock::now();

@@ -17,6 +17,19 @@ float nt_eff_ionpot(int modelgridindex, int uniqueionindex);
 float nt_prob_num_auger(int modelgridindex, int index, bool energyweighted);
 double nt_ratecoeff_wfapprox(int modelgridindex, int element, int ion);
 double nt_deposition_rate_density_raw(int modelgridindex);
+// virtual packets (vpkt.cc:15-74): parameters of vpkt.txt, the compile-time grids and the accumulated spectra / maps
+struct VpktParams {
+  int nobs, nspectra, nrange, nrange_grid, vgrid_flag;
+  double tmin_input, tmax_input, tau_max, tmin_grid, tmax_grid, dlogt, dlognu;
+  const double *nz_obs, *phiobs, *exclude, *numin_input, *numax_input, *nu_grid_min, *nu_grid_max;
+  const float *delta_freq;
+};
+void vpkt_params(VpktParams *out);
+float vpkt_delta_t(int nt);
+double vpkt_vstokes(int stokes, int nt, int ind_comb, int nnu);
+double vpkt_vgrid(int stokes, int nt, int mt, int bin_range, int bin);
+void vpkt_zero_accumulators(void);  // the hook zeroes them before a snapshot step so that the dump is that step's sum
+void vpkt_counts(int out[4]);
 void coolinglist_entry(int i, int *type, int *level, int *upperlevel);  // kpkt.cc:27-35
 int gamma_nlines(int nucindex);                                         // gammapkt.cc:24-31
 void gamma_line(int nucindex, int k, double *energy, double *probability);

@@ -45,6 +45,21 @@ def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax
     open(path, "w").write("\n".join(out) + "\n")
 
 
+VPKT_TXT = """2
+0.5 -0.3
+0
+90
+1 6 0 26 -1 -2 -3 -4
+0 0 0
+0
+0 0
+10
+1
+10 30
+2 3500 6000 6000 10000
+"""
+
+
 def setup_classic1d(rundir, args):
     src = os.path.join(REF, "tests", "classicmode_inputfiles")
     os.makedirs(rundir, exist_ok=True)
@@ -54,6 +69,10 @@ def setup_classic1d(rundir, args):
         shutil.copy(os.path.join(REF, "data", f), rundir)
     write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep,
                     resume=args.resume)
+    if args.vpkt:
+        # vpkt.txt (vpkt.cc:667-836): two observers; six spectra per observer (all opacities, iron lines removed, no
+        # lines, no bf, no ff, no es); compiled time and frequency windows; tau_max 10; velocity maps in two bands
+        open(os.path.join(rundir, "vpkt.txt"), "w").write(VPKT_TXT)
     n = gen_atomic_data.generate(rundir, tuple(int(z) for z in args.elements.split(",")), args.nions, args.nlevels,
                                  args.dense_levels, args.sparsity, args.seed)
     print(f"run dir {rundir}: {n} lines")
@@ -108,6 +127,7 @@ def main():
     ap.add_argument("--sparsity", type=float, default=0.15)
     ap.add_argument("--seed", type=int, default=20240607)
     ap.add_argument("--ngrey", type=int, default=None, help="kilonova1d: override num_grey_timesteps of input.txt")
+    ap.add_argument("--vpkt", action="store_true", help="classic1d: also write a vpkt.txt for VPKT_ON builds")
     ap.add_argument("--resume", action="store_true",
                     help="write input.txt to continue from the gridsave/packets files of timestep itstep-1")
     args = ap.parse_args()

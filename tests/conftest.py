@@ -33,6 +33,6 @@ def gpu_lib():
 
 
 @pytest.fixture(scope="session", params=["classic_nogrey_ts12.npz", "classic_grey_ts8.npz", "kilonova_lte_ts1.npz",
-                                        "nebular_nlte_ts8.npz", "classic_1d_ts12.npz"])
+                                        "nebular_nlte_ts8.npz", "classic_1d_ts12.npz", "classic_vpkt_ts30.npz"])
 def fixture_name(request):
     return request.param

@@ -64,6 +64,27 @@ def summary(static, cell, est, post, pre):
     for i, nm in enumerate(("gamma_dep", "positron_dep", "electron_dep", "electron_emission", "alpha_dep",
                             "alpha_emission", "gamma_emission", "cmf_lum", "nt_energy_deposited")):
         d["ts_" + nm] = ts[i]
+    # virtual packets (VPKT_ON; vpkt.cc:388-406,581-627): counts, Stokes I per (observer, spectrum), I / Q / U of the
+    # full spectrum in three frequency bands per observer, and the velocity maps' totals
+    nvs = int(est.get("nvstokes", 0) or 0)
+    if nvs > 0:
+        for i, nm in enumerate(("nvpkt", "nvpkt_esc1", "nvpkt_esc2", "nvpkt_esc3")):
+            d["ts_" + nm] = ts[9 + i]
+        nobs, nspec = int(static["vpkt_nobs"]), int(static["vpkt_nspectra"])
+        v = np.asarray(est["vstokes"][:nvs]).reshape(3, int(static["vpkt_vmtbins"]), nobs * nspec,
+                                                       int(static["vpkt_vmnubins"]))
+        for ic in range(nobs * nspec):
+            d[f"vI_o{ic // nspec}_s{ic % nspec}"] = v[0, :, ic, :].sum()
+        for ob in range(nobs):
+            for s3, nm in enumerate("IQU"):
+                for g, part in enumerate(np.array_split(v[s3, :, ob * nspec, :].sum(0), 3)):
+                    d[f"v{nm}_o{ob}_band{g}"] = part.sum()
+        nvg = int(est.get("nvgrid", 0) or 0)
+        if nvg > 0:
+            g4 = np.asarray(est["vgrid"][:nvg]).reshape(3, -1, int(static["vpkt_nrange_grid"]), nobs)
+            for s3, nm in enumerate("IQU"):
+                for r in range(int(static["vpkt_nrange_grid"])):
+                    d[f"vgrid{nm}_r{r}"] = g4[s3, :, r, :].sum()
     ctr = np.asarray(est["counters"])
     for i in range(31):  # stats::eventcounters except UPDATECELL / COOLINGRATECALC / NESC (scheduler-specific)
         d[f"ctr{i:02d}"] = float(ctr[i])
