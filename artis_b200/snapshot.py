@@ -49,6 +49,9 @@ def section(snap, prefix, fields):
     for kind, ctype, fname, _ in fields:
         key = f"{prefix}.{fname}"
         if key not in snap:
+            # written before an ABI extension: every extension is a switch that is off (0 / no entries) in older dumps
+            if kind == "S":
+                d[fname] = 0
             continue
         d[fname] = snap[key][0].item() if kind == "S" else snap[key]
     return d
