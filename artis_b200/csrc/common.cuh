@@ -124,6 +124,29 @@ struct Ctx {
   int *error_flag;           // set non-zero by a packet that hits a reference abort() branch
 };
 
+// Build-mode switches as the device code tests them. They are run-time flags of the static tables (one library serves
+// every artisoptions_*.h); the ARTIS_NO_* macros compile a family of them out for same-box A/B measurements of what the
+// extra code paths cost the classic-mode kernels (profiles/r1_notes.md).
+#ifdef ARTIS_NO_VPKT
+#define ARTIS_OPT_VPKT(c) false
+#else
+#define ARTIS_OPT_VPKT(c) ((c).st.opt_vpkt_on != 0)
+#endif
+#ifdef ARTIS_NO_GRID1D
+#define ARTIS_OPT_GRID1D(c) false
+#else
+#define ARTIS_OPT_GRID1D(c) ((c).st.opt_grid_type == 1)
+#endif
+#ifdef ARTIS_NO_NEBULAR
+#define ARTIS_OPT_DETAILED_BF(c) false
+#define ARTIS_OPT_MULTIBIN(c) false
+#define ARTIS_OPT_NT_SF(c) false
+#else
+#define ARTIS_OPT_DETAILED_BF(c) ((c).st.opt_detailed_bf_estimators != 0)
+#define ARTIS_OPT_MULTIBIN(c) ((c).st.opt_multibin_radfield != 0)
+#define ARTIS_OPT_NT_SF(c) ((c).st.opt_nt_on != 0 && (c).st.opt_nt_solve_spencerfano != 0)
+#endif
+
 // ---- Philox4x32-10 counter-based stream (Salmon et al. 2011), one stream per packet and timestep -------------
 // key = (seed_lo ^ packet.number, seed_hi); counter = (draw index lo, draw index hi, nts, rank). The draw index
 // restarts at 0 every timestep and is kept in a device array between the passes of one timestep, so nothing has to
@@ -376,6 +399,11 @@ struct Tally {
   int rpkt_steps, lines_scanned, lines_tau, bf_evaluated, estim_atomics, gamma_steps, ma_jumps, ma_trans_scanned,
       kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates, handoffs;
   int stats[34];  // stats::eventcounters increments of this thread (stats.h:48-84), flushed once per thread and pass
+  // VPKT_ON: a virtual-packet request left by the event that has just been processed (vpkt.cuh vpkt_flush_request runs it
+  // at the one place per scheduler where events return): realtype 1-3 (0 = none) and, for an electron scattering, the
+  // direction and Stokes Q, U the packet arrived with
+  int vpkt_req;
+  double vpkt_dir[3], vpkt_q, vpkt_u;
 };
 ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   long long *k = c.es.counters;

@@ -140,6 +140,7 @@ ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long lon
       have = true;
     }
     do_packet_kind<KIND>(c, p, t2, k, rng, tl);
+    if (ARTIS_OPT_VPKT(c)) vpkt_flush_request(c, p, k, tl);
     events++;
     const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
     if (!(active && kind_of(c, p) == kind && events < max_events)) {

@@ -106,7 +106,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.last_event = 6;
     p.emissiontype = -9999999;
     mark_emission(p);
-    if (c.st.opt_vpkt_on) vpkt_call_estimators(c, p, p.prop_time, 2);  // kpkt.cc:631-634 (t_current == prop_time)
+    if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 2;  // kpkt.cc:631-634 (t_current == prop_time)
   } else if (type == COOLINGTYPE_FB) {
     const int level = c.st.cool_level[i];
     const int upper = c.st.cool_upperlevel[i];
@@ -121,7 +121,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, upper);
     p.trueemissiontype = p.emissiontype;
     mark_emission(p);
-    if (c.st.opt_vpkt_on) vpkt_call_estimators(c, p, p.prop_time, 2);  // kpkt.cc:691-694
+    if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 2;  // kpkt.cc:691-694
   } else if (type == COOLINGTYPE_COLLEXC) {
     // kpkt.cc:695-759: walk the level's upward transitions until the running contribution reaches rndcool; the
     // running values are CellTables.collexc_cum (same arithmetic, same order), so this is a search for the first
@@ -175,7 +175,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
 ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   est_add(&c.es.ts_scalars[ARTIS_TS_NT_ENERGY_DEPOSITED], p.e_cmf);
   const int mgi = cell_mgi(c, p.where);
-  if (c.st.opt_nt_on && c.st.opt_nt_solve_spencerfano && c.cs.thick[mgi] != 1) {
+  if (ARTIS_OPT_NT_SF(c) && c.cs.thick[mgi] != 1) {
     const double zrand = rng_uniform(rng);
     // get_ntion_energyrate (nonthermal.cc:1847-1856): the same sum serves frac_ionization and select_nt_ionization2
     double ratetotal = 0.;

@@ -228,7 +228,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         p.next_trans = linelistindex + 1;
         p.emissiontype = linelistindex;
         mark_emission(p);
-        if (c.st.opt_vpkt_on) vpkt_call_estimators(c, p, p.prop_time, 3);  // macroatom.cc:292-295
+        if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 3;  // macroatom.cc:292-295
         end_packet = true;
         break;
       }
@@ -278,7 +278,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         p.next_trans = 0;
         p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, level);
         mark_emission(p);
-        if (c.st.opt_vpkt_on) vpkt_call_estimators(c, p, p.prop_time, 3);  // macroatom.cc:376-379
+        if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 3;  // macroatom.cc:376-379
         ui -= 1;
         gl = gl_lower;
         end_packet = true;

@@ -149,14 +149,14 @@ ARTIS_DEV double boundary_cross_1d(const Ctx &c, P &p, int *snext) {
 // rpkt.cc:659-661 / gammapkt.cc:551-553: the largest credible distance to a cell boundary
 template <class P>
 ARTIS_DEV double max_sdist(const Ctx &c, const P &p, const double sdist) {
-  return c.st.opt_grid_type == 1 ? 2 * c.st.rmax * (p.prop_time + sdist / CLIGHT_PROP) / c.st.tmin
+  return ARTIS_OPT_GRID1D(c) ? 2 * c.st.rmax * (p.prop_time + sdist / CLIGHT_PROP) / c.st.tmin
                                  : c.st.rmax * p.prop_time / c.st.tmin;
 }
 
 // ---- boundary.cc:101-330 boundary_cross ----------------------------------------------------------------------------
 template <class P>
 ARTIS_DEV double boundary_cross(const Ctx &c, P &p, int *snext) {
-  if (c.st.opt_grid_type == 1) return boundary_cross_1d(c, p, snext);
+  if (ARTIS_OPT_GRID1D(c)) return boundary_cross_1d(c, p, snext);
   const double tstart = p.prop_time;
   const int cellindex = p.where;
   const double tmin = c.st.tmin;

@@ -43,7 +43,7 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
   // covers nu gets gamma_contr[i] * distance_e_cmf / nu * doppler, where gamma_contr is the per-continuum scratch of the
   // last opacity evaluation (at k.nu). The reference keeps that scratch as an nbfcontinua-long array per host
   // thread; here the term is re-evaluated at k.nu from the per-cell table -- same function, same inputs, same bits.
-  if (c.st.opt_detailed_bf_estimators && kv && distance_e_cmf != 0) {
+  if (ARTIS_OPT_DETAILED_BF(c) && kv && distance_e_cmf != 0) {
     const int tc = tabcell(c, mgi);
     const double distance_e_cmf_over_nu = distance_e_cmf / nu * doppler_packet(c, p);
     if (k.defer_bfest) {  // the warp runs the sweep right after the step (same terms, same factor)
@@ -55,7 +55,7 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
     }
   }
   // radfield.cc:843-874: frequency-binned J and nuJ of the multi-bin radiation field model
-  if (c.st.opt_multibin_radfield) {
+  if (ARTIS_OPT_MULTIBIN(c)) {
     const int binindex = radfield_select_bin(c, nu);
     if (binindex >= 0) {
       const size_t mgibinindex = (size_t)tabcell(c, mgi) * c.st.opt_radfieldbincount + binindex;
@@ -307,7 +307,7 @@ ARTIS_DEV void escat_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
 #include "vpkt.cuh"
 namespace artis {
 
-ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
+ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
   const double nu = p.nu_cmf;
   const double dopplerfactor = doppler_packet(c, p);
   const double kappa_cont = k.total * dopplerfactor;
@@ -321,9 +321,14 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, KappaCache &k,
     p.nscatterings += 1;
     p.last_event = 12;
     stat_inc(tl, COUNTER_ESCOUNTER);
-    if (c.st.opt_vpkt_on) {  // rpkt.cc:359-363: virtual packets see the packet as it arrives at the scattering
+    if (ARTIS_OPT_VPKT(c)) {  // rpkt.cc:359-363: virtual packets see the packet as it arrives at the scattering
       p.last_cross = ARTIS_CROSS_NONE;
-      if (vpkt_call_estimators(c, p, p.prop_time, 1)) k.valid = false;
+      tl.vpkt_req = 1;
+      tl.vpkt_dir[0] = p.dir[0];
+      tl.vpkt_dir[1] = p.dir[1];
+      tl.vpkt_dir[2] = p.dir[2];
+      tl.vpkt_q = p.stokes[1];
+      tl.vpkt_u = p.stokes[2];
     }
     escat_rpkt(c, p, rng);
     p.em_pos[0] = p.pos[0];

@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
   Tally tl = {};
   KappaCache k;
   k.valid = false;
-  k.defer_bfest = HAS_THIN && c.st.opt_detailed_bf_estimators != 0;
+  k.defer_bfest = HAS_THIN && ARTIS_OPT_DETAILED_BF(c);
   bool have = false, resumed = false;
   int idx = 0, role = 0;
   long long events = 0;
@@ -482,6 +482,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
           break;
       }
     }
+    if (ARTIS_OPT_VPKT(c) && have) vpkt_flush_request(c, p, k, tl);  // the one call site of the virtual-packet ray trace
     if (have && !stepped) {  // thin lane that handed its opacity evaluation over
       __stcg(rngctr + idx, (unsigned long long)rng.ctr);
       packet_store_cg(pkts + idx, p);

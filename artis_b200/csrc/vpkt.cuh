@@ -7,9 +7,9 @@
 // lines removed; no lines; no bf / ff / es), and the Stokes vector weighted by exp(-tau) is binned into the observer's
 // time- and frequency-resolved spectra and, optionally, a velocity map.
 //
-// Included by rpkt_events.cuh between the frame transforms (vpkt.cc:898-1069, which it uses) and the event handlers
-// (which call vpkt_call_estimators). The routine takes its packet BY VALUE and is not inlined into the transport
-// kernels: the caller's packet stays in registers, and builds without VPKT_ON only pay for a never-taken call.
+// Included by rpkt_events.cuh after the frame transforms (vpkt.cc:898-1069, which it uses). The event handlers leave a
+// request in the thread's Tally; vpkt_flush_request runs it after the event. The ray trace takes its packet BY VALUE and
+// is not inlined into the transport kernels: the caller's packet stays in registers, and each kernel has one call site.
 #pragma once
 
 namespace artis {
@@ -311,6 +311,26 @@ ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const ArtisPacket pk, 
   if (escaped) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT_ESC1 + realtype - 1], (double)escaped);
   tally_flush(c, tl);
   return vflag;
+}
+
+// The events only leave a request (Tally.vpkt_req): the reference calls vpkt_call_estimators at the end of the emitting
+// routine (macroatom.cc:292,376, kpkt.cc:631,691 -- nothing the ray depends on changes afterwards) or just before the
+// electron scattering changes the direction and the Stokes vector (rpkt.cc:359 -- those five numbers travel with the
+// request). Each scheduler calls this once, right after an event returns, so that the transport kernels hold a single
+// call site of the out-of-line ray trace.
+ARTIS_DEV void vpkt_flush_request(const Ctx &c, const ArtisPacket &p, KappaCache &k, Tally &tl) {
+  const int realtype = tl.vpkt_req;
+  if (realtype == 0) return;
+  tl.vpkt_req = 0;
+  ArtisPacket q = p;
+  if (realtype == 1) {
+    q.dir[0] = tl.vpkt_dir[0];
+    q.dir[1] = tl.vpkt_dir[1];
+    q.dir[2] = tl.vpkt_dir[2];
+    q.stokes[1] = tl.vpkt_q;
+    q.stokes[2] = tl.vpkt_u;
+  }
+  if (vpkt_call_estimators(c, q, q.prop_time, realtype)) k.valid = false;
 }
 
 }  // namespace artis

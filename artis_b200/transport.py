@@ -15,6 +15,10 @@ from . import abi
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 DEFAULT_LIB = os.environ.get("ARTIS_GPU_LIB", os.path.join(HERE, "libartis_gpu.so"))  # override: kernel tuning experiments
+# VPKT_ON is a compile-time switch of the reference (artisoptions.h) and of this library: the virtual-packet ray trace
+# costs the other build modes 5-19 % when it is merely present in the transport kernels (profiles/r1_notes.md), so it is
+# compiled into a second library from the same sources. A VPKT_ON driver links this one instead.
+VPKT_LIB = os.path.join(HERE, "libartis_gpu_vpkt.so")
 
 
 class ArtisGpuError(RuntimeError):
@@ -27,15 +31,19 @@ class Transport:
         if not os.path.exists(path):
             raise ArtisGpuError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                                 "(there is no CPU fallback)")
-        self.lib = C.CDLL(path)
-        abi.declare(self.lib)
-        self.lib.artis_gpu_launch_count.restype = C.c_longlong
-        self.lib.artis_gpu_table_bytes.restype = C.c_size_t
+        self._load(path)
         self._keep = []
         self.static = None
         self.npkts = 0
 
     # ---- helpers
+    def _load(self, path):
+        self.libpath = path
+        self.lib = C.CDLL(path)
+        abi.declare(self.lib)
+        self.lib.artis_gpu_launch_count.restype = C.c_longlong
+        self.lib.artis_gpu_table_bytes.restype = C.c_size_t
+
     def _check(self, rc, what):
         if rc != 0:
             buf = C.create_string_buffer(1024)
@@ -46,6 +54,14 @@ class Transport:
     def init(self, static, device=0, rank=0, nranks=1, seed=1281360349):
         static = dict(static)
         static["abi_version"] = abi.ABI_VERSION
+        base = os.path.join(HERE, "libartis_gpu.so")
+        want = VPKT_LIB if static.get("opt_vpkt_on") else base
+        if os.path.realpath(self.libpath) in (os.path.realpath(base), os.path.realpath(VPKT_LIB)) and \
+                os.path.realpath(self.libpath) != os.path.realpath(want):
+            if not os.path.exists(want):
+                raise ArtisGpuError(f"{want} not found: build it with __graft_entry__.build() (there is no CPU fallback)")
+            self.lib.artis_gpu_finalize()
+            self._load(want)  # the library that matches the build mode, as a driver would link it
         st, keep = abi.build_struct(abi.ArtisStaticTables, abi.STATIC_FIELDS, static)
         self._keep.append(keep)
         self.static = static
