@@ -14,6 +14,7 @@
 #include <string>
 
 #include "kernels.cuh"
+#include "spectra.cuh"
 
 namespace {
 
@@ -59,6 +60,27 @@ __global__ void k_ma(long long n) {
 __global__ void k_cool(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_cool(d_ctx, i);
+}
+// light curves + angle-averaged spectrum of the resident packets (spectra.cuh). The 4 x ntstep light-curve sums are a few
+// hundred addresses that every escaped packet of the ensemble adds to: they are accumulated per block in shared memory
+// and flushed once; the ntstep x nnubins spectrum bins are spread thinly and take global FP64 reductions directly.
+__global__ void __launch_bounds__(256) k_bin_escaped(const artis::BinSpec b, const ArtisPacket *pkts, long long n, int lc_in_smem) {
+  extern __shared__ double lc_smem[];
+  const int nlc = 4 * b.ntstep;
+  double *lc_local = b.lc;
+  if (lc_in_smem) {
+    for (int i = threadIdx.x; i < nlc; i += blockDim.x) lc_smem[i] = 0.;
+    __syncthreads();
+    lc_local = lc_smem;
+  }
+  const double tmin = d_ctx.st.tmin;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_bin_escaped(b, tmin, pkts, i, lc_local);
+  if (lc_in_smem) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < nlc; i += blockDim.x)
+      if (lc_smem[i] != 0.) atomicAdd(&b.lc[i], lc_smem[i]);
+  }
 }
 // one kernel per event kind, each compiled with only that kind's physics
 template <int KIND>
@@ -703,6 +725,12 @@ void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_s
 void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
+void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long n) {
+  if (n <= 0) return;
+  const size_t smem = (size_t)4 * b.ntstep * sizeof(double);
+  const int in_smem = smem <= 32768;
+  k_bin_escaped<<<grid_for(n, 256, 8), 256, in_smem ? smem : 0, g_stream>>>(b, p, n, in_smem);
+}
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
   k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, r, n, buckets);
   k_bucket_scan<<<1, 1, 0, g_stream>>>(buckets, kind_sizes);
@@ -875,7 +903,7 @@ int be_comm_allreduce(double *d, size_t nd, long long *l, size_t nl, int *i, siz
   if (g_nccl.comm == nullptr || g_nccl.nranks <= 1) return ARTIS_OK;  // single shard: nothing to reduce
   const int ncclSum = 0, ncclInt32 = 2, ncclInt64 = 4, ncclFloat64 = 8;
   int rc = g_nccl.AllReduce(d, d, nd, ncclFloat64, ncclSum, g_nccl.comm, g_stream);
-  if (rc == 0) rc = g_nccl.AllReduce(l, l, nl, ncclInt64, ncclSum, g_nccl.comm, g_stream);
+  if (rc == 0 && nl > 0) rc = g_nccl.AllReduce(l, l, nl, ncclInt64, ncclSum, g_nccl.comm, g_stream);
   if (rc == 0 && ni > 0) rc = g_nccl.AllReduce(i, i, ni, ncclInt32, ncclSum, g_nccl.comm, g_stream);
   if (rc != 0) {
     *err = std::string("ncclAllReduce: ") + g_nccl.GetErrorString(rc);

@@ -105,8 +105,8 @@ class Transport:
         return out
 
     def last_timings(self):
-        ms = (C.c_double * 4)()
-        n = self.lib.artis_gpu_last_timings(ms, 4)
+        ms = (C.c_double * 5)()
+        n = self.lib.artis_gpu_last_timings(ms, 5)
         return [ms[i] for i in range(n)]
 
     def set_tuning(self, max_events_per_pass=0, block_threads=0):
@@ -143,6 +143,16 @@ class Transport:
         n = C.c_size_t()
         self._check(self.lib.artis_gpu_estimator_block(C.byref(ptr), C.byref(n)), "artis_gpu_estimator_block")
         return ptr.value, n.value
+
+    # ---- light curves + spectrum of the resident packets (write_partial_lightcurve_spectra, spectrum.cc:641)
+    def bin_escaped(self, tmax, nprocs=1, nnubins=1000, allreduce=False, stokes=False):
+        """-> lc[4, ntstep] (r lum, r lumcmf, gamma lum, gamma lumcmf), flux[ntstep, nnubins], stokes[3, ntstep, nnubins] | None"""
+        ntstep = int(self.static["ntstep"])
+        lc, flux = np.zeros((4, ntstep)), np.zeros((ntstep, nnubins))
+        sto = np.zeros((3, ntstep, nnubins)) if stokes else None
+        self._check(self.lib.artis_gpu_bin_escaped(float(tmax), int(nprocs), int(nnubins), int(bool(allreduce)), _pd(lc), _pd(flux),
+                                                   _pd(sto) if stokes else None), "artis_gpu_bin_escaped")
+        return lc, flux, sto
 
     # ---- deterministic probes (K10)
     def probe_boundary_cross(self, pkts):

@@ -307,6 +307,11 @@ def main():
         tot_ms += ms
         ctr_sum += c
     launches = T.launch_count() - launches0
+    # light curves + spectrum of the packets left resident by the last step (artis_gpu_bin_escaped; outside the timed region)
+    tmax_run = float(st["ts_start"][-1] + st["ts_width"][-1])
+    for _ in range(3):
+        lc_out, _, _ = T.bin_escaped(tmax_run, world, 1000, allreduce=False)
+    bin_ms = T.last_timings()[4]
     inter_rank = float(ctr_sum[45])
     alg_bytes = float(algorithmic_bytes(ctr_sum))
     if world > 1:
@@ -363,7 +368,8 @@ def main():
                            "drain_ms_to_10pct_1pct_done": [round(float(c[61 + i]) * 1e-6, 1) for i in range(3)],
                            "warp_iters_by_kind": [float(x) / a.steps for x in ctr_sum[51:56]],
                            "mean_busy_lanes_by_kind": [round(float(ctr_sum[56 + i]) / max(float(ctr_sum[51 + i]), 1.0), 2) for i in range(5)],
-                           "events_per_s": float(ctr_sum[49]) * world / (tot_ms * 1e-3)},
+                           "events_per_s": float(ctr_sum[49]) * world / (tot_ms * 1e-3),
+                           "bin_escaped_ms": bin_ms, "bin_escaped_record_GBps": P * 304 / (bin_ms * 1e-3) / 1e9 if bin_ms > 0 else None},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": measured_traffic(P),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6537.6",

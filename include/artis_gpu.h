@@ -173,7 +173,8 @@ int artis_gpu_packets_upload(const ArtisPacket *host_packets, int npkts);
 int artis_gpu_transport_resident(int nts);
 int artis_gpu_packets_download(ArtisPacket *host_packets, int npkts);
 /* milliseconds spent in the kernels of the last transport_resident call (CUDA events on the library's stream):
- * [0] total, [1] bucketing, [2] transport kernels, [3] cell_precompute of the last upload_cellstate; returns number of values written */
+ * [0] total, [1] bucketing, [2] transport kernels, [3] cell_precompute of the last upload_cellstate, [4] the last
+ * artis_gpu_bin_escaped kernel; returns number of values written */
 int artis_gpu_last_timings(double *ms, int n);
 /* Introspection for the measurement harness: kernels launched by the library since init, and bytes held by the
  * per-cell tables that replace the reference's cellhistory cache. */
@@ -193,6 +194,20 @@ int artis_gpu_download_estimators(ArtisEstimators *est);
 /* Device address and length (in doubles) of the contiguous FP64 estimator block, for callers that run their own
  * collective on it (e.g. torch.distributed). */
 int artis_gpu_estimator_block(void **dev_ptr, size_t *ndoubles);
+
+/* ---- light curves and spectrum of the resident packets ------------------------------------ */
+/* Replaces the packet loop and the MPI reductions of write_partial_lightcurve_spectra (spectrum.cc:641-700; call site
+ * sn3d.cc:603) for a driver that keeps its packets on the device: every resident packet with type ESCAPE is binned by
+ * add_to_lc_res (light_curve.cc:34-54) and, for escape_type RPKT, add_to_spec_res (spectrum.cc:602-615, 339-372) with
+ * current_abin = -1 (all angles) and no emission/absorption resolution (WRITE_PARTIAL_EMISSIONABSORPTIONSPEC = false).
+ *   tmax, nprocs  globals::tmax, globals::nprocs        nnubins  globals::nnubins (MNUBINS = 1000, exspec.h:5)
+ *   allreduce     non-zero: sum over the shards of artis_gpu_comm_init before the download (spectrum.cc:688-699)
+ *   lc            out [4][ntstep]: r-packet lum, r-packet lumcmf, gamma lum, gamma lumcmf (the arrays write_light_curve takes)
+ *   spec_flux     out [ntstep][nnubins]: spectra->timesteps[nt].flux[nnu]
+ *   stokes        out [3][ntstep][nnubins] (stokes_i/q/u of add_to_spec) or NULL
+ * The frequency grid is init_spectra(nu_min_r, nu_max_r) (spectrum.cc:483-499), float delta_freq included. Sums are
+ * accumulated with FP64 atomics, so a bin agrees with the reference's serial sum to rounding (not bit for bit). */
+int artis_gpu_bin_escaped(double tmax, int nprocs, int nnubins, int allreduce, double *lc, double *spec_flux, double *stokes);
 
 /* ---- K10: deterministic probes (test entry points for SURVEY 8a A4-A8, A11, A12, A14) ------------------ */
 /* Each probe runs the corresponding device function for n independent packet states on the GPU. */

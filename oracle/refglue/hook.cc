@@ -7,6 +7,8 @@
 //   ARTIS_HOOK_DIR=<dir>           where to write (default ".")
 //   ARTIS_HOOK_STOP_AFTER_TS=N     exit(0) after timestep N's transport (bounds the run)
 //   ARTIS_HOOK_PROBES=N            with snapshots: also store N deterministic probes (inputs + reference outputs)
+//   ARTIS_HOOK_SPECTRA=1           with snapshots: also store the light curves and the spectrum that the reference's
+//                                  add_to_lc_res / add_to_spec_res make of the post-transport packets (spectra.*)
 //   ARTIS_HOOK_SKIP_POST=1         with snapshots: do not store the (large) post-transport packet array
 // Always appends one line per timestep to <dir>/hook_timing.txt:
 //   nts npkts seconds interactions cellcrossings escounter nesc threads
@@ -27,6 +29,9 @@
 #include "rpkt.h"
 #include "update_grid.h"
 #include "vectors.h"
+#include "exspec.h"
+#include "light_curve.h"
+#include "spectrum.h"
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -251,6 +256,39 @@ void write_probes(FILE *f, const struct packet *packets, const int npkts, const 
   globals::kappa_rpkt_cont[tid].recalculate_required = true;
 }
 
+// the packet loop of write_partial_lightcurve_spectra (spectrum.cc:672-682) with the reference's own callees, plus the
+// Stokes spectra that exspec passes to the same function
+void write_spectra(FILE *f, const struct packet *pkts, const int npkts) {
+  globals::nnubins = MNUBINS;  // spectrum.cc:649
+  const int ntstep = globals::ntstep, nnubins = globals::nnubins;
+  struct spec *sp[4];
+  for (auto &x : sp) {
+    x = alloc_spectra(false);
+    init_spectra(x, globals::nu_min_r, globals::nu_max_r, false);
+  }
+  std::vector<double> lc(4 * (size_t)ntstep, 0.);
+  for (int ii = 0; ii < npkts; ii++) {
+    if (pkts[ii].type != TYPE_ESCAPE) continue;
+    if (pkts[ii].escape_type == TYPE_RPKT) {
+      add_to_lc_res(&pkts[ii], -1, &lc[0], &lc[ntstep]);
+      add_to_spec_res(&pkts[ii], -1, sp[0], sp[1], sp[2], sp[3]);
+    } else if (pkts[ii].escape_type == TYPE_GAMMA) {
+      add_to_lc_res(&pkts[ii], -1, &lc[2 * (size_t)ntstep], &lc[3 * (size_t)ntstep]);
+    }
+  }
+  std::vector<double> flux(4 * (size_t)ntstep * nnubins);
+  for (int k = 0; k < 4; k++)
+    for (int nt = 0; nt < ntstep; nt++)
+      for (int nnu = 0; nnu < nnubins; nnu++) flux[((size_t)k * ntstep + nt) * nnubins + nnu] = sp[k]->timesteps[nt].flux[nnu];
+  const double params[3] = {globals::tmax, (double)globals::nprocs, (double)nnubins};
+  write_record(f, "spectra.params", "f8", params, 3, 8);
+  write_record(f, "spectra.lc", "f8", lc.data(), lc.size(), 8);
+  write_record(f, "spectra.flux", "f8", flux.data(), (size_t)ntstep * nnubins, 8);
+  write_record(f, "spectra.stokes", "f8", flux.data() + (size_t)ntstep * nnubins, 3 * (size_t)ntstep * nnubins, 8);
+  write_record(f, "spectra.delta_freq", "f4", sp[0]->delta_freq, nnubins, 4);
+  for (auto &x : sp) free_spectra(x);
+}
+
 }  // namespace
 
 void update_packets(const int my_rank, const int nts, struct packet *packets) {
@@ -314,6 +352,7 @@ void update_packets(const int my_rank, const int nts, struct packet *packets) {
     refglue::flatten_estimators(&E, &st, nts);
     write_estim(f, &E);
     if (!skip_post) write_record(f, "packets.post", "pkt", packets, npkts, sizeof(struct packet));
+    if (getenv("ARTIS_HOOK_SPECTRA")) write_spectra(f, packets, npkts);
     const double secs[1] = {seconds};
     write_record(f, "meta.ref_seconds", "f8", secs, 1, sizeof(double));
     fclose(f);

@@ -21,6 +21,7 @@
 #include <string>
 
 #include "../../artis_b200/csrc/kernels.cuh"
+#include "../../artis_b200/csrc/spectra.cuh"
 
 namespace {
 artis::Ctx g_ctx;
@@ -41,6 +42,9 @@ void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g
 void be_run_corrphoto(long long n) { for (long long i = 0; i < n; i++) artis::body_corrphoto(g_ctx, i); }
 void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
 void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
+void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long n) {
+  for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, g_ctx.st.tmin, p, i, b.lc);
+}
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
   for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, p, r, i, buckets);
   artis::body_bucket_scan(g_ctx, buckets, kind_sizes);

@@ -1,0 +1,130 @@
+"""Light curves and spectrum of the resident packets (artis_gpu_bin_escaped) against the reference's own
+add_to_lc_res / add_to_spec_res output.
+
+Golden vector: tests/golden/spectra_classic_vpkt_ts30.npz, written by oracle/tools/ref_spectra.py -- the post-transport
+packets of one reference timestep and the arrays the reference's functions made of them. The sums are FP64 atomics on
+the device, so a bin may differ from the reference's serial sum by rounding: TOL below. Which bins are non-zero is exact.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import goldenlib
+from artis_b200 import abi
+from artis_b200.transport import Transport
+
+TOL = 1e-13  # relative, per bin: at most a few hundred additions of positive terms per bin in these cases
+
+
+def load_spectra_fixture():
+    z = np.load(os.path.join(goldenlib.GOLDEN, "spectra_classic_vpkt_ts30.npz"))
+    fx = goldenlib.load_fixture("classic_vpkt_ts30.npz")  # static tables of the same run directory
+    static = dict(fx["static"])
+    static["opt_vpkt_on"] = 0  # binning needs no virtual packets: stay on the default library
+    post = np.frombuffer(z["packets_post"].tobytes(), dtype=abi.PACKET_DTYPE).copy()
+    ntstep = int(static["ntstep"])
+    tmax, nprocs, nnubins = float(z["params"][0]), int(z["params"][1]), int(z["params"][2])
+    return {"static": static, "post": post, "tmax": tmax, "nprocs": nprocs, "nnubins": nnubins,
+            "lc": z["lc"].reshape(4, ntstep), "flux": z["flux"].reshape(ntstep, nnubins),
+            "stokes": z["stokes"].reshape(3, ntstep, nnubins)}
+
+
+def assert_bins(got, want, what):
+    assert np.array_equal(got != 0, want != 0), f"{what}: different set of non-zero bins"
+    nz = want != 0
+    if nz.any():
+        rel = np.abs(got[nz] - want[nz]) / np.abs(want[nz])
+        assert rel.max() <= TOL, (what, rel.max())
+
+
+def check_against_golden(lib):
+    g = load_spectra_fixture()
+    T = Transport(lib)
+    T.init(g["static"])
+    T.packets_upload(g["post"])
+    lc, flux, stokes = T.bin_escaped(g["tmax"], g["nprocs"], g["nnubins"], stokes=True)
+    assert (g["flux"] != 0).sum() > 300 and (g["lc"][2] != 0).sum() > 0  # the fixture exercises r-packets and gammas
+    assert_bins(lc, g["lc"], "light curves")
+    assert_bins(flux, g["flux"], "spectrum")
+    assert_bins(stokes, g["stokes"], "stokes spectra")
+    # without the Stokes planes the other outputs are unchanged; a second call starts from zero again
+    lc2, flux2, none = T.bin_escaped(g["tmax"], g["nprocs"], g["nnubins"])
+    assert none is None
+    assert_bins(lc2, g["lc"], "light curves (2nd call)")
+    assert_bins(flux2, g["flux"], "spectrum (2nd call)")
+    # nprocs is a plain normalisation (spectrum.cc:360)
+    lc3, flux3, _ = T.bin_escaped(g["tmax"], 4, g["nnubins"])
+    assert np.allclose(lc3 * 4, g["lc"] * g["nprocs"], rtol=1e-12, atol=0)
+    assert np.allclose(flux3 * 4, g["flux"] * g["nprocs"], rtol=1e-12, atol=0)
+    # no escaped packet, and no packet at all
+    none_escaped = g["post"][g["post"]["type"] != abi.TYPE_ESCAPE][:64].copy()
+    T.packets_upload(none_escaped)
+    lc4, flux4, _ = T.bin_escaped(g["tmax"], 1, g["nnubins"])
+    assert not lc4.any() and not flux4.any()
+    T.packets_upload(none_escaped[:0])
+    lc5, flux5, _ = T.bin_escaped(g["tmax"], 1, g["nnubins"])
+    assert not lc5.any() and not flux5.any()
+    with pytest.raises(Exception):
+        T.bin_escaped(g["tmax"], 0, g["nnubins"])  # nprocs = 0 would divide by zero
+    T.finalize()
+    return g
+
+
+def synthetic_escaped(g, n, seed):
+    """n packets, three quarters of them escaped, with arrival times and frequencies spread over (and beyond) the time
+    and frequency grids so that every range check of add_to_spec / add_to_lc_res is hit."""
+    rng = np.random.default_rng(seed)
+    st = g["static"]
+    p = np.resize(g["post"], n).copy()
+    p["type"] = np.where(rng.random(n) < 0.75, abi.TYPE_ESCAPE, 11)
+    p["escape_type"] = np.where(rng.random(n) < 0.8, 11, 10)
+    tmin, tmax = float(st["tmin"]), g["tmax"]
+    p["escape_time"] = np.exp(rng.uniform(np.log(tmin * 0.8), np.log(tmax * 1.2), n)).astype(np.int32)
+    mu = rng.uniform(-1, 1, n)
+    phi = rng.uniform(0, 2 * np.pi, n)
+    d = np.stack([np.sqrt(1 - mu * mu) * np.cos(phi), np.sqrt(1 - mu * mu) * np.sin(phi), mu], axis=1)
+    p["dir"] = d
+    p["pos"] = rng.uniform(-1, 1, (n, 3)) * float(st["rmax"]) * (p["escape_time"] / tmin)[:, None]
+    p["nu_rf"] = np.exp(rng.uniform(np.log(float(st["nu_min_r"]) * 0.5), np.log(float(st["nu_max_r"]) * 2), n))
+    p["e_rf"] = rng.uniform(0.5, 1.5, n) * 1e40
+    p["e_cmf"] = p["e_rf"] * rng.uniform(0.9, 1.1, n)
+    p["stokes"] = rng.uniform(-1, 1, (n, 3))
+    return p
+
+
+def test_restatement_spectra_match_reference(oracle_lib):
+    check_against_golden(oracle_lib)
+
+
+@pytest.mark.gpu
+def test_cuda_spectra_match_reference(gpu_lib):
+    check_against_golden(gpu_lib)
+
+
+@pytest.mark.gpu
+def test_cuda_spectra_match_restatement_at_scale(gpu_lib, oracle_lib):
+    g = load_spectra_fixture()
+    pk = synthetic_escaped(g, 2_000_000, 7)
+    out = []
+    for lib in (gpu_lib, oracle_lib):
+        T = Transport(lib)
+        T.init(g["static"])
+        T.packets_upload(pk)
+        out.append(T.bin_escaped(g["tmax"], 3, g["nnubins"], stokes=True))
+        T.finalize()
+    (lc_g, fl_g, st_g), (lc_o, fl_o, st_o) = out
+    assert (fl_o != 0).mean() > 0.5  # most bins hit
+    assert np.array_equal(fl_g != 0, fl_o != 0)
+    # light-curve bins hold ~1e4 terms each, summed in a different order on the device
+    assert np.allclose(lc_g, lc_o, rtol=1e-11, atol=0)
+    assert np.allclose(fl_g, fl_o, rtol=1e-12, atol=0)
+    # Stokes terms have both signs: compare against the size of the terms, not of the (cancelling) sum
+    scale = np.abs(fl_o)[None]
+    assert (np.abs(st_g - st_o) <= 1e-12 * scale).all()
+    # every in-range escaped packet lands in exactly one light-curve bin: a checksum of the whole ensemble
+    esc = (pk["type"] == abi.TYPE_ESCAPE) & (pk["escape_type"] == 11)
+    t_arr = pk["escape_time"] - (pk["pos"] * pk["dir"]).sum(1) / 2.99792458e10
+    inr = esc & (t_arr > float(g["static"]["tmin"])) & (t_arr < g["tmax"])
+    width = np.asarray(g["static"]["ts_width"])
+    assert np.isclose((lc_g[0] * width).sum() * 3, pk["e_rf"][inr].sum(), rtol=1e-10)
