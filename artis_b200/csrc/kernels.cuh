@@ -73,6 +73,13 @@ ARTIS_DEV int kind_of(const Ctx &c, const ArtisPacket &p) {
 constexpr int KIND_KAPPA = NKIND;
 constexpr int KIND_THIN_RESUME = NKIND + 1;
 constexpr int NRING = NKIND + 2;
+// Ring heads, tails and the active-packet count take every warp's atomics for the whole step: one 128-byte line each, so
+// that they sit in different L2 slices instead of queueing behind one another (words of 8 bytes).
+#ifndef ARTIS_RING_STRIDE
+#define ARTIS_RING_STRIDE 16
+#endif
+constexpr int RING_META_STRIDE = ARTIS_RING_STRIDE;
+constexpr int RING_META_WORDS = (2 * NRING + 2) * RING_META_STRIDE;
 ARTIS_DEV bool packet_active(const Ctx &c, const ArtisPacket &p) { return p.type != ARTIS_TYPE_ESCAPE && p.prop_time < c.t2; }
 
 struct QueueView {

@@ -85,4 +85,12 @@ ARTIS_DEV void body_bin_escaped(const BinSpec &b, const double tmin, const Artis
   }
 }
 
+
+// ---- escaped-packet compaction: the escaped packets, in array order, packed for one small D2H -----------
+constexpr int ESC_CHUNK = 256;  // packets per block of the count / scatter kernels
+// `reported` marks packets that an earlier only_new call has already delivered
+ARTIS_DEV bool escaped_selected(const ArtisPacket *pkts, const unsigned char *reported, const int only_new, const long long i) {
+  return pkts[i].type == ARTIS_TYPE_ESCAPE && !(only_new && reported[i]);
+}
+
 }  // namespace artis

@@ -82,6 +82,77 @@ __global__ void __launch_bounds__(256) k_bin_escaped(const artis::BinSpec b, con
       if (lc_smem[i] != 0.) atomicAdd(&b.lc[i], lc_smem[i]);
   }
 }
+// escaped-packet compaction in array order: per-chunk counts, one scan, cooperative 304-byte copies
+__global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_count(const ArtisPacket *pkts, long long n, const unsigned char *reported,
+                                                                   int only_new, int *counts) {
+  const long long i = blockIdx.x * (long long)artis::ESC_CHUNK + threadIdx.x;
+  const int sel = i < n && artis::escaped_selected(pkts, reported, only_new, i);
+  const int c = __syncthreads_count(sel);
+  if (threadIdx.x == 0) counts[blockIdx.x] = c;
+}
+// exclusive scan of nchunks counts in place; counts[nchunks] = total. One block: the array is n/256 ints.
+__global__ void __launch_bounds__(1024) k_escaped_scan(int *counts, int nchunks) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int base = 0; base < nchunks; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < nchunks ? counts[i] : 0;
+    int x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int t = warp_tot[lane];
+      for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, t, d);
+        if (lane >= d) t += y;
+      }
+      warp_tot[lane] = t;
+    }
+    __syncthreads();
+    const int before = carry + (w > 0 ? warp_tot[w - 1] : 0) + x - v;
+    if (i < nchunks) counts[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) counts[nchunks] = carry;
+}
+__global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_scatter(const ArtisPacket *pkts, long long n, unsigned char *reported,
+                                                                     int only_new, const int *offsets, ArtisPacket *out) {
+  __shared__ int warp_base[artis::ESC_CHUNK / 32];
+  const long long i = blockIdx.x * (long long)artis::ESC_CHUNK + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const bool sel = i < n && artis::escaped_selected(pkts, reported, only_new, i);
+  const unsigned m = __ballot_sync(0xffffffffu, sel);
+  if (lane == 0) warp_base[w] = __popc(m);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = offsets[blockIdx.x];
+    for (int k = 0; k < artis::ESC_CHUNK / 32; k++) {
+      const int c = warp_base[k];
+      warp_base[k] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  // the warp copies its selected packets one after the other, 19 lanes x 16 bytes each
+  const long long warp_first = i - lane;
+  int rank = 0;
+  for (unsigned rest = m; rest; rest &= rest - 1, rank++) {
+    const int src_lane = __ffs(rest) - 1;
+    const uint4 *src = reinterpret_cast<const uint4 *>(pkts + warp_first + src_lane);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + warp_base[w] + rank);
+    if (lane < (int)(sizeof(ArtisPacket) / 16)) dst[lane] = src[lane];
+  }
+  if (sel && only_new) reported[i] = 1;
+}
 // one kernel per event kind, each compiled with only that kind's physics
 template <int KIND>
 __global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned long long *rngctr, artis::QueueView qv,
@@ -290,18 +361,23 @@ __device__ __forceinline__ void kcache_load(artis::KappaCache &k, const double *
   for (int g = 0; g < ng; g++) k.gamma_contr[g] = __ldcg(kc + 8 + g);
 }
 // ring primitives (protocol in the comment above)
+constexpr int RMS = artis::RING_META_STRIDE;
+#ifndef ARTIS_REFILL_BACKOFF
+#define ARTIS_REFILL_BACKOFF 4
+#endif
+constexpr int REFILL_BACKOFF = ARTIS_REFILL_BACKOFF;
 __device__ __forceinline__ long long ring_backlog(const PersistView &pv, const int r) {
-  const unsigned long long h = ld_volatile_u64(pv.head + r), t = ld_volatile_u64(pv.tail + r);
+  const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
   return t > h ? (long long)(t - h) : 0;
 }
 // lane 0: claim up to `want` entries of ring r; returns the count and the first ticket
 __device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, const int want, unsigned long long *base) {
   for (int tries = 0; tries < 4; tries++) {
-    const unsigned long long h = ld_volatile_u64(pv.head + r), t = ld_volatile_u64(pv.tail + r);
+    const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
     const long long avail = t > h ? (long long)(t - h) : 0;
     const int take = avail < want ? (int)avail : want;
     if (take == 0) return 0;
-    if (atomicCAS(pv.head + r, h, h + (unsigned long long)take) == h) {
+    if (atomicCAS(pv.head + r * RMS, h, h + (unsigned long long)take) == h) {
       *base = h;
       return take;
     }
@@ -348,6 +424,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
   RpktStepState st;
   st.mgi = 0;
   unsigned long long idle_since = 0ull;
+  int refill_skip = 0;  // iterations left during which a partly busy warp does not look at its (just found empty) ring
   est_private_begin(nullptr, 0u);
   if ((ROLES & (1u << KIND_RPKT_GREY)) != 0 && blockIdx.x == 0 && threadIdx.x == 0)
     *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
@@ -355,7 +432,9 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
   while (true) {
     __syncwarp(full);
     const unsigned need = __ballot_sync(full, !have);
-    if (need != 0u) {
+    if (need != full && refill_skip > 0) {
+      refill_skip--;
+    } else if (need != 0u) {
       if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
         long long backlog = 0;
         if (lane < NRING && ((ROLES >> lane) & 1u) != 0) backlog = ring_backlog(pv, lane);
@@ -438,6 +517,9 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
         have = true;
       }
       if (need == full && take_a + take_b == 0) continue;  // lost the race for the last entries
+      // a claim costs the warp two L2 round trips on the busiest words of the device: after an empty answer the busy
+      // lanes run a few iterations before the warp asks again (a warp without any work asks at once)
+      refill_skip = (take_a + take_b < want) ? REFILL_BACKOFF : 0;
     }
     __syncwarp(full);
     bool done = false;
@@ -532,7 +614,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
         if (m != 0u) {
           const int leader = __ffs(m) - 1;
           unsigned long long b = 0ull;
-          if (lane == leader) b = atomicAdd(pv.tail + kk, (unsigned long long)__popc(m));
+          if (lane == leader) b = atomicAdd(pv.tail + kk * RMS, (unsigned long long)__popc(m));
           b = __shfl_sync(full, b, leader);
           if (done && k2 == kk) ring_put(pv, kk, b + (unsigned long long)__popc(m & lt_mask), idx);
         }
@@ -731,6 +813,16 @@ void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long
   const int in_smem = smem <= 32768;
   k_bin_escaped<<<grid_for(n, 256, 8), 256, in_smem ? smem : 0, g_stream>>>(b, p, n, in_smem);
 }
+// counts must hold n / ESC_CHUNK + 2 ints; afterwards counts[0..nchunks) are the chunks' output offsets, counts[nchunks] the total
+void be_run_escaped_count(const ArtisPacket *p, long long n, const unsigned char *reported, int only_new, int *counts) {
+  const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
+  if (nchunks > 0) k_escaped_count<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(p, n, reported, only_new, counts);
+  k_escaped_scan<<<1, 1024, 0, g_stream>>>(counts, nchunks);
+}
+void be_run_escaped_scatter(const ArtisPacket *p, long long n, unsigned char *reported, int only_new, const int *offsets, ArtisPacket *out) {
+  const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
+  if (nchunks > 0) k_escaped_scatter<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(p, n, reported, only_new, offsets, out);
+}
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
   k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, r, n, buckets);
   k_bucket_scan<<<1, 1, 0, g_stream>>>(buckets, kind_sizes);
@@ -749,7 +841,7 @@ void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueV
   }
 }
 // barrier-free scheduler: rings = NRING rings of `cap` ints (initial entries written by be_run_bucket, -1 elsewhere),
-// pmeta = head[NRING], tail[NRING], n_active (int), t_start.
+// pmeta = head[NRING], tail[NRING], n_active (int), t_start, each on its own RING_META_STRIDE words.
 // g_scheduler_kernels == 2: the light kernel (macro-atom/k-packet and opacity-on-request roles, <= 80 registers, 3 blocks
 // per SM) and the heavy kernel (everything else, 1 block per SM) run side by side on two streams and exchange packets
 // through the rings; 1: one kernel with every role (2 blocks per SM of ~250 registers).
@@ -758,10 +850,10 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
   PersistView pv;
   for (int k = 0; k < NRING; k++) pv.ring[k] = rings + (size_t)k * cap;
   pv.head = pmeta;
-  pv.tail = pmeta + NRING;
-  pv.n_active = reinterpret_cast<int *>(pmeta + 2 * NRING);
+  pv.tail = pmeta + NRING * RMS;
+  pv.n_active = reinterpret_cast<int *>(pmeta + 2 * NRING * RMS);
   pv.n_initial = n_initial;
-  pv.t_start = pmeta + 2 * NRING + 1;
+  pv.t_start = pmeta + (2 * NRING + 1) * RMS;
   pv.cap = cap;
   const int kstride = 8 + g_nbfcontinua_ground;
   const bool two = g_scheduler_kernels == 2;
@@ -788,13 +880,13 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
     // launch can make the driver grow the local-memory pool, which waits for running kernels -- with the other
     // persistent kernel already spinning that would never end.
     unsigned long long *scratch = nullptr;
-    if (cudaMalloc(&scratch, 16 * sizeof(unsigned long long)) == cudaSuccess) {
-      note(cudaMemsetAsync(scratch, 0, 16 * sizeof(unsigned long long), g_stream), "memset");
+    if (cudaMalloc(&scratch, artis::RING_META_WORDS * sizeof(unsigned long long)) == cudaSuccess) {
+      note(cudaMemsetAsync(scratch, 0, artis::RING_META_WORDS * sizeof(unsigned long long), g_stream), "memset");
       PersistView w = pv;
       w.head = scratch;
-      w.tail = scratch + NRING;
-      w.n_active = reinterpret_cast<int *>(scratch + 2 * NRING);
-      w.t_start = scratch + 2 * NRING + 1;
+      w.tail = scratch + NRING * RMS;
+      w.n_active = reinterpret_cast<int *>(scratch + 2 * NRING * RMS);
+      w.t_start = scratch + (2 * NRING + 1) * RMS;
       w.n_initial = 0;
       k_transport_persistent<ROLES_ALL, 2><<<1, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
       k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS><<<1, 128, 0, g_stream>>>(p, r, w, maxev, timeout);

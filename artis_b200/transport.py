@@ -154,6 +154,15 @@ class Transport:
                                                    _pd(sto) if stokes else None), "artis_gpu_bin_escaped")
         return lc, flux, sto
 
+    def download_escaped(self, only_new=False, capacity=None):
+        """the escaped packets of the resident ensemble in array order (only_new: not delivered by an earlier only_new call)"""
+        cap = self.npkts if capacity is None else capacity
+        out = np.zeros(cap, dtype=abi.PACKET_DTYPE)
+        n = C.c_int(0)
+        self._check(self.lib.artis_gpu_packets_download_escaped(out.ctypes.data_as(C.c_void_p), cap, int(bool(only_new)),
+                                                                C.byref(n)), "artis_gpu_packets_download_escaped")
+        return out[:n.value]
+
     # ---- deterministic probes (K10)
     def probe_boundary_cross(self, pkts):
         n = pkts.size

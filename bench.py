@@ -90,7 +90,7 @@ def measured_traffic(packets):
     """dram__bytes_read.sum + dram__bytes_write.sum of one transport launch from the committed ncu capture, when that
     capture was taken at this packet count; None otherwise (the number is not measured under this run)"""
     try:
-        t = json.load(open(os.path.join(REPO, "profiles", "r1_final_traffic.json")))
+        t = json.load(open(os.path.join(REPO, "profiles", "r1_end_traffic.json")))
         return float(t["dram_bytes_per_launch"]) if int(t["packets_per_gpu"]) == int(packets) else None
     except Exception:
         return None
@@ -375,7 +375,7 @@ def main():
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6537.6",
                              "kernel": "k_transport_persistent", "launches_per_step": 1,
                              "algorithmic_bytes_per_launch": alg_bytes / a.steps,
-                             "traffic_source": "profiles/r1_final_traffic.json (ncu dram bytes per launch at this packet "
+                             "traffic_source": "profiles/r1_end_traffic.json (ncu dram bytes per launch at this packet "
                                                "count; null at other counts)"},
                 "e2e": {"value": e2e_inter / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                         "d2h_bytes_per_step": nbytes + ndoubles * 8},

@@ -208,6 +208,13 @@ int artis_gpu_estimator_block(void **dev_ptr, size_t *ndoubles);
  * The frequency grid is init_spectra(nu_min_r, nu_max_r) (spectrum.cc:483-499), float delta_freq included. Sums are
  * accumulated with FP64 atomics, so a bin agrees with the reference's serial sum to rounding (not bit for bit). */
 int artis_gpu_bin_escaped(double tmax, int nprocs, int nnubins, int allreduce, double *lc, double *spec_flux, double *stokes);
+/* The escaped packets of the resident ensemble, packed in array order into out[0..*n_out): the subset that the host
+ * loops over the packet array select with `type == TYPE_ESCAPE` (spectrum.cc:673, exspec.cc, packet.cc:152
+ * write_packets), so that a driver with resident packets moves *n_out x 304 bytes instead of npkts x 304.
+ * only_new != 0: only packets that no earlier only_new call since the last artis_gpu_packets_upload has delivered (an
+ * escaped packet is never processed again, update_packets.cc:287), i.e. this timestep's escapes when called once per
+ * timestep. If *n_out > capacity the call fails with ARTIS_ERR_ABI, *n_out holds the count and nothing is marked. */
+int artis_gpu_packets_download_escaped(ArtisPacket *out, int capacity, int only_new, int *n_out);
 
 /* ---- K10: deterministic probes (test entry points for SURVEY 8a A4-A8, A11, A12, A14) ------------------ */
 /* Each probe runs the corresponding device function for n independent packet states on the GPU. */

@@ -45,6 +45,25 @@ void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_co
 void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long n) {
   for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, g_ctx.st.tmin, p, i, b.lc);
 }
+void be_run_escaped_count(const ArtisPacket *p, long long n, const unsigned char *reported, int only_new, int *counts) {
+  const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
+  int run = 0;
+  for (int c = 0; c < nchunks; c++) {
+    counts[c] = run;
+    for (long long i = (long long)c * artis::ESC_CHUNK; i < n && i < (long long)(c + 1) * artis::ESC_CHUNK; i++)
+      run += artis::escaped_selected(p, reported, only_new, i);
+  }
+  counts[nchunks] = run;
+}
+void be_run_escaped_scatter(const ArtisPacket *p, long long n, unsigned char *reported, int only_new, const int *offsets, ArtisPacket *out) {
+  (void)offsets;
+  int k = 0;
+  for (long long i = 0; i < n; i++) {
+    if (!artis::escaped_selected(p, reported, only_new, i)) continue;
+    out[k++] = p[i];
+    if (only_new) reported[i] = 1;
+  }
+}
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
   for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, p, r, i, buckets);
   artis::body_bucket_scan(g_ctx, buckets, kind_sizes);

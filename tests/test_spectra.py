@@ -76,7 +76,8 @@ def synthetic_escaped(g, n, seed):
     and frequency grids so that every range check of add_to_spec / add_to_lc_res is hit."""
     rng = np.random.default_rng(seed)
     st = g["static"]
-    p = np.resize(g["post"], n).copy()
+    rows = g["post"].view(np.uint8).reshape(-1, 304)[np.arange(n) % g["post"].size]  # (np.resize would repack the dtype)
+    p = np.ascontiguousarray(rows).view(abi.PACKET_DTYPE).reshape(-1)
     p["type"] = np.where(rng.random(n) < 0.75, abi.TYPE_ESCAPE, 11)
     p["escape_type"] = np.where(rng.random(n) < 0.8, 11, 10)
     tmin, tmax = float(st["tmin"]), g["tmax"]
@@ -91,6 +92,46 @@ def synthetic_escaped(g, n, seed):
     p["e_cmf"] = p["e_rf"] * rng.uniform(0.9, 1.1, n)
     p["stokes"] = rng.uniform(-1, 1, (n, 3))
     return p
+
+
+def check_escaped_compaction(lib, n):
+    """array-order compaction of the escaped packets; only_new delivers every escaped packet exactly once"""
+    g = load_spectra_fixture()
+    pk = g["post"].copy() if n is None else synthetic_escaped(g, n, 11)
+    pk["number"] = np.arange(pk.size)
+    T = Transport(lib)
+    T.init(g["static"])
+    T.packets_upload(pk)
+    # whole 304-byte records, padding included (a boolean index on the structured array would drop the padding bytes)
+    want = pk.view(np.uint8).reshape(-1, 304)[pk["type"] == abi.TYPE_ESCAPE]
+    raw = lambda a: a.view(np.uint8).reshape(-1, 304)  # noqa: E731
+    got = T.download_escaped()
+    assert got.size == want.shape[0] and np.array_equal(raw(got), want)
+    assert np.array_equal(got["number"], np.flatnonzero(pk["type"] == abi.TYPE_ESCAPE))  # array order
+    first = T.download_escaped(only_new=True)
+    assert np.array_equal(raw(first), want)
+    assert T.download_escaped(only_new=True).size == 0            # all delivered
+    assert np.array_equal(raw(T.download_escaped()), want)        # the plain call is not affected by the marks
+    with pytest.raises(Exception):
+        T.download_escaped(capacity=want.shape[0] - 1)            # too small a buffer is an error, not a truncation
+    # a new ensemble forgets the marks; an ensemble without escapes gives nothing
+    T.packets_upload(pk)
+    assert T.download_escaped(only_new=True).size == want.shape[0]
+    T.packets_upload(pk[pk["type"] != abi.TYPE_ESCAPE].copy())
+    assert T.download_escaped().size == 0
+    T.finalize()
+
+
+def test_restatement_escaped_compaction(oracle_lib):
+    check_escaped_compaction(oracle_lib, None)
+    check_escaped_compaction(oracle_lib, 5000)
+
+
+@pytest.mark.gpu
+def test_cuda_escaped_compaction(gpu_lib):
+    check_escaped_compaction(gpu_lib, None)
+    for n in (1, 255, 256, 257, 1_000_003):  # chunk edges and more chunks than one scan sweep
+        check_escaped_compaction(gpu_lib, n)
 
 
 def test_restatement_spectra_match_reference(oracle_lib):
