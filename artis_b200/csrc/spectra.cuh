@@ -12,7 +12,7 @@
 namespace artis {
 
 struct BinSpec {
-  double tmax;             // globals::tmax
+  double tmin, tmax;       // globals::tmin, globals::tmax
   double nu_min, nu_max;   // globals::nu_min_r / nu_max_r (init_spectra's arguments at spectrum.cc:670)
   double dlognu;           // (log(nu_max) - log(nu_min)) / nnubins, spectrum.cc:354
   int nnubins;             // globals::nnubins (MNUBINS, exspec.h:5)
@@ -45,7 +45,8 @@ ARTIS_DEV int bin_timestep(const BinSpec &b, const double time) {
 }
 
 // lc_local: the block's private copy of b.lc (shared memory) or b.lc itself
-ARTIS_DEV void body_bin_escaped(const BinSpec &b, const double tmin, const ArtisPacket *pkts, const long long n, double *lc_local) {
+ARTIS_DEV void body_bin_escaped(const BinSpec &b, const ArtisPacket *pkts, const long long n, double *lc_local) {
+  const double tmin = b.tmin;
   const ArtisPacket &p = pkts[n];
   if (p.type != ARTIS_TYPE_ESCAPE) return;
   const int et = p.escape_type;

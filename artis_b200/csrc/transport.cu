@@ -73,9 +73,8 @@ __global__ void __launch_bounds__(256) k_bin_escaped(const artis::BinSpec b, con
     __syncthreads();
     lc_local = lc_smem;
   }
-  const double tmin = d_ctx.st.tmin;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    artis::body_bin_escaped(b, tmin, pkts, i, lc_local);
+    artis::body_bin_escaped(b, pkts, i, lc_local);
   if (lc_in_smem) {
     __syncthreads();
     for (int i = threadIdx.x; i < nlc; i += blockDim.x)
@@ -363,9 +362,13 @@ __device__ __forceinline__ void kcache_load(artis::KappaCache &k, const double *
 // ring primitives (protocol in the comment above)
 constexpr int RMS = artis::RING_META_STRIDE;
 #ifndef ARTIS_REFILL_BACKOFF
-#define ARTIS_REFILL_BACKOFF 4
+#define ARTIS_REFILL_BACKOFF 16
 #endif
 constexpr int REFILL_BACKOFF = ARTIS_REFILL_BACKOFF;
+#ifndef ARTIS_REFILL_MIN
+#define ARTIS_REFILL_MIN 1
+#endif
+constexpr int REFILL_MIN = ARTIS_REFILL_MIN;  // a partly busy warp refills only when at least this many lanes are idle
 __device__ __forceinline__ long long ring_backlog(const PersistView &pv, const int r) {
   const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
   return t > h ? (long long)(t - h) : 0;
@@ -432,8 +435,8 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
   while (true) {
     __syncwarp(full);
     const unsigned need = __ballot_sync(full, !have);
-    if (need != full && refill_skip > 0) {
-      refill_skip--;
+    if (need != full && (refill_skip > 0 || __popc(need) < REFILL_MIN)) {
+      if (refill_skip > 0) refill_skip--;
     } else if (need != 0u) {
       if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
         long long backlog = 0;

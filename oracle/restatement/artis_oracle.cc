@@ -43,7 +43,7 @@ void be_run_corrphoto(long long n) { for (long long i = 0; i < n; i++) artis::bo
 void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
 void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
 void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long n) {
-  for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, g_ctx.st.tmin, p, i, b.lc);
+  for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, p, i, b.lc);
 }
 void be_run_escaped_count(const ArtisPacket *p, long long n, const unsigned char *reported, int only_new, int *counts) {
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);

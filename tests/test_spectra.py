@@ -138,6 +138,27 @@ def test_restatement_spectra_match_reference(oracle_lib):
     check_against_golden(oracle_lib)
 
 
+def energy_checksum(g, pk, lc, nprocs):
+    """every escaped r-packet that arrives inside (tmin, tmax) lands in exactly one light-curve bin"""
+    esc = (pk["type"] == abi.TYPE_ESCAPE) & (pk["escape_type"] == 11)
+    t_arr = pk["escape_time"] - (pk["pos"] * pk["dir"]).sum(1) / 2.99792458e10
+    inr = esc & (t_arr > float(g["static"]["tmin"])) & (t_arr < g["tmax"])
+    width = np.asarray(g["static"]["ts_width"])
+    assert np.isclose((lc[0] * width).sum() * nprocs, pk["e_rf"][inr].sum(), rtol=1e-10)
+
+
+def test_restatement_spectra_energy_checksum(oracle_lib):
+    g = load_spectra_fixture()
+    pk = synthetic_escaped(g, 200_000, 5)  # arrival times before tmin and after tmax included
+    T = Transport(oracle_lib)
+    T.init(g["static"])
+    T.packets_upload(pk)
+    lc, flux, _ = T.bin_escaped(g["tmax"], 3, g["nnubins"])
+    energy_checksum(g, pk, lc, 3)
+    assert (flux != 0).mean() > 0.5
+    T.finalize()
+
+
 @pytest.mark.gpu
 def test_cuda_spectra_match_reference(gpu_lib):
     check_against_golden(gpu_lib)
@@ -163,9 +184,4 @@ def test_cuda_spectra_match_restatement_at_scale(gpu_lib, oracle_lib):
     # Stokes terms have both signs: compare against the size of the terms, not of the (cancelling) sum
     scale = np.abs(fl_o)[None]
     assert (np.abs(st_g - st_o) <= 1e-12 * scale).all()
-    # every in-range escaped packet lands in exactly one light-curve bin: a checksum of the whole ensemble
-    esc = (pk["type"] == abi.TYPE_ESCAPE) & (pk["escape_type"] == 11)
-    t_arr = pk["escape_time"] - (pk["pos"] * pk["dir"]).sum(1) / 2.99792458e10
-    inr = esc & (t_arr > float(g["static"]["tmin"])) & (t_arr < g["tmax"])
-    width = np.asarray(g["static"]["ts_width"])
-    assert np.isclose((lc_g[0] * width).sum() * 3, pk["e_rf"][inr].sum(), rtol=1e-10)
+    energy_checksum(g, pk, lc_g, 3)
