@@ -375,6 +375,7 @@ __device__ __forceinline__ long long ring_backlog(const PersistView &pv, const i
 }
 // lane 0: claim up to `want` entries of ring r; returns the count and the first ticket
 __device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, const int want, unsigned long long *base) {
+#ifdef ARTIS_CLAIM_RELOAD  // A/B switch: the earlier protocol re-read both words after a lost race
   for (int tries = 0; tries < 4; tries++) {
     const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
     const long long avail = t > h ? (long long)(t - h) : 0;
@@ -386,6 +387,23 @@ __device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, co
     }
   }
   return 0;
+#else
+  // a lost race hands back the current head: retry with it and the (older, hence conservative) tail, one round trip less
+  unsigned long long h = ld_volatile_u64(pv.head + r * RMS);
+  const unsigned long long t = ld_volatile_u64(pv.tail + r * RMS);
+  for (int tries = 0; tries < 4; tries++) {
+    const long long avail = t > h ? (long long)(t - h) : 0;
+    const int take = avail < want ? (int)avail : want;
+    if (take == 0) return 0;
+    const unsigned long long seen = atomicCAS(pv.head + r * RMS, h, h + (unsigned long long)take);
+    if (seen == h) {
+      *base = h;
+      return take;
+    }
+    h = seen;
+  }
+  return 0;
+#endif
 }
 __device__ __forceinline__ int ring_take(const PersistView &pv, const int r, const unsigned long long ticket) {
   int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);

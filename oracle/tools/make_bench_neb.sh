@@ -8,7 +8,7 @@
 set -e
 cd "$(dirname "$0")/../.."
 RUN=oracle/_ref/runs/bench_neb
-ARGS="--nions 4 --nlevels 100 --dense-levels 12 --sparsity 0.1"
+ARGS="--nions 4 --nlevels 100 --dense-levels 12 --sparsity 0.51"  # 48577 lines / 1035 continua / 1200 levels
 rm -f oracle/_ref/nebular/inc/artisoptions.h
 ARTIS_MPKTS=100000 make -C oracle ref MODE=nebular -j8 > /dev/null
 rm -rf $RUN
