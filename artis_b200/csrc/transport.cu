@@ -375,7 +375,7 @@ __device__ __forceinline__ long long ring_backlog(const PersistView &pv, const i
 }
 // lane 0: claim up to `want` entries of ring r; returns the count and the first ticket
 __device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, const int want, unsigned long long *base) {
-#ifdef ARTIS_CLAIM_RELOAD  // A/B switch: the earlier protocol re-read both words after a lost race
+#ifndef ARTIS_CLAIM_CASRETRY  // default: both words are read again after a lost race (the variant below measured 1 % slower)
   for (int tries = 0; tries < 4; tries++) {
     const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
     const long long avail = t > h ? (long long)(t - h) : 0;
