@@ -362,7 +362,7 @@ __device__ __forceinline__ void kcache_load(artis::KappaCache &k, const double *
 // ring primitives (protocol in the comment above)
 constexpr int RMS = artis::RING_META_STRIDE;
 #ifndef ARTIS_REFILL_BACKOFF
-#define ARTIS_REFILL_BACKOFF 16
+#define ARTIS_REFILL_BACKOFF 10
 #endif
 constexpr int REFILL_BACKOFF = ARTIS_REFILL_BACKOFF;
 #ifndef ARTIS_REFILL_MIN
