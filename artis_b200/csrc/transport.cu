@@ -532,6 +532,7 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
           const long long packed = __double_as_longlong(__ldcg(ss + 2));
           st.snext = (int)(packed >> 32);
           st.mgi = (int)(packed & 0xffffffffll);
+          st.mgi_next = rpkt_step_mgi_next(c, p, st);
           resumed = true;
         }
         events = 0;
