@@ -402,9 +402,6 @@ struct Tally {
   // VPKT_ON: a virtual-packet request left by the event that has just been processed (vpkt.cuh vpkt_flush_request runs it
   // at the one place per scheduler where events return): realtype 1-3 (0 = none) and, for an electron scattering, the
   // direction and Stokes Q, U the packet arrived with
-  int cont_req, cont_ui, cont_gl, cont_upper;  // a free-bound emission asked for its frequency (select_continuum_nu request)
-  float cont_Te;
-  int emit_req;  // an event of the macro-atom / k-packet kind turned the packet into an r-packet: emitt_rpkt_flush draws its direction
   int vpkt_req;
   double vpkt_dir[3], vpkt_q, vpkt_u;
 };

@@ -428,7 +428,6 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
       fatal(c, 441);
       p.prop_time = t2;
   }
-  emission_flush(c, p, rng, tl);
 }
 
 // do_packet restricted to the packet types of one scheduler kind (kernels.cuh kind_of): each wavefront kernel only
@@ -460,7 +459,6 @@ ARTIS_DEV void do_packet_kind(const Ctx &c, ArtisPacket &p, const double t2, Kap
         p.prop_time = t2;
       }
     }
-    emission_flush(c, p, rng, tl);
   } else {
     do_packet(c, p, t2, k, rng, tl);
   }

@@ -25,7 +25,7 @@ ARTIS_DEV void do_kpkt_bb(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   const float T_e = c.cs.Te[mgi];
   p.nu_cmf = sample_planck(c, (double)T_e, rng);
   if (!isfinite(p.nu_cmf)) fatal(c, 301);
-  emitt_rpkt_request(p, tl);
+  emitt_rpkt(c, p, rng);
   p.next_trans = 0;
   stat_inc(tl, COUNTER_K_STAT_TO_R_BB);
   p.interactions++;
@@ -98,7 +98,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     const double z = rng_uniform_pos(rng);
     p.nu_cmf = -KB * T_e / H * log(z);
     if (!isfinite(p.nu_cmf)) fatal(c, 304);
-    emitt_rpkt_request(p, tl);
+    emitt_rpkt(c, p, rng);
     p.next_trans = 0;
     stat_inc(tl, COUNTER_K_STAT_TO_R_FF);
     p.interactions += 1;
@@ -111,8 +111,8 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     const int level = c.st.cool_level[i];
     const int upper = c.st.cool_upperlevel[i];
     const int gl_lower = c.st.ion_leveloffset[ui] + level;
-    continuum_nu_request(tl, ui, gl_lower, upper, T_e);
-    emitt_rpkt_request(p, tl);
+    p.nu_cmf = select_continuum_nu(c, ui, gl_lower, upper, T_e, rng);
+    emitt_rpkt(c, p, rng);
     p.next_trans = 0;
     stat_inc(tl, COUNTER_K_STAT_TO_R_FB);
     p.interactions += 1;

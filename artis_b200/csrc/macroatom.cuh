@@ -128,25 +128,6 @@ ARTIS_DEV double select_continuum_nu(const Ctx &c, const int ui_lower, const int
 }
 
 // common tail of every r-packet emission from a macro-atom / k-packet
-// The frequency draw of a free-bound emission (k-packet cooling and macro-atom recombination) is requested by the event
-// and made at one place per kernel, like the direction draw (rpkt_events.cuh emitt_rpkt_request): one copy of the
-// ~1900-instruction inverse-CDF instead of two.
-ARTIS_DEV void continuum_nu_request(Tally &tl, const int ui_lower, const int gl_lower, const int upperionlevel, const float T_e) {
-  tl.cont_req = 1;
-  tl.cont_ui = ui_lower;
-  tl.cont_gl = gl_lower;
-  tl.cont_upper = upperionlevel;
-  tl.cont_Te = T_e;
-}
-// both deferred draws, in the order the events made them: frequency, then direction (which needs nu_cmf for nu_rf)
-ARTIS_DEV void emission_flush(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
-  if (tl.cont_req != 0) {
-    tl.cont_req = 0;
-    p.nu_cmf = select_continuum_nu(c, tl.cont_ui, tl.cont_gl, tl.cont_upper, tl.cont_Te, rng);
-    if (!isfinite(p.nu_cmf)) fatal(c, 225);
-  }
-  emitt_rpkt_flush(c, p, rng, tl);
-}
 ARTIS_DEV void mark_emission(ArtisPacket &p) {
   p.em_pos[0] = p.pos[0];
   p.em_pos[1] = p.pos[1];
@@ -242,7 +223,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         p.interactions += 1;
         tl.interactions++;
         p.last_event = 0;
-        emitt_rpkt_request(p, tl);
+        emitt_rpkt(c, p, rng);
         if (linelistindex == activatingline) stat_inc(tl, COUNTER_RESONANCESCATTERINGS);
         p.next_trans = linelistindex + 1;
         p.emissiontype = linelistindex;
@@ -287,12 +268,13 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
           return;
         }
         const int gl_lower = gl0_lower + lower;
-        continuum_nu_request(tl, ui - 1, gl_lower, level, T_e);
+        p.nu_cmf = select_continuum_nu(c, ui - 1, gl_lower, level, T_e, rng);
+        if (!isfinite(p.nu_cmf)) fatal(c, 225);
         stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_FB);
         p.interactions += 1;
         tl.interactions++;
         p.last_event = 2;
-        emitt_rpkt_request(p, tl);
+        emitt_rpkt(c, p, rng);
         p.next_trans = 0;
         p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, level);
         mark_emission(p);

@@ -133,22 +133,6 @@ ARTIS_DEV void emitt_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
   p.stokes[2] = 0.;
   set_pol_dir(p);
 }
-// The events of the macro-atom / k-packet kind end in five different places with "emit an r-packet"; inlined five times
-// the direction draw + Doppler + polarisation frame were a quarter of that kind's code (4750 of 16000 instructions, measured
-// on the SASS) in a kernel that stalls on instruction fetch as often as on memory. They record the request instead and
-// the one copy of emitt_rpkt runs where the event returns (do_packet_kind / do_packet). Nothing between the request and
-// the flush reads the direction or the rest-frame frequency, and no random number is drawn in between.
-ARTIS_DEV void emitt_rpkt_request(ArtisPacket &p, Tally &tl) {
-  p.type = ARTIS_TYPE_RPKT;
-  p.last_cross = ARTIS_CROSS_NONE;
-  tl.emit_req = 1;
-}
-ARTIS_DEV void emitt_rpkt_flush(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
-  if (tl.emit_req != 0) {
-    tl.emit_req = 0;
-    emitt_rpkt(c, p, rng);
-  }
-}
 
 // ---- vpkt.cc:898-1069 rot_angle / meridian / lorentz / frame_transform ----------------------------------------------
 ARTIS_DEV double rot_angle(const double *n1, const double *n2, const double *ref1, const double *ref2) {
