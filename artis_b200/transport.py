@@ -119,6 +119,15 @@ class Transport:
         return int(self.lib.artis_gpu_table_bytes())
 
     # ---- estimators
+    def comm_unique_id(self):
+        """rank 0: the 128-byte NCCL id that every shard passes to comm_init (hand it round like MPI_Bcast would)"""
+        buf = C.create_string_buffer(128)
+        self._check(self.lib.artis_gpu_comm_unique_id(buf), "artis_gpu_comm_unique_id")
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, nranks):
+        self._check(self.lib.artis_gpu_comm_init(C.create_string_buffer(unique_id, 128), rank, nranks), "artis_gpu_comm_init")
+
     def reduce_estimators(self, nts=None):
         self._check(self.lib.artis_gpu_reduce_estimators(self.nts if nts is None else nts), "artis_gpu_reduce_estimators")
 
