@@ -148,11 +148,13 @@ struct Ctx {
 #endif
 
 // ---- Philox4x32-10 counter-based stream (Salmon et al. 2011), one stream per packet and timestep -------------
-// key = (seed_lo ^ packet.number, seed_hi); counter = (draw index lo, draw index hi, nts, rank). The draw index
-// restarts at 0 every timestep and is kept in a device array between the passes of one timestep, so nothing has to
-// survive in the host's struct packet. Interval conventions of SURVEY Q17. One Philox call yields two doubles.
+// key = (seed_lo, seed_hi); counter = (draw block, packet.number, nts, rank): the seed and the packet number sit in
+// different words, so two seeds never share a set of streams (with the number XORed into the key, seeds that differ in
+// low bits gave the same streams permuted among the packets). The draw index restarts at 0 every timestep and is kept in
+// a device array between the passes of one timestep, so nothing has to survive in the host's struct packet. Interval
+// conventions of SURVEY Q17. One Philox call yields two doubles.
 struct Rng {
-  uint32_t k0, k1, c2, c3;
+  uint32_t k0, k1, c1, c2, c3;
   uint64_t ctr;      // number of doubles drawn so far
   double spare;      // second double of the last block
 };
@@ -184,8 +186,9 @@ ARTIS_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
 }
 ARTIS_DEV Rng rng_init(const Ctx &c, const int number, const uint64_t ctr) {
   Rng r;
-  r.k0 = (uint32_t)(c.seed & 0xffffffffu) ^ (uint32_t)number;
+  r.k0 = (uint32_t)(c.seed & 0xffffffffu);
   r.k1 = (uint32_t)(c.seed >> 32);
+  r.c1 = (uint32_t)number;
   r.c2 = (uint32_t)c.nts;
   r.c3 = (uint32_t)c.rank;
   r.ctr = ctr;
@@ -207,7 +210,9 @@ ARTIS_DEV double rng_uniform(Rng &r) {
     return x;
   }
   uint32_t o[4];
-  philox4x32_10((uint32_t)(blk & 0xffffffffu), (uint32_t)(blk >> 32), r.c2, r.c3, r.k0, r.k1, o);
+  // a packet draws far fewer than 2^33 numbers per timestep; the high word of the block index is folded into the
+  // timestep word so that even such a stream would stay unique
+  philox4x32_10((uint32_t)(blk & 0xffffffffu), r.c1, r.c2 ^ ((uint32_t)(blk >> 32) << 16), r.c3, r.k0, r.k1, o);
   if (odd) return bits_to_unit(o[2], o[3]);  // stream resumed on an odd draw (spare was lost between passes)
   r.spare = bits_to_unit(o[2], o[3]);
   return bits_to_unit(o[0], o[1]);
@@ -341,50 +346,31 @@ ARTIS_DEV void scatter_dir(Rng &r, const double dir_in[3], const double cos_thet
 
 // ---- estimator / counter accumulation ------------------------------------------------------------------------
 #ifdef __CUDACC__
-// Block-private estimators. With a 1D model every packet of the timestep adds to the same ~100 cells' J / nuJ /
-// heating sums: hundreds of millions of FP64 atomics on a few hundred addresses, which serialise in L2 and back up the
-// load path behind them (profiles/r1_final: 47% of all long-scoreboard stalls sat behind them). A kernel that opts in
-// (est_private_begin) accumulates into a copy of the estimator block in its dynamic shared memory and adds that copy
-// to the global block once, at its end (est_private_flush). The copy is used only when the whole block fits.
-extern __shared__ double artis_est_smem[];
-__shared__ double *artis_est_global;   // global estimator block this copy shadows, nullptr = no private copy
-__shared__ unsigned artis_est_count;   // its length in doubles
-ARTIS_DEV void est_add(double *addr, double v) {
-  double *const base = artis_est_global;
-  if (base != nullptr) {
-    const unsigned long long off = (unsigned long long)(addr - base);
-    if (off < (unsigned long long)artis_est_count) {
-      atomicAdd(&artis_est_smem[off], v);
-      return;
-    }
-  }
-  atomicAdd(addr, v);
-}
-// all threads of the block call these; ndoubles == 0 selects plain global atomics
-ARTIS_DEV void est_private_begin(double *global_block, unsigned ndoubles) {
-  if (threadIdx.x == 0) {
-    artis_est_global = ndoubles > 0 ? global_block : nullptr;
-    artis_est_count = ndoubles;
-  }
-  for (unsigned i = threadIdx.x; i < ndoubles; i += blockDim.x) artis_est_smem[i] = 0.;
-  __syncthreads();
-}
-ARTIS_DEV void est_private_flush() {
-  __syncthreads();
-  double *const base = artis_est_global;
-  const unsigned n = artis_est_count;
-  if (base != nullptr) {
-    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
-      const double v = artis_est_smem[i];
-      if (v != 0.) atomicAdd(base + i, v);
-    }
-  }
+// FP64 estimator sums (safeadd, sn3d.h:104-127). With a 1D model every packet of the timestep adds to the same ~100
+// cells' J / nuJ / heating sums, and the lanes of a warp are mostly in the same cell (packets are bucketed by cell):
+// the lanes that are about to add to the SAME address are found with __match_any_sync, their values are summed with
+// shuffles and the lowest lane issues one red.global.add.f64 for all of them. The lanes taking part are exactly those
+// converged at the call (__activemask), so this is safe inside divergent event code. Returns the number of global
+// reductions issued by this lane (1 for a group leader, else 0): ARTIS_CTR_ESTIM_ATOMICS counts what reaches L2.
+ARTIS_DEV int est_add(double *addr, double v) {
+  const unsigned act = __activemask();
+  const unsigned peers = __match_any_sync(act, (unsigned long long)addr);
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(peers) - 1;
+  double s = v;
+  for (unsigned rest = peers & (peers - 1u); rest != 0u; rest &= rest - 1u)  // every peer walks the same list
+    s += __shfl_sync(peers, v, __ffs(rest) - 1);
+  if (lane == leader) atomicAdd(addr, s);
+  return lane == leader ? 1 : 0;
 }
 ARTIS_DEV void ctr_add(long long *addr, long long v) { atomicAdd((unsigned long long *)addr, (unsigned long long)v); }
 ARTIS_DEV void int_add(int *addr, int v) { atomicAdd(addr, v); }
 ARTIS_DEV int int_fetch_add(int *addr, int v) { return atomicAdd(addr, v); }
 #else
-ARTIS_DEV void est_add(double *addr, double v) { *addr += v; }
+ARTIS_DEV int est_add(double *addr, double v) {
+  *addr += v;
+  return 1;
+}
 ARTIS_DEV void ctr_add(long long *addr, long long v) { *addr += v; }
 ARTIS_DEV void int_add(int *addr, int v) { *addr += v; }
 ARTIS_DEV int int_fetch_add(int *addr, int v) {
@@ -427,8 +413,14 @@ ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
 }
 // stats::increment (stats.cc:151): per-thread tally instead of one global atomic per event
 ARTIS_DEV void stat_inc(Tally &t, int counter) { t.stats[counter]++; }
+// the FIRST fatal code of a timestep is the one reported (later ones are usually its consequences)
 ARTIS_DEV void fatal(const Ctx &c, int code) {
-  if (c.error_flag) *c.error_flag = code;
+  if (c.error_flag == nullptr) return;
+#ifdef __CUDA_ARCH__
+  atomicCAS(c.error_flag, 0, code);
+#else
+  if (*c.error_flag == 0) *c.error_flag = code;
+#endif
 }
 
 // stats::eventcounters (stats.h:48-84)

@@ -81,8 +81,7 @@ ARTIS_DEV void rlc_emiss_gamma(const Ctx &c, const ArtisPacket &p, const int mgi
     double heating_cont = ((meanf_sigma(xx) * c.cs.nnetot[mgi]) + sig_photo_electric(c, p, mgi) +
                            (sig_pair_prod(c, p, mgi) * (1. - (2.46636e+20 / p.nu_cmf))));
     heating_cont = heating_cont * p.e_rf * dist * (1. - (2. * dot3(vel_vec, p.dir) / CLIGHT));
-    est_add(&c.es.rpkt_emiss[mgi], 1.e-20 * heating_cont);
-    tl.estim_atomics++;
+    tl.estim_atomics += est_add(&c.es.rpkt_emiss[mgi], 1.e-20 * heating_cont);
   }
 }
 // gammapkt.cc:363-397: bisection on the partial Compton cross-section

@@ -239,8 +239,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         p.last_event = 10;
         p.type = ARTIS_TYPE_KPKT;
         end_packet = true;
-        est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
-        tl.estim_atomics++;
+        tl.estim_atomics += est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
         break;
       }
       case MA_INTERNALDOWNSAME: {  // macroatom.cc:174-220
@@ -291,8 +290,7 @@ ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
         p.last_event = 11;
         p.type = ARTIS_TYPE_KPKT;
         end_packet = true;
-        est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
-        tl.estim_atomics++;
+        tl.estim_atomics += est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
         break;
       }
       case MA_INTERNALDOWNLOWER: {  // macroatom.cc:766-813

@@ -21,8 +21,7 @@ ARTIS_DEV void bfest_sweep(const Ctx &c, const int tc, const int mgi, const doub
     double gcontr;
     kappa_bf_term(c, tc, i, knu, expfac, &gcontr);
     if (gcontr != 0.) {
-      est_add(&row[i], gcontr * factor);
-      tl.estim_atomics++;
+      tl.estim_atomics += est_add(&row[i], gcontr * factor);
     }
   }
 }
@@ -31,14 +30,14 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
   if (mgi == c.st.npts_model) return;
   const double distance_e_cmf = distance * p.e_cmf;
   const double nu = p.nu_cmf;
-  est_add(&c.es.J[mgi], distance_e_cmf);
-  est_add(&c.es.nuJ[mgi], distance_e_cmf * nu);
+  tl.estim_atomics += est_add(&c.es.J[mgi], distance_e_cmf);
+  tl.estim_atomics += est_add(&c.es.nuJ[mgi], distance_e_cmf * nu);
   // The reference adds globals::kappa_rpkt_cont[tid].ffheating and phixslist[tid].groundcont_gamma_contr, i.e.
   // whatever the last opacity evaluation of that host thread left behind -- in grey cells that is the opacity of
   // some other cell/packet. Here the scratch only counts when it was evaluated for this cell.
   const bool kv = k.valid && (k.mgi == mgi);
-  est_add(&c.es.ffheatingestimator[mgi], distance_e_cmf * (kv ? k.ffheating : 0.));
-  tl.estim_atomics += 3;
+  // grey cells (no valid opacity scratch) would add +0.0: skipped
+  if (kv) tl.estim_atomics += est_add(&c.es.ffheatingestimator[mgi], distance_e_cmf * k.ffheating);
   // radfield.cc:764-829 update_bfestimators (DETAILED_BF_ESTIMATORS_ON): every continuum whose cross-section table
   // covers nu gets gamma_contr[i] * distance_e_cmf / nu * doppler, where gamma_contr is the per-continuum scratch of the
   // last opacity evaluation (at k.nu). The reference keeps that scratch as an nbfcontinua-long array per host
@@ -59,10 +58,10 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
     const int binindex = radfield_select_bin(c, nu);
     if (binindex >= 0) {
       const size_t mgibinindex = (size_t)tabcell(c, mgi) * c.st.opt_radfieldbincount + binindex;
-      est_add(&c.es.radfieldbin_J_raw[mgibinindex], distance_e_cmf);
-      est_add(&c.es.radfieldbin_nuJ_raw[mgibinindex], distance_e_cmf * nu);
+      tl.estim_atomics += est_add(&c.es.radfieldbin_J_raw[mgibinindex], distance_e_cmf);
+      tl.estim_atomics += est_add(&c.es.radfieldbin_nuJ_raw[mgibinindex], distance_e_cmf * nu);
       int_add(&c.es.radfieldbin_contribcount[mgibinindex], 1);
-      tl.estim_atomics += 3;
+      tl.estim_atomics += 1;
     }
   }
   // without a valid opacity scratch for this cell every contribution below is +0.0: nothing to add (grey cells)
@@ -80,12 +79,10 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
           const double contr = k.gamma_contr[i];
           if (contr == 0.) continue;  // adds +0.0 to both estimators
           if (!c.st.opt_no_lut_photoion) {
-            est_add(&c.es.gammaestimator[ionestimindex], contr * distance_e_cmf_over_nu);
-            tl.estim_atomics++;
+            tl.estim_atomics += est_add(&c.es.gammaestimator[ionestimindex], contr * distance_e_cmf_over_nu);
           }
           if (!c.st.opt_no_lut_bfheating) {
-            est_add(&c.es.bfheatingestimator[ionestimindex], contr * distance_e_cmf * (1. - nu_edge / nu));
-            tl.estim_atomics++;
+            tl.estim_atomics += est_add(&c.es.bfheatingestimator[ionestimindex], contr * distance_e_cmf * (1. - nu_edge / nu));
           }
         }
       } else {
@@ -101,8 +98,7 @@ ARTIS_DEV void rlc_emiss_rpkt(const Ctx &c, const ArtisPacket &p, const double d
     get_velocity(p.pos, vel_vec, p.prop_time);
     double cont = (double)(c.cs.kappagrey[mgi] * c.cs.rho[mgi]);  // float product (grey_emissivities.cc:97)
     cont = cont * p.e_rf * dist * (1. - (2. * dot3(vel_vec, p.dir) / CLIGHT));
-    est_add(&c.es.rpkt_emiss[mgi], 1.e-20 * cont);
-    tl.estim_atomics++;
+    tl.estim_atomics += est_add(&c.es.rpkt_emiss[mgi], 1.e-20 * cont);
   }
 }
 

@@ -156,7 +156,6 @@ __global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_scatter(const Arti
 template <int KIND>
 __global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned long long *rngctr, artis::QueueView qv,
                                                    long long max_events) {
-  artis::est_private_begin(nullptr, 0u);
   artis::body_wavefront<KIND>(d_ctx, pkts, rngctr, qv, max_events);
 }
 // ---- barrier-free scheduler ------------------------------------------------------------------------------------------
@@ -446,12 +445,16 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
   st.mgi = 0;
   unsigned long long idle_since = 0ull;
   int refill_skip = 0;  // iterations left during which a partly busy warp does not look at its (just found empty) ring
-  est_private_begin(nullptr, 0u);
   if ((ROLES & (1u << KIND_RPKT_GREY)) != 0 && blockIdx.x == 0 && threadIdx.x == 0)
     *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
   long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
+  // where the warp's cycles go (lane k keeps kind k's event cycles; lane 0 the scheduler's own): a handful of clock reads
+  // per iteration against thousands of cycles of event code
+  long long cyc_kind = 0, cyc_refill = 0, cyc_push = 0, cyc_idle = 0;
+  int last_active = -1;  // active-packet count at the last idle poll: the hang guard looks for progress, not for work
   while (true) {
     __syncwarp(full);
+    const long long tick0 = clock64();
     const unsigned need = __ballot_sync(full, !have);
     if (need != full && (refill_skip > 0 || __popc(need) < REFILL_MIN)) {
       if (refill_skip > 0) refill_skip--;
@@ -486,12 +489,19 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
           unsigned long long now = 0ull;
           if (lane == 0) now = global_ns();
           now = __shfl_sync(full, now, 0);
-          if (idle_since == 0ull) idle_since = now;
+          // Hang guard: the timestep is given up (code 900) only when the number of active packets has not changed for
+          // the whole timeout -- a warp that merely finds its rings empty while a few long histories finish elsewhere
+          // (thick grey cells, virtual-packet ray traces) keeps waiting.
+          if (idle_since == 0ull || left != last_active) {
+            idle_since = now;
+            last_active = left;
+          }
           if (now - idle_since > idle_timeout_ns) {  // a lost packet would otherwise hang the device
             if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
             break;
           }
           __nanosleep(1000);
+          cyc_idle += clock64() - tick0;
           continue;
         }
         role = best_kind;
@@ -544,6 +554,8 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
       refill_skip = (take_a + take_b < want) ? REFILL_BACKOFF : 0;
     }
     __syncwarp(full);
+    const long long tick1 = clock64();
+    cyc_refill += tick1 - tick0;
     bool done = false;
     int k2 = -1;
     {
@@ -629,6 +641,8 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
       }
     }
     __syncwarp(full);
+    const long long tick2 = clock64();
+    if (lane == role) cyc_kind += tick2 - tick1;
     if (__ballot_sync(full, done) != 0u) {
 #pragma unroll
       for (int kk = 0; kk < NRING; kk++) {
@@ -652,12 +666,19 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
         if (before > n0 / 100 && after <= n0 / 100) c.es.counters[ARTIS_CTR_DRAIN_NS_1PCT] = now;
         if (after <= 0) c.es.counters[ARTIS_CTR_DRAIN_NS_DONE] = now;
       }
+      cyc_push += clock64() - tick2;
     }
   }
   tally_flush(c, tl);
   if (lane < NKIND && fill_iters > 0) {
     ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + lane], fill_iters);
     ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + lane], fill_lanes);
+    ctr_add(&c.es.counters[ARTIS_CTR_WARP_CYCLES0 + lane], cyc_kind);
+  }
+  if (lane == 0) {
+    ctr_add(&c.es.counters[ARTIS_CTR_REFILL_CYCLES], cyc_refill);
+    ctr_add(&c.es.counters[ARTIS_CTR_PUSH_CYCLES], cyc_push);
+    ctr_add(&c.es.counters[ARTIS_CTR_IDLE_CYCLES], cyc_idle);
   }
 }
 
@@ -665,7 +686,43 @@ __global__ void k_bucket_hist(ArtisPacket *pkts, unsigned long long *rngctr, int
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     artis::body_bucket_hist(d_ctx, pkts, rngctr, i, counts);
 }
-__global__ void k_bucket_scan(int *counts, int *kind_sizes) { artis::body_bucket_scan(d_ctx, counts, kind_sizes); }
+// exclusive prefix sum over the (kind, cell) counts, one 1024-thread block per kind (a 3D model has a model cell per
+// propagation cell: 1e6 counts per kind); also the size of each kind's queue
+__global__ void __launch_bounds__(1024) k_bucket_scan(int *counts, int *kind_sizes) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  const int per = d_ctx.st.npts_model + 1;
+  int *row = counts + (size_t)blockIdx.x * per;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int base = 0; base < per; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < per ? row[i] : 0;
+    int x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int t = warp_tot[lane];
+      for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, t, d);
+        if (lane >= d) t += y;
+      }
+      warp_tot[lane] = t;
+    }
+    __syncthreads();
+    const int before = carry + (w > 0 ? warp_tot[w - 1] : 0) + x - v;
+    if (i < per) row[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) kind_sizes[blockIdx.x] = carry;
+}
 __global__ void k_bucket_scatter(const ArtisPacket *pkts, int n, int *offsets, int *const *queues) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     artis::body_bucket_scatter(d_ctx, pkts, i, offsets, queues);
@@ -714,6 +771,7 @@ cudaStream_t g_stream2 = nullptr;
 cudaEvent_t g_ev_fork = nullptr, g_ev_join = nullptr;
 double *g_stepstate = nullptr;
 bool g_persistent_warmed = false;
+unsigned long long g_idle_timeout_ns = 20ull * 1000000000ull;  // hang guard of the persistent kernel (artis_gpu_set_tuning)
 int g_nbfcontinua_ground = 0;
 double *g_est_block = nullptr;
 size_t g_est_ndoubles = 0;
@@ -847,7 +905,7 @@ void be_run_escaped_scatter(const ArtisPacket *p, long long n, unsigned char *re
 }
 void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
   k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, r, n, buckets);
-  k_bucket_scan<<<1, 1, 0, g_stream>>>(buckets, kind_sizes);
+  k_bucket_scan<<<artis::NKIND, 1024, 0, g_stream>>>(buckets, kind_sizes);
   k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, buckets, queues);
 }
 void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueView &qv, int kind, long long maxev, int block) {
@@ -896,7 +954,7 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
   pv.stepstate = g_stepstate;
   pv.kstride = kstride;
   pv.offload_kappa = two ? 1 : 0;
-  const unsigned long long timeout = 20ull * 1000000000ull;
+  const unsigned long long timeout = g_idle_timeout_ns;
   if (!g_persistent_warmed) {
     // First launch of each persistent kernel with nothing to do (n_active == 0: every warp leaves at once). A first
     // launch can make the driver grow the local-memory pool, which waits for running kernels -- with the other
@@ -936,6 +994,7 @@ void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, 
 void be_set_scheduler_kernels(int n) {
   if (n == 1 || (n == 2 && g_blocks_light >= 1)) g_scheduler_kernels = n;
 }
+void be_set_idle_timeout_ms(long long ms) { g_idle_timeout_ns = (unsigned long long)ms * 1000000ull; }
 void be_set_estimator_block(double *block, size_t ndoubles) {
   g_est_block = block;
   g_est_ndoubles = ndoubles;
@@ -1011,21 +1070,37 @@ int be_comm_init(const char *id, int rank, int nranks, std::string *err) {
   g_nccl.nranks = nranks;
   return ARTIS_OK;
 }
-// one sum all-reduce over the FP64 estimator block, one over the int64 counters and one over the int32 line
-// counters, issued on the transport stream right behind the last transport kernel
+// the exchange step of a timestep: sum all-reduces over the FP64 estimator block, the int64 counters and the int32 line
+// counters as ONE NCCL group (a single launch), issued on the transport stream right behind the last transport kernel;
+// its device time is kept for artis_gpu_last_timings()[5]
+double g_allreduce_ms = 0.;
 int be_comm_allreduce(double *d, size_t nd, long long *l, size_t nl, int *i, size_t ni, std::string *err) {
+  g_allreduce_ms = 0.;
   if (g_nccl.comm == nullptr || g_nccl.nranks <= 1) return ARTIS_OK;  // single shard: nothing to reduce
   const int ncclSum = 0, ncclInt32 = 2, ncclInt64 = 4, ncclFloat64 = 8;
-  int rc = g_nccl.AllReduce(d, d, nd, ncclFloat64, ncclSum, g_nccl.comm, g_stream);
+  auto group_start = (int (*)())dlsym(g_nccl.h, "ncclGroupStart");
+  auto group_end = (int (*)())dlsym(g_nccl.h, "ncclGroupEnd");
+  note(cudaEventRecord(g_ev0, g_stream), "event record");
+  int rc = group_start ? group_start() : 0;
+  if (rc == 0) rc = g_nccl.AllReduce(d, d, nd, ncclFloat64, ncclSum, g_nccl.comm, g_stream);
   if (rc == 0 && nl > 0) rc = g_nccl.AllReduce(l, l, nl, ncclInt64, ncclSum, g_nccl.comm, g_stream);
   if (rc == 0 && ni > 0) rc = g_nccl.AllReduce(i, i, ni, ncclInt32, ncclSum, g_nccl.comm, g_stream);
+  if (group_end) {
+    const int rc2 = group_end();
+    if (rc == 0) rc = rc2;
+  }
   if (rc != 0) {
     *err = std::string("ncclAllReduce: ") + g_nccl.GetErrorString(rc);
     return ARTIS_ERR_NCCL;
   }
-  note(cudaStreamSynchronize(g_stream), "allreduce sync");
+  float ms = 0.f;
+  note(cudaEventRecord(g_ev1, g_stream), "event record");
+  note(cudaEventSynchronize(g_ev1), "allreduce sync");
+  note(cudaEventElapsedTime(&ms, g_ev0, g_ev1), "event elapsed");
+  g_allreduce_ms = ms;
   return ARTIS_OK;
 }
+double be_last_allreduce_ms() { return g_allreduce_ms; }
 
 }  // namespace
 

@@ -105,8 +105,8 @@ class Transport:
         return out
 
     def last_timings(self):
-        ms = (C.c_double * 5)()
-        n = self.lib.artis_gpu_last_timings(ms, 5)
+        ms = (C.c_double * 6)()
+        n = self.lib.artis_gpu_last_timings(ms, 6)
         return [ms[i] for i in range(n)]
 
     def set_tuning(self, max_events_per_pass=0, block_threads=0):

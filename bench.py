@@ -38,14 +38,16 @@ BENCH_TS = 25
 REF_EXE = os.path.join(REPO, "oracle", "_ref", "classic", "sn3d_ref")
 WORKLOAD_NAME = ("classicmode W7-like 1D model (tests/classicmode_inputfiles, artisoptions_classic.h, 100^3 grid), "
                  "synthetic atomic data {nlines} lines / {nbf} bf continua / {nlev} levels, timestep {ts}")
-FALLBACK_FIXTURE = "classic_nogrey_ts12.npz"
+FIXTURE = None  # --workload fixture: a committed golden fixture instead of the named workload (smoke runs only)
 
 
 def select_workload(name):
     """--workload nebular: BASELINE.json config 2, the one-zone nebular NLTE model (tests/nebularonezone_inputfiles,
     artisoptions_nltenebular.h with the overrides of tests/setup_nebularonezone.sh, 50^3 grid) at timestep 8; the
-    default stays the classic-mode model, whose timestep is the interaction-rich one the metric is about."""
-    global BENCH_RUN, BENCH_TS, REF_EXE, WORKLOAD_NAME, FALLBACK_FIXTURE
+    default stays the classic-mode model, whose timestep is the interaction-rich one the metric is about.
+    --workload fixture: the 16^3-grid parity fixture tests/golden/classic_nogrey_ts12.npz; never the default, and its
+    line says what it is (it has no reference arm)."""
+    global BENCH_RUN, BENCH_TS, REF_EXE, WORKLOAD_NAME, FIXTURE
     if name == "nebular":
         BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_neb")
         BENCH_TS = 8
@@ -53,24 +55,37 @@ def select_workload(name):
         WORKLOAD_NAME = ("nebular one-zone NLTE model (tests/nebularonezone_inputfiles, artisoptions_nltenebular.h with the "
                          "overrides of tests/setup_nebularonezone.sh, 50^3 grid), synthetic atomic data {nlines} lines / "
                          "{nbf} bf continua / {nlev} levels, timestep {ts}")
-        FALLBACK_FIXTURE = "nebular_nlte_ts8.npz"
+    elif name == "fixture":
+        FIXTURE = "classic_nogrey_ts12.npz"
 
 
 # ---------------------------------------------------------------------------------------------------------------------
 def load_workload():
-    """(static, cell, packets_pre, name). The bench snapshot lives under oracle/_ref (git-ignored, travels to the GPU
-    box); if it is missing the committed golden fixture is used and the workload name says so."""
+    """(static, cell, packets_pre, name). The bench snapshot lives under oracle/_ref/runs (git-ignored; made by
+    __graft_entry__.build() where /root/reference exists and carried to the GPU box with the working tree). A missing
+    snapshot is an error: the bench never measures another workload under the named one's flag."""
     from artis_b200 import snapshot
+    if FIXTURE is not None:
+        sys.path.insert(0, os.path.join(REPO, "tests"))
+        import goldenlib
+        fx = goldenlib.load_fixture(FIXTURE)
+        return fx["static"], fx["cell"], fx["pre"], f"parity fixture tests/golden/{FIXTURE} (16^3 grid; --workload fixture)"
     snap = os.path.join(BENCH_RUN, f"snap_ts{BENCH_TS}.bin")
-    if os.path.exists(snap):
-        s = snapshot.load(snap)
-        st, cs = snapshot.static_tables(s), snapshot.cell_state(s)
-        name = WORKLOAD_NAME.format(nlines=st["nlines"], nbf=st["nbfcontinua"], nlev=st["nlevels_total"], ts=BENCH_TS)
-        return st, cs, s["packets.pre"].copy(), name
-    sys.path.insert(0, os.path.join(REPO, "tests"))
-    import goldenlib
-    fx = goldenlib.load_fixture(FALLBACK_FIXTURE)
-    return fx["static"], fx["cell"], fx["pre"], f"FALLBACK golden fixture {FALLBACK_FIXTURE} (bench snapshot missing)"
+    if not os.path.exists(snap):
+        raise SystemExit(f"bench.py: the workload snapshot {snap} is missing. It is a run of the unmodified reference made by "
+                         "__graft_entry__.build() (oracle/tools/make_bench_run.sh / make_bench_neb.sh) where /root/reference "
+                         "exists; run build() there before the bench. (`--workload fixture` runs the small parity fixture "
+                         "instead and says so.)")
+    s = snapshot.load(snap)
+    st, cs = snapshot.static_tables(s), snapshot.cell_state(s)
+    name = WORKLOAD_NAME.format(nlines=st["nlines"], nbf=st["nbfcontinua"], nlev=st["nlevels_total"], ts=BENCH_TS)
+    return st, cs, s["packets.pre"].copy(), name
+
+
+def workload_key(name, packets):
+    """identifies (workload, packets per GPU): the key under which an ncu DRAM-traffic capture is filed"""
+    import hashlib
+    return hashlib.sha1(f"{name}|{int(packets)}".encode()).hexdigest()[:16]
 
 
 def replicate(pre, P, rank, step):
@@ -86,14 +101,20 @@ def replicate(pre, P, rank, step):
     return out
 
 
-def measured_traffic(packets):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one transport launch from the committed ncu capture, when that
-    capture was taken at this packet count; None otherwise (the number is not measured under this run)"""
+TRAFFIC_FILE = os.path.join("profiles", "r2_traffic.json")
+
+
+def measured_traffic(name, packets):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one transport launch from the committed ncu capture of THIS
+    workload at THIS packet count (matched on workload_key); None otherwise -- the number is never borrowed from a
+    capture of something else"""
     try:
-        t = json.load(open(os.path.join(REPO, "profiles", "r1_end_traffic.json")))
-        return float(t["dram_bytes_per_launch"]) if int(t["packets_per_gpu"]) == int(packets) else None
+        for t in json.load(open(os.path.join(REPO, TRAFFIC_FILE))):
+            if t.get("workload_key") == workload_key(name, packets):
+                return float(t["dram_bytes_per_launch"])
     except Exception:
-        return None
+        pass
+    return None
 
 
 def algorithmic_bytes(ctr):
@@ -139,7 +160,8 @@ def run_reference(nproc, steps, warmup):
     GSL shim) on the host cores: `nproc` independent single-thread processes (= MPI ranks of the reference: packets
     sharded, everything else replicated; MPI itself is not in the image) each transporting the workload timestep from
     the same checkpoint with its own seed. Returns (interactions, seconds, sample description)."""
-    if not (os.path.exists(REF_EXE) and os.path.exists(os.path.join(BENCH_RUN, f"gridsave_ts{BENCH_TS}.tmp"))):
+    if FIXTURE is not None or not (os.path.exists(REF_EXE) and
+                                   os.path.exists(os.path.join(BENCH_RUN, f"gridsave_ts{BENCH_TS}.tmp"))):
         return None
     keep = ("adata.txt", "transitiondata.txt", "phixsdata_v2.txt", "compositiondata.txt", "model.txt", "abundances.txt",
             "input.txt", "ratecoeff.dat", "bflist.dat", "recombrates.txt", f"gridsave_ts{BENCH_TS}.tmp",
@@ -182,7 +204,7 @@ def run_reference(nproc, steps, warmup):
                 tot_inter += inter
                 tot_sec += sec
     sample = (f"{nproc} concurrent single-thread sn3d_ref processes x {npk} packets, timestep {BENCH_TS} of the workload "
-              f"run, update_packets call only (std::chrono in oracle/refglue/hook.cc), {steps} step(s)")
+              f"run, update_packets call only (std::chrono in oracle/refglue/hook.cc), {steps} step(s) after {warmup} warm-up")
     return tot_inter, tot_sec, sample
 
 
@@ -204,7 +226,7 @@ def main():
     ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
     ap.add_argument("--scheduler-kernels", type=int, default=0, choices=(0, 1, 2),
                     help="1: one persistent kernel with every role, 2: light + heavy kernels side by side (0: library default)")
-    ap.add_argument("--workload", default="classic", choices=["classic", "nebular"])
+    ap.add_argument("--workload", default="classic", choices=["classic", "nebular", "fixture"])
     a = ap.parse_args()
     select_workload(a.workload)
     rank = int(os.environ.get("RANK", "0"))
@@ -217,17 +239,17 @@ def main():
         st, cs, pre, wname = load_workload()
         cores = host_cores()
         res = run_reference(cores, max(1, a.steps), min(a.warmup, 1))
-        if res is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/classic/sn3d_ref or its checkpoint is "
-                              "missing (built from /root/reference by `make -C oracle ref`)"}))
-            return 0
+        kind = "reference"
+        if res is None:  # oracle/_ref did not travel: the CPU restatement of the path, one process per core
+            res = run_port(st, cs, pre, cores, max(1, a.steps), min(a.warmup, 1))
+            kind = "port"
         inter, sec, sample = res
         v = inter / sec
         line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": 1e3 * sec / max(1, a.steps), "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
                 "config": {"workload": wname, "packets_per_rank": int(pre.size), "ranks": cores},
-                "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+                "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         print(json.dumps(line))
@@ -251,19 +273,19 @@ def main():
     if a.scheduler_kernels:
         T.set_tuning(block_threads=-3 if a.scheduler_kernels == 1 else -4)
     precompute_ms = T.last_timings()[3]
-    # the contiguous FP64 estimator block as a torch tensor (for the NCCL all-reduce that replaces
-    # mpi_reduce_estimators, sn3d.cc:316-384)
     ptr, ndoubles = T.estimator_block()
-
-    class _Blk:
-        __cuda_array_interface__ = {"shape": (ndoubles,), "typestr": "<f8", "data": (ptr, False), "version": 2}
-    est_t = torch.as_tensor(_Blk(), device=torch.device("cuda", local_rank))
+    if world > 1:
+        # the exchange step goes through the library's own NCCL communicator (artis_gpu_comm_init /
+        # artis_gpu_reduce_estimators, the replacement of mpi_reduce_estimators, sn3d.cc:316-384); torch.distributed only
+        # hands the 128-byte NCCL id round and takes the max over ranks of the timings
+        ids = [T.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        T.comm_init(ids[0], rank, world)
     # pinned host staging for the end-to-end leg
     nbytes = P * 304
     pinned = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
     from artis_b200 import abi
     host_pk = pinned.numpy().view(abi.PACKET_DTYPE)
-    est_host = torch.empty(ndoubles, dtype=torch.float64, pin_memory=True)
 
     def barrier():
         torch.cuda.synchronize()
@@ -279,14 +301,11 @@ def main():
         barrier()
         T.transport_resident()
         ms = T.last_timings()[0]
+        ar = 0.0
         if world > 1:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            dist.all_reduce(est_t)
-            e1.record()
-            e1.synchronize()
-            ms += e0.elapsed_time(e1)
-        return ms
+            T.reduce_estimators()          # one NCCL group on the transport stream, timed with CUDA events in the library
+            ar = T.last_timings()[5]
+        return ms + ar, ar
 
     for w in range(a.warmup):
         one_step(1000 + w, False)
@@ -294,10 +313,12 @@ def main():
     sampler.start()
     launches0 = T.launch_count()
     tot_ms = 0.0
-    ctr_sum = np.zeros(64, dtype=np.int64)
+    ctr_sum = np.zeros(96, dtype=np.int64)
     kernel_ms = 0.0
+    allreduce_ms = 0.0
     for s in range(a.steps):
-        ms = one_step(s, True)
+        ms, ar = one_step(s, True)
+        allreduce_ms += ar
         kernel_ms += T.last_timings()[2]
         c = T.download_estimators()["counters"]
         if world > 1:
@@ -312,14 +333,10 @@ def main():
     for _ in range(3):
         lc_out, _, _ = T.bin_escaped(tmax_run, world, 1000, allreduce=False)
     bin_ms = T.last_timings()[4]
-    inter_rank = float(ctr_sum[45])
-    alg_bytes = float(algorithmic_bytes(ctr_sum))
-    if world > 1:
-        t = torch.tensor([inter_rank], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t)
-        inter_all = float(t.item())
-    else:
-        inter_all = inter_rank
+    # with N > 1 the library's all-reduce has summed the work counters over the shards as well (they ride in the same
+    # NCCL group as the estimators): every rank holds the job's totals
+    inter_all = float(ctr_sum[45])
+    alg_bytes = float(algorithmic_bytes(ctr_sum)) / world  # of this rank's kernel (equal shards)
     value = inter_all / (tot_ms * 1e-3)
 
     # end-to-end through the C ABI with host buffers
@@ -331,8 +348,8 @@ def main():
         t0 = time.perf_counter()
         T.update_packets(host_pk)                      # H2D packets, all passes, D2H packets
         if world > 1:
-            dist.all_reduce(est_t)
-        est_host.copy_(est_t, non_blocking=False)      # D2H of the step's result (the estimator block)
+            T.reduce_estimators()
+        T.download_estimators()                        # D2H of the step's result (the estimator blocks)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if world > 1:
@@ -364,53 +381,73 @@ def main():
                            "atomic data replicated, one estimator all-reduce per step",
                            "l2": "per-step working set (304 B x packets + per-cell tables) exceeds the 126 MB L2",
                            "s_per_timestep": tot_ms / a.steps * 1e-3, "cell_precompute_ms": precompute_ms,
-                           "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps, "handoffs_per_step": float(ctr_sum[50]) / a.steps,
+                           "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps / world, "handoffs_per_step": float(ctr_sum[50]) / a.steps / world,
                            "drain_ms_to_10pct_1pct_done": [round(float(c[61 + i]) * 1e-6, 1) for i in range(3)],
-                           "warp_iters_by_kind": [float(x) / a.steps for x in ctr_sum[51:56]],
-                           "mean_busy_lanes_by_kind": [round(float(ctr_sum[56 + i]) / max(float(ctr_sum[51 + i]), 1.0), 2) for i in range(5)],
-                           "events_per_s": float(ctr_sum[49]) * world / (tot_ms * 1e-3),
+                           "warp_iters_by_kind": [float(x) / a.steps / world for x in ctr_sum[64:72]],
+                           "mean_busy_lanes_by_kind": [round(float(ctr_sum[72 + i]) / max(float(ctr_sum[64 + i]), 1.0), 2) for i in range(8)],
+                           "warp_Mcycles_by_kind": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[80:88]],
+                           "warp_Mcycles_refill_push_idle": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[88:91]],
+                           "allreduce_ms_per_step": allreduce_ms / a.steps,
+                           "estimator_block_bytes": int(ndoubles * 8),
+                           "events_per_s": float(ctr_sum[49]) / (tot_ms * 1e-3),
                            "bin_escaped_ms": bin_ms, "bin_escaped_record_GBps": P * 304 / (bin_ms * 1e-3) / 1e9 if bin_ms > 0 else None},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": measured_traffic(P),
+                             "frac": achieved / peak, "traffic": measured_traffic(wname, P),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6537.6",
                              "kernel": "k_transport_persistent", "launches_per_step": 1,
                              "algorithmic_bytes_per_launch": alg_bytes / a.steps,
-                             "traffic_source": "profiles/r1_end_traffic.json (ncu dram bytes per launch at this packet "
-                                               "count; null at other counts)"},
+                             "traffic_source": TRAFFIC_FILE + " (ncu dram bytes per launch, filed under the workload key; "
+                                               "null when no capture of this workload and packet count is committed)",
+                             "workload_key": workload_key(wname, P)},
                 "e2e": {"value": e2e_inter / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                         "d2h_bytes_per_step": nbytes + ndoubles * 8},
                 "gpu_launches": int(launches), "clocks": sampler.summary()}
         if world == 1 and a.cpu_baseline != "off":
-            res = run_reference(1, 1, 0)
-            if res is not None:
-                inter, sec, sample = res
-                line["cpu_baseline"] = {"value": inter / sec, "unit": UNIT, "cores": 1, "kind": "reference",
-                                        "sample": sample}
-            else:
-                line["cpu_baseline"] = cpu_port_baseline(st, cs, pre)
+            # the reference's own update_packets on every host core of this box: one warm-up step, one timed step
+            cores = host_cores()
+            res = run_reference(cores, 1, 1)
+            kind = "reference"
+            if res is None:
+                res = run_port(st, cs, pre, cores, 1, 0)
+                kind = "port"
+            inter, sec, sample = res
+            line["cpu_baseline"] = {"value": inter / sec, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
-def cpu_port_baseline(st, cs, pre):
-    """fallback when oracle/_ref did not travel: the oracle's CPU restatement on one core"""
+def _port_worker(args):
+    st, cs, pre, seed = args
     from artis_b200.transport import Transport
-    lib = os.path.join(REPO, "oracle", "libartis_oracle.so")
-    if not os.path.exists(lib):
-        subprocess.run(["make", "-C", os.path.join(REPO, "oracle"), "restatement"], check=True,
-                       stdout=subprocess.DEVNULL)
-    O = Transport(lib)
-    O.init(st)
+    O = Transport(os.path.join(REPO, "oracle", "libartis_oracle.so"))
+    O.init(st, seed=seed)
     O.upload_cellstate(cs)
     O.zero_estimators()
     pk = pre.copy()
     t0 = time.perf_counter()
     O.update_packets(pk)
-    dt = time.perf_counter() - t0
-    return {"value": float(pk["interactions"].sum()) / dt, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"oracle restatement, {pk.size} packets, one step"}
+    return float(pk["interactions"].sum()), time.perf_counter() - t0
+
+
+def run_port(st, cs, pre, nproc, steps, warmup):
+    """Stand-in for run_reference when oracle/_ref did not travel: the oracle's CPU restatement of the path
+    (oracle/libartis_oracle.so), `nproc` single-thread processes each transporting the workload's packets with its own
+    seed. Returns (interactions, seconds, sample description)."""
+    import multiprocessing as mp
+    lib = os.path.join(REPO, "oracle", "libartis_oracle.so")
+    if not os.path.exists(lib):
+        subprocess.run(["make", "-C", os.path.join(REPO, "oracle"), "restatement"], check=True, stdout=subprocess.DEVNULL)
+    tot_inter, tot_sec = 0.0, 0.0
+    with mp.get_context("spawn").Pool(nproc) as pool:
+        for it in range(warmup + steps):
+            rows = pool.map(_port_worker, [(st, cs, pre, 900001 + 7919 * (it * nproc + r)) for r in range(nproc)])
+            if it >= warmup:
+                tot_inter += sum(r[0] for r in rows)
+                tot_sec += max(r[1] for r in rows)
+    return tot_inter, tot_sec, (f"oracle restatement (CPU port), {nproc} concurrent single-thread processes x {pre.size} "
+                                f"packets, {steps} step(s) after {warmup} warm-up")
 
 
 if __name__ == "__main__":

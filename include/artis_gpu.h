@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define ARTIS_GPU_ABI_VERSION 5
+#define ARTIS_GPU_ABI_VERSION 6
 
 enum artis_gpu_error {
   ARTIS_OK = 0,
@@ -140,13 +140,20 @@ enum {
   ARTIS_CTR_SOFT_REPAIRS = 47,    /* clamps of SURVEY Q6 applied */
   ARTIS_CTR_KAPPA_EVALS = 48,     /* calculate_kappa_rpkt_cont recomputes (cache misses) */
   ARTIS_CTR_PACKET_UPDATES = 49,  /* do_packet calls */
-  ARTIS_CTR_HANDOFFS = 50,        /* packets handed back to their ring in mid-visit by a consolidating warp */
-  ARTIS_CTR_WARP_ITERS0 = 51,     /* [51,56): scheduler iterations a warp ran in kind 0..4 */
-  ARTIS_CTR_BUSY_LANES0 = 56,     /* [56,61): lanes holding a packet, summed over those iterations */
+  ARTIS_CTR_HANDOFFS = 50,        /* packets handed from one scheduler ring to another in mid-timestep */
+  /* [51,61): unused since ABI 6 (were the per-kind scheduler statistics of five kinds) */
   ARTIS_CTR_DRAIN_NS_10PCT = 61,  /* ns from the transport launch until 10% / 1% / none of the packets are still active */
   ARTIS_CTR_DRAIN_NS_1PCT = 62,
   ARTIS_CTR_DRAIN_NS_DONE = 63,
-  ARTIS_CTR_COUNT = 64
+  /* scheduler statistics per event kind k = 0..7 (kernels.cuh: 0 macro-atom events / k-packets, 1 r-packet in a non-grey
+   * cell, 2 gamma, 3 pellets, 4 r-packet in a grey or empty cell, 5 macro-atom jumps within an ion) */
+  ARTIS_CTR_WARP_ITERS0 = 64,     /* [64,72): scheduler iterations a warp ran in kind k */
+  ARTIS_CTR_BUSY_LANES0 = 72,     /* [72,80): lanes holding a packet, summed over those iterations */
+  ARTIS_CTR_WARP_CYCLES0 = 80,    /* [80,88): SM cycles (clock64) the warps spent in the event code of kind k */
+  ARTIS_CTR_REFILL_CYCLES = 88,   /* ... claiming ring entries and loading packets */
+  ARTIS_CTR_PUSH_CYCLES = 89,     /* ... storing packets and pushing them on the ring of their next kind */
+  ARTIS_CTR_IDLE_CYCLES = 90,     /* ... waiting with every ring of their roles empty */
+  ARTIS_CTR_COUNT = 96
 };
 
 /* ---- life cycle --------------------------------------------------------------------------------------- */
@@ -174,14 +181,17 @@ int artis_gpu_transport_resident(int nts);
 int artis_gpu_packets_download(ArtisPacket *host_packets, int npkts);
 /* milliseconds spent in the kernels of the last transport_resident call (CUDA events on the library's stream):
  * [0] total, [1] bucketing, [2] transport kernels, [3] cell_precompute of the last upload_cellstate, [4] the last
- * artis_gpu_bin_escaped kernel; returns number of values written */
+ * artis_gpu_bin_escaped kernel, [5] the NCCL group of the last artis_gpu_reduce_estimators / all-reduced bin_escaped;
+ * returns number of values written */
 int artis_gpu_last_timings(double *ms, int n);
 /* Introspection for the measurement harness: kernels launched by the library since init, and bytes held by the
  * per-cell tables that replace the reference's cellhistory cache. */
 long long artis_gpu_launch_count(void);
 size_t artis_gpu_table_bytes(void);
 /* Tunables (0 keeps the default): events a thread may process before it yields its packet for re-bucketing;
- * threads per block. */
+ * threads per block. block_threads <= -1000 sets the hang guard of the persistent scheduler instead: the timestep is
+ * given up with ARTIS_ERR_TRANSPORT (device code 900) when no packet has finished for (-1000 - block_threads) seconds
+ * (default 20; the guard looks at progress of the whole timestep, not at how long one warp has been idle). */
 int artis_gpu_set_tuning(int max_events_per_pass, int block_threads);
 
 /* ---- estimators --------------------------------------------------------------------------------------- */

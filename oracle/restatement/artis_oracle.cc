@@ -83,6 +83,8 @@ bool be_run_persistent(ArtisPacket *, unsigned long long *, int *, int, unsigned
 void be_fill_bytes(void *p, int byte, size_t n) { memset(p, byte, n); }
 void be_set_estimator_block(double *, size_t) {}
 void be_set_scheduler_kernels(int) {}
+void be_set_idle_timeout_ms(long long) {}
+double be_last_allreduce_ms() { return 0.; }
 void be_run_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   for (int i = 0; i < n; i++) artis::body_probe_boundary(g_ctx, p, i, a, b, c);
 }
