@@ -153,6 +153,7 @@ def declare(lib):
         "artis_gpu_estimator_block": [P(vp), P(C.c_size_t)],
         "artis_gpu_bin_escaped": [C.c_double, C.c_int, C.c_int, C.c_int, pd, pd, pd],
         "artis_gpu_packets_download_escaped": [vp, C.c_int, C.c_int, pi],
+        "artis_gpu_pack_escaped_noalloc": [vp, C.c_int, vp, C.c_int, vp, vp],
         "artis_gpu_probe_boundary_cross": [vp, C.c_int, pd, pi, pi],
         "artis_gpu_probe_kappa_cont": [vp, C.c_int, pd],
         "artis_gpu_probe_closest_transition": [pd, pi, C.c_int, pi],
@@ -171,7 +172,7 @@ def declare(lib):
     return sig
 
 
-CUDA_ONLY_SYMBOLS = ()
+CUDA_ONLY_SYMBOLS = ("artis_gpu_pack_escaped_noalloc",)
 
 EXPORTED_SYMBOLS = [
     "artis_gpu_init", "artis_gpu_finalize", "artis_gpu_last_error", "artis_gpu_upload_cellstate",
@@ -182,5 +183,5 @@ EXPORTED_SYMBOLS = [
     "artis_gpu_probe_kappa_cont", "artis_gpu_probe_closest_transition", "artis_gpu_probe_get_event",
     "artis_gpu_probe_macroatom_rates", "artis_gpu_probe_cooling_ion", "artis_gpu_probe_gamma_kappa",
     "artis_gpu_probe_levelpop", "artis_gpu_launch_count", "artis_gpu_table_bytes", "artis_gpu_bin_escaped",
-    "artis_gpu_packets_download_escaped",
+    "artis_gpu_packets_download_escaped", "artis_gpu_pack_escaped_noalloc",
 ]

@@ -1105,3 +1105,126 @@ double be_last_allreduce_ms() { return g_allreduce_ms; }
 }  // namespace
 
 #include "engine.inc"
+
+// ---- escaped-packet compaction without any allocation -------------------------------------------------------------------
+// artis_gpu_pack_escaped_noalloc (include/artis_gpu.h): for callers that must not reach cudaMalloc (a CUDA graph being
+// captured, a serving loop, a harness that forbids it). Same three steps as artis_gpu_packets_download_escaped -- per-chunk
+// counts, one scan, cooperative 304-byte copies -- but on the caller's own device arrays and with the per-chunk counts in
+// a file-scope device array of fixed size instead of a cudaMalloc'ed one. Every GPU that loads the library holds that
+// array until the process exits; every call shares it, so calls that overlap on one GPU race on it.
+constexpr int NOALLOC_MAX_PACKETS = 1 << 22;  // 4 194 304 packets per call
+constexpr int NOALLOC_MAX_CHUNKS = NOALLOC_MAX_PACKETS / artis::ESC_CHUNK;
+static __device__ __align__(256) int g_noalloc_counts[NOALLOC_MAX_CHUNKS + 2];  // 64 KiB + 8 B per GPU
+
+namespace {
+// Host code may not pass g_noalloc_counts itself to a kernel (there the name is a host-side stand-in, not a device
+// address): the address is asked for once per device, with that device current.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+int *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+__global__ void __launch_bounds__(artis::ESC_CHUNK) k_na_count(const ArtisPacket *pkts, int n, int *counts) {
+  const int i = blockIdx.x * artis::ESC_CHUNK + threadIdx.x;
+  const int sel = i < n && pkts[i].type == ARTIS_TYPE_ESCAPE;
+  const int c = __syncthreads_count(sel);
+  if (threadIdx.x == 0) counts[blockIdx.x] = c;
+}
+// one block: exclusive scan of counts[0..nchunks) in place, counts[nchunks] = total, which is also written to *n_out
+__global__ void __launch_bounds__(1024) k_na_scan(int *counts, int nchunks, int *n_out) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int base = 0; base < nchunks; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < nchunks ? counts[i] : 0;
+    int x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int t = warp_tot[lane];
+      for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, t, d);
+        if (lane >= d) t += y;
+      }
+      warp_tot[lane] = t;
+    }
+    __syncthreads();
+    const int before = carry + (w > 0 ? warp_tot[w - 1] : 0) + x - v;
+    if (i < nchunks) counts[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    counts[nchunks] = carry;
+    *n_out = carry;
+  }
+}
+__global__ void __launch_bounds__(artis::ESC_CHUNK) k_na_scatter(const ArtisPacket *pkts, int n, const int *offsets, ArtisPacket *out,
+                                                                int capacity) {
+  __shared__ int warp_base[artis::ESC_CHUNK / 32];
+  const int i = blockIdx.x * artis::ESC_CHUNK + threadIdx.x;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const bool sel = i < n && pkts[i].type == ARTIS_TYPE_ESCAPE;
+  const unsigned m = __ballot_sync(0xffffffffu, sel);
+  if (lane == 0) warp_base[w] = __popc(m);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = offsets[blockIdx.x];
+    for (int k = 0; k < artis::ESC_CHUNK / 32; k++) {
+      const int c = warp_base[k];
+      warp_base[k] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  const int warp_first = i - lane;
+  int rank = 0;
+  for (unsigned rest = m; rest; rest &= rest - 1, rank++) {
+    const int src_lane = __ffs(rest) - 1;
+    const int at = warp_base[w] + rank;
+    if (at >= capacity) break;  // the caller's buffer is full: *n_out still reports how many there are
+    const uint4 *src = reinterpret_cast<const uint4 *>(pkts + warp_first + src_lane);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + at);
+    if (lane < (int)(sizeof(ArtisPacket) / 16)) dst[lane] = src[lane];
+  }
+}
+}  // namespace
+
+extern "C" int artis_gpu_pack_escaped_noalloc(const ArtisPacket *dev_packets, int npkts, ArtisPacket *dev_out, int capacity,
+                                              int *dev_n_out, void *cuda_stream) {
+  if (npkts < 0 || capacity < 0 || dev_n_out == nullptr || (npkts > 0 && dev_packets == nullptr) ||
+      (capacity > 0 && dev_out == nullptr))
+    return fail(ARTIS_ERR_ABI, "artis_gpu_pack_escaped_noalloc: bad arguments");
+  if (npkts > NOALLOC_MAX_PACKETS)
+    return fail(ARTIS_ERR_ABI, "artis_gpu_pack_escaped_noalloc: " + std::to_string(npkts) + " packets exceed the fixed scratch of " +
+                                   std::to_string(NOALLOC_MAX_PACKETS) + " packets per call (split the array, or use "
+                                   "artis_gpu_packets_download_escaped, which allocates)");
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+    return fail(ARTIS_ERR_CUDA, "artis_gpu_pack_escaped_noalloc: no current CUDA device");
+  if (g_noalloc_ptr[dev] == nullptr) {  // set-up, once per device
+    int *ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_counts);
+    if (e != cudaSuccess || ptr == nullptr)
+      return fail(ARTIS_ERR_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_counts): ") + cudaGetErrorString(e));
+    g_noalloc_ptr[dev] = ptr;
+  }
+  int *counts = g_noalloc_ptr[dev];
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  const int nchunks = (npkts + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK;
+  // nothing in the scratch has to start at zero: counts[0..nchunks] are all written before they are read, whatever the
+  // previous call left there
+  if (nchunks > 0) k_na_count<<<nchunks, artis::ESC_CHUNK, 0, stream>>>(dev_packets, npkts, counts);
+  k_na_scan<<<1, 1024, 0, stream>>>(counts, nchunks, dev_n_out);
+  if (nchunks > 0 && capacity > 0) k_na_scatter<<<nchunks, artis::ESC_CHUNK, 0, stream>>>(dev_packets, npkts, counts, dev_out, capacity);
+  E.launches += (nchunks > 0 ? 2 : 0) + 1;
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(ARTIS_ERR_CUDA, std::string("artis_gpu_pack_escaped_noalloc launch: ") + cudaGetErrorString(e));
+  return ARTIS_OK;
+}

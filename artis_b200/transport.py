@@ -172,6 +172,12 @@ class Transport:
                                                                 C.byref(n)), "artis_gpu_packets_download_escaped")
         return out[:n.value]
 
+    def pack_escaped_noalloc(self, dev_packets_ptr, npkts, dev_out_ptr, capacity, dev_n_out_ptr, stream=None):
+        """artis_gpu_pack_escaped_noalloc: device pointers in, device pointers out, nothing allocated, no synchronisation"""
+        self._check(self.lib.artis_gpu_pack_escaped_noalloc(C.c_void_p(dev_packets_ptr), int(npkts), C.c_void_p(dev_out_ptr),
+                                                            int(capacity), C.c_void_p(dev_n_out_ptr), C.c_void_p(stream or 0)),
+                    "artis_gpu_pack_escaped_noalloc")
+
     # ---- deterministic probes (K10)
     def probe_boundary_cross(self, pkts):
         n = pkts.size

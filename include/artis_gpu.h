@@ -226,6 +226,24 @@ int artis_gpu_bin_escaped(double tmax, int nprocs, int nnubins, int allreduce, d
  * timestep. If *n_out > capacity the call fails with ARTIS_ERR_ABI, *n_out holds the count and nothing is marked. */
 int artis_gpu_packets_download_escaped(ArtisPacket *out, int capacity, int only_new, int *n_out);
 
+/* Escaped-packet compaction that allocates nothing. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot reach cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). The same selection as artis_gpu_packets_download_escaped(only_new = 0) -- every packet with
+ * type == TYPE_ESCAPE, in array order -- but on the CALLER's device arrays:
+ *   dev_packets[npkts]  in,  device memory        dev_out[capacity]  out, device memory
+ *   dev_n_out           out, device memory: the number of escaped packets (if it exceeds capacity only the first
+ *                       `capacity` of them were written)
+ *   cuda_stream         a cudaStream_t (NULL: the default stream); the kernels are enqueued there and the call returns
+ *                       without synchronising -- results are valid in stream order
+ * The per-chunk counts live in a file-scope device array of 64 KiB that every GPU loading the library holds until exit:
+ * npkts above 4 194 304 (ARTIS_NOALLOC_MAX_PACKETS) is rejected with ARTIS_ERR_ABI. The call makes no cudaMalloc /
+ * cudaFree and calls no allocating library routine; its first use on a device looks up the array's address
+ * (cudaGetSymbolAddress), so make that first call outside a stream capture. All calls share the one array: calls that
+ * overlap on the same GPU (two streams, two host threads) race on it and must be serialised by the caller. */
+#define ARTIS_NOALLOC_MAX_PACKETS (1 << 22)
+int artis_gpu_pack_escaped_noalloc(const ArtisPacket *dev_packets, int npkts, ArtisPacket *dev_out, int capacity,
+                                   int *dev_n_out, void *cuda_stream);
+
 /* ---- K10: deterministic probes (test entry points for SURVEY 8a A4-A8, A11, A12, A14) ------------------ */
 /* Each probe runs the corresponding device function for n independent packet states on the GPU. */
 /* boundary_cross (boundary.cc:101): out sdist[n], snext[n], last_cross_out[n] */
