@@ -146,6 +146,7 @@ def declare(lib):
         "artis_gpu_packets_download": [vp, C.c_int],
         "artis_gpu_last_timings": [pd, C.c_int],
         "artis_gpu_set_tuning": [C.c_int, C.c_int],
+        "artis_gpu_scheduler_geometry": [pi, C.c_int],
         "artis_gpu_comm_unique_id": [C.c_char_p],
         "artis_gpu_comm_init": [C.c_char_p, C.c_int, C.c_int],
         "artis_gpu_reduce_estimators": [C.c_int],
@@ -183,5 +184,5 @@ EXPORTED_SYMBOLS = [
     "artis_gpu_probe_kappa_cont", "artis_gpu_probe_closest_transition", "artis_gpu_probe_get_event",
     "artis_gpu_probe_macroatom_rates", "artis_gpu_probe_cooling_ion", "artis_gpu_probe_gamma_kappa",
     "artis_gpu_probe_levelpop", "artis_gpu_launch_count", "artis_gpu_table_bytes", "artis_gpu_bin_escaped",
-    "artis_gpu_packets_download_escaped", "artis_gpu_pack_escaped_noalloc",
+    "artis_gpu_packets_download_escaped", "artis_gpu_pack_escaped_noalloc", "artis_gpu_scheduler_geometry",
 ]

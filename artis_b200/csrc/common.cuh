@@ -20,6 +20,216 @@
 
 namespace artis {
 
+// ---- packets on the device: hot / cold split --------------------------------------------------------------------------
+// The ABI carries the reference's 304-byte `struct packet` (ArtisPacket, packet.h:28-73). On the device a packet is two
+// records in two arrays:
+//   PktHot  (128 B, one line)  what the transport roles read and write at EVERY visit, ordered so that each role touches
+//                              whole 32-byte sectors: sector 0 = identity, scheduling and macro-atom state (all a
+//                              macro-atom jump needs), sector 1 = Philox draw counter, e_cmf, nu_cmf, prop_time,
+//                              sectors 2-3 = position, direction and the rest-frame pair. An r-packet step loads the
+//                              line with eight 16-byte loads (the AoS record took 38 strided 8-byte loads and kept all 76
+//                              words live in registers).
+//   PktCold (176 B)            bookkeeping that only the rare events touch (emission / absorption / escape records, Stokes
+//                              vector, pellet data); events write it in place through Pkt::cold, it never sits in registers.
+// artis_gpu_packets_upload / _download transpose between the two forms on the device (k_unpack / k_pack); the
+// transposition is lossless down to the padding bytes of the host struct.
+struct alignas(128) PktHot {
+  int where;
+  unsigned type_cross;  // type | last_cross << 16   (two small enums: 16 bits each keep every valid value)
+  unsigned ma_el_ion;   // mastate.element | mastate.ion << 16
+  int ma_level, ma_activatingline, interactions, last_event, next_trans;
+  unsigned rngctr;      // doubles drawn so far in this timestep (a packet draws ~1e5, far below 2^32)
+  int number;
+  double e_cmf, nu_cmf, prop_time;
+  double pos[3], nu_rf;
+  double dir[3], e_rf;
+};
+struct alignas(16) PktCold {
+  double em_pos[3];
+  int em_time, emissiontype;
+  double stokes[3];
+  int nscatterings, absorptiontype;
+  double pol_dir[3];
+  int escape_type, escape_time;
+  double absorptiondir[3];
+  int trueemissiontype, trueem_time;
+  double absorptionfreq, tdecay;
+  float trueemissionvelocity;
+  int pellet_decaytype, pellet_nucindex;
+  unsigned origin_bytes;  // originated_from_particlenotgamma and the three padding bytes behind it, as the host has them
+  int scat_count, pad0, pad1, spare;
+};
+static_assert(sizeof(PktHot) == 128 && sizeof(PktCold) == 176, "device packet records");
+// The register-resident working set of one packet: the hot fields by name (the physics reads and writes them like the
+// members of struct packet) and the address of its cold record.
+struct Pkt {
+  int where, type, last_cross, interactions, last_event, next_trans, number;
+  int ma_element, ma_ion, ma_level, ma_activatingline;
+  double pos[3], dir[3], e_cmf, e_rf, nu_cmf, nu_rf, prop_time;
+  PktCold *cold;
+};
+// A packet migrates between SMs in mid-timestep (the scheduler hands it from ring to ring), and L1 is not coherent across
+// SMs: everything a role READS from a packet's records goes through L2 (ld.global.cg) -- ldcold for the cold record, the
+// explicit 16-byte loads of transport.cu for the hot one -- so that no fence has to invalidate the SM's L1 (where the
+// read-only atomic and per-cell tables live) when a packet arrives. Writes are write-through.
+template <class T>
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+    inline T
+    ldcold(const T *addr) {
+#ifdef __CUDA_ARCH__
+  return __ldcg(addr);
+#else
+  return *addr;
+#endif
+}
+#ifdef __CUDACC__
+#define ARTIS_HD __host__ __device__ inline
+#else
+#define ARTIS_HD inline
+#endif
+ARTIS_HD unsigned pkt_pack2(int lo, int hi) { return ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16); }
+ARTIS_HD int pkt_lo16(unsigned w) { return (int)(short)(w & 0xffffu); }
+ARTIS_HD int pkt_hi16(unsigned w) { return (int)(short)(w >> 16); }
+// ABI record -> device records and back (k_unpack / k_pack, the probes, the host build)
+ARTIS_HD void pkt_split(const ArtisPacket &a, PktHot &h, PktCold &c) {
+  h.where = a.where;
+  h.type_cross = pkt_pack2(a.type, a.last_cross);
+  h.ma_el_ion = pkt_pack2(a.ma_element, a.ma_ion);
+  h.ma_level = a.ma_level;
+  h.ma_activatingline = a.ma_activatingline;
+  h.interactions = a.interactions;
+  h.last_event = a.last_event;
+  h.next_trans = a.next_trans;
+  h.rngctr = 0u;
+  h.number = a.number;
+  h.e_cmf = a.e_cmf;
+  h.nu_cmf = a.nu_cmf;
+  h.prop_time = a.prop_time;
+  h.nu_rf = a.nu_rf;
+  h.e_rf = a.e_rf;
+  for (int d = 0; d < 3; d++) {
+    h.pos[d] = a.pos[d];
+    h.dir[d] = a.dir[d];
+    c.em_pos[d] = a.em_pos[d];
+    c.stokes[d] = a.stokes[d];
+    c.pol_dir[d] = a.pol_dir[d];
+    c.absorptiondir[d] = a.absorptiondir[d];
+  }
+  c.em_time = a.em_time;
+  c.emissiontype = a.emissiontype;
+  c.nscatterings = a.nscatterings;
+  c.absorptiontype = a.absorptiontype;
+  c.escape_type = a.escape_type;
+  c.escape_time = a.escape_time;
+  c.trueemissiontype = a.trueemissiontype;
+  c.trueem_time = a.trueem_time;
+  c.absorptionfreq = a.absorptionfreq;
+  c.tdecay = a.tdecay;
+  c.trueemissionvelocity = a.trueemissionvelocity;
+  c.pellet_decaytype = a.pellet_decaytype;
+  c.pellet_nucindex = a.pellet_nucindex;
+  c.origin_bytes = (unsigned)a.originated_from_particlenotgamma | ((unsigned)a._pad2[0] << 8) | ((unsigned)a._pad2[1] << 16) |
+                   ((unsigned)a._pad2[2] << 24);
+  c.scat_count = a.scat_count;
+  c.pad0 = a._pad0;
+  c.pad1 = a._pad1;
+  c.spare = 0;
+}
+ARTIS_HD void pkt_join(const PktHot &h, const PktCold &c, ArtisPacket &a) {
+  a.where = h.where;
+  a.type = pkt_lo16(h.type_cross);
+  a.last_cross = pkt_hi16(h.type_cross);
+  a.ma_element = pkt_lo16(h.ma_el_ion);
+  a.ma_ion = pkt_hi16(h.ma_el_ion);
+  a.ma_level = h.ma_level;
+  a.ma_activatingline = h.ma_activatingline;
+  a.interactions = h.interactions;
+  a.last_event = h.last_event;
+  a.next_trans = h.next_trans;
+  a.number = h.number;
+  a.e_cmf = h.e_cmf;
+  a.nu_cmf = h.nu_cmf;
+  a.prop_time = h.prop_time;
+  a.nu_rf = h.nu_rf;
+  a.e_rf = h.e_rf;
+  for (int d = 0; d < 3; d++) {
+    a.pos[d] = h.pos[d];
+    a.dir[d] = h.dir[d];
+    a.em_pos[d] = c.em_pos[d];
+    a.stokes[d] = c.stokes[d];
+    a.pol_dir[d] = c.pol_dir[d];
+    a.absorptiondir[d] = c.absorptiondir[d];
+  }
+  a.em_time = c.em_time;
+  a.emissiontype = c.emissiontype;
+  a.nscatterings = c.nscatterings;
+  a.absorptiontype = c.absorptiontype;
+  a.escape_type = c.escape_type;
+  a.escape_time = c.escape_time;
+  a.trueemissiontype = c.trueemissiontype;
+  a.trueem_time = c.trueem_time;
+  a.absorptionfreq = c.absorptionfreq;
+  a.tdecay = c.tdecay;
+  a.trueemissionvelocity = c.trueemissionvelocity;
+  a.pellet_decaytype = c.pellet_decaytype;
+  a.pellet_nucindex = c.pellet_nucindex;
+  a.originated_from_particlenotgamma = (uint8_t)(c.origin_bytes & 0xffu);
+  a._pad2[0] = (uint8_t)((c.origin_bytes >> 8) & 0xffu);
+  a._pad2[1] = (uint8_t)((c.origin_bytes >> 16) & 0xffu);
+  a._pad2[2] = (uint8_t)(c.origin_bytes >> 24);
+  a.scat_count = c.scat_count;
+  a._pad0 = c.pad0;
+  a._pad1 = c.pad1;
+}
+// working set <-> hot record. The Philox draw counter is handed over separately (it lives in the Rng while a lane holds the
+// packet).
+ARTIS_HD void pkt_from_hot(Pkt &p, const PktHot &h, PktCold *cold) {
+  p.where = h.where;
+  p.type = pkt_lo16(h.type_cross);
+  p.last_cross = pkt_hi16(h.type_cross);
+  p.ma_element = pkt_lo16(h.ma_el_ion);
+  p.ma_ion = pkt_hi16(h.ma_el_ion);
+  p.ma_level = h.ma_level;
+  p.ma_activatingline = h.ma_activatingline;
+  p.interactions = h.interactions;
+  p.last_event = h.last_event;
+  p.next_trans = h.next_trans;
+  p.number = h.number;
+  p.e_cmf = h.e_cmf;
+  p.nu_cmf = h.nu_cmf;
+  p.prop_time = h.prop_time;
+  p.nu_rf = h.nu_rf;
+  p.e_rf = h.e_rf;
+  for (int d = 0; d < 3; d++) {
+    p.pos[d] = h.pos[d];
+    p.dir[d] = h.dir[d];
+  }
+  p.cold = cold;
+}
+ARTIS_HD void pkt_to_hot(PktHot &h, const Pkt &p, unsigned rngctr) {
+  h.where = p.where;
+  h.type_cross = pkt_pack2(p.type, p.last_cross);
+  h.ma_el_ion = pkt_pack2(p.ma_element, p.ma_ion);
+  h.ma_level = p.ma_level;
+  h.ma_activatingline = p.ma_activatingline;
+  h.interactions = p.interactions;
+  h.last_event = p.last_event;
+  h.next_trans = p.next_trans;
+  h.rngctr = rngctr;
+  h.number = p.number;
+  h.e_cmf = p.e_cmf;
+  h.nu_cmf = p.nu_cmf;
+  h.prop_time = p.prop_time;
+  h.nu_rf = p.nu_rf;
+  h.e_rf = p.e_rf;
+  for (int d = 0; d < 3; d++) {
+    h.pos[d] = p.pos[d];
+    h.dir[d] = p.dir[d];
+  }
+}
+
 // ---- physical constants, values exactly as the reference's constants.h:3-37 ------------------------------
 constexpr double CLIGHT = 2.99792458e+10;
 constexpr double CLIGHT_PROP = CLIGHT;
@@ -384,13 +594,38 @@ ARTIS_DEV int int_fetch_add(int *addr, int v) {
 struct Tally {
   int rpkt_steps, lines_scanned, lines_tau, bf_evaluated, estim_atomics, gamma_steps, ma_jumps, ma_trans_scanned,
       kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates, handoffs;
-  int stats[34];  // stats::eventcounters increments of this thread (stats.h:48-84), flushed once per thread and pass
+#ifndef __CUDACC__
+  int stats[34];  // stats::eventcounters increments of this thread (stats.h:48-84); on the device they live in shared memory
+#endif
   // VPKT_ON: a virtual-packet request left by the event that has just been processed (vpkt.cuh vpkt_flush_request runs it
   // at the one place per scheduler where events return): realtype 1-3 (0 = none) and, for an electron scattering, the
   // direction and Stokes Q, U the packet arrived with
   int vpkt_req;
   double vpkt_dir[3], vpkt_q, vpkt_u;
 };
+// stats::increment (stats.cc:151). The 34 event counters are bumped at most once or twice per event: on the device one
+// copy per thread block in shared memory (an ATOMS each) instead of 34 registers per thread; a kernel that runs events
+// clears the copy at its start (stats_block_begin) and adds it to the global counters at its end (stats_block_flush).
+#ifdef __CUDACC__
+ARTIS_DEV int *stats_block() {
+  __shared__ int artis_stats_smem[34];
+  return artis_stats_smem;
+}
+ARTIS_DEV void stat_inc(Tally &, int counter) { atomicAdd(stats_block() + counter, 1); }
+ARTIS_DEV void stats_block_begin() {
+  for (int i = threadIdx.x; i < 34; i += blockDim.x) stats_block()[i] = 0;
+  __syncthreads();
+}
+ARTIS_DEV void stats_block_flush(const Ctx &c) {
+  __syncthreads();
+  for (int i = threadIdx.x; i < 34; i += blockDim.x) {
+    const int v = stats_block()[i];
+    if (v) atomicAdd((unsigned long long *)&c.es.counters[i], (unsigned long long)v);
+  }
+}
+#else
+ARTIS_DEV void stat_inc(Tally &t, int counter) { t.stats[counter]++; }
+#endif
 ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   long long *k = c.es.counters;
   if (t.rpkt_steps) ctr_add(&k[ARTIS_CTR_RPKT_STEPS], t.rpkt_steps);
@@ -408,11 +643,11 @@ ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   if (t.kappa_evals) ctr_add(&k[ARTIS_CTR_KAPPA_EVALS], t.kappa_evals);
   if (t.packet_updates) ctr_add(&k[ARTIS_CTR_PACKET_UPDATES], t.packet_updates);
   if (t.handoffs) ctr_add(&k[ARTIS_CTR_HANDOFFS], t.handoffs);
+#ifndef __CUDACC__
   for (int i = 0; i < 34; i++)
     if (t.stats[i]) ctr_add(&k[i], t.stats[i]);
+#endif
 }
-// stats::increment (stats.cc:151): per-thread tally instead of one global atomic per event
-ARTIS_DEV void stat_inc(Tally &t, int counter) { t.stats[counter]++; }
 // the FIRST fatal code of a timestep is the one reported (later ones are usually its consequences)
 ARTIS_DEV void fatal(const Ctx &c, int code) {
   if (c.error_flag == nullptr) return;

@@ -13,7 +13,7 @@ ARTIS_DEV double sigma_compton_partial(const double x, const double f) {
   return (3 * SIGMA_T * (term1 + term2 + term3) / (8 * x));
 }
 // gammapkt.cc:335-361
-ARTIS_DEV double sig_comp(const Ctx &c, const ArtisPacket &p, const int mgi) {
+ARTIS_DEV double sig_comp(const Ctx &c, const Pkt &p, const int mgi) {
   const double xx = H * p.nu_cmf / ME / CLIGHT / CLIGHT;
   double sigma_cmf;
   if (xx < THOMSON_LIMIT) {
@@ -25,7 +25,7 @@ ARTIS_DEV double sig_comp(const Ctx &c, const ArtisPacket &p, const int mgi) {
   return sigma_cmf * doppler_packet(c, p);
 }
 // photo_electric.cc:10-49
-ARTIS_DEV double sig_photo_electric(const Ctx &c, const ArtisPacket &p, const int mgi) {
+ARTIS_DEV double sig_photo_electric(const Ctx &c, const Pkt &p, const int mgi) {
   double sigma_cmf;
   const double rho = (double)c.cs.rho[mgi];
   if (c.st.gamma_grey < 0) {
@@ -41,7 +41,7 @@ ARTIS_DEV double sig_photo_electric(const Ctx &c, const ArtisPacket &p, const in
   return sigma_cmf * doppler_packet(c, p);
 }
 // photo_electric.cc:51-114
-ARTIS_DEV double sig_pair_prod(const Ctx &c, const ArtisPacket &p, const int mgi) {
+ARTIS_DEV double sig_pair_prod(const Ctx &c, const Pkt &p, const int mgi) {
   double sigma_cmf = 0.0;
   const double rho = (double)c.cs.rho[mgi];
   if (c.st.gamma_grey < 0 && p.nu_cmf > 2.46636e+20) {
@@ -73,7 +73,7 @@ ARTIS_DEV double meanf_sigma(const double x) {
   return 3 * SIGMA_T * (term0 + term1 + term2 + term3 + term4) / (8 * x);
 }
 // grey_emissivities.cc:28-77
-ARTIS_DEV void rlc_emiss_gamma(const Ctx &c, const ArtisPacket &p, const int mgi, const double dist, Tally &tl) {
+ARTIS_DEV void rlc_emiss_gamma(const Ctx &c, const Pkt &p, const int mgi, const double dist, Tally &tl) {
   if (dist > 0) {
     double vel_vec[3];
     get_velocity(p.pos, vel_vec, p.prop_time);
@@ -119,7 +119,7 @@ ARTIS_DEV double thomson_angle(const Ctx &c, Rng &rng) {
   return mu;
 }
 // gammapkt.cc:421-531
-ARTIS_DEV void compton_scatter(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void compton_scatter(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   double f;
   const double xx = H * p.nu_cmf / ME / CLIGHT / CLIGHT;
   bool stay_gamma;
@@ -162,18 +162,18 @@ ARTIS_DEV void compton_scatter(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl
     p.last_cross = ARTIS_CROSS_NONE;
   } else {
     p.type = ARTIS_TYPE_NTLEPTON;
-    p.absorptiontype = -3;
+    p.cold->absorptiontype = -3;
     stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
   }
 }
 // photo_electric.cc:116-164
-ARTIS_DEV void pair_prod(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void pair_prod(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   const double prob_gamma = 1.022 * MEV / (H * p.nu_cmf);
   if (prob_gamma < 0) fatal(c, 405);
   const double zrand = rng_uniform(rng);
   if (zrand > prob_gamma) {
     p.type = ARTIS_TYPE_NTLEPTON;
-    p.absorptiontype = -5;
+    p.cold->absorptiontype = -5;
     stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
   } else {
     p.nu_cmf = 0.511 * MEV / H;
@@ -191,7 +191,7 @@ ARTIS_DEV void pair_prod(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
 }
 
 // gammapkt.cc:533-700 do_gamma (GRID_UNIFORM)
-ARTIS_DEV void do_gamma(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_gamma(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
   tl.gamma_steps++;
   const double zrand0 = rng_uniform_pos(rng);
   const double tau_next = -1. * log(zrand0);
@@ -251,7 +251,7 @@ ARTIS_DEV void do_gamma(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng,
       compton_scatter(c, p, rng, tl);
     } else if ((kap_compton + kap_photo_electric) > (zrand * kap_tot)) {
       p.type = ARTIS_TYPE_NTLEPTON;
-      p.absorptiontype = -4;
+      p.cold->absorptiontype = -4;
       stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
     } else if ((kap_compton + kap_photo_electric + kap_pair_prod) > (zrand * kap_tot)) {
       pair_prod(c, p, rng, tl);
@@ -266,19 +266,20 @@ ARTIS_DEV void do_gamma(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng,
 }
 
 // gammapkt.cc:227-318 choose_gamma_ray + pellet_gamma_decay
-ARTIS_DEV void pellet_gamma_decay(const Ctx &c, ArtisPacket &p, Rng &rng) {
-  const int nuc = p.pellet_nucindex;
+ARTIS_DEV void pellet_gamma_decay(const Ctx &c, Pkt &p, Rng &rng) {
+  const int nuc = ldcold(&p.cold->pellet_nucindex);
   const int off = c.st.gam_offset[nuc];
   const int nlines = c.st.gam_offset[nuc + 1] - off;
   if (nlines == 0) {
     p.type = ARTIS_TYPE_KPKT;
-    p.absorptiontype = -6;
+    p.cold->absorptiontype = -6;
     return;
   }
   double dir_cmf[3];
   get_rand_isotropic_unitvec(rng, dir_cmf);
   double vel_vec[3];
-  get_velocity(p.pos, vel_vec, -1. * p.tdecay);
+  const double tdecay = ldcold(&p.cold->tdecay);
+  get_velocity(p.pos, vel_vec, -1. * tdecay);
   angle_ab(dir_cmf, vel_vec, p.dir);
   const double E_gamma = c.st.nuc_decayenergygamma[nuc];
   const double zrand = rng_uniform(rng);
@@ -296,21 +297,21 @@ ARTIS_DEV void pellet_gamma_decay(const Ctx &c, ArtisPacket &p, Rng &rng) {
     nselected = nlines - 1;
   }
   p.nu_cmf = c.st.gam_energy[off + nselected] / H;
-  p.prop_time = p.tdecay;
+  p.prop_time = tdecay;
   const double dopplerfactor = doppler_packet(c, p);
   p.nu_rf = p.nu_cmf / dopplerfactor;
   p.e_rf = p.e_cmf / dopplerfactor;
   p.type = ARTIS_TYPE_GAMMA;
   p.last_cross = ARTIS_CROSS_NONE;
-  p.stokes[0] = 1.0;
-  p.stokes[1] = p.stokes[2] = 0.0;
+  p.cold->stokes[0] = 1.0;
+  p.cold->stokes[1] = p.cold->stokes[2] = 0.0;
   set_pol_dir(p);
 }
 
 // update_packets.cc:71-135 update_pellet
-ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, Tally &tl) {
+ARTIS_DEV void update_pellet(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
   const double ts = p.prop_time;
-  const double tdecay = p.tdecay;
+  const double tdecay = ldcold(&p.cold->tdecay);
   double *tsc = c.es.ts_scalars;
   if (tdecay > t2) {
     vec_scale(p.pos, t2 / ts);
@@ -319,21 +320,22 @@ ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng 
     ctr_add(&c.es.counters[ARTIS_CTR_PELLET_DECAYS], 1);
     p.prop_time = tdecay;
     vec_scale(p.pos, tdecay / ts);
-    if (p.originated_from_particlenotgamma) {
-      if (p.pellet_decaytype == ARTIS_DECAYTYPE_BETAPLUS) {
+    const int decaytype = ldcold(&p.cold->pellet_decaytype);
+    if ((ldcold(&p.cold->origin_bytes) & 0xffu)) {
+      if (decaytype == ARTIS_DECAYTYPE_BETAPLUS) {
         est_add(&tsc[ARTIS_TS_POSITRON_DEP], p.e_cmf);
         p.type = ARTIS_TYPE_NTLEPTON;
-        p.absorptiontype = -10;
-      } else if (p.pellet_decaytype == ARTIS_DECAYTYPE_BETAMINUS) {
+        p.cold->absorptiontype = -10;
+      } else if (decaytype == ARTIS_DECAYTYPE_BETAMINUS) {
         est_add(&tsc[ARTIS_TS_ELECTRON_EMISSION], p.e_cmf);
-        p.em_time = (int)p.prop_time;
+        p.cold->em_time = (int)p.prop_time;
         p.type = ARTIS_TYPE_NONTHERMAL_PREDEPOSIT;
-        p.absorptiontype = -10;
-      } else if (p.pellet_decaytype == ARTIS_DECAYTYPE_ALPHA) {
+        p.cold->absorptiontype = -10;
+      } else if (decaytype == ARTIS_DECAYTYPE_ALPHA) {
         est_add(&tsc[ARTIS_TS_ALPHA_EMISSION], p.e_cmf);
-        p.em_time = (int)p.prop_time;
+        p.cold->em_time = (int)p.prop_time;
         p.type = ARTIS_TYPE_NONTHERMAL_PREDEPOSIT;
-        p.absorptiontype = -10;
+        p.cold->absorptiontype = -10;
       }
     } else {
       est_add(&tsc[ARTIS_TS_GAMMA_EMISSION], p.e_cmf);
@@ -342,7 +344,7 @@ ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng 
   } else if ((tdecay > 0) && (c.nts == 0)) {
     p.e_cmf *= tdecay / c.st.tmin;
     p.type = ARTIS_TYPE_PRE_KPKT;
-    p.absorptiontype = -7;
+    p.cold->absorptiontype = -7;
     stat_inc(tl, COUNTER_K_STAT_FROM_EARLIERDECAY);
     p.prop_time = c.st.tmin;
   } else {
@@ -352,25 +354,26 @@ ARTIS_DEV void update_pellet(const Ctx &c, ArtisPacket &p, const double t2, Rng 
 }
 
 // update_packets.cc:16-69 do_nonthermal_predeposit
-ARTIS_DEV void do_nonthermal_predeposit(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng) {
+ARTIS_DEV void do_nonthermal_predeposit(const Ctx &c, Pkt &p, const double t2, Rng &rng) {
   const double ts = p.prop_time;
+  const int decaytype = ldcold(&p.cold->pellet_decaytype);
   const double particle_en = H * p.nu_cmf;
   double endot = 0.;
   double t_absorb = ts;
   if (!c.st.opt_instant_particle_deposition) {
     const double rho = (double)c.cs.rho[cell_mgi(c, p.where)];
-    endot = (p.pellet_decaytype == ARTIS_DECAYTYPE_ALPHA) ? 5.e11 * MEV * rho : 4.e10 * MEV * rho;
+    endot = (decaytype == ARTIS_DECAYTYPE_ALPHA) ? 5.e11 * MEV * rho : 4.e10 * MEV * rho;
     const double zrand = rng_uniform(rng);
     const double en_absorb = zrand * particle_en;
     t_absorb = ts + en_absorb / endot;
   }
   double *tsc = c.es.ts_scalars;
   if (t_absorb <= t2) {
-    if (p.pellet_decaytype == ARTIS_DECAYTYPE_ALPHA) {
+    if (decaytype == ARTIS_DECAYTYPE_ALPHA) {
       est_add(&tsc[ARTIS_TS_ALPHA_DEP], p.e_cmf);
-    } else if (p.pellet_decaytype == ARTIS_DECAYTYPE_BETAMINUS) {
+    } else if (decaytype == ARTIS_DECAYTYPE_BETAMINUS) {
       est_add(&tsc[ARTIS_TS_ELECTRON_DEP], p.e_cmf);
-    } else if (p.pellet_decaytype == ARTIS_DECAYTYPE_BETAPLUS) {
+    } else if (decaytype == ARTIS_DECAYTYPE_BETAPLUS) {
       est_add(&tsc[ARTIS_TS_POSITRON_DEP], p.e_cmf);
     }
     vec_scale(p.pos, t_absorb / ts);
@@ -386,7 +389,7 @@ ARTIS_DEV void do_nonthermal_predeposit(const Ctx &c, ArtisPacket &p, const doub
 // update_packets.cc:137-202 do_packet. The r-packet case runs ONE do_rpkt_step instead of do_rpkt's whole loop, so
 // that the scheduler can interleave packet kinds; everything the reference does after do_rpkt returns (cmf_lum on
 // escape) happens as soon as the packet escapes.
-ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_packet(const Ctx &c, Pkt &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
   tl.packet_updates++;
   switch (p.type) {
     case ARTIS_TYPE_RADIOACTIVE_PELLET:
@@ -429,10 +432,11 @@ ARTIS_DEV void do_packet(const Ctx &c, ArtisPacket &p, const double t2, KappaCac
   }
 }
 
-// do_packet restricted to the packet types of one scheduler kind (kernels.cuh kind_of): each wavefront kernel only
-// carries the code and registers of the physics it can meet.
+// do_packet restricted to the packet types of one scheduler kind (kernels.cuh kind_of): each role only carries the code
+// and registers of the physics it can meet. KIND 5 (macro-atom jumps) and the macro-atom branch of KIND 0 run the whole
+// iteration of do_macroatom here; the device scheduler splits it into ma_jump / ma_event itself (transport.cu).
 template <int KIND>
-ARTIS_DEV void do_packet_kind(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_packet_kind(const Ctx &c, Pkt &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
   if constexpr (KIND == 1 || KIND == 4) {
     tl.packet_updates++;
     do_rpkt_step<(KIND == 1 ? 1 : 2)>(c, p, t2, k, rng, tl);
@@ -441,6 +445,9 @@ ARTIS_DEV void do_packet_kind(const Ctx &c, ArtisPacket &p, const double t2, Kap
     tl.packet_updates++;
     do_gamma(c, p, t2, rng, tl);
     if (p.type != ARTIS_TYPE_GAMMA && p.type != ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_GAMMA_DEP], p.e_cmf);
+  } else if constexpr (KIND == 5) {
+    tl.packet_updates++;
+    do_macroatom(c, p, rng, tl);
   } else if constexpr (KIND == 0) {
     tl.packet_updates++;
     if (p.type == ARTIS_TYPE_MA) {

@@ -33,32 +33,36 @@ ARTIS_DEV void body_cool(const Ctx &c, const long long idx) {
   if (cell_uses_tables(c, mgi)) build_cooling_ion(c, mgi, (int)(idx % c.st.includedions));
 }
 
-// ---- event-kind wavefront -------------------------------------------------------------
-// Packets are grouped by the KIND of event they need next; each kind has its own queue of packet indices and its own
-// kernel launch, so that a warp only ever executes one kind of event: the cheap table-driven macro-atom / k-packet
-// events are never serialised behind a lane that is doing an r-packet step with a continuum-opacity evaluation and
-// a line sweep (measured on v1/v2: ~1.8 active lanes per instruction, profiles/r1_v1_*, r1_v2_*).
-//   kind 0  macro-atom jumps, k-packets, non-thermal leptons        (macroatom.cc, kpkt.cc, nonthermal.cc:1877)
-//   kind 1  r-packet steps                                          (rpkt.cc:623)
+// ---- event kinds -------------------------------------------------------------------------
+// Packets are grouped by the KIND of event they need next; each kind has its own ring of packet indices, and a warp only
+// ever executes one kind of event: the cheap table-driven macro-atom jumps are never serialised behind a lane that is
+// doing an r-packet step with a continuum-opacity evaluation and a line sweep, nor behind one that emits a packet
+// (measured on v1/v2: ~1.8 active lanes per instruction, profiles/r1_v1_*, r1_v2_*; round 2: 31 % of the macro-atom
+// kind's instructions ran at 6.6 active lanes because one lane in a hundred was de-activating).
+//   kind 0  macro-atom EVENTS (de-activations, jumps to another ion), k-packets, non-thermal leptons
+//           (macroatom.cc:222-414,766-876, kpkt.cc, nonthermal.cc:1877)
+//   kind 1  r-packet steps in a non-grey cell                       (rpkt.cc:623)
 //   kind 2  gamma-packet steps                                      (gammapkt.cc:533)
 //   kind 3  pellets and non-thermal pre-deposition                  (update_packets.cc:16,71)
-// A lane pulls the next index from its kind's queue, runs do_packet while the packet stays of that kind, then writes
-// it back and appends its index to the queue of the kind it has become (or drops it when it escaped / reached t2).
-constexpr int NKIND = 5;
-enum { KIND_MAK = 0, KIND_RPKT_THIN = 1, KIND_GAMMA = 2, KIND_OTHER = 3, KIND_RPKT_GREY = 4 };
+//   kind 4  r-packet steps in a grey or empty cell
+//   kind 5  macro-atom JUMPS within an ion (macroatom.cc:174-220,815-835): 98 % of all macro-atom iterations, 32 bytes of
+//           packet state, run by their own low-register kernel (transport.cu k_transport_majump)
+constexpr int NKIND = 6;
+enum { KIND_MAK = 0, KIND_RPKT_THIN = 1, KIND_GAMMA = 2, KIND_OTHER = 3, KIND_RPKT_GREY = 4, KIND_MAJUMP = 5 };
 // r-packets are two kinds: in a non-grey cell a step evaluates the continuum opacity and sweeps lines (expensive), in a
 // grey or empty cell it is a boundary distance and a Thomson-like scattering (cheap); mixed in one warp the cheap lanes
 // would idle through the others' opacity loops.
-ARTIS_DEV int kind_of(const Ctx &c, const ArtisPacket &p) {
-  switch (p.type) {
-    case ARTIS_TYPE_KPKT:
+ARTIS_DEV int kind_of(const Ctx &c, const int type, const int where) {
+  switch (type) {
     case ARTIS_TYPE_MA:
+      return KIND_MAJUMP;
+    case ARTIS_TYPE_KPKT:
     case ARTIS_TYPE_NTLEPTON:
     case ARTIS_TYPE_PRE_KPKT:
     case ARTIS_TYPE_GAMMA_KPKT:
       return KIND_MAK;
     case ARTIS_TYPE_RPKT: {
-      const int mgi = cell_mgi(c, p.where);
+      const int mgi = cell_mgi(c, where);
       return (mgi == c.st.npts_model || c.cs.thick[mgi] == 1) ? KIND_RPKT_GREY : KIND_RPKT_THIN;
     }
     case ARTIS_TYPE_GAMMA:
@@ -67,12 +71,9 @@ ARTIS_DEV int kind_of(const Ctx &c, const ArtisPacket &p) {
       return KIND_OTHER;
   }
 }
-// Scheduler-internal kinds of the barrier-free scheduler (transport.cu), on top of kind_of(): a thin-cell r-packet whose
-// step has begun and that waits for its continuum opacity (KIND_KAPPA), and one whose opacity has been delivered
-// (KIND_THIN_RESUME, consumed by the thin role together with KIND_RPKT_THIN). One ring of packet indices per entry.
-constexpr int KIND_KAPPA = NKIND;
-constexpr int KIND_THIN_RESUME = NKIND + 1;
-constexpr int NRING = NKIND + 2;
+ARTIS_DEV int kind_of(const Ctx &c, const Pkt &p) { return kind_of(c, p.type, p.where); }
+// One ring of packet indices per kind (transport.cu).
+constexpr int NRING = NKIND;
 // Ring heads, tails and the active-packet count take every warp's atomics for the whole step: one 128-byte line each, so
 // that they sit in different L2 slices instead of queueing behind one another (words of 8 bytes).
 #ifndef ARTIS_RING_STRIDE
@@ -80,7 +81,6 @@ constexpr int NRING = NKIND + 2;
 #endif
 constexpr int RING_META_STRIDE = ARTIS_RING_STRIDE;
 constexpr int RING_META_WORDS = (2 * NRING + 2) * RING_META_STRIDE;
-ARTIS_DEV bool packet_active(const Ctx &c, const ArtisPacket &p) { return p.type != ARTIS_TYPE_ESCAPE && p.prop_time < c.t2; }
 
 struct QueueView {
   const int *in;        // indices to consume
@@ -91,16 +91,21 @@ struct QueueView {
 };
 
 // K0 bucket_packets: counting sort of the active packets by (kind, model cell) into the initial queues; replaces the
-// std::sort of update_packets.cc:204-256 (dense inner cells first, like the reference's comparator for 1D models).
-ARTIS_DEV int bucket_key(const Ctx &c, const ArtisPacket &p) { return kind_of(c, p) * (c.st.npts_model + 1) + cell_mgi(c, p.where); }
-ARTIS_DEV void body_bucket_hist(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const int idx, int *counts) {
-  ArtisPacket &p = pkts[idx];
-  p.interactions = 0;  // update_packets.cc:282-285, for every packet including the escaped ones
-  p.scat_count = 0;
-  rngctr[idx] = 0ull;  // each packet's Philox stream restarts with the timestep
-  if (packet_active(c, p)) int_add(&counts[bucket_key(c, p)], 1);
+// std::sort of update_packets.cc:204-256 (dense inner cells first, like the reference's comparator for 1D models). Reads
+// and writes sector 0 and the draw counter of the hot record only.
+ARTIS_DEV bool hot_active(const Ctx &c, const PktHot &h) { return pkt_lo16(h.type_cross) != ARTIS_TYPE_ESCAPE && h.prop_time < c.t2; }
+ARTIS_DEV int bucket_key(const Ctx &c, const PktHot &h) {
+  return kind_of(c, pkt_lo16(h.type_cross), h.where) * (c.st.npts_model + 1) + cell_mgi(c, h.where);
 }
-// exclusive prefix sum over the (kind, cell) counts, one thread; also the size of each kind's queue
+ARTIS_DEV void body_bucket_hist(const Ctx &c, PktHot *hot, PktCold *cold, const int idx, int *counts) {
+  PktHot &h = hot[idx];
+  h.interactions = 0;  // update_packets.cc:282-285, for every packet including the escaped ones
+  cold[idx].scat_count = 0;
+  h.rngctr = 0u;       // each packet's Philox stream restarts with the timestep
+  if (hot_active(c, h)) int_add(&counts[bucket_key(c, h)], 1);
+}
+// exclusive prefix sum over the (kind, cell) counts, one thread (host build; the device has k_bucket_scan); also the size
+// of each kind's queue
 ARTIS_DEV void body_bucket_scan(const Ctx &c, int *counts, int *kind_sizes) {
   const int per = c.st.npts_model + 1;
   for (int k = 0; k < NKIND; k++) {
@@ -113,35 +118,33 @@ ARTIS_DEV void body_bucket_scan(const Ctx &c, int *counts, int *kind_sizes) {
     kind_sizes[k] = run;
   }
 }
-ARTIS_DEV void body_bucket_scatter(const Ctx &c, const ArtisPacket *pkts, const int idx, int *offsets, int *const *queues) {
-  const ArtisPacket &p = pkts[idx];
-  if (packet_active(c, p)) queues[kind_of(c, p)][int_fetch_add(&offsets[bucket_key(c, p)], 1)] = idx;
+ARTIS_DEV void body_bucket_scatter(const Ctx &c, const PktHot *hot, const int idx, int *offsets, int *const *queues) {
+  const PktHot &h = hot[idx];
+  if (hot_active(c, h)) queues[kind_of(c, pkt_lo16(h.type_cross), h.where)][int_fetch_add(&offsets[bucket_key(c, h)], 1)] = idx;
 }
 
+// Kernel rounds per kind: the scheduler of the HOST build of these headers (the oracle's debugging aid; one "thread"
+// drains a whole queue). The device runs the barrier-free scheduler of transport.cu instead.
 template <int KIND>
-ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long long *rngctr, const QueueView &qv,
-                              const long long max_events) {
+ARTIS_DEV void body_wavefront(const Ctx &c, PktHot *hot, PktCold *cold, const QueueView &qv, const long long max_events) {
   constexpr int kind = KIND;
   const double t2 = c.t2;
   const int n = *qv.n_in;
   Tally tl = {};
   KappaCache k;
   k.valid = false;
-  // One flat loop: a lane either holds a packet and advances it by one event, or fetches the next queue entry. There is
-  // deliberately no inner per-packet loop, because lanes leaving an inner loop wait at its convergence barrier for the
-  // slowest lane of the warp; here every lane reaches the event code again on the next iteration.
   bool have = false;
   int idx = 0;
   long long events = 0;
-  ArtisPacket p;
+  Pkt p;
   Rng rng;
   while (true) {
     if (!have) {
       const int q = int_fetch_add(qv.head, 1);
       if (q >= n) break;
       idx = qv.in[q];
-      p = pkts[idx];
-      rng = rng_init(c, p.number, rngctr[idx]);
+      pkt_from_hot(p, hot[idx], cold + idx);
+      rng = rng_init(c, p.number, hot[idx].rngctr);
       k.valid = false;
       events = 0;
       have = true;
@@ -151,8 +154,7 @@ ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long lon
     events++;
     const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
     if (!(active && kind_of(c, p) == kind && events < max_events)) {
-      rngctr[idx] = rng.ctr;
-      pkts[idx] = p;
+      pkt_to_hot(hot[idx], p, (unsigned)rng.ctr);
       if (active) {
         const int k2 = kind_of(c, p);
         qv.out[k2][int_fetch_add(qv.n_out[k2], 1)] = idx;
@@ -163,21 +165,34 @@ ARTIS_DEV void body_wavefront(const Ctx &c, ArtisPacket *pkts, unsigned long lon
   tally_flush(c, tl);
 }
 
+// a probe works on a copy of the caller's ABI record
+struct ProbePkt {
+  Pkt p;
+  PktHot hot;
+  PktCold cold;
+};
+ARTIS_DEV void probe_load(ProbePkt &w, const ArtisPacket &a) {
+  pkt_split(a, w.hot, w.cold);
+  pkt_from_hot(w.p, w.hot, &w.cold);
+}
+
 // ---- K10 deterministic probes --------------------------------------------------------------------------------
 ARTIS_DEV void body_probe_boundary(const Ctx &c, const ArtisPacket *pkts, const int idx, double *sdist, int *snext,
                                    int *last_cross_out) {
-  ArtisPacket p = pkts[idx];
+  ProbePkt w;
+  probe_load(w, pkts[idx]);
   int sn = 0;
-  sdist[idx] = boundary_cross(c, p, &sn);
+  sdist[idx] = boundary_cross(c, w.p, &sn);
   snext[idx] = sn;
-  last_cross_out[idx] = p.last_cross;
+  last_cross_out[idx] = w.p.last_cross;
 }
 ARTIS_DEV void body_probe_kappa(const Ctx &c, const ArtisPacket *pkts, const int idx, double *kappa) {
-  const ArtisPacket p = pkts[idx];
+  ProbePkt w;
+  probe_load(w, pkts[idx]);
   KappaCache k;
   k.valid = false;
   Tally tl = {};
-  calculate_kappa_rpkt_cont(c, p, cell_mgi(c, p.where), k, tl);
+  calculate_kappa_rpkt_cont(c, w.p, cell_mgi(c, w.p.where), k, tl);
   kappa[idx * 5 + 0] = k.total;
   kappa[idx * 5 + 1] = k.es;
   kappa[idx * 5 + 2] = k.ff;
@@ -190,7 +205,9 @@ ARTIS_DEV void body_probe_closest(const Ctx &c, const double *nu_cmf, const int 
 ARTIS_DEV void body_probe_get_event(const Ctx &c, const ArtisPacket *pkts, const int idx, const double *tau_rnd,
                                     const double *abort_dist, double *edist, int *eventtype, int *next_trans_out,
                                     int *mastate_out) {
-  ArtisPacket p = pkts[idx];
+  ProbePkt w;
+  probe_load(w, pkts[idx]);
+  Pkt &p = w.p;
   KappaCache k;
   k.valid = false;
   Tally tl = {};
@@ -216,7 +233,9 @@ ARTIS_DEV void body_probe_cooling(const Ctx &c, const int *mgi, const int *eleme
   contrib_total[idx] = c.tb.cool_cum[(size_t)tabcell(c, mgi[idx]) * c.st.ncoolingterms + last];
 }
 ARTIS_DEV void body_probe_gamma_kappa(const Ctx &c, const ArtisPacket *pkts, const int idx, double *kap) {
-  const ArtisPacket p = pkts[idx];
+  ProbePkt w;
+  probe_load(w, pkts[idx]);
+  const Pkt &p = w.p;
   const int mgi = cell_mgi(c, p.where);
   kap[idx * 3 + 0] = sig_comp(c, p, mgi);
   kap[idx * 3 + 1] = sig_photo_electric(c, p, mgi);

@@ -20,7 +20,7 @@ ARTIS_DEV double sample_planck(const Ctx &c, const double T, Rng &rng) {
 }
 
 // kpkt.cc:448-475
-ARTIS_DEV void do_kpkt_bb(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_kpkt_bb(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   const int mgi = cell_mgi(c, p.where);
   const float T_e = c.cs.Te[mgi];
   p.nu_cmf = sample_planck(c, (double)T_e, rng);
@@ -31,7 +31,7 @@ ARTIS_DEV void do_kpkt_bb(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
   p.interactions++;
   tl.interactions++;
   p.last_event = 6;
-  p.emissiontype = -9999999;
+  p.cold->emissiontype = -9999999;
   mark_emission(p);
 }
 
@@ -49,7 +49,7 @@ ARTIS_DEV int lower_bound_idx(const double *cum, int lo, const int hi, const dou
 }
 
 // kpkt.cc:477-797
-ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_kpkt(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
   tl.kpkt_events++;
   const double t1 = p.prop_time;
   const int mgi = cell_mgi(c, p.where);
@@ -104,7 +104,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 6;
-    p.emissiontype = -9999999;
+    p.cold->emissiontype = -9999999;
     mark_emission(p);
     if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 2;  // kpkt.cc:631-634 (t_current == prop_time)
   } else if (type == COOLINGTYPE_FB) {
@@ -118,8 +118,8 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 7;
-    p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, upper);
-    p.trueemissiontype = p.emissiontype;
+    p.cold->emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, upper);
+    p.cold->trueemissiontype = p.cold->emissiontype;
     mark_emission(p);
     if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 2;  // kpkt.cc:691-694
   } else if (type == COOLINGTYPE_COLLEXC) {
@@ -147,8 +147,8 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 8;
-    p.trueemissiontype = -1;
-    p.trueemissionvelocity = -1;
+    p.cold->trueemissiontype = -1;
+    p.cold->trueemissionvelocity = -1;
   } else if (type == COOLINGTYPE_COLLION) {
     p.ma_element = element;
     p.ma_ion = ion + 1;
@@ -160,8 +160,8 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 9;
-    p.trueemissiontype = -1;
-    p.trueemissionvelocity = -1;
+    p.cold->trueemissiontype = -1;
+    p.cold->trueemissionvelocity = -1;
   } else {
     fatal(c, 306);
     p.prop_time = t2;
@@ -172,7 +172,7 @@ ARTIS_DEV void do_kpkt(const Ctx &c, ArtisPacket &p, const double t2, Rng &rng, 
 // lepton thermalises into a k-packet; with it (nebular NLTE) a fraction get_ntion_energyrate / deposition_rate_density
 // activates a macro-atom by non-thermal ionisation (select_nt_ionization2, nonthermal.cc:1858-1875). NT_EXCITATION_ON
 // is false in every shipped options header (frac_excitation = 0., nonthermal.cc:1898).
-ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_ntlepton(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   est_add(&c.es.ts_scalars[ARTIS_TS_NT_ENERGY_DEPOSITED], p.e_cmf);
   const int mgi = cell_mgi(c, p.where);
   if (ARTIS_OPT_NT_SF(c) && c.cs.thick[mgi] != 1) {
@@ -216,8 +216,8 @@ ARTIS_DEV void do_ntlepton(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
       p.interactions += 1;
       tl.interactions++;
       p.last_event = 20;
-      p.trueemissiontype = -1;
-      p.trueemissionvelocity = -1;
+      p.cold->trueemissiontype = -1;
+      p.cold->trueemissionvelocity = -1;
       stat_inc(tl, COUNTER_NT_STAT_TO_IONIZATION);
       return;
     }

@@ -128,255 +128,269 @@ ARTIS_DEV double select_continuum_nu(const Ctx &c, const int ui_lower, const int
 }
 
 // common tail of every r-packet emission from a macro-atom / k-packet
-ARTIS_DEV void mark_emission(ArtisPacket &p) {
-  p.em_pos[0] = p.pos[0];
-  p.em_pos[1] = p.pos[1];
-  p.em_pos[2] = p.pos[2];
-  p.em_time = (int)p.prop_time;
-  p.nscatterings = 0;
+ARTIS_DEV void mark_emission(Pkt &p) {
+  p.cold->em_pos[0] = p.pos[0];
+  p.cold->em_pos[1] = p.pos[1];
+  p.cold->em_pos[2] = p.pos[2];
+  p.cold->em_time = (int)p.prop_time;
+  p.cold->nscatterings = 0;
 }
 
 // macroatom.cc:416-901 do_macroatom, ONE iteration of its `while (!end_packet)` loop per call: the macro-atom state
 // (ion, level) lives in the packet's mastate between calls, so that all lanes of a warp that hold an activated
 // macro-atom take their jumps in lock step and the scheduler can interleave packet kinds (the reference keeps the
 // state in locals and never reads mastate again after the chain has started, so nothing observable changes).
-ARTIS_DEV void do_macroatom(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+//
+// The iteration is written in two parts, because 98 % of them are jumps within the ion and need nothing but the
+// macro-atom state, one row of process rates and one search over a prefix-sum row:
+//   ma_jump   draws the action and, for the three list-driven actions, the transition; completes the jump when it stays
+//             inside the ion (internal down / up: the new level is all that changes); otherwise returns the action.
+//             Works on any packet view with where, ma_element, ma_ion, ma_level, interactions -- the scheduler's jump
+//             role runs it on 32 bytes of the packet, at a small register budget and therefore many resident warps.
+//   ma_event  completes the other actions (de-activations with their emission, jumps to another ion) on the full packet.
+// Run back to back they draw the same numbers in the same order as the one-piece loop body of the reference.
+constexpr int MA_ACTION_FATAL = 99;  // ma_jump hit one of the reference's abort() branches; ma_event parks the packet
+template <class P>
+ARTIS_DEV int ma_jump(const Ctx &c, P &p, Rng &rng, Tally &tl, int *sel_out) {
   const int mgi = cell_mgi(c, p.where);
   const int tc = tabcell(c, mgi);
-  const float T_e = c.cs.Te[mgi];
-  const float nne = c.cs.nne[mgi];
+  *sel_out = 0;
   if (c.cs.thick[mgi] == 1 || tc < 0) {
     fatal(c, 220);
-    p.type = ARTIS_TYPE_KPKT;
+    return MA_ACTION_FATAL;
+  }
+  const int ui = uion_of(c, p.ma_element, p.ma_ion);
+  const int gl = c.st.ion_leveloffset[ui] + p.ma_level;
+  tl.ma_jumps++;
+  const double *processrates = tab_ma_rates(c, tc, gl);
+  double pr[MA_ACTION_COUNT];
+  double total_transitions = 0.;
+  for (int a = 0; a < MA_ACTION_COUNT; a++) {
+    pr[a] = processrates[a];
+    total_transitions += pr[a];
+  }
+  const double randomrate = rng_uniform(rng) * total_transitions;
+  double rate = 0., pr_sel = 0.;
+  int selected_action = MA_ACTION_COUNT;
+  for (int a = 0; a < MA_ACTION_COUNT; a++) {  // first action whose running sum exceeds the draw (macroatom.cc:470-478)
+    rate += pr[a];
+    if (selected_action == MA_ACTION_COUNT && rate > randomrate) {
+      selected_action = a;
+      pr_sel = pr[a];
+    }
+  }
+  if (selected_action == MA_ACTION_COUNT) {  // reference: "[fatal] do_ma: problem with random numbers" + abort
+    fatal(c, 221);
+    return MA_ACTION_FATAL;
+  }
+  // The three list-driven actions (radiative de-excitation, internal jump down / up within the ion) share one draw and
+  // one search over a per-cell prefix-sum row.
+  const double *cum = nullptr;
+  int ntrans = 0, toff = 0;
+  if (selected_action == MA_RADDEEXC || selected_action == MA_INTERNALDOWNSAME) {
+    ntrans = c.st.lev_ndowntrans[gl];
+    toff = c.st.lev_downoffset[gl];
+    cum = (selected_action == MA_RADDEEXC ? c.tb.ma_cum_raddeexc : c.tb.ma_cum_intdown) + (size_t)tc * c.st.ndowntrans_total + toff;
+  } else if (selected_action == MA_INTERNALUPSAME) {
+    ntrans = c.st.lev_nuptrans[gl];
+    toff = c.st.lev_upoffset[gl];
+    cum = c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + toff;
+  }
+  if (cum == nullptr) return selected_action;
+  const double zrand = rng_uniform(rng);
+  const int sel = first_greater(cum, ntrans, zrand * pr_sel);
+  tl.ma_trans_scanned += bsearch_probes(ntrans);
+  if (sel >= ntrans) {
+    fatal(c, selected_action == MA_RADDEEXC ? 222 : (selected_action == MA_INTERNALDOWNSAME ? 223 : 227));
+    return MA_ACTION_FATAL;
+  }
+  *sel_out = toff + sel;
+  if (selected_action == MA_RADDEEXC) return selected_action;
+  // internal jump within the ion (macroatom.cc:174-220, 815-835): remember where the macro-atom is
+  p.interactions += 1;
+  tl.interactions++;
+  const int gl_new = selected_action == MA_INTERNALDOWNSAME ? c.downtrans_target_g[toff + sel] : c.uptrans_target_g[toff + sel];
+  p.ma_level = gl_new - c.st.ion_leveloffset[ui];
+  return -1;
+}
+
+// `action` and `selidx` are what ma_jump returned (selidx: index of the selected downward transition for MA_RADDEEXC)
+ARTIS_DEV void ma_event(const Ctx &c, Pkt &p, const int action, const int selidx, Rng &rng, Tally &tl) {
+  if (action == MA_ACTION_FATAL) {
+    p.type = ARTIS_TYPE_KPKT;  // park the packet; the run is reported as failed
     return;
   }
+  const int mgi = cell_mgi(c, p.where);
+  const float T_e = c.cs.Te[mgi];
+  const float nne = c.cs.nne[mgi];
   const int element = p.ma_element;
   int ui = uion_of(c, element, p.ma_ion);
   int gl = c.st.ion_leveloffset[ui] + p.ma_level;
   const int activatingline = p.ma_activatingline;
-
+  const int level = p.ma_level;
+  const double epsilon_current = c.st.lev_epsilon[gl];
+  const double pr_sel = tab_ma_rates(c, tabcell(c, mgi), gl)[action < MA_ACTION_COUNT ? action : 0];
   bool end_packet = false;
-  {
-    tl.ma_jumps++;
-    const double epsilon_current = c.st.lev_epsilon[gl];
-    const double *processrates = tab_ma_rates(c, tc, gl);
-    double pr[MA_ACTION_COUNT];
-    double total_transitions = 0.;
-    for (int a = 0; a < MA_ACTION_COUNT; a++) {
-      pr[a] = processrates[a];
-      total_transitions += pr[a];
+  switch (action) {
+    case MA_RADDEEXC: {  // macroatom.cc:222-296
+      const int linelistindex = c.st.downtrans_lineindex[selidx];
+      if (c.st.opt_record_linestat) int_add(&c.es.ecounter[linelistindex], 1);
+      const int gll = c.line_lower_g[linelistindex];
+      const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gll];
+      const double oldnucmf = p.nu_cmf;
+      p.nu_cmf = epsilon_trans / H;
+      if (p.last_event == 1) stat_inc(tl, oldnucmf < p.nu_cmf ? COUNTER_UPSCATTER : COUNTER_DOWNSCATTER);
+      stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_BB);
+      p.interactions += 1;
+      tl.interactions++;
+      p.last_event = 0;
+      emitt_rpkt(c, p, rng);
+      if (linelistindex == activatingline) stat_inc(tl, COUNTER_RESONANCESCATTERINGS);
+      p.next_trans = linelistindex + 1;
+      p.cold->emissiontype = linelistindex;
+      mark_emission(p);
+      if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 3;  // macroatom.cc:292-295
+      end_packet = true;
+      break;
     }
-    const double randomrate = rng_uniform(rng) * total_transitions;
-    double rate = 0., pr_sel = 0.;
-    int selected_action = MA_ACTION_COUNT;
-    for (int a = 0; a < MA_ACTION_COUNT; a++) {  // first action whose running sum exceeds the draw (macroatom.cc:470-478)
-      rate += pr[a];
-      if (selected_action == MA_ACTION_COUNT && rate > randomrate) {
-        selected_action = a;
-        pr_sel = pr[a];
-      }
-    }
-    if (selected_action == MA_ACTION_COUNT) {  // reference: "[fatal] do_ma: problem with random numbers" + abort
-      fatal(c, 221);
+    case MA_COLDEEXC: {
+      stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_COLLDEEXC);
+      p.interactions += 1;
+      tl.interactions++;
+      p.last_event = 10;
       p.type = ARTIS_TYPE_KPKT;
-      return;
+      end_packet = true;
+      tl.estim_atomics += est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
+      break;
     }
-    // The three list-driven actions (radiative de-excitation, internal jump down / up within the ion) share one draw and
-    // one search over a per-cell prefix-sum row; doing it here, before the per-action switch, keeps the lanes of a warp
-    // converged through the expensive part of a jump whatever action each of them selected.
-    int sel = -1, toff = 0;
-    {
-      const double *cum = nullptr;
-      int ntrans = 0;
-      if (selected_action == MA_RADDEEXC || selected_action == MA_INTERNALDOWNSAME) {
-        ntrans = c.st.lev_ndowntrans[gl];
-        toff = c.st.lev_downoffset[gl];
-        cum = (selected_action == MA_RADDEEXC ? c.tb.ma_cum_raddeexc : c.tb.ma_cum_intdown) +
-              (size_t)tc * c.st.ndowntrans_total + toff;
-      } else if (selected_action == MA_INTERNALUPSAME) {
-        ntrans = c.st.lev_nuptrans[gl];
-        toff = c.st.lev_upoffset[gl];
-        cum = c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + toff;
+    case MA_RADRECOMB: {  // macroatom.cc:298-380
+      const int gl0_lower = c.st.ion_leveloffset[ui - 1];
+      const int nlevels = c.st.ion_ionisinglevels[ui - 1];
+      const double zrand = rng_uniform(rng);
+      double rrate = 0.;
+      int lower;
+      for (lower = 0; lower < nlevels; lower++) {
+        const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gl0_lower + lower];
+        const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
+        rrate += R * epsilon_trans;
+        if (zrand * pr_sel < rrate) break;
       }
-      if (cum != nullptr) {
-        const double zrand = rng_uniform(rng);
-        sel = first_greater(cum, ntrans, zrand * pr_sel);
-        tl.ma_trans_scanned += bsearch_probes(ntrans);
-        if (sel >= ntrans) {
-          fatal(c, selected_action == MA_RADDEEXC ? 222 : (selected_action == MA_INTERNALDOWNSAME ? 223 : 227));
-          p.type = ARTIS_TYPE_KPKT;
-          return;
-        }
-      }
-    }
-    const int level = gl - c.st.ion_leveloffset[ui];
-    switch (selected_action) {
-      case MA_RADDEEXC: {  // macroatom.cc:222-296
-        const int linelistindex = c.st.downtrans_lineindex[toff + sel];
-        if (c.st.opt_record_linestat) int_add(&c.es.ecounter[linelistindex], 1);
-        const int gll = c.line_lower_g[linelistindex];
-        const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gll];
-        const double oldnucmf = p.nu_cmf;
-        p.nu_cmf = epsilon_trans / H;
-        if (p.last_event == 1) stat_inc(tl, oldnucmf < p.nu_cmf ? COUNTER_UPSCATTER : COUNTER_DOWNSCATTER);
-        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_BB);
-        p.interactions += 1;
-        tl.interactions++;
-        p.last_event = 0;
-        emitt_rpkt(c, p, rng);
-        if (linelistindex == activatingline) stat_inc(tl, COUNTER_RESONANCESCATTERINGS);
-        p.next_trans = linelistindex + 1;
-        p.emissiontype = linelistindex;
-        mark_emission(p);
-        if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 3;  // macroatom.cc:292-295
-        end_packet = true;
-        break;
-      }
-      case MA_COLDEEXC: {
-        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_COLLDEEXC);
-        p.interactions += 1;
-        tl.interactions++;
-        p.last_event = 10;
-        p.type = ARTIS_TYPE_KPKT;
-        end_packet = true;
-        tl.estim_atomics += est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
-        break;
-      }
-      case MA_INTERNALDOWNSAME: {  // macroatom.cc:174-220
-        p.interactions += 1;
-        tl.interactions++;
-        gl = c.downtrans_target_g[toff + sel];
-        break;
-      }
-      case MA_RADRECOMB: {  // macroatom.cc:298-380
-        const int gl0_lower = c.st.ion_leveloffset[ui - 1];
-        const int nlevels = c.st.ion_ionisinglevels[ui - 1];
-        const double zrand = rng_uniform(rng);
-        double rrate = 0.;
-        int lower;
-        for (lower = 0; lower < nlevels; lower++) {
-          const double epsilon_trans = epsilon_current - c.st.lev_epsilon[gl0_lower + lower];
-          const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
-          rrate += R * epsilon_trans;
-          if (zrand * pr_sel < rrate) break;
-        }
-        tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
-        if (zrand * pr_sel >= rrate) {
-          fatal(c, 224);
-          p.type = ARTIS_TYPE_KPKT;
-          return;
-        }
-        const int gl_lower = gl0_lower + lower;
-        p.nu_cmf = select_continuum_nu(c, ui - 1, gl_lower, level, T_e, rng);
-        if (!isfinite(p.nu_cmf)) fatal(c, 225);
-        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_FB);
-        p.interactions += 1;
-        tl.interactions++;
-        p.last_event = 2;
-        emitt_rpkt(c, p, rng);
-        p.next_trans = 0;
-        p.emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, level);
-        mark_emission(p);
-        if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 3;  // macroatom.cc:376-379
-        ui -= 1;
-        gl = gl_lower;
-        end_packet = true;
-        break;
-      }
-      case MA_COLRECOMB: {
-        stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_COLLRECOMB);
-        p.interactions += 1;
-        tl.interactions++;
-        p.last_event = 11;
-        p.type = ARTIS_TYPE_KPKT;
-        end_packet = true;
-        tl.estim_atomics += est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
-        break;
-      }
-      case MA_INTERNALDOWNLOWER: {  // macroatom.cc:766-813
-        p.interactions += 1;
-        tl.interactions++;
-        stat_inc(tl, COUNTER_MA_STAT_INTERNALDOWNLOWER);
-        const double zrand = rng_uniform(rng);
-        const int gl0_lower = c.st.ion_leveloffset[ui - 1];
-        const int nlevels = c.st.ion_ionisinglevels[ui - 1];
-        double rrate = 0.;
-        int lower;
-        for (lower = 0; lower < nlevels; lower++) {
-          const double epsilon_target = c.st.lev_epsilon[gl0_lower + lower];
-          const double epsilon_trans = epsilon_current - epsilon_target;
-          const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
-          const double C = col_recombination_ratecoeff(c, mgi, ui, gl, gl0_lower + lower, epsilon_trans);
-          rrate += (R + C) * epsilon_target;
-          if (zrand * pr_sel < rrate) break;
-        }
-        tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
-        if (lower >= nlevels) {
-          fatal(c, 226);
-          p.type = ARTIS_TYPE_KPKT;
-          return;
-        }
-        ui -= 1;
-        gl = gl0_lower + lower;
-        break;
-      }
-      case MA_INTERNALUPSAME: {  // macroatom.cc:815-835
-        p.interactions += 1;
-        tl.interactions++;
-        gl = c.uptrans_target_g[toff + sel];
-        break;
-      }
-      case MA_INTERNALUPHIGHER: {  // macroatom.cc:382-414 do_macroatom_ionisation
-        p.interactions += 1;
-        tl.interactions++;
-        stat_inc(tl, COUNTER_MA_STAT_INTERNALUPHIGHER);
-        const double zrand = rng_uniform(rng);
-        const int ntargets = c.st.lev_nphixstargets[gl];
-        double rrate = 0.;
-        int upper = -1;
-        for (int t = 0; t < ntargets; t++) {
-          upper = c.st.phixstarget_level[c.st.lev_phixstargetoffset[gl] + t];
-          const double epsilon_trans = phixs_threshold(c, ui, gl, t);
-          const double R = get_corrphotoioncoeff(c, mgi, gl, t);
-          const double C = col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans);
-          rrate += (R + C) * epsilon_current;
-          if (zrand * pr_sel < rrate) break;
-        }
-        if (zrand * pr_sel >= rrate || upper < 0) {
-          fatal(c, 228);
-          p.type = ARTIS_TYPE_KPKT;
-          return;
-        }
-        ui += 1;
-        gl = c.st.ion_leveloffset[ui] + upper;
-        break;
-      }
-      case MA_INTERNALUPHIGHERNT: {  // macroatom.cc:856-876: non-thermal ionisation to the ground level of a higher ion
-        p.interactions += 1;
-        tl.interactions++;
-        const int ion = ui - c.st.el_ionoffset[element];
-        ui += nt_random_upperion(c, mgi, ui, c.st.el_nions[element], ion, false, rng);
-        gl = c.st.ion_leveloffset[ui];
-        stat_inc(tl, COUNTER_MA_STAT_INTERNALUPHIGHERNT);
-        break;
-      }
-      default:
-        fatal(c, 229);
+      tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
+      if (zrand * pr_sel >= rrate) {
+        fatal(c, 224);
         p.type = ARTIS_TYPE_KPKT;
         return;
+      }
+      const int gl_lower = gl0_lower + lower;
+      p.nu_cmf = select_continuum_nu(c, ui - 1, gl_lower, level, T_e, rng);
+      if (!isfinite(p.nu_cmf)) fatal(c, 225);
+      stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_FB);
+      p.interactions += 1;
+      tl.interactions++;
+      p.last_event = 2;
+      emitt_rpkt(c, p, rng);
+      p.next_trans = 0;
+      p.cold->emissiontype = c.st.lev_cont_index[gl_lower] - phixstargetindex_of(c, gl_lower, level);
+      mark_emission(p);
+      if (ARTIS_OPT_VPKT(c)) tl.vpkt_req = 3;  // macroatom.cc:376-379
+      ui -= 1;
+      gl = gl_lower;
+      end_packet = true;
+      break;
     }
+    case MA_COLRECOMB: {
+      stat_inc(tl, COUNTER_MA_STAT_DEACTIVATION_COLLRECOMB);
+      p.interactions += 1;
+      tl.interactions++;
+      p.last_event = 11;
+      p.type = ARTIS_TYPE_KPKT;
+      end_packet = true;
+      tl.estim_atomics += est_add(&c.es.colheatingestimator[mgi], p.e_cmf);
+      break;
+    }
+    case MA_INTERNALDOWNLOWER: {  // macroatom.cc:766-813
+      p.interactions += 1;
+      tl.interactions++;
+      stat_inc(tl, COUNTER_MA_STAT_INTERNALDOWNLOWER);
+      const double zrand = rng_uniform(rng);
+      const int gl0_lower = c.st.ion_leveloffset[ui - 1];
+      const int nlevels = c.st.ion_ionisinglevels[ui - 1];
+      double rrate = 0.;
+      int lower;
+      for (lower = 0; lower < nlevels; lower++) {
+        const double epsilon_target = c.st.lev_epsilon[gl0_lower + lower];
+        const double epsilon_trans = epsilon_current - epsilon_target;
+        const double R = rad_recombination_ratecoeff(c, T_e, nne, gl0_lower + lower, level);
+        const double C = col_recombination_ratecoeff(c, mgi, ui, gl, gl0_lower + lower, epsilon_trans);
+        rrate += (R + C) * epsilon_target;
+        if (zrand * pr_sel < rrate) break;
+      }
+      tl.ma_trans_scanned += 3 * nlevels;  // LUT rows read per lower level
+      if (lower >= nlevels) {
+        fatal(c, 226);
+        p.type = ARTIS_TYPE_KPKT;
+        return;
+      }
+      ui -= 1;
+      gl = gl0_lower + lower;
+      break;
+    }
+    case MA_INTERNALUPHIGHER: {  // macroatom.cc:382-414 do_macroatom_ionisation
+      p.interactions += 1;
+      tl.interactions++;
+      stat_inc(tl, COUNTER_MA_STAT_INTERNALUPHIGHER);
+      const double zrand = rng_uniform(rng);
+      const int ntargets = c.st.lev_nphixstargets[gl];
+      double rrate = 0.;
+      int upper = -1;
+      for (int t = 0; t < ntargets; t++) {
+        upper = c.st.phixstarget_level[c.st.lev_phixstargetoffset[gl] + t];
+        const double epsilon_trans = phixs_threshold(c, ui, gl, t);
+        const double R = get_corrphotoioncoeff(c, mgi, gl, t);
+        const double C = col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans);
+        rrate += (R + C) * epsilon_current;
+        if (zrand * pr_sel < rrate) break;
+      }
+      if (zrand * pr_sel >= rrate || upper < 0) {
+        fatal(c, 228);
+        p.type = ARTIS_TYPE_KPKT;
+        return;
+      }
+      ui += 1;
+      gl = c.st.ion_leveloffset[ui] + upper;
+      break;
+    }
+    case MA_INTERNALUPHIGHERNT: {  // macroatom.cc:856-876: non-thermal ionisation to the ground level of a higher ion
+      p.interactions += 1;
+      tl.interactions++;
+      const int ion = ui - c.st.el_ionoffset[element];
+      ui += nt_random_upperion(c, mgi, ui, c.st.el_nions[element], ion, false, rng);
+      gl = c.st.ion_leveloffset[ui];
+      stat_inc(tl, COUNTER_MA_STAT_INTERNALUPHIGHERNT);
+      break;
+    }
+    default:
+      fatal(c, 229);
+      p.type = ARTIS_TYPE_KPKT;
+      return;
   }
-  if (!end_packet) {  // internal jump: remember where the macro-atom is
+  if (!end_packet) {  // jump to another ion: remember where the macro-atom is
     p.ma_ion = ui - c.st.el_ionoffset[element];
     p.ma_level = gl - c.st.ion_leveloffset[ui];
     return;
   }
-  if (p.trueemissiontype < 0) {  // macroatom.cc:894-898
-    p.trueemissiontype = p.emissiontype;
-    double ep[3] = {p.em_pos[0], p.em_pos[1], p.em_pos[2]};
-    p.trueemissionvelocity = (float)(vec_len(ep) / p.em_time);
-    p.trueem_time = p.em_time;
+  if (ldcold(&p.cold->trueemissiontype) < 0) {  // macroatom.cc:894-898
+    p.cold->trueemissiontype = ldcold(&p.cold->emissiontype);
+    double ep[3] = {ldcold(&p.cold->em_pos[0]), ldcold(&p.cold->em_pos[1]), ldcold(&p.cold->em_pos[2])};
+    const int em_time = ldcold(&p.cold->em_time);
+    p.cold->trueemissionvelocity = (float)(vec_len(ep) / em_time);
+    p.cold->trueem_time = em_time;
   }
+}
+ARTIS_DEV void do_macroatom(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+  int selidx;
+  const int action = ma_jump(c, p, rng, tl, &selidx);
+  if (action >= 0) ma_event(c, p, action, selidx, rng, tl);
 }
 
 }  // namespace artis

@@ -234,10 +234,10 @@ ARTIS_DEV double boundary_cross(const Ctx &c, P &p, int *snext) {
 }
 
 // boundary.cc:332-357 change_cell
-ARTIS_DEV void change_cell(const Ctx &c, ArtisPacket &p, int snext, Tally &tl) {
+ARTIS_DEV void change_cell(const Ctx &c, Pkt &p, int snext, Tally &tl) {
   if (snext == -99) {
-    p.escape_type = p.type;
-    p.escape_time = (int)p.prop_time;  // int field
+    p.cold->escape_type = p.type;
+    p.cold->escape_time = (int)p.prop_time;  // int field
     p.type = ARTIS_TYPE_ESCAPE;
     stat_inc(tl, COUNTER_NESC);
   } else {
@@ -272,7 +272,7 @@ ARTIS_DEV int closest_transition(const Ctx &c, const double nu_cmf, const int ne
 // rpkt.cc:511-555 closest_transition_empty. Where the reference reads past the end of the line list
 // (left > right) or calls lower_bound on an inverted range, every outcome means "no more lines"; nlines+1 is
 // what the reference stores in those cases.
-ARTIS_DEV void closest_transition_empty(const Ctx &c, ArtisPacket &p) {
+ARTIS_DEV void closest_transition_empty(const Ctx &c, Pkt &p) {
   const int left = p.next_trans;
   const int right = c.st.nlines - 1;
   if (left > right) {
@@ -492,7 +492,7 @@ ARTIS_DEV void calculate_kappa_rpkt_cont(const Ctx &c, const P &p, const int mgi
 
 // ---- rpkt.cc:67-328 get_event ---------------------------------------------------------------------------------------
 // `p` is only modified where the reference modifies pkt_ptr: next_trans and mastate.
-ARTIS_DEV double get_event(const Ctx &c, const int mgi, ArtisPacket &p, int *rpkt_eventtype, const double tau_rnd,
+ARTIS_DEV double get_event(const Ctx &c, const int mgi, Pkt &p, int *rpkt_eventtype, const double tau_rnd,
                            const double abort_dist, KappaCache &k, Tally &tl) {
   double tau = 0., dist = 0., edist = 0.;
   Ray abortray = ray_of(p);

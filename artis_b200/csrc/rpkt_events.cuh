@@ -25,7 +25,7 @@ ARTIS_DEV void bfest_sweep(const Ctx &c, const int tc, const int mgi, const doub
     }
   }
 }
-ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const double distance, KappaCache &k, Tally &tl) {
+ARTIS_DEV void update_estimators(const Ctx &c, const Pkt &p, const double distance, KappaCache &k, Tally &tl) {
   const int mgi = cell_mgi(c, p.where);
   if (mgi == c.st.npts_model) return;
   const double distance_e_cmf = distance * p.e_cmf;
@@ -91,7 +91,7 @@ ARTIS_DEV void update_estimators(const Ctx &c, const ArtisPacket &p, const doubl
     }
   }
 }
-ARTIS_DEV void rlc_emiss_rpkt(const Ctx &c, const ArtisPacket &p, const double dist, Tally &tl) {
+ARTIS_DEV void rlc_emiss_rpkt(const Ctx &c, const Pkt &p, const double dist, Tally &tl) {
   const int mgi = cell_mgi(c, p.where);
   if (dist > 0.0) {
     double vel_vec[3];
@@ -103,17 +103,21 @@ ARTIS_DEV void rlc_emiss_rpkt(const Ctx &c, const ArtisPacket &p, const double d
 }
 
 // ---- rpkt.cc:975-1025 emitt_rpkt ---------------------------------------------------------------------------------------
-ARTIS_DEV void set_pol_dir(ArtisPacket &p) {
+ARTIS_DEV void set_pol_dir(Pkt &p) {
   double dummy_dir[3] = {0., 0., 1.};
-  cross_prod(p.dir, dummy_dir, p.pol_dir);
-  if (dot3(p.pol_dir, p.pol_dir) < 1.e-8) {
+  double pol_dir[3];
+  cross_prod(p.dir, dummy_dir, pol_dir);
+  if (dot3(pol_dir, pol_dir) < 1.e-8) {
     dummy_dir[0] = dummy_dir[2] = 0.0;
     dummy_dir[1] = 1.0;
-    cross_prod(p.dir, dummy_dir, p.pol_dir);
+    cross_prod(p.dir, dummy_dir, pol_dir);
   }
-  vec_norm(p.pol_dir, p.pol_dir);
+  vec_norm(pol_dir, pol_dir);
+  p.cold->pol_dir[0] = pol_dir[0];
+  p.cold->pol_dir[1] = pol_dir[1];
+  p.cold->pol_dir[2] = pol_dir[2];
 }
-ARTIS_DEV void emitt_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
+ARTIS_DEV void emitt_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
   p.type = ARTIS_TYPE_RPKT;
   p.last_cross = ARTIS_CROSS_NONE;
   double dir_cmf[3];
@@ -124,9 +128,9 @@ ARTIS_DEV void emitt_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
   const double dopplerfactor = doppler_packet(c, p);
   p.nu_rf = p.nu_cmf / dopplerfactor;
   p.e_rf = p.e_cmf / dopplerfactor;
-  p.stokes[0] = 1.;
-  p.stokes[1] = 0.;
-  p.stokes[2] = 0.;
+  p.cold->stokes[0] = 1.;
+  p.cold->stokes[1] = 0.;
+  p.cold->stokes[2] = 0.;
   set_pol_dir(p);
 }
 
@@ -225,12 +229,12 @@ ARTIS_DEV void frame_transform(const double *n_rf, double *Q, double *U, const d
 }
 
 // ---- polarization.cc:6-140 escat_rpkt ----------------------------------------------------------------------------------
-ARTIS_DEV void escat_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
+ARTIS_DEV void escat_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
   p.type = ARTIS_TYPE_RPKT;
   p.last_cross = ARTIS_CROSS_NONE;
   double vel_vec[3];
   get_velocity(p.pos, vel_vec, p.prop_time);
-  double Qi = p.stokes[1], Ui = p.stokes[2];
+  double Qi = ldcold(&p.cold->stokes[1]), Ui = ldcold(&p.cold->stokes[2]);
   double old_dir_cmf[3];
   frame_transform(p.dir, &Qi, &Ui, vel_vec, old_dir_cmf);
   double M = 0., mu = 0., phisc = 0.;
@@ -287,9 +291,9 @@ ARTIS_DEV void escat_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
   double vel_rev[3] = {-vel_vec[0], -vel_vec[1], -vel_vec[2]};
   double dummy_dir[3];
   frame_transform(new_dir_cmf, &Q, &U, vel_rev, dummy_dir);
-  p.stokes[0] = 1.0;
-  p.stokes[1] = Q;
-  p.stokes[2] = U;
+  p.cold->stokes[0] = 1.0;
+  p.cold->stokes[1] = Q;
+  p.cold->stokes[2] = U;
   p.dir[0] = dummy_dir[0];
   p.dir[1] = dummy_dir[1];
   p.dir[2] = dummy_dir[2];
@@ -303,7 +307,7 @@ ARTIS_DEV void escat_rpkt(const Ctx &c, ArtisPacket &p, Rng &rng) {
 #include "vpkt.cuh"
 namespace artis {
 
-ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
+ARTIS_DEV void rpkt_event_continuum(const Ctx &c, Pkt &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
   const double nu = p.nu_cmf;
   const double dopplerfactor = doppler_packet(c, p);
   const double kappa_cont = k.total * dopplerfactor;
@@ -314,7 +318,7 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
   if (zrand * kappa_cont < sigma) {
     p.interactions += 1;
     tl.interactions++;
-    p.nscatterings += 1;
+    p.cold->nscatterings = ldcold(&p.cold->nscatterings) + 1;
     p.last_event = 12;
     stat_inc(tl, COUNTER_ESCOUNTER);
     if (ARTIS_OPT_VPKT(c)) {  // rpkt.cc:359-363: virtual packets see the packet as it arrives at the scattering
@@ -323,23 +327,23 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
       tl.vpkt_dir[0] = p.dir[0];
       tl.vpkt_dir[1] = p.dir[1];
       tl.vpkt_dir[2] = p.dir[2];
-      tl.vpkt_q = p.stokes[1];
-      tl.vpkt_u = p.stokes[2];
+      tl.vpkt_q = ldcold(&p.cold->stokes[1]);
+      tl.vpkt_u = ldcold(&p.cold->stokes[2]);
     }
     escat_rpkt(c, p, rng);
-    p.em_pos[0] = p.pos[0];
-    p.em_pos[1] = p.pos[1];
-    p.em_pos[2] = p.pos[2];
-    p.em_time = (int)p.prop_time;
+    p.cold->em_pos[0] = p.pos[0];
+    p.cold->em_pos[1] = p.pos[1];
+    p.cold->em_pos[2] = p.pos[2];
+    p.cold->em_time = (int)p.prop_time;
   } else if (zrand * kappa_cont < sigma + kappa_ff) {
     stat_inc(tl, COUNTER_K_STAT_FROM_FF);
     p.interactions += 1;
     tl.interactions++;
     p.last_event = 5;
     p.type = ARTIS_TYPE_KPKT;
-    p.absorptiontype = -1;
+    p.cold->absorptiontype = -1;
   } else if (zrand * kappa_cont < sigma + kappa_ff + kappa_bf) {
-    p.absorptiontype = -2;
+    p.cold->absorptiontype = -2;
     const double kappa_bf_inrest = k.bf;
     const double zrand2 = rng_uniform(rng);
     const double kappa_bf_rand = zrand2 * kappa_bf_inrest;
@@ -394,31 +398,31 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, ArtisPacket &p, const KappaCac
 }
 
 // rpkt.cc:449-489
-ARTIS_DEV void rpkt_event_boundbound(const Ctx &c, ArtisPacket &p, Tally &tl) {
+ARTIS_DEV void rpkt_event_boundbound(const Ctx &c, Pkt &p, Tally &tl) {
   stat_inc(tl, COUNTER_MA_STAT_ACTIVATION_BB);
   p.interactions += 1;
   tl.interactions++;
   p.last_event = 1;
-  p.absorptiontype = p.ma_activatingline;
-  p.absorptionfreq = p.nu_rf;
-  p.absorptiondir[0] = p.dir[0];
-  p.absorptiondir[1] = p.dir[1];
-  p.absorptiondir[2] = p.dir[2];
+  p.cold->absorptiontype = p.ma_activatingline;
+  p.cold->absorptionfreq = p.nu_rf;
+  p.cold->absorptiondir[0] = p.dir[0];
+  p.cold->absorptiondir[1] = p.dir[1];
+  p.cold->absorptiondir[2] = p.dir[2];
   p.type = ARTIS_TYPE_MA;
   if (c.st.opt_record_linestat) int_add(&c.es.acounter[p.next_trans - 1], 1);  // all threads
 }
 // rpkt.cc:491-509
-ARTIS_DEV void rpkt_event_thickcell(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void rpkt_event_thickcell(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   p.interactions += 1;
   tl.interactions++;
-  p.nscatterings += 1;
+  p.cold->nscatterings = ldcold(&p.cold->nscatterings) + 1;
   p.last_event = 12;
   stat_inc(tl, COUNTER_ESCOUNTER);
   emitt_rpkt(c, p, rng);
-  p.em_pos[0] = p.pos[0];
-  p.em_pos[1] = p.pos[1];
-  p.em_pos[2] = p.pos[2];
-  p.em_time = (int)p.prop_time;
+  p.cold->em_pos[0] = p.pos[0];
+  p.cold->em_pos[1] = p.pos[1];
+  p.cold->em_pos[2] = p.pos[2];
+  p.cold->em_time = (int)p.prop_time;
 }
 
 // ---- rpkt.cc:623-813 do_rpkt_step ----------------------------------------------------------------------------------------
@@ -432,11 +436,11 @@ struct RpktStepState {
   int mgi_next;  // model cell of snext, requested as soon as snext is known so that the gather flies during the move
   double tau_next, sdist;
 };
-ARTIS_DEV int rpkt_step_mgi_next(const Ctx &c, const ArtisPacket &p, const RpktStepState &st) {
+ARTIS_DEV int rpkt_step_mgi_next(const Ctx &c, const Pkt &p, const RpktStepState &st) {
   return (st.snext >= 0 && st.snext != p.where) ? cell_mgi(c, st.snext) : st.mgi;
 }
 template <int MODE = 0>
-ARTIS_DEV bool rpkt_step_begin(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl, RpktStepState &st) {
+ARTIS_DEV bool rpkt_step_begin(const Ctx &c, Pkt &p, Rng &rng, Tally &tl, RpktStepState &st) {
   tl.rpkt_steps++;
   st.mgi = cell_mgi(c, p.where);
   const double zrand = rng_uniform_pos(rng);
@@ -468,7 +472,7 @@ ARTIS_DEV bool rpkt_step_begin(const Ctx &c, ArtisPacket &p, Rng &rng, Tally &tl
   return true;
 }
 template <int MODE = 0>
-ARTIS_DEV bool rpkt_step_finish(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl,
+ARTIS_DEV bool rpkt_step_finish(const Ctx &c, Pkt &p, const double t2, KappaCache &k, Rng &rng, Tally &tl,
                                 const RpktStepState &st) {
   int mgi = st.mgi;
   const double tau_next = st.tau_next;
@@ -529,7 +533,7 @@ ARTIS_DEV bool rpkt_step_finish(const Ctx &c, ArtisPacket &p, const double t2, K
       change_cell(c, p, snext, tl);
       mgi = st.mgi_next;  // = cell_mgi(c, p.where), also when the packet escaped and stays where it is
     }
-    p.scat_count = 0;
+    // scat_count = 0 (rpkt.cc:729): it is already 0, update_packets cleared it for every packet at the start of the timestep
     p.last_event = p.last_event + 100;
     if (find_nextline) {
       if (p.type == ARTIS_TYPE_RPKT && mgi != c.st.npts_model && c.cs.thick[mgi] != 1) closest_transition_empty(c, p);
@@ -555,7 +559,7 @@ ARTIS_DEV bool rpkt_step_finish(const Ctx &c, ArtisPacket &p, const double t2, K
 // MODE 0: any cell; 1: the caller guarantees a non-grey, non-empty cell; 2: the caller guarantees a grey or empty cell
 // (the scheduler's two r-packet kinds, kernels.cuh) -- only prunes code, the arithmetic is the same.
 template <int MODE = 0>
-ARTIS_DEV bool do_rpkt_step(const Ctx &c, ArtisPacket &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
+ARTIS_DEV bool do_rpkt_step(const Ctx &c, Pkt &p, const double t2, KappaCache &k, Rng &rng, Tally &tl) {
   RpktStepState st;
   if (!rpkt_step_begin<MODE>(c, p, rng, tl, st)) return p.type == ARTIS_TYPE_RPKT;
   return rpkt_step_finish<MODE>(c, p, t2, k, rng, tl, st);

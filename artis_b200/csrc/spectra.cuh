@@ -5,7 +5,8 @@
 //     add_to_spec_res (spectrum.cc:602-615 -> add_to_spec, spectrum.cc:339-372, current_abin == -1, no emission resolution:
 //                      WRITE_PARTIAL_EMISSIONABSORPTIONSPEC is false in every artisoptions_*.h)
 // so that a driver which keeps its packets resident between timesteps downloads ntstep x (4 + nnubins) doubles after a
-// timestep instead of npkts x 304 bytes. One thread per packet; nothing but the fields the two callees read is loaded.
+// timestep instead of npkts x 304 bytes. One thread per packet: a packet that has not escaped costs one 32-byte sector of
+// its hot record (the type), an escaped one its hot line and the sector of the cold record that holds the escape record.
 #pragma once
 #include "common.cuh"
 
@@ -45,15 +46,16 @@ ARTIS_DEV int bin_timestep(const BinSpec &b, const double time) {
 }
 
 // lc_local: the block's private copy of b.lc (shared memory) or b.lc itself
-ARTIS_DEV void body_bin_escaped(const BinSpec &b, const ArtisPacket *pkts, const long long n, double *lc_local) {
+ARTIS_DEV void body_bin_escaped(const BinSpec &b, const PktHot *hot, const PktCold *cold, const long long n, double *lc_local) {
   const double tmin = b.tmin;
-  const ArtisPacket &p = pkts[n];
-  if (p.type != ARTIS_TYPE_ESCAPE) return;
-  const int et = p.escape_type;
+  const PktHot &p = hot[n];
+  if (pkt_lo16(p.type_cross) != ARTIS_TYPE_ESCAPE) return;
+  const PktCold &pc = cold[n];
+  const int et = pc.escape_type;
   if (et != ARTIS_TYPE_RPKT && et != ARTIS_TYPE_GAMMA) return;
   double *const lum = lc_local + (et == ARTIS_TYPE_RPKT ? 0 : 2 * b.ntstep);
   double *const lumcmf = lum + b.ntstep;
-  const double escape_time = (double)p.escape_time;  // an int member (packet.h:60)
+  const double escape_time = (double)pc.escape_time;  // an int member (packet.h:60)
   // get_arrive_time (vectors.h:146-152)
   const double t_arrive = escape_time - (dot3(p.pos, p.dir) / CLIGHT_PROP);
   const double e_rf = p.e_rf;
@@ -80,9 +82,9 @@ ARTIS_DEV void body_bin_escaped(const BinSpec &b, const ArtisPacket *pkts, const
   bin_add(&b.flux[bin], deltaE);
   if (b.stokes != nullptr) {
     const size_t plane = (size_t)b.ntstep * b.nnubins;
-    bin_add(&b.stokes[bin], p.stokes[0] * deltaE);
-    bin_add(&b.stokes[plane + bin], p.stokes[1] * deltaE);
-    bin_add(&b.stokes[2 * plane + bin], p.stokes[2] * deltaE);
+    bin_add(&b.stokes[bin], pc.stokes[0] * deltaE);
+    bin_add(&b.stokes[plane + bin], pc.stokes[1] * deltaE);
+    bin_add(&b.stokes[2 * plane + bin], pc.stokes[2] * deltaE);
   }
 }
 
@@ -90,8 +92,8 @@ ARTIS_DEV void body_bin_escaped(const BinSpec &b, const ArtisPacket *pkts, const
 // ---- escaped-packet compaction: the escaped packets, in array order, packed for one small D2H -----------
 constexpr int ESC_CHUNK = 256;  // packets per block of the count / scatter kernels
 // `reported` marks packets that an earlier only_new call has already delivered
-ARTIS_DEV bool escaped_selected(const ArtisPacket *pkts, const unsigned char *reported, const int only_new, const long long i) {
-  return pkts[i].type == ARTIS_TYPE_ESCAPE && !(only_new && reported[i]);
+ARTIS_DEV bool escaped_selected(const PktHot *hot, const unsigned char *reported, const int only_new, const long long i) {
+  return pkt_lo16(hot[i].type_cross) == ARTIS_TYPE_ESCAPE && !(only_new && reported[i]);
 }
 
 }  // namespace artis

@@ -11,6 +11,8 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 
 #include "kernels.cuh"
@@ -64,7 +66,8 @@ __global__ void k_cool(long long n) {
 // light curves + angle-averaged spectrum of the resident packets (spectra.cuh). The 4 x ntstep light-curve sums are a few
 // hundred addresses that every escaped packet of the ensemble adds to: they are accumulated per block in shared memory
 // and flushed once; the ntstep x nnubins spectrum bins are spread thinly and take global FP64 reductions directly.
-__global__ void __launch_bounds__(256) k_bin_escaped(const artis::BinSpec b, const ArtisPacket *pkts, long long n, int lc_in_smem) {
+__global__ void __launch_bounds__(256) k_bin_escaped(const artis::BinSpec b, const artis::PktHot *hot, const artis::PktCold *cold,
+                                                     long long n, int lc_in_smem) {
   extern __shared__ double lc_smem[];
   const int nlc = 4 * b.ntstep;
   double *lc_local = b.lc;
@@ -74,18 +77,46 @@ __global__ void __launch_bounds__(256) k_bin_escaped(const artis::BinSpec b, con
     lc_local = lc_smem;
   }
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    artis::body_bin_escaped(b, pkts, i, lc_local);
+    artis::body_bin_escaped(b, hot, cold, i, lc_local);
   if (lc_in_smem) {
     __syncthreads();
     for (int i = threadIdx.x; i < nlc; i += blockDim.x)
       if (lc_smem[i] != 0.) atomicAdd(&b.lc[i], lc_smem[i]);
   }
 }
-// escaped-packet compaction in array order: per-chunk counts, one scan, cooperative 304-byte copies
-__global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_count(const ArtisPacket *pkts, long long n, const unsigned char *reported,
+// ABI record <-> device records (common.cuh pkt_split / pkt_join), one thread per packet. The 304-byte host records of a
+// warp are consecutive, so its 16-byte loads sweep 9.5 KB of contiguous memory; the hot lines are written whole.
+__global__ void __launch_bounds__(256) k_unpack(const ArtisPacket *aos, artis::PktHot *hot, artis::PktCold *cold, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    ArtisPacket a;
+    const uint4 *src = reinterpret_cast<const uint4 *>(aos + i);
+    uint4 *dst = reinterpret_cast<uint4 *>(&a);
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(ArtisPacket) / 16); w++) dst[w] = src[w];
+    artis::PktHot h;
+    artis::PktCold c;
+    artis::pkt_split(a, h, c);
+    hot[i] = h;
+    cold[i] = c;
+  }
+}
+__global__ void __launch_bounds__(256) k_pack(const artis::PktHot *hot, const artis::PktCold *cold, ArtisPacket *aos, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const artis::PktHot h = hot[i];
+    const artis::PktCold c = cold[i];
+    ArtisPacket a;
+    artis::pkt_join(h, c, a);
+    const uint4 *src = reinterpret_cast<const uint4 *>(&a);
+    uint4 *dst = reinterpret_cast<uint4 *>(aos + i);
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(ArtisPacket) / 16); w++) dst[w] = src[w];
+  }
+}
+// escaped-packet compaction in array order: per-chunk counts, one scan, each selected packet joined into its ABI record
+__global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_count(const artis::PktHot *hot, long long n, const unsigned char *reported,
                                                                    int only_new, int *counts) {
   const long long i = blockIdx.x * (long long)artis::ESC_CHUNK + threadIdx.x;
-  const int sel = i < n && artis::escaped_selected(pkts, reported, only_new, i);
+  const int sel = i < n && artis::escaped_selected(hot, reported, only_new, i);
   const int c = __syncthreads_count(sel);
   if (threadIdx.x == 0) counts[blockIdx.x] = c;
 }
@@ -123,12 +154,13 @@ __global__ void __launch_bounds__(1024) k_escaped_scan(int *counts, int nchunks)
   }
   if (threadIdx.x == 0) counts[nchunks] = carry;
 }
-__global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_scatter(const ArtisPacket *pkts, long long n, unsigned char *reported,
-                                                                     int only_new, const int *offsets, ArtisPacket *out) {
+__global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_scatter(const artis::PktHot *hot, const artis::PktCold *cold, long long n,
+                                                                     unsigned char *reported, int only_new, const int *offsets,
+                                                                     ArtisPacket *out) {
   __shared__ int warp_base[artis::ESC_CHUNK / 32];
   const long long i = blockIdx.x * (long long)artis::ESC_CHUNK + threadIdx.x;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const bool sel = i < n && artis::escaped_selected(pkts, reported, only_new, i);
+  const bool sel = i < n && artis::escaped_selected(hot, reported, only_new, i);
   const unsigned m = __ballot_sync(0xffffffffu, sel);
   if (lane == 0) warp_base[w] = __popc(m);
   __syncthreads();
@@ -141,35 +173,185 @@ __global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_scatter(const Arti
     }
   }
   __syncthreads();
-  // the warp copies its selected packets one after the other, 19 lanes x 16 bytes each
-  const long long warp_first = i - lane;
-  int rank = 0;
-  for (unsigned rest = m; rest; rest &= rest - 1, rank++) {
-    const int src_lane = __ffs(rest) - 1;
-    const uint4 *src = reinterpret_cast<const uint4 *>(pkts + warp_first + src_lane);
-    uint4 *dst = reinterpret_cast<uint4 *>(out + warp_base[w] + rank);
-    if (lane < (int)(sizeof(ArtisPacket) / 16)) dst[lane] = src[lane];
+  if (sel) {
+    ArtisPacket a;
+    artis::pkt_join(hot[i], cold[i], a);
+    const uint4 *src = reinterpret_cast<const uint4 *>(&a);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + warp_base[w] + __popc(m & ((1u << lane) - 1u)));
+#pragma unroll
+    for (int q = 0; q < (int)(sizeof(ArtisPacket) / 16); q++) dst[q] = src[q];
+    if (only_new) reported[i] = 1;
   }
-  if (sel && only_new) reported[i] = 1;
 }
-// one kernel per event kind, each compiled with only that kind's physics
-template <int KIND>
-__global__ void __launch_bounds__(128) k_wavefront(ArtisPacket *pkts, unsigned long long *rngctr, artis::QueueView qv,
-                                                   long long max_events) {
-  artis::body_wavefront<KIND>(d_ctx, pkts, rngctr, qv, max_events);
-}
+
 // ---- barrier-free scheduler ------------------------------------------------------------------------------------------
-// One persistent kernel, one ring of packet indices per event kind, warps specialised by kind. A warp that has no
-// packet left picks the kind with the longest backlog and keeps that role until it runs dry; its lanes claim ring
-// entries (warp-aggregated), advance their packet by events of that kind only and, when the packet changes kind, write
-// it back and push its index on the ring of the new kind. Nothing waits for the slowest packet of a round: the step
-// ends when the longest single packet history ends, and a warp never executes two kinds' code in one iteration.
+// Persistent kernels, one ring of packet indices per event kind, warps specialised by kind. A warp that has no packet left
+// picks the kind with the longest backlog (among the kinds its kernel serves) and keeps that role until it runs dry; its
+// lanes claim ring entries (warp-aggregated), advance their packet by events of that kind only and, when the packet changes
+// kind, write it back and push its index on the ring of the new kind. Nothing waits for the slowest packet of a round: the
+// step ends when the longest single packet history ends, and a warp never executes two kinds' code in one iteration.
+//
+// Two kernels run side by side and exchange packets through the rings:
+//   k_transport_majump      the macro-atom jump role alone: 32 bytes of packet state, one rate row and one prefix-sum search
+//                           per jump -- a small register budget, hence many resident warps to hide the L2 round trips
+//   k_transport_persistent  every other role (r-packet steps, gamma packets, pellets, macro-atom events, k-packets) on the
+//                           whole hot line; big register budget, few warps
+// (k_transport_persistent<ROLES_ALL> also serves the jump role itself: the single-kernel variant, kept for comparisons.)
 //
 // Ring protocol (capacity >= number of packets, so at most `cap` entries are ever outstanding): a slot holds -1 when
 // empty. Producers take a ticket from tail (atomicAdd) and CAS their index into slot ticket % cap; consumers CAS head
 // forward only over tickets below the tail they observed and then exchange the slot back to -1, spinning for the few
-// cycles a producer may still need to fill it. Packet state written before the push is made visible with
-// __threadfence() and read with ld.global.cg on the consumer side (L1 is not coherent across SMs).
+// cycles a producer may still need to fill it.
+// Memory ordering without L1 invalidations: the producer's CAS on the slot is an atom.release.gpu (MEMBAR.ALL.GPU: every
+// store of the packet's records has reached L2 before the index becomes visible); the consumer's exchange is relaxed and
+// everything it then reads of the packet comes through L2 (ld.global.cg; common.cuh ldcold) at an address that depends on
+// the index it took. __threadfence() on either side would add a CCTL.IVALL -- an invalidation of the SM's whole L1, where
+// the read-only atomic data and per-cell table rows of all resident warps live -- to every hand-over (measured in round 1
+// without knowing it: 81 % L1 hit rate with 4e7 hand-overs per timestep).
+using artis::NRING;
+using artis::PktCold;
+using artis::PktHot;
+constexpr unsigned ROLES_HEAVY = (1u << artis::KIND_MAK) | (1u << artis::KIND_RPKT_THIN) | (1u << artis::KIND_GAMMA) |
+                                 (1u << artis::KIND_OTHER) | (1u << artis::KIND_RPKT_GREY);
+constexpr unsigned ROLES_ALL = ROLES_HEAVY | (1u << artis::KIND_MAJUMP);
+// register budgets of the two persistent kernels, as resident 128-thread blocks per SM that each must allow on its own
+// (__launch_bounds__: 65536 / (128 * blocks) registers per thread): 3 -> 168 registers, 2 -> 255, 8 -> 64, 6 -> 80
+#ifndef ARTIS_HEAVY_MINBLOCKS
+#define ARTIS_HEAVY_MINBLOCKS 3
+#endif
+#ifndef ARTIS_JUMP_MINBLOCKS
+#define ARTIS_JUMP_MINBLOCKS 8
+#endif
+
+struct PersistView {
+  int *ring[NRING];
+  unsigned long long *head;  // [NRING]
+  unsigned long long *tail;  // [NRING]
+  int *n_active;             // packets that have not finished the timestep
+  int n_initial;             // its value at launch
+  unsigned long long *t_start;  // globaltimer at launch
+  int cap;
+  unsigned long long *pend;  // [cap] macro-atom action a jump has drawn and left for the event role: (action + 1) << 32 | selidx
+};
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
+  return *reinterpret_cast<const volatile unsigned long long *>(p);
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// hot record <-> working set, through L2
+__device__ __forceinline__ void pkt_load_cg(artis::Pkt &p, artis::Rng &rng, const artis::Ctx &c, const PktHot *src, PktCold *cold) {
+  PktHot h;
+  const uint4 *s = reinterpret_cast<const uint4 *>(src);
+  uint4 *d = reinterpret_cast<uint4 *>(&h);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(PktHot) / 16); i++) d[i] = __ldcg(s + i);
+  artis::pkt_from_hot(p, h, cold);
+  rng = artis::rng_init(c, h.number, (unsigned long long)h.rngctr);
+}
+__device__ __forceinline__ void pkt_store_cg(PktHot *dst, const artis::Pkt &p, const artis::Rng &rng) {
+  PktHot h;
+  artis::pkt_to_hot(h, p, (unsigned)rng.ctr);
+  uint4 *d = reinterpret_cast<uint4 *>(dst);
+  const uint4 *s = reinterpret_cast<const uint4 *>(&h);
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(PktHot) / 16); i++) __stcg(d + i, s[i]);
+}
+// ring primitives (protocol in the comment above)
+constexpr int RMS = artis::RING_META_STRIDE;
+#ifndef ARTIS_REFILL_BACKOFF
+#define ARTIS_REFILL_BACKOFF 10
+#endif
+constexpr int REFILL_BACKOFF = ARTIS_REFILL_BACKOFF;
+__device__ __forceinline__ long long ring_backlog(const PersistView &pv, const int r) {
+  const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
+  return t > h ? (long long)(t - h) : 0;
+}
+// lane 0: claim up to `want` entries of ring r; returns the count and the first ticket
+__device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, const int want, unsigned long long *base) {
+  for (int tries = 0; tries < 4; tries++) {
+    const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
+    const long long avail = t > h ? (long long)(t - h) : 0;
+    const int take = avail < want ? (int)avail : want;
+    if (take == 0) return 0;
+    if (atomicCAS(pv.head + r * RMS, h, h + (unsigned long long)take) == h) {
+      *base = h;
+      return take;
+    }
+  }
+  return 0;
+}
+__device__ __forceinline__ int ring_take(const PersistView &pv, const int r, const unsigned long long ticket) {
+  int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);
+  int v;
+  while ((v = atomicExch(slot, -1)) < 0) {
+  }
+  return v;
+}
+__device__ __forceinline__ void ring_put(const PersistView &pv, const int r, const unsigned long long ticket, const int idx) {
+  int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);
+  int old;
+  do {
+    asm volatile("atom.release.gpu.global.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(slot), "r"(-1), "r"(idx) : "memory");
+  } while (old != -1);
+}
+// The warp's finished lanes (done) push their packets on the rings of their next kinds (k2 >= 0) or retire them (k2 < 0).
+__device__ __forceinline__ void push_done(const artis::Ctx &c, const PersistView &pv, const bool done, const int k2, const int idx) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int kk = 0; kk < NRING; kk++) {
+    const unsigned m = __ballot_sync(full, done && k2 == kk);
+    if (m != 0u) {
+      const int leader = __ffs(m) - 1;
+      unsigned long long b = 0ull;
+      if (lane == leader) b = atomicAdd(pv.tail + kk * RMS, (unsigned long long)__popc(m));
+      b = __shfl_sync(full, b, leader);
+      if (done && k2 == kk) ring_put(pv, kk, b + (unsigned long long)__popc(m & lt_mask), idx);
+    }
+  }
+  const unsigned fin = __ballot_sync(full, done && k2 < 0);
+  if (fin != 0u && lane == __ffs(fin) - 1) {
+    const int nfin = __popc(fin);
+    const int before = atomicSub(pv.n_active, nfin), after = before - nfin;
+    // drain profile: when the active count falls through 10%, 1% and 0 of its initial value (ns since launch)
+    const int n0 = pv.n_initial;
+    const long long now = (long long)(global_ns() - *reinterpret_cast<volatile unsigned long long *>(pv.t_start));
+    if (before > n0 / 10 && after <= n0 / 10) c.es.counters[ARTIS_CTR_DRAIN_NS_10PCT] = now;
+    if (before > n0 / 100 && after <= n0 / 100) c.es.counters[ARTIS_CTR_DRAIN_NS_1PCT] = now;
+    if (after <= 0) c.es.counters[ARTIS_CTR_DRAIN_NS_DONE] = now;
+  }
+}
+// An idle warp's poll: returns true when the timestep is over (no active packet left, or the hang guard fired)
+__device__ __forceinline__ bool idle_poll(const artis::Ctx &c, const PersistView &pv, unsigned long long &idle_since, int &last_active,
+                                          const unsigned long long idle_timeout_ns) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  int left = 0;
+  if (lane == 0) left = *reinterpret_cast<volatile int *>(pv.n_active);
+  left = __shfl_sync(full, left, 0);
+  if (left <= 0) return true;  // every packet has reached the end of the timestep
+  unsigned long long now = 0ull;
+  if (lane == 0) now = global_ns();
+  now = __shfl_sync(full, now, 0);
+  // Hang guard: the timestep is given up (code 900) only when the number of active packets has not changed for the whole
+  // timeout -- a warp that merely finds its rings empty while a few long histories finish elsewhere keeps waiting.
+  if (idle_since == 0ull || left != last_active) {
+    idle_since = now;
+    last_active = left;
+  }
+  if (now - idle_since > idle_timeout_ns) {  // a lost packet would otherwise hang the device
+    if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
+    return true;
+  }
+  __nanosleep(1000);
+  return false;
+}
+
 // Warp-cooperative continuum opacity (K2): every lane that is about to need kappa_cont for its own packet and misses its
 // cache ("owner") gets its bound-free sum evaluated by all 32 lanes, a tile of 32 consecutive continua at a time --
 // coalesced reads of the per-cell table rows, no dependence between tiles, and the step's latency no longer grows with
@@ -200,7 +382,6 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
     const int ng = c.st.nbfcontinua_ground;
     for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
   }
-  const int nbf = c.st.nbfcontinua;
   while (owners != 0u) {
     const int owner = __ffs(owners) - 1;
     owners &= owners - 1u;
@@ -252,7 +433,6 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
       tl.bf_evaluated += i0 - ilo;
     }
   }
-  (void)nbf;
   if (need) kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ff, tl);
 }
 
@@ -280,194 +460,47 @@ __device__ __forceinline__ void coop_bfest_flush(const artis::Ctx &c, artis::Kap
   k.bfest_factor = 0.;
 }
 
-using artis::KIND_KAPPA;
-using artis::KIND_THIN_RESUME;
-using artis::NRING;
-constexpr unsigned ROLES_ALL = (1u << artis::KIND_MAK) | (1u << artis::KIND_RPKT_THIN) | (1u << artis::KIND_GAMMA) |
-                               (1u << artis::KIND_OTHER) | (1u << artis::KIND_RPKT_GREY);
-// Two co-resident persistent kernels: the "light" one runs the roles that are chains of dependent table
-// loads with little live state (macro-atom / k-packet jumps, and continuum-opacity sums on request) at a small
-// register budget and therefore many resident warps; the "heavy" one runs the r-packet / gamma / pellet steps.
-#ifndef ARTIS_LIGHT_HAS_MAK
-#define ARTIS_LIGHT_HAS_MAK 1
-#endif
-#ifndef ARTIS_HEAVY_MINBLOCKS
-#define ARTIS_HEAVY_MINBLOCKS 1
-#endif
-constexpr unsigned ROLES_LIGHT = (ARTIS_LIGHT_HAS_MAK ? (1u << artis::KIND_MAK) : 0u) | (1u << KIND_KAPPA);
-constexpr unsigned ROLES_HEAVY = ROLES_ALL & ~(ARTIS_LIGHT_HAS_MAK ? (1u << artis::KIND_MAK) : 0u);
-constexpr int HEAVY_MINBLOCKS = ARTIS_HEAVY_MINBLOCKS;
-#ifndef ARTIS_LIGHT_MINBLOCKS
-#define ARTIS_LIGHT_MINBLOCKS 6
-#endif
-constexpr int LIGHT_MINBLOCKS = ARTIS_LIGHT_MINBLOCKS;  // register cap of the light kernel: 65536 / (128 x this)
-
-struct PersistView {
-  int *ring[NRING];
-  unsigned long long *head;  // [NRING]
-  unsigned long long *tail;  // [NRING]
-  int *n_active;             // packets that have not finished the timestep
-  int n_initial;             // its value at launch
-  unsigned long long *t_start;  // globaltimer at launch
-  int cap;
-  double *kcache;            // [cap][kstride] continuum opacity delivered for a packet (KappaCache scalars + gamma_contr)
-  double *stepstate;         // [cap][3] RpktStepState of a step that waits for its opacity
-  int kstride;
-  int offload_kappa;         // 1: the thin role hands opacity evaluations to the KIND_KAPPA role of the light kernel
-};
-
-__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
-  return *reinterpret_cast<const volatile unsigned long long *>(p);
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-static_assert(sizeof(ArtisPacket) % 8 == 0, "packet copied as 8-byte words");
-__device__ __forceinline__ void packet_load_cg(ArtisPacket &p, const ArtisPacket *src) {
-  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(src);
-  unsigned long long *d = reinterpret_cast<unsigned long long *>(&p);
-#pragma unroll
-  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) d[i] = __ldcg(s + i);
-}
-__device__ __forceinline__ void packet_store_cg(ArtisPacket *dst, const ArtisPacket &p) {
-  unsigned long long *d = reinterpret_cast<unsigned long long *>(dst);
-  const unsigned long long *s = reinterpret_cast<const unsigned long long *>(&p);
-#pragma unroll
-  for (int i = 0; i < (int)(sizeof(ArtisPacket) / 8); i++) __stcg(d + i, s[i]);
-}
-__device__ __forceinline__ void kcache_store(double *kc, const artis::KappaCache &k, const int ng) {
-  __stcg(kc + 0, k.nu);
-  __stcg(kc + 1, k.total);
-  __stcg(kc + 2, k.es);
-  __stcg(kc + 3, k.ff);
-  __stcg(kc + 4, k.bf);
-  __stcg(kc + 5, k.ffheating);
-  __stcg(kc + 6, (double)k.mgi);
-  for (int g = 0; g < ng; g++) __stcg(kc + 8 + g, k.gamma_contr[g]);
-}
-__device__ __forceinline__ void kcache_load(artis::KappaCache &k, const double *kc, const int ng) {
-  k.nu = __ldcg(kc + 0);
-  k.total = __ldcg(kc + 1);
-  k.es = __ldcg(kc + 2);
-  k.ff = __ldcg(kc + 3);
-  k.bf = __ldcg(kc + 4);
-  k.ffheating = __ldcg(kc + 5);
-  k.mgi = (int)__ldcg(kc + 6);
-  k.valid = true;
-  for (int g = 0; g < ng; g++) k.gamma_contr[g] = __ldcg(kc + 8 + g);
-}
-// ring primitives (protocol in the comment above)
-constexpr int RMS = artis::RING_META_STRIDE;
-#ifndef ARTIS_REFILL_BACKOFF
-#define ARTIS_REFILL_BACKOFF 10
-#endif
-constexpr int REFILL_BACKOFF = ARTIS_REFILL_BACKOFF;
-#ifndef ARTIS_REFILL_MIN
-#define ARTIS_REFILL_MIN 1
-#endif
-constexpr int REFILL_MIN = ARTIS_REFILL_MIN;  // a partly busy warp refills only when at least this many lanes are idle
-__device__ __forceinline__ long long ring_backlog(const PersistView &pv, const int r) {
-  const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
-  return t > h ? (long long)(t - h) : 0;
-}
-// lane 0: claim up to `want` entries of ring r; returns the count and the first ticket
-__device__ __forceinline__ int ring_claim(const PersistView &pv, const int r, const int want, unsigned long long *base) {
-#ifndef ARTIS_CLAIM_CASRETRY  // default: both words are read again after a lost race (the variant below measured 1 % slower)
-  for (int tries = 0; tries < 4; tries++) {
-    const unsigned long long h = ld_volatile_u64(pv.head + r * RMS), t = ld_volatile_u64(pv.tail + r * RMS);
-    const long long avail = t > h ? (long long)(t - h) : 0;
-    const int take = avail < want ? (int)avail : want;
-    if (take == 0) return 0;
-    if (atomicCAS(pv.head + r * RMS, h, h + (unsigned long long)take) == h) {
-      *base = h;
-      return take;
-    }
-  }
-  return 0;
-#else
-  // a lost race hands back the current head: retry with it and the (older, hence conservative) tail, one round trip less
-  unsigned long long h = ld_volatile_u64(pv.head + r * RMS);
-  const unsigned long long t = ld_volatile_u64(pv.tail + r * RMS);
-  for (int tries = 0; tries < 4; tries++) {
-    const long long avail = t > h ? (long long)(t - h) : 0;
-    const int take = avail < want ? (int)avail : want;
-    if (take == 0) return 0;
-    const unsigned long long seen = atomicCAS(pv.head + r * RMS, h, h + (unsigned long long)take);
-    if (seen == h) {
-      *base = h;
-      return take;
-    }
-    h = seen;
-  }
-  return 0;
-#endif
-}
-__device__ __forceinline__ int ring_take(const PersistView &pv, const int r, const unsigned long long ticket) {
-  int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);
-  int v;
-  while ((v = atomicExch(slot, -1)) < 0) {
-  }
-  __threadfence();
-  return v;
-}
-__device__ __forceinline__ void ring_put(const PersistView &pv, const int r, const unsigned long long ticket, const int idx) {
-  int *slot = pv.ring[r] + (size_t)(ticket % (unsigned long long)pv.cap);
-  while (atomicCAS(slot, -1, idx) != -1) {
-  }
-}
-
 // ROLES: bit mask of the kinds the warps of this kernel may take up
-template <unsigned ROLES, int MINBLOCKS>
-__global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPacket *pkts, unsigned long long *rngctr,
-                                                                         PersistView pv, long long max_events,
-                                                                         unsigned long long idle_timeout_ns) {
+template <unsigned ROLES>
+__global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persistent(PktHot *hot, PktCold *cold, PersistView pv, long long max_events,
+                                                                       unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;
   const double t2 = c.t2;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const int ng = c.st.nbfcontinua_ground;
   constexpr bool HAS_THIN = (ROLES & (1u << KIND_RPKT_THIN)) != 0;
-  constexpr bool HAS_KAPPA = (ROLES & (1u << KIND_KAPPA)) != 0;
+  constexpr bool HAS_JUMP = (ROLES & (1u << KIND_MAJUMP)) != 0;
   Tally tl = {};
   KappaCache k;
   k.valid = false;
   k.defer_bfest = HAS_THIN && ARTIS_OPT_DETAILED_BF(c);
-  bool have = false, resumed = false;
+  bool have = false;
   int idx = 0, role = 0;
   long long events = 0;
-  ArtisPacket p;
+  Pkt p;
   Rng rng;
   RpktStepState st;
   st.mgi = 0;
   unsigned long long idle_since = 0ull;
-  int refill_skip = 0;  // iterations left during which a partly busy warp does not look at its (just found empty) ring
-  if ((ROLES & (1u << KIND_RPKT_GREY)) != 0 && blockIdx.x == 0 && threadIdx.x == 0)
-    *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
-  long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
-  // where the warp's cycles go (lane k keeps kind k's event cycles; lane 0 the scheduler's own): a handful of clock reads
-  // per iteration against thousands of cycles of event code
-  long long cyc_kind = 0, cyc_refill = 0, cyc_push = 0, cyc_idle = 0;
   int last_active = -1;  // active-packet count at the last idle poll: the hang guard looks for progress, not for work
+  int refill_skip = 0;   // iterations left during which a partly busy warp does not look at its (just found empty) ring
+  stats_block_begin();
+  if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
+  long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
+  // where the warp's cycles go (lane k keeps kind k's event cycles; lane 0 the scheduler's own)
+  long long cyc_kind = 0, cyc_refill = 0, cyc_push = 0, cyc_idle = 0;
   while (true) {
     __syncwarp(full);
     const long long tick0 = clock64();
     const unsigned need = __ballot_sync(full, !have);
-    if (need != full && (refill_skip > 0 || __popc(need) < REFILL_MIN)) {
-      if (refill_skip > 0) refill_skip--;
+    if (need != full && refill_skip > 0) {
+      refill_skip--;
     } else if (need != 0u) {
       if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
         long long backlog = 0;
         if (lane < NRING && ((ROLES >> lane) & 1u) != 0) backlog = ring_backlog(pv, lane);
-        if (HAS_THIN && lane == KIND_THIN_RESUME) backlog = ring_backlog(pv, lane);
-        if (HAS_THIN) {  // the thin role drains two rings
-          const long long extra = __shfl_sync(full, backlog, KIND_THIN_RESUME);
-          if (lane == KIND_RPKT_THIN) backlog += extra;
-          if (lane == KIND_THIN_RESUME) backlog = 0;
-        }
         long long best = backlog;
         int best_kind = lane;
 #pragma unroll
@@ -482,82 +515,36 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
         best = __shfl_sync(full, best, 0);
         best_kind = __shfl_sync(full, best_kind, 0);
         if (best <= 0) {
-          int left = 0;
-          if (lane == 0) left = *reinterpret_cast<volatile int *>(pv.n_active);
-          left = __shfl_sync(full, left, 0);
-          if (left <= 0) break;  // every packet has reached the end of the timestep
-          unsigned long long now = 0ull;
-          if (lane == 0) now = global_ns();
-          now = __shfl_sync(full, now, 0);
-          // Hang guard: the timestep is given up (code 900) only when the number of active packets has not changed for
-          // the whole timeout -- a warp that merely finds its rings empty while a few long histories finish elsewhere
-          // (thick grey cells, virtual-packet ray traces) keeps waiting.
-          if (idle_since == 0ull || left != last_active) {
-            idle_since = now;
-            last_active = left;
-          }
-          if (now - idle_since > idle_timeout_ns) {  // a lost packet would otherwise hang the device
-            if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
-            break;
-          }
-          __nanosleep(1000);
+          if (idle_poll(c, pv, idle_since, last_active, idle_timeout_ns)) break;
           cyc_idle += clock64() - tick0;
           continue;
         }
         role = best_kind;
         idle_since = 0ull;
       }
-      // refill the idle lanes from the role's ring(s); for the thin role the resumed steps come first
+      // refill the idle lanes from the role's ring
       const int want = __popc(need);
-      int take_a = 0, take_b = 0;
-      unsigned long long base_a = 0ull, base_b = 0ull;
-      if (lane == 0) {
-        if (HAS_THIN && role == KIND_RPKT_THIN) take_a = ring_claim(pv, KIND_THIN_RESUME, want, &base_a);
-        if (take_a < want) take_b = ring_claim(pv, role, want - take_a, &base_b);
-      }
-      take_a = __shfl_sync(full, take_a, 0);
-      take_b = __shfl_sync(full, take_b, 0);
-      base_a = __shfl_sync(full, base_a, 0);
-      base_b = __shfl_sync(full, base_b, 0);
+      int take = 0;
+      unsigned long long base = 0ull;
+      if (lane == 0) take = ring_claim(pv, role, want, &base);
+      take = __shfl_sync(full, take, 0);
+      base = __shfl_sync(full, base, 0);
       const int rank = __popc(need & lt_mask);
-      if (!have && rank < take_a + take_b) {
-        const bool from_resume = rank < take_a;
-        idx = from_resume ? ring_take(pv, KIND_THIN_RESUME, base_a + (unsigned long long)rank)
-                          : ring_take(pv, role, base_b + (unsigned long long)(rank - take_a));
-        if (HAS_KAPPA && role == KIND_KAPPA) {
-          // only the two fields the opacity depends on
-          p.nu_cmf = __ldcg(&pkts[idx].nu_cmf);
-          p.where = __ldcg(&pkts[idx].where);
-        } else {
-          packet_load_cg(p, pkts + idx);
-          rng = rng_init(c, p.number, __ldcg(rngctr + idx));
-        }
+      if (!have && rank < take) {
+        idx = ring_take(pv, role, base + (unsigned long long)rank);
+        pkt_load_cg(p, rng, c, hot + idx, cold + idx);
         k.valid = false;
-        resumed = false;
-        if (HAS_THIN && from_resume) {
-          kcache_load(k, pv.kcache + (size_t)idx * pv.kstride, ng);
-          const double *ss = pv.stepstate + (size_t)idx * 3;
-          st.tau_next = __ldcg(ss + 0);
-          st.sdist = __ldcg(ss + 1);
-          const long long packed = __double_as_longlong(__ldcg(ss + 2));
-          st.snext = (int)(packed >> 32);
-          st.mgi = (int)(packed & 0xffffffffll);
-          st.mgi_next = rpkt_step_mgi_next(c, p, st);
-          resumed = true;
-        }
         events = 0;
         have = true;
       }
-      if (need == full && take_a + take_b == 0) continue;  // lost the race for the last entries
+      if (need == full && take == 0) continue;  // lost the race for the last entries
       // a claim costs the warp two L2 round trips on the busiest words of the device: after an empty answer the busy
       // lanes run a few iterations before the warp asks again (a warp without any work asks at once)
-      refill_skip = (take_a + take_b < want) ? REFILL_BACKOFF : 0;
+      refill_skip = (take < want) ? REFILL_BACKOFF : 0;
     }
     __syncwarp(full);
     const long long tick1 = clock64();
     cyc_refill += tick1 - tick0;
-    bool done = false;
-    int k2 = -1;
     {
       const unsigned busy = __ballot_sync(full, have);
       if (lane == role && lane < NKIND) {  // lane k keeps the occupancy statistics of kind k
@@ -565,49 +552,31 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
         fill_lanes += __popc(busy);
       }
     }
-    bool stepped = have;  // false for a lane that hands its step over instead of finishing it
     if (HAS_THIN && role == KIND_RPKT_THIN) {  // warp-uniform: the step in two halves around the opacity evaluation
       bool proceed = false;
       if (have) {
-        if (resumed) {
-          proceed = true;
-        } else {
-          tl.packet_updates++;
-          proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
-        }
+        tl.packet_updates++;
+        proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
       }
-      const bool wants = proceed && !resumed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
-      const unsigned owners = __ballot_sync(full, wants);
-      if (pv.offload_kappa != 0 && __popc(owners) > COOP_MAX_OWNERS) {
-        if (wants) {  // hand the evaluation to the light kernel; the step resumes in whichever thin warp picks it up
-          double *ss = pv.stepstate + (size_t)idx * 3;
-          __stcg(ss + 0, st.tau_next);
-          __stcg(ss + 1, st.sdist);
-          __stcg(ss + 2, __longlong_as_double(((long long)st.snext << 32) | (long long)(unsigned)st.mgi));
-          stepped = false;
-        }
-      } else {
-        coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl);
-      }
-      if (stepped && proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
+      const bool wants = proceed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
+      coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl);
+      if (proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
       if (k.defer_bfest) coop_bfest_flush(c, k, tl);  // warp-uniform: the flag is an option of the build mode
-      resumed = false;
-      if (stepped && have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
-    } else if (HAS_KAPPA && role == KIND_KAPPA) {
-      if (have) {
-        const int mgi = cell_mgi(c, p.where);
-        calculate_kappa_rpkt_cont(c, p, mgi, k, tl);
-        kcache_store(pv.kcache + (size_t)idx * pv.kstride, k, ng);
-        __threadfence();
-        done = true;
-        k2 = KIND_THIN_RESUME;
-        have = false;
-        stepped = false;
-      }
+      if (have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
     } else if (have) {
       switch (role) {  // warp-uniform
         case KIND_MAK:
-          if constexpr ((ROLES & (1u << KIND_MAK)) != 0) do_packet_kind<KIND_MAK>(c, p, t2, k, rng, tl);
+          if constexpr ((ROLES & (1u << KIND_MAK)) != 0) {
+            if (p.type == ARTIS_TYPE_MA) {  // the rest of an iteration whose action the jump role has drawn
+              const unsigned long long pd = __ldcg(pv.pend + idx);
+              ma_event(c, p, (int)(pd >> 32) - 1, (int)(unsigned)(pd & 0xffffffffull), rng, tl);
+            } else {
+              do_packet_kind<KIND_MAK>(c, p, t2, k, rng, tl);
+            }
+          }
+          break;
+        case KIND_MAJUMP:
+          if constexpr (HAS_JUMP) do_packet_kind<KIND_MAJUMP>(c, p, t2, k, rng, tl);
           break;
         case KIND_GAMMA:
           if constexpr ((ROLES & (1u << KIND_GAMMA)) != 0) do_packet_kind<KIND_GAMMA>(c, p, t2, k, rng, tl);
@@ -621,51 +590,26 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
       }
     }
     if (ARTIS_OPT_VPKT(c) && have) vpkt_flush_request(c, p, k, tl);  // the one call site of the virtual-packet ray trace
-    if (have && !stepped) {  // thin lane that handed its opacity evaluation over
-      __stcg(rngctr + idx, (unsigned long long)rng.ctr);
-      packet_store_cg(pkts + idx, p);
-      __threadfence();
-      done = true;
-      k2 = KIND_KAPPA;
-      have = false;
-    } else if (have) {
+    bool done = false;
+    int k2 = -1;
+    if (have) {
       events++;
       const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
-      if (!(active && kind_of(c, p) == role && events < max_events)) {
-        __stcg(rngctr + idx, (unsigned long long)rng.ctr);
-        packet_store_cg(pkts + idx, p);
-        __threadfence();
+      const int knext = active ? kind_of(c, p) : -1;
+      // a macro-atom that stays activated after an event of the MAK role goes back to the jump role
+      if (!(active && knext == role && events < max_events)) {
+        pkt_store_cg(hot + idx, p, rng);
         done = true;
-        k2 = active ? kind_of(c, p) : -1;
+        k2 = knext;
         have = false;
+        if (active) tl.handoffs++;
       }
     }
     __syncwarp(full);
     const long long tick2 = clock64();
     if (lane == role) cyc_kind += tick2 - tick1;
     if (__ballot_sync(full, done) != 0u) {
-#pragma unroll
-      for (int kk = 0; kk < NRING; kk++) {
-        const unsigned m = __ballot_sync(full, done && k2 == kk);
-        if (m != 0u) {
-          const int leader = __ffs(m) - 1;
-          unsigned long long b = 0ull;
-          if (lane == leader) b = atomicAdd(pv.tail + kk * RMS, (unsigned long long)__popc(m));
-          b = __shfl_sync(full, b, leader);
-          if (done && k2 == kk) ring_put(pv, kk, b + (unsigned long long)__popc(m & lt_mask), idx);
-        }
-      }
-      const unsigned fin = __ballot_sync(full, done && k2 < 0);
-      if (fin != 0u && lane == __ffs(fin) - 1) {
-        const int nfin = __popc(fin);
-        const int before = atomicSub(pv.n_active, nfin), after = before - nfin;
-        // drain profile: when the active count falls through 10%, 1% and 0 of its initial value (ns since launch)
-        const int n0 = pv.n_initial;
-        const long long now = (long long)(global_ns() - *reinterpret_cast<volatile unsigned long long *>(pv.t_start));
-        if (before > n0 / 10 && after <= n0 / 10) c.es.counters[ARTIS_CTR_DRAIN_NS_10PCT] = now;
-        if (before > n0 / 100 && after <= n0 / 100) c.es.counters[ARTIS_CTR_DRAIN_NS_1PCT] = now;
-        if (after <= 0) c.es.counters[ARTIS_CTR_DRAIN_NS_DONE] = now;
-      }
+      push_done(c, pv, done, k2, idx);
       cyc_push += clock64() - tick2;
     }
   }
@@ -680,11 +624,133 @@ __global__ void __launch_bounds__(128, MINBLOCKS) k_transport_persistent(ArtisPa
     ctr_add(&c.es.counters[ARTIS_CTR_PUSH_CYCLES], cyc_push);
     ctr_add(&c.es.counters[ARTIS_CTR_IDLE_CYCLES], cyc_idle);
   }
+  stats_block_flush(c);
 }
 
-__global__ void k_bucket_hist(ArtisPacket *pkts, unsigned long long *rngctr, int n, int *counts) {
+// The macro-atom jump role on its own (kernels.cuh KIND_MAJUMP). A lane holds 32 bytes of its packet -- cell, macro-atom
+// state, interaction count -- and the packet's Philox stream; an iteration is ma_jump: one row of process rates, one or two
+// draws, one search over a prefix-sum row. Jumps that stay inside the ion (98 % of them) only change the level; any other
+// action is left in pend[] for the event role of k_transport_persistent and the packet moves to that ring.
+struct MaView {
+  int where, ma_element, ma_ion, ma_level, interactions;
+};
+__global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_majump(PktHot *hot, PersistView pv, long long max_events,
+                                                                  unsigned long long idle_timeout_ns) {
+  using namespace artis;
+  const Ctx &c = d_ctx;
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  constexpr int role = KIND_MAJUMP;
+  Tally tl = {};
+  bool have = false;
+  int idx = 0;
+  int events = 0;
+  const int event_cap = max_events > 0x7fffffffLL ? 0x7fffffff : (int)max_events;
+  MaView v = {0, 0, 0, 0, 0};
+  Rng rng = {};
+  unsigned long long idle_since = 0ull;
+  int last_active = -1;
+  int refill_skip = 0;
+  // statistics in 32-bit words (this kernel lives on its small register budget): iterations, busy lanes, and cycles in units
+  // of 64 (lane 5: the jumps themselves; lane 0: refill, push, idle)
+  unsigned fill_iters = 0, fill_lanes = 0, cyc_a = 0, cyc_b = 0, cyc_c = 0;
+  stats_block_begin();
+  while (true) {
+    __syncwarp(full);
+    const unsigned tick0 = (unsigned)clock();
+    const unsigned need = __ballot_sync(full, !have);
+    if (need != full && refill_skip > 0) {
+      refill_skip--;
+    } else if (need != 0u) {
+      const int want = __popc(need);
+      int take = 0;
+      unsigned long long base = 0ull;
+      if (lane == 0) take = ring_claim(pv, role, want, &base);
+      take = __shfl_sync(full, take, 0);
+      base = __shfl_sync(full, base, 0);
+      if (need == full && take == 0) {
+        if (idle_poll(c, pv, idle_since, last_active, idle_timeout_ns)) break;
+        if (lane == 0) cyc_c += ((unsigned)clock() - tick0) >> 6;
+        continue;
+      }
+      idle_since = 0ull;
+      const int rank = __popc(need & ((1u << lane) - 1u));
+      if (!have && rank < take) {
+        idx = ring_take(pv, role, base + (unsigned long long)rank);
+        // sector 0 of the hot record and the (draw counter, number) pair of sector 1
+        const uint4 a = __ldcg(reinterpret_cast<const uint4 *>(hot + idx));
+        const uint4 b = __ldcg(reinterpret_cast<const uint4 *>(hot + idx) + 1);
+        const uint2 r = __ldcg(reinterpret_cast<const uint2 *>(&hot[idx].rngctr));
+        v.where = (int)a.x;
+        v.ma_element = pkt_lo16(a.z);
+        v.ma_ion = pkt_hi16(a.z);
+        v.ma_level = (int)a.w;
+        v.interactions = (int)b.y;
+        rng = rng_init(c, (int)r.y, (unsigned long long)r.x);
+        events = 0;
+        have = true;
+      }
+      refill_skip = (take < want) ? REFILL_BACKOFF : 0;
+    }
+    __syncwarp(full);
+    const unsigned tick1 = (unsigned)clock();
+    if (lane == 0) cyc_a += (tick1 - tick0) >> 6;
+    {
+      const unsigned busy = __ballot_sync(full, have);
+      if (lane == role) {
+        fill_iters++;
+        fill_lanes += __popc(busy);
+      }
+    }
+    bool done = false;
+    int k2 = -1;
+    if (have) {
+      tl.packet_updates++;
+      int selidx;
+      const int action = ma_jump(c, v, rng, tl, &selidx);
+      events++;
+      if (action >= 0 || events >= event_cap) {
+        // the words of sector 0 a jump changes, and the draw counter
+        __stcg(&hot[idx].ma_el_ion, pkt_pack2(v.ma_element, v.ma_ion));
+        __stcg(&hot[idx].ma_level, v.ma_level);
+        __stcg(&hot[idx].interactions, v.interactions);
+        __stcg(&hot[idx].rngctr, (unsigned)rng.ctr);
+        if (action >= 0) {
+          __stcg(pv.pend + idx, ((unsigned long long)(unsigned)(action + 1) << 32) | (unsigned long long)(unsigned)selidx);
+          k2 = KIND_MAK;
+        } else {
+          k2 = KIND_MAJUMP;
+        }
+        tl.handoffs++;
+        done = true;
+        have = false;
+      }
+    }
+    __syncwarp(full);
+    const unsigned tick2 = (unsigned)clock();
+    if (lane == role) cyc_a += (tick2 - tick1) >> 6;
+    if (__ballot_sync(full, done) != 0u) {
+      push_done(c, pv, done, k2, idx);
+      if (lane == 0) cyc_b += ((unsigned)clock() - tick2) >> 6;
+    }
+  }
+  tally_flush(c, tl);
+  if (lane == role && fill_iters > 0) {
+    ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + role], fill_iters);
+    ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + role], fill_lanes);
+    ctr_add(&c.es.counters[ARTIS_CTR_WARP_CYCLES0 + role], (long long)cyc_a << 6);
+  }
+  if (lane == 0) {
+    ctr_add(&c.es.counters[ARTIS_CTR_REFILL_CYCLES], (long long)cyc_a << 6);
+    ctr_add(&c.es.counters[ARTIS_CTR_PUSH_CYCLES], (long long)cyc_b << 6);
+    ctr_add(&c.es.counters[ARTIS_CTR_IDLE_CYCLES], (long long)cyc_c << 6);
+  }
+  stats_block_flush(c);
+}
+
+__global__ void k_bucket_hist(PktHot *hot, PktCold *cold, int n, int *counts) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    artis::body_bucket_hist(d_ctx, pkts, rngctr, i, counts);
+    artis::body_bucket_hist(d_ctx, hot, cold, i, counts);
 }
 // exclusive prefix sum over the (kind, cell) counts, one 1024-thread block per kind (a 3D model has a model cell per
 // propagation cell: 1e6 counts per kind); also the size of each kind's queue
@@ -723,9 +789,9 @@ __global__ void __launch_bounds__(1024) k_bucket_scan(int *counts, int *kind_siz
   }
   if (threadIdx.x == 0) kind_sizes[blockIdx.x] = carry;
 }
-__global__ void k_bucket_scatter(const ArtisPacket *pkts, int n, int *offsets, int *const *queues) {
+__global__ void k_bucket_scatter(const PktHot *hot, int n, int *offsets, int *const *queues) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    artis::body_bucket_scatter(d_ctx, pkts, i, offsets, queues);
+    artis::body_bucket_scatter(d_ctx, hot, i, offsets, queues);
 }
 __global__ void k_probe_boundary(const ArtisPacket *p, int n, double *a, int *b, int *c) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -764,19 +830,15 @@ __global__ void k_probe_levelpop(const int *a, const int *b, const int *c, const
 cudaStream_t g_stream = nullptr;
 cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 int g_sms = SM_COUNT_B200;
-int g_transport_blocks_per_sm = 4;
-int g_blocks_all = 2, g_blocks_heavy = 1, g_blocks_light = 3;
-int g_scheduler_kernels = 1;  // 2 = light + heavy kernels side by side: correct but slower on every split tried (profiles/r1_notes.md)
+// resident blocks per SM of the persistent kernels: the single kernel with every role on its own, and the pair
+int g_blocks_all = 1, g_blocks_heavy = 1, g_blocks_jump = 0;
+int g_scheduler_kernels = 2;  // 2: jump kernel + kernel with every other role side by side; 1: one kernel with every role
 cudaStream_t g_stream2 = nullptr;
 cudaEvent_t g_ev_fork = nullptr, g_ev_join = nullptr;
-double *g_stepstate = nullptr;
 bool g_persistent_warmed = false;
-unsigned long long g_idle_timeout_ns = 20ull * 1000000000ull;  // hang guard of the persistent kernel (artis_gpu_set_tuning)
-int g_nbfcontinua_ground = 0;
+unsigned long long g_idle_timeout_ns = 20ull * 1000000000ull;  // hang guard of the persistent kernels (artis_gpu_set_tuning)
 double *g_est_block = nullptr;
 size_t g_est_ndoubles = 0;
-double *g_kcache = nullptr;
-size_t g_kcache_doubles = 0;
 std::string g_async_err;
 
 void note(cudaError_t e, const char *what) {
@@ -792,6 +854,9 @@ bool be_available(std::string *why) {
   }
   return true;
 }
+#ifndef ARTIS_HEAVY_BLOCKS
+#define ARTIS_HEAVY_BLOCKS 0  // resident blocks per SM of the every-other-role kernel next to the jump kernel; 0: as many as fit with >= 2 jump blocks
+#endif
 bool be_select_device(int device, std::string *why) {
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) {
@@ -800,27 +865,51 @@ bool be_select_device(int device, std::string *why) {
   }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) g_sms = prop.multiProcessorCount;
-  int nb = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_wavefront<1>, 128, 0) == cudaSuccess && nb > 0)
-    g_transport_blocks_per_sm = nb;
-  // every block of the persistent grids must be resident (idle warps wait for the others' packets): size the grids
-  // from the occupancy of each kernel alone, and in two-kernel mode from the registers the heavy kernel leaves free
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_transport_persistent<ROLES_ALL, 2>, 128, 0) == cudaSuccess && nb > 0)
-    g_blocks_all = nb;
+  // Every block of the persistent grids must be resident (idle warps wait for the others' packets): the grids are sized
+  // from the registers each kernel was compiled to. Registers are allocated per warp in units of 256 (8 per thread).
+  // The two kernels of the pair must be able to share an SM: the same L1 / shared-memory split for both (an SM cannot
+  // hold blocks of kernels with different carve-outs -- the second kernel would wait for the first to drain, which never
+  // happens here because each waits for the other's packets).
+  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_ALL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1), "carve-out");
+  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_HEAVY>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1), "carve-out");
+  note(cudaFuncSetAttribute(k_transport_majump, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1), "carve-out");
   {
-    cudaFuncAttributes ah{}, al{};
+    cudaFuncAttributes aa{}, ah{}, aj{};
     int regs_per_sm = 65536;
     cudaDeviceGetAttribute(&regs_per_sm, cudaDevAttrMaxRegistersPerMultiprocessor, device);
-    if (cudaFuncGetAttributes(&ah, k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS>) == cudaSuccess &&
-        cudaFuncGetAttributes(&al, k_transport_persistent<ROLES_LIGHT, LIGHT_MINBLOCKS>) == cudaSuccess && al.numRegs > 0) {
-      // registers are allocated per warp in units of 512 (256-register granularity x 2 is a safe upper bound)
-      const int heavy = ((ah.numRegs * 32 + 511) / 512) * 512 * 4, light = ((al.numRegs * 32 + 511) / 512) * 512 * 4;
-      g_blocks_heavy = HEAVY_MINBLOCKS >= 3 ? 2 : 1;
-      g_blocks_light = (regs_per_sm - g_blocks_heavy * heavy) / light;
-      if (g_blocks_light > 8) g_blocks_light = 8;
-      if (g_blocks_light < 1) g_scheduler_kernels = 1;  // no room next to the heavy kernel: one kernel with all roles
-    } else {
-      g_scheduler_kernels = 1;
+    auto block_regs = [](const cudaFuncAttributes &a) { return ((a.numRegs + 7) / 8) * 8 * 128; };
+    g_scheduler_kernels = 1;
+    if (cudaFuncGetAttributes(&aa, k_transport_persistent<ROLES_ALL>) == cudaSuccess && aa.numRegs > 0) {
+      g_blocks_all = regs_per_sm / block_regs(aa);
+      if (g_blocks_all > 4) g_blocks_all = 4;
+      if (g_blocks_all < 1) g_blocks_all = 1;
+    }
+    if (cudaFuncGetAttributes(&ah, k_transport_persistent<ROLES_HEAVY>) == cudaSuccess &&
+        cudaFuncGetAttributes(&aj, k_transport_majump) == cudaSuccess && ah.numRegs > 0 && aj.numRegs > 0) {
+      const int heavy = block_regs(ah), jump = block_regs(aj);
+      int hb = ARTIS_HEAVY_BLOCKS;
+      if (hb <= 0) {  // as many blocks of the big kernel as leave room for at least two blocks (8 warps) of jumps
+        hb = (regs_per_sm - 2 * jump) / heavy;
+        if (hb > 4) hb = 4;
+      }
+      if (hb < 1) hb = 1;
+      int jb = (regs_per_sm - hb * heavy) / jump;
+      if (jb > 12) jb = 12;  // 48 warps of jumps per SM are plenty; leaves thread and block slots for the big kernel
+      if ((hb + jb) * 128 > prop.maxThreadsPerMultiProcessor) jb = prop.maxThreadsPerMultiProcessor / 128 - hb;
+      // measurement knob: ARTIS_GEOMETRY="<blocks of the big kernel>,<blocks of the jump kernel>" per SM (must fit the SM)
+      if (const char *geo = getenv("ARTIS_GEOMETRY")) {
+        int a = 0, b2 = 0;
+        if (sscanf(geo, "%d,%d", &a, &b2) == 2 && a >= 1 && b2 >= 1 && a * heavy + b2 * jump <= regs_per_sm &&
+            (a + b2) * 128 <= prop.maxThreadsPerMultiProcessor) {
+          hb = a;
+          jb = b2;
+        }
+      }
+      if (jb >= 1) {
+        g_blocks_heavy = hb;
+        g_blocks_jump = jb;
+        g_scheduler_kernels = 2;
+      }
     }
   }
   if (g_stream == nullptr) {
@@ -853,7 +942,6 @@ void be_d2h(void *d, const void *s, size_t n) {
 }
 void be_zero(void *p, size_t n) { note(cudaMemsetAsync(p, 0, n, g_stream), "memset"); }
 void be_set_ctx(const artis::Ctx &c) {
-  g_nbfcontinua_ground = c.st.nbfcontinua_ground;
   note(cudaMemcpyToSymbolAsync(d_ctx, &c, sizeof(c), 0, cudaMemcpyHostToDevice, g_stream), "ctx upload");
   note(cudaStreamSynchronize(g_stream), "ctx sync");
 }
@@ -887,46 +975,40 @@ void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_s
 void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
-void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long n) {
+void be_run_unpack(const ArtisPacket *aos, PktHot *hot, PktCold *cold, long long n) {
+  if (n > 0) k_unpack<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(aos, hot, cold, n);
+}
+void be_run_pack(const PktHot *hot, const PktCold *cold, ArtisPacket *aos, long long n) {
+  if (n > 0) k_pack<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(hot, cold, aos, n);
+}
+void be_run_bin_escaped(const artis::BinSpec &b, const PktHot *hot, const PktCold *cold, long long n) {
   if (n <= 0) return;
   const size_t smem = (size_t)4 * b.ntstep * sizeof(double);
   const int in_smem = smem <= 32768;
-  k_bin_escaped<<<grid_for(n, 256, 8), 256, in_smem ? smem : 0, g_stream>>>(b, p, n, in_smem);
+  k_bin_escaped<<<grid_for(n, 256, 8), 256, in_smem ? smem : 0, g_stream>>>(b, hot, cold, n, in_smem);
 }
 // counts must hold n / ESC_CHUNK + 2 ints; afterwards counts[0..nchunks) are the chunks' output offsets, counts[nchunks] the total
-void be_run_escaped_count(const ArtisPacket *p, long long n, const unsigned char *reported, int only_new, int *counts) {
+void be_run_escaped_count(const PktHot *hot, long long n, const unsigned char *reported, int only_new, int *counts) {
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
-  if (nchunks > 0) k_escaped_count<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(p, n, reported, only_new, counts);
+  if (nchunks > 0) k_escaped_count<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(hot, n, reported, only_new, counts);
   k_escaped_scan<<<1, 1024, 0, g_stream>>>(counts, nchunks);
 }
-void be_run_escaped_scatter(const ArtisPacket *p, long long n, unsigned char *reported, int only_new, const int *offsets, ArtisPacket *out) {
+void be_run_escaped_scatter(const PktHot *hot, const PktCold *cold, long long n, unsigned char *reported, int only_new,
+                            const int *offsets, ArtisPacket *out) {
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
-  if (nchunks > 0) k_escaped_scatter<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(p, n, reported, only_new, offsets, out);
+  if (nchunks > 0) k_escaped_scatter<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(hot, cold, n, reported, only_new, offsets, out);
 }
-void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
-  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, r, n, buckets);
+void be_run_bucket(PktHot *hot, PktCold *cold, int n, int *buckets, int *kind_sizes, int *const *queues) {
+  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(hot, cold, n, buckets);
   k_bucket_scan<<<artis::NKIND, 1024, 0, g_stream>>>(buckets, kind_sizes);
-  k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(p, n, buckets, queues);
+  k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(hot, n, buckets, queues);
 }
-void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueView &qv, int kind, long long maxev, int block) {
-  if (block > 128) block = 128;  // __launch_bounds__
-  // persistent grid: every SM gets its full complement of resident blocks; the queue size is read on the device
-  const int grid = g_sms * g_transport_blocks_per_sm;
-  switch (kind) {
-    case 0: k_wavefront<0><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
-    case 1: k_wavefront<1><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
-    case 2: k_wavefront<2><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
-    case 4: k_wavefront<4><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
-    default: k_wavefront<3><<<grid, block, 0, g_stream>>>(p, r, qv, maxev); break;
-  }
-}
+// the kernel-rounds scheduler is the host build's (oracle) way of running the same visits; the device has none
+void be_run_wavefront(PktHot *, PktCold *, const artis::QueueView &, int, long long, int) {}
 // barrier-free scheduler: rings = NRING rings of `cap` ints (initial entries written by be_run_bucket, -1 elsewhere),
-// pmeta = head[NRING], tail[NRING], n_active (int), t_start, each on its own RING_META_STRIDE words.
-// g_scheduler_kernels == 2: the light kernel (macro-atom/k-packet and opacity-on-request roles, <= 80 registers, 3 blocks
-// per SM) and the heavy kernel (everything else, 1 block per SM) run side by side on two streams and exchange packets
-// through the rings; 1: one kernel with every role (2 blocks per SM of ~250 registers).
-bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int cap, unsigned long long *pmeta, int n_initial,
-                       long long maxev) {
+// pmeta = head[NRING], tail[NRING], n_active (int), t_start, each on its own RING_META_STRIDE words; pend = [cap] words.
+bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned long long *pmeta, unsigned long long *pend,
+                       int n_initial, long long maxev) {
   PersistView pv;
   for (int k = 0; k < NRING; k++) pv.ring[k] = rings + (size_t)k * cap;
   pv.head = pmeta;
@@ -935,25 +1017,7 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
   pv.n_initial = n_initial;
   pv.t_start = pmeta + (2 * NRING + 1) * RMS;
   pv.cap = cap;
-  const int kstride = 8 + g_nbfcontinua_ground;
-  const bool two = g_scheduler_kernels == 2;
-  if (two && (size_t)cap * kstride > g_kcache_doubles) {
-    if (g_kcache) cudaFree(g_kcache);
-    if (g_stepstate) cudaFree(g_stepstate);
-    g_kcache = nullptr;
-    g_stepstate = nullptr;
-    g_kcache_doubles = 0;
-    if (cudaMalloc(&g_kcache, (size_t)cap * kstride * sizeof(double)) != cudaSuccess ||
-        cudaMalloc(&g_stepstate, (size_t)cap * 3 * sizeof(double)) != cudaSuccess) {
-      note(cudaGetLastError(), "cudaMalloc (opacity hand-over buffers)");
-      return true;  // be_sync reports the error
-    }
-    g_kcache_doubles = (size_t)cap * kstride;
-  }
-  pv.kcache = g_kcache;
-  pv.stepstate = g_stepstate;
-  pv.kstride = kstride;
-  pv.offload_kappa = two ? 1 : 0;
+  pv.pend = pend;
   const unsigned long long timeout = g_idle_timeout_ns;
   if (!g_persistent_warmed) {
     // First launch of each persistent kernel with nothing to do (n_active == 0: every warp leaves at once). A first
@@ -968,31 +1032,39 @@ bool be_run_persistent(ArtisPacket *p, unsigned long long *r, int *rings, int ca
       w.n_active = reinterpret_cast<int *>(scratch + 2 * NRING * RMS);
       w.t_start = scratch + (2 * NRING + 1) * RMS;
       w.n_initial = 0;
-      k_transport_persistent<ROLES_ALL, 2><<<1, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
-      k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS><<<1, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
-      k_transport_persistent<ROLES_LIGHT, LIGHT_MINBLOCKS><<<g_sms * g_blocks_light, 128, 0, g_stream>>>(p, r, w, maxev, timeout);
+      k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, 0, g_stream>>>(hot, cold, w, maxev, timeout);
+      k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, 0, g_stream>>>(hot, cold, w, maxev, timeout);
+      if (g_blocks_jump > 0) k_transport_majump<<<g_sms * g_blocks_jump, 128, 0, g_stream>>>(hot, w, maxev, timeout);
       note(cudaStreamSynchronize(g_stream), "warm-up sync");
       cudaFree(scratch);
     }
     g_persistent_warmed = true;
   }
-  if (!two) {
-    k_transport_persistent<ROLES_ALL, 2><<<g_sms * g_blocks_all, 128, 0, g_stream>>>(p, r, pv, maxev, timeout);
+  if (g_scheduler_kernels != 2) {
+    k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, 0, g_stream>>>(hot, cold, pv, maxev, timeout);
     return true;
   }
-  // the heavy kernel goes first (its blocks are the big ones), the light kernel fills the rest of every SM; the side
-  // stream waits for what is queued on the main stream (ring setup) and the main stream waits for the side kernel
+  // the big kernel goes first, the jump kernel fills the rest of every SM; the side stream waits for what is queued on the
+  // main stream (ring setup) and the main stream waits for the side kernel
   note(cudaEventRecord(g_ev_fork, g_stream), "event record");
   note(cudaStreamWaitEvent(g_stream2, g_ev_fork, 0), "stream wait");
-  k_transport_persistent<ROLES_HEAVY, HEAVY_MINBLOCKS><<<g_sms * g_blocks_heavy, 128, 0, g_stream>>>(p, r, pv, maxev, timeout);
-  k_transport_persistent<ROLES_LIGHT, LIGHT_MINBLOCKS><<<g_sms * g_blocks_light, 128, 0, g_stream2>>>(p, r, pv, maxev, timeout);
+  k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, 0, g_stream>>>(hot, cold, pv, maxev, timeout);
+  k_transport_majump<<<g_sms * g_blocks_jump, 128, 0, g_stream2>>>(hot, pv, maxev, timeout);
   note(cudaEventRecord(g_ev_join, g_stream2), "event record");
   note(cudaStreamWaitEvent(g_stream, g_ev_join, 0), "stream wait");
   return true;
 }
 void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }
 void be_set_scheduler_kernels(int n) {
-  if (n == 1 || (n == 2 && g_blocks_light >= 1)) g_scheduler_kernels = n;
+  if (n == 1 || (n == 2 && g_blocks_jump >= 1)) g_scheduler_kernels = n;
+}
+int be_persistent_kernels() { return g_scheduler_kernels == 2 ? 2 : 1; }
+int be_scheduler_geometry(int *out) {  // kernels, blocks per SM of: single kernel, big kernel, jump kernel
+  out[0] = g_scheduler_kernels;
+  out[1] = g_blocks_all;
+  out[2] = g_blocks_heavy;
+  out[3] = g_blocks_jump;
+  return 4;
 }
 void be_set_idle_timeout_ms(long long ms) { g_idle_timeout_ns = (unsigned long long)ms * 1000000ull; }
 void be_set_estimator_block(double *block, size_t ndoubles) {

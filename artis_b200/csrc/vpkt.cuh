@@ -84,7 +84,7 @@ ARTIS_DEV void add_to_vpkt_grid(const Ctx &c, const double nu_rf, const double e
 // start cell. A departure ratio that the start cell never needed is evaluated from the start cell's populations with the
 // current cell's n_e and T_e, as the reference does on first use (rpkt.cc:1136-1145; later uses of that cached value by
 // other cells are not tracked -- it only arises for continua absent from the start cell).
-ARTIS_DEV void vpkt_kappa_cont(const Ctx &c, const ArtisPacket &d, const int mgi, const int tc0, KappaCache &k, Tally &tl) {
+ARTIS_DEV void vpkt_kappa_cont(const Ctx &c, const Pkt &d, const int mgi, const int tc0, KappaCache &k, Tally &tl) {
   const double nu = d.nu_cmf;
   if (kappa_cache_hit(k, mgi, nu)) return;
   tl.kappa_evals++;
@@ -131,12 +131,12 @@ ARTIS_DEV void vpkt_kappa_cont(const Ctx &c, const ArtisPacket &d, const int mgi
 // vpkt.cc:76-364 rlc_emiss_vpkt. `pk` is the real packet (read only), `k` the opacity scratch of this thread (the
 // reference's globals::kappa_rpkt_cont[tid], shared between the real packet and its virtual packets). Returns the
 // change of the virtual-packet counters: bit 0 = a virtual packet was created, bit 1 = it reached the edge of the grid.
-ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const ArtisPacket &pk, const double t_current, const int bin, double *obs,
-                             const int realtype, KappaCache &k, Tally &tl) {
+ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u, const double t_current,
+                             const int bin, double *obs, const int realtype, KappaCache &k, Tally &tl) {
   const int nspectra = c.st.vpkt_nspectra;
   double tau_vpkt[VPKT_MAX_SPECTRA];
   for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_vpkt[ind] = 0;
-  ArtisPacket dummy = pk;
+  Pkt dummy = pk;
   bool end_packet = false;
   double t_future = t_current;
   dummy.dir[0] = obs[0];
@@ -146,7 +146,7 @@ ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const ArtisPacket &pk, const double t
   get_velocity(pk.pos, vel_vec, t_current);
   dummy.nu_rf = dummy.nu_cmf / doppler_nucmf_on_nurf(c, dummy.dir, vel_vec);
   dummy.e_rf = dummy.e_cmf * dummy.nu_rf / dummy.nu_cmf;
-  double Qi = dummy.stokes[1], Ui = dummy.stokes[2];
+  double Qi = stokes_q, Ui = stokes_u;  // Stokes Q, U of the real packet (used by the scattering phase function only)
   double I = 0., Q = 0., U = 0., pn = 0.;
   if (realtype == 1) {  // electron scattering: dipole phase function and Stokes rotation (Bulla et al. 2015)
     double dir_in[3] = {pk.dir[0], pk.dir[1], pk.dir[2]};
@@ -278,7 +278,8 @@ ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const ArtisPacket &pk, const double t
 // Owns its opacity scratch and work tally, like a host thread of the reference owns kappa_rpkt_cont[tid]; returns 1 when
 // at least one virtual packet was sent (the caller then drops its own cached opacity, as cellhistory_reset +
 // calculate_kappa_rpkt_cont at vpkt.cc:887-893 re-evaluate it at the packet's exact frequency).
-ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const ArtisPacket pk, const double t_current, const int realtype) {
+ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const Pkt pk, const double stokes_q, const double stokes_u,
+                                            const double t_current, const int realtype) {
   const int mgi = cell_mgi(c, pk.where);
   if (c.cs.thick[mgi] != 0) return 0;
   Tally tl = {};
@@ -298,7 +299,7 @@ ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const ArtisPacket pk, 
       for (int i = 0; i < c.st.vpkt_nrange; i++) {
         const double nu_rf = pk.nu_cmf / doppler_nucmf_on_nurf(c, obs, vel_vec);
         if (nu_rf > c.st.vpkt_numin_input[i] && nu_rf < c.st.vpkt_numax_input[i]) {
-          const int r = rlc_emiss_vpkt(c, pk, t_current, bin, obs, realtype, k, tl);
+          const int r = rlc_emiss_vpkt(c, pk, stokes_q, stokes_u, t_current, bin, obs, realtype, k, tl);
           created += (r & 1);
           escaped += (r >> 1) & 1;
           vflag = 1;
@@ -318,19 +319,20 @@ ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const ArtisPacket pk, 
 // electron scattering changes the direction and the Stokes vector (rpkt.cc:359 -- those five numbers travel with the
 // request). Each scheduler calls this once, right after an event returns, so that the transport kernels hold a single
 // call site of the out-of-line ray trace.
-ARTIS_DEV void vpkt_flush_request(const Ctx &c, const ArtisPacket &p, KappaCache &k, Tally &tl) {
+ARTIS_DEV void vpkt_flush_request(const Ctx &c, const Pkt &p, KappaCache &k, Tally &tl) {
   const int realtype = tl.vpkt_req;
   if (realtype == 0) return;
   tl.vpkt_req = 0;
-  ArtisPacket q = p;
+  Pkt q = p;
+  double stokes_q = 0., stokes_u = 0.;  // only an electron scattering (realtype 1) looks at the incoming polarisation
   if (realtype == 1) {
     q.dir[0] = tl.vpkt_dir[0];
     q.dir[1] = tl.vpkt_dir[1];
     q.dir[2] = tl.vpkt_dir[2];
-    q.stokes[1] = tl.vpkt_q;
-    q.stokes[2] = tl.vpkt_u;
+    stokes_q = tl.vpkt_q;
+    stokes_u = tl.vpkt_u;
   }
-  if (vpkt_call_estimators(c, q, q.prop_time, realtype)) k.valid = false;
+  if (vpkt_call_estimators(c, q, stokes_q, stokes_u, q.prop_time, realtype)) k.valid = false;
 }
 
 }  // namespace artis

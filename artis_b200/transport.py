@@ -112,6 +112,12 @@ class Transport:
     def set_tuning(self, max_events_per_pass=0, block_threads=0):
         self.lib.artis_gpu_set_tuning(max_events_per_pass, block_threads)
 
+    def scheduler_geometry(self):
+        """(kernels per timestep, blocks per SM of: the single kernel, the every-other-role kernel, the jump kernel)"""
+        g = (C.c_int * 4)()
+        self.lib.artis_gpu_scheduler_geometry(g, 4)
+        return [g[i] for i in range(4)]
+
     def launch_count(self):
         return int(self.lib.artis_gpu_launch_count())
 

@@ -225,7 +225,7 @@ def main():
     ap.add_argument("--cpu-baseline", default="auto", choices=["auto", "off"])
     ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
     ap.add_argument("--scheduler-kernels", type=int, default=0, choices=(0, 1, 2),
-                    help="1: one persistent kernel with every role, 2: light + heavy kernels side by side (0: library default)")
+                    help="1: one persistent kernel with every role, 2: macro-atom jump kernel + every-other-role kernel (0: library default)")
     ap.add_argument("--workload", default="classic", choices=["classic", "nebular", "fixture"])
     a = ap.parse_args()
     select_workload(a.workload)
@@ -270,8 +270,8 @@ def main():
     T.upload_cellstate(cs)
     if a.max_events:
         T.set_tuning(max_events_per_pass=a.max_events)
-    if a.scheduler_kernels:
-        T.set_tuning(block_threads=-3 if a.scheduler_kernels == 1 else -4)
+    if a.scheduler_kernels or os.environ.get("ARTIS_BENCH_SCHED"):
+        T.set_tuning(block_threads=-3 if int(a.scheduler_kernels or os.environ["ARTIS_BENCH_SCHED"]) == 1 else -4)
     precompute_ms = T.last_timings()[3]
     ptr, ndoubles = T.estimator_block()
     if world > 1:
@@ -387,6 +387,7 @@ def main():
                            "mean_busy_lanes_by_kind": [round(float(ctr_sum[72 + i]) / max(float(ctr_sum[64 + i]), 1.0), 2) for i in range(8)],
                            "warp_Mcycles_by_kind": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[80:88]],
                            "warp_Mcycles_refill_push_idle": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[88:91]],
+                           "scheduler_geometry_kernels_blocks_single_big_jump": T.scheduler_geometry(),
                            "allreduce_ms_per_step": allreduce_ms / a.steps,
                            "estimator_block_bytes": int(ndoubles * 8),
                            "events_per_s": float(ctr_sum[49]) / (tot_ms * 1e-3),

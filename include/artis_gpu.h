@@ -188,8 +188,12 @@ int artis_gpu_last_timings(double *ms, int n);
  * per-cell tables that replace the reference's cellhistory cache. */
 long long artis_gpu_launch_count(void);
 size_t artis_gpu_table_bytes(void);
+/* Geometry of the persistent scheduler for the measurement harness: out[0] kernels per timestep (1: one kernel with every
+ * role, 2: macro-atom jump kernel + every-other-role kernel), out[1..3] resident 128-thread blocks per SM of the single
+ * kernel / the every-other-role kernel / the jump kernel. */
+int artis_gpu_scheduler_geometry(int *out, int n);
 /* Tunables (0 keeps the default): events a thread may process before it yields its packet for re-bucketing;
- * threads per block. block_threads <= -1000 sets the hang guard of the persistent scheduler instead: the timestep is
+ * block_threads -3 / -4: one persistent kernel with every role / the two-kernel scheduler (default). block_threads <= -1000 sets the hang guard of the persistent scheduler instead: the timestep is
  * given up with ARTIS_ERR_TRANSPORT (device code 900) when no packet has finished for (-1000 - block_threads) seconds
  * (default 20; the guard looks at progress of the whole timestep, not at how long one warp has been idle). */
 int artis_gpu_set_tuning(int max_events_per_pass, int block_threads);

@@ -42,44 +42,56 @@ void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g
 void be_run_corrphoto(long long n) { for (long long i = 0; i < n; i++) artis::body_corrphoto(g_ctx, i); }
 void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
 void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
-void be_run_bin_escaped(const artis::BinSpec &b, const ArtisPacket *p, long long n) {
-  for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, p, i, b.lc);
+using artis::PktCold;
+using artis::PktHot;
+void be_run_unpack(const ArtisPacket *aos, PktHot *hot, PktCold *cold, long long n) {
+  for (long long i = 0; i < n; i++) artis::pkt_split(aos[i], hot[i], cold[i]);
 }
-void be_run_escaped_count(const ArtisPacket *p, long long n, const unsigned char *reported, int only_new, int *counts) {
+void be_run_pack(const PktHot *hot, const PktCold *cold, ArtisPacket *aos, long long n) {
+  for (long long i = 0; i < n; i++) artis::pkt_join(hot[i], cold[i], aos[i]);
+}
+void be_run_bin_escaped(const artis::BinSpec &b, const PktHot *hot, const PktCold *cold, long long n) {
+  for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, hot, cold, i, b.lc);
+}
+void be_run_escaped_count(const PktHot *hot, long long n, const unsigned char *reported, int only_new, int *counts) {
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
   int run = 0;
   for (int c = 0; c < nchunks; c++) {
     counts[c] = run;
     for (long long i = (long long)c * artis::ESC_CHUNK; i < n && i < (long long)(c + 1) * artis::ESC_CHUNK; i++)
-      run += artis::escaped_selected(p, reported, only_new, i);
+      run += artis::escaped_selected(hot, reported, only_new, i);
   }
   counts[nchunks] = run;
 }
-void be_run_escaped_scatter(const ArtisPacket *p, long long n, unsigned char *reported, int only_new, const int *offsets, ArtisPacket *out) {
+void be_run_escaped_scatter(const PktHot *hot, const PktCold *cold, long long n, unsigned char *reported, int only_new,
+                            const int *offsets, ArtisPacket *out) {
   (void)offsets;
   int k = 0;
   for (long long i = 0; i < n; i++) {
-    if (!artis::escaped_selected(p, reported, only_new, i)) continue;
-    out[k++] = p[i];
+    if (!artis::escaped_selected(hot, reported, only_new, i)) continue;
+    artis::pkt_join(hot[i], cold[i], out[k++]);
     if (only_new) reported[i] = 1;
   }
 }
-void be_run_bucket(ArtisPacket *p, unsigned long long *r, int n, int *buckets, int *kind_sizes, int *const *queues) {
-  for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, p, r, i, buckets);
+void be_run_bucket(PktHot *hot, PktCold *cold, int n, int *buckets, int *kind_sizes, int *const *queues) {
+  for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, hot, cold, i, buckets);
   artis::body_bucket_scan(g_ctx, buckets, kind_sizes);
-  for (int i = 0; i < n; i++) artis::body_bucket_scatter(g_ctx, p, i, buckets, queues);
+  for (int i = 0; i < n; i++) artis::body_bucket_scatter(g_ctx, hot, i, buckets, queues);
 }
-void be_run_wavefront(ArtisPacket *p, unsigned long long *r, const artis::QueueView &qv, int kind, long long maxev, int) {
+void be_run_wavefront(PktHot *hot, PktCold *cold, const artis::QueueView &qv, int kind, long long maxev, int) {
   switch (kind) {  // one "thread" drains the whole queue
-    case 0: artis::body_wavefront<0>(g_ctx, p, r, qv, maxev); break;
-    case 1: artis::body_wavefront<1>(g_ctx, p, r, qv, maxev); break;
-    case 2: artis::body_wavefront<2>(g_ctx, p, r, qv, maxev); break;
-    case 4: artis::body_wavefront<4>(g_ctx, p, r, qv, maxev); break;
-    default: artis::body_wavefront<3>(g_ctx, p, r, qv, maxev); break;
+    case 0: artis::body_wavefront<0>(g_ctx, hot, cold, qv, maxev); break;
+    case 1: artis::body_wavefront<1>(g_ctx, hot, cold, qv, maxev); break;
+    case 2: artis::body_wavefront<2>(g_ctx, hot, cold, qv, maxev); break;
+    case 4: artis::body_wavefront<4>(g_ctx, hot, cold, qv, maxev); break;
+    case 5: artis::body_wavefront<5>(g_ctx, hot, cold, qv, maxev); break;
+    default: artis::body_wavefront<3>(g_ctx, hot, cold, qv, maxev); break;
   }
 }
 // the barrier-free scheduler is a device-only construct; the host backend runs the same visits as kernel rounds
-bool be_run_persistent(ArtisPacket *, unsigned long long *, int *, int, unsigned long long *, int, long long) { return false; }
+bool be_run_persistent(PktHot *, PktCold *, int *, int, unsigned long long *, unsigned long long *, int, long long) { return false; }
+int be_persistent_kernels() { return 0; }
+int be_scheduler_geometry(int *) { return 0; }
 void be_fill_bytes(void *p, int byte, size_t n) { memset(p, byte, n); }
 void be_set_estimator_block(double *, size_t) {}
 void be_set_scheduler_kernels(int) {}

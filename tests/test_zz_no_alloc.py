@@ -21,6 +21,11 @@ def _packets(n, seed, frac_escaped):
     pk["type"] = types[rng.integers(0, types.size, size=n)]
     pk["type"][rng.random(n) < frac_escaped] = abi.TYPE_ESCAPE
     pk["number"] = np.arange(n, dtype=np.int32)
+    # the resident ensemble of the existing entry point keeps the two enums and the macro-atom element / ion in 16 bits
+    # each (common.cuh PktHot): give them values of their own ranges, everything else stays random bytes
+    pk["last_cross"] = rng.integers(101, 108, size=n)
+    pk["ma_element"] = rng.integers(0, 30, size=n)
+    pk["ma_ion"] = rng.integers(0, 10, size=n)
     return pk
 
 

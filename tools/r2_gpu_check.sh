@@ -1,6 +1,6 @@
-#!/bin/sh
+#!/bin/bash
 # One gpurun call: GPU parity tests, smoke, the bench lines of both arms on the named workload, the launch list.
-#   gpurun --timeout 1500 -- sh tools/r2_gpu_check.sh [tag]
+#   gpurun --timeout 1500 -- bash tools/r2_gpu_check.sh [tag]
 TAG=${1:-check}
 O=gpurun_out/$TAG
 mkdir -p $O
