@@ -270,7 +270,7 @@ enum { RPKT_EVENTTYPE_NONE = -1, RPKT_EVENTTYPE_BB = 550, RPKT_EVENTTYPE_CONT = 
 // which is the correctly rounded quotient (Markstein's theorem: the reciprocal is correctly rounded and nu_edge's
 // significand is not all ones -- checked at init, the plain division is used otherwise), i.e. the same bits as
 // nu / nu_edge at a fifth of the instructions (no reciprocal seed, no Newton iterations).
-struct ContRec {
+struct alignas(16) ContRec {
   double nu_edge;
   double inv_nu_edge;   // 0 when the fast quotient is not provably exact for this divisor
   double probability;
@@ -375,7 +375,13 @@ ARTIS_DEV uint32_t mulhi32(uint32_t a, uint32_t b) {
   return (uint32_t)(((uint64_t)a * (uint64_t)b) >> 32);
 #endif
 }
-ARTIS_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]) {
+// Out of line on the device (ARTIS_DEV_NOINLINE; arguments and result in registers): the generator is called from ~40
+// places of the transport kernels, and the kernels' code footprint -- not their arithmetic -- is what the schedulers wait
+// for (profiles/r2_notes.md: no-instruction stalls 8 cycles per issued instruction with 1.6 MB of SASS).
+struct Philox4 {
+  uint32_t x, y, z, w;
+};
+ARTIS_DEV_NOINLINE Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
   for (int r = 0; r < 10; r++) {
@@ -389,10 +395,12 @@ ARTIS_DEV void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
     k0 += W0;
     k1 += W1;
   }
-  out[0] = c0;
-  out[1] = c1;
-  out[2] = c2;
-  out[3] = c3;
+  Philox4 o;
+  o.x = c0;
+  o.y = c1;
+  o.z = c2;
+  o.w = c3;
+  return o;
 }
 ARTIS_DEV Rng rng_init(const Ctx &c, const int number, const uint64_t ctr) {
   Rng r;
@@ -419,13 +427,12 @@ ARTIS_DEV double rng_uniform(Rng &r) {
     r.spare = -1.;
     return x;
   }
-  uint32_t o[4];
   // a packet draws far fewer than 2^33 numbers per timestep; the high word of the block index is folded into the
   // timestep word so that even such a stream would stay unique
-  philox4x32_10((uint32_t)(blk & 0xffffffffu), r.c1, r.c2 ^ ((uint32_t)(blk >> 32) << 16), r.c3, r.k0, r.k1, o);
-  if (odd) return bits_to_unit(o[2], o[3]);  // stream resumed on an odd draw (spare was lost between passes)
-  r.spare = bits_to_unit(o[2], o[3]);
-  return bits_to_unit(o[0], o[1]);
+  const Philox4 o = philox4x32_10((uint32_t)(blk & 0xffffffffu), r.c1, r.c2 ^ ((uint32_t)(blk >> 32) << 16), r.c3, r.k0, r.k1);
+  if (odd) return bits_to_unit(o.z, o.w);  // stream resumed on an odd draw (spare was lost between passes)
+  r.spare = bits_to_unit(o.z, o.w);
+  return bits_to_unit(o.x, o.y);
 }
 // (0,1) like gsl_rng_uniform_pos
 ARTIS_DEV double rng_uniform_pos(Rng &r) {
@@ -562,7 +569,7 @@ ARTIS_DEV void scatter_dir(Rng &r, const double dir_in[3], const double cos_thet
 // shuffles and the lowest lane issues one red.global.add.f64 for all of them. The lanes taking part are exactly those
 // converged at the call (__activemask), so this is safe inside divergent event code. Returns the number of global
 // reductions issued by this lane (1 for a group leader, else 0): ARTIS_CTR_ESTIM_ATOMICS counts what reaches L2.
-ARTIS_DEV int est_add(double *addr, double v) {
+ARTIS_DEV_NOINLINE int est_add(double *addr, double v) {  // one copy in a kernel: ~40 call sites, a shuffle loop each
   const unsigned act = __activemask();
   const unsigned peers = __match_any_sync(act, (unsigned long long)addr);
   const int lane = threadIdx.x & 31;
@@ -648,6 +655,24 @@ ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
     if (t.stats[i]) ctr_add(&k[i], t.stats[i]);
 #endif
 }
+// Event routines out of line. A step of a packet is straight-line code that every warp iteration runs once; what it may
+// END in -- a scattering with its Stokes rotations, an emission, a macro-atom de-activation, a k-packet's cooling-channel
+// search -- is rare per step, large (FP64 trigonometry, rejection loops) and was inlined at several places each: the
+// transport kernel was 1.6 MB of SASS and its warps spent 8 cycles per issued instruction waiting for instructions. Each
+// such routine now exists once per kernel behind a real call. Its working state goes through memory for the call (a copy
+// of the packet's working set, its Philox stream and the work tally: EvState), so that the caller's packet never has its
+// address taken and stays in registers on the per-step path.
+struct EvState {
+  Pkt p;
+  Rng rng;
+  Tally tl;
+};
+#ifdef __CUDA_ARCH__
+#define ARTIS_EVENT_OOL 1
+#else
+#define ARTIS_EVENT_OOL 0
+#endif
+
 // the FIRST fatal code of a timestep is the one reported (later ones are usually its consequences)
 ARTIS_DEV void fatal(const Ctx &c, int code) {
   if (c.error_flag == nullptr) return;

@@ -119,7 +119,7 @@ ARTIS_DEV double thomson_angle(const Ctx &c, Rng &rng) {
   return mu;
 }
 // gammapkt.cc:421-531
-ARTIS_DEV void compton_scatter(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void compton_scatter_body(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   double f;
   const double xx = H * p.nu_cmf / ME / CLIGHT / CLIGHT;
   bool stay_gamma;
@@ -166,8 +166,23 @@ ARTIS_DEV void compton_scatter(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
     stat_inc(tl, COUNTER_NT_STAT_FROM_GAMMA);
   }
 }
+ARTIS_DEV_NOINLINE void compton_scatter_ool(const Ctx &c, EvState *s) { compton_scatter_body(c, s->p, s->rng, s->tl); }
+ARTIS_DEV void compton_scatter(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  compton_scatter_ool(c, &s);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  compton_scatter_body(c, p, rng, tl);
+#endif
+}
 // photo_electric.cc:116-164
-ARTIS_DEV void pair_prod(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void pair_prod_body(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   const double prob_gamma = 1.022 * MEV / (H * p.nu_cmf);
   if (prob_gamma < 0) fatal(c, 405);
   const double zrand = rng_uniform(rng);
@@ -188,6 +203,21 @@ ARTIS_DEV void pair_prod(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
     p.type = ARTIS_TYPE_GAMMA;
     p.last_cross = ARTIS_CROSS_NONE;
   }
+}
+ARTIS_DEV_NOINLINE void pair_prod_ool(const Ctx &c, EvState *s) { pair_prod_body(c, s->p, s->rng, s->tl); }
+ARTIS_DEV void pair_prod(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  pair_prod_ool(c, &s);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  pair_prod_body(c, p, rng, tl);
+#endif
 }
 
 // gammapkt.cc:533-700 do_gamma (GRID_UNIFORM)
@@ -309,7 +339,7 @@ ARTIS_DEV void pellet_gamma_decay(const Ctx &c, Pkt &p, Rng &rng) {
 }
 
 // update_packets.cc:71-135 update_pellet
-ARTIS_DEV void update_pellet(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
+ARTIS_DEV void update_pellet_body(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
   const double ts = p.prop_time;
   const double tdecay = ldcold(&p.cold->tdecay);
   double *tsc = c.es.ts_scalars;
@@ -352,9 +382,24 @@ ARTIS_DEV void update_pellet(const Ctx &c, Pkt &p, const double t2, Rng &rng, Ta
     p.prop_time = t2;
   }
 }
+ARTIS_DEV_NOINLINE void update_pellet_ool(const Ctx &c, EvState *s, const double t2) { update_pellet_body(c, s->p, t2, s->rng, s->tl); }
+ARTIS_DEV void update_pellet(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  update_pellet_ool(c, &s, t2);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  update_pellet_body(c, p, t2, rng, tl);
+#endif
+}
 
 // update_packets.cc:16-69 do_nonthermal_predeposit
-ARTIS_DEV void do_nonthermal_predeposit(const Ctx &c, Pkt &p, const double t2, Rng &rng) {
+ARTIS_DEV void do_nonthermal_predeposit_body(const Ctx &c, Pkt &p, const double t2, Rng &rng) {
   const double ts = p.prop_time;
   const int decaytype = ldcold(&p.cold->pellet_decaytype);
   const double particle_en = H * p.nu_cmf;
@@ -384,6 +429,19 @@ ARTIS_DEV void do_nonthermal_predeposit(const Ctx &c, Pkt &p, const double t2, R
     vec_scale(p.pos, t2 / ts);
     p.prop_time = t2;
   }
+}
+ARTIS_DEV_NOINLINE void do_nonthermal_predeposit_ool(const Ctx &c, EvState *s, const double t2) { do_nonthermal_predeposit_body(c, s->p, t2, s->rng); }
+ARTIS_DEV void do_nonthermal_predeposit(const Ctx &c, Pkt &p, const double t2, Rng &rng) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  do_nonthermal_predeposit_ool(c, &s, t2);
+  p = s.p;
+  rng = s.rng;
+#else
+  do_nonthermal_predeposit_body(c, p, t2, rng);
+#endif
 }
 
 // update_packets.cc:137-202 do_packet. The r-packet case runs ONE do_rpkt_step instead of do_rpkt's whole loop, so
@@ -466,7 +524,17 @@ ARTIS_DEV void do_packet_kind(const Ctx &c, Pkt &p, const double t2, KappaCache 
       }
     }
   } else {
-    do_packet(c, p, t2, k, rng, tl);
+    // KIND_OTHER: pellets and non-thermal pre-deposition only (update_packets.cc:137-202 for these two types) -- calling
+    // the whole do_packet here would put a second copy of every other kind's physics into the kernel
+    tl.packet_updates++;
+    if (p.type == ARTIS_TYPE_RADIOACTIVE_PELLET) {
+      update_pellet(c, p, t2, rng, tl);
+    } else if (p.type == ARTIS_TYPE_NONTHERMAL_PREDEPOSIT) {
+      do_nonthermal_predeposit(c, p, t2, rng);
+    } else {
+      fatal(c, 441);
+      p.prop_time = t2;
+    }
   }
 }
 

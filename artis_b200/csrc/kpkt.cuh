@@ -20,7 +20,7 @@ ARTIS_DEV double sample_planck(const Ctx &c, const double T, Rng &rng) {
 }
 
 // kpkt.cc:448-475
-ARTIS_DEV void do_kpkt_bb(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_kpkt_bb_body(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   const int mgi = cell_mgi(c, p.where);
   const float T_e = c.cs.Te[mgi];
   p.nu_cmf = sample_planck(c, (double)T_e, rng);
@@ -33,6 +33,21 @@ ARTIS_DEV void do_kpkt_bb(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   p.last_event = 6;
   p.cold->emissiontype = -9999999;
   mark_emission(p);
+}
+ARTIS_DEV_NOINLINE void do_kpkt_bb_ool(const Ctx &c, EvState *s) { do_kpkt_bb_body(c, s->p, s->rng, s->tl); }
+ARTIS_DEV void do_kpkt_bb(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  do_kpkt_bb_ool(c, &s);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  do_kpkt_bb_body(c, p, rng, tl);
+#endif
 }
 
 // std::lower_bound over cum[lo .. hi]: first index with cum[i] >= value (hi + 1 if none)
@@ -49,7 +64,7 @@ ARTIS_DEV int lower_bound_idx(const double *cum, int lo, const int hi, const dou
 }
 
 // kpkt.cc:477-797
-ARTIS_DEV void do_kpkt(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_kpkt_body(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
   tl.kpkt_events++;
   const double t1 = p.prop_time;
   const int mgi = cell_mgi(c, p.where);
@@ -167,12 +182,27 @@ ARTIS_DEV void do_kpkt(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &t
     p.prop_time = t2;
   }
 }
+ARTIS_DEV_NOINLINE void do_kpkt_ool(const Ctx &c, EvState *s, const double t2) { do_kpkt_body(c, s->p, t2, s->rng, s->tl); }
+ARTIS_DEV void do_kpkt(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  do_kpkt_ool(c, &s, t2);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  do_kpkt_body(c, p, t2, rng, tl);
+#endif
+}
 
 // nonthermal.cc:1877-1978 do_ntlepton. Without the Spencer-Fano solution (classic, kilonova_lte) every non-thermal
 // lepton thermalises into a k-packet; with it (nebular NLTE) a fraction get_ntion_energyrate / deposition_rate_density
 // activates a macro-atom by non-thermal ionisation (select_nt_ionization2, nonthermal.cc:1858-1875). NT_EXCITATION_ON
 // is false in every shipped options header (frac_excitation = 0., nonthermal.cc:1898).
-ARTIS_DEV void do_ntlepton(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+ARTIS_DEV void do_ntlepton_body(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   est_add(&c.es.ts_scalars[ARTIS_TS_NT_ENERGY_DEPOSITED], p.e_cmf);
   const int mgi = cell_mgi(c, p.where);
   if (ARTIS_OPT_NT_SF(c) && c.cs.thick[mgi] != 1) {
@@ -225,6 +255,21 @@ ARTIS_DEV void do_ntlepton(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   p.last_event = 22;
   p.type = ARTIS_TYPE_KPKT;
   stat_inc(tl, COUNTER_NT_STAT_TO_KPKT);
+}
+ARTIS_DEV_NOINLINE void do_ntlepton_ool(const Ctx &c, EvState *s) { do_ntlepton_body(c, s->p, s->rng, s->tl); }
+ARTIS_DEV void do_ntlepton(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  do_ntlepton_ool(c, &s);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  do_ntlepton_body(c, p, rng, tl);
+#endif
 }
 
 }  // namespace artis

@@ -63,7 +63,7 @@ ARTIS_DEV double gl8(const Ctx &c, const int tablerow, const double nu_edge, con
 // integrals are evaluated once with a fixed 8-point rule per smooth sub-interval (pieces are split at the knots of
 // the cross-section table) and the tails are their suffix sums. Selection rule and interpolation are the
 // reference's, including the extrapolation when no piece is selected. Tolerance: |dnu/nu| <= 1e-3 (tests).
-ARTIS_DEV double select_continuum_nu(const Ctx &c, const int ui_lower, const int gl_lower, const int upperionlevel, const float T_e,
+ARTIS_DEV_NOINLINE double select_continuum_nu(const Ctx &c, const int ui_lower, const int gl_lower, const int upperionlevel, const float T_e,
                                      Rng &rng) {
   const int t = phixstargetindex_of(c, gl_lower, upperionlevel);
   if (t < 0) {
@@ -215,7 +215,7 @@ ARTIS_DEV int ma_jump(const Ctx &c, P &p, Rng &rng, Tally &tl, int *sel_out) {
 }
 
 // `action` and `selidx` are what ma_jump returned (selidx: index of the selected downward transition for MA_RADDEEXC)
-ARTIS_DEV void ma_event(const Ctx &c, Pkt &p, const int action, const int selidx, Rng &rng, Tally &tl) {
+ARTIS_DEV void ma_event_body(const Ctx &c, Pkt &p, const int action, const int selidx, Rng &rng, Tally &tl) {
   if (action == MA_ACTION_FATAL) {
     p.type = ARTIS_TYPE_KPKT;  // park the packet; the run is reported as failed
     return;
@@ -386,6 +386,21 @@ ARTIS_DEV void ma_event(const Ctx &c, Pkt &p, const int action, const int selidx
     p.cold->trueemissionvelocity = (float)(vec_len(ep) / em_time);
     p.cold->trueem_time = em_time;
   }
+}
+ARTIS_DEV_NOINLINE void ma_event_ool(const Ctx &c, EvState *s, const int action, const int selidx) { ma_event_body(c, s->p, action, selidx, s->rng, s->tl); }
+ARTIS_DEV void ma_event(const Ctx &c, Pkt &p, const int action, const int selidx, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  ma_event_ool(c, &s, action, selidx);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  ma_event_body(c, p, action, selidx, rng, tl);
+#endif
 }
 ARTIS_DEV void do_macroatom(const Ctx &c, Pkt &p, Rng &rng, Tally &tl) {
   int selidx;

@@ -326,14 +326,9 @@ ARTIS_DEV int bf_stop_index(const Ctx &c, const double nu) {
 }
 // One term of the sum for a continuum with nu >= nu_edge: returns kappa_bf_contr at frequency nu (0 if skipped);
 // *gcontr receives sigma_bf*probability*corrfactor (the gamma_contr of rpkt.cc:1158-1166) or 0.
-ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr,
-                               int *ground_slot = nullptr) {
-  // every load is issued before the first use, and sigma_bf is interpolated even for a term that ends up skipped: the
-  // dependent nnlevel -> branch -> table row -> cross-section chain was the latency of the whole sum
-  const double *cell = c.tb.bf_cell + 2 * ((size_t)tc * c.st.nbfcontinua + i);
-  const double nnlevel = cell[0];
-  const double depratio = cell[1];
-  const ContRec r = c.cont_rec[i];
+// the arithmetic of one term, given its per-cell pair (level population, departure ratio) and its static record
+ARTIS_DEV double kappa_bf_term_core(const Ctx &c, const double nnlevel, const double depratio, const ContRec &r, const double nu,
+                                    const double expfac, double *gcontr) {
   const double sigma_bf = phixs_fromtable(c, r.tablerow, r.nu_edge, nu, r.inv_nu_edge);
   const double nu_max_phixs = r.nu_edge * c.st.last_phixs_nuovernuedge;
   // nnlevel < 0: element absent / unimportant ion (rpkt.cc:1101-1104); otherwise rpkt.cc:1128
@@ -342,8 +337,18 @@ ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const do
   double corrfactor = 1 - stimfactor;
   if (corrfactor < 0) corrfactor = 0.;
   *gcontr = counts ? sigma_bf * r.probability * corrfactor : 0.;
-  if (ground_slot != nullptr) *ground_slot = r.ground_slot;
   return counts ? nnlevel * sigma_bf * r.probability * corrfactor : 0.;
+}
+ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr,
+                               int *ground_slot = nullptr) {
+  // every load is issued before the first use, and sigma_bf is interpolated even for a term that ends up skipped: the
+  // dependent nnlevel -> branch -> table row -> cross-section chain was the latency of the whole sum
+  const double *cell = c.tb.bf_cell + 2 * ((size_t)tc * c.st.nbfcontinua + i);
+  const double nnlevel = cell[0];
+  const double depratio = cell[1];
+  const ContRec r = c.cont_rec[i];
+  if (ground_slot != nullptr) *ground_slot = r.ground_slot;
+  return kappa_bf_term_core(c, nnlevel, depratio, r, nu, expfac, gcontr);
 }
 // ground-continuum slot that term i feeds (rpkt.cc:1158), or -1
 ARTIS_DEV int kappa_bf_ground_slot(const Ctx &c, const int i) { return c.cont_rec[i].ground_slot; }

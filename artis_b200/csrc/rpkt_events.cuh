@@ -117,7 +117,7 @@ ARTIS_DEV void set_pol_dir(Pkt &p) {
   p.cold->pol_dir[1] = pol_dir[1];
   p.cold->pol_dir[2] = pol_dir[2];
 }
-ARTIS_DEV void emitt_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
+ARTIS_DEV void emitt_rpkt_body(const Ctx &c, Pkt &p, Rng &rng) {
   p.type = ARTIS_TYPE_RPKT;
   p.last_cross = ARTIS_CROSS_NONE;
   double dir_cmf[3];
@@ -132,6 +132,19 @@ ARTIS_DEV void emitt_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
   p.cold->stokes[1] = 0.;
   p.cold->stokes[2] = 0.;
   set_pol_dir(p);
+}
+ARTIS_DEV_NOINLINE void emitt_rpkt_ool(const Ctx &c, EvState *s) { emitt_rpkt_body(c, s->p, s->rng); }
+ARTIS_DEV void emitt_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  emitt_rpkt_ool(c, &s);
+  p = s.p;
+  rng = s.rng;
+#else
+  emitt_rpkt_body(c, p, rng);
+#endif
 }
 
 // ---- vpkt.cc:898-1069 rot_angle / meridian / lorentz / frame_transform ----------------------------------------------
@@ -229,7 +242,7 @@ ARTIS_DEV void frame_transform(const double *n_rf, double *Q, double *U, const d
 }
 
 // ---- polarization.cc:6-140 escat_rpkt ----------------------------------------------------------------------------------
-ARTIS_DEV void escat_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
+ARTIS_DEV void escat_rpkt_body(const Ctx &c, Pkt &p, Rng &rng) {
   p.type = ARTIS_TYPE_RPKT;
   p.last_cross = ARTIS_CROSS_NONE;
   double vel_vec[3];
@@ -301,13 +314,26 @@ ARTIS_DEV void escat_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
   p.nu_rf = p.nu_cmf / dopplerfactor;
   p.e_rf = p.e_cmf / dopplerfactor;
 }
+ARTIS_DEV_NOINLINE void escat_rpkt_ool(const Ctx &c, EvState *s) { escat_rpkt_body(c, s->p, s->rng); }
+ARTIS_DEV void escat_rpkt(const Ctx &c, Pkt &p, Rng &rng) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  escat_rpkt_ool(c, &s);
+  p = s.p;
+  rng = s.rng;
+#else
+  escat_rpkt_body(c, p, rng);
+#endif
+}
 
 // ---- rpkt.cc:330-447 rpkt_event_continuum --------------------------------------------------------------------------
 }  // namespace artis
 #include "vpkt.cuh"
 namespace artis {
 
-ARTIS_DEV void rpkt_event_continuum(const Ctx &c, Pkt &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
+ARTIS_DEV void rpkt_event_continuum_body(const Ctx &c, Pkt &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
   const double nu = p.nu_cmf;
   const double dopplerfactor = doppler_packet(c, p);
   const double kappa_cont = k.total * dopplerfactor;
@@ -395,6 +421,21 @@ ARTIS_DEV void rpkt_event_continuum(const Ctx &c, Pkt &p, const KappaCache &k, c
   } else {
     fatal(c, 103);
   }
+}
+ARTIS_DEV_NOINLINE void rpkt_event_continuum_ool(const Ctx &c, EvState *s, const KappaCache &k, const int mgi) { rpkt_event_continuum_body(c, s->p, k, mgi, s->rng, s->tl); }
+ARTIS_DEV void rpkt_event_continuum(const Ctx &c, Pkt &p, const KappaCache &k, const int mgi, Rng &rng, Tally &tl) {
+#if ARTIS_EVENT_OOL
+  EvState s;
+  s.p = p;
+  s.rng = rng;
+  s.tl = tl;
+  rpkt_event_continuum_ool(c, &s, k, mgi);
+  p = s.p;
+  rng = s.rng;
+  tl = s.tl;
+#else
+  rpkt_event_continuum_body(c, p, k, mgi, rng, tl);
+#endif
 }
 
 // rpkt.cc:449-489

@@ -352,70 +352,161 @@ __device__ __forceinline__ bool idle_poll(const artis::Ctx &c, const PersistView
   return false;
 }
 
-// Warp-cooperative continuum opacity (K2): every lane that is about to need kappa_cont for its own packet and misses its
-// cache ("owner") gets its bound-free sum evaluated by all 32 lanes, a tile of 32 consecutive continua at a time --
-// coalesced reads of the per-cell table rows, no dependence between tiles, and the step's latency no longer grows with
-// the number of continua below the packet's frequency (up to all 3204 for a UV packet, on one lane before). The result
-// is left in the owner's cache exactly as calculate_kappa_rpkt_cont would leave it, so the unchanged get_event that
-// follows finds a hit. Summation order = rpkt.cuh BF_TILE trees, the same as the host restatement.
+// ---- warp-cooperative continuum opacity with staged tiles (K2) ---------------------------------------------------------
+// Every lane of a thin-cell r-packet warp that is about to need kappa_cont for its own packet and misses its cache
+// ("owner") gets its bound-free sum evaluated by all 32 lanes, a tile of 32 consecutive continua at a time. The result is
+// left in the owner's cache exactly as calculate_kappa_rpkt_cont would leave it, so the unchanged get_event that follows
+// finds a hit. Summation order = rpkt.cuh BF_TILE trees (tile = 32 consecutive terms reduced as a binary tree, tile sums
+// added in order), the same as the per-lane loop and the host build: identical bits.
+//
+// What a term reads: the cell's (level population, departure ratio) pair -- 16 bytes of the row bf_cell[cell][.] -- its
+// static 32-byte ContRec, and two neighbouring floats of its cross-section table. The first two are CONTIGUOUS over the
+// terms of one sum (rows indexed by continuum), ~900 terms = 43 KB per evaluation: they are brought into shared memory by
+// the TMA engine (cp.async.bulk, one 1-D bulk copy per array and chunk, completion on an mbarrier), two chunks ahead of the
+// arithmetic and across the boundary between one owner's sum and the next, so that the lanes never wait for them and
+// issue no load instructions for them; the dependent table gather is the only global load left in the loop. In round 1
+// the same sum issued 3-4 dependent L2 loads per term from two warps per scheduler and was 61 % of the timestep.
 static_assert(artis::BF_TILE == 32, "one continuum per lane");
-constexpr int COOP_UNROLL = 4;
-#ifndef ARTIS_COOP_MAX_OWNERS
-#define ARTIS_COOP_MAX_OWNERS 8
+#ifndef ARTIS_KAPPA_CHUNK_TILES
+#define ARTIS_KAPPA_CHUNK_TILES 4
 #endif
-constexpr int COOP_MAX_OWNERS = ARTIS_COOP_MAX_OWNERS;
+constexpr int KCH_TILES = ARTIS_KAPPA_CHUNK_TILES;          // tiles per staged chunk
+constexpr int KCH = KCH_TILES * artis::BF_TILE;            // terms per chunk
+constexpr int KSTAGES = 2;
+struct alignas(16) KappaStage {
+  double2 cell[KSTAGES][KCH];          // bf_cell pairs
+  artis::ContRec rec[KSTAGES][KCH];    // static records
+  unsigned long long bar[KSTAGES];     // one mbarrier per stage (this warp's)
+};
+constexpr size_t KAPPA_SMEM_PER_BLOCK = 4 * sizeof(KappaStage);  // 128-thread blocks
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, const unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, const unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, const unsigned bytes, unsigned long long *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, const unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (ok == 0u);
+}
+// called once per warp before the first evaluation
+__device__ __forceinline__ void kappa_stage_init(KappaStage *ks) {
+  if ((threadIdx.x & 31) == 0) {
+    for (int s2 = 0; s2 < KSTAGES; s2++) mbar_init(&ks->bar[s2], 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncwarp();
+}
+// `nchunk`: chunks this warp has staged since the kernel began (stage = nchunk % KSTAGES, mbarrier parity from it)
 __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool wants, const int mgi, const double nu_cmf,
-                                                artis::KappaCache &k, artis::Tally &tl) {
+                                                artis::KappaCache &k, artis::Tally &tl, KappaStage *ks, unsigned &nchunk) {
   using namespace artis;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const bool need = wants && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, mgi, nu_cmf);
-  unsigned owners = __ballot_sync(full, need);
-  // With many owners the per-lane evaluation inside get_event has the better throughput (32 sums advance at once);
-  // the cooperative form is for sparsely filled warps, where it cuts the latency of the step (the tail of a timestep).
-  if (owners == 0u || __popc(owners) > COOP_MAX_OWNERS) return;
-  double sigma = 0., kappa_ff = 0., kappa_bf = 0.;
+  const unsigned owners = __ballot_sync(full, need);
+  if (owners == 0u) return;
+  // every owner prepares its own sum in parallel: the cheap terms, the range of continua, exp(-h nu / k T_e)
+  double sigma = 0., kappa_ff = 0., kappa_bf = 0., my_expfac = 0.;
+  int my_ilo = 0, my_i0 = 0, my_tc = 0;
   if (need) {
     tl.kappa_evals++;
     sigma = SIGMA_T * c.cs.nne[mgi];
     kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
     const int ng = c.st.nbfcontinua_ground;
     for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
+    my_tc = tabcell(c, mgi);
+    my_expfac = exp(-HOVERKB * nu_cmf / (double)c.cs.Te[mgi]);
+    my_i0 = bf_stop_index(c, nu_cmf);
+    my_ilo = bf_start_index(c, nu_cmf, my_i0);
+    tl.bf_evaluated += my_i0 - my_ilo;
   }
-  while (owners != 0u) {
-    const int owner = __ffs(owners) - 1;
-    owners &= owners - 1u;
-    const double nu = __shfl_sync(full, nu_cmf, owner);
-    const int omgi = __shfl_sync(full, mgi, owner);
-    const int tc = tabcell(c, omgi);
-    const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[omgi]);
-    const int i0 = bf_stop_index(c, nu);
-    const int ilo = bf_start_index(c, nu, i0);
-    double sum = 0.;
-    for (int base = ilo; base < i0; base += BF_TILE * COOP_UNROLL) {
-      // COOP_UNROLL tiles in flight per lane: their loads overlap, their trees interleave; tile sums are still added
-      // in tile order
-      double t[COOP_UNROLL], gcontr[COOP_UNROLL];
-      int slot[COOP_UNROLL];
+  const int nbf = c.st.nbfcontinua;
+  // the issue cursor runs KSTAGES chunks ahead of the arithmetic, across owners
+  unsigned iss_rest = owners;
+  int iss_j = 0, iss_nch = 0, iss_ilo = 0, iss_i0 = 0, iss_tc = 0;
+  unsigned iss_count = nchunk;
+  auto iss_next_owner = [&]() {  // warp-uniform
+    iss_nch = 0;
+    while (iss_rest != 0u && iss_nch == 0) {
+      const int o = __ffs(iss_rest) - 1;
+      iss_rest &= iss_rest - 1u;
+      iss_ilo = __shfl_sync(full, my_ilo, o);
+      iss_i0 = __shfl_sync(full, my_i0, o);
+      iss_tc = __shfl_sync(full, my_tc, o);
+      iss_j = 0;
+      iss_nch = (iss_i0 - iss_ilo + KCH - 1) / KCH;
+    }
+  };
+  auto issue_one = [&]() {  // warp-uniform; lane 0 talks to the TMA engine
+    if (iss_nch == 0) return;
+    if (lane == 0) {
+      const int st = (int)(iss_count % KSTAGES);
+      const int base = iss_ilo + iss_j * KCH;
+      const int n = (iss_i0 - base) < KCH ? (iss_i0 - base) : KCH;
+      // the lanes have finished reading this stage (__syncwarp before the call): order their reads before the engine's writes
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      mbar_expect_tx(&ks->bar[st], (unsigned)n * 48u);
+      bulk_g2s(&ks->cell[st][0], c.tb.bf_cell + 2 * ((size_t)iss_tc * nbf + base), (unsigned)n * 16u, &ks->bar[st]);
+      bulk_g2s(&ks->rec[st][0], c.cont_rec + base, (unsigned)n * 32u, &ks->bar[st]);
+    }
+    iss_count++;
+    iss_j++;
+    if (iss_j == iss_nch) iss_next_owner();
+  };
+  iss_next_owner();
 #pragma unroll
-      for (int u = 0; u < COOP_UNROLL; u++) {
-        const int i = base + u * BF_TILE + lane;
+  for (int s2 = 0; s2 < KSTAGES; s2++) issue_one();
+  unsigned rest = owners;
+  while (rest != 0u) {
+    const int owner = __ffs(rest) - 1;
+    rest &= rest - 1u;
+    const double nu = __shfl_sync(full, nu_cmf, owner);
+    const double expfac = __shfl_sync(full, my_expfac, owner);
+    const int ilo = __shfl_sync(full, my_ilo, owner);
+    const int i0 = __shfl_sync(full, my_i0, owner);
+    double sum = 0.;
+    for (int base = ilo; base < i0; base += KCH) {
+      const int st = (int)(nchunk % KSTAGES);
+      mbar_wait(&ks->bar[st], (nchunk / KSTAGES) & 1u);
+      nchunk++;
+      double t[KCH_TILES], gcontr[KCH_TILES];
+      int slot[KCH_TILES];
+#pragma unroll
+      for (int u = 0; u < KCH_TILES; u++) {
+        const int q = u * BF_TILE + lane;
         t[u] = 0.;
         gcontr[u] = 0.;
         slot[u] = -1;
-        if (i < i0) {
-          int sl;
-          t[u] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr[u], &sl);
-          if (gcontr[u] != 0.) slot[u] = sl;
+        if (base + q < i0) {
+          const double2 cellv = ks->cell[st][q];
+          const ContRec r = ks->rec[st][q];
+          t[u] = kappa_bf_term_core(c, cellv.x, cellv.y, r, nu, expfac, &gcontr[u]);
+          if (gcontr[u] != 0.) slot[u] = r.ground_slot;
         }
       }
+      __syncwarp(full);  // every lane has its operands out of the stage: it can be refilled
+      issue_one();
 #pragma unroll
       for (int off = 1; off < BF_TILE; off <<= 1) {  // adjacent pairs first: the tree of rpkt.cuh PairTree
 #pragma unroll
-        for (int u = 0; u < COOP_UNROLL; u++) t[u] += __shfl_down_sync(full, t[u], off);
+        for (int u = 0; u < KCH_TILES; u++) t[u] += __shfl_down_sync(full, t[u], off);
       }
 #pragma unroll
-      for (int u = 0; u < COOP_UNROLL; u++) {
+      for (int u = 0; u < KCH_TILES; u++) {
         sum += t[u];  // lane 0 holds each tile sum in tree order; only lane 0's running sum is used
         unsigned g = __ballot_sync(full, slot[u] >= 0);
         while (g != 0u) {  // ground-continuum contributions, in index order like the serial loop
@@ -428,10 +519,7 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
       }
     }
     sum = __shfl_sync(full, sum, 0);
-    if (lane == owner) {
-      kappa_bf = sum;
-      tl.bf_evaluated += i0 - ilo;
-    }
+    if (lane == owner) kappa_bf = sum;
   }
   if (need) kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ff, tl);
 }
@@ -487,6 +575,10 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
   int last_active = -1;  // active-packet count at the last idle poll: the hang guard looks for progress, not for work
   int refill_skip = 0;   // iterations left during which a partly busy warp does not look at its (just found empty) ring
   stats_block_begin();
+  extern __shared__ __align__(16) unsigned char kappa_smem[];
+  KappaStage *const ks = reinterpret_cast<KappaStage *>(kappa_smem) + (threadIdx.x >> 5);
+  unsigned nchunk = 0u;
+  if (HAS_THIN) kappa_stage_init(ks);
   if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
   long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
   // where the warp's cycles go (lane k keeps kind k's event cycles; lane 0 the scheduler's own)
@@ -559,7 +651,7 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
         proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
       }
       const bool wants = proceed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
-      coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl);
+      coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl, ks, nchunk);
       if (proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
       if (k.defer_bfest) coop_bfest_flush(c, k, tl);  // warp-uniform: the flag is an option of the build mode
       if (have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
@@ -870,18 +962,23 @@ bool be_select_device(int device, std::string *why) {
   // The two kernels of the pair must be able to share an SM: the same L1 / shared-memory split for both (an SM cannot
   // hold blocks of kernels with different carve-outs -- the second kernel would wait for the first to drain, which never
   // happens here because each waits for the other's packets).
-  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_ALL>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1), "carve-out");
-  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_HEAVY>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1), "carve-out");
-  note(cudaFuncSetAttribute(k_transport_majump, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1), "carve-out");
+  constexpr int CARVEOUT_PERCENT = 50;  // of the 228 KB: room for the opacity stages of three big blocks, the rest stays L1
+  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_ALL>, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
+  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_HEAVY>, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
+  note(cudaFuncSetAttribute(k_transport_majump, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
+  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KAPPA_SMEM_PER_BLOCK), "dynamic smem");
+  note(cudaFuncSetAttribute(k_transport_persistent<ROLES_HEAVY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KAPPA_SMEM_PER_BLOCK), "dynamic smem");
   {
     cudaFuncAttributes aa{}, ah{}, aj{};
     int regs_per_sm = 65536;
     cudaDeviceGetAttribute(&regs_per_sm, cudaDevAttrMaxRegistersPerMultiprocessor, device);
     auto block_regs = [](const cudaFuncAttributes &a) { return ((a.numRegs + 7) / 8) * 8 * 128; };
+    // blocks of the big kernel that the shared-memory carve-out holds (opacity stages + 1 KB the system keeps per block)
+    const int smem_blocks = (int)((size_t)CARVEOUT_PERCENT * 228 * 1024 / 100 / (KAPPA_SMEM_PER_BLOCK + 1024));
     g_scheduler_kernels = 1;
     if (cudaFuncGetAttributes(&aa, k_transport_persistent<ROLES_ALL>) == cudaSuccess && aa.numRegs > 0) {
       g_blocks_all = regs_per_sm / block_regs(aa);
-      if (g_blocks_all > 4) g_blocks_all = 4;
+      if (g_blocks_all > smem_blocks) g_blocks_all = smem_blocks;
       if (g_blocks_all < 1) g_blocks_all = 1;
     }
     if (cudaFuncGetAttributes(&ah, k_transport_persistent<ROLES_HEAVY>) == cudaSuccess &&
@@ -890,7 +987,7 @@ bool be_select_device(int device, std::string *why) {
       int hb = ARTIS_HEAVY_BLOCKS;
       if (hb <= 0) {  // as many blocks of the big kernel as leave room for at least two blocks (8 warps) of jumps
         hb = (regs_per_sm - 2 * jump) / heavy;
-        if (hb > 4) hb = 4;
+        if (hb > smem_blocks) hb = smem_blocks;
       }
       if (hb < 1) hb = 1;
       int jb = (regs_per_sm - hb * heavy) / jump;
@@ -900,7 +997,7 @@ bool be_select_device(int device, std::string *why) {
       if (const char *geo = getenv("ARTIS_GEOMETRY")) {
         int a = 0, b2 = 0;
         if (sscanf(geo, "%d,%d", &a, &b2) == 2 && a >= 1 && b2 >= 1 && a * heavy + b2 * jump <= regs_per_sm &&
-            (a + b2) * 128 <= prop.maxThreadsPerMultiProcessor) {
+            (a + b2) * 128 <= prop.maxThreadsPerMultiProcessor && a <= smem_blocks) {
           hb = a;
           jb = b2;
         }
@@ -1032,8 +1129,8 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
       w.n_active = reinterpret_cast<int *>(scratch + 2 * NRING * RMS);
       w.t_start = scratch + (2 * NRING + 1) * RMS;
       w.n_initial = 0;
-      k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, 0, g_stream>>>(hot, cold, w, maxev, timeout);
-      k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, 0, g_stream>>>(hot, cold, w, maxev, timeout);
+      k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, w, maxev, timeout);
+      k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, w, maxev, timeout);
       if (g_blocks_jump > 0) k_transport_majump<<<g_sms * g_blocks_jump, 128, 0, g_stream>>>(hot, w, maxev, timeout);
       note(cudaStreamSynchronize(g_stream), "warm-up sync");
       cudaFree(scratch);
@@ -1041,14 +1138,14 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
     g_persistent_warmed = true;
   }
   if (g_scheduler_kernels != 2) {
-    k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, 0, g_stream>>>(hot, cold, pv, maxev, timeout);
+    k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, pv, maxev, timeout);
     return true;
   }
   // the big kernel goes first, the jump kernel fills the rest of every SM; the side stream waits for what is queued on the
   // main stream (ring setup) and the main stream waits for the side kernel
   note(cudaEventRecord(g_ev_fork, g_stream), "event record");
   note(cudaStreamWaitEvent(g_stream2, g_ev_fork, 0), "stream wait");
-  k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, 0, g_stream>>>(hot, cold, pv, maxev, timeout);
+  k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, pv, maxev, timeout);
   k_transport_majump<<<g_sms * g_blocks_jump, 128, 0, g_stream2>>>(hot, pv, maxev, timeout);
   note(cudaEventRecord(g_ev_join, g_stream2), "event record");
   note(cudaStreamWaitEvent(g_stream, g_ev_join, 0), "stream wait");

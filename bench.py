@@ -270,6 +270,8 @@ def main():
     T.upload_cellstate(cs)
     if a.max_events:
         T.set_tuning(max_events_per_pass=a.max_events)
+    if os.environ.get("ARTIS_HANG_S"):  # measurement runs of experimental builds: give up a stuck timestep quickly
+        T.set_tuning(block_threads=-1000 - int(os.environ["ARTIS_HANG_S"]))
     if a.scheduler_kernels or os.environ.get("ARTIS_BENCH_SCHED"):
         T.set_tuning(block_threads=-3 if int(a.scheduler_kernels or os.environ["ARTIS_BENCH_SCHED"]) == 1 else -4)
     precompute_ms = T.last_timings()[3]

@@ -51,7 +51,7 @@ def main():
         print()
         sys.stdout.flush()
         subprocess.run([sys.executable, os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_lines.py"), sass, dis,
-                        kernel, "25"])
+                        kernel, "45"])
 
 
 if __name__ == "__main__":

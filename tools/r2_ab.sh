@@ -19,9 +19,12 @@ except Exception as e:
     print("$name FAILED", e, open("$O/bench_$name.err").read()[-500:])
 PY
 }
+export ARTIS_HANG_S=5
 run default ARTIS_X=0
-run single ARTIS_X=0 ARTIS_BENCH_SCHED=1
-run g1_5 ARTIS_GEOMETRY=1,5
-run g2_2 ARTIS_GEOMETRY=2,2
-run g1_3 ARTIS_GEOMETRY=1,3
-run g2_1 ARTIS_GEOMETRY=2,1
+run single ARTIS_BENCH_SCHED=1
+for v in $VARIANTS; do
+  run $v ARTIS_GPU_LIB=$PWD/variants/libartis_gpu_$v.so
+done
+for g in $GEOMETRIES; do
+  run g$g ARTIS_GEOMETRY=$g
+done
