@@ -72,8 +72,12 @@ ARTIS_DEV int kind_of(const Ctx &c, const int type, const int where) {
   }
 }
 ARTIS_DEV int kind_of(const Ctx &c, const Pkt &p) { return kind_of(c, p.type, p.where); }
-// One ring of packet indices per kind (transport.cu).
-constexpr int NRING = NKIND;
+// One ring of packet indices per kind (transport.cu), plus two scheduler-internal ones for the thin-cell r-packet step, whose
+// continuum-opacity sum runs in the light kernel: KIND_KAPPA = a step that has begun and waits for its opacity (consumed
+// by the opacity role), KIND_THIN_RESUME = its opacity has been delivered (consumed by the thin role, before new steps).
+constexpr int KIND_KAPPA = NKIND;
+constexpr int KIND_THIN_RESUME = NKIND + 1;
+constexpr int NRING = NKIND + 2;
 // Ring heads, tails and the active-packet count take every warp's atomics for the whole step: one 128-byte line each, so
 // that they sit in different L2 slices instead of queueing behind one another (words of 8 bytes).
 #ifndef ARTIS_RING_STRIDE

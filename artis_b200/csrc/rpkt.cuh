@@ -339,6 +339,34 @@ ARTIS_DEV double kappa_bf_term_core(const Ctx &c, const double nnlevel, const do
   *gcontr = counts ? sigma_bf * r.probability * corrfactor : 0.;
   return counts ? nnlevel * sigma_bf * r.probability * corrfactor : 0.;
 }
+// The same term as straight-line code for the cooperative sum (transport.cu), whose loop should neither branch nor outgrow
+// the instruction buffers: both quotients by the two-FMA form (exact: ContRec), the table index clamped instead of
+// tested, selects instead of branches. The clamped form equals atomic.cc:87-137 wherever 0 <= i < NPHIXSPOINTS - 1; a lane
+// outside that range or without an exact reciprocal (never, for the data sets seen so far) takes kappa_bf_term_core.
+ARTIS_DEV double kappa_bf_term_fast(const Ctx &c, const double nnlevel, const double depratio, const ContRec &r, const double nu,
+                                    const double expfac, double *gcontr) {
+  const double inv = r.inv_nu_edge, invinc = c.inv_nphixsnuincrement;
+  const double q = nu * inv;
+  const double x = fma(fma(-r.nu_edge, q, nu), inv, q);  // nu / nu_edge, correctly rounded
+  const double y = x - 1.0;
+  const double q2 = y * invinc;
+  const double ireal = fma(fma(-c.st.nphixsnuincrement, q2, y), invinc, q2);  // (nu / nu_edge - 1) / NPHIXSNUINCREMENT
+  const int i = (int)floor(ireal);
+  const int npts = c.st.nphixspoints;
+  const bool fast = (inv != 0.) && (invinc != 0.) && (i >= 0) && (i < npts - 1);
+  if (!fast) return kappa_bf_term_core(c, nnlevel, depratio, r, nu, expfac, gcontr);
+  const float *xs = c.st.phixs_tables + (size_t)r.tablerow * npts;
+  const double a = xs[i];
+  const double b = xs[i + 1];
+  const double factor_b = ireal - i;
+  const double sigma_bf = (double)(float)(((1. - factor_b) * a) + (factor_b * b));
+  const double nu_max_phixs = r.nu_edge * c.st.last_phixs_nuovernuedge;
+  const bool counts = (nnlevel > 0.) && (nu <= nu_max_phixs);
+  double corrfactor = 1 - depratio * expfac;
+  if (corrfactor < 0) corrfactor = 0.;
+  *gcontr = counts ? sigma_bf * r.probability * corrfactor : 0.;
+  return counts ? nnlevel * sigma_bf * r.probability * corrfactor : 0.;
+}
 ARTIS_DEV double kappa_bf_term(const Ctx &c, const int tc, const int i, const double nu, const double expfac, double *gcontr,
                                int *ground_slot = nullptr) {
   // every load is issued before the first use, and sigma_bf is interpolated even for a term that ends up skipped: the

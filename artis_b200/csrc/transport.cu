@@ -192,10 +192,13 @@ __global__ void __launch_bounds__(artis::ESC_CHUNK) k_escaped_scatter(const arti
 // step ends when the longest single packet history ends, and a warp never executes two kinds' code in one iteration.
 //
 // Two kernels run side by side and exchange packets through the rings:
-//   k_transport_majump      the macro-atom jump role alone: 32 bytes of packet state, one rate row and one prefix-sum search
-//                           per jump -- a small register budget, hence many resident warps to hide the L2 round trips
-//   k_transport_persistent  every other role (r-packet steps, gamma packets, pellets, macro-atom events, k-packets) on the
-//                           whole hot line; big register budget, few warps
+//   k_transport_light       the two roles that are chains of table reads on almost no packet state: macro-atom jumps (32
+//                           bytes of the packet, one rate row and one prefix-sum search per jump) and the continuum-opacity
+//                           sums of thin-cell r-packet steps (cell and frequency; ~900 bound-free terms per sum, staged by
+//                           TMA) -- a small register budget and little code, hence many resident warps to hide the L2
+//                           round trips and the instruction fetches
+//   k_transport_persistent  every other role (r-packet steps around their opacity sum, gamma packets, pellets, macro-atom
+//                           events, k-packets) on the whole hot line; big register budget, few warps
 // (k_transport_persistent<ROLES_ALL> also serves the jump role itself: the single-kernel variant, kept for comparisons.)
 //
 // Ring protocol (capacity >= number of packets, so at most `cap` entries are ever outstanding): a slot holds -1 when
@@ -232,6 +235,9 @@ struct PersistView {
   unsigned long long *t_start;  // globaltimer at launch
   int cap;
   unsigned long long *pend;  // [cap] macro-atom action a jump has drawn and left for the event role: (action + 1) << 32 | selidx
+  double *kcache;            // [cap][kstride] continuum opacity delivered for a packet: KappaCache scalars + gamma_contr
+  double *stepstate;         // [cap][3] RpktStepState of a step that waits for its opacity
+  int kstride;
 };
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
@@ -260,8 +266,25 @@ __device__ __forceinline__ void pkt_store_cg(PktHot *dst, const artis::Pkt &p, c
 #pragma unroll
   for (int i = 0; i < (int)(sizeof(PktHot) / 16); i++) __stcg(d + i, s[i]);
 }
+// opacity hand-over record: [0] nu, [1] total, [2] es, [3] ff, [4] bf, [5] ffheating, [6] mgi, [8 + g] gamma_contr[g]
+__device__ __forceinline__ void kcache_load(artis::KappaCache &k, const double *kc, const int ng) {
+  k.nu = __ldcg(kc + 0);
+  k.total = __ldcg(kc + 1);
+  k.es = __ldcg(kc + 2);
+  k.ff = __ldcg(kc + 3);
+  k.bf = __ldcg(kc + 4);
+  k.ffheating = __ldcg(kc + 5);
+  k.mgi = (int)__ldcg(kc + 6);
+  k.valid = true;
+  for (int g = 0; g < ng; g++) k.gamma_contr[g] = __ldcg(kc + 8 + g);
+}
 // ring primitives (protocol in the comment above)
 constexpr int RMS = artis::RING_META_STRIDE;
+// 1: the two-kernel scheduler hands the opacity sums of the thin-cell steps to the light kernel (KIND_KAPPA role); 0: the
+// thin role's own warp evaluates them between the two halves of the step (measured: profiles/r2_notes.md)
+#ifndef ARTIS_KAPPA_OFFLOAD
+#define ARTIS_KAPPA_OFFLOAD 0
+#endif
 #ifndef ARTIS_REFILL_BACKOFF
 #define ARTIS_REFILL_BACKOFF 10
 #endif
@@ -368,7 +391,7 @@ __device__ __forceinline__ bool idle_poll(const artis::Ctx &c, const PersistView
 // the same sum issued 3-4 dependent L2 loads per term from two warps per scheduler and was 61 % of the timestep.
 static_assert(artis::BF_TILE == 32, "one continuum per lane");
 #ifndef ARTIS_KAPPA_CHUNK_TILES
-#define ARTIS_KAPPA_CHUNK_TILES 4
+#define ARTIS_KAPPA_CHUNK_TILES 2
 #endif
 constexpr int KCH_TILES = ARTIS_KAPPA_CHUNK_TILES;          // tiles per staged chunk
 constexpr int KCH = KCH_TILES * artis::BF_TILE;            // terms per chunk
@@ -379,6 +402,8 @@ struct alignas(16) KappaStage {
   unsigned long long bar[KSTAGES];     // one mbarrier per stage (this warp's)
 };
 constexpr size_t KAPPA_SMEM_PER_BLOCK = 4 * sizeof(KappaStage);  // 128-thread blocks
+constexpr size_t LIGHT_SMEM = ARTIS_KAPPA_OFFLOAD != 0 ? KAPPA_SMEM_PER_BLOCK : 0;  // dynamic shared memory of the pair's kernels
+constexpr size_t HEAVY_SMEM = ARTIS_KAPPA_OFFLOAD != 0 ? 0 : KAPPA_SMEM_PER_BLOCK;
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, const unsigned count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -410,24 +435,21 @@ __device__ __forceinline__ void kappa_stage_init(KappaStage *ks) {
   }
   __syncwarp();
 }
-// `nchunk`: chunks this warp has staged since the kernel began (stage = nchunk % KSTAGES, mbarrier parity from it)
-__device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool wants, const int mgi, const double nu_cmf,
-                                                artis::KappaCache &k, artis::Tally &tl, KappaStage *ks, unsigned &nchunk) {
+// `nchunk`: chunks this warp has staged since the kernel began (stage = nchunk % KSTAGES, mbarrier parity from it).
+// need / nu_cmf / mgi: this lane's request; returns its bound-free sum; gc(slot, v) is called on the owner lane for every
+// ground-continuum contribution, in index order like the serial loop (rpkt.cc:1158-1166).
+template <class GC>
+__device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool need, const int mgi, const double nu_cmf,
+                                                 artis::Tally &tl, KappaStage *ks, unsigned &nchunk, GC gc) {
   using namespace artis;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const bool need = wants && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, mgi, nu_cmf);
   const unsigned owners = __ballot_sync(full, need);
-  if (owners == 0u) return;
-  // every owner prepares its own sum in parallel: the cheap terms, the range of continua, exp(-h nu / k T_e)
-  double sigma = 0., kappa_ff = 0., kappa_bf = 0., my_expfac = 0.;
+  if (owners == 0u) return 0.;
+  // every owner prepares its own sum in parallel: the range of continua, exp(-h nu / k T_e)
+  double kappa_bf = 0., my_expfac = 0.;
   int my_ilo = 0, my_i0 = 0, my_tc = 0;
   if (need) {
-    tl.kappa_evals++;
-    sigma = SIGMA_T * c.cs.nne[mgi];
-    kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
-    const int ng = c.st.nbfcontinua_ground;
-    for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
     my_tc = tabcell(c, mgi);
     my_expfac = exp(-HOVERKB * nu_cmf / (double)c.cs.Te[mgi]);
     my_i0 = bf_stop_index(c, nu_cmf);
@@ -494,7 +516,7 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
         if (base + q < i0) {
           const double2 cellv = ks->cell[st][q];
           const ContRec r = ks->rec[st][q];
-          t[u] = kappa_bf_term_core(c, cellv.x, cellv.y, r, nu, expfac, &gcontr[u]);
+          t[u] = kappa_bf_term_fast(c, cellv.x, cellv.y, r, nu, expfac, &gcontr[u]);
           if (gcontr[u] != 0.) slot[u] = r.ground_slot;
         }
       }
@@ -514,13 +536,29 @@ __device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool 
           g &= g - 1u;
           const double v = __shfl_sync(full, gcontr[u], src);
           const int sl = __shfl_sync(full, slot[u], src);
-          if (lane == owner) k.gamma_contr[sl] += v;
+          if (lane == owner) gc(sl, v);
         }
       }
     }
     sum = __shfl_sync(full, sum, 0);
     if (lane == owner) kappa_bf = sum;
   }
+  return kappa_bf;
+}
+// the single-kernel variant: the thin role's own warp evaluates the sums of its lanes and leaves them in their caches
+__device__ __forceinline__ void coop_kappa_warm(const artis::Ctx &c, const bool wants, const int mgi, const double nu_cmf,
+                                                artis::KappaCache &k, artis::Tally &tl, KappaStage *ks, unsigned &nchunk) {
+  using namespace artis;
+  const bool need = wants && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, mgi, nu_cmf);
+  double sigma = 0., kappa_ff = 0.;
+  if (need) {
+    tl.kappa_evals++;
+    sigma = SIGMA_T * c.cs.nne[mgi];
+    kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
+    const int ng = c.st.nbfcontinua_ground;
+    for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
+  }
+  const double kappa_bf = coop_kappa_sum(c, need, mgi, nu_cmf, tl, ks, nchunk, [&](const int sl, const double v) { k.gamma_contr[sl] += v; });
   if (need) kappa_store(c, k, mgi, nu_cmf, sigma, kappa_ff, kappa_bf, kappa_ff, tl);
 }
 
@@ -560,11 +598,12 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
   const unsigned lt_mask = (1u << lane) - 1u;
   constexpr bool HAS_THIN = (ROLES & (1u << KIND_RPKT_THIN)) != 0;
   constexpr bool HAS_JUMP = (ROLES & (1u << KIND_MAJUMP)) != 0;
+  constexpr bool KAPPA_HERE = HAS_JUMP || ARTIS_KAPPA_OFFLOAD == 0;  // this kernel's thin role evaluates its own opacity sums
   Tally tl = {};
   KappaCache k;
   k.valid = false;
   k.defer_bfest = HAS_THIN && ARTIS_OPT_DETAILED_BF(c);
-  bool have = false;
+  bool have = false, resumed = false;
   int idx = 0, role = 0;
   long long events = 0;
   Pkt p;
@@ -578,7 +617,7 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
   extern __shared__ __align__(16) unsigned char kappa_smem[];
   KappaStage *const ks = reinterpret_cast<KappaStage *>(kappa_smem) + (threadIdx.x >> 5);
   unsigned nchunk = 0u;
-  if (HAS_THIN) kappa_stage_init(ks);
+  if (KAPPA_HERE) kappa_stage_init(ks);
   if (blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long *>(pv.t_start) = global_ns();
   long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
   // where the warp's cycles go (lane k keeps kind k's event cycles; lane 0 the scheduler's own)
@@ -592,7 +631,12 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
     } else if (need != 0u) {
       if (need == full) {  // the whole warp is out of work: choose the kind with the longest backlog
         long long backlog = 0;
-        if (lane < NRING && ((ROLES >> lane) & 1u) != 0) backlog = ring_backlog(pv, lane);
+        if (lane < NKIND && ((ROLES >> lane) & 1u) != 0) backlog = ring_backlog(pv, lane);
+        if (HAS_THIN && !KAPPA_HERE) {  // the thin role drains two rings
+          long long extra = 0;
+          if (lane == KIND_RPKT_THIN) extra = ring_backlog(pv, KIND_THIN_RESUME);
+          backlog += extra;
+        }
         long long best = backlog;
         int best_kind = lane;
 #pragma unroll
@@ -614,18 +658,38 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
         role = best_kind;
         idle_since = 0ull;
       }
-      // refill the idle lanes from the role's ring
+      // refill the idle lanes from the role's ring(s); for the thin role the resumed steps come first
       const int want = __popc(need);
-      int take = 0;
-      unsigned long long base = 0ull;
-      if (lane == 0) take = ring_claim(pv, role, want, &base);
-      take = __shfl_sync(full, take, 0);
-      base = __shfl_sync(full, base, 0);
+      int take_a = 0, take_b = 0;
+      unsigned long long base_a = 0ull, base_b = 0ull;
+      if (lane == 0) {
+        if (HAS_THIN && !KAPPA_HERE && role == KIND_RPKT_THIN) take_a = ring_claim(pv, KIND_THIN_RESUME, want, &base_a);
+        if (take_a < want) take_b = ring_claim(pv, role, want - take_a, &base_b);
+      }
+      take_a = __shfl_sync(full, take_a, 0);
+      take_b = __shfl_sync(full, take_b, 0);
+      base_a = __shfl_sync(full, base_a, 0);
+      base_b = __shfl_sync(full, base_b, 0);
+      const int take = take_a + take_b;
       const int rank = __popc(need & lt_mask);
       if (!have && rank < take) {
-        idx = ring_take(pv, role, base + (unsigned long long)rank);
+        const bool from_resume = rank < take_a;
+        idx = from_resume ? ring_take(pv, KIND_THIN_RESUME, base_a + (unsigned long long)rank)
+                          : ring_take(pv, role, base_b + (unsigned long long)(rank - take_a));
         pkt_load_cg(p, rng, c, hot + idx, cold + idx);
         k.valid = false;
+        resumed = false;
+        if (HAS_THIN && !KAPPA_HERE && from_resume) {
+          kcache_load(k, pv.kcache + (size_t)idx * pv.kstride, c.st.nbfcontinua_ground);
+          const double *ss = pv.stepstate + (size_t)idx * 3;
+          st.tau_next = __ldcg(ss + 0);
+          st.sdist = __ldcg(ss + 1);
+          const long long packed = __double_as_longlong(__ldcg(ss + 2));
+          st.snext = (int)(packed >> 32);
+          st.mgi = (int)(packed & 0xffffffffll);
+          st.mgi_next = rpkt_step_mgi_next(c, p, st);
+          resumed = true;
+        }
         events = 0;
         have = true;
       }
@@ -644,17 +708,33 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
         fill_lanes += __popc(busy);
       }
     }
+    bool parked = false;  // thin lane that has handed its step to the opacity role
     if (HAS_THIN && role == KIND_RPKT_THIN) {  // warp-uniform: the step in two halves around the opacity evaluation
       bool proceed = false;
       if (have) {
-        tl.packet_updates++;
-        proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
+        if (resumed) {
+          proceed = true;
+        } else {
+          tl.packet_updates++;
+          proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
+        }
       }
-      const bool wants = proceed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
-      coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl, ks, nchunk);
-      if (proceed) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
+      const bool wants = proceed && !resumed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
+      if constexpr (KAPPA_HERE) {
+        // the sum is evaluated here, by this warp
+        coop_kappa_warm(c, wants, st.mgi, p.nu_cmf, k, tl, ks, nchunk);
+      } else if (wants) {
+        // two-kernel scheduler: the step waits on the KIND_KAPPA ring while a warp of the light kernel evaluates its sum
+        double *ss = pv.stepstate + (size_t)idx * 3;
+        __stcg(ss + 0, st.tau_next);
+        __stcg(ss + 1, st.sdist);
+        __stcg(ss + 2, __longlong_as_double(((long long)st.snext << 32) | (long long)(unsigned)st.mgi));
+        parked = true;
+      }
+      if (proceed && !parked) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
       if (k.defer_bfest) coop_bfest_flush(c, k, tl);  // warp-uniform: the flag is an option of the build mode
-      if (have && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
+      resumed = false;
+      if (have && !parked && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
     } else if (have) {
       switch (role) {  // warp-uniform
         case KIND_MAK:
@@ -684,7 +764,13 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
     if (ARTIS_OPT_VPKT(c) && have) vpkt_flush_request(c, p, k, tl);  // the one call site of the virtual-packet ray trace
     bool done = false;
     int k2 = -1;
-    if (have) {
+    if (have && parked) {
+      pkt_store_cg(hot + idx, p, rng);
+      done = true;
+      k2 = KIND_KAPPA;
+      have = false;
+      tl.handoffs++;
+    } else if (have) {
       events++;
       const bool active = (p.type != ARTIS_TYPE_ESCAPE) && (p.prop_time < t2);
       const int knext = active ? kind_of(c, p) : -1;
@@ -719,23 +805,28 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
   stats_block_flush(c);
 }
 
-// The macro-atom jump role on its own (kernels.cuh KIND_MAJUMP). A lane holds 32 bytes of its packet -- cell, macro-atom
-// state, interaction count -- and the packet's Philox stream; an iteration is ma_jump: one row of process rates, one or two
-// draws, one search over a prefix-sum row. Jumps that stay inside the ion (98 % of them) only change the level; any other
-// action is left in pend[] for the event role of k_transport_persistent and the packet moves to that ring.
+// The light kernel: the two roles that need almost no packet state and are chains of table reads -- a small register budget,
+// hence many resident warps to hide the L2 round trips and the instruction fetches.
+//   KIND_MAJUMP  macro-atom jumps within an ion. A lane holds 32 bytes of its packet (cell, macro-atom state, interaction
+//                count) and the packet's Philox stream; an iteration is ma_jump: one row of process rates, one or two draws,
+//                one search over a prefix-sum row. Jumps that stay inside the ion (98 % of them) only change the level; any
+//                other action is left in pend[] for the event role of k_transport_persistent and the packet moves to that ring.
+//   KIND_KAPPA   continuum-opacity sums for thin-cell r-packet steps that k_transport_persistent has begun: a lane reads the
+//                packet's cell and frequency, the warp evaluates the requests of its lanes one after the other with all 32
+//                lanes (coop_kappa_sum, tiles staged by TMA), the result goes to the packet's kcache row and the packet to
+//                the KIND_THIN_RESUME ring, where a thin-role warp finishes the step.
 struct MaView {
   int where, ma_element, ma_ion, ma_level, interactions;
 };
-__global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_majump(PktHot *hot, PersistView pv, long long max_events,
-                                                                  unsigned long long idle_timeout_ns) {
+__global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_light(PktHot *hot, PersistView pv, long long max_events,
+                                                                              unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  constexpr int role = KIND_MAJUMP;
   Tally tl = {};
   bool have = false;
-  int idx = 0;
+  int idx = 0, role = KIND_MAJUMP;
   int events = 0;
   const int event_cap = max_events > 0x7fffffffLL ? 0x7fffffff : (int)max_events;
   MaView v = {0, 0, 0, 0, 0};
@@ -744,9 +835,13 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_majump(
   int last_active = -1;
   int refill_skip = 0;
   // statistics in 32-bit words (this kernel lives on its small register budget): iterations, busy lanes, and cycles in units
-  // of 64 (lane 5: the jumps themselves; lane 0: refill, push, idle)
+  // of 64 (lanes KIND_MAJUMP and KIND_KAPPA: the role's own cycles; lane 0: refill, push, idle)
   unsigned fill_iters = 0, fill_lanes = 0, cyc_a = 0, cyc_b = 0, cyc_c = 0;
   stats_block_begin();
+  extern __shared__ __align__(16) unsigned char kappa_smem[];
+  KappaStage *const ks = reinterpret_cast<KappaStage *>(kappa_smem) + (threadIdx.x >> 5);
+  unsigned nchunk = 0u;
+  if (ARTIS_KAPPA_OFFLOAD != 0) kappa_stage_init(ks);
   while (true) {
     __syncwarp(full);
     const unsigned tick0 = (unsigned)clock();
@@ -754,31 +849,44 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_majump(
     if (need != full && refill_skip > 0) {
       refill_skip--;
     } else if (need != 0u) {
+      if (need == full) {  // out of work: the role with the longer backlog
+        long long bj = 0, bk = 0;
+        if (lane == 0) {
+          bj = ring_backlog(pv, KIND_MAJUMP);
+          bk = ARTIS_KAPPA_OFFLOAD != 0 ? ring_backlog(pv, KIND_KAPPA) : 0;
+        }
+        bj = __shfl_sync(full, bj, 0);
+        bk = __shfl_sync(full, bk, 0);
+        if (bj <= 0 && bk <= 0) {
+          if (idle_poll(c, pv, idle_since, last_active, idle_timeout_ns)) break;
+          if (lane == 0) cyc_c += ((unsigned)clock() - tick0) >> 6;
+          continue;
+        }
+        role = (bk > 0 && bk >= bj) ? KIND_KAPPA : KIND_MAJUMP;
+        idle_since = 0ull;
+      }
       const int want = __popc(need);
       int take = 0;
       unsigned long long base = 0ull;
       if (lane == 0) take = ring_claim(pv, role, want, &base);
       take = __shfl_sync(full, take, 0);
       base = __shfl_sync(full, base, 0);
-      if (need == full && take == 0) {
-        if (idle_poll(c, pv, idle_since, last_active, idle_timeout_ns)) break;
-        if (lane == 0) cyc_c += ((unsigned)clock() - tick0) >> 6;
-        continue;
-      }
-      idle_since = 0ull;
+      if (need == full && take == 0) continue;  // lost the race for the last entries
       const int rank = __popc(need & ((1u << lane) - 1u));
       if (!have && rank < take) {
         idx = ring_take(pv, role, base + (unsigned long long)rank);
-        // sector 0 of the hot record and the (draw counter, number) pair of sector 1
-        const uint4 a = __ldcg(reinterpret_cast<const uint4 *>(hot + idx));
-        const uint4 b = __ldcg(reinterpret_cast<const uint4 *>(hot + idx) + 1);
-        const uint2 r = __ldcg(reinterpret_cast<const uint2 *>(&hot[idx].rngctr));
-        v.where = (int)a.x;
-        v.ma_element = pkt_lo16(a.z);
-        v.ma_ion = pkt_hi16(a.z);
-        v.ma_level = (int)a.w;
-        v.interactions = (int)b.y;
-        rng = rng_init(c, (int)r.y, (unsigned long long)r.x);
+        if (role == KIND_MAJUMP) {
+          // sector 0 of the hot record and the (draw counter, number) pair of sector 1
+          const uint4 a = __ldcg(reinterpret_cast<const uint4 *>(hot + idx));
+          const uint4 b = __ldcg(reinterpret_cast<const uint4 *>(hot + idx) + 1);
+          const uint2 r = __ldcg(reinterpret_cast<const uint2 *>(&hot[idx].rngctr));
+          v.where = (int)a.x;
+          v.ma_element = pkt_lo16(a.z);
+          v.ma_ion = pkt_hi16(a.z);
+          v.ma_level = (int)a.w;
+          v.interactions = (int)b.y;
+          rng = rng_init(c, (int)r.y, (unsigned long long)r.x);
+        }
         events = 0;
         have = true;
       }
@@ -796,7 +904,49 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_majump(
     }
     bool done = false;
     int k2 = -1;
-    if (have) {
+    if (ARTIS_KAPPA_OFFLOAD != 0 && role == KIND_KAPPA) {  // warp-uniform
+      // rpkt.cc:1209-1309 calculate_kappa_rpkt_cont for the packets of the warp's lanes, written to their kcache rows
+      int mgi = 0;
+      double nu_cmf = 0., sigma = 0., kappa_ff = 0.;
+      double *kc = nullptr;
+      if (have) {
+        mgi = cell_mgi(c, __ldcg(&hot[idx].where));
+        nu_cmf = __ldcg(&hot[idx].nu_cmf);
+        kc = pv.kcache + (size_t)idx * pv.kstride;
+        tl.kappa_evals++;
+        sigma = SIGMA_T * c.cs.nne[mgi];
+        kappa_ff = calculate_kappa_ff(c, mgi, nu_cmf);
+        const int ng = c.st.nbfcontinua_ground;
+        for (int g = 0; g < ng; g++) __stcg(kc + 8 + g, 0.);
+      }
+      const double kappa_bf = coop_kappa_sum(c, have, mgi, nu_cmf, tl, ks, nchunk, [&](const int sl, const double val) {
+        __stcg(kc + 8 + sl, __ldcg(kc + 8 + sl) + val);
+      });
+      if (have) {
+        double total = sigma + kappa_bf + kappa_ff, es = sigma, ff = kappa_ff, bf = kappa_bf;
+        if (!isfinite(total)) {  // rpkt.cc:1280-1294 soft fallback, as rpkt.cuh kappa_store
+          if (isfinite(es)) {
+            ff = 0.;
+            bf = 0.;
+            total = es;
+            tl.soft_repairs++;
+          } else {
+            fatal(c, 101);
+          }
+        }
+        __stcg(kc + 0, nu_cmf);
+        __stcg(kc + 1, total);
+        __stcg(kc + 2, es);
+        __stcg(kc + 3, ff);
+        __stcg(kc + 4, bf);
+        __stcg(kc + 5, kappa_ff);
+        __stcg(kc + 6, (double)mgi);
+        tl.handoffs++;
+        done = true;
+        k2 = KIND_THIN_RESUME;
+        have = false;
+      }
+    } else if (have) {
       tl.packet_updates++;
       int selidx;
       const int action = ma_jump(c, v, rng, tl, &selidx);
@@ -820,17 +970,18 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_majump(
     }
     __syncwarp(full);
     const unsigned tick2 = (unsigned)clock();
-    if (lane == role) cyc_a += (tick2 - tick1) >> 6;
+    if (lane == role) cyc_b += (tick2 - tick1) >> 6;
     if (__ballot_sync(full, done) != 0u) {
       push_done(c, pv, done, k2, idx);
       if (lane == 0) cyc_b += ((unsigned)clock() - tick2) >> 6;
     }
   }
   tally_flush(c, tl);
-  if (lane == role && fill_iters > 0) {
-    ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + role], fill_iters);
-    ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + role], fill_lanes);
-    ctr_add(&c.es.counters[ARTIS_CTR_WARP_CYCLES0 + role], (long long)cyc_a << 6);
+  // a warp may have served both roles: its role cycles are filed under the role it ends in (statistics only)
+  if ((lane == KIND_MAJUMP || lane == KIND_KAPPA) && fill_iters > 0) {
+    ctr_add(&c.es.counters[ARTIS_CTR_WARP_ITERS0 + lane], fill_iters);
+    ctr_add(&c.es.counters[ARTIS_CTR_BUSY_LANES0 + lane], fill_lanes);
+    ctr_add(&c.es.counters[ARTIS_CTR_WARP_CYCLES0 + lane], (long long)cyc_b << 6);
   }
   if (lane == 0) {
     ctr_add(&c.es.counters[ARTIS_CTR_REFILL_CYCLES], (long long)cyc_a << 6);
@@ -931,6 +1082,9 @@ bool g_persistent_warmed = false;
 unsigned long long g_idle_timeout_ns = 20ull * 1000000000ull;  // hang guard of the persistent kernels (artis_gpu_set_tuning)
 double *g_est_block = nullptr;
 size_t g_est_ndoubles = 0;
+int g_nbfcontinua_ground = 0;
+double *g_kcache = nullptr, *g_stepstate = nullptr;
+size_t g_kcache_doubles = 0;
 std::string g_async_err;
 
 void note(cudaError_t e, const char *what) {
@@ -962,11 +1116,12 @@ bool be_select_device(int device, std::string *why) {
   // The two kernels of the pair must be able to share an SM: the same L1 / shared-memory split for both (an SM cannot
   // hold blocks of kernels with different carve-outs -- the second kernel would wait for the first to drain, which never
   // happens here because each waits for the other's packets).
-  constexpr int CARVEOUT_PERCENT = 50;  // of the 228 KB: room for the opacity stages of three big blocks, the rest stays L1
+  constexpr int CARVEOUT_PERCENT = 50;  // of the 228 KB: room for the opacity stages of four light blocks, the rest stays L1
   note(cudaFuncSetAttribute(k_transport_persistent<ROLES_ALL>, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
   note(cudaFuncSetAttribute(k_transport_persistent<ROLES_HEAVY>, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
-  note(cudaFuncSetAttribute(k_transport_majump, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
+  note(cudaFuncSetAttribute(k_transport_light, cudaFuncAttributePreferredSharedMemoryCarveout, CARVEOUT_PERCENT), "carve-out");
   note(cudaFuncSetAttribute(k_transport_persistent<ROLES_ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KAPPA_SMEM_PER_BLOCK), "dynamic smem");
+  note(cudaFuncSetAttribute(k_transport_light, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KAPPA_SMEM_PER_BLOCK), "dynamic smem");
   note(cudaFuncSetAttribute(k_transport_persistent<ROLES_HEAVY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)KAPPA_SMEM_PER_BLOCK), "dynamic smem");
   {
     cudaFuncAttributes aa{}, ah{}, aj{};
@@ -982,22 +1137,22 @@ bool be_select_device(int device, std::string *why) {
       if (g_blocks_all < 1) g_blocks_all = 1;
     }
     if (cudaFuncGetAttributes(&ah, k_transport_persistent<ROLES_HEAVY>) == cudaSuccess &&
-        cudaFuncGetAttributes(&aj, k_transport_majump) == cudaSuccess && ah.numRegs > 0 && aj.numRegs > 0) {
+        cudaFuncGetAttributes(&aj, k_transport_light) == cudaSuccess && ah.numRegs > 0 && aj.numRegs > 0) {
       const int heavy = block_regs(ah), jump = block_regs(aj);
       int hb = ARTIS_HEAVY_BLOCKS;
       if (hb <= 0) {  // as many blocks of the big kernel as leave room for at least two blocks (8 warps) of jumps
         hb = (regs_per_sm - 2 * jump) / heavy;
-        if (hb > smem_blocks) hb = smem_blocks;
       }
       if (hb < 1) hb = 1;
       int jb = (regs_per_sm - hb * heavy) / jump;
-      if (jb > 12) jb = 12;  // 48 warps of jumps per SM are plenty; leaves thread and block slots for the big kernel
+      if (LIGHT_SMEM != 0 && jb > smem_blocks) jb = smem_blocks;  // whichever kernel holds the opacity stages
+      if (HEAVY_SMEM != 0 && hb > smem_blocks) hb = smem_blocks;
       if ((hb + jb) * 128 > prop.maxThreadsPerMultiProcessor) jb = prop.maxThreadsPerMultiProcessor / 128 - hb;
       // measurement knob: ARTIS_GEOMETRY="<blocks of the big kernel>,<blocks of the jump kernel>" per SM (must fit the SM)
       if (const char *geo = getenv("ARTIS_GEOMETRY")) {
         int a = 0, b2 = 0;
         if (sscanf(geo, "%d,%d", &a, &b2) == 2 && a >= 1 && b2 >= 1 && a * heavy + b2 * jump <= regs_per_sm &&
-            (a + b2) * 128 <= prop.maxThreadsPerMultiProcessor && a <= smem_blocks) {
+            (a + b2) * 128 <= prop.maxThreadsPerMultiProcessor && (LIGHT_SMEM != 0 ? b2 : a) <= smem_blocks) {
           hb = a;
           jb = b2;
         }
@@ -1039,6 +1194,7 @@ void be_d2h(void *d, const void *s, size_t n) {
 }
 void be_zero(void *p, size_t n) { note(cudaMemsetAsync(p, 0, n, g_stream), "memset"); }
 void be_set_ctx(const artis::Ctx &c) {
+  g_nbfcontinua_ground = c.st.nbfcontinua_ground;
   note(cudaMemcpyToSymbolAsync(d_ctx, &c, sizeof(c), 0, cudaMemcpyHostToDevice, g_stream), "ctx upload");
   note(cudaStreamSynchronize(g_stream), "ctx sync");
 }
@@ -1115,6 +1271,24 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
   pv.t_start = pmeta + (2 * NRING + 1) * RMS;
   pv.cap = cap;
   pv.pend = pend;
+  // opacity hand-over rows of the two-kernel scheduler (8 scalars + the ground-continuum contributions per packet)
+  const int kstride = (8 + g_nbfcontinua_ground + 1) & ~1;
+  if ((size_t)cap * kstride > g_kcache_doubles) {
+    if (g_kcache) cudaFree(g_kcache);
+    if (g_stepstate) cudaFree(g_stepstate);
+    g_kcache = nullptr;
+    g_stepstate = nullptr;
+    g_kcache_doubles = 0;
+    if (cudaMalloc(&g_kcache, (size_t)cap * kstride * sizeof(double)) != cudaSuccess ||
+        cudaMalloc(&g_stepstate, (size_t)cap * 3 * sizeof(double)) != cudaSuccess) {
+      note(cudaGetLastError(), "cudaMalloc (opacity hand-over buffers)");
+      return true;  // be_sync reports the error
+    }
+    g_kcache_doubles = (size_t)cap * kstride;
+  }
+  pv.kcache = g_kcache;
+  pv.stepstate = g_stepstate;
+  pv.kstride = kstride;
   const unsigned long long timeout = g_idle_timeout_ns;
   if (!g_persistent_warmed) {
     // First launch of each persistent kernel with nothing to do (n_active == 0: every warp leaves at once). A first
@@ -1130,8 +1304,8 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
       w.t_start = scratch + (2 * NRING + 1) * RMS;
       w.n_initial = 0;
       k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, w, maxev, timeout);
-      k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, w, maxev, timeout);
-      if (g_blocks_jump > 0) k_transport_majump<<<g_sms * g_blocks_jump, 128, 0, g_stream>>>(hot, w, maxev, timeout);
+      k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, HEAVY_SMEM, g_stream>>>(hot, cold, w, maxev, timeout);
+      if (g_blocks_jump > 0) k_transport_light<<<g_sms * g_blocks_jump, 128, LIGHT_SMEM, g_stream>>>(hot, w, maxev, timeout);
       note(cudaStreamSynchronize(g_stream), "warm-up sync");
       cudaFree(scratch);
     }
@@ -1141,12 +1315,16 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
     k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, pv, maxev, timeout);
     return true;
   }
-  // the big kernel goes first, the jump kernel fills the rest of every SM; the side stream waits for what is queued on the
-  // main stream (ring setup) and the main stream waits for the side kernel
+  // Both kernels must be resident on every SM at once. The kernel that needs shared memory (the opacity stages) is
+  // launched first, so the L1 / shared-memory split it brings to an SM also fits the blocks of the other kernel, which
+  // need next to none -- launched the other way round, the split chosen for the first kernel leaves no room for the
+  // second one's blocks and they wait for the first kernel to drain, which it never does (each waits for the other's
+  // packets). The side stream waits for what is queued on the main stream (ring setup), the main stream for the side kernel.
   note(cudaEventRecord(g_ev_fork, g_stream), "event record");
   note(cudaStreamWaitEvent(g_stream2, g_ev_fork, 0), "stream wait");
-  k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, pv, maxev, timeout);
-  k_transport_majump<<<g_sms * g_blocks_jump, 128, 0, g_stream2>>>(hot, pv, maxev, timeout);
+  if (LIGHT_SMEM != 0) k_transport_light<<<g_sms * g_blocks_jump, 128, LIGHT_SMEM, g_stream2>>>(hot, pv, maxev, timeout);
+  k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, HEAVY_SMEM, g_stream>>>(hot, cold, pv, maxev, timeout);
+  if (LIGHT_SMEM == 0) k_transport_light<<<g_sms * g_blocks_jump, 128, LIGHT_SMEM, g_stream2>>>(hot, pv, maxev, timeout);
   note(cudaEventRecord(g_ev_join, g_stream2), "event record");
   note(cudaStreamWaitEvent(g_stream, g_ev_join, 0), "stream wait");
   return true;

@@ -20,11 +20,12 @@ except Exception as e:
 PY
 }
 export ARTIS_HANG_S=5
-run default ARTIS_X=0
-run single ARTIS_BENCH_SCHED=1
-for v in $VARIANTS; do
-  run $v ARTIS_GPU_LIB=$PWD/variants/libartis_gpu_$v.so
-done
-for g in $GEOMETRIES; do
-  run g$g ARTIS_GEOMETRY=$g
+# RUNS: space-separated name:lib:geometry (lib "-" = the shipped library, geometry "-" = the library's default)
+for spec in $RUNS; do
+  IFS=: read name lib geo <<< "$spec"
+  envs="ARTIS_X=0"
+  [ "$lib" != "-" ] && envs="$envs ARTIS_GPU_LIB=$PWD/variants/libartis_gpu_$lib.so"
+  [ "$geo" != "-" ] && envs="$envs ARTIS_GEOMETRY=$geo"
+  [ "$name" = "single" ] && envs="$envs ARTIS_BENCH_SCHED=1"
+  run $name $envs
 done
