@@ -163,6 +163,7 @@ def declare(lib):
         "artis_gpu_probe_cooling_ion": [pi, pi, pi, C.c_int, pd],
         "artis_gpu_probe_gamma_kappa": [vp, C.c_int, pd],
         "artis_gpu_probe_levelpop": [pi, pi, pi, pi, C.c_int, pd],
+        "artis_gpu_probe_select_continuum_nu": [pi, pi, pi, pi, P(C.c_float), pd, C.c_int, pd],
     }
     for name, args in sig.items():
         if name in CUDA_ONLY_SYMBOLS and not hasattr(lib, name):
@@ -184,5 +185,5 @@ EXPORTED_SYMBOLS = [
     "artis_gpu_probe_kappa_cont", "artis_gpu_probe_closest_transition", "artis_gpu_probe_get_event",
     "artis_gpu_probe_macroatom_rates", "artis_gpu_probe_cooling_ion", "artis_gpu_probe_gamma_kappa",
     "artis_gpu_probe_levelpop", "artis_gpu_launch_count", "artis_gpu_table_bytes", "artis_gpu_bin_escaped",
-    "artis_gpu_packets_download_escaped", "artis_gpu_pack_escaped_noalloc", "artis_gpu_scheduler_geometry",
+    "artis_gpu_packets_download_escaped", "artis_gpu_pack_escaped_noalloc", "artis_gpu_scheduler_geometry", "artis_gpu_probe_select_continuum_nu",
 ]

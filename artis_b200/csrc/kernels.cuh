@@ -245,6 +245,13 @@ ARTIS_DEV void body_probe_gamma_kappa(const Ctx &c, const ArtisPacket *pkts, con
   kap[idx * 3 + 1] = sig_photo_electric(c, p, mgi);
   kap[idx * 3 + 2] = sig_pair_prod(c, p, mgi);
 }
+// select_continuum_nu (ratecoeff.cc:628) with the random number injected: (element, lower ion, lower level, level of the
+// upper ion, T_e, zrand) -> frequency
+ARTIS_DEV void body_probe_scnu(const Ctx &c, const int *element, const int *ion, const int *level, const int *upper, const float *T_e,
+                               const double *zrand, const int idx, double *nu) {
+  const int ui = uion_of(c, element[idx], ion[idx]);
+  nu[idx] = select_continuum_nu_z(c, ui, c.st.ion_leveloffset[ui] + level[idx], upper[idx], T_e[idx], zrand[idx]);
+}
 ARTIS_DEV void body_probe_levelpop(const Ctx &c, const int *mgi, const int *element, const int *ion, const int *level,
                                    const int idx, double *pop) {
   pop[idx] = tab_levelpop(c, tabcell(c, mgi[idx]), glevel_of(c, element[idx], ion[idx], level[idx]));

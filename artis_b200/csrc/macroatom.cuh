@@ -63,8 +63,8 @@ ARTIS_DEV double gl8(const Ctx &c, const int tablerow, const double nu_edge, con
 // integrals are evaluated once with a fixed 8-point rule per smooth sub-interval (pieces are split at the knots of
 // the cross-section table) and the tails are their suffix sums. Selection rule and interpolation are the
 // reference's, including the extrapolation when no piece is selected. Tolerance: |dnu/nu| <= 1e-3 (tests).
-ARTIS_DEV_NOINLINE double select_continuum_nu(const Ctx &c, const int ui_lower, const int gl_lower, const int upperionlevel, const float T_e,
-                                     Rng &rng) {
+ARTIS_DEV_NOINLINE double select_continuum_nu_z(const Ctx &c, const int ui_lower, const int gl_lower, const int upperionlevel,
+                                                const float T_e, const double zrand) {
   const int t = phixstargetindex_of(c, gl_lower, upperionlevel);
   if (t < 0) {
     fatal(c, 210);
@@ -75,7 +75,6 @@ ARTIS_DEV_NOINLINE double select_continuum_nu(const Ctx &c, const int ui_lower, 
   const double nu_max_phixs = nu_threshold * c.st.last_phixs_nuovernuedge;
   const int npieces = c.st.nphixspoints;
   const int tablerow = c.st.lev_phixstable[gl_lower];
-  const double zrand = 1. - rng_uniform(rng);  // (0, 1]
   const double deltanu = (nu_max_phixs - nu_threshold) / npieces;
   const double knotstep = nu_threshold * c.st.nphixsnuincrement;
   // pass 1: total; pass 2: walk the tails from the blue end of the reference's loop
@@ -125,6 +124,12 @@ ARTIS_DEV_NOINLINE double select_continuum_nu(const Ctx &c, const int ui_lower, 
     }
   }
   return nu_threshold;
+}
+// the draw of ratecoeff.cc:643: zrand = 1 - uniform in (0, 1]
+ARTIS_DEV double select_continuum_nu(const Ctx &c, const int ui_lower, const int gl_lower, const int upperionlevel, const float T_e,
+                                     Rng &rng) {
+  const double zrand = 1. - rng_uniform(rng);
+  return select_continuum_nu_z(c, ui_lower, gl_lower, upperionlevel, T_e, zrand);
 }
 
 // common tail of every r-packet emission from a macro-atom / k-packet

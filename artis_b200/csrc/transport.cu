@@ -1065,6 +1065,10 @@ __global__ void k_probe_gamma_kappa(const ArtisPacket *p, int n, double *o) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) artis::body_probe_gamma_kappa(d_ctx, p, i, o);
 }
+__global__ void k_probe_scnu(const int *a, const int *b, const int *c2, const int *d, const float *T, const double *z, int n, double *o) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) artis::body_probe_scnu(d_ctx, a, b, c2, d, T, z, i, o);
+}
 __global__ void k_probe_levelpop(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) artis::body_probe_levelpop(d_ctx, a, b, c, d, i, o);
@@ -1358,6 +1362,9 @@ void be_run_probe_ma_rates(const int *a, const int *b, const int *c, const int *
 }
 void be_run_probe_cooling(const int *a, const int *b, const int *c, int n, double *o) { k_probe_cooling<<<PROBE_GRID(n)>>>(a, b, c, n, o); }
 void be_run_probe_gamma_kappa(const ArtisPacket *p, int n, double *o) { k_probe_gamma_kappa<<<PROBE_GRID(n)>>>(p, n, o); }
+void be_run_probe_scnu(const int *a, const int *b, const int *c2, const int *d, const float *T, const double *z, int n, double *o) {
+  k_probe_scnu<<<PROBE_GRID(n)>>>(a, b, c2, d, T, z, n, o);
+}
 void be_run_probe_levelpop(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
   k_probe_levelpop<<<PROBE_GRID(n)>>>(a, b, c, d, n, o);
 }

@@ -235,6 +235,16 @@ class Transport:
         self._check(self.lib.artis_gpu_probe_gamma_kappa(pkts.ctypes.data_as(C.c_void_p), n, _pd(out)), "probe_gamma_kappa")
         return out
 
+    def probe_select_continuum_nu(self, element, lowerion, lower, upper, T_e, zrand):
+        a = [np.ascontiguousarray(x, np.int32) for x in (element, lowerion, lower, upper)]
+        t = np.ascontiguousarray(T_e, np.float32)
+        z = np.ascontiguousarray(zrand, np.float64)
+        out = np.zeros(z.size)
+        self._check(self.lib.artis_gpu_probe_select_continuum_nu(_pi(a[0]), _pi(a[1]), _pi(a[2]), _pi(a[3]),
+                                                                 t.ctypes.data_as(C.POINTER(C.c_float)), _pd(z), z.size, _pd(out)),
+                    "probe_select_continuum_nu")
+        return out
+
     def probe_levelpop(self, mgi, element, ion, level):
         a = [np.ascontiguousarray(x, np.int32) for x in (mgi, element, ion, level)]
         n = a[0].size

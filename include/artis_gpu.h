@@ -267,6 +267,12 @@ int artis_gpu_probe_macroatom_rates(const int *mgi, const int *element, const in
 int artis_gpu_probe_cooling_ion(const int *mgi, const int *element, const int *ion, int n, double *contrib_total);
 /* gamma opacities (gammapkt.cc:335, photo_electric.cc:10,51): out kap[n*3] = compton, photoelectric, pair */
 int artis_gpu_probe_gamma_kappa(const ArtisPacket *pkts, int n, double *kap);
+/* select_continuum_nu (ratecoeff.cc:628) with its random number injected (zrand = 1 - gsl_rng_uniform, ratecoeff.cc:643):
+ * the free-bound emission frequency for recombination onto (element, lowerion, lower) from level `upperionlevel` of the ion
+ * above at electron temperature T_e: out nu[n]. The reference integrates with adaptive GSL qag to
+ * CONTINUUM_NU_INTEGRAL_ACCURACY (1e-2 / 1e-3); stated tolerance of the comparison: 1e-3 relative. */
+int artis_gpu_probe_select_continuum_nu(const int *element, const int *lowerion, const int *lower, const int *upperionlevel,
+                                        const float *T_e, const double *zrand, int n, double *nu);
 /* get_levelpop (ltepop.cc:432): out pop[n] */
 int artis_gpu_probe_levelpop(const int *mgi, const int *element, const int *ion, const int *level, int n, double *pop);
 

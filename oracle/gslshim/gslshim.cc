@@ -92,7 +92,19 @@ unsigned long gsl_rng_get(gsl_rng *r) {
   r->buffer[r->x] = j;
   return (unsigned long)j;
 }
-double gsl_rng_uniform(gsl_rng *r) { return gsl_rng_get(r) / (double)M_BIG; }
+// Test hook (not part of GSL): the next gsl_rng_uniform call returns `u` instead of drawing. The reference's
+// select_continuum_nu (ratecoeff.cc:643) draws its random number itself; with this its result becomes a deterministic
+// function of (continuum, T_e, u) that the probe of oracle/refglue/hook.cc records.
+static double g_forced_uniform = -1.;
+extern "C" void gslshim_force_uniform(double u) { g_forced_uniform = u; }
+double gsl_rng_uniform(gsl_rng *r) {
+  if (g_forced_uniform >= 0.) {
+    const double u = g_forced_uniform;
+    g_forced_uniform = -1.;
+    return u;
+  }
+  return gsl_rng_get(r) / (double)M_BIG;
+}
 double gsl_rng_uniform_pos(gsl_rng *r) {
   double x;
   do {

@@ -26,6 +26,7 @@
 #include "boundary.h"
 #include "ltepop.h"
 #include "photo_electric.h"
+#include "ratecoeff.h"
 #include "rpkt.h"
 #include "update_grid.h"
 #include "vectors.h"
@@ -100,6 +101,7 @@ std::set<int> parse_list(const char *env) {
 // ---- deterministic probes: the reference's own functions called on packet states built
 // from packets.pre; inputs and outputs go into the snapshot so that the CUDA probes (artis_gpu_probe_*) can be
 // compared entry by entry. Runs before the reference transport; touches only the per-thread caches.
+extern "C" void gslshim_force_uniform(double u);  // oracle/gslshim/gslshim.cc (test hook of the GSL stand-in)
 double hash01(unsigned long long x) {
   x ^= x >> 33;
   x *= 0xff51afd7ed558ccdULL;
@@ -251,6 +253,42 @@ void write_probes(FILE *f, const struct packet *packets, const int npkts, const 
   write_record(f, "probe.cool_element", "i4", ce.data(), ce.size(), 4);
   write_record(f, "probe.cool_ion", "i4", ci.data(), ci.size(), 4);
   write_record(f, "probe.cool_total", "f8", cool.data(), cool.size(), 8);
+  // select_continuum_nu (ratecoeff.cc:628-684) with its random number injected through the GSL stand-in: a sample of
+  // bound-free continua x the T_e of the probed cells x a spread of draws (the function returns the frequency at which
+  // the tail integral of the emission profile equals zrand = 1 - u of the total)
+  {
+    std::vector<int> se, si, sl, su;
+    std::vector<float> sT;
+    std::vector<double> sz, snu;
+    const double draws[] = {0.0, 0.004, 0.05, 0.3, 0.5, 0.75, 0.93, 0.995};
+    const int nbf = globals::nbfcontinua;
+    const int stride_c = nbf > 160 ? nbf / 160 : 1;
+    for (int i = 0; i < nbf; i += stride_c) {
+      const int el = globals::allcont[i].element, ion = globals::allcont[i].ion, lev = globals::allcont[i].level;
+      const int upper = get_phixsupperlevel(el, ion, lev, globals::allcont[i].phixstargetindex);
+      for (size_t ci2 = 0; ci2 < cells.size(); ci2 += (cells.size() > 2 ? cells.size() - 1 : 1)) {
+        const float T_e = grid::get_Te(cells[ci2]);
+        for (double u : draws) {
+          gslshim_force_uniform(u);
+          const double nu = select_continuum_nu(el, ion, lev, upper, T_e);
+          se.push_back(el);
+          si.push_back(ion);
+          sl.push_back(lev);
+          su.push_back(upper);
+          sT.push_back(T_e);
+          sz.push_back(1. - u);
+          snu.push_back(nu);
+        }
+      }
+    }
+    write_record(f, "probe.scnu_element", "i4", se.data(), se.size(), 4);
+    write_record(f, "probe.scnu_ion", "i4", si.data(), si.size(), 4);
+    write_record(f, "probe.scnu_level", "i4", sl.data(), sl.size(), 4);
+    write_record(f, "probe.scnu_upper", "i4", su.data(), su.size(), 4);
+    write_record(f, "probe.scnu_Te", "f4", sT.data(), sT.size(), 4);
+    write_record(f, "probe.scnu_zrand", "f8", sz.data(), sz.size(), 8);
+    write_record(f, "probe.scnu_nu", "f8", snu.data(), snu.size(), 8);
+  }
   // leave the per-thread caches as update_packets expects to find them
   globals::cellhistory[tid].cellnumber = -99;
   globals::kappa_rpkt_cont[tid].recalculate_required = true;

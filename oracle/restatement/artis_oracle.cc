@@ -116,6 +116,9 @@ void be_run_probe_cooling(const int *a, const int *b, const int *c, int n, doubl
 void be_run_probe_gamma_kappa(const ArtisPacket *p, int n, double *o) {
   for (int i = 0; i < n; i++) artis::body_probe_gamma_kappa(g_ctx, p, i, o);
 }
+void be_run_probe_scnu(const int *a, const int *b, const int *c2, const int *d, const float *T, const double *z, int n, double *o) {
+  for (int i = 0; i < n; i++) artis::body_probe_scnu(g_ctx, a, b, c2, d, T, z, i, o);
+}
 void be_run_probe_levelpop(const int *a, const int *b, const int *c, const int *d, int n, double *o) {
   for (int i = 0; i < n; i++) artis::body_probe_levelpop(g_ctx, a, b, c, d, i, o);
 }

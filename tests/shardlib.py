@@ -1,4 +1,4 @@
-"""Packet sharding across ranks: every rank transports its own packets with the grid, atomic data and
+"""TEST HELPER (not part of the product package). Packet sharding across ranks: every rank transports its own packets with the grid, atomic data and
 cell tables replicated; the only exchange of a timestep is the sum of the estimator arrays, the reference's
 mpi_reduce_estimators (sn3d.cc:316-384, called at sn3d.cc:582). On GPUs that sum is one NCCL all-reduce of the
 contiguous estimator block (Transport.estimator_block, used by bench.py); this module holds the backend-independent

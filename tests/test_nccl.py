@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 
 import goldenlib
-from artis_b200 import sharding
+import shardlib as sharding
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
