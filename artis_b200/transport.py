@@ -104,6 +104,17 @@ class Transport:
                     "artis_gpu_packets_download")
         return out
 
+    # ---- packet files from the resident ensemble (sn3d.cc:387-398, packet.cc:152-209)
+    def packets_write_temp(self, path):
+        self._check(self.lib.artis_gpu_packets_write_temp(os.fsencode(path)), "artis_gpu_packets_write_temp")
+
+    def packets_read_temp(self, path, npkts):
+        self._check(self.lib.artis_gpu_packets_read_temp(os.fsencode(path), int(npkts)), "artis_gpu_packets_read_temp")
+        self.npkts = int(npkts)
+
+    def packets_write_text(self, path):
+        self._check(self.lib.artis_gpu_packets_write_text(os.fsencode(path)), "artis_gpu_packets_write_text")
+
     def last_timings(self):
         ms = (C.c_double * 6)()
         n = self.lib.artis_gpu_last_timings(ms, 6)

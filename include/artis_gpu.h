@@ -248,6 +248,17 @@ int artis_gpu_packets_download_escaped(ArtisPacket *out, int capacity, int only_
 int artis_gpu_pack_escaped_noalloc(const ArtisPacket *dev_packets, int npkts, ArtisPacket *dev_out, int capacity,
                                    int *dev_n_out, void *cuda_stream);
 
+/* ---- packet files from the resident ensemble ------------------------------------------------ */
+/* The driver's packet checkpoint and final packet file, written from / read into the resident ensemble a bounded chunk at
+ * a time (a driver that keeps its packets on the device between timesteps never needs the whole array on the host):
+ *   artis_gpu_packets_write_temp  = write_temp_packetsfile (sn3d.cc:387-398): the raw 304-byte records, byte for byte
+ *   artis_gpu_packets_read_temp   = read_temp_packetsfile (packet.cc:198-209): such a file becomes the resident ensemble
+ *   artis_gpu_packets_write_text  = write_packets (packet.cc:152-196): packets*.out, same header, columns and conversions
+ * `path` is the file name the driver would build ("packets_%.4d_ts%d.tmp", "packets%.2d_%.4d.out"). */
+int artis_gpu_packets_write_temp(const char *path);
+int artis_gpu_packets_read_temp(const char *path, int npkts);
+int artis_gpu_packets_write_text(const char *path);
+
 /* ---- K10: deterministic probes (test entry points for SURVEY 8a A4-A8, A11, A12, A14) ------------------ */
 /* Each probe runs the corresponding device function for n independent packet states on the GPU. */
 /* boundary_cross (boundary.cc:101): out sdist[n], snext[n], last_cross_out[n] */

@@ -626,7 +626,7 @@ inline void flatten_estimators(ArtisEstimators *E, Storage *st, const int nts) {
   ts[ARTIS_TS_GAMMA_EMISSION] = T.gamma_emission;
   ts[ARTIS_TS_CMF_LUM] = T.cmf_lum;
   ts[ARTIS_TS_NT_ENERGY_DEPOSITED] = nonthermal::nt_energy_deposited;
-  long long *ctr = st->L(64);
+  long long *ctr = st->L(ARTIS_CTR_COUNT);
   for (int i = 0; i < stats::COUNTER_COUNT; i++) ctr[i] = stats::get_counter((enum stats::eventcounters)i);
   ctr[ARTIS_CTR_NESC] = globals::nesc;
   ctr[ARTIS_CTR_PELLET_DECAYS] = T.pellet_decays;
