@@ -89,6 +89,94 @@ ARTIS_DEV void body_bin_escaped(const BinSpec &b, const PktHot *hot, const PktCo
 }
 
 
+// ---- resolved outputs (spectrum.cc:339-452 with do_emission_res; :602-620 and light_curve.cc:55-62 with current_abin >= 0) ----
+constexpr int NPHIBINS = 10, NCOSTHETABINS = 10, MABINS = NPHIBINS * NCOSTHETABINS;  // exspec.h:7-9
+struct ResSpec {
+  double syn_dir[3];           // globals::syn_dir
+  int nelements, max_nions;
+  const int *line_element, *line_ion;          // linelist[].elementindex / .ionindex
+  const int *allcont_of_lut;                   // bflist index (-1 - emissiontype) -> allcont index
+  const int *cont_element, *cont_ion;          // allcont[].element / .ion
+  int nlines, nbfcontinua;
+  double *emission, *trueemission;             // [ntstep][nnubins][proccount], proccount = 2 * nelements * max_nions + 1
+  double *absorption;                          // [ntstep][nnubins][nelements * max_nions]
+  double *lc_res;                              // [MABINS][ntstep]
+  double *flux_res;                            // [MABINS][ntstep][nnubins]
+};
+// vectors.h:158-192
+ARTIS_DEV int escapedirectionbin(const double dir_in[3], const double syn_dir[3]) {
+  const double xhat[3] = {1.0, 0.0, 0.0};
+  const double dirmag = vec_len(dir_in);
+  const double dir[3] = {dir_in[0] / dirmag, dir_in[1] / dirmag, dir_in[2] / dirmag};
+  const double costheta = dot3(dir, syn_dir);
+  const int costhetabin = (int)((costheta + 1.0) * NPHIBINS / 2.0);
+  double vec1[3], vec2[3], vec3[3];
+  cross_prod(dir, syn_dir, vec1);
+  cross_prod(xhat, syn_dir, vec2);
+  const double cosphi = dot3(vec1, vec2) / vec_len(vec1) / vec_len(vec2);
+  cross_prod(vec2, syn_dir, vec3);
+  const double testphi = dot3(vec1, vec3);
+  int phibin;
+  if (testphi > 0) {
+    phibin = (int)(acos(cosphi) / 2. / PI * NPHIBINS);
+  } else {
+    phibin = (int)((acos(cosphi) + PI) / 2. / PI * NPHIBINS);
+  }
+  return (costhetabin * NPHIBINS) + phibin;
+}
+// spectrum.cc:306-337 columnindex_from_emissiontype; -1 where the reference would assert
+ARTIS_DEV int columnindex_from_emissiontype(const ResSpec &r, const int et) {
+  if (et >= 0) return et < r.nlines ? r.line_element[et] * r.max_nions + r.line_ion[et] : -1;
+  if (et == -9999999) return 2 * r.nelements * r.max_nions;
+  const int et_new = -1 - et;
+  if (r.nbfcontinua == 0) return 2 * r.nelements * r.max_nions;
+  if (et_new >= r.nbfcontinua) return -1;
+  const int i = r.allcont_of_lut[et_new];
+  return r.nelements * r.max_nions + r.cont_element[i] * r.max_nions + r.cont_ion[i];
+}
+ARTIS_DEV void body_bin_resolved(const BinSpec &b, const ResSpec &r, const PktHot *hot, const PktCold *cold, const long long n,
+                                 int *error_flag) {
+  const PktHot &p = hot[n];
+  if (pkt_lo16(p.type_cross) != ARTIS_TYPE_ESCAPE) return;
+  const PktCold &pc = cold[n];
+  if (pc.escape_type != ARTIS_TYPE_RPKT) return;
+  const double t_arrive = (double)pc.escape_time - (dot3(p.pos, p.dir) / CLIGHT_PROP);
+  if (!(t_arrive > b.tmin && t_arrive < b.tmax)) return;
+  const int nt = bin_timestep(b, t_arrive);
+  const int abin = escapedirectionbin(p.dir, r.syn_dir);
+  if (abin < 0 || abin >= MABINS) {  // assert_always(na < MABINS)
+    if (error_flag) *error_flag = 801;
+    return;
+  }
+  bin_add(&r.lc_res[(size_t)abin * b.ntstep + nt], p.e_rf / b.ts_width[nt] * MABINS / b.nprocs);
+  const double nu_rf = p.nu_rf;
+  if (!(nu_rf > b.nu_min && nu_rf < b.nu_max)) return;
+  const int nnu = (int)((log(nu_rf) - log(b.nu_min)) / b.dlognu);
+  if (nnu >= b.nnubins) return;
+  constexpr double PARSEC = 3.0857e+18;
+  const double deltaE = p.e_rf / b.ts_width[nt] / b.delta_freq[nnu] / 4.e12 / PI / PARSEC / PARSEC / b.nprocs * 1.;
+  const double deltaE_abin = p.e_rf / b.ts_width[nt] / b.delta_freq[nnu] / 4.e12 / PI / PARSEC / PARSEC / b.nprocs * (double)MABINS;
+  bin_add(&r.flux_res[((size_t)abin * b.ntstep + nt) * b.nnubins + nnu], deltaE_abin);
+  const int proccount = 2 * r.nelements * r.max_nions + 1, ioncount = r.nelements * r.max_nions;
+  const size_t cell = (size_t)nt * b.nnubins;
+  const int nproc = columnindex_from_emissiontype(r, pc.emissiontype);
+  const int truenproc = columnindex_from_emissiontype(r, pc.trueemissiontype);
+  if (nproc < 0 || nproc >= proccount || truenproc < 0 || truenproc >= proccount) {  // assert_always in the reference
+    if (error_flag) *error_flag = 802;
+    return;
+  }
+  bin_add(&r.emission[(cell + nnu) * proccount + nproc], deltaE);
+  bin_add(&r.trueemission[(cell + nnu) * proccount + truenproc], deltaE);
+  const int nnu_abs = (int)((log(pc.absorptionfreq) - log(b.nu_min)) / b.dlognu);
+  if (pc.absorptionfreq > 0. && nnu_abs >= 0 && nnu_abs < b.nnubins) {
+    const int at = pc.absorptiontype;
+    if (at >= 0 && at < r.nlines) {
+      const double deltaE_absorption = p.e_rf / b.ts_width[nt] / b.delta_freq[nnu_abs] / 4.e12 / PI / PARSEC / PARSEC / b.nprocs * 1.;
+      bin_add(&r.absorption[(cell + nnu_abs) * ioncount + r.line_element[at] * r.max_nions + r.line_ion[at]], deltaE_absorption);
+    }
+  }
+}
+
 // ---- escaped-packet compaction: the escaped packets, in array order, packed for one small D2H -----------
 constexpr int ESC_CHUNK = 256;  // packets per block of the count / scatter kernels
 // `reported` marks packets that an earlier only_new call has already delivered

@@ -180,6 +180,21 @@ class Transport:
                                                    _pd(sto) if stokes else None), "artis_gpu_bin_escaped")
         return lc, flux, sto
 
+    def bin_escaped_resolved(self, tmax, syn_dir, nprocs=1, nnubins=1000):
+        """-> emission, trueemission [ntstep, nnubins, 2 * nel * maxion + 1], absorption [ntstep, nnubins, nel * maxion],
+        lc_res [100, ntstep], flux_res [100, ntstep, nnubins]"""
+        s = self.static
+        ntstep, nel, mi = int(s["ntstep"]), int(s["nelements"]), int(s["max_nions"])
+        em = np.zeros((ntstep, nnubins, 2 * nel * mi + 1))
+        tem = np.zeros_like(em)
+        ab = np.zeros((ntstep, nnubins, nel * mi))
+        lc = np.zeros((100, ntstep))
+        fl = np.zeros((100, ntstep, nnubins))
+        sd = np.ascontiguousarray(syn_dir, np.float64)
+        self._check(self.lib.artis_gpu_bin_escaped_resolved(float(tmax), int(nprocs), int(nnubins), _pd(sd), _pd(em), _pd(tem), _pd(ab),
+                                                            _pd(lc), _pd(fl)), "artis_gpu_bin_escaped_resolved")
+        return em, tem, ab, lc, fl
+
     def download_escaped(self, only_new=False, capacity=None):
         """the escaped packets of the resident ensemble in array order (only_new: not delivered by an earlier only_new call)"""
         cap = self.npkts if capacity is None else capacity

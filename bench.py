@@ -382,7 +382,10 @@ def main():
                 "config": {"workload": wname, "packets_per_gpu": P, "parallelism": f"packets sharded x{world}, grid and "
                            "atomic data replicated, one estimator all-reduce per step",
                            "l2": "per-step working set (304 B x packets + per-cell tables) exceeds the 126 MB L2",
-                           "s_per_timestep": tot_ms / a.steps * 1e-3, "cell_precompute_ms": precompute_ms,
+                           "s_per_timestep": (tot_ms / a.steps + cell_upload_wall_ms) * 1e-3,
+                           "s_per_timestep_parts_ms": {"transport_and_reduce": tot_ms / a.steps, "upload_cellstate_wall": cell_upload_wall_ms,
+                                                       "of_which_table_kernels": precompute_ms},
+                           "cell_precompute_ms": precompute_ms,
                            "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps / world, "handoffs_per_step": float(ctr_sum[50]) / a.steps / world,
                            "drain_ms_to_10pct_1pct_done": [round(float(c[61 + i]) * 1e-6, 1) for i in range(3)],
                            "warp_iters_by_kind": [float(x) / a.steps / world for x in ctr_sum[64:72]],

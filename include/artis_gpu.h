@@ -222,6 +222,20 @@ int artis_gpu_estimator_block(void **dev_ptr, size_t *ndoubles);
  * The frequency grid is init_spectra(nu_min_r, nu_max_r) (spectrum.cc:483-499), float delta_freq included. Sums are
  * accumulated with FP64 atomics, so a bin agrees with the reference's serial sum to rounding (not bit for bit). */
 int artis_gpu_bin_escaped(double tmax, int nprocs, int nnubins, int allreduce, double *lc, double *spec_flux, double *stokes);
+/* The resolved outputs of the same packet loop, for exspec-style products (what tests/setup_classicmode.sh switches on with
+ * WRITE_PARTIAL_EMISSIONABSORPTIONSPEC) -- every resident packet that escaped as an r-packet:
+ *   emission, trueemission  out [ntstep][nnubins][2 * nelements * max_nions + 1]: the angle-averaged spectrum resolved by the
+ *                           process of the last / the true emission (add_to_spec with do_emission_res, spectrum.cc:373-386;
+ *                           columns of columnindex_from_emissiontype, spectrum.cc:306-337: bound-bound per ion, bound-free per
+ *                           ion, free-free)
+ *   absorption              out [ntstep][nnubins][nelements * max_nions]: by the ion of the last line absorption, in the
+ *                           frequency bin of the absorbed photon (spectrum.cc:410-421)
+ *   lc_res                  out [MABINS = 100][ntstep]: light curve of each escape-direction bin (add_to_lc_res with
+ *                           current_abin >= 0, light_curve.cc:55-62; get_escapedirectionbin, vectors.h:158-192)
+ *   flux_res                out [100][ntstep][nnubins]: spectrum of each escape-direction bin (add_to_spec_res, spectrum.cc:616)
+ *   syn_dir                 globals::syn_dir (unit vector to the observer) */
+int artis_gpu_bin_escaped_resolved(double tmax, int nprocs, int nnubins, const double *syn_dir, double *emission, double *trueemission,
+                                   double *absorption, double *lc_res, double *flux_res);
 /* The escaped packets of the resident ensemble, packed in array order into out[0..*n_out): the subset that the host
  * loops over the packet array select with `type == TYPE_ESCAPE` (spectrum.cc:673, exspec.cc, packet.cc:152
  * write_packets), so that a driver with resident packets moves *n_out x 304 bytes instead of npkts x 304.

@@ -327,6 +327,51 @@ void write_spectra(FILE *f, const struct packet *pkts, const int npkts) {
   for (auto &x : sp) free_spectra(x);
 }
 
+// emission / absorption-resolved angle-averaged spectrum (add_to_spec with do_emission_res, spectrum.cc:339-452) and the
+// angle-resolved spectra and light curves of all MABINS escape-direction bins (add_to_spec_res / add_to_lc_res with
+// current_abin >= 0, spectrum.cc:602-620, light_curve.cc:55-62; vectors.h:158-192), by the reference's own functions
+void write_spectra_resolved(FILE *f, const struct packet *pkts, const int npkts) {
+  globals::nnubins = MNUBINS;
+  const int ntstep = globals::ntstep, nnubins = globals::nnubins;
+  const int proccount = 2 * get_nelements() * get_max_nions() + 1, ioncount = get_nelements() * get_max_nions();
+  struct spec *sp = alloc_spectra(true);
+  init_spectra(sp, globals::nu_min_r, globals::nu_max_r, true);
+  std::vector<struct spec *> spa(MABINS);
+  for (auto &x : spa) {
+    x = alloc_spectra(false);
+    init_spectra(x, globals::nu_min_r, globals::nu_max_r, false);
+  }
+  std::vector<double> lcres((size_t)MABINS * ntstep, 0.), lcdummy((size_t)ntstep, 0.);
+  for (int ii = 0; ii < npkts; ii++) {
+    if (pkts[ii].type != TYPE_ESCAPE || pkts[ii].escape_type != TYPE_RPKT) continue;
+    add_to_spec_res(&pkts[ii], -1, sp, nullptr, nullptr, nullptr);
+    for (int a = 0; a < MABINS; a++) {
+      add_to_lc_res(&pkts[ii], a, &lcres[(size_t)a * ntstep], lcdummy.data());
+      add_to_spec_res(&pkts[ii], a, spa[a], nullptr, nullptr, nullptr);
+    }
+  }
+  std::vector<double> em((size_t)ntstep * nnubins * proccount), tem(em.size()), ab((size_t)ntstep * nnubins * ioncount);
+  for (int nt = 0; nt < ntstep; nt++) {
+    memcpy(&em[(size_t)nt * nnubins * proccount], sp->timesteps[nt].emission, sizeof(double) * nnubins * proccount);
+    memcpy(&tem[(size_t)nt * nnubins * proccount], sp->timesteps[nt].trueemission, sizeof(double) * nnubins * proccount);
+    memcpy(&ab[(size_t)nt * nnubins * ioncount], sp->timesteps[nt].absorption, sizeof(double) * nnubins * ioncount);
+  }
+  std::vector<double> fluxres((size_t)MABINS * ntstep * nnubins);
+  for (int a = 0; a < MABINS; a++)
+    for (int nt = 0; nt < ntstep; nt++)
+      memcpy(&fluxres[((size_t)a * ntstep + nt) * nnubins], spa[a]->timesteps[nt].flux, sizeof(double) * nnubins);
+  const double params[6] = {globals::tmax, (double)globals::nprocs, (double)nnubins, globals::syn_dir[0], globals::syn_dir[1],
+                            globals::syn_dir[2]};
+  write_record(f, "spectra.res_params", "f8", params, 6, 8);
+  write_record(f, "spectra.res_emission", "f8", em.data(), em.size(), 8);
+  write_record(f, "spectra.res_trueemission", "f8", tem.data(), tem.size(), 8);
+  write_record(f, "spectra.res_absorption", "f8", ab.data(), ab.size(), 8);
+  write_record(f, "spectra.res_lc", "f8", lcres.data(), lcres.size(), 8);
+  write_record(f, "spectra.res_flux", "f8", fluxres.data(), fluxres.size(), 8);
+  free_spectra(sp);
+  for (auto &x : spa) free_spectra(x);
+}
+
 }  // namespace
 
 void update_packets(const int my_rank, const int nts, struct packet *packets) {
@@ -391,6 +436,7 @@ void update_packets(const int my_rank, const int nts, struct packet *packets) {
     write_estim(f, &E);
     if (!skip_post) write_record(f, "packets.post", "pkt", packets, npkts, sizeof(struct packet));
     if (getenv("ARTIS_HOOK_SPECTRA")) write_spectra(f, packets, npkts);
+    if (getenv("ARTIS_HOOK_SPECTRA_RES")) write_spectra_resolved(f, packets, npkts);
     const double secs[1] = {seconds};
     write_record(f, "meta.ref_seconds", "f8", secs, 1, sizeof(double));
     fclose(f);

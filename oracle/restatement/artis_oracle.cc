@@ -53,6 +53,9 @@ void be_run_pack(const PktHot *hot, const PktCold *cold, ArtisPacket *aos, long 
 void be_run_bin_escaped(const artis::BinSpec &b, const PktHot *hot, const PktCold *cold, long long n) {
   for (long long i = 0; i < n; i++) artis::body_bin_escaped(b, hot, cold, i, b.lc);
 }
+void be_run_bin_resolved(const artis::BinSpec &b, const artis::ResSpec &r, const PktHot *hot, const PktCold *cold, long long n, int *error_flag) {
+  for (long long i = 0; i < n; i++) artis::body_bin_resolved(b, r, hot, cold, i, error_flag);
+}
 void be_run_escaped_count(const PktHot *hot, long long n, const unsigned char *reported, int only_new, int *counts) {
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
   int run = 0;
