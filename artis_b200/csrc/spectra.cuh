@@ -177,6 +177,49 @@ ARTIS_DEV void body_bin_resolved(const BinSpec &b, const ResSpec &r, const PktHo
   }
 }
 
+// ---- estimator normalisation: update_grid.cc:1041-1134 (estimator_normfactor, normalise_J / normalise_nuJ,
+// ffheating / colheating scaling), radfield.cc:1458-1475 get_T_J_from_J, grey_emissivities.cc:124-139 normalise_grey -- per
+// model cell, so that a driver whose packets and estimators stay on the device downloads six numbers per cell
+constexpr double STEBO = 5.670400e-5;            // constants.h:22
+constexpr double ONEOVER4PI = 7.957747153555701e-02;  // constants.h:35
+struct NormSpec {
+  int npts_model, nprocs;
+  double t_mid, tmin, deltat, mintemp, maxtemp;
+  const int *nonemptymgi_of_mgi;   // < 0: no propagation cell maps to this model cell (get_numassociatedcells == 0)
+  const double *vol_init;          // grid::vol_init_modelcell(mgi)
+  const float *TR;                 // the cell's current T_R: get_T_J_from_J falls back to it when J is not finite
+  const double *J, *nuJ, *ff, *col, *rpkt_emiss;  // raw estimators
+  double *out;                     // [npts_model][6]: J, nuJ, ffheating, colheating, rpkt_emiss (all normalised), T_J
+  double *gamma_dep_pathint;       // time_step[nts].gamma_dep_pathint (sum over cells)
+};
+ARTIS_DEV void body_normalise(const NormSpec &n, const int mgi) {
+  double *o = n.out + (size_t)mgi * 6;
+  if (n.nonemptymgi_of_mgi[mgi] < 0) {
+    for (int k = 0; k < 6; k++) o[k] = 0.;
+    return;
+  }
+  const double deltaV = n.vol_init[mgi] * pow(n.t_mid / n.tmin, 3);
+  const double estimator_normfactor = 1 / deltaV / n.deltat / n.nprocs;
+  const double estimator_normfactor_over4pi = ONEOVER4PI * estimator_normfactor;
+  const double J = n.J[mgi] * estimator_normfactor_over4pi;
+  o[0] = J;
+  o[1] = n.nuJ[mgi] * estimator_normfactor_over4pi;
+  o[2] = n.ff[mgi] * estimator_normfactor;
+  o[3] = n.col[mgi] * estimator_normfactor;
+  double T_J = pow(J * PI / STEBO, 1. / 4.);
+  if (!isfinite(T_J)) {
+    T_J = (double)n.TR[mgi];
+  } else if (T_J > n.maxtemp) {
+    T_J = n.maxtemp;
+  } else if (T_J < n.mintemp) {
+    T_J = n.mintemp;
+  }
+  o[5] = T_J;
+  // normalise_grey
+  bin_add(n.gamma_dep_pathint, n.rpkt_emiss[mgi] * 1.e20 / n.nprocs);
+  o[4] = n.rpkt_emiss[mgi] * ONEOVER4PI / deltaV / n.deltat / n.nprocs;
+}
+
 // ---- escaped-packet compaction: the escaped packets, in array order, packed for one small D2H -----------
 constexpr int ESC_CHUNK = 256;  // packets per block of the count / scatter kernels
 // `reported` marks packets that an earlier only_new call has already delivered

@@ -89,6 +89,9 @@ __global__ void __launch_bounds__(256) k_bin_resolved(const artis::BinSpec b, co
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_bin_resolved(b, r, hot, cold, i, error_flag);
 }
+__global__ void k_normalise(const artis::NormSpec n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n.npts_model; i += gridDim.x * blockDim.x) artis::body_normalise(n, i);
+}
 // ABI record <-> device records (common.cuh pkt_split / pkt_join), one thread per packet. The 304-byte host records of a
 // warp are consecutive, so its 16-byte loads sweep 9.5 KB of contiguous memory; the hot lines are written whole.
 __global__ void __launch_bounds__(256) k_unpack(const ArtisPacket *aos, artis::PktHot *hot, artis::PktCold *cold, long long n) {
@@ -1251,6 +1254,9 @@ void be_run_bin_escaped(const artis::BinSpec &b, const PktHot *hot, const PktCol
 }
 void be_run_bin_resolved(const artis::BinSpec &b, const artis::ResSpec &r, const PktHot *hot, const PktCold *cold, long long n, int *error_flag) {
   if (n > 0) k_bin_resolved<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(b, r, hot, cold, n, error_flag);
+}
+void be_run_normalise(const artis::NormSpec &n) {
+  if (n.npts_model > 0) k_normalise<<<grid_for(n.npts_model, 256, 8), 256, 0, g_stream>>>(n);
 }
 // counts must hold n / ESC_CHUNK + 2 ints; afterwards counts[0..nchunks) are the chunks' output offsets, counts[nchunks] the total
 void be_run_escaped_count(const PktHot *hot, long long n, const unsigned char *reported, int only_new, int *counts) {

@@ -164,6 +164,27 @@ class Transport:
         self._check(self.lib.artis_gpu_download_estimators(C.byref(est)), "artis_gpu_download_estimators")
         return d
 
+    def upload_estimators(self, est):
+        """dict of numpy arrays (the names of ArtisEstimators) -> the device-resident estimators"""
+        s = self.static
+        d = dict(est)
+        for k, v in (("npts_model", s["npts_model"]), ("nelements", s["nelements"]), ("max_nions", s["max_nions"]),
+                     ("nlines", s["nlines"]), ("nradfieldbins", 0), ("nbfrate", 0), ("nvstokes", 0), ("nvgrid", 0)):
+            d.setdefault(k, v)
+        st, keep = abi.build_struct(abi.ArtisEstimators, abi.ESTIM_FIELDS, d)
+        self._check(self.lib.artis_gpu_upload_estimators(C.byref(st)), "artis_gpu_upload_estimators")
+
+    def normalise_estimators(self, vol_init_modelcell, nprocs, maxtemp):
+        """-> (cells[npts_model, 6] = J, nuJ, ff, col, rpkt_emiss normalised and T_J; gamma_dep_pathint)"""
+        nm = int(self.static["npts_model"])
+        vol = np.ascontiguousarray(vol_init_modelcell, np.float64)
+        assert vol.size >= nm
+        out = np.zeros((nm, 6))
+        g = np.zeros(1)
+        self._check(self.lib.artis_gpu_normalise_estimators(_pd(vol), int(nprocs), float(maxtemp), _pd(out), _pd(g)),
+                    "artis_gpu_normalise_estimators")
+        return out, float(g[0])
+
     def estimator_block(self):
         ptr = C.c_void_p()
         n = C.c_size_t()

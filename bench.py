@@ -268,6 +268,11 @@ def main():
     T = Transport()
     T.init(st, device=local_rank, rank=rank, nranks=world)
     T.upload_cellstate(cs)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()      # the other per-timestep call of a driver: cell state in, the per-cell tables rebuilt
+    T.upload_cellstate(cs)
+    torch.cuda.synchronize()
+    cell_upload_wall_ms = (time.perf_counter() - t0) * 1e3
     if a.max_events:
         T.set_tuning(max_events_per_pass=a.max_events)
     if os.environ.get("ARTIS_HANG_S"):  # measurement runs of experimental builds: give up a stuck timestep quickly

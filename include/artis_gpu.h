@@ -262,6 +262,23 @@ int artis_gpu_packets_download_escaped(ArtisPacket *out, int capacity, int only_
 int artis_gpu_pack_escaped_noalloc(const ArtisPacket *dev_packets, int npkts, ArtisPacket *dev_out, int capacity,
                                    int *dev_n_out, void *cuda_stream);
 
+/* ---- estimator normalisation on the device ------------------------------------------------- */
+/* What update_grid does to the raw estimators of a timestep before it uses them (update_grid.cc:1041-1134:
+ * estimator_normfactor = 1 / deltaV / deltat / nprocs, radfield::normalise_J / normalise_nuJ with the 1/4pi, the
+ * ffheating / colheating scaling), radfield::get_T_J_from_J (radfield.cc:1458-1475, clamped to [MINTEMP, MAXTEMP], T_R of the
+ * cell if J is not finite) and normalise_grey (grey_emissivities.cc:124-139), for the estimators resident on the device and
+ * the timestep of the last artis_gpu_upload_cellstate:
+ *   vol_init_modelcell  in  [npts_model]  grid::vol_init_modelcell(mgi)       nprocs  globals::nprocs      maxtemp  MAXTEMP
+ *   out_cells           out [npts_model][6]: J, nuJ, ffheatingestimator, colheatingestimator, rpkt_emiss (normalised), T_J;
+ *                       zeros for model cells without propagation cells
+ *   gamma_dep_pathint   out time_step[nts].gamma_dep_pathint
+ * The device estimators themselves are left raw (the all-reduce and artis_gpu_download_estimators still see them). */
+int artis_gpu_normalise_estimators(const double *vol_init_modelcell, int nprocs, double maxtemp, double *out_cells,
+                                   double *gamma_dep_pathint);
+/* The inverse of artis_gpu_download_estimators for the FP64 arrays and the counters (restart of a driver whose
+ * estimators live on the device); NULL members are left as they are on the device. */
+int artis_gpu_upload_estimators(const ArtisEstimators *est);
+
 /* ---- packet files from the resident ensemble ------------------------------------------------ */
 /* The driver's packet checkpoint and final packet file, written from / read into the resident ensemble a bounded chunk at
  * a time (a driver that keeps its packets on the device between timesteps never needs the whole array on the host):

@@ -26,6 +26,8 @@
 #include "boundary.h"
 #include "ltepop.h"
 #include "photo_electric.h"
+#include "grey_emissivities.h"
+#include "radfield.h"
 #include "ratecoeff.h"
 #include "rpkt.h"
 #include "update_grid.h"
@@ -437,6 +439,41 @@ void update_packets(const int my_rank, const int nts, struct packet *packets) {
     if (!skip_post) write_record(f, "packets.post", "pkt", packets, npkts, sizeof(struct packet));
     if (getenv("ARTIS_HOOK_SPECTRA")) write_spectra(f, packets, npkts);
     if (getenv("ARTIS_HOOK_SPECTRA_RES")) write_spectra_resolved(f, packets, npkts);
+    if (getenv("ARTIS_HOOK_NORMALISE")) {
+      // what update_grid makes of the raw estimators at the start of the next timestep (update_grid.cc:1041-1134) and
+      // normalise_grey (grey_emissivities.cc:124-139), by the reference's own functions. Destructive: combine with
+      // ARTIS_HOOK_STOP_AFTER_TS.
+      const int nm = grid::get_npts_model();
+      std::vector<double> vol(nm, 0.), nJ(nm, 0.), nnuJ(nm, 0.), nff(nm, 0.), ncol(nm, 0.), nre(nm, 0.), nTJ(nm, 0.);
+      const double deltat = globals::time_step[nts].width;
+      for (int mgi = 0; mgi < nm; mgi++) {
+        vol[mgi] = grid::vol_init_modelcell(mgi);
+        if (grid::get_numassociatedcells(mgi) <= 0) continue;
+        const double deltaV = grid::vol_init_modelcell(mgi) * pow(globals::time_step[nts].mid / globals::tmin, 3);
+        const double estimator_normfactor = 1 / deltaV / deltat / globals::nprocs;
+        const double estimator_normfactor_over4pi = ONEOVER4PI * estimator_normfactor;
+        radfield::normalise_J(mgi, estimator_normfactor_over4pi);
+        nTJ[mgi] = radfield::get_T_J_from_J(mgi);
+        radfield::normalise_nuJ(mgi, estimator_normfactor_over4pi);
+        globals::ffheatingestimator[mgi] *= estimator_normfactor;
+        globals::colheatingestimator[mgi] *= estimator_normfactor;
+        nJ[mgi] = refglue::radfield_J()[mgi];
+        nnuJ[mgi] = refglue::radfield_nuJ()[mgi];
+        nff[mgi] = globals::ffheatingestimator[mgi];
+        ncol[mgi] = globals::colheatingestimator[mgi];
+      }
+      normalise_grey(nts);
+      for (int mgi = 0; mgi < nm; mgi++) nre[mgi] = globals::rpkt_emiss[mgi];
+      const double scal[4] = {globals::time_step[nts].gamma_dep_pathint, (double)globals::nprocs, MINTEMP, MAXTEMP};
+      write_record(f, "norm.vol_init", "f8", vol.data(), nm, 8);
+      write_record(f, "norm.J", "f8", nJ.data(), nm, 8);
+      write_record(f, "norm.nuJ", "f8", nnuJ.data(), nm, 8);
+      write_record(f, "norm.ff", "f8", nff.data(), nm, 8);
+      write_record(f, "norm.col", "f8", ncol.data(), nm, 8);
+      write_record(f, "norm.rpkt_emiss", "f8", nre.data(), nm, 8);
+      write_record(f, "norm.TJ", "f8", nTJ.data(), nm, 8);
+      write_record(f, "norm.scalars", "f8", scal, 4, 8);
+    }
     const double secs[1] = {seconds};
     write_record(f, "meta.ref_seconds", "f8", secs, 1, sizeof(double));
     fclose(f);

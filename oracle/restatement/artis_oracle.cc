@@ -56,6 +56,9 @@ void be_run_bin_escaped(const artis::BinSpec &b, const PktHot *hot, const PktCol
 void be_run_bin_resolved(const artis::BinSpec &b, const artis::ResSpec &r, const PktHot *hot, const PktCold *cold, long long n, int *error_flag) {
   for (long long i = 0; i < n; i++) artis::body_bin_resolved(b, r, hot, cold, i, error_flag);
 }
+void be_run_normalise(const artis::NormSpec &n) {
+  for (int i = 0; i < n.npts_model; i++) artis::body_normalise(n, i);
+}
 void be_run_escaped_count(const PktHot *hot, long long n, const unsigned char *reported, int only_new, int *counts) {
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
   int run = 0;
