@@ -397,7 +397,8 @@ ARTIS_DEV void build_corrphoto(const Ctx &c, const int mgi, const int i) {
 }
 
 // macroatom.cc:57-159 calculate_macroatom_transitionrates for one (cell, level)
-ARTIS_DEV void build_ma_level(const Ctx &c, const int mgi, const int gl, const double t_mid) {
+ARTIS_DEV void build_ma_level_into(const Ctx &c, const int mgi, const int gl, const double t_mid, double *out,
+                                   double *cum_rad, double *cum_down, double *cum_up) {
   const int tc = tabcell(c, mgi);
   const int ui = c.lev_uion[gl];
   const int gl0 = c.st.ion_leveloffset[ui];
@@ -410,8 +411,6 @@ ARTIS_DEV void build_ma_level(const Ctx &c, const int mgi, const int gl, const d
   for (int a = 0; a < MA_ACTION_COUNT; a++) pr[a] = 0.;
 
   const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
-  double *cum_rad = c.tb.ma_cum_raddeexc + (size_t)tc * c.st.ndowntrans_total + doff;
-  double *cum_down = c.tb.ma_cum_intdown + (size_t)tc * c.st.ndowntrans_total + doff;
   for (int i = 0; i < ndown; i++) {
     const int lineindex = c.st.downtrans_lineindex[doff + i];
     const int gll = c.line_lower_g[lineindex];
@@ -443,7 +442,6 @@ ARTIS_DEV void build_ma_level(const Ctx &c, const int mgi, const int gl, const d
   }
 
   const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
-  double *cum_up = c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + uoff;
   for (int i = 0; i < nup; i++) {
     const int lineindex = c.st.uptrans_lineindex[uoff + i];
     const int glu = c.line_upper_g[lineindex];
@@ -466,13 +464,21 @@ ARTIS_DEV void build_ma_level(const Ctx &c, const int mgi, const int gl, const d
       pr[MA_INTERNALUPHIGHER] += (R + C) * epsilon_current;
     }
   }
-  double *out = c.tb.ma_rates + ((size_t)tc * c.st.nlevels_total + gl) * MA_ACTION_COUNT;
   for (int a = 0; a < MA_ACTION_COUNT; a++) out[a] = pr[a];
+}
+// the dense tables (one row per level of every cell, built by the cell_precompute kernels)
+ARTIS_DEV void build_ma_level(const Ctx &c, const int mgi, const int gl, const double t_mid) {
+  const size_t tc = (size_t)tabcell(c, mgi);
+  const int doff = c.st.lev_downoffset[gl], uoff = c.st.lev_upoffset[gl];
+  build_ma_level_into(c, mgi, gl, t_mid, c.tb.ma_rates + (tc * c.st.nlevels_total + gl) * MA_ACTION_COUNT,
+                      c.tb.ma_cum_raddeexc + tc * c.st.ndowntrans_total + doff,
+                      c.tb.ma_cum_intdown + tc * c.st.ndowntrans_total + doff, c.tb.ma_cum_intup + tc * c.st.nuptrans_total + uoff);
 }
 
 // kpkt.cc:167-308 calculate_kpkt_rates_ion for one (cell, ion); `oldcoolingsum` = sum of cooling_contrib_ion of the
 // ions before this one in (element, ion) order, accumulated like the selection loop of do_kpkt (kpkt.cc:527-536)
-ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
+// `cool` is indexed with the global cooling-term index, `cexc` with the global upward-transition index
+ARTIS_DEV void build_cooling_ion_into(const Ctx &c, const int mgi, const int ui, double *cool, double *cexc) {
   const int tc = tabcell(c, mgi);
   const int element = c.uion_element[ui];
   const float nne = c.cs.nne[mgi];
@@ -481,8 +487,6 @@ ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
   for (int u = 0; u < ui; u++) oldcoolingsum += c.cs.cooling_contrib_ion[(size_t)mgi * c.st.includedions + u];
   double contrib = oldcoolingsum;
   int i = c.st.ion_coolingoffset[ui];
-  double *cool = c.tb.cool_cum + (size_t)tc * c.st.ncoolingterms;
-  double *cexc = c.tb.collexc_cum + (size_t)tc * c.st.nuptrans_total;
   const int gl0 = c.st.ion_leveloffset[ui];
   const int nlevels = c.st.ion_nlevels[ui];
   const int ionisinglevels = c.st.ion_ionisinglevels[ui];
@@ -530,6 +534,124 @@ ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
   // fill the tail when levels >= ionisinglevels own (uncomputed) list slots: the reference leaves them untouched
   // and asserts i == offset + ncoolingterms (kpkt.cc:300); here a mismatch is reported as a fatal table error
   if (i != c.st.ion_coolingoffset[ui] + c.st.ion_ncoolingterms[ui]) fatal(c, 202);
+}
+ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
+  const size_t tc = (size_t)tabcell(c, mgi);
+  build_cooling_ion_into(c, mgi, ui, c.tb.cool_cum + tc * c.st.ncoolingterms, c.tb.collexc_cum + tc * c.st.nuptrans_total);
+}
+
+// ---- rows on demand ----------------------------------------------------------------------------------------------------
+// Upward transitions of an ion's levels are one contiguous range of the uptrans arrays (checked at init, engine.inc).
+ARTIS_DEV int ion_upfirst(const Ctx &c, const int ui) { return c.st.lev_upoffset[c.st.ion_leveloffset[ui]]; }
+ARTIS_DEV int ion_upcount(const Ctx &c, const int ui) {
+  const int last = c.st.ion_leveloffset[ui] + c.st.ion_nlevels[ui] - 1;
+  return c.st.lev_upoffset[last] + c.st.lev_nuptrans[last] - ion_upfirst(c, ui);
+}
+// doubles in the row of level gl: process rates | running rad. de-excitation | running internal down | running internal up
+ARTIS_DEV int ma_row_doubles(const Ctx &c, const int gl) {
+  return MA_ACTION_COUNT + 2 * c.st.lev_ndowntrans[gl] + c.st.lev_nuptrans[gl];
+}
+ARTIS_DEV int cool_row_doubles(const Ctx &c, const int ui) { return c.st.ion_ncoolingterms[ui] + ion_upcount(c, ui); }
+
+// The row `key` (level gl, or nlevels_total + ion) of table cell tc: where it is if some event has built it already, else
+// built here by the calling thread and published with one compare-and-swap. Two threads that miss at the same time both
+// build (the values are identical: same inputs, same arithmetic) and the loser's copy is wasted arena space; nobody ever
+// waits for anybody. Out of line: the builders are the cell_precompute code, not the event loop's.
+ARTIS_DEV_NOINLINE const double *row_get(const Ctx &c, const int mgi, const int tc, const int key) {
+  const CellTables &tb = c.tb;
+  unsigned *slot = tb.row_ptr + (size_t)tc * (c.st.nlevels_total + c.st.includedions) + key;
+#ifdef __CUDA_ARCH__
+  unsigned have = __ldcg(slot);
+#else
+  unsigned have = *slot;
+#endif
+  if (have != 0u) return tb.row_arena + (size_t)(have - 1u) * 16;
+  const bool is_level = key < c.st.nlevels_total;
+  const int ui = key - c.st.nlevels_total;
+  const int ndoubles = is_level ? ma_row_doubles(c, key) : cool_row_doubles(c, ui);
+  const unsigned long long units = (unsigned long long)(ndoubles + 15) / 16;
+#ifdef __CUDA_ARCH__
+  const unsigned long long at = atomicAdd(tb.row_top, units);
+#else
+  // host build (one thread, and no caller holds a row while it asks for another): a full arena is started afresh on the spot
+  if (*tb.row_top + units > tb.row_soft && *tb.row_top > 0) {
+    const size_t slots = (size_t)tb.ncells * (c.st.nlevels_total + c.st.includedions);
+    for (size_t i = 0; i < slots; i++) tb.row_ptr[i] = 0u;
+    *tb.row_top = 0;
+    *tb.row_stop += 1;  // counted by the engine
+    slot = tb.row_ptr + (size_t)tc * (c.st.nlevels_total + c.st.includedions) + key;
+  }
+  const unsigned long long at = *tb.row_top;
+  *tb.row_top += units;
+#endif
+#ifdef __CUDA_ARCH__
+  if (at + units > tb.row_soft) *reinterpret_cast<volatile int *>(tb.row_stop) = 1;
+#endif
+  if (at + units > tb.row_cap) {  // the reserve above row_soft is sized so that this cannot happen (engine.inc)
+    fatal(c, 240);
+    return tb.row_arena;
+  }
+  double *row = tb.row_arena + (size_t)at * 16;
+  if (is_level) {
+    const int nd = c.st.lev_ndowntrans[key];
+    build_ma_level_into(c, mgi, key, c.t_mid, row, row + MA_ACTION_COUNT, row + MA_ACTION_COUNT + nd,
+                        row + MA_ACTION_COUNT + 2 * nd);
+  } else {
+    const int ncool = c.st.ion_ncoolingterms[ui];
+    build_cooling_ion_into(c, mgi, ui, row - c.st.ion_coolingoffset[ui], row + ncool - ion_upfirst(c, ui));
+  }
+#ifdef __CUDA_ARCH__
+  __threadfence();
+  const unsigned prev = atomicCAS(slot, 0u, (unsigned)at + 1u);
+  if (prev != 0u) return tb.row_arena + (size_t)(prev - 1u) * 16;
+#else
+  *slot = (unsigned)at + 1u;
+#endif
+  return row;
+}
+
+struct MaRow {
+  const double *pr;        // [MA_ACTION_COUNT]
+  const double *cum_rad;   // [lev_ndowntrans]
+  const double *cum_down;  // [lev_ndowntrans]
+  const double *cum_up;    // [lev_nuptrans]
+};
+ARTIS_DEV MaRow ma_row(const Ctx &c, const int mgi, const int tc, const int gl) {
+  MaRow r;
+  if (c.tb.row_ptr != nullptr) {
+    const double *row = row_get(c, mgi, tc, gl);
+    const int nd = c.st.lev_ndowntrans[gl];
+    r.pr = row;
+    r.cum_rad = row + MA_ACTION_COUNT;
+    r.cum_down = row + MA_ACTION_COUNT + nd;
+    r.cum_up = row + MA_ACTION_COUNT + 2 * nd;
+  } else {
+    const int doff = c.st.lev_downoffset[gl], uoff = c.st.lev_upoffset[gl];
+    r.pr = tab_ma_rates(c, tc, gl);
+    r.cum_rad = c.tb.ma_cum_raddeexc + (size_t)tc * c.st.ndowntrans_total + doff;
+    r.cum_down = c.tb.ma_cum_intdown + (size_t)tc * c.st.ndowntrans_total + doff;
+    r.cum_up = c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + uoff;
+  }
+  return r;
+}
+ARTIS_DEV const double *ma_rates_row(const Ctx &c, const int mgi, const int tc, const int gl) {
+  return c.tb.row_ptr != nullptr ? row_get(c, mgi, tc, gl) : tab_ma_rates(c, tc, gl);
+}
+struct CoolRow {
+  const double *cool;  // indexed with the global cooling-term index (ion_coolingoffset[ui] ...)
+  const double *cexc;  // indexed with the global upward-transition index (lev_upoffset[...] ...)
+};
+ARTIS_DEV CoolRow cool_row(const Ctx &c, const int mgi, const int tc, const int ui) {
+  CoolRow r;
+  if (c.tb.row_ptr != nullptr) {
+    const double *row = row_get(c, mgi, tc, c.st.nlevels_total + ui);
+    r.cool = row - c.st.ion_coolingoffset[ui];
+    r.cexc = row + c.st.ion_ncoolingterms[ui] - ion_upfirst(c, ui);
+  } else {
+    r.cool = c.tb.cool_cum + (size_t)tc * c.st.ncoolingterms;
+    r.cexc = c.tb.collexc_cum + (size_t)tc * c.st.nuptrans_total;
+  }
+  return r;
 }
 
 }  // namespace artis

@@ -302,6 +302,16 @@ struct CellTables {
   // [ncells][nbfcontinua], NO_LUT_PHOTOION builds only: get_corrphotoioncoeff (ratecoeff.cc:1247) of allcont[i], i.e.
   // the bf-rate estimator of the previous timestep or the integral over the radiation field model
   double *corrphoto;
+  // ---- rows on demand (large 3-D models: the five macro-atom / cooling arrays above would be ~1.5 MB per cell) ----
+  // row_ptr != nullptr: ma_rates, ma_cum_*, cool_cum and collexc_cum are nullptr; the row of a (cell, level) or of a
+  // (cell, ion) is built by the first event that needs it (celltables.cuh row_get: the analogue of cellhistory,
+  // macroatom.cc:161-172, kpkt.cc:167-308) in a bounded arena, 128 bytes at a time so that no two rows share a cache line.
+  unsigned *row_ptr;              // [ncells][nlevels_total + includedions]: 0 = not built, else 1 + offset in 128-byte units
+  double *row_arena;              // [row_cap * 16]
+  unsigned long long *row_top;    // units of 128 bytes handed out so far (device counter)
+  unsigned long long row_cap;     // units the arena holds
+  unsigned long long row_soft;    // above this fill the scheduler drains and the host starts the arena afresh
+  int *row_stop;                  // set when row_top has passed row_soft
 };
 
 struct Ctx {

@@ -227,14 +227,14 @@ ARTIS_DEV void body_probe_get_event(const Ctx &c, const ArtisPacket *pkts, const
 ARTIS_DEV void body_probe_ma_rates(const Ctx &c, const int *mgi, const int *element, const int *ion, const int *level,
                                    const int idx, double *rates) {
   const int gl = glevel_of(c, element[idx], ion[idx], level[idx]);
-  const double *pr = tab_ma_rates(c, tabcell(c, mgi[idx]), gl);
+  const double *pr = ma_rates_row(c, mgi[idx], tabcell(c, mgi[idx]), gl);
   for (int a = 0; a < MA_ACTION_COUNT; a++) rates[idx * MA_ACTION_COUNT + a] = pr[a];
 }
 ARTIS_DEV void body_probe_cooling(const Ctx &c, const int *mgi, const int *element, const int *ion, const int idx,
                                   double *contrib_total) {
   const int ui = uion_of(c, element[idx], ion[idx]);
   const int last = c.st.ion_coolingoffset[ui] + c.st.ion_ncoolingterms[ui] - 1;
-  contrib_total[idx] = c.tb.cool_cum[(size_t)tabcell(c, mgi[idx]) * c.st.ncoolingterms + last];
+  contrib_total[idx] = cool_row(c, mgi[idx], tabcell(c, mgi[idx]), ui).cool[last];
 }
 ARTIS_DEV void body_probe_gamma_kappa(const Ctx &c, const ArtisPacket *pkts, const int idx, double *kap) {
   ProbePkt w;

@@ -98,7 +98,8 @@ ARTIS_DEV void do_kpkt_body(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tal
   }
   const int ilow = c.st.ion_coolingoffset[ui];
   const int ihigh = ilow + c.st.ion_ncoolingterms[ui] - 1;
-  const double *cool = c.tb.cool_cum + (size_t)tc * c.st.ncoolingterms;
+  const CoolRow crow = cool_row(c, mgi, tc, ui);
+  const double *cool = crow.cool;
   int i = lower_bound_idx(cool, ilow, ihigh, rndcool);
   tl.cool_scanned += bsearch_probes(ihigh - ilow + 1) + ui + 1;  // list probes + ion totals scanned
   if (i > ihigh) {  // assert_always(i <= ihigh) in the reference
@@ -144,7 +145,7 @@ ARTIS_DEV void do_kpkt_body(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tal
     const int level = c.st.cool_level[i];
     const int gl = c.st.ion_leveloffset[ui] + level;
     const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
-    const double *cexc = c.tb.collexc_cum + (size_t)tc * c.st.nuptrans_total;
+    const double *cexc = crow.cexc;
     const int ii = lower_bound_idx(cexc, uoff, uoff + nup - 1, rndcool);
     if (ii >= uoff + nup) {  // "WARNING: Could not select an upper level" + abort
       fatal(c, 305);

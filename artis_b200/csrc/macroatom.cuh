@@ -167,7 +167,8 @@ ARTIS_DEV int ma_jump(const Ctx &c, P &p, Rng &rng, Tally &tl, int *sel_out) {
   const int ui = uion_of(c, p.ma_element, p.ma_ion);
   const int gl = c.st.ion_leveloffset[ui] + p.ma_level;
   tl.ma_jumps++;
-  const double *processrates = tab_ma_rates(c, tc, gl);
+  const MaRow row = ma_row(c, mgi, tc, gl);
+  const double *processrates = row.pr;
   double pr[MA_ACTION_COUNT];
   double total_transitions = 0.;
   for (int a = 0; a < MA_ACTION_COUNT; a++) {
@@ -195,11 +196,11 @@ ARTIS_DEV int ma_jump(const Ctx &c, P &p, Rng &rng, Tally &tl, int *sel_out) {
   if (selected_action == MA_RADDEEXC || selected_action == MA_INTERNALDOWNSAME) {
     ntrans = c.st.lev_ndowntrans[gl];
     toff = c.st.lev_downoffset[gl];
-    cum = (selected_action == MA_RADDEEXC ? c.tb.ma_cum_raddeexc : c.tb.ma_cum_intdown) + (size_t)tc * c.st.ndowntrans_total + toff;
+    cum = selected_action == MA_RADDEEXC ? row.cum_rad : row.cum_down;
   } else if (selected_action == MA_INTERNALUPSAME) {
     ntrans = c.st.lev_nuptrans[gl];
     toff = c.st.lev_upoffset[gl];
-    cum = c.tb.ma_cum_intup + (size_t)tc * c.st.nuptrans_total + toff;
+    cum = row.cum_up;
   }
   if (cum == nullptr) return selected_action;
   const double zrand = rng_uniform(rng);
@@ -234,7 +235,7 @@ ARTIS_DEV void ma_event_body(const Ctx &c, Pkt &p, const int action, const int s
   const int activatingline = p.ma_activatingline;
   const int level = p.ma_level;
   const double epsilon_current = c.st.lev_epsilon[gl];
-  const double pr_sel = tab_ma_rates(c, tabcell(c, mgi), gl)[action < MA_ACTION_COUNT ? action : 0];
+  const double pr_sel = ma_rates_row(c, mgi, tabcell(c, mgi), gl)[action < MA_ACTION_COUNT ? action : 0];
   bool end_packet = false;
   switch (action) {
     case MA_RADDEEXC: {  // macroatom.cc:222-296

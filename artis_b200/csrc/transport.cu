@@ -594,6 +594,16 @@ __device__ __forceinline__ void coop_bfest_flush(const artis::Ctx &c, artis::Kap
   k.bfest_factor = 0.;
 }
 
+// rows on demand (celltables.cuh row_get): true once the row arena has passed its soft limit. The warps then put the
+// packets they hold back into the hot array and leave; the host forgets the rows and launches the scheduler again on the
+// packets that have not finished (engine.inc artis_gpu_transport_resident). Warp-uniform.
+__device__ __forceinline__ bool row_arena_stop(const artis::Ctx &c, const int lane) {
+  if (c.tb.row_ptr == nullptr) return false;
+  int stop = 0;
+  if (lane == 0) stop = *reinterpret_cast<volatile int *>(c.tb.row_stop);
+  return __shfl_sync(0xffffffffu, stop, 0) != 0;
+}
+
 // ROLES: bit mask of the kinds the warps of this kernel may take up
 template <unsigned ROLES>
 __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persistent(PktHot *hot, PktCold *cold, PersistView pv, long long max_events,
@@ -632,6 +642,10 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
   long long cyc_kind = 0, cyc_refill = 0, cyc_push = 0, cyc_idle = 0;
   while (true) {
     __syncwarp(full);
+    if (row_arena_stop(c, lane)) {
+      if (have) pkt_store_cg(hot + idx, p, rng);
+      break;
+    }
     const long long tick0 = clock64();
     const unsigned need = __ballot_sync(full, !have);
     if (need != full && refill_skip > 0) {
@@ -852,6 +866,15 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_light(P
   if (ARTIS_KAPPA_OFFLOAD != 0) kappa_stage_init(ks);
   while (true) {
     __syncwarp(full);
+    if (row_arena_stop(c, lane)) {
+      if (have && role == KIND_MAJUMP) {
+        __stcg(&hot[idx].ma_el_ion, pkt_pack2(v.ma_element, v.ma_ion));
+        __stcg(&hot[idx].ma_level, v.ma_level);
+        __stcg(&hot[idx].interactions, v.interactions);
+        __stcg(&hot[idx].rngctr, (unsigned)rng.ctr);
+      }
+      break;
+    }
     const unsigned tick0 = (unsigned)clock();
     const unsigned need = __ballot_sync(full, !have);
     if (need != full && refill_skip > 0) {
@@ -1352,6 +1375,11 @@ void be_set_scheduler_kernels(int n) {
   if (n == 1 || (n == 2 && g_blocks_jump >= 1)) g_scheduler_kernels = n;
 }
 int be_persistent_kernels() { return g_scheduler_kernels == 2 ? 2 : 1; }
+// threads the scheduler keeps resident (bound of the rows that can be under construction at once)
+long long be_resident_lanes() {
+  const int per_sm = g_blocks_all > g_blocks_heavy + g_blocks_jump ? g_blocks_all : g_blocks_heavy + g_blocks_jump;
+  return (long long)g_sms * per_sm * 128;
+}
 int be_scheduler_geometry(int *out) {  // kernels, blocks per SM of: single kernel, big kernel, jump kernel
   out[0] = g_scheduler_kernels;
   out[1] = g_blocks_all;

@@ -39,6 +39,7 @@ REF_EXE = os.path.join(REPO, "oracle", "_ref", "classic", "sn3d_ref")
 WORKLOAD_NAME = ("classicmode W7-like 1D model (tests/classicmode_inputfiles, artisoptions_classic.h, 100^3 grid), "
                  "synthetic atomic data {nlines} lines / {nbf} bf continua / {nlev} levels, timestep {ts}")
 FIXTURE = None  # --workload fixture: a committed golden fixture instead of the named workload (smoke runs only)
+MODEL3D = False  # --workload 3d: BASELINE.json config 4, the classic workload promoted to one model cell per propagation cell
 
 
 def select_workload(name):
@@ -47,8 +48,17 @@ def select_workload(name):
     default stays the classic-mode model, whose timestep is the interaction-rich one the metric is about.
     --workload fixture: the 16^3-grid parity fixture tests/golden/classic_nogrey_ts12.npz; never the default, and its
     line says what it is (it has no reference arm)."""
-    global BENCH_RUN, BENCH_TS, REF_EXE, WORKLOAD_NAME, FIXTURE
-    if name == "nebular":
+    global BENCH_RUN, BENCH_TS, REF_EXE, WORKLOAD_NAME, FIXTURE, MODEL3D
+    if name == "3d":
+        # BASELINE.json config 4 (SURVEY 8d S4): tools/model3d.py promote() of the classic workload -- the state of the
+        # classic run's timestep sampled onto a 3-D model with one model cell per non-empty propagation cell (5.2e5 of
+        # them), 1.25e7 packets per GPU spread over the sphere. The reference arm of this workload is the classic 1-D-model
+        # run it is promoted from (same physics per packet; the reference on the promoted model is hours of host update_grid).
+        MODEL3D = True
+        WORKLOAD_NAME = ("config 4: 3-D model, one model cell per non-empty cell of the 100^3 grid, promoted (tools/model3d.py) "
+                         "from the " + WORKLOAD_NAME)
+        os.environ.setdefault("ARTIS_ROW_ARENA_MB", "65536")
+    elif name == "nebular":
         BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_neb")
         BENCH_TS = 8
         REF_EXE = os.path.join(REPO, "oracle", "_ref", "nebular", "sn3d_ref")
@@ -79,6 +89,11 @@ def load_workload():
     s = snapshot.load(snap)
     st, cs = snapshot.static_tables(s), snapshot.cell_state(s)
     name = WORKLOAD_NAME.format(nlines=st["nlines"], nbf=st["nbfcontinua"], nlev=st["nlevels_total"], ts=BENCH_TS)
+    if MODEL3D:
+        sys.path.insert(0, os.path.join(REPO, "tools"))
+        import model3d
+        st, cs, _ = model3d.promote(st, cs)
+        name += f"; {int(st['npts_model'])} model cells"
     return st, cs, s["packets.pre"].copy(), name
 
 
@@ -88,7 +103,7 @@ def workload_key(name, packets):
     return hashlib.sha1(f"{name}|{int(packets)}".encode()).hexdigest()[:16]
 
 
-def replicate(pre, P, rank, step):
+def replicate(pre, P, rank, step, static=None):
     """P statistically identical packets: the snapshot's packets tiled, each copy with its own packet.number (its
     Philox stream) and with energies scaled so that the total energy is that of the snapshot (packet.cc:106-108)."""
     reps = -(-P // pre.size)
@@ -98,6 +113,9 @@ def replicate(pre, P, rank, step):
         out[f] *= scale
     base = (step * 8 + rank) * P
     out["number"] = (np.arange(P, dtype=np.int64) + base).astype(np.int32)
+    if MODEL3D and static is not None:  # the copies of a packet go to different places of the (spherically symmetric) model
+        import model3d
+        model3d.rotate_copies(out, pre.size, static, seed=20240607 + step * 8 + rank)
     return out
 
 
@@ -220,15 +238,17 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--packets", type=int, default=1000000, help="packets per GPU")
+    ap.add_argument("--packets", type=int, default=0, help="packets per GPU (default 1e6; 1.25e7 for --workload 3d)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-baseline", default="auto", choices=["auto", "off"])
     ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
     ap.add_argument("--scheduler-kernels", type=int, default=0, choices=(0, 1, 2),
                     help="1: one persistent kernel with every role, 2: macro-atom jump kernel + every-other-role kernel (0: library default)")
-    ap.add_argument("--workload", default="classic", choices=["classic", "nebular", "fixture"])
+    ap.add_argument("--workload", default="classic", choices=["classic", "nebular", "fixture", "3d"])
     a = ap.parse_args()
     select_workload(a.workload)
+    if a.packets <= 0:
+        a.packets = 12500000 if a.workload == "3d" else 1000000
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -244,6 +264,8 @@ def main():
             res = run_port(st, cs, pre, cores, max(1, a.steps), min(a.warmup, 1))
             kind = "port"
         inter, sec, sample = res
+        if MODEL3D:
+            sample += "; the 1-D-model run the 3-D workload is promoted from"
         v = inter / sec
         line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": 1e3 * sec / max(1, a.steps), "higher_is_better": True, "scaling": "weak",
@@ -302,7 +324,7 @@ def main():
 
     def one_step(step, timed):
         """device-resident step: returns (device ms of transport [+ all-reduce], interactions of this rank)"""
-        pk = replicate(pre, P, rank, step)
+        pk = replicate(pre, P, rank, step, st)
         T.packets_upload(pk)  # untimed: inputs are resident in HBM when the timed region starts
         T.zero_estimators()
         barrier()
@@ -349,7 +371,7 @@ def main():
     # end-to-end through the C ABI with host buffers
     e2e_sec, e2e_inter = 0.0, 0.0
     for s in range(max(1, min(a.steps, 3)) + 1):
-        host_pk[:] = replicate(pre, P, rank, 2000 + s)
+        host_pk[:] = replicate(pre, P, rank, 2000 + s, st)
         T.zero_estimators()
         barrier()
         t0 = time.perf_counter()
@@ -391,7 +413,12 @@ def main():
                            "s_per_timestep_parts_ms": {"transport_and_reduce": tot_ms / a.steps, "upload_cellstate_wall": cell_upload_wall_ms,
                                                        "of_which_table_kernels": precompute_ms},
                            "cell_precompute_ms": precompute_ms,
-                           "table_bytes": T.table_bytes(), "passes_per_step": float(ctr_sum[46]) / a.steps / world, "handoffs_per_step": float(ctr_sum[50]) / a.steps / world,
+                           "table_bytes": T.table_bytes(),
+                           "rows_on_demand": ({"arena_restarts_per_step": float(ctr_sum[91]) / a.steps / world,
+                                               "row_bytes_built_per_step": 128.0 * float(ctr_sum[92]) / a.steps / world}
+                                              if ctr_sum[92] > 0 else None),
+                           "estimator_block_bytes": int(ndoubles) * 8,
+                           "passes_per_step": float(ctr_sum[46]) / a.steps / world, "handoffs_per_step": float(ctr_sum[50]) / a.steps / world,
                            "drain_ms_to_10pct_1pct_done": [round(float(c[61 + i]) * 1e-6, 1) for i in range(3)],
                            "warp_iters_by_kind": [float(x) / a.steps / world for x in ctr_sum[64:72]],
                            "mean_busy_lanes_by_kind": [round(float(ctr_sum[72 + i]) / max(float(ctr_sum[64 + i]), 1.0), 2) for i in range(8)],
@@ -418,10 +445,14 @@ def main():
             cores = host_cores()
             res = run_reference(cores, 1, 1)
             kind = "reference"
+            if res is None and MODEL3D:
+                raise SystemExit("bench.py --workload 3d: oracle/_ref (the reference build and its run) is missing")
             if res is None:
                 res = run_port(st, cs, pre, cores, 1, 0)
                 kind = "port"
             inter, sec, sample = res
+            if MODEL3D:
+                sample += "; the 1-D-model run the 3-D workload is promoted from"
             line["cpu_baseline"] = {"value": inter / sec, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
         print(json.dumps(line))
     if world > 1:

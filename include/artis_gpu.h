@@ -153,6 +153,8 @@ enum {
   ARTIS_CTR_REFILL_CYCLES = 88,   /* ... claiming ring entries and loading packets */
   ARTIS_CTR_PUSH_CYCLES = 89,     /* ... storing packets and pushing them on the ring of their next kind */
   ARTIS_CTR_IDLE_CYCLES = 90,     /* ... waiting with every ring of their roles empty */
+  ARTIS_CTR_ROW_FLUSHES = 91,     /* rows-on-demand tables: times the row arena was started afresh in the last transport */
+  ARTIS_CTR_ROW_UNITS = 92,       /* ... 128-byte units of rows built in the last transport (all arena generations) */
   ARTIS_CTR_COUNT = 96
 };
 

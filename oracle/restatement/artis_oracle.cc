@@ -98,6 +98,7 @@ void be_run_wavefront(PktHot *hot, PktCold *cold, const artis::QueueView &qv, in
 bool be_run_persistent(PktHot *, PktCold *, int *, int, unsigned long long *, unsigned long long *, int, long long) { return false; }
 int be_persistent_kernels() { return 0; }
 int be_scheduler_geometry(int *) { return 0; }
+long long be_resident_lanes() { return 1; }
 void be_fill_bytes(void *p, int byte, size_t n) { memset(p, byte, n); }
 void be_set_estimator_block(double *, size_t) {}
 void be_set_scheduler_kernels(int) {}

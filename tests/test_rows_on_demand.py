@@ -1,0 +1,158 @@
+"""Rows on demand (CellTables.row_ptr, celltables.cuh row_get): the macro-atom and cooling rows of a (cell, level) / (cell, ion)
+built by the first event that needs them in a bounded arena, instead of every row of every cell by cell_precompute -- what
+a 1e6-cell model (BASELINE.json config 4) needs: the dense rows are ~1.5 MB per cell. The reference does the same thing per
+thread in cellhistory (macroatom.cc:161-172, kpkt.cc:167-308, update_grid.cc:659-761).
+
+Checked here: (1) with an arena that holds every row, packets and estimators are BIT-IDENTICAL to the dense tables (the rows
+are built by the same functions from the same inputs, and every packet owns its random stream); (2) the row probes (A11
+macro-atom rates, cooling sums) still match the reference's golden values; (3) with an arena so small that it fills many
+times per timestep -- the scheduler drains, the rows are forgotten, the unfinished packets are launched again -- every packet
+still finishes the timestep, the counters are conserved and the estimators agree with the dense run within Monte Carlo
+noise (packets in flight at a flush redraw their pending macro-atom action)."""
+import os
+
+import numpy as np
+import pytest
+
+import goldenlib
+import probelib
+import statlib
+from artis_b200 import abi
+from artis_b200.transport import Transport
+
+FIXTURES = ["classic_nogrey_ts12.npz", "nebular_nlte_ts8.npz"]
+
+
+def run(lib, fx, mode, arena_mb=None, seed=99, geometry=None):
+    old = {k: os.environ.get(k) for k in ("ARTIS_TABLES", "ARTIS_ROW_ARENA_MB")}
+    os.environ["ARTIS_TABLES"] = mode
+    if arena_mb is not None:
+        os.environ["ARTIS_ROW_ARENA_MB"] = str(arena_mb)
+    try:
+        T = Transport(lib)
+        T.init(fx["static"], seed=seed)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    T.upload_cellstate(fx["cell"])
+    T.zero_estimators()
+    pk = fx["pre"].copy()
+    T.update_packets(pk)
+    est = T.download_estimators()
+    return T, pk, est
+
+
+def check_identical(lib, name, probe_mode):
+    fx = goldenlib.load_fixture(name)
+    Td, pd, ed = run(lib, fx, "dense")
+    dense_bytes = Td.table_bytes()
+    Td.finalize()
+    Ts, ps, es = run(lib, fx, "sparse")
+    for f in pd.dtype.names:
+        assert np.array_equal(pd[f], ps[f], equal_nan=True), (name, f)
+    for k in ("J", "nuJ", "ffheatingestimator", "colheatingestimator", "gammaestimator", "bfheatingestimator", "ts_scalars"):
+        assert np.array_equal(ed[k], es[k], equal_nan=True), (name, k)
+    assert np.array_equal(ed["counters"][:51], es["counters"][:51])
+    c = es["counters"]
+    assert c[abi.CTR_ROW_FLUSHES] == 0 and c[abi.CTR_ROW_UNITS] > 0
+    print(name, "dense table bytes", dense_bytes, "rows built on demand:", int(c[abi.CTR_ROW_UNITS]) * 128, "bytes")
+    assert int(c[abi.CTR_ROW_UNITS]) * 128 < dense_bytes
+    # the row probes read through the same accessor
+    probelib.check_probes(Ts, fx, probe_mode)
+    Ts.finalize()
+
+
+def check_flushes(lib, name, arena_mb):
+    fx = goldenlib.load_fixture(name)
+    Td, pd, ed = run(lib, fx, "dense")
+    Td.finalize()
+    Ts, ps, es = run(lib, fx, "sparse", arena_mb=arena_mb)
+    c = es["counters"]
+    print(name, "arena", arena_mb, "MB: flushes", int(c[abi.CTR_ROW_FLUSHES]), "row bytes built", int(c[abi.CTR_ROW_UNITS]) * 128)
+    assert c[abi.CTR_ROW_FLUSHES] >= 2
+    st = fx["static"]
+    t2 = st["ts_start"][fx["nts"]] + st["ts_width"][fx["nts"]]
+    assert np.array_equal(ps["number"], fx["pre"]["number"])
+    assert ((ps["type"] == abi.TYPE_ESCAPE) | (ps["prop_time"] == t2)).all()
+    newly = (ps["type"] == abi.TYPE_ESCAPE) & (fx["pre"]["type"] != abi.TYPE_ESCAPE)
+    assert c[33] == newly.sum()
+    assert c[45] == ps["interactions"].sum() - fx["pre"]["interactions"].sum() or c[45] == ps["interactions"].sum()
+    good = statlib.good_cells(st, fx["cell"])
+    n = st["npts_model"]
+    assert np.isclose(es["J"][:n][good].sum(), ed["J"][:n][good].sum(), rtol=3e-2)
+    assert np.isclose(newly.sum(), ((pd["type"] == abi.TYPE_ESCAPE) & (fx["pre"]["type"] != abi.TYPE_ESCAPE)).sum(), rtol=0.1, atol=30)
+    Ts.finalize()
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_restatement_rows_on_demand_identical_to_dense(oracle_lib, name):
+    check_identical(oracle_lib, name, "oracle")
+
+
+def test_restatement_rows_on_demand_survive_arena_flushes(oracle_lib):
+    check_flushes(oracle_lib, FIXTURES[0], 0.01)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", FIXTURES)
+def test_cuda_rows_on_demand_identical_to_dense(gpu_lib, name):
+    check_identical(gpu_lib, name, "gpu")
+
+
+@pytest.mark.gpu
+def test_cuda_rows_on_demand_survive_arena_flushes(gpu_lib):
+    # the smallest arena the library accepts on the device is twice the reserve for rows under construction
+    check_flushes(gpu_lib, FIXTURES[0], 1)
+
+
+# ---- config 4 in small: every non-empty propagation cell its own model cell (tools/model3d.py) -------------------------
+def check_promoted(lib, name, probe_mode):
+    """Size-independent property of the 3-D promotion: the model cells of a shell hold the shell's state, so a packet lives
+    the life it lives in the 1-D model while the per-cell arrays have a row per propagation cell, and the estimators of
+    the cells of a shell add up to the shell's. Not bit for bit: the continuum opacity of a packet is kept while it stays
+    in its MODEL cell and its frequency moves by less than 1e-4 (rpkt.cc:1215-1222, rpkt.cuh kappa_cache_hit), and in the
+    3-D model every boundary crossing changes the model cell -- a packet in fifty sees a re-evaluated opacity at a
+    frequency 1e-5 away and moves by a relative 1e-9."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import model3d
+    fx = goldenlib.load_fixture(name)
+    Td, pd, ed = run(lib, fx, "dense")
+    Td.finalize()
+    st3, cs3, shell = model3d.promote(fx["static"], fx["cell"])
+    n1, n3 = int(fx["static"]["npts_model"]), int(st3["npts_model"])
+    assert n3 > 20 * n1
+    fx3 = dict(fx, static=st3, cell=cs3)
+    Ts, ps, es = run(lib, fx3, "sparse")
+    same = (pd["type"] == ps["type"]) & (pd["where"] == ps["where"]) & (pd["interactions"] == ps["interactions"])
+    exact = same & (pd["pos"] == ps["pos"]).all(1) & (pd["nu_cmf"] == ps["nu_cmf"])
+    print(name, "same history", same.mean(), "bit-identical", exact.mean())
+    assert same.mean() > 0.99 and exact.mean() > 0.95
+    dpos = np.linalg.norm(pd["pos"][same] - ps["pos"][same], axis=1) / np.linalg.norm(pd["pos"][same], axis=1)
+    assert dpos.max() < 1e-6, dpos.max()
+    assert np.allclose(pd["nu_cmf"][same], ps["nu_cmf"][same], rtol=1e-6)
+    for k in ("J", "nuJ", "ffheatingestimator", "colheatingestimator", "rpkt_emiss"):
+        by_shell = np.bincount(shell, weights=es[k][:n3], minlength=n1 + 1)[:n1]
+        want = ed[k][:n1]
+        if want.sum() == 0:  # e.g. rpkt_emiss outside the grey-opacity timesteps
+            assert by_shell.sum() == 0, k
+            continue
+        assert abs(by_shell.sum() / want.sum() - 1) < 2e-3, k
+        big = want > 1e-3 * want.max()
+        assert np.allclose(by_shell[big], want[big], rtol=0.05), k
+    assert np.allclose(ed["counters"][:46], es["counters"][:46], rtol=0.02, atol=5)
+    print(name, "model cells", n1, "->", n3, "rows built", int(es["counters"][abi.CTR_ROW_UNITS]) * 128, "bytes; table bytes",
+          Ts.table_bytes())
+    Ts.finalize()
+
+
+def test_restatement_promoted_3d_model_identical_histories(oracle_lib):
+    check_promoted(oracle_lib, FIXTURES[0], "oracle")
+
+
+@pytest.mark.gpu
+def test_cuda_promoted_3d_model_identical_histories(gpu_lib):
+    check_promoted(gpu_lib, FIXTURES[0], "gpu")
