@@ -34,6 +34,7 @@ PACKET_DTYPE = np.dtype({
 
 ABI_VERSION = int(re.search(r"#define ARTIS_GPU_ABI_VERSION (\d+)", open(os.path.join(INCLUDE, "artis_gpu.h")).read()).group(1))
 
+ERR_UNSUPPORTED = 6  # ARTIS_ERR_UNSUPPORTED
 CTR_ROW_FLUSHES, CTR_ROW_UNITS = 91, 92  # ARTIS_CTR_ROW_* (include/artis_gpu.h)
 TYPE_ESCAPE, TYPE_PELLET, TYPE_GAMMA, TYPE_RPKT, TYPE_KPKT, TYPE_MA = 32, 100, 10, 11, 12, 13
 TYPE_NTLEPTON, TYPE_NT_PREDEPOSIT, TYPE_PRE_KPKT, TYPE_GAMMA_KPKT = 20, 21, 120, 121

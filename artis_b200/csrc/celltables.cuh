@@ -541,6 +541,10 @@ ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
 }
 
 // ---- rows on demand ----------------------------------------------------------------------------------------------------
+#ifndef ARTIS_ROWS_ON_DEMAND
+#define ARTIS_ROWS_ON_DEMAND 1   // 0: the accessors below read the dense tables only (A/B builds)
+#endif
+ARTIS_DEV bool rows_on_demand(const Ctx &c) { return ARTIS_ROWS_ON_DEMAND != 0 && c.tb.row_ptr != nullptr; }
 // Upward transitions of an ion's levels are one contiguous range of the uptrans arrays (checked at init, engine.inc).
 ARTIS_DEV int ion_upfirst(const Ctx &c, const int ui) { return c.st.lev_upoffset[c.st.ion_leveloffset[ui]]; }
 ARTIS_DEV int ion_upcount(const Ctx &c, const int ui) {
@@ -618,7 +622,7 @@ struct MaRow {
 };
 ARTIS_DEV MaRow ma_row(const Ctx &c, const int mgi, const int tc, const int gl) {
   MaRow r;
-  if (c.tb.row_ptr != nullptr) {
+  if (rows_on_demand(c)) {
     const double *row = row_get(c, mgi, tc, gl);
     const int nd = c.st.lev_ndowntrans[gl];
     r.pr = row;
@@ -635,7 +639,7 @@ ARTIS_DEV MaRow ma_row(const Ctx &c, const int mgi, const int tc, const int gl) 
   return r;
 }
 ARTIS_DEV const double *ma_rates_row(const Ctx &c, const int mgi, const int tc, const int gl) {
-  return c.tb.row_ptr != nullptr ? row_get(c, mgi, tc, gl) : tab_ma_rates(c, tc, gl);
+  return rows_on_demand(c) ? row_get(c, mgi, tc, gl) : tab_ma_rates(c, tc, gl);
 }
 struct CoolRow {
   const double *cool;  // indexed with the global cooling-term index (ion_coolingoffset[ui] ...)
@@ -643,7 +647,7 @@ struct CoolRow {
 };
 ARTIS_DEV CoolRow cool_row(const Ctx &c, const int mgi, const int tc, const int ui) {
   CoolRow r;
-  if (c.tb.row_ptr != nullptr) {
+  if (rows_on_demand(c)) {
     const double *row = row_get(c, mgi, tc, c.st.nlevels_total + ui);
     r.cool = row - c.st.ion_coolingoffset[ui];
     r.cexc = row + c.st.ion_ncoolingterms[ui] - ion_upfirst(c, ui);

@@ -598,7 +598,7 @@ __device__ __forceinline__ void coop_bfest_flush(const artis::Ctx &c, artis::Kap
 // packets they hold back into the hot array and leave; the host forgets the rows and launches the scheduler again on the
 // packets that have not finished (engine.inc artis_gpu_transport_resident). Warp-uniform.
 __device__ __forceinline__ bool row_arena_stop(const artis::Ctx &c, const int lane) {
-  if (c.tb.row_ptr == nullptr) return false;
+  if (!artis::rows_on_demand(c)) return false;
   int stop = 0;
   if (lane == 0) stop = *reinterpret_cast<volatile int *>(c.tb.row_stop);
   return __shfl_sync(0xffffffffu, stop, 0) != 0;

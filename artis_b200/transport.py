@@ -19,6 +19,7 @@ DEFAULT_LIB = os.environ.get("ARTIS_GPU_LIB", os.path.join(HERE, "libartis_gpu.s
 # costs the other build modes 5-19 % when it is merely present in the transport kernels (profiles/r1_notes.md), so it is
 # compiled into a second library from the same sources. A VPKT_ON driver links this one instead.
 VPKT_LIB = os.path.join(HERE, "libartis_gpu_vpkt.so")
+ROWS_LIB = os.path.join(HERE, "libartis_gpu_rows.so")  # macro-atom / cooling rows on demand: models of ~1e5 cells and more
 
 
 class ArtisGpuError(RuntimeError):
@@ -56,7 +57,7 @@ class Transport:
         static["abi_version"] = abi.ABI_VERSION
         base = os.path.join(HERE, "libartis_gpu.so")
         want = VPKT_LIB if static.get("opt_vpkt_on") else base
-        if os.path.realpath(self.libpath) in (os.path.realpath(base), os.path.realpath(VPKT_LIB)) and \
+        if os.path.realpath(self.libpath) in (os.path.realpath(base), os.path.realpath(VPKT_LIB), os.path.realpath(ROWS_LIB)) and \
                 os.path.realpath(self.libpath) != os.path.realpath(want):
             if not os.path.exists(want):
                 raise ArtisGpuError(f"{want} not found: build it with __graft_entry__.build() (there is no CPU fallback)")
@@ -65,7 +66,15 @@ class Transport:
         st, keep = abi.build_struct(abi.ArtisStaticTables, abi.STATIC_FIELDS, static)
         self._keep.append(keep)
         self.static = static
-        self._check(self.lib.artis_gpu_init(C.byref(st), device, rank, nranks, C.c_ulonglong(seed)), "artis_gpu_init")
+        rc = self.lib.artis_gpu_init(C.byref(st), device, rank, nranks, C.c_ulonglong(seed))
+        if rc == abi.ERR_UNSUPPORTED and os.path.realpath(self.libpath) == os.path.realpath(base) and os.path.exists(ROWS_LIB):
+            buf = C.create_string_buffer(1024)
+            self.lib.artis_gpu_last_error(buf, 1024)
+            if b"libartis_gpu_rows.so" in buf.value:  # the model is too large for dense rows (or ARTIS_TABLES=sparse)
+                self.lib.artis_gpu_finalize()
+                self._load(ROWS_LIB)
+                rc = self.lib.artis_gpu_init(C.byref(st), device, rank, nranks, C.c_ulonglong(seed))
+        self._check(rc, "artis_gpu_init")
 
     def finalize(self):
         self.lib.artis_gpu_finalize()

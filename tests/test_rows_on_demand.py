@@ -54,8 +54,12 @@ def check_identical(lib, name, probe_mode):
     for f in pd.dtype.names:
         assert np.array_equal(pd[f], ps[f], equal_nan=True), (name, f)
     for k in ("J", "nuJ", "ffheatingestimator", "colheatingestimator", "gammaestimator", "bfheatingestimator", "ts_scalars"):
-        assert np.array_equal(ed[k], es[k], equal_nan=True), (name, k)
-    assert np.array_equal(ed["counters"][:51], es["counters"][:51])
+        if probe_mode == "oracle":
+            assert np.array_equal(ed[k], es[k], equal_nan=True), (name, k)
+        else:  # the same terms, added by atomics in whatever order the warps arrive
+            assert np.allclose(ed[k], es[k], rtol=1e-11, atol=0, equal_nan=True), (name, k)
+    physics = np.r_[0:39, 40:46]  # event counters and work counters; not the estimator atomics (they depend on which lanes
+    assert np.array_equal(ed["counters"][physics], es["counters"][physics])  # share a warp) nor the scheduler statistics
     c = es["counters"]
     assert c[abi.CTR_ROW_FLUSHES] == 0 and c[abi.CTR_ROW_UNITS] > 0
     print(name, "dense table bytes", dense_bytes, "rows built on demand:", int(c[abi.CTR_ROW_UNITS]) * 128, "bytes")
