@@ -419,9 +419,9 @@ ARTIS_DEV void build_ma_level_into(const Ctx &c, const int mgi, const int gl, co
     const double R = rad_deexcitation_ratecoeff(c, tc, gl, gll, epsilon_trans, lineindex, t_mid);
     const double C = col_deexcitation_ratecoeff(T_e, nne, epsilon_trans, lineref(c, lineindex),
                                                 (double)c.st.lev_statweight[gll], statweight);
-    pr[MA_RADDEEXC] += R * epsilon_trans;
-    pr[MA_COLDEEXC] += C * epsilon_trans;
-    pr[MA_INTERNALDOWNSAME] += (R + C) * epsilon_target;
+    pr[MA_RADDEEXC] = fma(R, epsilon_trans, pr[MA_RADDEEXC]);
+    pr[MA_COLDEEXC] = fma(C, epsilon_trans, pr[MA_COLDEEXC]);
+    pr[MA_INTERNALDOWNSAME] = fma(R + C, epsilon_target, pr[MA_INTERNALDOWNSAME]);
     cum_rad[i] = pr[MA_RADDEEXC];
     cum_down[i] = pr[MA_INTERNALDOWNSAME];
   }
@@ -435,9 +435,9 @@ ARTIS_DEV void build_ma_level_into(const Ctx &c, const int mgi, const int gl, co
       const double epsilon_trans = epsilon_current - epsilon_target;
       const double R = rad_recombination_ratecoeff(c, T_e, nne, gll, level);
       const double C = col_recombination_ratecoeff(c, mgi, ui, gl, gll, epsilon_trans);
-      pr[MA_INTERNALDOWNLOWER] += (R + C) * epsilon_target;
-      pr[MA_RADRECOMB] += R * epsilon_trans;
-      pr[MA_COLRECOMB] += C * epsilon_trans;
+      pr[MA_INTERNALDOWNLOWER] = fma(R + C, epsilon_target, pr[MA_INTERNALDOWNLOWER]);
+      pr[MA_RADRECOMB] = fma(R, epsilon_trans, pr[MA_RADRECOMB]);
+      pr[MA_COLRECOMB] = fma(C, epsilon_trans, pr[MA_COLRECOMB]);
     }
   }
 
@@ -450,7 +450,7 @@ ARTIS_DEV void build_ma_level_into(const Ctx &c, const int mgi, const int gl, co
     const double C = col_excitation_ratecoeff(T_e, nne, lineref(c, lineindex), epsilon_trans, statweight,
                                               (double)c.st.lev_statweight[glu]);
     const double NT = 0.;  // nonthermal::nt_excitation_ratecoeff: NT_EXCITATION_ON is false in every options header
-    pr[MA_INTERNALUPSAME] += (R + C + NT) * epsilon_current;
+    pr[MA_INTERNALUPSAME] = fma(R + C + NT, epsilon_current, pr[MA_INTERNALUPSAME]);
     cum_up[i] = pr[MA_INTERNALUPSAME];
   }
 
@@ -461,7 +461,7 @@ ARTIS_DEV void build_ma_level_into(const Ctx &c, const int mgi, const int gl, co
       const double epsilon_trans = phixs_threshold(c, ui, gl, t);
       const double R = get_corrphotoioncoeff(c, mgi, gl, t);
       const double C = col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans);
-      pr[MA_INTERNALUPHIGHER] += (R + C) * epsilon_current;
+      pr[MA_INTERNALUPHIGHER] = fma(R + C, epsilon_current, pr[MA_INTERNALUPHIGHER]);
     }
   }
   for (int a = 0; a < MA_ACTION_COUNT; a++) out[a] = pr[a];
@@ -477,14 +477,18 @@ ARTIS_DEV void build_ma_level(const Ctx &c, const int mgi, const int gl, const d
 
 // kpkt.cc:167-308 calculate_kpkt_rates_ion for one (cell, ion); `oldcoolingsum` = sum of cooling_contrib_ion of the
 // ions before this one in (element, ion) order, accumulated like the selection loop of do_kpkt (kpkt.cc:527-536)
-// `cool` is indexed with the global cooling-term index, `cexc` with the global upward-transition index
-ARTIS_DEV void build_cooling_ion_into(const Ctx &c, const int mgi, const int ui, double *cool, double *cexc) {
+// `cool` is indexed with the global cooling-term index, `cexc` with the global upward-transition index.
+// STORE = false, start from zero: calculate_cooling_rates' C_ion (kpkt.cc:310-365, the same template with
+// update_cooling_contrib_list = false), returned.
+template <bool STORE>
+ARTIS_DEV double cooling_ion_sum(const Ctx &c, const int mgi, const int ui, double *cool, double *cexc) {
   const int tc = tabcell(c, mgi);
   const int element = c.uion_element[ui];
   const float nne = c.cs.nne[mgi];
   const float T_e = c.cs.Te[mgi];
   double oldcoolingsum = 0.;
-  for (int u = 0; u < ui; u++) oldcoolingsum += c.cs.cooling_contrib_ion[(size_t)mgi * c.st.includedions + u];
+  if (STORE)
+    for (int u = 0; u < ui; u++) oldcoolingsum += c.cs.cooling_contrib_ion[(size_t)mgi * c.st.includedions + u];
   double contrib = oldcoolingsum;
   int i = c.st.ion_coolingoffset[ui];
   const int gl0 = c.st.ion_leveloffset[ui];
@@ -494,7 +498,8 @@ ARTIS_DEV void build_cooling_ion_into(const Ctx &c, const int mgi, const int ui,
   const int ioncharge = c.st.ion_ionstage[ui] - 1;
   if (ioncharge > 0) {
     contrib += 1.426e-27 * sqrtf(T_e) * pow((double)ioncharge, 2) * nncurrention * nne;
-    cool[i++] = contrib;
+    if (STORE) cool[i] = contrib;
+    i++;
   }
   const bool hasupper = ion_has_upper(c, ui);
   for (int level = 0; level < nlevels; level++) {
@@ -513,27 +518,34 @@ ARTIS_DEV void build_cooling_ion_into(const Ctx &c, const int mgi, const int ui,
                                                   (double)c.st.lev_statweight[glu]) *
                          epsilon_trans;
         contrib += C;
-        cexc[uoff + ii] = contrib;
+        if (STORE) cexc[uoff + ii] = contrib;
       }
-      cool[i++] = contrib;
+      if (STORE) cool[i] = contrib;
+      i++;
     }
     if (hasupper && level < ionisinglevels) {
       const int ntargets = c.st.lev_nphixstargets[gl];
       for (int t = 0; t < ntargets; t++) {
         const double epsilon_trans = phixs_threshold(c, ui, gl, t);
         contrib += nnlevel * col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans) * epsilon_trans;
-        cool[i++] = contrib;
+        if (STORE) cool[i] = contrib;
+        i++;
       }
       for (int t = 0; t < ntargets; t++) {
         const double nnupperion = ionstagepop_ui(c, mgi, element, ui + 1);
         contrib += get_bfcoolingcoeff(c, gl, t, T_e) * nnupperion * nne;
-        cool[i++] = contrib;
+        if (STORE) cool[i] = contrib;
+        i++;
       }
     }
   }
   // fill the tail when levels >= ionisinglevels own (uncomputed) list slots: the reference leaves them untouched
   // and asserts i == offset + ncoolingterms (kpkt.cc:300); here a mismatch is reported as a fatal table error
   if (i != c.st.ion_coolingoffset[ui] + c.st.ion_ncoolingterms[ui]) fatal(c, 202);
+  return contrib;
+}
+ARTIS_DEV void build_cooling_ion_into(const Ctx &c, const int mgi, const int ui, double *cool, double *cexc) {
+  cooling_ion_sum<true>(c, mgi, ui, cool, cexc);
 }
 ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
   const size_t tc = (size_t)tabcell(c, mgi);
@@ -613,6 +625,150 @@ ARTIS_DEV_NOINLINE const double *row_get(const Ctx &c, const int mgi, const int 
 #endif
   return row;
 }
+
+#ifdef __CUDACC__
+// The row of level gl built by the 32 lanes of a warp (all of them call, with the same arguments). The lanes evaluate the
+// rate coefficients of 32 transitions at a time -- the Sobolev escape probabilities, collision strengths and recombination
+// coefficients are the work -- and then every lane adds the 32 contributions in list order from shuffled operands, so that
+// each running sum sees the roundings of build_ma_level_into (one fused multiply-add per transition, in order): the row is
+// bit for bit the row one thread builds, in a thirtieth of the time. Returns the row (also when another warp was faster).
+__device__ __noinline__ const double *coop_build_ma_row(const Ctx &c, const int mgi, const int tc, const int gl, const int lane) {
+  const unsigned full = 0xffffffffu;
+  const CellTables &tb = c.tb;
+  unsigned *slot = tb.row_ptr + (size_t)tc * (c.st.nlevels_total + c.st.includedions) + gl;
+  const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
+  const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
+  unsigned long long at = 0ull;
+  unsigned have = 0u;
+  int bad = 0;
+  if (lane == 0) {
+    have = __ldcg(slot);
+    if (have == 0u) {
+      const unsigned long long units = (unsigned long long)(MA_ACTION_COUNT + 2 * ndown + nup + 15) / 16;
+      at = atomicAdd(tb.row_top, units);
+      if (at + units > tb.row_soft) *reinterpret_cast<volatile int *>(tb.row_stop) = 1;
+      if (at + units > tb.row_cap) {
+        fatal(c, 240);
+        bad = 1;
+      }
+    }
+  }
+  have = __shfl_sync(full, have, 0);
+  if (have != 0u) return tb.row_arena + (size_t)(have - 1u) * 16;
+  if (__shfl_sync(full, bad, 0) != 0) return tb.row_arena;
+  at = __shfl_sync(full, at, 0);
+  double *row = tb.row_arena + (size_t)at * 16;
+  double *cum_rad = row + MA_ACTION_COUNT, *cum_down = cum_rad + ndown, *cum_up = cum_down + ndown;
+  const int ui = c.lev_uion[gl];
+  const int level = gl - c.st.ion_leveloffset[ui];
+  const float T_e = c.cs.Te[mgi];
+  const float nne = c.cs.nne[mgi];
+  const double epsilon_current = c.st.lev_epsilon[gl];
+  const double statweight = (double)c.st.lev_statweight[gl];
+  const double t_mid = c.t_mid;
+  double pr[MA_ACTION_COUNT];
+  for (int a = 0; a < MA_ACTION_COUNT; a++) pr[a] = 0.;
+
+  for (int base = 0; base < ndown; base += 32) {
+    const int i = base + lane;
+    double R = 0., C = 0., e_trans = 0., e_target = 0.;
+    if (i < ndown) {
+      const int lineindex = c.st.downtrans_lineindex[doff + i];
+      const int gll = c.line_lower_g[lineindex];
+      e_target = c.st.lev_epsilon[gll];
+      e_trans = epsilon_current - e_target;
+      R = rad_deexcitation_ratecoeff(c, tc, gl, gll, e_trans, lineindex, t_mid);
+      C = col_deexcitation_ratecoeff(T_e, nne, e_trans, lineref(c, lineindex), (double)c.st.lev_statweight[gll], statweight);
+    }
+    const int cnt = ndown - base < 32 ? ndown - base : 32;
+    double my_rad = 0., my_down = 0.;
+    for (int j = 0; j < cnt; j++) {
+      const double Rj = __shfl_sync(full, R, j), Cj = __shfl_sync(full, C, j);
+      const double etj = __shfl_sync(full, e_trans, j), egj = __shfl_sync(full, e_target, j);
+      pr[MA_RADDEEXC] = fma(Rj, etj, pr[MA_RADDEEXC]);
+      pr[MA_COLDEEXC] = fma(Cj, etj, pr[MA_COLDEEXC]);
+      pr[MA_INTERNALDOWNSAME] = fma(Rj + Cj, egj, pr[MA_INTERNALDOWNSAME]);
+      if (lane == j) {
+        my_rad = pr[MA_RADDEEXC];
+        my_down = pr[MA_INTERNALDOWNSAME];
+      }
+    }
+    if (i < ndown) {
+      cum_rad[i] = my_rad;
+      cum_down[i] = my_down;
+    }
+  }
+
+  if (ion_has_lower(c, ui) && level <= c.st.ion_maxrecombininglevel[ui]) {
+    const int gl0_lower = c.st.ion_leveloffset[ui - 1];
+    const int nlevels = c.st.ion_ionisinglevels[ui - 1];
+    for (int base = 0; base < nlevels; base += 32) {
+      const int lower = base + lane;
+      double R = 0., C = 0., e_trans = 0., e_target = 0.;
+      if (lower < nlevels) {
+        const int gll = gl0_lower + lower;
+        e_target = c.st.lev_epsilon[gll];
+        e_trans = epsilon_current - e_target;
+        R = rad_recombination_ratecoeff(c, T_e, nne, gll, level);
+        C = col_recombination_ratecoeff(c, mgi, ui, gl, gll, e_trans);
+      }
+      const int cnt = nlevels - base < 32 ? nlevels - base : 32;
+      for (int j = 0; j < cnt; j++) {
+        const double Rj = __shfl_sync(full, R, j), Cj = __shfl_sync(full, C, j);
+        const double etj = __shfl_sync(full, e_trans, j), egj = __shfl_sync(full, e_target, j);
+        pr[MA_INTERNALDOWNLOWER] = fma(Rj + Cj, egj, pr[MA_INTERNALDOWNLOWER]);
+        pr[MA_RADRECOMB] = fma(Rj, etj, pr[MA_RADRECOMB]);
+        pr[MA_COLRECOMB] = fma(Cj, etj, pr[MA_COLRECOMB]);
+      }
+    }
+  }
+
+  for (int base = 0; base < nup; base += 32) {
+    const int i = base + lane;
+    double RC = 0.;
+    if (i < nup) {
+      const int lineindex = c.st.uptrans_lineindex[uoff + i];
+      const int glu = c.line_upper_g[lineindex];
+      const double e_trans = c.st.lev_epsilon[glu] - epsilon_current;
+      const double R = rad_excitation_ratecoeff(c, mgi, tc, gl, glu, e_trans, lineindex, t_mid);
+      const double C = col_excitation_ratecoeff(T_e, nne, lineref(c, lineindex), e_trans, statweight, (double)c.st.lev_statweight[glu]);
+      const double NT = 0.;
+      RC = R + C + NT;
+    }
+    const int cnt = nup - base < 32 ? nup - base : 32;
+    double my_up = 0.;
+    for (int j = 0; j < cnt; j++) {
+      pr[MA_INTERNALUPSAME] = fma(__shfl_sync(full, RC, j), epsilon_current, pr[MA_INTERNALUPSAME]);
+      if (lane == j) my_up = pr[MA_INTERNALUPSAME];
+    }
+    if (i < nup) cum_up[i] = my_up;
+  }
+
+  if (ion_has_upper(c, ui) && level < c.st.ion_ionisinglevels[ui]) {  // a handful of targets: every lane the same sums
+    if (c.st.opt_nt_on) pr[MA_INTERNALUPHIGHERNT] = nt_ionization_ratecoeff(c, mgi, ui) * epsilon_current;
+    const int ntargets = c.st.lev_nphixstargets[gl];
+    for (int t = 0; t < ntargets; t++) {
+      const double e_trans = phixs_threshold(c, ui, gl, t);
+      const double R = get_corrphotoioncoeff(c, mgi, gl, t);
+      const double C = col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, e_trans);
+      pr[MA_INTERNALUPHIGHER] = fma(R + C, epsilon_current, pr[MA_INTERNALUPHIGHER]);
+    }
+  }
+  if (lane < MA_ACTION_COUNT) {
+    double v = pr[0];
+#pragma unroll
+    for (int a = 1; a < MA_ACTION_COUNT; a++)
+      if (lane == a) v = pr[a];
+    row[lane] = v;
+  }
+  __threadfence();
+  __syncwarp(full);
+  unsigned prev = 0u;
+  if (lane == 0) prev = atomicCAS(slot, 0u, (unsigned)at + 1u);
+  prev = __shfl_sync(full, prev, 0);
+  return prev != 0u ? tb.row_arena + (size_t)(prev - 1u) * 16 : row;
+}
+#endif
 
 struct MaRow {
   const double *pr;        // [MA_ACTION_COUNT]

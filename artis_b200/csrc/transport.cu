@@ -933,6 +933,27 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_light(P
         fill_lanes += __popc(busy);
       }
     }
+#if ARTIS_ROWS_ON_DEMAND
+    if (role == KIND_MAJUMP && rows_on_demand(c)) {  // warp-uniform
+      // rows the lanes' jumps need and nobody has built yet: the warp builds them one after the other with all 32 lanes
+      int b_mgi = 0, b_tc = -1, b_gl = 0;
+      bool miss = false;
+      if (have) {
+        b_mgi = cell_mgi(c, v.where);
+        b_tc = tabcell(c, b_mgi);
+        if (b_tc >= 0 && c.cs.thick[b_mgi] != 1) {
+          b_gl = c.st.ion_leveloffset[uion_of(c, v.ma_element, v.ma_ion)] + v.ma_level;
+          miss = __ldcg(c.tb.row_ptr + (size_t)b_tc * (c.st.nlevels_total + c.st.includedions) + b_gl) == 0u;
+        }
+      }
+      unsigned todo = __ballot_sync(full, miss);
+      while (todo != 0u) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1u;
+        coop_build_ma_row(c, __shfl_sync(full, b_mgi, src), __shfl_sync(full, b_tc, src), __shfl_sync(full, b_gl, src), lane);
+      }
+    }
+#endif
     bool done = false;
     int k2 = -1;
     if (ARTIS_KAPPA_OFFLOAD != 0 && role == KIND_KAPPA) {  // warp-uniform
