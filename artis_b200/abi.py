@@ -158,6 +158,7 @@ def declare(lib):
         "artis_gpu_packets_download_escaped": [vp, C.c_int, C.c_int, pi],
         "artis_gpu_bin_escaped_resolved": [C.c_double, C.c_int, C.c_int, pd, pd, pd, pd, pd, pd],
         "artis_gpu_normalise_estimators": [pd, C.c_int, C.c_double, pd, pd],
+        "artis_gpu_cooling_rates": [pd, pd, C.c_int],
         "artis_gpu_upload_estimators": [P(ArtisEstimators)],
         "artis_gpu_packets_write_temp": [C.c_char_p],
         "artis_gpu_packets_read_temp": [C.c_char_p, C.c_int],
@@ -195,5 +196,5 @@ EXPORTED_SYMBOLS = [
     "artis_gpu_probe_levelpop", "artis_gpu_launch_count", "artis_gpu_table_bytes", "artis_gpu_bin_escaped",
     "artis_gpu_packets_download_escaped", "artis_gpu_pack_escaped_noalloc", "artis_gpu_scheduler_geometry", "artis_gpu_probe_select_continuum_nu",
     "artis_gpu_packets_write_temp", "artis_gpu_packets_read_temp", "artis_gpu_packets_write_text", "artis_gpu_bin_escaped_resolved",
-    "artis_gpu_normalise_estimators", "artis_gpu_upload_estimators",
+    "artis_gpu_normalise_estimators", "artis_gpu_upload_estimators", "artis_gpu_cooling_rates",
 ]

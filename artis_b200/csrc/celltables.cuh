@@ -547,6 +547,55 @@ ARTIS_DEV double cooling_ion_sum(const Ctx &c, const int mgi, const int ui, doub
 ARTIS_DEV void build_cooling_ion_into(const Ctx &c, const int mgi, const int ui, double *cool, double *cexc) {
   cooling_ion_sum<true>(c, mgi, ui, cool, cexc);
 }
+// kpkt.cc:84-165 calculate_cooling_rates for one (cell, ion): C_ion in the reference's own order of addition -- the
+// free-free term, then the collisional-excitation sum of every level (get_cooling_ion_coll_exc, kpkt.cc:40-66, summed on
+// its own), then level by level the collisional ionisations and the free-bound terms
+ARTIS_DEV double cooling_rates_ion(const Ctx &c, const int mgi, const int ui) {
+  const int tc = tabcell(c, mgi);
+  const int element = c.uion_element[ui];
+  const float nne = c.cs.nne[mgi];
+  const float T_e = c.cs.Te[mgi];
+  const int gl0 = c.st.ion_leveloffset[ui];
+  const int nlevels = c.st.ion_nlevels[ui];
+  const double nncurrention = ionstagepop_ui(c, mgi, element, ui);
+  double C_ion = 0.;
+  const int ioncharge = c.st.ion_ionstage[ui] - 1;
+  if (ioncharge > 0) C_ion += 1.426e-27 * sqrtf(T_e) * pow((double)ioncharge, 2) * nncurrention * nne;
+  double C_exc = 0.;
+  for (int level = 0; level < nlevels; level++) {
+    const int gl = gl0 + level;
+    const double nnlevel = tab_levelpop(c, tc, gl);
+    const double epsilon_current = c.st.lev_epsilon[gl];
+    const double statweight = (double)c.st.lev_statweight[gl];
+    const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
+    for (int ii = 0; ii < nup; ii++) {
+      const int lineindex = c.st.uptrans_lineindex[uoff + ii];
+      const int glu = c.line_upper_g[lineindex];
+      const double epsilon_trans = c.st.lev_epsilon[glu] - epsilon_current;
+      C_exc += nnlevel *
+               col_excitation_ratecoeff(T_e, nne, lineref(c, lineindex), epsilon_trans, statweight, (double)c.st.lev_statweight[glu]) *
+               epsilon_trans;
+    }
+  }
+  C_ion += C_exc;
+  if (ion_has_upper(c, ui)) {
+    const int ionisinglevels = c.st.ion_ionisinglevels[ui];
+    for (int level = 0; level < ionisinglevels; level++) {
+      const int gl = gl0 + level;
+      const double nnlevel = tab_levelpop(c, tc, gl);
+      const int ntargets = c.st.lev_nphixstargets[gl];
+      for (int t = 0; t < ntargets; t++) {
+        const double epsilon_trans = phixs_threshold(c, ui, gl, t);
+        C_ion += nnlevel * col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans) * epsilon_trans;
+      }
+      for (int t = 0; t < ntargets; t++) {
+        const double nnupperion = ionstagepop_ui(c, mgi, element, ui + 1);
+        C_ion += get_bfcoolingcoeff(c, gl, t, T_e) * nnupperion * nne;
+      }
+    }
+  }
+  return C_ion;
+}
 ARTIS_DEV void build_cooling_ion(const Ctx &c, const int mgi, const int ui) {
   const size_t tc = (size_t)tabcell(c, mgi);
   build_cooling_ion_into(c, mgi, ui, c.tb.cool_cum + tc * c.st.ncoolingterms, c.tb.collexc_cum + tc * c.st.nuptrans_total);

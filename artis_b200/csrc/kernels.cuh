@@ -27,6 +27,20 @@ ARTIS_DEV void body_ma(const Ctx &c, const long long idx) {
   const int mgi = c.mgi_of_tabcell[tc];
   if (cell_uses_tables(c, mgi)) build_ma_level(c, mgi, (int)(idx % c.st.nlevels_total), c.t_mid);
 }
+// calculate_cooling_rates (kpkt.cc:84-165): idx over (table cell, ion) -> contrib[mgi][ion]; then idx over table cells ->
+// total[mgi] = the ions' sums added in (element, ion) order
+ARTIS_DEV void body_cooling_rates_ion(const Ctx &c, const long long idx, double *contrib) {
+  const int tc = (int)(idx / c.st.includedions);
+  const int ui = (int)(idx % c.st.includedions);
+  const int mgi = c.mgi_of_tabcell[tc];
+  contrib[(size_t)mgi * c.st.includedions + ui] = cooling_rates_ion(c, mgi, ui);
+}
+ARTIS_DEV void body_cooling_rates_total(const Ctx &c, const long long tc, const double *contrib, double *total) {
+  const int mgi = c.mgi_of_tabcell[tc];
+  double C_total = 0.;
+  for (int ui = 0; ui < c.st.includedions; ui++) C_total += contrib[(size_t)mgi * c.st.includedions + ui];
+  total[mgi] = C_total;
+}
 ARTIS_DEV void body_cool(const Ctx &c, const long long idx) {
   const int tc = (int)(idx / c.st.includedions);
   const int mgi = c.mgi_of_tabcell[tc];

@@ -59,6 +59,14 @@ __global__ void k_ma(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_ma(d_ctx, i);
 }
+__global__ void k_cooling_rates_ion(long long n, double *contrib) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_cooling_rates_ion(d_ctx, i, contrib);
+}
+__global__ void k_cooling_rates_total(long long n, const double *contrib, double *total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_cooling_rates_total(d_ctx, i, contrib, total);
+}
 __global__ void k_cool(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_cool(d_ctx, i);
@@ -1283,6 +1291,11 @@ void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8),
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
+void be_run_cooling_rates(long long ncells, int nions, double *contrib, double *total) {
+  if (ncells <= 0) return;
+  k_cooling_rates_ion<<<grid_for(ncells * nions, 64, 8), 64, 0, g_stream>>>(ncells * nions, contrib);
+  k_cooling_rates_total<<<grid_for(ncells, 128, 8), 128, 0, g_stream>>>(ncells, contrib, total);
+}
 void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
 void be_run_unpack(const ArtisPacket *aos, PktHot *hot, PktCold *cold, long long n) {
   if (n > 0) k_unpack<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(aos, hot, cold, n);

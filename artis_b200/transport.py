@@ -194,6 +194,13 @@ class Transport:
                     "artis_gpu_normalise_estimators")
         return out, float(g[0])
 
+    def cooling_rates(self, install=False):
+        """-> (totalcooling[npts_model + 1], cooling_contrib_ion[npts_model + 1, includedions]) of the uploaded cell state"""
+        nm, ni = int(self.static["npts_model"]) + 1, int(self.static["includedions"])
+        total, contrib = np.zeros(nm), np.zeros((nm, ni))
+        self._check(self.lib.artis_gpu_cooling_rates(_pd(total), _pd(contrib), 1 if install else 0), "artis_gpu_cooling_rates")
+        return total, contrib
+
     def estimator_block(self):
         ptr = C.c_void_p()
         n = C.c_size_t()

@@ -264,6 +264,18 @@ int artis_gpu_packets_download_escaped(ArtisPacket *out, int capacity, int only_
 int artis_gpu_pack_escaped_noalloc(const ArtisPacket *dev_packets, int npkts, ArtisPacket *dev_out, int capacity,
                                    int *dev_n_out, void *cuda_stream);
 
+/* ---- per-cell precompute on the device --------------------------------------------------------- */
+/* calculate_cooling_rates (kpkt.cc:84-165, called by update_grid after the temperature solve, update_grid.cc:1205) for
+ * every non-empty model cell of the cell state of the last artis_gpu_upload_cellstate, in the reference's order of
+ * addition:
+ *   totalcooling         out [npts_model + 1]                  grid::modelgrid[mgi].totalcooling
+ *   cooling_contrib_ion  out [(npts_model + 1) * includedions] grid::modelgrid[mgi].cooling_contrib_ion[element][ion]
+ * (entries of empty cells are 0). install != 0 also makes them the device-resident cell state's values and rebuilds the
+ * cooling rows that start from them, for a driver that uploads its cell state without them. The other lazily computed
+ * per-cell quantities of the reference (level populations, bound-free departure ratios, corrphotoioncoeff per
+ * continuum, macro-atom and cooling rows) are built by artis_gpu_upload_cellstate itself. */
+int artis_gpu_cooling_rates(double *totalcooling, double *cooling_contrib_ion, int install);
+
 /* ---- estimator normalisation on the device ------------------------------------------------- */
 /* What update_grid does to the raw estimators of a timestep before it uses them (update_grid.cc:1041-1134:
  * estimator_normfactor = 1 / deltaV / deltat / nprocs, radfield::normalise_J / normalise_nuJ with the 1/4pi, the

@@ -41,6 +41,10 @@ void be_run_levelpop(long long n) { for (long long i = 0; i < n; i++) artis::bod
 void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g_ctx, i); }
 void be_run_corrphoto(long long n) { for (long long i = 0; i < n; i++) artis::body_corrphoto(g_ctx, i); }
 void be_run_ma(long long n) { for (long long i = 0; i < n; i++) artis::body_ma(g_ctx, i); }
+void be_run_cooling_rates(long long ncells, int nions, double *contrib, double *total) {
+  for (long long i = 0; i < ncells * nions; i++) artis::body_cooling_rates_ion(g_ctx, i, contrib);
+  for (long long i = 0; i < ncells; i++) artis::body_cooling_rates_total(g_ctx, i, contrib, total);
+}
 void be_run_cool(long long n) { for (long long i = 0; i < n; i++) artis::body_cool(g_ctx, i); }
 using artis::PktCold;
 using artis::PktHot;
