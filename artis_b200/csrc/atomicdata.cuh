@@ -58,7 +58,7 @@ ARTIS_DEV double levelpop_g(const Ctx &c, int mgi, int element, int ui, int gl) 
   const int gl0 = c.st.ion_leveloffset[ui];
   const int level = gl - gl0;
   double nn;
-  if (level > 0 && c.st.opt_nlte_pops_on && c.st.ion_nlevels_nlte[ui] > 0) {
+  if (level > 0 && ARTIS_OPT_NLTE(c) && c.st.ion_nlevels_nlte[ui] > 0) {
     const int nlev_nlte = c.st.ion_nlevels_nlte[ui];
     const double *pops = c.cs.nlte_pops + (size_t)mgi * c.cs.total_nlte_levels;
     if (level <= nlev_nlte) {  // LEVEL_IS_NLTE (artisoptions_nltenebular.h): levels 1..nlevels_nlte

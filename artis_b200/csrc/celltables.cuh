@@ -169,7 +169,7 @@ ARTIS_DEV double col_ionization_ratecoeff(const Ctx &c, const float T_e, const f
 // ratecoeff.cc:1247-1310 get_corrphotoioncoeff. LUT mode (NO_LUT_PHOTOION false): W * interpolated coefficient *
 // renormalisation. NO_LUT_PHOTOION: the per-cell table filled by build_corrphoto below.
 ARTIS_DEV double get_corrphotoioncoeff(const Ctx &c, const int mgi, const int gl_lower, const int t) {
-  if (c.st.opt_no_lut_photoion) {
+  if (ARTIS_OPT_NOLUT_PHOTOION(c)) {
     const int i = c.allcont_of_lut[-1 - c.st.lev_cont_index[gl_lower] + t];
     return c.tb.corrphoto[(size_t)tabcell(c, mgi) * c.st.nbfcontinua + i];
   }
@@ -455,7 +455,7 @@ ARTIS_DEV void build_ma_level_into(const Ctx &c, const int mgi, const int gl, co
   }
 
   if (ion_has_upper(c, ui) && level < c.st.ion_ionisinglevels[ui]) {
-    if (c.st.opt_nt_on) pr[MA_INTERNALUPHIGHERNT] = nt_ionization_ratecoeff(c, mgi, ui) * epsilon_current;  // macroatom.cc:143-146
+    if (ARTIS_OPT_NT(c)) pr[MA_INTERNALUPHIGHERNT] = nt_ionization_ratecoeff(c, mgi, ui) * epsilon_current;  // macroatom.cc:143-146
     const int ntargets = c.st.lev_nphixstargets[gl];
     for (int t = 0; t < ntargets; t++) {
       const double epsilon_trans = phixs_threshold(c, ui, gl, t);
@@ -794,7 +794,7 @@ __device__ __noinline__ const double *coop_build_ma_row(const Ctx &c, const int 
   }
 
   if (ion_has_upper(c, ui) && level < c.st.ion_ionisinglevels[ui]) {  // a handful of targets: every lane the same sums
-    if (c.st.opt_nt_on) pr[MA_INTERNALUPHIGHERNT] = nt_ionization_ratecoeff(c, mgi, ui) * epsilon_current;
+    if (ARTIS_OPT_NT(c)) pr[MA_INTERNALUPHIGHERNT] = nt_ionization_ratecoeff(c, mgi, ui) * epsilon_current;
     const int ntargets = c.st.lev_nphixstargets[gl];
     for (int t = 0; t < ntargets; t++) {
       const double e_trans = phixs_threshold(c, ui, gl, t);

@@ -347,6 +347,10 @@ struct Ctx {
 // Build-mode switches as the device code tests them. They are run-time flags of the static tables (one library serves
 // every artisoptions_*.h); the ARTIS_NO_* macros compile a family of them out for same-box A/B measurements of what the
 // extra code paths cost the classic-mode kernels (profiles/r1_notes.md).
+#ifdef ARTIS_CLASSIC_ONLY
+#define ARTIS_NO_GRID1D
+#define ARTIS_NO_NEBULAR
+#endif
 #ifdef ARTIS_NO_VPKT
 #define ARTIS_OPT_VPKT(c) false
 #else
@@ -365,6 +369,24 @@ struct Ctx {
 #define ARTIS_OPT_DETAILED_BF(c) ((c).st.opt_detailed_bf_estimators != 0)
 #define ARTIS_OPT_MULTIBIN(c) ((c).st.opt_multibin_radfield != 0)
 #define ARTIS_OPT_NT_SF(c) ((c).st.opt_nt_on != 0 && (c).st.opt_nt_solve_spencerfano != 0)
+#endif
+
+// ARTIS_CLASSIC_ONLY: every switch of artisoptions_classic.h a compile-time constant -- the experiment behind "per-mode
+// libraries" (profiles/r2_notes.md): how much of the kernels is code of other build modes?
+#ifdef ARTIS_CLASSIC_ONLY
+#define ARTIS_OPT_NT(c) false
+#define ARTIS_OPT_NLTE(c) false
+#define ARTIS_OPT_NOLUT_PHOTOION(c) false
+#define ARTIS_OPT_NOLUT_BFHEATING(c) false
+#define ARTIS_OPT_RELDOPPLER(c) false
+#define ARTIS_OPT_INSTANT_DEPOSITION(c) true
+#else
+#define ARTIS_OPT_NT(c) ((c).st.opt_nt_on != 0)
+#define ARTIS_OPT_NLTE(c) ((c).st.opt_nlte_pops_on != 0)
+#define ARTIS_OPT_NOLUT_PHOTOION(c) ((c).st.opt_no_lut_photoion != 0)
+#define ARTIS_OPT_NOLUT_BFHEATING(c) ((c).st.opt_no_lut_bfheating != 0)
+#define ARTIS_OPT_RELDOPPLER(c) ((c).st.opt_relativistic_doppler != 0)
+#define ARTIS_OPT_INSTANT_DEPOSITION(c) ((c).st.opt_instant_particle_deposition != 0)
 #endif
 
 // ---- Philox4x32-10 counter-based stream (Salmon et al. 2011), one stream per packet and timestep -------------
@@ -490,7 +512,7 @@ ARTIS_DEV void angle_ab(const double dir1[3], const double vel[3], double dir2[3
 ARTIS_DEV double doppler_nucmf_on_nurf(const Ctx &c, const double dir_rf[3], const double vel_rf[3]) {
   const double ndotv = dot3(dir_rf, vel_rf);
   double dopplerfactor = 1. - (ndotv / CLIGHT);
-  if (c.st.opt_relativistic_doppler) {
+  if (ARTIS_OPT_RELDOPPLER(c)) {
     const double betasq = dot3(vel_rf, vel_rf) / CLIGHTSQUARED;
     dopplerfactor = dopplerfactor / sqrt(1 - betasq);
   }

@@ -405,7 +405,7 @@ ARTIS_DEV void do_nonthermal_predeposit_body(const Ctx &c, Pkt &p, const double 
   const double particle_en = H * p.nu_cmf;
   double endot = 0.;
   double t_absorb = ts;
-  if (!c.st.opt_instant_particle_deposition) {
+  if (!ARTIS_OPT_INSTANT_DEPOSITION(c)) {
     const double rho = (double)c.cs.rho[cell_mgi(c, p.where)];
     endot = (decaytype == ARTIS_DECAYTYPE_ALPHA) ? 5.e11 * MEV * rho : 4.e10 * MEV * rho;
     const double zrand = rng_uniform(rng);

@@ -545,7 +545,7 @@ ARTIS_DEV double get_event(const Ctx &c, const int mgi, Pkt &p, int *rpkt_eventt
       double ldist;
       if (d.nu_cmf <= nu_trans) {
         ldist = 0;
-      } else if (!c.st.opt_relativistic_doppler) {
+      } else if (!ARTIS_OPT_RELDOPPLER(c)) {
         ldist = CLIGHT * d.prop_time * (d.nu_cmf / nu_trans - 1);
       } else {
         const double nu_r = nu_trans / d.nu_rf;

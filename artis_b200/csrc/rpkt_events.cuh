@@ -65,7 +65,7 @@ ARTIS_DEV void update_estimators(const Ctx &c, const Pkt &p, const double distan
     }
   }
   // without a valid opacity scratch for this cell every contribution below is +0.0: nothing to add (grey cells)
-  if (kv && (!c.st.opt_no_lut_photoion || !c.st.opt_no_lut_bfheating)) {
+  if (kv && (!ARTIS_OPT_NOLUT_PHOTOION(c) || !ARTIS_OPT_NOLUT_BFHEATING(c))) {
     const int nelements = c.st.nelements, max_nions = c.st.max_nions;
     const double distance_e_cmf_over_nu = distance_e_cmf / nu;
     const int ng = c.st.nbfcontinua_ground;
@@ -78,10 +78,10 @@ ARTIS_DEV void update_estimators(const Ctx &c, const Pkt &p, const double distan
           const int ionestimindex = mgi * nelements * max_nions + element * max_nions + ion;
           const double contr = k.gamma_contr[i];
           if (contr == 0.) continue;  // adds +0.0 to both estimators
-          if (!c.st.opt_no_lut_photoion) {
+          if (!ARTIS_OPT_NOLUT_PHOTOION(c)) {
             tl.estim_atomics += est_add(&c.es.gammaestimator[ionestimindex], contr * distance_e_cmf_over_nu);
           }
-          if (!c.st.opt_no_lut_bfheating) {
+          if (!ARTIS_OPT_NOLUT_BFHEATING(c)) {
             tl.estim_atomics += est_add(&c.es.bfheatingestimator[ionestimindex], contr * distance_e_cmf * (1. - nu_edge / nu));
           }
         }

@@ -20,6 +20,17 @@ DEFAULT_LIB = os.environ.get("ARTIS_GPU_LIB", os.path.join(HERE, "libartis_gpu.s
 # compiled into a second library from the same sources. A VPKT_ON driver links this one instead.
 VPKT_LIB = os.path.join(HERE, "libartis_gpu_vpkt.so")
 ROWS_LIB = os.path.join(HERE, "libartis_gpu_rows.so")  # macro-atom / cooling rows on demand: models of ~1e5 cells and more
+# the switches of artisoptions_classic.h compiled in, as the reference compiles them in (7 % faster than testing them at
+# run time: the kernels are bound by instruction supply, profiles/r2_notes.md); chosen when the static tables carry exactly
+# that option set. ARTIS_GPU_GENERIC=1 keeps the run-time-option library for every mode.
+CLASSIC_LIB = os.path.join(HERE, "libartis_gpu_classic.so")
+
+
+def is_classic_option_set(static):
+    g = lambda k: int(np.asarray(static.get(k, 0)).reshape(-1)[0])  # noqa: E731
+    return (g("opt_grid_type") == 0 and not g("opt_nt_on") and not g("opt_nlte_pops_on") and not g("opt_no_lut_photoion")
+            and not g("opt_no_lut_bfheating") and not g("opt_relativistic_doppler") and g("opt_instant_particle_deposition")
+            and not g("opt_detailed_bf_estimators") and not g("opt_multibin_radfield") and not g("opt_vpkt_on"))
 
 
 class ArtisGpuError(RuntimeError):
@@ -57,7 +68,10 @@ class Transport:
         static["abi_version"] = abi.ABI_VERSION
         base = os.path.join(HERE, "libartis_gpu.so")
         want = VPKT_LIB if static.get("opt_vpkt_on") else base
-        if os.path.realpath(self.libpath) in (os.path.realpath(base), os.path.realpath(VPKT_LIB), os.path.realpath(ROWS_LIB)) and \
+        if want == base and is_classic_option_set(static) and os.path.exists(CLASSIC_LIB) and not os.environ.get("ARTIS_GPU_GENERIC"):
+            want = CLASSIC_LIB
+        if os.path.realpath(self.libpath) in (os.path.realpath(base), os.path.realpath(VPKT_LIB), os.path.realpath(ROWS_LIB),
+                                              os.path.realpath(CLASSIC_LIB)) and \
                 os.path.realpath(self.libpath) != os.path.realpath(want):
             if not os.path.exists(want):
                 raise ArtisGpuError(f"{want} not found: build it with __graft_entry__.build() (there is no CPU fallback)")
@@ -67,7 +81,8 @@ class Transport:
         self._keep.append(keep)
         self.static = static
         rc = self.lib.artis_gpu_init(C.byref(st), device, rank, nranks, C.c_ulonglong(seed))
-        if rc == abi.ERR_UNSUPPORTED and os.path.realpath(self.libpath) == os.path.realpath(base) and os.path.exists(ROWS_LIB):
+        if rc == abi.ERR_UNSUPPORTED and os.path.realpath(self.libpath) in (os.path.realpath(base), os.path.realpath(CLASSIC_LIB)) \
+                and os.path.exists(ROWS_LIB):
             buf = C.create_string_buffer(1024)
             self.lib.artis_gpu_last_error(buf, 1024)
             if b"libartis_gpu_rows.so" in buf.value:  # the model is too large for dense rows (or ARTIS_TABLES=sparse)

@@ -140,3 +140,37 @@ def test_scheduler_variants_give_identical_packets(gpu_lib, fixture_name):
         T.finalize()
     for name in outs[0].dtype.names:
         assert np.array_equal(outs[0][name], outs[1][name], equal_nan=True), ("two-kernel", name)
+
+
+def test_classic_build_and_runtime_option_build_agree(gpu_lib, monkeypatch):
+    """libartis_gpu_classic.so (the switches of artisoptions_classic.h compiled in; what Transport picks for that option
+    set) against libartis_gpu.so (every switch a run-time field) on a classic fixture: the probes hold for both, and the
+    same seeded packets live the same lives (two builds of the sources: a few packets in a hundred see a last-bit
+    difference of a contracted multiply-add and part ways somewhere in a thousand events)"""
+    from artis_b200 import transport
+    fx = goldenlib.load_fixture("classic_nogrey_ts12.npz")
+    outs = []
+    for generic in (False, True):
+        if generic:
+            monkeypatch.setenv("ARTIS_GPU_GENERIC", "1")
+        T = _ready(gpu_lib, fx, seed=4242)
+        want = transport.DEFAULT_LIB if generic else transport.CLASSIC_LIB
+        assert T.libpath == want, (T.libpath, want)
+        probelib.check_probes(T, fx, "gpu")
+        pk = fx["pre"].copy()
+        T.update_packets(pk)
+        outs.append((pk, T.download_estimators()))
+        T.finalize()
+    (a, ea), (b, eb) = outs
+    same = (a["type"] == b["type"]) & (a["where"] == b["where"]) & (a["interactions"] == b["interactions"])
+    print("same history", same.mean())
+    assert same.mean() > 0.97
+    assert np.allclose(a["nu_cmf"][same], b["nu_cmf"][same], rtol=1e-6)
+    # and the classic build refuses another option set instead of mis-running it
+    neb = goldenlib.load_fixture("nebular_nlte_ts8.npz")
+    Tc = Transport(transport.CLASSIC_LIB)
+    st = dict(neb["static"])
+    st["abi_version"] = abi.ABI_VERSION
+    s, keep = abi.build_struct(abi.ArtisStaticTables, abi.STATIC_FIELDS, st)
+    import ctypes as C
+    assert Tc.lib.artis_gpu_init(C.byref(s), 0, 0, 1, C.c_ulonglong(1)) == abi.ERR_UNSUPPORTED

@@ -23,11 +23,13 @@ from artis_b200.transport import Transport
 FIXTURES = ["classic_nogrey_ts12.npz", "nebular_nlte_ts8.npz"]
 
 
-def run(lib, fx, mode, arena_mb=None, seed=99, geometry=None):
-    old = {k: os.environ.get(k) for k in ("ARTIS_TABLES", "ARTIS_ROW_ARENA_MB")}
+def run(lib, fx, mode, arena_mb=None, seed=99, soft_mb=None):
+    old = {k: os.environ.get(k) for k in ("ARTIS_TABLES", "ARTIS_ROW_ARENA_MB", "ARTIS_ROW_SOFT_MB")}
     os.environ["ARTIS_TABLES"] = mode
     if arena_mb is not None:
         os.environ["ARTIS_ROW_ARENA_MB"] = str(arena_mb)
+    if soft_mb is not None:
+        os.environ["ARTIS_ROW_SOFT_MB"] = str(soft_mb)
     try:
         T = Transport(lib)
         T.init(fx["static"], seed=seed)
@@ -81,11 +83,11 @@ def check_identical(lib, name, probe_mode):
     Ts.finalize()
 
 
-def check_flushes(lib, name, arena_mb):
+def check_flushes(lib, name, arena_mb, soft_mb=None):
     fx = goldenlib.load_fixture(name)
     Td, pd, ed = run(lib, fx, "dense")
     Td.finalize()
-    Ts, ps, es = run(lib, fx, "sparse", arena_mb=arena_mb)
+    Ts, ps, es = run(lib, fx, "sparse", arena_mb=arena_mb, soft_mb=soft_mb)
     c = es["counters"]
     print(name, "arena", arena_mb, "MB: flushes", int(c[abi.CTR_ROW_FLUSHES]), "row bytes built", int(c[abi.CTR_ROW_UNITS]) * 128)
     assert c[abi.CTR_ROW_FLUSHES] >= 2
@@ -120,8 +122,9 @@ def test_cuda_rows_on_demand_identical_to_dense(gpu_lib, name):
 
 @pytest.mark.gpu
 def test_cuda_rows_on_demand_survive_arena_flushes(gpu_lib):
-    # the smallest arena the library accepts on the device is twice the reserve for rows under construction
-    check_flushes(gpu_lib, FIXTURES[0], 1)
+    # the arena the library accepts on the device is at least twice the reserve for rows under construction (hundreds of
+    # MB); the restart threshold is lowered instead
+    check_flushes(gpu_lib, FIXTURES[0], 1, soft_mb=0.004)
 
 
 # ---- config 4 in small: every non-empty propagation cell its own model cell (tools/model3d.py) -------------------------
