@@ -314,6 +314,16 @@ struct CellTables {
   int *row_stop;                  // set when row_top has passed row_soft
 };
 
+// VPKT_ON, deferred ray trace (vpkt.cuh): what an event leaves behind for its virtual packets -- the packet as
+// it was at the event, 128 bytes. The persistent scheduler appends these to a list; k_vpkt_trace traces them afterwards.
+struct alignas(16) VpktReq {
+  int where, last_cross, next_trans, realtype;  // realtype 1 electron scattering, 2 k-packet -> r-packet, 3 macro-atom
+  double pos[3], dir[3];                        // dir: the direction the packet ARRIVED with (only realtype 1 reads it)
+  double e_cmf, nu_cmf, prop_time, stokes_q, stokes_u;
+  double pad_[3];
+};
+static_assert(sizeof(VpktReq) == 128, "VpktReq is one 128-byte line");
+
 struct Ctx {
   ArtisStaticTables st;   // pointers are device addresses
   ArtisCellState cs;      // 〃
@@ -342,6 +352,12 @@ struct Ctx {
   double ts_width;
   double t_mid;
   int *error_flag;           // set non-zero by a packet that hits a reference abort() branch
+  // VPKT_ON with the barrier-free scheduler: the request list (nullptr: rays are traced where their events happen)
+  VpktReq *vreq;
+  unsigned long long *vreq_n;   // requests appended so far
+  int *vreq_stop;               // set when the list has passed vreq_soft: the scheduler drains, the list is traced, and the
+  unsigned long long vreq_cap;  // unfinished packets are launched again (engine.inc)
+  unsigned long long vreq_soft;
 };
 
 // Build-mode switches as the device code tests them. They are run-time flags of the static tables (one library serves

@@ -115,11 +115,15 @@ ARTIS_DEV bool hot_active(const Ctx &c, const PktHot &h) { return pkt_lo16(h.typ
 ARTIS_DEV int bucket_key(const Ctx &c, const PktHot &h) {
   return kind_of(c, pkt_lo16(h.type_cross), h.where) * (c.st.npts_model + 1) + cell_mgi(c, h.where);
 }
-ARTIS_DEV void body_bucket_hist(const Ctx &c, PktHot *hot, PktCold *cold, const int idx, int *counts) {
+// `fresh`: the first launch of a timestep. A relaunch after the row arena has filled (rows on demand, engine.inc) buckets the
+// packets that have not finished and leaves their interaction counts and random streams where they are.
+ARTIS_DEV void body_bucket_hist(const Ctx &c, PktHot *hot, PktCold *cold, const int idx, int *counts, const bool fresh) {
   PktHot &h = hot[idx];
-  h.interactions = 0;  // update_packets.cc:282-285, for every packet including the escaped ones
-  cold[idx].scat_count = 0;
-  h.rngctr = 0u;       // each packet's Philox stream restarts with the timestep
+  if (fresh) {
+    h.interactions = 0;  // update_packets.cc:282-285, for every packet including the escaped ones
+    cold[idx].scat_count = 0;
+    h.rngctr = 0u;       // each packet's Philox stream restarts with the timestep
+  }
   if (hot_active(c, h)) int_add(&counts[bucket_key(c, h)], 1);
 }
 // exclusive prefix sum over the (kind, cell) counts, one thread (host build; the device has k_bucket_scan); also the size

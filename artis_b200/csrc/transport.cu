@@ -301,6 +301,22 @@ constexpr int RMS = artis::RING_META_STRIDE;
 #ifndef ARTIS_KAPPA_OFFLOAD
 #define ARTIS_KAPPA_OFFLOAD 0
 #endif
+// Virtual packets in the barrier-free scheduler. ARTIS_VPKT_DEFER 1 (default): events record their requests and k_vpkt_trace
+// traces the list when the scheduler has finished; 0: the rays are traced inside the transport kernel, right after the event --
+// ARTIS_VPKT_COOP 1: by the whole warp when few lanes have a request (vpkt.cuh coop_vpkt_flush), 0: by the lane alone.
+// ARTIS_VPKT_TRACE_COOP 1: k_vpkt_trace gives a request to a warp, 0 (default): to a thread.
+#ifndef ARTIS_VPKT_DEFER
+#define ARTIS_VPKT_DEFER 1
+#endif
+#ifndef ARTIS_VPKT_COOP
+#define ARTIS_VPKT_COOP 1
+#endif
+#ifndef ARTIS_VPKT_TRACE_COOP
+#define ARTIS_VPKT_TRACE_COOP 0
+#endif
+#ifndef ARTIS_VPKT_TRACE_MINBLOCKS
+#define ARTIS_VPKT_TRACE_MINBLOCKS 4
+#endif
 #ifndef ARTIS_REFILL_BACKOFF
 #define ARTIS_REFILL_BACKOFF 10
 #endif
@@ -605,7 +621,15 @@ __device__ __forceinline__ void coop_bfest_flush(const artis::Ctx &c, artis::Kap
 // rows on demand (celltables.cuh row_get): true once the row arena has passed its soft limit. The warps then put the
 // packets they hold back into the hot array and leave; the host forgets the rows and launches the scheduler again on the
 // packets that have not finished (engine.inc artis_gpu_transport_resident). Warp-uniform.
+// The same exit serves the virtual-packet request list when it has passed its soft limit (vpkt.cuh vpkt_enqueue).
 __device__ __forceinline__ bool row_arena_stop(const artis::Ctx &c, const int lane) {
+#if !defined(ARTIS_NO_VPKT) && ARTIS_VPKT_DEFER
+  if (ARTIS_OPT_VPKT(c)) {
+    int vstop = 0;
+    if (lane == 0) vstop = *reinterpret_cast<volatile int *>(c.vreq_stop);
+    if (__shfl_sync(0xffffffffu, vstop, 0) != 0) return true;
+  }
+#endif
   if (!artis::rows_on_demand(c)) return false;
   int stop = 0;
   if (lane == 0) stop = *reinterpret_cast<volatile int *>(c.tb.row_stop);
@@ -791,7 +815,14 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
           break;
       }
     }
-    if (ARTIS_OPT_VPKT(c) && have) vpkt_flush_request(c, p, k, tl);  // the one call site of the virtual-packet ray trace
+#if !defined(ARTIS_NO_VPKT) && ARTIS_VPKT_DEFER
+    // virtual packets: the event has left a request; it is recorded for k_vpkt_trace and the packet goes on (vpkt.cuh)
+    if (ARTIS_OPT_VPKT(c) && vpkt_enqueue(c, have, p, tl)) k.valid = false;
+#elif !defined(ARTIS_NO_VPKT) && ARTIS_VPKT_COOP
+    if (ARTIS_OPT_VPKT(c)) coop_vpkt_flush(c, have, p, k, tl);  // A/B builds: the rays traced here, by the whole warp / side by side
+#else
+    if (ARTIS_OPT_VPKT(c) && have) vpkt_flush_request(c, p, k, tl);  // A/B builds: one lane traces its rays alone
+#endif
     bool done = false;
     int k2 = -1;
     if (have && parked) {
@@ -1051,9 +1082,32 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_light(P
   stats_block_flush(c);
 }
 
-__global__ void k_bucket_hist(PktHot *hot, PktCold *cold, int n, int *counts) {
+// VPKT_ON: the virtual packets of the requests the scheduler's events have recorded (vpkt.cuh). One request per thread (its
+// rays towards the observers one after the other, the start cell's opacity shared between them), or per warp.
+#ifndef ARTIS_NO_VPKT
+__global__ void __launch_bounds__(128, ARTIS_VPKT_TRACE_MINBLOCKS) k_vpkt_trace(const artis::VpktReq *req, const long long n) {
+  using namespace artis;
+  const Ctx &c = d_ctx;
+  Tally tl = {};
+  stats_block_begin();
+  constexpr bool COOP = ARTIS_VPKT_TRACE_COOP != 0;
+  const long long unit = COOP ? 32 : 1;
+  const long long stride = (long long)gridDim.x * blockDim.x / unit;
+  for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / unit; i < n; i += stride) {
+    VpktReq r;
+    const uint4 *src = reinterpret_cast<const uint4 *>(req + i);
+    uint4 *dst = reinterpret_cast<uint4 *>(&r);
+#pragma unroll
+    for (int q = 0; q < 8; q++) dst[q] = __ldcg(src + q);
+    vpkt_trace_request<COOP>(c, r, tl);
+  }
+  tally_flush(c, tl);
+  stats_block_flush(c);
+}
+#endif
+__global__ void k_bucket_hist(PktHot *hot, PktCold *cold, int n, int *counts, bool fresh) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    artis::body_bucket_hist(d_ctx, hot, cold, i, counts);
+    artis::body_bucket_hist(d_ctx, hot, cold, i, counts, fresh);
 }
 // exclusive prefix sum over the (kind, cell) counts, one 1024-thread block per kind (a 3D model has a model cell per
 // propagation cell: 1e6 counts per kind); also the size of each kind's queue
@@ -1326,8 +1380,8 @@ void be_run_escaped_scatter(const PktHot *hot, const PktCold *cold, long long n,
   const int nchunks = (int)((n + artis::ESC_CHUNK - 1) / artis::ESC_CHUNK);
   if (nchunks > 0) k_escaped_scatter<<<nchunks, artis::ESC_CHUNK, 0, g_stream>>>(hot, cold, n, reported, only_new, offsets, out);
 }
-void be_run_bucket(PktHot *hot, PktCold *cold, int n, int *buckets, int *kind_sizes, int *const *queues) {
-  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(hot, cold, n, buckets);
+void be_run_bucket(PktHot *hot, PktCold *cold, int n, int *buckets, int *kind_sizes, int *const *queues, bool fresh) {
+  k_bucket_hist<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(hot, cold, n, buckets, fresh);
   k_bucket_scan<<<artis::NKIND, 1024, 0, g_stream>>>(buckets, kind_sizes);
   k_bucket_scatter<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(hot, n, buckets, queues);
 }
@@ -1405,6 +1459,24 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
   return true;
 }
 void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }
+// VPKT_ON: trace the n recorded requests (on the transport stream, inside the timed region of the timestep)
+void be_run_vpkt_trace(const artis::VpktReq *req, long long n) {
+#ifndef ARTIS_NO_VPKT
+  if (n <= 0) return;
+  const long long unit = ARTIS_VPKT_TRACE_COOP != 0 ? 32 : 1;
+  long long blocks = (n * unit + 127) / 128;
+  const long long most = (long long)g_sms * 16;  // grid-stride beyond that
+  if (blocks > most) blocks = most;
+  k_vpkt_trace<<<(unsigned)blocks, 128, 0, g_stream>>>(req, n);
+#endif
+}
+bool be_vpkt_deferred() {
+#if !defined(ARTIS_NO_VPKT) && ARTIS_VPKT_DEFER
+  return true;
+#else
+  return false;
+#endif
+}
 void be_set_scheduler_kernels(int n) {
   if (n == 1 || (n == 2 && g_blocks_jump >= 1)) g_scheduler_kernels = n;
 }

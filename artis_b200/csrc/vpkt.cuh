@@ -84,55 +84,257 @@ ARTIS_DEV void add_to_vpkt_grid(const Ctx &c, const double nu_rf, const double e
 // start cell. A departure ratio that the start cell never needed is evaluated from the start cell's populations with the
 // current cell's n_e and T_e, as the reference does on first use (rpkt.cc:1136-1145; later uses of that cached value by
 // other cells are not tracked -- it only arises for continua absent from the start cell).
-ARTIS_DEV void vpkt_kappa_cont(const Ctx &c, const Pkt &d, const int mgi, const int tc0, KappaCache &k, Tally &tl) {
-  const double nu = d.nu_cmf;
-  if (kappa_cache_hit(k, mgi, nu)) return;
-  tl.kappa_evals++;
-  double sigma = 0., kappa_ff = 0., kappa_bf = 0., kappa_ffheating = 0.;
+// One term of that bound-free sum (0 when the continuum is skipped): `tc` = table row of the current cell, `tc0` of the
+// start cell.
+ARTIS_DEV double vpkt_bf_term(const Ctx &c, const int tc, const int tc0, const int mgi, const int i, const double nu, const double T_e,
+                              const double expfac) {
+  if (c.tb.bf_cell[2 * ((size_t)tc * c.st.nbfcontinua + i)] < 0.) return 0.;  // absent from the current cell
+  const int gl = c.cont_level_g[i];
+  const double nnlevel = tab_levelpop(c, tc0, gl);
+  const ContRec r = c.cont_rec[i];
+  if (!(nnlevel > 0.) || !(nu <= r.nu_edge * c.st.last_phixs_nuovernuedge)) return 0.;
+  const double *start = c.tb.bf_cell + 2 * ((size_t)tc0 * c.st.nbfcontinua + i);
+  double departure_ratio;
+  if (start[0] > 0.) {
+    departure_ratio = start[1];
+  } else {
+    const int glu = c.cont_upper_g[i];
+    const double sf = calculate_sahafact_g(c, gl, glu, T_e, H * r.nu_edge);
+    departure_ratio = tab_levelpop(c, tc0, glu) / nnlevel * (double)c.cs.nne[mgi] * sf;
+  }
+  const double sigma_bf = phixs_fromtable(c, r.tablerow, r.nu_edge, nu, r.inv_nu_edge);
+  double corrfactor = 1 - departure_ratio * expfac;
+  if (corrfactor < 0) corrfactor = 0.;
+  return nnlevel * sigma_bf * r.probability * corrfactor;
+}
+// ---- the ray trace, written once for two executions ---------------------------------------------------------------------------
+//   COOP = false  one thread traces the ray (the host build, the kernel-per-kind scheduler, and a lane of the persistent kernels
+//                 when most lanes of its warp have rays of their own to trace: 32 rays side by side);
+//   COOP = true   all 32 lanes of a warp trace ONE ray (device only; the persistent kernels when few lanes have a request).
+//                 Every lane carries the same copy of the ray -- the geometry (boundary_cross, move_pkt, the frame transforms)
+//                 is computed redundantly and costs what it costs one lane -- and the two loops that are a ray's work are
+//                 shared out: the bound-free sum of a cell's continuum opacity, a tile of 32 continua at a time, and the line
+//                 sweep of a cell, 32 consecutive list entries at a time (a lane per line evaluates the distance to its
+//                 resonance point and its Sobolev depth: five dependent table reads, 32 chains in flight instead of one).
+// Both give the same bits: the bound-free sum runs in the tile order of rpkt.cuh (tiles of BF_TILE consecutive continua
+// reduced as a binary tree -- PairTree for one thread, shuffle-down 1, 2, 4, 8, 16 for a warp -- tile sums added in order), and
+// the Sobolev depths are added IN LIST ORDER with the tau_max test after each one, as vpkt.cc:283-292 does (a warp adds them
+// from shuffled operands, every lane the same sums).
+//
+// Two things the reference does not do, neither of which changes a result:
+//  (1) The continuum opacity of the START cell at the packet's frequency is the same for every observer of a request; it is
+//      evaluated once (VpktKappa `first`) instead of once per ray. The reference's per-ray cache reset (vpkt.cc:887) would
+//      recompute the identical number from identical inputs.
+//  (2) Lines first. A ray is abandoned as soon as every spectrum's optical depth exceeds tau_max, and most rays of a
+//      supernova model die on the lines of their second or third cell. Before paying for a cell's ~900-term continuum sum the
+//      cell's line sweep is run on a COPY of the optical depths without the continuum term: if that alone passes tau_max for
+//      every spectrum, so does the reference's own sequence -- floating-point addition is monotone, so adding the
+//      (non-negative) continuum term first can only leave every later partial sum at least as large -- and the ray is dead
+//      either way: it is dropped without the sum. A ray that survives the probe evaluates the sum and repeats the sweep in
+//      the reference's order. The work counters count the real sweep only.
+// -DARTIS_VPKT_PROFILE: where a ray's cycles go (measurement builds only): counters[51..58] = cycles in set-up, boundary_cross,
+// the probe sweep, the continuum sum, the real sweep, the move, the binning; counters[59] = rays, [60] = cells
+#if defined(ARTIS_VPKT_PROFILE) && defined(__CUDA_ARCH__)
+#define VP_T0() long long vp_t = clock64()
+#define VP_ADD(slot)                                                                       \
+  do {                                                                                     \
+    const long long vp_n = clock64();                                                      \
+    if (lead) atomicAdd((unsigned long long *)&c.es.counters[slot], (unsigned long long)(vp_n - vp_t)); \
+    vp_t = vp_n;                                                                           \
+  } while (0)
+#define VP_COUNT(slot) \
+  if (lead) atomicAdd((unsigned long long *)&c.es.counters[slot], 1ull)
+#else
+#define VP_T0()
+#define VP_ADD(slot)
+#define VP_COUNT(slot)
+#endif
+struct VpktKappa {  // the opacity scratch of a ray: KappaCache without the ground-continuum array nobody reads here
+  bool valid;
+  int mgi;
+  double nu, total, es, ff, bf;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ int vp_popc(const unsigned m) { return __popc(m); }
+__device__ __forceinline__ int vp_ctz(const unsigned m) { return __ffs(m) - 1; }
+template <bool COOP>
+__device__ __forceinline__ int vp_lane() {
+  return COOP ? (int)(threadIdx.x & 31) : 0;
+}
+template <bool COOP>
+__device__ __forceinline__ unsigned vp_ballot(const bool pred) {
+  return COOP ? __ballot_sync(0xffffffffu, pred) : (pred ? 1u : 0u);
+}
+template <bool COOP>
+__device__ __forceinline__ double vp_shfl(const double v, const int src) {
+  return COOP ? __shfl_sync(0xffffffffu, v, src) : v;
+}
+template <bool COOP>
+__device__ __forceinline__ int vp_shfl_i(const int v, const int src) {
+  return COOP ? __shfl_sync(0xffffffffu, v, src) : v;
+}
+#else
+inline int vp_popc(const unsigned m) { return __builtin_popcount(m); }
+inline int vp_ctz(const unsigned m) { return __builtin_ctz(m); }
+template <bool COOP>
+inline int vp_lane() {
+  return 0;
+}
+template <bool COOP>
+inline unsigned vp_ballot(const bool pred) {
+  return pred ? 1u : 0u;
+}
+template <bool COOP>
+inline double vp_shfl(const double v, const int) {
+  return v;
+}
+template <bool COOP>
+inline int vp_shfl_i(const int v, const int) {
+  return v;
+}
+#endif
+
+template <bool COOP>
+ARTIS_DEV void vpkt_kappa_cont(const Ctx &c, const double nu, const int mgi, const int tc0, VpktKappa &k, Tally &tl) {
+  const bool lead = vp_lane<COOP>() == 0;
+  if (k.valid && (mgi == k.mgi) && (fabs(k.nu / nu - 1.0) < 1e-4)) return;  // rpkt.cuh kappa_cache_hit
+  if (lead) tl.kappa_evals++;
+  double sigma = 0., kappa_ff = 0., kappa_bf = 0.;
   if (c.st.do_r_lc) {
     if (c.st.opacity_case == 4) {
       sigma = SIGMA_T * c.cs.nne[mgi];
       kappa_ff = calculate_kappa_ff(c, mgi, nu);
-      kappa_ffheating = kappa_ff;
       const int tc = tabcell(c, mgi);
       const double T_e = (double)c.cs.Te[mgi];
       const double expfac = exp(-HOVERKB * nu / T_e);
       const int i0 = bf_stop_index(c, nu);
       const int ilo = bf_start_index(c, nu, i0);
-      tl.bf_evaluated += i0 - ilo;
-      for (int i = ilo; i < i0; i++) {
-        if (c.tb.bf_cell[2 * ((size_t)tc * c.st.nbfcontinua + i)] < 0.) continue;  // absent from the current cell
-        const int gl = c.cont_level_g[i];
-        const double nnlevel = tab_levelpop(c, tc0, gl);
-        const ContRec r = c.cont_rec[i];
-        if (!(nnlevel > 0.) || !(nu <= r.nu_edge * c.st.last_phixs_nuovernuedge)) continue;
-        const double *start = c.tb.bf_cell + 2 * ((size_t)tc0 * c.st.nbfcontinua + i);
-        double departure_ratio;
-        if (start[0] > 0.) {
-          departure_ratio = start[1];
-        } else {
-          const int glu = c.cont_upper_g[i];
-          const double sf = calculate_sahafact_g(c, gl, glu, T_e, H * r.nu_edge);
-          departure_ratio = tab_levelpop(c, tc0, glu) / nnlevel * (double)c.cs.nne[mgi] * sf;
+      if (lead) tl.bf_evaluated += i0 - ilo;
+#ifdef __CUDACC__
+      if constexpr (COOP) {
+        const int lane = vp_lane<COOP>();
+        for (int base = ilo; base < i0; base += BF_TILE) {
+          const int i = base + lane;
+          double t = (i < i0) ? vpkt_bf_term(c, tc, tc0, mgi, i, nu, T_e, expfac) : 0.;
+#pragma unroll
+          for (int off = 1; off < BF_TILE; off <<= 1) t += __shfl_down_sync(0xffffffffu, t, off);
+          kappa_bf += t;  // lane 0 holds the tile sums in tree order
         }
-        const double sigma_bf = phixs_fromtable(c, r.tablerow, r.nu_edge, nu, r.inv_nu_edge);
-        double corrfactor = 1 - departure_ratio * expfac;
-        if (corrfactor < 0) corrfactor = 0.;
-        kappa_bf += nnlevel * sigma_bf * r.probability * corrfactor;
+        kappa_bf = __shfl_sync(0xffffffffu, kappa_bf, 0);
+      } else
+#endif
+      {
+        const int iend = ilo + ((i0 - ilo + BF_TILE - 1) / BF_TILE) * BF_TILE;  // the last tile is padded with zero terms
+        PairTree tree;
+        for (int i = ilo; i < iend; i++) {
+          const double t = (i < i0) ? vpkt_bf_term(c, tc, tc0, mgi, i, nu, T_e, expfac) : 0.;
+          double tile_sum;
+          if (tree.push((i - ilo) & (BF_TILE - 1), t, &tile_sum)) kappa_bf += tile_sum;
+        }
       }
     } else {
       kappa_ff = 1e5 * calculate_kappa_ff(c, mgi, nu);
     }
   }
-  for (int g = 0; g < c.st.nbfcontinua_ground; g++) k.gamma_contr[g] = 0.;  // no estimator reads it for a virtual packet
-  kappa_store(c, k, mgi, nu, sigma, kappa_ff, kappa_bf, kappa_ffheating, tl);
+  k.nu = nu;  // rpkt.cuh kappa_store
+  k.mgi = mgi;
+  k.valid = true;
+  k.total = sigma + kappa_bf + kappa_ff;
+  k.es = sigma;
+  k.ff = kappa_ff;
+  k.bf = kappa_bf;
+  if (!isfinite(k.total)) {  // rpkt.cc:1280-1294 soft fallback
+    if (isfinite(k.es)) {
+      k.ff = 0.;
+      k.bf = 0.;
+      k.total = k.es;
+      if (lead) tl.soft_repairs++;
+    } else {
+      fatal(c, 101);
+    }
+  }
 }
 
-// vpkt.cc:76-364 rlc_emiss_vpkt. `pk` is the real packet (read only), `k` the opacity scratch of this thread (the
-// reference's globals::kappa_rpkt_cont[tid], shared between the real packet and its virtual packets). Returns the
-// change of the virtual-packet counters: bit 0 = a virtual packet was created, bit 1 = it reached the edge of the grid.
-ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u, const double t_current,
-                             const int bin, double *obs, const int realtype, KappaCache &k, Tally &tl) {
+// vpkt.cc:254-303, the `while (ldist < sdist)` loop of one cell: adds the Sobolev depth of every line the ray redshifts through
+// on its way across the cell (path sdist, entered at co-moving frequency nu_cmf) to the spectra's optical depths, in list
+// order from list entry next_trans on; returns true as soon as every spectrum has passed tau_max (the ray is dead).
+// W list entries per round: 1 for one thread, 32 for a warp.
+template <bool COOP>
+ARTIS_DEV bool vpkt_line_sweep(const Ctx &c, const double nu_cmf, const double t_current, const double sdist, const int tc0,
+                               int &next_trans, double *tau_vpkt, Tally &tl, const bool count) {
+  if (!(0. < sdist)) return false;
+  const int lane = vp_lane<COOP>();
+  const int nspectra = c.st.vpkt_nspectra;
+  const int right = c.st.nlines - 1;
+  while (true) {
+    // closest_transition (rpkt.cuh): no line left at this frequency, or the list is exhausted. (The reference stores
+    // nlines + 1 and keeps looping with ldist unchanged, vpkt.cc:297-300, which does not terminate; it is only reached by a
+    // packet redder than the reddest line. No line is left in this or any later cell: the sweep ends.)
+    if (nu_cmf < c.st.line_nu[right] || next_trans > right) {
+      next_trans = c.st.nlines + 1;
+      return false;
+    }
+    int first = next_trans;
+    if (first <= 0) first = (nu_cmf >= c.st.line_nu[0]) ? 0 : linelist_lower_bound(c, first, nu_cmf);
+    const int lineindex = first + lane;
+    const bool inlist = lineindex <= right;
+    double nutrans = 1., ldist = 0.;
+    if (inlist) {
+      nutrans = c.st.line_nu[lineindex];
+      ldist = (nu_cmf < nutrans) ? 0. : CLIGHT * t_current * (nu_cmf / nutrans - 1);
+    }
+    const int nlist = vp_popc(vp_ballot<COOP>(inlist));
+    // the entry that ends the sweep: the first one beyond the cell (not consumed) or exactly on its edge (consumed)
+    const unsigned stop = vp_ballot<COOP>(inlist && !(ldist < sdist));
+    int consumed = nlist;
+    bool ends = false, beyond = false;
+    if (stop != 0u) {
+      const int s = vp_ctz(stop);
+      beyond = vp_shfl<COOP>(ldist, s) > sdist;
+      consumed = beyond ? s : s + 1;
+      ends = true;
+    }
+    double dtau = 0.;
+    int anumber = 0;
+    if (lane < consumed) {
+      const double t_line = t_current + ldist / CLIGHT;
+      const int glu = c.line_upper_g[lineindex], gll = c.line_lower_g[lineindex];
+      const double A_ul = (double)c.st.line_einstein_A[lineindex];
+      const double B_ul = CLIGHTSQUAREDOVERTWOH / pow(nutrans, 3) * A_ul;
+      const double B_lu = (double)c.st.lev_statweight[glu] / (double)c.st.lev_statweight[gll] * B_ul;
+      const double n_u = tab_levelpop(c, tc0, glu);
+      const double n_l = tab_levelpop(c, tc0, gll);
+      anumber = c.st.el_anumber[c.st.line_element[lineindex]];
+      dtau = (B_lu * n_l - B_ul * n_u) * HCLIGHTOVERFOURPI * t_line;
+    }
+    if (count && lane == 0) {
+      tl.lines_scanned += consumed + (beyond ? 1 : 0);
+      tl.lines_tau += consumed;
+    }
+    for (int j = 0; j < consumed; j++) {  // in list order, with the test after every line
+      const double v = vp_shfl<COOP>(dtau, j);
+      const int a = vp_shfl_i<COOP>(anumber, j);
+      for (int ind = 0; ind < nspectra; ind++) {
+        const double ex = c.st.vpkt_exclude[ind];
+        if (ex != -1 && ((double)a != ex)) tau_vpkt[ind] += v;
+      }
+      if (vpkt_check_tau(c, tau_vpkt) == 0) return true;
+    }
+    next_trans = first + consumed;
+    if (ends) return false;
+  }
+}
+
+// vpkt.cc:76-364 rlc_emiss_vpkt. `pk` is the real packet (read only), `k` the opacity scratch of the request, `first` the
+// start cell's opacity shared by the request's rays. Returns the change of the virtual-packet counters: bit 0 = a virtual
+// packet was created, bit 1 = it reached the edge of the grid. COOP: warp-uniform arguments and result.
+template <bool COOP>
+ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u,
+                                      const double t_current, const int bin, double *obs, const int realtype, VpktKappa &k,
+                                      VpktKappa &first, Tally &tl) {
+  const bool lead = vp_lane<COOP>() == 0;
+  VP_T0();
+  VP_COUNT(59);
   const int nspectra = c.st.vpkt_nspectra;
   double tau_vpkt[VPKT_MAX_SPECTRA];
   for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_vpkt[ind] = 0;
@@ -182,13 +384,31 @@ ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q,
     pn = 1 / (4 * PI);
   }
   int mgi = cell_mgi(c, dummy.where);
-  const int tc0 = tabcell(c, mgi);  // level populations of the whole ray come from the start cell (see vpkt_kappa_cont)
+  const int tc0 = tabcell(c, mgi);  // level populations of the whole ray come from the start cell (see vpkt_bf_term)
+  bool at_start = true;
+  k.valid = false;  // cellhistory_reset(mgi, false) at vpkt.cc:887: a ray starts without a cached opacity ...
+  if (first.valid) k = first;  // ... and would evaluate exactly this one first
+  VP_ADD(51);
   while (!end_packet) {
-    double ldist = 0;
+    VP_COUNT(60);
     int snext = 0;
     const double sdist = boundary_cross(c, dummy, &snext);
     const double s_cont = sdist * t_current * t_current * t_current / (t_future * t_future * t_future);
-    vpkt_kappa_cont(c, dummy, mgi, tc0, k, tl);
+    VP_ADD(52);
+    {  // lines first (see above): the cell's sweep on a copy, without the continuum term
+      double tau_probe[VPKT_MAX_SPECTRA];
+      for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_probe[ind] = tau_vpkt[ind];
+      int next_probe = dummy.next_trans;
+      const bool dead = vpkt_line_sweep<COOP>(c, dummy.nu_cmf, t_current, sdist, tc0, next_probe, tau_probe, tl, false);
+      VP_ADD(53);
+      if (dead) return 1;
+    }
+    vpkt_kappa_cont<COOP>(c, dummy.nu_cmf, mgi, tc0, k, tl);
+    VP_ADD(54);
+    if (at_start) {
+      first = k;
+      at_start = false;
+    }
     const double kap_cont = k.total;
     const double kap_cont_nobf = kap_cont - k.bf, kap_cont_noff = kap_cont - k.ff, kap_cont_noes = kap_cont - k.es;
     for (int ind = 0; ind < nspectra; ind++) {
@@ -203,42 +423,10 @@ ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q,
         tau_vpkt[ind] += kap_cont * s_cont;
     }
     if (vpkt_check_tau(c, tau_vpkt) == 0) return 1;
-    while (ldist < sdist) {
-      const int lineindex = closest_transition(c, dummy.nu_cmf, dummy.next_trans);
-      if (lineindex >= 0) {
-        tl.lines_scanned++;
-        const double nutrans = c.st.line_nu[lineindex];
-        dummy.next_trans = lineindex + 1;
-        if (dummy.nu_cmf < nutrans) {
-          ldist = 0;
-        } else {
-          ldist = CLIGHT * t_current * (dummy.nu_cmf / nutrans - 1);
-        }
-        if (ldist > sdist) {  // the line lies in the next cell: start there with this line
-          dummy.next_trans -= 1;
-          break;
-        }
-        tl.lines_tau++;
-        const double t_line = t_current + ldist / CLIGHT;
-        const int glu = c.line_upper_g[lineindex], gll = c.line_lower_g[lineindex];
-        const double A_ul = (double)c.st.line_einstein_A[lineindex];
-        const double B_ul = CLIGHTSQUAREDOVERTWOH / pow(nutrans, 3) * A_ul;
-        const double B_lu = (double)c.st.lev_statweight[glu] / (double)c.st.lev_statweight[gll] * B_ul;
-        const double n_u = tab_levelpop(c, tc0, glu);
-        const double n_l = tab_levelpop(c, tc0, gll);
-        const int anumber = c.st.el_anumber[c.st.line_element[lineindex]];
-        for (int ind = 0; ind < nspectra; ind++) {
-          const double ex = c.st.vpkt_exclude[ind];
-          if (ex != -1 && ((double)anumber != ex)) tau_vpkt[ind] += (B_lu * n_l - B_ul * n_u) * HCLIGHTOVERFOURPI * t_line;
-        }
-        if (vpkt_check_tau(c, tau_vpkt) == 0) return 1;
-      } else {
-        // The reference sets next_trans = nlines + 1 and keeps looping with ldist unchanged (vpkt.cc:297-300), which
-        // does not terminate; it is only reached by a packet redder than the reddest line of the list. No line is left
-        // in this or any later cell, so the sweep of the cell ends here.
-        dummy.next_trans = c.st.nlines + 1;
-        break;
-      }
+    {
+      const bool dead = vpkt_line_sweep<COOP>(c, dummy.nu_cmf, t_current, sdist, tc0, dummy.next_trans, tau_vpkt, tl, true);
+      VP_ADD(55);
+      if (dead) return 1;
     }
     t_future += (sdist / CLIGHT_PROP);
     dummy.prop_time = t_future;
@@ -247,44 +435,47 @@ ARTIS_DEV int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q,
       end_packet = true; // packet leaving the grid; here COUNTER_NESC counts real packets only
     } else {
       dummy.where = snext;
-      stat_inc(tl, COUNTER_CELLCROSSINGS);
+      if (lead) stat_inc(tl, COUNTER_CELLCROSSINGS);
     }
     mgi = cell_mgi(c, dummy.where);
+    VP_ADD(56);
     if (mgi == c.st.npts_model) break;        // reached an empty cell
     if (c.cs.thick[mgi] == 1) return 1;       // a virtual packet dies in a grey cell
   }
-  // final Stokes vector, binned on the fly
-  const double t_arrive = t_current - (dot3(pk.pos, dummy.dir) / CLIGHT_PROP);
-  for (int ind = 0; ind < nspectra; ind++) {
-    const double prob = pn * exp(-tau_vpkt[ind]);
-    const double stokes[3] = {I * prob, Q * prob, U * prob};
-    add_to_vspecpol(c, dummy.nu_rf, dummy.e_rf, stokes, bin, ind, t_arrive);
-  }
-  if (c.st.vpkt_vgrid_flag == 1) {
-    const double prob = pn * exp(-tau_vpkt[0]);
-    const double stokes[3] = {I * prob, Q * prob, U * prob};
-    for (int bin_range = 0; bin_range < c.st.vpkt_nrange_grid; bin_range++) {
-      if (dummy.nu_rf > c.st.vpkt_nu_grid_min[bin_range] && dummy.nu_rf < c.st.vpkt_nu_grid_max[bin_range]) {
-        if (t_arrive > c.st.vpkt_tmin_grid && t_arrive < c.st.vpkt_tmax_grid)
-          add_to_vpkt_grid(c, dummy.nu_rf, dummy.e_rf, stokes, vel_vec, bin_range, bin, obs);
+  if (lead) {  // final Stokes vector, binned on the fly
+    const double t_arrive = t_current - (dot3(pk.pos, dummy.dir) / CLIGHT_PROP);
+    for (int ind = 0; ind < nspectra; ind++) {
+      const double prob = pn * exp(-tau_vpkt[ind]);
+      const double stokes[3] = {I * prob, Q * prob, U * prob};
+      add_to_vspecpol(c, dummy.nu_rf, dummy.e_rf, stokes, bin, ind, t_arrive);
+    }
+    if (c.st.vpkt_vgrid_flag == 1) {
+      const double prob = pn * exp(-tau_vpkt[0]);
+      const double stokes[3] = {I * prob, Q * prob, U * prob};
+      for (int bin_range = 0; bin_range < c.st.vpkt_nrange_grid; bin_range++) {
+        if (dummy.nu_rf > c.st.vpkt_nu_grid_min[bin_range] && dummy.nu_rf < c.st.vpkt_nu_grid_max[bin_range]) {
+          if (t_arrive > c.st.vpkt_tmin_grid && t_arrive < c.st.vpkt_tmax_grid)
+            add_to_vpkt_grid(c, dummy.nu_rf, dummy.e_rf, stokes, vel_vec, bin_range, bin, obs);
+        }
       }
     }
   }
   return 3;
 }
 
-// vpkt.cc:837-896 vpkt_call_estimators for one interaction of the real packet `pk` (taken by value: the caller's copy is
-// not touched -- the only field the reference modifies, next_trans, is rewritten with the value it already has).
-// Owns its opacity scratch and work tally, like a host thread of the reference owns kappa_rpkt_cont[tid]; returns 1 when
-// at least one virtual packet was sent (the caller then drops its own cached opacity, as cellhistory_reset +
-// calculate_kappa_rpkt_cont at vpkt.cc:887-893 re-evaluate it at the packet's exact frequency).
-ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const Pkt pk, const double stokes_q, const double stokes_u,
-                                            const double t_current, const int realtype) {
+// vpkt.cc:837-896 vpkt_call_estimators for one interaction of the real packet `pk` (read only -- the one field the reference
+// modifies, next_trans, is rewritten with the value it already has). Returns 1 when at least one virtual packet was sent
+// (the caller then drops its own cached opacity, as cellhistory_reset + calculate_kappa_rpkt_cont at vpkt.cc:887-893
+// re-evaluate it at the packet's exact frequency). COOP: warp-uniform arguments and result; lane 0 counts.
+template <bool COOP>
+ARTIS_DEV int vpkt_call_estimators(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u, const double t_current,
+                                   const int realtype, Tally &tl) {
+  const bool lead = vp_lane<COOP>() == 0;
   const int mgi = cell_mgi(c, pk.where);
   if (c.cs.thick[mgi] != 0) return 0;
-  Tally tl = {};
-  KappaCache k;
+  VpktKappa k, first;
   k.valid = false;
+  first.valid = false;
   double vel_vec[3];
   get_velocity(pk.pos, vel_vec, t_current);
   int vflag = 0, created = 0, escaped = 0;
@@ -299,18 +490,18 @@ ARTIS_DEV_NOINLINE int vpkt_call_estimators(const Ctx &c, const Pkt pk, const do
       for (int i = 0; i < c.st.vpkt_nrange; i++) {
         const double nu_rf = pk.nu_cmf / doppler_nucmf_on_nurf(c, obs, vel_vec);
         if (nu_rf > c.st.vpkt_numin_input[i] && nu_rf < c.st.vpkt_numax_input[i]) {
-          const int r = rlc_emiss_vpkt(c, pk, stokes_q, stokes_u, t_current, bin, obs, realtype, k, tl);
+          const int r = rlc_emiss_vpkt<COOP>(c, pk, stokes_q, stokes_u, t_current, bin, obs, realtype, k, first, tl);
           created += (r & 1);
           escaped += (r >> 1) & 1;
           vflag = 1;
-          k.valid = false;  // cellhistory_reset(mgi, false) at vpkt.cc:887
         }
       }
     }
   }
-  if (created) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT], (double)created);
-  if (escaped) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT_ESC1 + realtype - 1], (double)escaped);
-  tally_flush(c, tl);
+  if (lead) {
+    if (created) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT], (double)created);
+    if (escaped) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT_ESC1 + realtype - 1], (double)escaped);
+  }
   return vflag;
 }
 
@@ -332,7 +523,168 @@ ARTIS_DEV void vpkt_flush_request(const Ctx &c, const Pkt &p, KappaCache &k, Tal
     stokes_q = tl.vpkt_q;
     stokes_u = tl.vpkt_u;
   }
-  if (vpkt_call_estimators(c, q, stokes_q, stokes_u, q.prop_time, realtype)) k.valid = false;
+  if (vpkt_call_estimators<false>(c, q, stokes_q, stokes_u, q.prop_time, realtype, tl)) k.valid = false;
 }
+
+// vpkt_call_estimators without the rays: would this interaction send at least one virtual packet? (the thick-cell test and
+// the observers' time and frequency windows, vpkt.cc:850-880)
+ARTIS_DEV bool vpkt_wanted(const Ctx &c, const Pkt &pk, const double t_current) {
+  const int mgi = cell_mgi(c, pk.where);
+  if (c.cs.thick[mgi] != 0) return false;
+  double vel_vec[3];
+  get_velocity(pk.pos, vel_vec, t_current);
+  for (int bin = 0; bin < c.st.vpkt_nobs; bin++) {
+    double obs[3];
+    const double nz = c.st.vpkt_nz_obs[bin];
+    obs[0] = sqrt(1 - nz * nz) * cos(c.st.vpkt_phiobs[bin]);
+    obs[1] = sqrt(1 - nz * nz) * sin(c.st.vpkt_phiobs[bin]);
+    obs[2] = nz;
+    const double t_arrive = t_current - (dot3(pk.pos, obs) / CLIGHT_PROP);
+    if (t_arrive >= c.st.vpkt_tmin_input && t_arrive <= c.st.vpkt_tmax_input) {
+      for (int i = 0; i < c.st.vpkt_nrange; i++) {
+        const double nu_rf = pk.nu_cmf / doppler_nucmf_on_nurf(c, obs, vel_vec);
+        if (nu_rf > c.st.vpkt_numin_input[i] && nu_rf < c.st.vpkt_numax_input[i]) return true;
+      }
+    }
+  }
+  return false;
+}
+
+#ifdef __CUDACC__
+// ---- deferred ray trace (the barrier-free scheduler's default) ------------------------------------------------------------------
+// Nothing a real packet does afterwards depends on its virtual packets, and nothing a virtual packet reads changes within a
+// timestep (cell state, level populations, the packet as it was at the event). So the event only RECORDS the request -- the
+// packet's position, frequency, energy, arrival direction and Stokes Q / U, 128 bytes -- and goes on; when the scheduler has
+// finished, k_vpkt_trace (transport.cu) traces the whole list with every warp of the device running the same few KB of
+// ray-trace code. In the transport kernel the same rays cost 4-5x as much: its warps are few (168 registers), they interleave
+// the ray trace with five other kinds of event code, and they wait for instructions more than for data (profiles/r2_notes.md).
+// Warp-uniform call; returns true on the lanes whose event sent virtual packets (they drop their cached opacity, as the
+// reference re-evaluates it at vpkt.cc:887-893).
+__device__ __forceinline__ bool vpkt_enqueue(const Ctx &c, const bool have, const Pkt &p, Tally &tl) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int realtype = have ? tl.vpkt_req : 0;
+  tl.vpkt_req = 0;
+  if (__ballot_sync(full, realtype != 0) == 0u) return false;
+  const bool send = realtype != 0 && vpkt_wanted(c, p, p.prop_time);
+  const unsigned m = __ballot_sync(full, send);
+  if (m == 0u) return false;
+  const int leader = __ffs(m) - 1;
+  unsigned long long base = 0ull;
+  if (lane == leader) {
+    base = atomicAdd(c.vreq_n, (unsigned long long)__popc(m));
+    if (base + (unsigned long long)__popc(m) > c.vreq_soft) *reinterpret_cast<volatile int *>(c.vreq_stop) = 1;
+  }
+  base = __shfl_sync(full, base, leader);
+  if (send) {
+    const unsigned long long at = base + (unsigned long long)__popc(m & ((1u << lane) - 1u));
+    if (at < c.vreq_cap) {  // always, by the margin between vreq_soft and vreq_cap (engine.inc)
+      VpktReq r;
+      r.where = p.where;
+      r.last_cross = p.last_cross;
+      r.next_trans = p.next_trans;
+      r.realtype = realtype;
+      for (int d = 0; d < 3; d++) {
+        r.pos[d] = p.pos[d];
+        r.dir[d] = (realtype == 1) ? tl.vpkt_dir[d] : p.dir[d];
+      }
+      r.e_cmf = p.e_cmf;
+      r.nu_cmf = p.nu_cmf;
+      r.prop_time = p.prop_time;
+      r.stokes_q = (realtype == 1) ? tl.vpkt_q : 0.;
+      r.stokes_u = (realtype == 1) ? tl.vpkt_u : 0.;
+      r.pad_[0] = r.pad_[1] = r.pad_[2] = 0.;
+      const uint4 *src = reinterpret_cast<const uint4 *>(&r);
+      uint4 *dst = reinterpret_cast<uint4 *>(c.vreq + at);
+#pragma unroll
+      for (int q = 0; q < 8; q++) __stcg(dst + q, src[q]);
+    } else {
+      fatal(c, 950);
+    }
+  }
+  return send;
+}
+// one request of the list, by one thread (COOP = false) or by the 32 lanes of a warp together (COOP = true)
+template <bool COOP>
+__device__ __forceinline__ void vpkt_trace_request(const Ctx &c, const VpktReq &r, Tally &tl) {
+  Pkt q;
+  q.where = r.where;
+  q.type = ARTIS_TYPE_RPKT;
+  q.last_cross = r.last_cross;
+  q.interactions = 0;
+  q.last_event = 0;
+  q.next_trans = r.next_trans;
+  q.number = 0;
+  q.ma_element = q.ma_ion = q.ma_level = q.ma_activatingline = 0;
+  for (int d = 0; d < 3; d++) {
+    q.pos[d] = r.pos[d];
+    q.dir[d] = r.dir[d];
+  }
+  q.e_cmf = r.e_cmf;
+  q.e_rf = 0.;  // a ray sets its own rest-frame energy and frequency (rlc_emiss_vpkt)
+  q.nu_cmf = r.nu_cmf;
+  q.nu_rf = 0.;
+  q.prop_time = r.prop_time;
+  q.cold = nullptr;
+  vpkt_call_estimators<COOP>(c, q, r.stokes_q, r.stokes_u, r.prop_time, r.realtype, tl);
+}
+
+// The persistent kernels' one call site when the rays are NOT deferred (A/B builds), reached by all 32 lanes together. The requests the lanes' events have left are
+// served by the whole warp one after the other when there are few of them (the other lanes would only wait), and by their own
+// lanes side by side when there are many (32 rays in flight per warp, nobody waits and no geometry is computed 32 times).
+#ifndef ARTIS_VPKT_COOP_MAXREQ
+#define ARTIS_VPKT_COOP_MAXREQ 6
+#endif
+__device__ __forceinline__ void coop_vpkt_flush(const Ctx &c, const bool have, const Pkt &p, KappaCache &k, Tally &tl) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int myreq = have ? tl.vpkt_req : 0;
+  unsigned req = __ballot_sync(full, myreq != 0);
+  if (req == 0u) return;
+  if (__popc(req) > ARTIS_VPKT_COOP_MAXREQ) {
+    if (myreq != 0) vpkt_flush_request(c, p, k, tl);
+    __syncwarp(full);
+    return;
+  }
+  tl.vpkt_req = 0;
+  Pkt mine = p;
+  double my_q = 0., my_u = 0.;
+  if (myreq == 1) {  // an electron scattering: the packet as it arrived (vpkt_flush_request)
+    mine.dir[0] = tl.vpkt_dir[0];
+    mine.dir[1] = tl.vpkt_dir[1];
+    mine.dir[2] = tl.vpkt_dir[2];
+    my_q = tl.vpkt_q;
+    my_u = tl.vpkt_u;
+  }
+  while (req != 0u) {
+    const int owner = __ffs(req) - 1;
+    req &= req - 1u;
+    Pkt q;
+    q.where = __shfl_sync(full, mine.where, owner);
+    q.type = __shfl_sync(full, mine.type, owner);
+    q.last_cross = __shfl_sync(full, mine.last_cross, owner);
+    q.interactions = 0;
+    q.last_event = 0;
+    q.next_trans = __shfl_sync(full, mine.next_trans, owner);
+    q.number = 0;
+    q.ma_element = q.ma_ion = q.ma_level = q.ma_activatingline = 0;
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      q.pos[d] = __shfl_sync(full, mine.pos[d], owner);
+      q.dir[d] = __shfl_sync(full, mine.dir[d], owner);
+    }
+    q.e_cmf = __shfl_sync(full, mine.e_cmf, owner);
+    q.e_rf = __shfl_sync(full, mine.e_rf, owner);
+    q.nu_cmf = __shfl_sync(full, mine.nu_cmf, owner);
+    q.nu_rf = __shfl_sync(full, mine.nu_rf, owner);
+    q.prop_time = __shfl_sync(full, mine.prop_time, owner);
+    q.cold = nullptr;  // the ray trace reads nothing of the cold record
+    const double sq = __shfl_sync(full, my_q, owner), su = __shfl_sync(full, my_u, owner);
+    const int realtype = __shfl_sync(full, myreq, owner);
+    const int sent = vpkt_call_estimators<true>(c, q, sq, su, q.prop_time, realtype, tl);
+    if (sent && lane == owner) k.valid = false;
+  }
+}
+#endif  // __CUDACC__
 
 }  // namespace artis

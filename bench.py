@@ -65,6 +65,23 @@ def select_workload(name):
         WORKLOAD_NAME = ("nebular one-zone NLTE model (tests/nebularonezone_inputfiles, artisoptions_nltenebular.h with the "
                          "overrides of tests/setup_nebularonezone.sh, 50^3 grid), synthetic atomic data {nlines} lines / "
                          "{nbf} bf continua / {nlev} levels, timestep {ts}")
+    elif name == "vpkt":
+        # BASELINE.json config 5: the classic model with VPKT_ON + POL_ON + DIPOLE, five observers, at
+        # timestep 30 (inside the compiled 10-30 d window of vpkt.h: every eligible event sends its five virtual packets)
+        BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_vpkt")
+        BENCH_TS = 30
+        REF_EXE = os.path.join(REPO, "oracle", "_ref", "classic_vpkt", "sn3d_ref")
+        WORKLOAD_NAME = ("config 5: " + WORKLOAD_NAME + ", VPKT_ON + POL_ON + DIPOLE, vpkt.txt with 5 observers x 1 spectrum "
+                         "(SURVEY S5)")
+    elif name == "kilonova":
+        # BASELINE.json config 3: the kilonova LTE build mode on the 1-D kilonova test model with a line list
+        # of more than 1e6 lines (the closest_transition / line-sweep stress), timestep 7
+        BENCH_RUN = os.path.join(REPO, "oracle", "_ref", "runs", "bench_kn")
+        BENCH_TS = 7
+        REF_EXE = os.path.join(REPO, "oracle", "_ref", "kilonova", "sn3d_ref")
+        WORKLOAD_NAME = ("config 3: kilonova LTE 1-D model (tests/kilonova_inputfiles, artisoptions_kilonova_lte.h with the "
+                         "overrides of tests/setup_kilonova.sh, 50^3 grid), synthetic atomic data {nlines} lines / {nbf} bf "
+                         "continua / {nlev} levels, timestep {ts}")
     elif name == "fixture":
         FIXTURE = "classic_nogrey_ts12.npz"
 
@@ -89,6 +106,9 @@ def load_workload():
     s = snapshot.load(snap)
     st, cs = snapshot.static_tables(s), snapshot.cell_state(s)
     name = WORKLOAD_NAME.format(nlines=st["nlines"], nbf=st["nbfcontinua"], nlev=st["nlevels_total"], ts=BENCH_TS)
+    if os.environ.get("ARTIS_BENCH_VPKT_OFF") and st.get("opt_vpkt_on"):  # A/B only: what the virtual packets of config 5 cost
+        st["opt_vpkt_on"] = 0
+        name += " [A/B: virtual packets switched OFF]"
     if MODEL3D:
         sys.path.insert(0, os.path.join(REPO, "tools"))
         import model3d
@@ -182,7 +202,8 @@ def run_reference(nproc, steps, warmup):
                                    os.path.exists(os.path.join(BENCH_RUN, f"gridsave_ts{BENCH_TS}.tmp"))):
         return None
     keep = ("adata.txt", "transitiondata.txt", "phixsdata_v2.txt", "compositiondata.txt", "model.txt", "abundances.txt",
-            "input.txt", "ratecoeff.dat", "bflist.dat", "recombrates.txt", f"gridsave_ts{BENCH_TS}.tmp",
+            "input.txt", "ratecoeff.dat", "bflist.dat", "recombrates.txt", "vpkt.txt", "gridcontributions.txt",
+            "vspecpol_0_0_even.tmp", "vspecpol_0_0_odd.tmp", f"gridsave_ts{BENCH_TS}.tmp",
             f"packets_0000_ts{BENCH_TS}.tmp")
     tot_inter, tot_sec = 0.0, 0.0
     npk = 0
@@ -244,7 +265,7 @@ def main():
     ap.add_argument("--max-events", type=int, default=0, help="events per packet and pass (0: library default)")
     ap.add_argument("--scheduler-kernels", type=int, default=0, choices=(0, 1, 2),
                     help="1: one persistent kernel with every role, 2: macro-atom jump kernel + every-other-role kernel (0: library default)")
-    ap.add_argument("--workload", default="classic", choices=["classic", "nebular", "fixture", "3d"])
+    ap.add_argument("--workload", default="classic", choices=["classic", "nebular", "fixture", "3d", "vpkt", "kilonova"])
     a = ap.parse_args()
     select_workload(a.workload)
     if a.packets <= 0:
@@ -425,6 +446,12 @@ def main():
                            "warp_Mcycles_by_kind": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[80:88]],
                            "warp_Mcycles_refill_push_idle": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[88:91]],
                            "scheduler_geometry_kernels_blocks_single_big_jump": T.scheduler_geometry(),
+                           # -DARTIS_VPKT_PROFILE builds only (vpkt.cuh): Mcycles per step in set-up, boundary_cross, probe sweep,
+                           # continuum sum, real sweep, move, (unused), (unused); then rays and cells per step
+                           "vpkt_requests_per_step": float(ctr_sum[57]) / a.steps / world if st.get("opt_vpkt_on") else None,
+                           "vpkt_list_restarts_per_step": float(ctr_sum[58]) / a.steps / world if st.get("opt_vpkt_on") else None,
+                           "vpkt_profile": ([round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[51:59]] +
+                                            [float(x) / a.steps / world for x in ctr_sum[59:61]]) if ctr_sum[59] > 0 else None,
                            "allreduce_ms_per_step": allreduce_ms / a.steps,
                            "estimator_block_bytes": int(ndoubles * 8),
                            "events_per_s": float(ctr_sum[49]) / (tot_ms * 1e-3),

@@ -141,7 +141,9 @@ enum {
   ARTIS_CTR_KAPPA_EVALS = 48,     /* calculate_kappa_rpkt_cont recomputes (cache misses) */
   ARTIS_CTR_PACKET_UPDATES = 49,  /* do_packet calls */
   ARTIS_CTR_HANDOFFS = 50,        /* packets handed from one scheduler ring to another in mid-timestep */
-  /* [51,61): unused since ABI 6 (were the per-kind scheduler statistics of five kinds) */
+  /* [51,61): unused since ABI 6 (were the per-kind scheduler statistics of five kinds), except: */
+  ARTIS_CTR_VPKT_REQUESTS = 57,   /* VPKT_ON: interactions whose virtual packets were traced from the request list in the last transport */
+  ARTIS_CTR_VPKT_RESTARTS = 58,   /* ... times the request list filled and the scheduler was launched again */
   ARTIS_CTR_DRAIN_NS_10PCT = 61,  /* ns from the transport launch until 10% / 1% / none of the packets are still active */
   ARTIS_CTR_DRAIN_NS_1PCT = 62,
   ARTIS_CTR_DRAIN_NS_DONE = 63,

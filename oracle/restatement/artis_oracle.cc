@@ -83,8 +83,8 @@ void be_run_escaped_scatter(const PktHot *hot, const PktCold *cold, long long n,
     if (only_new) reported[i] = 1;
   }
 }
-void be_run_bucket(PktHot *hot, PktCold *cold, int n, int *buckets, int *kind_sizes, int *const *queues) {
-  for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, hot, cold, i, buckets);
+void be_run_bucket(PktHot *hot, PktCold *cold, int n, int *buckets, int *kind_sizes, int *const *queues, bool fresh) {
+  for (int i = 0; i < n; i++) artis::body_bucket_hist(g_ctx, hot, cold, i, buckets, fresh);
   artis::body_bucket_scan(g_ctx, buckets, kind_sizes);
   for (int i = 0; i < n; i++) artis::body_bucket_scatter(g_ctx, hot, i, buckets, queues);
 }
@@ -101,6 +101,8 @@ void be_run_wavefront(PktHot *hot, PktCold *cold, const artis::QueueView &qv, in
 // the barrier-free scheduler is a device-only construct; the host backend runs the same visits as kernel rounds
 bool be_run_persistent(PktHot *, PktCold *, int *, int, unsigned long long *, unsigned long long *, int, long long) { return false; }
 int be_persistent_kernels() { return 0; }
+void be_run_vpkt_trace(const artis::VpktReq *, long long) {}  // the host build traces virtual packets where their events happen
+bool be_vpkt_deferred() { return false; }
 int be_scheduler_geometry(int *) { return 0; }
 long long be_resident_lanes() { return 1; }
 void be_fill_bytes(void *p, int byte, size_t n) { memset(p, byte, n); }

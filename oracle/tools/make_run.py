@@ -45,6 +45,19 @@ def write_input_txt(path, template, itstep, ftstep, ntstep=None, tmin=None, tmax
     open(path, "w").write("\n".join(out) + "\n")
 
 
+# SURVEY 8d S5 (BASELINE.json config 5): five observers at phi = 0, one spectrum each (all opacities), the compiled time and
+# frequency windows, the input file's thick-cell limit, tau_max 10, no velocity maps
+VPKT_TXT_S5 = """5
+-0.8 -0.4 0 0.4 0.8
+0 0 0 0 0
+0
+0 0 0
+0
+0 0
+10
+0
+"""
+
 VPKT_TXT = """2
 0.5 -0.3
 0
@@ -72,7 +85,7 @@ def setup_classic1d(rundir, args):
     if args.vpkt:
         # vpkt.txt (vpkt.cc:667-836): two observers; six spectra per observer (all opacities, iron lines removed, no
         # lines, no bf, no ff, no es); compiled time and frequency windows; tau_max 10; velocity maps in two bands
-        open(os.path.join(rundir, "vpkt.txt"), "w").write(VPKT_TXT)
+        open(os.path.join(rundir, "vpkt.txt"), "w").write(VPKT_TXT_S5 if args.vpkt == "s5" else VPKT_TXT)
     n = gen_atomic_data.generate(rundir, tuple(int(z) for z in args.elements.split(",")), args.nions, args.nlevels,
                                  args.dense_levels, args.sparsity, args.seed)
     print(f"run dir {rundir}: {n} lines")
@@ -90,7 +103,7 @@ def setup_kilonova1d(rundir, args):
     for f in os.listdir(os.path.join(REF, "data")):
         shutil.copy(os.path.join(REF, "data", f), rundir)
     write_input_txt(os.path.join(rundir, "input.txt"), os.path.join(src, "input-newrun.txt"), args.itstep, args.ftstep,
-                    ngrey=args.ngrey)
+                    ngrey=args.ngrey, resume=args.resume)
     n = gen_atomic_data.generate(rundir, (26, 27, 28), 5, args.nlevels, args.dense_levels, args.sparsity, args.seed,
                                  ion_ranges={26: (1, 5), 27: (2, 4), 28: (2, 5)},
                                  abundance_only=[(2, 4), (24, 60), (38, 95), (58, 145), (60, 150), (88, 220), (92, 230)],
@@ -127,7 +140,8 @@ def main():
     ap.add_argument("--sparsity", type=float, default=0.15)
     ap.add_argument("--seed", type=int, default=20240607)
     ap.add_argument("--ngrey", type=int, default=None, help="kilonova1d: override num_grey_timesteps of input.txt")
-    ap.add_argument("--vpkt", action="store_true", help="classic1d: also write a vpkt.txt for VPKT_ON builds")
+    ap.add_argument("--vpkt", nargs="?", const="fixture", default=None,
+                    help="classic1d: also write a vpkt.txt for VPKT_ON builds (`--vpkt s5`: the five observers of config 5)")
     ap.add_argument("--resume", action="store_true",
                     help="write input.txt to continue from the gridsave/packets files of timestep itstep-1")
     args = ap.parse_args()

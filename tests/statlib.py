@@ -113,6 +113,32 @@ def summary(static, cell, est, post, pre):
     return d
 
 
+def summary_pol(post, pre):
+    """Polarisation state of the REAL packets after the step (POL_ON builds; polarization.cc:6-140 escat_rpkt, the frame
+    transforms of vpkt.cc:898-1069): second moments and mean magnitudes of the Stokes Q / U that the electron scatterings
+    of this timestep leave in the resident r-packets and in those that escaped, their energy-weighted sums (zero within
+    noise for a spherical model, so the z-test checks the sign conventions too), the polarisation reference axis, and the
+    scattering counts that go with them. Kept apart from summary() so that the fixtures written before it keep their
+    column lists; used by the bench-workload ensembles (oracle/tools/ref_bench_rows.py)."""
+    d = {}
+    newesc = (post["type"] == 32) & _was_active(post, pre) & (post["escape_type"] == 11)
+    for tag, m in (("res", post["type"] == 11), ("esc", newesc)):
+        q, u, i0 = post["stokes"][m, 1], post["stokes"][m, 2], post["stokes"][m, 0]
+        e = post["e_rf"][m]
+        n = max(int(m.sum()), 1)
+        d[f"pol_{tag}_I_mean"] = i0.sum() / n
+        d[f"pol_{tag}_Q2_mean"] = (q * q).sum() / n
+        d[f"pol_{tag}_U2_mean"] = (u * u).sum() / n
+        d[f"pol_{tag}_absQ_mean"] = np.abs(q).sum() / n
+        d[f"pol_{tag}_absU_mean"] = np.abs(u).sum() / n
+        d[f"pol_{tag}_frac_polarised"] = float(((q != 0) | (u != 0)).sum()) / n
+        d[f"pol_{tag}_eQ_sum"] = (e * q).sum()
+        d[f"pol_{tag}_eU_sum"] = (e * u).sum()
+        d[f"pol_{tag}_poldir_z_abs_mean"] = np.abs(post["pol_dir"][m, 2]).sum() / n
+        d[f"pol_{tag}_nscat_mean"] = post["nscatterings"][m].sum() / n
+    return d
+
+
 def _was_active(post, pre):
     """mask over `post` of packets that were not yet escaped in `pre` (matched by packet.number: the reference
     re-orders the array, update_packets.cc:256)."""

@@ -162,7 +162,12 @@ def check_promoted(lib, name, probe_mode):
         assert abs(by_shell.sum() / want.sum() - 1) < 2e-3, k
         big = want > 1e-3 * want.max()
         assert np.allclose(by_shell[big], want[big], rtol=0.05), k
-    assert np.allclose(ed["counters"][:46], es["counters"][:46], rtol=0.02, atol=5)
+    # event and work counters; not ARTIS_CTR_ESTIM_ATOMICS (39): on the device it counts atomics AFTER warp aggregation, and the
+    # lanes of a warp share estimator addresses in the 78-shell model that they do not share with a model cell per grid cell
+    physics = np.r_[0:39, 40:46]
+    bad = [(int(i), int(ed["counters"][i]), int(es["counters"][i])) for i in physics
+           if not np.isclose(ed["counters"][i], es["counters"][i], rtol=0.02, atol=5)]
+    assert not bad, bad
     print(name, "model cells", n1, "->", n3, "rows built", int(es["counters"][abi.CTR_ROW_UNITS]) * 128, "bytes; table bytes",
           Ts.table_bytes())
     Ts.finalize()
