@@ -681,33 +681,15 @@ ARTIS_DEV_NOINLINE const double *row_get(const Ctx &c, const int mgi, const int 
 // coefficients are the work -- and then every lane adds the 32 contributions in list order from shuffled operands, so that
 // each running sum sees the roundings of build_ma_level_into (one fused multiply-add per transition, in order): the row is
 // bit for bit the row one thread builds, in a thirtieth of the time. Returns the row (also when another warp was faster).
-__device__ __noinline__ const double *coop_build_ma_row(const Ctx &c, const int mgi, const int tc, const int gl, const int lane) {
+// The arithmetic of build_ma_level_into by the 32 lanes of a warp: a lane per transition evaluates the rate coefficients (the
+// Sobolev escape probabilities, collision strengths and recombination coefficients are the work), and every lane then adds the
+// 32 contributions in list order from shuffled operands with the fused multiply-adds of the one-thread builder: the same bits.
+// Writes the nine process rates to row[0..8] and the three running sums to cum_rad / cum_down / cum_up.
+__device__ __forceinline__ void coop_build_ma_into(const Ctx &c, const int mgi, const int tc, const int gl, const int lane, double *row,
+                                                   double *cum_rad, double *cum_down, double *cum_up) {
   const unsigned full = 0xffffffffu;
-  const CellTables &tb = c.tb;
-  unsigned *slot = tb.row_ptr + (size_t)tc * (c.st.nlevels_total + c.st.includedions) + gl;
   const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
   const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
-  unsigned long long at = 0ull;
-  unsigned have = 0u;
-  int bad = 0;
-  if (lane == 0) {
-    have = __ldcg(slot);
-    if (have == 0u) {
-      const unsigned long long units = (unsigned long long)(MA_ACTION_COUNT + 2 * ndown + nup + 15) / 16;
-      at = atomicAdd(tb.row_top, units);
-      if (at + units > tb.row_soft) *reinterpret_cast<volatile int *>(tb.row_stop) = 1;
-      if (at + units > tb.row_cap) {
-        fatal(c, 240);
-        bad = 1;
-      }
-    }
-  }
-  have = __shfl_sync(full, have, 0);
-  if (have != 0u) return tb.row_arena + (size_t)(have - 1u) * 16;
-  if (__shfl_sync(full, bad, 0) != 0) return tb.row_arena;
-  at = __shfl_sync(full, at, 0);
-  double *row = tb.row_arena + (size_t)at * 16;
-  double *cum_rad = row + MA_ACTION_COUNT, *cum_down = cum_rad + ndown, *cum_up = cum_down + ndown;
   const int ui = c.lev_uion[gl];
   const int level = gl - c.st.ion_leveloffset[ui];
   const float T_e = c.cs.Te[mgi];
@@ -810,6 +792,140 @@ __device__ __noinline__ const double *coop_build_ma_row(const Ctx &c, const int 
       if (lane == a) v = pr[a];
     row[lane] = v;
   }
+}
+
+// cooling_ion_sum<true> by the 32 lanes of a warp: the collisional-excitation terms -- one per upward transition of every level
+// of the ion, thousands for an iron-group ion -- are evaluated a lane per transition and added in list order from shuffled
+// operands (every lane keeps the same running sum, the lane of a transition stores its value); the handful of other terms
+// per level are evaluated by every lane alike and stored by lane 0. Same additions in the same order as the one-thread loop.
+__device__ __forceinline__ void coop_cooling_ion_into(const Ctx &c, const int mgi, const int ui, const int lane, double *cool,
+                                                      double *cexc) {
+  const unsigned full = 0xffffffffu;
+  const int tc = tabcell(c, mgi);
+  const int element = c.uion_element[ui];
+  const float nne = c.cs.nne[mgi];
+  const float T_e = c.cs.Te[mgi];
+  double contrib = 0.;
+  for (int u = 0; u < ui; u++) contrib += c.cs.cooling_contrib_ion[(size_t)mgi * c.st.includedions + u];
+  int i = c.st.ion_coolingoffset[ui];
+  const int gl0 = c.st.ion_leveloffset[ui];
+  const int nlevels = c.st.ion_nlevels[ui];
+  const int ionisinglevels = c.st.ion_ionisinglevels[ui];
+  const double nncurrention = ionstagepop_ui(c, mgi, element, ui);
+  const int ioncharge = c.st.ion_ionstage[ui] - 1;
+  if (ioncharge > 0) {
+    contrib += 1.426e-27 * sqrtf(T_e) * pow((double)ioncharge, 2) * nncurrention * nne;
+    if (lane == 0) cool[i] = contrib;
+    i++;
+  }
+  const bool hasupper = ion_has_upper(c, ui);
+  for (int level = 0; level < nlevels; level++) {
+    const int gl = gl0 + level;
+    const double epsilon_current = c.st.lev_epsilon[gl];
+    const double nnlevel = tab_levelpop(c, tc, gl);
+    const double statweight = (double)c.st.lev_statweight[gl];
+    const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
+    if (nup > 0) {
+      for (int base = 0; base < nup; base += 32) {
+        const int ii = base + lane;
+        double C = 0.;
+        if (ii < nup) {
+          const int lineindex = c.st.uptrans_lineindex[uoff + ii];
+          const int glu = c.line_upper_g[lineindex];
+          const double epsilon_trans = c.st.lev_epsilon[glu] - epsilon_current;
+          C = nnlevel *
+              col_excitation_ratecoeff(T_e, nne, lineref(c, lineindex), epsilon_trans, statweight, (double)c.st.lev_statweight[glu]) *
+              epsilon_trans;
+        }
+        const int cnt = nup - base < 32 ? nup - base : 32;
+        double mine = 0.;
+        for (int j = 0; j < cnt; j++) {
+          contrib += __shfl_sync(full, C, j);
+          if (lane == j) mine = contrib;
+        }
+        if (ii < nup) cexc[uoff + ii] = mine;
+      }
+      if (lane == 0) cool[i] = contrib;
+      i++;
+    }
+    if (hasupper && level < ionisinglevels) {
+      const int ntargets = c.st.lev_nphixstargets[gl];
+      for (int t = 0; t < ntargets; t++) {
+        const double epsilon_trans = phixs_threshold(c, ui, gl, t);
+        contrib += nnlevel * col_ionization_ratecoeff(c, T_e, nne, ui, gl, t, epsilon_trans) * epsilon_trans;
+        if (lane == 0) cool[i] = contrib;
+        i++;
+      }
+      for (int t = 0; t < ntargets; t++) {
+        const double nnupperion = ionstagepop_ui(c, mgi, element, ui + 1);
+        contrib += get_bfcoolingcoeff(c, gl, t, T_e) * nnupperion * nne;
+        if (lane == 0) cool[i] = contrib;
+        i++;
+      }
+    }
+  }
+  if (i != c.st.ion_coolingoffset[ui] + c.st.ion_ncoolingterms[ui]) fatal(c, 202);
+}
+
+// rows on demand: the cooling row of (cell, ion) built by the whole warp (the event role's k-packets; transport.cu). Same
+// protocol as coop_build_ma_row below: space from the arena, the row written, its pointer published with a compare-and-swap.
+__device__ __noinline__ void coop_build_cool_row(const Ctx &c, const int mgi, const int tc, const int ui, const int lane) {
+  const unsigned full = 0xffffffffu;
+  const CellTables &tb = c.tb;
+  unsigned *slot = tb.row_ptr + (size_t)tc * (c.st.nlevels_total + c.st.includedions) + c.st.nlevels_total + ui;
+  unsigned long long at = 0ull;
+  unsigned have = 0u;
+  int bad = 0;
+  if (lane == 0) {
+    have = __ldcg(slot);
+    if (have == 0u) {
+      const unsigned long long units = (unsigned long long)(cool_row_doubles(c, ui) + 15) / 16;
+      at = atomicAdd(tb.row_top, units);
+      if (at + units > tb.row_soft) *reinterpret_cast<volatile int *>(tb.row_stop) = 1;
+      if (at + units > tb.row_cap) {
+        fatal(c, 240);
+        bad = 1;
+      }
+    }
+  }
+  have = __shfl_sync(full, have, 0);
+  if (have != 0u || __shfl_sync(full, bad, 0) != 0) return;
+  at = __shfl_sync(full, at, 0);
+  double *row = tb.row_arena + (size_t)at * 16;
+  coop_cooling_ion_into(c, mgi, ui, lane, row - c.st.ion_coolingoffset[ui], row + c.st.ion_ncoolingterms[ui] - ion_upfirst(c, ui));
+  __threadfence();
+  __syncwarp(full);
+  if (lane == 0) atomicCAS(slot, 0u, (unsigned)at + 1u);
+}
+
+__device__ __noinline__ const double *coop_build_ma_row(const Ctx &c, const int mgi, const int tc, const int gl, const int lane) {
+  const unsigned full = 0xffffffffu;
+  const CellTables &tb = c.tb;
+  unsigned *slot = tb.row_ptr + (size_t)tc * (c.st.nlevels_total + c.st.includedions) + gl;
+  const int ndown = c.st.lev_ndowntrans[gl], doff = c.st.lev_downoffset[gl];
+  const int nup = c.st.lev_nuptrans[gl], uoff = c.st.lev_upoffset[gl];
+  unsigned long long at = 0ull;
+  unsigned have = 0u;
+  int bad = 0;
+  if (lane == 0) {
+    have = __ldcg(slot);
+    if (have == 0u) {
+      const unsigned long long units = (unsigned long long)(MA_ACTION_COUNT + 2 * ndown + nup + 15) / 16;
+      at = atomicAdd(tb.row_top, units);
+      if (at + units > tb.row_soft) *reinterpret_cast<volatile int *>(tb.row_stop) = 1;
+      if (at + units > tb.row_cap) {
+        fatal(c, 240);
+        bad = 1;
+      }
+    }
+  }
+  have = __shfl_sync(full, have, 0);
+  if (have != 0u) return tb.row_arena + (size_t)(have - 1u) * 16;
+  if (__shfl_sync(full, bad, 0) != 0) return tb.row_arena;
+  at = __shfl_sync(full, at, 0);
+  double *row = tb.row_arena + (size_t)at * 16;
+  double *cum_rad = row + MA_ACTION_COUNT, *cum_down = cum_rad + ndown, *cum_up = cum_down + ndown;
+  coop_build_ma_into(c, mgi, tc, gl, lane, row, cum_rad, cum_down, cum_up);
   __threadfence();
   __syncwarp(full);
   unsigned prev = 0u;

@@ -63,6 +63,26 @@ ARTIS_DEV int lower_bound_idx(const double *cum, int lo, const int hi, const dou
   return lo;
 }
 
+// The ion whose cooling row do_kpkt is about to search, without touching the packet or its random stream (rows on demand: the
+// scheduler has the warp build a missing row before the event, transport.cu): the first statements of do_kpkt_body on a COPY
+// of the stream. -1: the event ends before it selects a cooling process.
+ARTIS_DEV int kpkt_peek_cooling_ion(const Ctx &c, const Pkt &p, const double t2, const Rng &rng) {
+  const double t1 = p.prop_time;
+  const int mgi = cell_mgi(c, p.where);
+  double deltat = 0.;
+  if (c.nts < c.st.n_kpktdiffusion_timesteps) deltat = c.st.kpktdiffusion_timescale * c.ts_width;
+  if (!(t1 + deltat <= t2)) return -1;
+  Rng peek = rng;
+  const double rndcool = rng_uniform(peek) * c.cs.totalcooling[mgi];
+  double coolingsum = 0.;
+  const int nions_total = c.st.includedions;
+  for (int ui = 0; ui < nions_total; ui++) {
+    coolingsum += c.cs.cooling_contrib_ion[(size_t)mgi * nions_total + ui];
+    if (coolingsum > rndcool) return ui;
+  }
+  return -1;
+}
+
 // kpkt.cc:477-797
 ARTIS_DEV void do_kpkt_body(const Ctx &c, Pkt &p, const double t2, Rng &rng, Tally &tl) {
   tl.kpkt_events++;

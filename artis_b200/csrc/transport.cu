@@ -55,9 +55,25 @@ __global__ void k_corrphoto(long long n) {
     if (lane == 0) c.tb.corrphoto[(size_t)tc * c.st.nbfcontinua + i] = v;
   }
 }
-__global__ void k_ma(long long n) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    artis::body_ma(d_ctx, i);
+// dense macro-atom tables: one warp per (cell, level), a lane per transition (celltables.cuh coop_build_ma_into; bit for bit
+// the rows of the one-thread builder body_ma, which the host build and the rows-on-demand path's single lanes use). A level
+// of a 1e6-line list has thousands of transitions: one thread per level left most of the device waiting for the longest rows.
+__global__ void __launch_bounds__(128) k_ma(long long n) {
+  using namespace artis;
+  const Ctx &c = d_ctx;
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long idx = warp; idx < n; idx += nwarps) {
+    const size_t tc = (size_t)(idx / c.st.nlevels_total);
+    const int gl = (int)(idx % c.st.nlevels_total);
+    const int mgi = c.mgi_of_tabcell[tc];
+    if (!cell_uses_tables(c, mgi)) continue;
+    const int doff = c.st.lev_downoffset[gl], uoff = c.st.lev_upoffset[gl];
+    coop_build_ma_into(c, mgi, (int)tc, gl, lane, c.tb.ma_rates + (tc * c.st.nlevels_total + gl) * MA_ACTION_COUNT,
+                       c.tb.ma_cum_raddeexc + tc * c.st.ndowntrans_total + doff,
+                       c.tb.ma_cum_intdown + tc * c.st.ndowntrans_total + doff, c.tb.ma_cum_intup + tc * c.st.nuptrans_total + uoff);
+  }
 }
 __global__ void k_cooling_rates_ion(long long n, double *contrib) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
@@ -67,9 +83,22 @@ __global__ void k_cooling_rates_total(long long n, const double *contrib, double
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_cooling_rates_total(d_ctx, i, contrib, total);
 }
-__global__ void k_cool(long long n) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    artis::body_cool(d_ctx, i);
+// dense cooling tables: one warp per (cell, ion) (celltables.cuh coop_cooling_ion_into; the rows of body_cool bit for bit).
+// One thread per (cell, ion) was 2000 threads for the classic model, each on a serial loop over ~2000 terms: 5.2 of the 5.5 ms
+// of the per-timestep table build.
+__global__ void __launch_bounds__(128) k_cool(long long n) {
+  using namespace artis;
+  const Ctx &c = d_ctx;
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long idx = warp; idx < n; idx += nwarps) {
+    const size_t tc = (size_t)(idx / c.st.includedions);
+    const int mgi = c.mgi_of_tabcell[tc];
+    if (!cell_uses_tables(c, mgi)) continue;
+    coop_cooling_ion_into(c, mgi, (int)(idx % c.st.includedions), lane, c.tb.cool_cum + tc * c.st.ncoolingterms,
+                          c.tb.collexc_cum + tc * c.st.nuptrans_total);
+  }
 }
 // light curves + angle-averaged spectrum of the resident packets (spectra.cuh). The 4 x ntstep light-curve sums are a few
 // hundred addresses that every escaped packet of the ensemble adds to: they are accumulated per block in shared memory
@@ -304,18 +333,24 @@ constexpr int RMS = artis::RING_META_STRIDE;
 // Virtual packets in the barrier-free scheduler. ARTIS_VPKT_DEFER 1 (default): events record their requests and k_vpkt_trace
 // traces the list when the scheduler has finished; 0: the rays are traced inside the transport kernel, right after the event --
 // ARTIS_VPKT_COOP 1: by the whole warp when few lanes have a request (vpkt.cuh coop_vpkt_flush), 0: by the lane alone.
-// ARTIS_VPKT_TRACE_COOP 1: k_vpkt_trace gives a request to a warp, 0 (default): to a thread.
+// ARTIS_VPKT_TRACE_MODE: how k_vpkt_trace works through the list -- 2 (default): a lane per request, the warp in lock step through
+// the phases of a cell (vpkt.cuh vpkt_trace_lockstep); 0: a thread per request at its own pace; 1: a warp per request.
 #ifndef ARTIS_VPKT_DEFER
 #define ARTIS_VPKT_DEFER 1
 #endif
 #ifndef ARTIS_VPKT_COOP
 #define ARTIS_VPKT_COOP 1
 #endif
-#ifndef ARTIS_VPKT_TRACE_COOP
-#define ARTIS_VPKT_TRACE_COOP 0
+#ifndef ARTIS_VPKT_TRACE_MODE
+#define ARTIS_VPKT_TRACE_MODE 2
 #endif
 #ifndef ARTIS_VPKT_TRACE_MINBLOCKS
 #define ARTIS_VPKT_TRACE_MINBLOCKS 4
+#endif
+// rows on demand: 1 = the event role's warps build the cooling rows their k-packets are about to search with all 32 lanes
+// before the event; 0 = the lane that misses a row builds it alone (A/B builds)
+#ifndef ARTIS_COOP_COOL_ROWS
+#define ARTIS_COOP_COOL_ROWS 1
 #endif
 #ifndef ARTIS_REFILL_BACKOFF
 #define ARTIS_REFILL_BACKOFF 10
@@ -789,7 +824,30 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
       if (k.defer_bfest) coop_bfest_flush(c, k, tl);  // warp-uniform: the flag is an option of the build mode
       resumed = false;
       if (have && !parked && p.type == ARTIS_TYPE_ESCAPE) est_add(&c.es.ts_scalars[ARTIS_TS_CMF_LUM], p.e_cmf);
-    } else if (have) {
+    } else {
+#if ARTIS_ROWS_ON_DEMAND && ARTIS_COOP_COOL_ROWS
+      if (role == KIND_MAK && rows_on_demand(c)) {  // warp-uniform
+        // cooling rows the lanes' k-packets are about to search and nobody has built yet: the warp builds them one after the
+        // other with all 32 lanes (a lane that built one alone walked ~2000 terms while its warp waited)
+        int b_mgi = 0, b_tc = -1, b_ui = -1;
+        bool miss = false;
+        if (have && p.type == ARTIS_TYPE_KPKT) {
+          b_mgi = cell_mgi(c, p.where);
+          b_tc = tabcell(c, b_mgi);
+          if (b_tc >= 0 && c.cs.thick[b_mgi] != 1) b_ui = kpkt_peek_cooling_ion(c, p, t2, rng);  // (a grey cell: do_kpkt_bb)
+          if (b_ui >= 0)
+            miss = __ldcg(c.tb.row_ptr + (size_t)b_tc * (c.st.nlevels_total + c.st.includedions) + c.st.nlevels_total + b_ui) == 0u;
+        }
+        unsigned todo = __ballot_sync(full, miss);
+        while (todo != 0u) {
+          const int src = __ffs(todo) - 1;
+          todo &= todo - 1u;
+          coop_build_cool_row(c, __shfl_sync(full, b_mgi, src), __shfl_sync(full, b_tc, src), __shfl_sync(full, b_ui, src), lane);
+        }
+      }
+#endif
+    }
+    if (!(HAS_THIN && role == KIND_RPKT_THIN) && have) {
       switch (role) {  // warp-uniform
         case KIND_MAK:
           if constexpr ((ROLES & (1u << KIND_MAK)) != 0) {
@@ -1085,12 +1143,16 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_light(P
 // VPKT_ON: the virtual packets of the requests the scheduler's events have recorded (vpkt.cuh). One request per thread (its
 // rays towards the observers one after the other, the start cell's opacity shared between them), or per warp.
 #ifndef ARTIS_NO_VPKT
-__global__ void __launch_bounds__(128, ARTIS_VPKT_TRACE_MINBLOCKS) k_vpkt_trace(const artis::VpktReq *req, const long long n) {
+__global__ void __launch_bounds__(128, ARTIS_VPKT_TRACE_MINBLOCKS) k_vpkt_trace(const artis::VpktReq *req, const long long n,
+                                                                               unsigned long long *cursor) {
   using namespace artis;
   const Ctx &c = d_ctx;
   Tally tl = {};
   stats_block_begin();
-  constexpr bool COOP = ARTIS_VPKT_TRACE_COOP != 0;
+#if ARTIS_VPKT_TRACE_MODE == 2
+  vpkt_trace_lockstep(c, req, n, cursor, tl);  // a lane per request, the warp through the phases of a cell together
+#else
+  constexpr bool COOP = ARTIS_VPKT_TRACE_MODE == 1;  // 1: a warp per request; 0: a thread per request, each at its own pace
   const long long unit = COOP ? 32 : 1;
   const long long stride = (long long)gridDim.x * blockDim.x / unit;
   for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / unit; i < n; i += stride) {
@@ -1101,6 +1163,7 @@ __global__ void __launch_bounds__(128, ARTIS_VPKT_TRACE_MINBLOCKS) k_vpkt_trace(
     for (int q = 0; q < 8; q++) dst[q] = __ldcg(src + q);
     vpkt_trace_request<COOP>(c, r, tl);
   }
+#endif
   tally_flush(c, tl);
   stats_block_flush(c);
 }
@@ -1344,13 +1407,13 @@ int grid_for(long long n, int block, int blocks_per_sm) {
 void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
-void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n); }
+void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cooling_rates(long long ncells, int nions, double *contrib, double *total) {
   if (ncells <= 0) return;
   k_cooling_rates_ion<<<grid_for(ncells * nions, 64, 8), 64, 0, g_stream>>>(ncells * nions, contrib);
   k_cooling_rates_total<<<grid_for(ncells, 128, 8), 128, 0, g_stream>>>(ncells, contrib, total);
 }
-void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n, 64, 8), 64, 0, g_stream>>>(n); }
+void be_run_cool(long long n) { if (n > 0) k_cool<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_unpack(const ArtisPacket *aos, PktHot *hot, PktCold *cold, long long n) {
   if (n > 0) k_unpack<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(aos, hot, cold, n);
 }
@@ -1460,14 +1523,14 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
 }
 void be_fill_bytes(void *p, int byte, size_t n) { note(cudaMemsetAsync(p, byte, n, g_stream), "memset"); }
 // VPKT_ON: trace the n recorded requests (on the transport stream, inside the timed region of the timestep)
-void be_run_vpkt_trace(const artis::VpktReq *req, long long n) {
+void be_run_vpkt_trace(const artis::VpktReq *req, long long n, unsigned long long *cursor) {
 #ifndef ARTIS_NO_VPKT
   if (n <= 0) return;
-  const long long unit = ARTIS_VPKT_TRACE_COOP != 0 ? 32 : 1;
+  const long long unit = ARTIS_VPKT_TRACE_MODE == 1 ? 32 : 1;
   long long blocks = (n * unit + 127) / 128;
-  const long long most = (long long)g_sms * 16;  // grid-stride beyond that
+  const long long most = (long long)g_sms * (ARTIS_VPKT_TRACE_MODE == 2 ? ARTIS_VPKT_TRACE_MINBLOCKS : 16);  // grid-stride beyond that
   if (blocks > most) blocks = most;
-  k_vpkt_trace<<<(unsigned)blocks, 128, 0, g_stream>>>(req, n);
+  k_vpkt_trace<<<(unsigned)blocks, 128, 0, g_stream>>>(req, n, cursor);
 #endif
 }
 bool be_vpkt_deferred() {

@@ -325,31 +325,29 @@ ARTIS_DEV bool vpkt_line_sweep(const Ctx &c, const double nu_cmf, const double t
   }
 }
 
-// vpkt.cc:76-364 rlc_emiss_vpkt. `pk` is the real packet (read only), `k` the opacity scratch of the request, `first` the
-// start cell's opacity shared by the request's rays. Returns the change of the virtual-packet counters: bit 0 = a virtual
-// packet was created, bit 1 = it reached the edge of the grid. COOP: warp-uniform arguments and result.
-template <bool COOP>
-ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u,
-                                      const double t_current, const int bin, double *obs, const int realtype, VpktKappa &k,
-                                      VpktKappa &first, Tally &tl) {
-  const bool lead = vp_lane<COOP>() == 0;
-  VP_T0();
-  VP_COUNT(59);
-  const int nspectra = c.st.vpkt_nspectra;
-  double tau_vpkt[VPKT_MAX_SPECTRA];
-  for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_vpkt[ind] = 0;
-  Pkt dummy = pk;
-  bool end_packet = false;
-  double t_future = t_current;
+// ---- vpkt.cc:76-364 rlc_emiss_vpkt in three pieces (the one-thread / one-warp ray below runs them in a row, the lock-step
+// tracer of the request list runs each piece for all its lanes at once) ----------------------------------------------------------
+// The Stokes vector a ray starts with and its probability density towards the observer (vpkt.cc:103-196)
+struct VpktStokes {
+  double I, Q, U, pn;
+};
+// set-up: `dummy` becomes the packet sent towards `obs` (which is rewritten with the rest-frame direction for a scattering,
+// vpkt.cc:178), `vel_vec` the velocity of the start position
+ARTIS_DEV void vpkt_ray_setup(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u, const double t_current,
+                              double *obs, const int realtype, Pkt &dummy, VpktStokes &sv, double *vel_vec) {
+  dummy = pk;
   dummy.dir[0] = obs[0];
   dummy.dir[1] = obs[1];
   dummy.dir[2] = obs[2];
-  double vel_vec[3], old_dir_cmf[3], obs_cmf[3], vel_rev[3], ref1[3], ref2[3];
+  double old_dir_cmf[3], obs_cmf[3], vel_rev[3], ref1[3], ref2[3];
   get_velocity(pk.pos, vel_vec, t_current);
   dummy.nu_rf = dummy.nu_cmf / doppler_nucmf_on_nurf(c, dummy.dir, vel_vec);
   dummy.e_rf = dummy.e_cmf * dummy.nu_rf / dummy.nu_cmf;
   double Qi = stokes_q, Ui = stokes_u;  // Stokes Q, U of the real packet (used by the scattering phase function only)
-  double I = 0., Q = 0., U = 0., pn = 0.;
+  sv.I = 0.;
+  sv.Q = 0.;
+  sv.U = 0.;
+  sv.pn = 0.;
   if (realtype == 1) {  // electron scattering: dipole phase function and Stokes rotation (Bulla et al. 2015)
     double dir_in[3] = {pk.dir[0], pk.dir[1], pk.dir[2]};
     frame_transform(dir_in, &Qi, &Ui, vel_vec, old_dir_cmf);
@@ -360,29 +358,86 @@ ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double 
     const double Qold = Qi * cos2i1 - Ui * sin2i1;
     const double Uold = Qi * sin2i1 + Ui * cos2i1;
     const double mu = dot3(old_dir_cmf, obs_cmf);
-    pn = 3. / (16. * PI) * (1 + mu * mu + (mu * mu - 1) * Qold);  // pow(mu, 2.) in the reference
+    sv.pn = 3. / (16. * PI) * (1 + mu * mu + (mu * mu - 1) * Qold);  // pow(mu, 2.) in the reference
     const double Inew = 0.75 * ((mu * mu + 1.0) + Qold * (mu * mu - 1.0));
     double Qnew = 0.75 * ((mu * mu - 1.0) + Qold * (mu * mu + 1.0));
     double Unew = 1.5 * mu * Uold;
     Qnew = Qnew / Inew;
     Unew = Unew / Inew;
-    I = Inew / Inew;
+    sv.I = Inew / Inew;
     meridian(obs_cmf, ref1, ref2);
     const double i2 = PI + rot_angle(obs_cmf, old_dir_cmf, ref1, ref2);
     const double cos2i2 = cos(2 * i2), sin2i2 = sin(2 * i2);
-    Q = Qnew * cos2i2 + Unew * sin2i2;
-    U = -Qnew * sin2i2 + Unew * cos2i2;
+    sv.Q = Qnew * cos2i2 + Unew * sin2i2;
+    sv.U = -Qnew * sin2i2 + Unew * cos2i2;
     vel_rev[0] = -vel_vec[0];
     vel_rev[1] = -vel_vec[1];
     vel_rev[2] = -vel_vec[2];
-    frame_transform(obs_cmf, &Q, &U, vel_rev, obs);  // writes the rest-frame direction back into obs (vpkt.cc:178)
+    frame_transform(obs_cmf, &sv.Q, &sv.U, vel_rev, obs);  // writes the rest-frame direction back into obs (vpkt.cc:178)
   }
   if (realtype == 2 || realtype == 3) {  // isotropic emission
-    I = 1;
-    Q = 0;
-    U = 0;
-    pn = 1 / (4 * PI);
+    sv.I = 1;
+    sv.Q = 0;
+    sv.U = 0;
+    sv.pn = 1 / (4 * PI);
   }
+}
+// the continuum term of a cell on every spectrum's optical depth (vpkt.cc:222-250); returns true when the ray is dead
+ARTIS_DEV bool vpkt_add_continuum(const Ctx &c, const VpktKappa &k, const double s_cont, double *tau_vpkt) {
+  const double kap_cont = k.total;
+  const double kap_cont_nobf = kap_cont - k.bf, kap_cont_noff = kap_cont - k.ff, kap_cont_noes = kap_cont - k.es;
+  for (int ind = 0; ind < c.st.vpkt_nspectra; ind++) {
+    const double ex = c.st.vpkt_exclude[ind];
+    if (ex == -2)
+      tau_vpkt[ind] += kap_cont_nobf * s_cont;
+    else if (ex == -3)
+      tau_vpkt[ind] += kap_cont_noff * s_cont;
+    else if (ex == -4)
+      tau_vpkt[ind] += kap_cont_noes * s_cont;
+    else
+      tau_vpkt[ind] += kap_cont * s_cont;
+  }
+  return vpkt_check_tau(c, tau_vpkt) == 0;
+}
+// the end of a ray that has left the model: its Stokes vector, binned on the fly (vpkt.cc:336-362)
+ARTIS_DEV void vpkt_ray_bin(const Ctx &c, const Pkt &pk, const Pkt &dummy, const double *tau_vpkt, const VpktStokes &sv,
+                            const double *vel_vec, const int bin, const double *obs, const double t_current) {
+  const double t_arrive = t_current - (dot3(pk.pos, dummy.dir) / CLIGHT_PROP);
+  for (int ind = 0; ind < c.st.vpkt_nspectra; ind++) {
+    const double prob = sv.pn * exp(-tau_vpkt[ind]);
+    const double stokes[3] = {sv.I * prob, sv.Q * prob, sv.U * prob};
+    add_to_vspecpol(c, dummy.nu_rf, dummy.e_rf, stokes, bin, ind, t_arrive);
+  }
+  if (c.st.vpkt_vgrid_flag == 1) {
+    const double prob = sv.pn * exp(-tau_vpkt[0]);
+    const double stokes[3] = {sv.I * prob, sv.Q * prob, sv.U * prob};
+    for (int bin_range = 0; bin_range < c.st.vpkt_nrange_grid; bin_range++) {
+      if (dummy.nu_rf > c.st.vpkt_nu_grid_min[bin_range] && dummy.nu_rf < c.st.vpkt_nu_grid_max[bin_range]) {
+        if (t_arrive > c.st.vpkt_tmin_grid && t_arrive < c.st.vpkt_tmax_grid)
+          add_to_vpkt_grid(c, dummy.nu_rf, dummy.e_rf, stokes, vel_vec, bin_range, bin, obs);
+      }
+    }
+  }
+}
+
+// One ray from set-up to binning. `pk` is the real packet (read only), `k` the opacity scratch of the request, `first` the
+// start cell's opacity shared by the request's rays. Returns the change of the virtual-packet counters: bit 0 = a virtual
+// packet was created, bit 1 = it reached the edge of the grid. COOP: warp-uniform arguments and result.
+template <bool COOP>
+ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double stokes_q, const double stokes_u,
+                                      const double t_current, const int bin, double *obs, const int realtype, VpktKappa &k,
+                                      VpktKappa &first, Tally &tl) {
+  const bool lead = vp_lane<COOP>() == 0;
+  VP_T0();
+  VP_COUNT(59);
+  double tau_vpkt[VPKT_MAX_SPECTRA];
+  for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_vpkt[ind] = 0;
+  Pkt dummy;
+  VpktStokes sv;
+  double vel_vec[3];
+  vpkt_ray_setup(c, pk, stokes_q, stokes_u, t_current, obs, realtype, dummy, sv, vel_vec);
+  bool end_packet = false;
+  double t_future = t_current;
   int mgi = cell_mgi(c, dummy.where);
   const int tc0 = tabcell(c, mgi);  // level populations of the whole ray come from the start cell (see vpkt_bf_term)
   bool at_start = true;
@@ -409,20 +464,7 @@ ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double 
       first = k;
       at_start = false;
     }
-    const double kap_cont = k.total;
-    const double kap_cont_nobf = kap_cont - k.bf, kap_cont_noff = kap_cont - k.ff, kap_cont_noes = kap_cont - k.es;
-    for (int ind = 0; ind < nspectra; ind++) {
-      const double ex = c.st.vpkt_exclude[ind];
-      if (ex == -2)
-        tau_vpkt[ind] += kap_cont_nobf * s_cont;
-      else if (ex == -3)
-        tau_vpkt[ind] += kap_cont_noff * s_cont;
-      else if (ex == -4)
-        tau_vpkt[ind] += kap_cont_noes * s_cont;
-      else
-        tau_vpkt[ind] += kap_cont * s_cont;
-    }
-    if (vpkt_check_tau(c, tau_vpkt) == 0) return 1;
+    if (vpkt_add_continuum(c, k, s_cont, tau_vpkt)) return 1;
     {
       const bool dead = vpkt_line_sweep<COOP>(c, dummy.nu_cmf, t_current, sdist, tc0, dummy.next_trans, tau_vpkt, tl, true);
       VP_ADD(55);
@@ -442,24 +484,7 @@ ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double 
     if (mgi == c.st.npts_model) break;        // reached an empty cell
     if (c.cs.thick[mgi] == 1) return 1;       // a virtual packet dies in a grey cell
   }
-  if (lead) {  // final Stokes vector, binned on the fly
-    const double t_arrive = t_current - (dot3(pk.pos, dummy.dir) / CLIGHT_PROP);
-    for (int ind = 0; ind < nspectra; ind++) {
-      const double prob = pn * exp(-tau_vpkt[ind]);
-      const double stokes[3] = {I * prob, Q * prob, U * prob};
-      add_to_vspecpol(c, dummy.nu_rf, dummy.e_rf, stokes, bin, ind, t_arrive);
-    }
-    if (c.st.vpkt_vgrid_flag == 1) {
-      const double prob = pn * exp(-tau_vpkt[0]);
-      const double stokes[3] = {I * prob, Q * prob, U * prob};
-      for (int bin_range = 0; bin_range < c.st.vpkt_nrange_grid; bin_range++) {
-        if (dummy.nu_rf > c.st.vpkt_nu_grid_min[bin_range] && dummy.nu_rf < c.st.vpkt_nu_grid_max[bin_range]) {
-          if (t_arrive > c.st.vpkt_tmin_grid && t_arrive < c.st.vpkt_tmax_grid)
-            add_to_vpkt_grid(c, dummy.nu_rf, dummy.e_rf, stokes, vel_vec, bin_range, bin, obs);
-        }
-      }
-    }
-  }
+  if (lead) vpkt_ray_bin(c, pk, dummy, tau_vpkt, sv, vel_vec, bin, obs, t_current);
   return 3;
 }
 
@@ -627,6 +652,245 @@ __device__ __forceinline__ void vpkt_trace_request(const Ctx &c, const VpktReq &
   q.prop_time = r.prop_time;
   q.cold = nullptr;
   vpkt_call_estimators<COOP>(c, q, r.stokes_q, r.stokes_u, r.prop_time, r.realtype, tl);
+}
+
+// ---- the request list traced in lock step (k_vpkt_trace, transport.cu) -----------------------------------------------------------
+// A thread per request that simply calls vpkt_call_estimators runs at 3.7 active lanes per instruction
+// (profiles/r2_c5_vpkt_trace_v1_ncu_summary.txt): the 32 rays of a warp are each somewhere else in their cell loop -- one in a
+// continuum sum, one in a line sweep, one crossing a boundary -- and the hardware runs the groups one after the other. Here a
+// lane still owns a request and traces its rays one after the other, but the WARP moves through the phases of a cell
+// together: (A) lanes without a request take the next one of the list, (B) lanes without a ray set up the next observer's,
+// (C) every ray finds its cell boundary, (D) runs its lines-first probe, (E) the rays that need a continuum opacity get
+// their bound-free sums from the whole warp, an owner at a time, 32 continua per round (coalesced rows, tile-tree order),
+// (F) continuum term and the real line sweep, (G) the move into the next cell or the end of the ray. Same arithmetic per ray
+// as rlc_emiss_vpkt<false>, in the same order: the same bits.
+__device__ __forceinline__ void vpkt_trace_lockstep(const Ctx &c, const VpktReq *req, const long long n, unsigned long long *cursor,
+                                                    Tally &tl) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const int nobs = c.st.vpkt_nobs, nrange = c.st.vpkt_nrange;
+  // the lane's request
+  bool has_req = false, exhausted = false;
+  Pkt pk;
+  double req_q = 0., req_u = 0.;
+  int realtype = 0, next_pair = 0, created = 0, escaped = 0;
+  VpktKappa first;
+  first.valid = false;
+  // the lane's ray
+  bool ray = false;
+  Pkt d;
+  VpktStokes sv;
+  VpktKappa k;
+  k.valid = false;
+  double tau_vpkt[VPKT_MAX_SPECTRA], vel_vec[3], obs[3], t_future = 0.;
+  int mgi = 0, tc0 = 0, bin = 0;
+  bool at_start = false;
+  while (true) {
+    // (A) requests
+    const unsigned want = __ballot_sync(full, !has_req && !exhausted);
+    if (want != 0u) {
+      unsigned long long base = 0ull;
+      if (lane == __ffs(want) - 1) base = atomicAdd(cursor, (unsigned long long)__popc(want));
+      base = __shfl_sync(full, base, __ffs(want) - 1);
+      if (!has_req && !exhausted) {
+        const long long idx = (long long)base + __popc(want & lt_mask);
+        if (idx < n) {
+          VpktReq r;
+          const uint4 *src = reinterpret_cast<const uint4 *>(req + idx);
+          uint4 *dst = reinterpret_cast<uint4 *>(&r);
+#pragma unroll
+          for (int q = 0; q < 8; q++) dst[q] = __ldcg(src + q);
+          pk.where = r.where;
+          pk.type = ARTIS_TYPE_RPKT;
+          pk.last_cross = r.last_cross;
+          pk.interactions = 0;
+          pk.last_event = 0;
+          pk.next_trans = r.next_trans;
+          pk.number = 0;
+          pk.ma_element = pk.ma_ion = pk.ma_level = pk.ma_activatingline = 0;
+          for (int q = 0; q < 3; q++) {
+            pk.pos[q] = r.pos[q];
+            pk.dir[q] = r.dir[q];
+          }
+          pk.e_cmf = r.e_cmf;
+          pk.e_rf = 0.;
+          pk.nu_cmf = r.nu_cmf;
+          pk.nu_rf = 0.;
+          pk.prop_time = r.prop_time;
+          pk.cold = nullptr;
+          req_q = r.stokes_q;
+          req_u = r.stokes_u;
+          realtype = r.realtype;
+          has_req = true;
+          next_pair = (c.cs.thick[cell_mgi(c, pk.where)] != 0) ? nobs * nrange : 0;  // vpkt.cc:846
+          created = escaped = 0;
+          first.valid = false;
+        } else {
+          exhausted = true;
+        }
+      }
+    }
+    if (__ballot_sync(full, has_req) == 0u) break;  // the list is done and so is every ray of this warp
+    // (B) the next observer (and frequency range) whose windows the request passes: vpkt.cc:850-880
+    bool starting = false;
+    if (has_req && !ray) {
+      const double t_current = pk.prop_time;
+      double vel0[3];
+      get_velocity(pk.pos, vel0, t_current);
+      while (next_pair < nobs * nrange) {
+        const int b = next_pair / nrange, i = next_pair - b * nrange;
+        next_pair++;
+        const double nz = c.st.vpkt_nz_obs[b];
+        obs[0] = sqrt(1 - nz * nz) * cos(c.st.vpkt_phiobs[b]);
+        obs[1] = sqrt(1 - nz * nz) * sin(c.st.vpkt_phiobs[b]);
+        obs[2] = nz;
+        const double t_arrive = t_current - (dot3(pk.pos, obs) / CLIGHT_PROP);
+        if (t_arrive >= c.st.vpkt_tmin_input && t_arrive <= c.st.vpkt_tmax_input) {
+          const double nu_rf = pk.nu_cmf / doppler_nucmf_on_nurf(c, obs, vel0);
+          if (nu_rf > c.st.vpkt_numin_input[i] && nu_rf < c.st.vpkt_numax_input[i]) {
+            bin = b;
+            starting = true;
+            break;
+          }
+        }
+      }
+      if (!starting) {  // the request is finished
+        if (created) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT], (double)created);
+        if (escaped) est_add(&c.es.ts_scalars[ARTIS_TS_NVPKT_ESC1 + realtype - 1], (double)escaped);
+        has_req = false;
+      }
+    }
+    __syncwarp(full);
+    if (starting) {
+      for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_vpkt[ind] = 0;
+      vpkt_ray_setup(c, pk, req_q, req_u, pk.prop_time, obs, realtype, d, sv, vel_vec);
+      t_future = pk.prop_time;
+      mgi = cell_mgi(c, d.where);
+      tc0 = tabcell(c, mgi);
+      at_start = true;
+      k.valid = false;
+      if (first.valid) k = first;
+      created++;
+      ray = true;
+    }
+    __syncwarp(full);
+    if (__ballot_sync(full, ray) == 0u) continue;
+    const double t_current = pk.prop_time;
+    // (C) the cell boundary
+    int snext = 0;
+    double sdist = 0., s_cont = 0.;
+    if (ray) {
+      sdist = boundary_cross(c, d, &snext);
+      s_cont = sdist * t_current * t_current * t_current / (t_future * t_future * t_future);
+    }
+    __syncwarp(full);
+    // (D) lines first
+    bool dead = false;
+    if (ray) {
+      double tau_probe[VPKT_MAX_SPECTRA];
+      for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_probe[ind] = tau_vpkt[ind];
+      int next_probe = d.next_trans;
+      dead = vpkt_line_sweep<false>(c, d.nu_cmf, t_current, sdist, tc0, next_probe, tau_probe, tl, false);
+    }
+    __syncwarp(full);
+    // (E) the continuum opacity of the cell: vpkt_kappa_cont<false> with the bound-free sum shared out
+    {
+      const double nu = d.nu_cmf;
+      const bool needk = ray && !dead && !(k.valid && (mgi == k.mgi) && (fabs(k.nu / nu - 1.0) < 1e-4));
+      double sigma = 0., kappa_ff = 0., kappa_bf = 0., T_e = 1., expfac = 0.;
+      int tc = 0, ilo = 0, i0 = 0;
+      bool needbf = false;
+      if (needk) {
+        tl.kappa_evals++;
+        if (c.st.do_r_lc) {
+          if (c.st.opacity_case == 4) {
+            sigma = SIGMA_T * c.cs.nne[mgi];
+            kappa_ff = calculate_kappa_ff(c, mgi, nu);
+            tc = tabcell(c, mgi);
+            T_e = (double)c.cs.Te[mgi];
+            expfac = exp(-HOVERKB * nu / T_e);
+            i0 = bf_stop_index(c, nu);
+            ilo = bf_start_index(c, nu, i0);
+            tl.bf_evaluated += i0 - ilo;
+            needbf = true;
+          } else {
+            kappa_ff = 1e5 * calculate_kappa_ff(c, mgi, nu);
+          }
+        }
+      }
+      unsigned owners = __ballot_sync(full, needbf);
+      while (owners != 0u) {
+        const int o = __ffs(owners) - 1;
+        owners &= owners - 1u;
+        const double o_nu = __shfl_sync(full, nu, o), o_Te = __shfl_sync(full, T_e, o), o_exp = __shfl_sync(full, expfac, o);
+        const int o_tc = __shfl_sync(full, tc, o), o_tc0 = __shfl_sync(full, tc0, o), o_mgi = __shfl_sync(full, mgi, o);
+        const int o_ilo = __shfl_sync(full, ilo, o), o_i0 = __shfl_sync(full, i0, o);
+        double sum = 0.;
+        for (int base = o_ilo; base < o_i0; base += BF_TILE) {
+          const int i = base + lane;
+          double t = (i < o_i0) ? vpkt_bf_term(c, o_tc, o_tc0, o_mgi, i, o_nu, o_Te, o_exp) : 0.;
+#pragma unroll
+          for (int off = 1; off < BF_TILE; off <<= 1) t += __shfl_down_sync(full, t, off);
+          sum += t;  // lane 0 holds the tile sums in tree order
+        }
+        sum = __shfl_sync(full, sum, 0);
+        if (lane == o) kappa_bf = sum;
+      }
+      if (needk) {  // rpkt.cuh kappa_store
+        k.nu = nu;
+        k.mgi = mgi;
+        k.valid = true;
+        k.total = sigma + kappa_bf + kappa_ff;
+        k.es = sigma;
+        k.ff = kappa_ff;
+        k.bf = kappa_bf;
+        if (!isfinite(k.total)) {
+          if (isfinite(k.es)) {
+            k.ff = 0.;
+            k.bf = 0.;
+            k.total = k.es;
+            tl.soft_repairs++;
+          } else {
+            fatal(c, 101);
+          }
+        }
+      }
+    }
+    __syncwarp(full);
+    // (F) the continuum term, then the cell's lines in the reference's order
+    if (ray && !dead) {
+      if (at_start) {
+        first = k;
+        at_start = false;
+      }
+      dead = vpkt_add_continuum(c, k, s_cont, tau_vpkt);
+      if (!dead) dead = vpkt_line_sweep<false>(c, d.nu_cmf, t_current, sdist, tc0, d.next_trans, tau_vpkt, tl, true);
+    }
+    __syncwarp(full);
+    // (G) into the next cell, or out of the model
+    if (ray && !dead) {
+      t_future += (sdist / CLIGHT_PROP);
+      d.prop_time = t_future;
+      move_pkt(c, d, sdist);
+      bool out = false;
+      if (snext == -99) {
+        out = true;
+      } else {
+        d.where = snext;
+        stat_inc(tl, COUNTER_CELLCROSSINGS);
+      }
+      mgi = cell_mgi(c, d.where);
+      if (out || mgi == c.st.npts_model) {  // left the grid / reached an empty cell: the ray arrives
+        vpkt_ray_bin(c, pk, d, tau_vpkt, sv, vel_vec, bin, obs, t_current);
+        escaped++;
+        ray = false;
+      } else if (c.cs.thick[mgi] == 1) {  // a virtual packet dies in a grey cell
+        ray = false;
+      }
+    }
+    if (ray && dead) ray = false;
+  }
 }
 
 // The persistent kernels' one call site when the rays are NOT deferred (A/B builds), reached by all 32 lanes together. The requests the lanes' events have left are

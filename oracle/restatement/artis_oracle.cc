@@ -101,7 +101,7 @@ void be_run_wavefront(PktHot *hot, PktCold *cold, const artis::QueueView &qv, in
 // the barrier-free scheduler is a device-only construct; the host backend runs the same visits as kernel rounds
 bool be_run_persistent(PktHot *, PktCold *, int *, int, unsigned long long *, unsigned long long *, int, long long) { return false; }
 int be_persistent_kernels() { return 0; }
-void be_run_vpkt_trace(const artis::VpktReq *, long long) {}  // the host build traces virtual packets where their events happen
+void be_run_vpkt_trace(const artis::VpktReq *, long long, unsigned long long *) {}  // the host build traces virtual packets where their events happen
 bool be_vpkt_deferred() { return false; }
 int be_scheduler_geometry(int *) { return 0; }
 long long be_resident_lanes() { return 1; }
