@@ -1,6 +1,7 @@
 """GPU parity on the BENCH workloads themselves: the models bench.py is quoted on -- the classic
 100^3 model at timestep 25, the same with virtual packets + polarisation at timestep 30 (config 5), the kilonova model with
-1.1e6 lines at timestep 7 (config 3) -- z-tested against ensembles of the unmodified reference run on exactly those inputs
+1.1e6 lines at timestep 7 (config 3), the one-zone nebular NLTE model on the 50^3 grid at timestep 8 (config 2) -- z-tested
+against ensembles of the unmodified reference run on exactly those inputs
 (oracle/tools/ref_bench_rows.py; tests/golden/bench_rows_*.npz hold the reference's summary rows and a fingerprint of the
 inputs). The inputs are the run directories that __graft_entry__.build() makes where /root/reference exists
 (oracle/_ref/runs/bench_*; bit-reproducible; they travel to the GPU box with the working tree, as for bench.py). The summary
@@ -31,7 +32,7 @@ def fingerprint(snap):  # oracle/tools/ref_bench_rows.py fingerprint()
     return h.hexdigest()
 
 
-@pytest.mark.parametrize("workload", ["classic", "vpkt", "kilonova"])
+@pytest.mark.parametrize("workload", ["classic", "vpkt", "kilonova", "nebular"])
 def test_cuda_ensemble_on_bench_workload(gpu_lib, workload):
     gold = os.path.join(HERE, "golden", f"bench_rows_{workload}.npz")
     if not os.path.exists(gold):
