@@ -293,6 +293,12 @@ struct CellTables {
   // [ncells][nbfcontinua][2]: level pop of allcont[i] (-1 if the continuum is skipped) and its departure ratio
   // (ch_allcont_departureratios, rpkt.cc:1136-1145), interleaved so that one 16-byte load brings both
   double *bf_cell;
+  // The LIVE continua of every cell, in list order (celltables.cuh bf_is_live): those whose term of the bound-free sum can be
+  // non-zero at some frequency. bf_live_off[tc] .. bf_live_off[tc + 1] index the cell's entries of bf_live_pair (the bf_cell
+  // pair) and bf_live_rec (a copy of the continuum's static record). nullptr: the sums run over the full list.
+  const long long *bf_live_off;  // [ncells + 1]
+  const double *bf_live_pair;    // [.][2]
+  const ContRec *bf_live_rec;    // [.]
   double *ma_rates;          // [ncells][nlevels_total][9]     chlevels.processrates (macroatom.cc:57-159)
   double *ma_cum_raddeexc;   // [ncells][ndowntrans_total]     running sum of individ_rad_deexc
   double *ma_cum_intdown;    // [ncells][ndowntrans_total]     running sum of individ_internal_down_same

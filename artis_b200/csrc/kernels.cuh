@@ -17,6 +17,19 @@ ARTIS_DEV void body_bf(const Ctx &c, const long long idx) {
   const int mgi = c.mgi_of_tabcell[tc];
   if (cell_uses_tables(c, mgi)) build_bf(c, mgi, (int)(idx % c.st.nbfcontinua));
 }
+// the live continua of a table cell (rpkt.cuh bf_is_live), from the pairs body_bf has written
+ARTIS_DEV bool body_bf_live_test(const Ctx &c, const int tc, const int i) {
+  const int mgi = c.mgi_of_tabcell[tc];
+  if (!cell_uses_tables(c, mgi)) return false;
+  const double *cell = c.tb.bf_cell + 2 * ((size_t)tc * c.st.nbfcontinua + i);
+  return bf_is_live(c, mgi, cell[0], cell[1], c.cont_rec[i].nu_edge);
+}
+ARTIS_DEV void body_bf_live_store(const Ctx &c, const int tc, const int i, const long long at, double *pair, ContRec *rec) {
+  const double *cell = c.tb.bf_cell + 2 * ((size_t)tc * c.st.nbfcontinua + i);
+  pair[2 * at] = cell[0];
+  pair[2 * at + 1] = cell[1];
+  rec[at] = c.cont_rec[i];
+}
 ARTIS_DEV void body_corrphoto(const Ctx &c, const long long idx) {
   const int tc = (int)(idx / c.st.nbfcontinua);
   const int mgi = c.mgi_of_tabcell[tc];

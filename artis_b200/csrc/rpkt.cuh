@@ -396,6 +396,70 @@ ARTIS_DEV int bf_start_index(const Ctx &c, const double nu, const int i0) {
   return lo;
 }
 
+// ---- live continua --------------------------------------------------------------------------------------------------------------
+// A term of the sum is n_level * sigma_bf(nu) * probability * max(0, 1 - departure_ratio * exp(-h nu / k T_e)) for
+// nu_edge <= nu <= nu_edge * last_phixs_nuovernuedge. In the dilute radiation fields of a supernova most excited levels sit
+// far below their Saha-Boltzmann population at T_e, the stimulated-recombination factor exceeds one over the whole
+// frequency range of the cross-section table, and the reference adds an exact zero -- for five terms out of six of the
+// classic model at maximum light, a further share because the ion is absent from the cell (rpkt.cc:1101-1104). Whether a
+// continuum can EVER contribute in a cell does not depend on the packet: exp(-h nu / k T_e) is smallest at the top of the
+// table, so departure_ratio * exp(-h nu_max / k T_e) >= 1 (with a margin of 1e-9 against the last bits of exp) means the
+// clamp gives zero at every frequency. cell_precompute lists the other continua per cell, in list order
+// (CellTables.bf_live_*), and the sums below run over that list: the same non-zero terms, so the same value up to the
+// rounding of the additions (the tiles are counted along the live list), which is what already separates this sum from
+// the reference's strictly serial one.
+ARTIS_DEV bool bf_is_live(const Ctx &c, const int mgi, const double nnlevel, const double depratio, const double nu_edge) {
+  if (!(nnlevel > 0.)) return false;
+  const double nu_top = nu_edge * c.st.last_phixs_nuovernuedge;
+  return depratio * exp(-HOVERKB * nu_top / (double)c.cs.Te[mgi]) < 1. + 1e-9;
+}
+// the list a cell's sum runs over: the live continua of the cell, or every continuum (no live lists built)
+struct BfList {
+  const double *pair;   // [n][2] level population (or -1) and departure ratio
+  const ContRec *rec;   // [n]
+  int n;
+};
+ARTIS_DEV BfList bf_list(const Ctx &c, const int tc) {
+  BfList l;
+  if (c.tb.bf_live_off != nullptr) {
+    const long long o = c.tb.bf_live_off[tc];
+    l.pair = c.tb.bf_live_pair + 2 * o;
+    l.rec = c.tb.bf_live_rec + o;
+    l.n = (int)(c.tb.bf_live_off[tc + 1] - o);
+  } else {
+    l.pair = c.tb.bf_cell + 2 * ((size_t)tc * c.st.nbfcontinua);
+    l.rec = c.cont_rec;
+    l.n = c.st.nbfcontinua;
+  }
+  return l;
+}
+// bf_stop_index / bf_start_index on such a list
+ARTIS_DEV int bf_list_stop(const BfList &l, const double nu) {
+  int lo = 0, hi = l.n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (nu < l.rec[mid].nu_edge) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
+  }
+  return lo;
+}
+ARTIS_DEV int bf_list_start(const Ctx &c, const BfList &l, const double nu, const int i0) {
+  int lo = 0, hi = i0;
+  const double reach = c.st.last_phixs_nuovernuedge;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (nu <= l.rec[mid].nu_edge * reach) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
+  }
+  return lo;
+}
+
 // Summation order: the terms are added in tiles of BF_TILE consecutive continua (counted from the first visited one),
 // each tile reduced as a balanced binary tree over adjacent pairs ((t0+t1)+(t2+t3))+..., and the tile sums accumulated
 // in order. A warp produces exactly this tree with shuffle-down reductions of offsets 1, 2, 4, 8, 16
@@ -441,10 +505,10 @@ ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, cons
   double kappa_bf_sum = 0.;
   const int ng = c.st.nbfcontinua_ground;
   for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
-  const int tc = tabcell(c, mgi);
+  const BfList l = bf_list(c, tabcell(c, mgi));
   const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[mgi]);
-  const int i0 = bf_stop_index(c, nu);
-  const int ilo = bf_start_index(c, nu, i0);
+  const int i0 = bf_list_stop(l, nu);
+  const int ilo = bf_list_start(c, l, nu, i0);
   tl.bf_evaluated += i0 - ilo;
   // whole tiles: the last one is padded with zero terms, exactly like the idle lanes of a warp
   const int iend = ilo + ((i0 - ilo + BF_TILE - 1) / BF_TILE) * BF_TILE;
@@ -460,8 +524,9 @@ ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, cons
       t[u] = 0.;
       if (i < i0) {
         double gcontr;
-        int slot;
-        t[u] = kappa_bf_term(c, tc, i, nu, expfac, &gcontr, &slot);
+        const ContRec r = l.rec[i];
+        const int slot = r.ground_slot;
+        t[u] = kappa_bf_term_core(c, l.pair[2 * i], l.pair[2 * i + 1], r, nu, expfac, &gcontr);
         if (gcontr != 0. && slot >= 0) k.gamma_contr[slot] += gcontr;
       }
     }

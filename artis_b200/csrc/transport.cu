@@ -33,6 +33,80 @@ __global__ void k_bf(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_bf(d_ctx, i);
 }
+// live continua of every cell (rpkt.cuh bf_is_live): count per cell, offsets, ordered compaction. One block per table cell.
+__global__ void __launch_bounds__(256) k_bf_live_count(long long *counts) {
+  __shared__ int warp_n[8];
+  const int tc = blockIdx.x;
+  const int nbf = d_ctx.st.nbfcontinua;
+  int n = 0;
+  for (int i = threadIdx.x; i < nbf; i += 256) n += artis::body_bf_live_test(d_ctx, tc, i) ? 1 : 0;
+  for (int off = 16; off >= 1; off >>= 1) n += __shfl_down_sync(0xffffffffu, n, off);
+  if ((threadIdx.x & 31) == 0) warp_n[threadIdx.x >> 5] = n;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < 8; w++) t += warp_n[w];
+    counts[tc] = t;
+  }
+}
+__global__ void __launch_bounds__(1024) k_scan_exclusive_ll(long long *a, const int n) {  // one block; a[n] receives the total
+  __shared__ long long warp_tot[32];
+  __shared__ long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + threadIdx.x;
+    const long long v = i < n ? a[i] : 0;
+    long long x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const long long y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      long long t = warp_tot[lane];
+      for (int d = 1; d < 32; d <<= 1) {
+        const long long y = __shfl_up_sync(0xffffffffu, t, d);
+        if (lane >= d) t += y;
+      }
+      warp_tot[lane] = t;
+    }
+    __syncthreads();
+    const long long before = carry + (w > 0 ? warp_tot[w - 1] : 0) + x - v;
+    if (i < n) a[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) a[n] = carry;
+}
+__global__ void __launch_bounds__(256) k_bf_live_fill(const long long *off, double *pair, artis::ContRec *rec) {
+  __shared__ int warp_n[8];
+  __shared__ long long base;
+  const int tc = blockIdx.x;
+  const int nbf = d_ctx.st.nbfcontinua;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x == 0) base = off[tc];
+  __syncthreads();
+  for (int start = 0; start < nbf; start += 256) {
+    const int i = start + threadIdx.x;
+    const bool live = i < nbf && artis::body_bf_live_test(d_ctx, tc, i);
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    if (lane == 0) warp_n[w] = __popc(m);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int k = 0; k < 8; k++) {
+      if (k < w) before += warp_n[k];
+      total += warp_n[k];
+    }
+    if (live) artis::body_bf_live_store(d_ctx, tc, i, base + before + __popc(m & ((1u << lane) - 1u)), pair, rec);
+    __syncthreads();
+    if (threadIdx.x == 0) base += total;
+    __syncthreads();
+  }
+}
 // one warp per (cell, continuum): the lanes split the knot intervals of the photoionisation integral
 __global__ void k_corrphoto(long long n) {
   using namespace artis;
@@ -515,18 +589,23 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
   if (owners == 0u) return 0.;
   // every owner prepares its own sum in parallel: the range of continua, exp(-h nu / k T_e)
   double kappa_bf = 0., my_expfac = 0.;
-  int my_ilo = 0, my_i0 = 0, my_tc = 0;
+  int my_ilo = 0, my_i0 = 0;
+  const double *my_pair = nullptr;  // the list the sum runs over (rpkt.cuh bf_list): the cell's live continua
+  const ContRec *my_rec = nullptr;
   if (need) {
-    my_tc = tabcell(c, mgi);
+    const BfList l = bf_list(c, tabcell(c, mgi));
+    my_pair = l.pair;
+    my_rec = l.rec;
     my_expfac = exp(-HOVERKB * nu_cmf / (double)c.cs.Te[mgi]);
-    my_i0 = bf_stop_index(c, nu_cmf);
-    my_ilo = bf_start_index(c, nu_cmf, my_i0);
+    my_i0 = bf_list_stop(l, nu_cmf);
+    my_ilo = bf_list_start(c, l, nu_cmf, my_i0);
     tl.bf_evaluated += my_i0 - my_ilo;
   }
-  const int nbf = c.st.nbfcontinua;
   // the issue cursor runs KSTAGES chunks ahead of the arithmetic, across owners
   unsigned iss_rest = owners;
-  int iss_j = 0, iss_nch = 0, iss_ilo = 0, iss_i0 = 0, iss_tc = 0;
+  int iss_j = 0, iss_nch = 0, iss_ilo = 0, iss_i0 = 0;
+  const double *iss_pair = nullptr;
+  const ContRec *iss_rec = nullptr;
   unsigned iss_count = nchunk;
   auto iss_next_owner = [&]() {  // warp-uniform
     iss_nch = 0;
@@ -535,7 +614,8 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
       iss_rest &= iss_rest - 1u;
       iss_ilo = __shfl_sync(full, my_ilo, o);
       iss_i0 = __shfl_sync(full, my_i0, o);
-      iss_tc = __shfl_sync(full, my_tc, o);
+      iss_pair = reinterpret_cast<const double *>(__shfl_sync(full, reinterpret_cast<unsigned long long>(my_pair), o));
+      iss_rec = reinterpret_cast<const ContRec *>(__shfl_sync(full, reinterpret_cast<unsigned long long>(my_rec), o));
       iss_j = 0;
       iss_nch = (iss_i0 - iss_ilo + KCH - 1) / KCH;
     }
@@ -549,8 +629,8 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
       // the lanes have finished reading this stage (__syncwarp before the call): order their reads before the engine's writes
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       mbar_expect_tx(&ks->bar[st], (unsigned)n * 48u);
-      bulk_g2s(&ks->cell[st][0], c.tb.bf_cell + 2 * ((size_t)iss_tc * nbf + base), (unsigned)n * 16u, &ks->bar[st]);
-      bulk_g2s(&ks->rec[st][0], c.cont_rec + base, (unsigned)n * 32u, &ks->bar[st]);
+      bulk_g2s(&ks->cell[st][0], iss_pair + 2 * (size_t)base, (unsigned)n * 16u, &ks->bar[st]);
+      bulk_g2s(&ks->rec[st][0], iss_rec + base, (unsigned)n * 32u, &ks->bar[st]);
     }
     iss_count++;
     iss_j++;
@@ -1365,6 +1445,14 @@ void *be_alloc(size_t n) {
   return p;
 }
 void be_free(void *p) { cudaFree(p); }
+size_t be_free_bytes() {
+  size_t fr = 0, tot = 0;
+  if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return fr;
+}
 void be_h2d(void *d, const void *s, size_t n) {
   note(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, g_stream), "H2D copy");
   note(cudaStreamSynchronize(g_stream), "H2D sync");  // the caller's buffer may be pageable / reused right away
@@ -1406,6 +1494,19 @@ int grid_for(long long n, int block, int blocks_per_sm) {
 }
 void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
+// live continua: per-cell counts -> offsets in off[0 .. ncells] (device); returns the total (synchronises)
+long long be_run_bf_live_count(long long ncells, long long *off) {
+  if (ncells <= 0) return 0;
+  k_bf_live_count<<<(unsigned)ncells, 256, 0, g_stream>>>(off);
+  k_scan_exclusive_ll<<<1, 1024, 0, g_stream>>>(off, (int)ncells);
+  long long total = 0;
+  note(cudaMemcpyAsync(&total, off + ncells, sizeof(total), cudaMemcpyDeviceToHost, g_stream), "D2H");
+  note(cudaStreamSynchronize(g_stream), "D2H sync");
+  return total;
+}
+void be_run_bf_live_fill(long long ncells, const long long *off, double *pair, artis::ContRec *rec) {
+  if (ncells > 0) k_bf_live_fill<<<(unsigned)ncells, 256, 0, g_stream>>>(off, pair, rec);
+}
 void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_cooling_rates(long long ncells, int nions, double *contrib, double *total) {
