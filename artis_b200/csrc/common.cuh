@@ -299,6 +299,10 @@ struct CellTables {
   const long long *bf_live_off;  // [ncells + 1]
   const double *bf_live_pair;    // [.][2]
   const ContRec *bf_live_rec;    // [.]
+  const int *bf_live_rank;       // [ncells][nbfcontinua + 1]: live continua of the cell before list entry i
+  // [ncells]: sum over the ions of Z^2 n_ion, the cell's factor of the free-free opacity (rpkt.cc:1040-1062): what every
+  // evaluation of kappa_ff used to re-add from 30 ion populations
+  const double *ff_zsum;
   double *ma_rates;          // [ncells][nlevels_total][9]     chlevels.processrates (macroatom.cc:57-159)
   double *ma_cum_raddeexc;   // [ncells][ndowntrans_total]     running sum of individ_rad_deexc
   double *ma_cum_intdown;    // [ncells][ndowntrans_total]     running sum of individ_internal_down_same
@@ -655,6 +659,7 @@ ARTIS_DEV int int_fetch_add(int *addr, int v) {
 struct Tally {
   int rpkt_steps, lines_scanned, lines_tau, bf_evaluated, estim_atomics, gamma_steps, ma_jumps, ma_trans_scanned,
       kpkt_events, cool_scanned, interactions, soft_repairs, kappa_evals, packet_updates, handoffs;
+  int bf_listed;  // continua the reference's loop visits for the same sums (rpkt.cc:1095-1207): bf_evaluated counts the live ones
 #ifndef __CUDACC__
   int stats[34];  // stats::eventcounters increments of this thread (stats.h:48-84); on the device they live in shared memory
 #endif
@@ -704,6 +709,7 @@ ARTIS_DEV void tally_flush(const Ctx &c, const Tally &t) {
   if (t.kappa_evals) ctr_add(&k[ARTIS_CTR_KAPPA_EVALS], t.kappa_evals);
   if (t.packet_updates) ctr_add(&k[ARTIS_CTR_PACKET_UPDATES], t.packet_updates);
   if (t.handoffs) ctr_add(&k[ARTIS_CTR_HANDOFFS], t.handoffs);
+  if (t.bf_listed) ctr_add(&k[ARTIS_CTR_BF_LISTED], t.bf_listed);
 #ifndef __CUDACC__
   for (int i = 0; i < 34; i++)
     if (t.stats[i]) ctr_add(&k[i], t.stats[i]);

@@ -17,6 +17,7 @@ ARTIS_DEV void body_bf(const Ctx &c, const long long idx) {
   const int mgi = c.mgi_of_tabcell[tc];
   if (cell_uses_tables(c, mgi)) build_bf(c, mgi, (int)(idx % c.st.nbfcontinua));
 }
+ARTIS_DEV void body_ff_zsum(const Ctx &c, const long long tc, double *out) { out[tc] = kappa_ff_zsum(c, c.mgi_of_tabcell[tc]); }
 // the live continua of a table cell (rpkt.cuh bf_is_live), from the pairs body_bf has written
 ARTIS_DEV bool body_bf_live_test(const Ctx &c, const int tc, const int i) {
   const int mgi = c.mgi_of_tabcell[tc];

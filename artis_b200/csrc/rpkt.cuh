@@ -287,9 +287,8 @@ ARTIS_DEV void closest_transition_empty(const Ctx &c, Pkt &p) {
 }
 
 // ---- rpkt.cc:1027-1073 calculate_kappa_ff -------------------------------------------------------------------------
-ARTIS_DEV double calculate_kappa_ff(const Ctx &c, const int mgi, const double nu) {
-  const float nne = c.cs.nne[mgi];
-  const float T_e = c.cs.Te[mgi];
+// the frequency-independent part: sum over the ions of Z^2 n_ion, in the reference's order of addition
+ARTIS_DEV double kappa_ff_zsum(const Ctx &c, const int mgi) {
   double kappa_ff = 0.;
   int ui = 0;
   for (int element = 0; element < c.st.nelements; element++) {
@@ -302,6 +301,14 @@ ARTIS_DEV double calculate_kappa_ff(const Ctx &c, const int mgi, const double nu
       }
     }
   }
+  return kappa_ff;
+}
+ARTIS_DEV double calculate_kappa_ff(const Ctx &c, const int mgi, const double nu) {
+  const float nne = c.cs.nne[mgi];
+  const float T_e = c.cs.Te[mgi];
+  // the ion sum is a property of the cell: cell_precompute has it (CellTables.ff_zsum, the same additions in the same order)
+  const int tc = (c.tb.ff_zsum != nullptr) ? tabcell(c, mgi) : -1;
+  double kappa_ff = (tc >= 0) ? c.tb.ff_zsum[tc] : kappa_ff_zsum(c, mgi);
   // sqrt(T_e) is evaluated in float in the reference (float argument, rpkt.cc:1064)
   kappa_ff *= 3.69255e8 / sqrtf(T_e) * pow(nu, -3) * nne * (1 - exp(-HOVERKB * nu / T_e));
   return kappa_ff;
@@ -433,31 +440,21 @@ ARTIS_DEV BfList bf_list(const Ctx &c, const int tc) {
   }
   return l;
 }
-// bf_stop_index / bf_start_index on such a list
-ARTIS_DEV int bf_list_stop(const BfList &l, const double nu) {
-  int lo = 0, hi = l.n;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (nu < l.rec[mid].nu_edge) {
-      hi = mid;
-    } else {
-      lo = mid + 1;
-    }
+// The range [*ilo, *i0) of the list that frequency nu reaches -- bf_start_index / bf_stop_index of the full list (two binary
+// searches over the static edge frequencies, which every cell shares and the L1 keeps), mapped onto the cell's live list
+// through the count of live continua before each list entry. Also returns what the reference's loop visits: *listed.
+ARTIS_DEV void bf_list_range(const Ctx &c, const int tc, const double nu, int *ilo, int *i0, int *listed) {
+  const int f0 = bf_stop_index(c, nu);
+  const int flo = bf_start_index(c, nu, f0);
+  *listed = f0 - flo;
+  if (c.tb.bf_live_off != nullptr) {
+    const int *rank = c.tb.bf_live_rank + (size_t)tc * (c.st.nbfcontinua + 1);
+    *i0 = rank[f0];
+    *ilo = rank[flo];
+  } else {
+    *i0 = f0;
+    *ilo = flo;
   }
-  return lo;
-}
-ARTIS_DEV int bf_list_start(const Ctx &c, const BfList &l, const double nu, const int i0) {
-  int lo = 0, hi = i0;
-  const double reach = c.st.last_phixs_nuovernuedge;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (nu <= l.rec[mid].nu_edge * reach) {
-      hi = mid;
-    } else {
-      lo = mid + 1;
-    }
-  }
-  return lo;
 }
 
 // Summation order: the terms are added in tiles of BF_TILE consecutive continua (counted from the first visited one),
@@ -505,11 +502,13 @@ ARTIS_DEV double calculate_kappa_bf_gammacontr(const Ctx &c, const int mgi, cons
   double kappa_bf_sum = 0.;
   const int ng = c.st.nbfcontinua_ground;
   for (int g = 0; g < ng; g++) k.gamma_contr[g] = 0.;
-  const BfList l = bf_list(c, tabcell(c, mgi));
+  const int tc = tabcell(c, mgi);
+  const BfList l = bf_list(c, tc);
   const double expfac = exp(-HOVERKB * nu / (double)c.cs.Te[mgi]);
-  const int i0 = bf_list_stop(l, nu);
-  const int ilo = bf_list_start(c, l, nu, i0);
+  int i0, ilo, listed;
+  bf_list_range(c, tc, nu, &ilo, &i0, &listed);
   tl.bf_evaluated += i0 - ilo;
+  tl.bf_listed += listed;
   // whole tiles: the last one is padded with zero terms, exactly like the idle lanes of a warp
   const int iend = ilo + ((i0 - ilo + BF_TILE - 1) / BF_TILE) * BF_TILE;
   PairTree tree;

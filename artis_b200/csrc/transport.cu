@@ -33,6 +33,10 @@ __global__ void k_bf(long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     artis::body_bf(d_ctx, i);
 }
+__global__ void k_ff_zsum(long long n, double *out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    artis::body_ff_zsum(d_ctx, i, out);
+}
 // live continua of every cell (rpkt.cuh bf_is_live): count per cell, offsets, ordered compaction. One block per table cell.
 __global__ void __launch_bounds__(256) k_bf_live_count(long long *counts) {
   __shared__ int warp_n[8];
@@ -82,7 +86,7 @@ __global__ void __launch_bounds__(1024) k_scan_exclusive_ll(long long *a, const 
   }
   if (threadIdx.x == 0) a[n] = carry;
 }
-__global__ void __launch_bounds__(256) k_bf_live_fill(const long long *off, double *pair, artis::ContRec *rec) {
+__global__ void __launch_bounds__(256) k_bf_live_fill(const long long *off, double *pair, artis::ContRec *rec, int *rank) {
   __shared__ int warp_n[8];
   __shared__ long long base;
   const int tc = blockIdx.x;
@@ -101,11 +105,14 @@ __global__ void __launch_bounds__(256) k_bf_live_fill(const long long *off, doub
       if (k < w) before += warp_n[k];
       total += warp_n[k];
     }
-    if (live) artis::body_bf_live_store(d_ctx, tc, i, base + before + __popc(m & ((1u << lane) - 1u)), pair, rec);
+    const long long at = base + before + __popc(m & ((1u << lane) - 1u));
+    if (live) artis::body_bf_live_store(d_ctx, tc, i, at, pair, rec);
+    if (i < nbf) rank[(size_t)tc * (nbf + 1) + i] = (int)(at - off[tc]);
     __syncthreads();
     if (threadIdx.x == 0) base += total;
     __syncthreads();
   }
+  if (threadIdx.x == 0) rank[(size_t)tc * (nbf + 1) + nbf] = (int)(base - off[tc]);
 }
 // one warp per (cell, continuum): the lanes split the knot intervals of the photoionisation integral
 __global__ void k_corrphoto(long long n) {
@@ -593,13 +600,15 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
   const double *my_pair = nullptr;  // the list the sum runs over (rpkt.cuh bf_list): the cell's live continua
   const ContRec *my_rec = nullptr;
   if (need) {
-    const BfList l = bf_list(c, tabcell(c, mgi));
+    const int tc = tabcell(c, mgi);
+    const BfList l = bf_list(c, tc);
     my_pair = l.pair;
     my_rec = l.rec;
     my_expfac = exp(-HOVERKB * nu_cmf / (double)c.cs.Te[mgi]);
-    my_i0 = bf_list_stop(l, nu_cmf);
-    my_ilo = bf_list_start(c, l, nu_cmf, my_i0);
+    int listed;
+    bf_list_range(c, tc, nu_cmf, &my_ilo, &my_i0, &listed);
     tl.bf_evaluated += my_i0 - my_ilo;
+    tl.bf_listed += listed;  // what the reference's loop would visit: the roofline accounting reports both
   }
   // the issue cursor runs KSTAGES chunks ahead of the arithmetic, across owners
   unsigned iss_rest = owners;
@@ -787,6 +796,7 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
   long long fill_iters = 0, fill_lanes = 0;  // iterations run in kind `lane`, and the busy lanes summed over them
   // where the warp's cycles go (lane k keeps kind k's event cycles; lane 0 the scheduler's own)
   long long cyc_kind = 0, cyc_refill = 0, cyc_push = 0, cyc_idle = 0;
+  long long cyc_thin_begin = 0, cyc_thin_kappa = 0;  // lane 0: the thin role's cycles before and inside the opacity evaluation
   while (true) {
     __syncwarp(full);
     if (row_arena_stop(c, lane)) {
@@ -888,6 +898,8 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
           proceed = rpkt_step_begin<1>(c, p, rng, tl, st);
         }
       }
+      __syncwarp(full);
+      const long long tick_a = clock64();
       const bool wants = proceed && !resumed && c.st.do_r_lc && c.st.opacity_case == 4 && !kappa_cache_hit(k, st.mgi, p.nu_cmf);
       if constexpr (KAPPA_HERE) {
         // the sum is evaluated here, by this warp
@@ -899,6 +911,12 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
         __stcg(ss + 1, st.sdist);
         __stcg(ss + 2, __longlong_as_double(((long long)st.snext << 32) | (long long)(unsigned)st.mgi));
         parked = true;
+      }
+      __syncwarp(full);
+      if (lane == 0) {
+        const long long tick_b = clock64();
+        cyc_thin_begin += tick_a - tick1;
+        cyc_thin_kappa += tick_b - tick_a;
       }
       if (proceed && !parked) rpkt_step_finish<1>(c, p, t2, k, rng, tl, st);
       if (k.defer_bfest) coop_bfest_flush(c, k, tl);  // warp-uniform: the flag is an option of the build mode
@@ -1000,6 +1018,8 @@ __global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persis
     ctr_add(&c.es.counters[ARTIS_CTR_REFILL_CYCLES], cyc_refill);
     ctr_add(&c.es.counters[ARTIS_CTR_PUSH_CYCLES], cyc_push);
     ctr_add(&c.es.counters[ARTIS_CTR_IDLE_CYCLES], cyc_idle);
+    if (cyc_thin_begin) ctr_add(&c.es.counters[ARTIS_CTR_THIN_BEGIN_CYCLES], cyc_thin_begin);
+    if (cyc_thin_kappa) ctr_add(&c.es.counters[ARTIS_CTR_THIN_KAPPA_CYCLES], cyc_thin_kappa);
   }
   stats_block_flush(c);
 }
@@ -1494,6 +1514,7 @@ int grid_for(long long n, int block, int blocks_per_sm) {
 }
 void be_run_levelpop(long long n) { if (n > 0) k_levelpop<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
 void be_run_bf(long long n) { if (n > 0) k_bf<<<grid_for(n, 256, 8), 256, 0, g_stream>>>(n); }
+void be_run_ff_zsum(long long n, double *out) { if (n > 0) k_ff_zsum<<<grid_for(n, 128, 8), 128, 0, g_stream>>>(n, out); }
 // live continua: per-cell counts -> offsets in off[0 .. ncells] (device); returns the total (synchronises)
 long long be_run_bf_live_count(long long ncells, long long *off) {
   if (ncells <= 0) return 0;
@@ -1504,8 +1525,8 @@ long long be_run_bf_live_count(long long ncells, long long *off) {
   note(cudaStreamSynchronize(g_stream), "D2H sync");
   return total;
 }
-void be_run_bf_live_fill(long long ncells, const long long *off, double *pair, artis::ContRec *rec) {
-  if (ncells > 0) k_bf_live_fill<<<(unsigned)ncells, 256, 0, g_stream>>>(off, pair, rec);
+void be_run_bf_live_fill(long long ncells, const long long *off, double *pair, artis::ContRec *rec, int *rank) {
+  if (ncells > 0) k_bf_live_fill<<<(unsigned)ncells, 256, 0, g_stream>>>(off, pair, rec, rank);
 }
 void be_run_corrphoto(long long n) { if (n > 0) k_corrphoto<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }
 void be_run_ma(long long n) { if (n > 0) k_ma<<<grid_for(n * 32, 128, 8), 128, 0, g_stream>>>(n); }

@@ -132,8 +132,8 @@ ARTIS_DEV double vpkt_bf_term(const Ctx &c, const int tc, const int tc0, const i
 //      (non-negative) continuum term first can only leave every later partial sum at least as large -- and the ray is dead
 //      either way: it is dropped without the sum. A ray that survives the probe evaluates the sum and repeats the sweep in
 //      the reference's order. The work counters count the real sweep only.
-// -DARTIS_VPKT_PROFILE: where a ray's cycles go (measurement builds only): counters[51..58] = cycles in set-up, boundary_cross,
-// the probe sweep, the continuum sum, the real sweep, the move, the binning; counters[59] = rays, [60] = cells
+// -DARTIS_VPKT_PROFILE: where a ray's cycles go (measurement builds only): counters[54..56] = cycles in boundary_cross + continuum sum, both line sweeps, set-up + move;
+// counters[59] = rays, [60] = cells
 #if defined(ARTIS_VPKT_PROFILE) && defined(__CUDA_ARCH__)
 #define VP_T0() long long vp_t = clock64()
 #define VP_ADD(slot)                                                                       \
@@ -443,19 +443,19 @@ ARTIS_DEV_NOINLINE int rlc_emiss_vpkt(const Ctx &c, const Pkt &pk, const double 
   bool at_start = true;
   k.valid = false;  // cellhistory_reset(mgi, false) at vpkt.cc:887: a ray starts without a cached opacity ...
   if (first.valid) k = first;  // ... and would evaluate exactly this one first
-  VP_ADD(51);
+  VP_ADD(56);  // (set-up shares the slot of the move: 51 is ARTIS_CTR_BF_LISTED)
   while (!end_packet) {
     VP_COUNT(60);
     int snext = 0;
     const double sdist = boundary_cross(c, dummy, &snext);
     const double s_cont = sdist * t_current * t_current * t_current / (t_future * t_future * t_future);
-    VP_ADD(52);
+    VP_ADD(54);  // (boundary_cross shares the slot of the continuum sum: 52 / 53 are the thin role's cycle counters)
     {  // lines first (see above): the cell's sweep on a copy, without the continuum term
       double tau_probe[VPKT_MAX_SPECTRA];
       for (int ind = 0; ind < VPKT_MAX_SPECTRA; ind++) tau_probe[ind] = tau_vpkt[ind];
       int next_probe = dummy.next_trans;
       const bool dead = vpkt_line_sweep<COOP>(c, dummy.nu_cmf, t_current, sdist, tc0, next_probe, tau_probe, tl, false);
-      VP_ADD(53);
+      VP_ADD(55);  // (probe sweep shares the slot of the real sweep)
       if (dead) return 1;
     }
     vpkt_kappa_cont<COOP>(c, dummy.nu_cmf, mgi, tc0, k, tl);

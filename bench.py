@@ -155,6 +155,13 @@ def measured_traffic(name, packets):
     return None
 
 
+def algorithmic_bytes_every_continuum(ctr):
+    """the same formula with n_bf = the continua the REFERENCE's loop visits for the same opacity evaluations (device counter
+    ARTIS_CTR_BF_LISTED): the library's own sums run over the live continua of the cell only, so its n_bf -- and
+    with it the bytes its algorithm needs -- is several times smaller on the classic model"""
+    return algorithmic_bytes(ctr) + 80 * (ctr[51] - ctr[38]) if ctr[51] > 0 else algorithmic_bytes(ctr)
+
+
 def algorithmic_bytes(ctr):
     """B = 208 n_rpkt_step + 8 n_scan + 64 n_tau + 80 n_bf + 16 n_est + (72 n_ma_jump + 8 n_ma_probe)
     + (72 n_kpkt + 8 n_cool_probe) + 240 n_gamma_step, all exact device counters of the timed steps."""
@@ -387,6 +394,7 @@ def main():
     # NCCL group as the estimators): every rank holds the job's totals
     inter_all = float(ctr_sum[45])
     alg_bytes = float(algorithmic_bytes(ctr_sum)) / world  # of this rank's kernel (equal shards)
+    alg_bytes_ref = float(algorithmic_bytes_every_continuum(ctr_sum)) / world
     value = inter_all / (tot_ms * 1e-3)
 
     # end-to-end through the C ABI with host buffers
@@ -444,13 +452,15 @@ def main():
                            "warp_iters_by_kind": [float(x) / a.steps / world for x in ctr_sum[64:72]],
                            "mean_busy_lanes_by_kind": [round(float(ctr_sum[72 + i]) / max(float(ctr_sum[64 + i]), 1.0), 2) for i in range(8)],
                            "warp_Mcycles_by_kind": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[80:88]],
+                           "rpkt_steps_and_kappa_evals_per_step": [float(ctr_sum[35]) / a.steps / world, float(ctr_sum[48]) / a.steps / world],
+                           "thin_role_Mcycles_begin_kappa": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[52:54]],
                            "warp_Mcycles_refill_push_idle": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[88:91]],
                            "scheduler_geometry_kernels_blocks_single_big_jump": T.scheduler_geometry(),
-                           # -DARTIS_VPKT_PROFILE builds only (vpkt.cuh): Mcycles per step in set-up, boundary_cross, probe sweep,
-                           # continuum sum, real sweep, move, (unused), (unused); then rays and cells per step
+                           # -DARTIS_VPKT_PROFILE builds only (vpkt.cuh): Mcycles per step in boundary_cross + continuum sum, the two line
+                           # sweeps, set-up + move; then rays and cells per step
                            "vpkt_requests_per_step": float(ctr_sum[57]) / a.steps / world if st.get("opt_vpkt_on") else None,
                            "vpkt_list_restarts_per_step": float(ctr_sum[58]) / a.steps / world if st.get("opt_vpkt_on") else None,
-                           "vpkt_profile": ([round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[51:59]] +
+                           "vpkt_profile": ([round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[54:57]] +
                                             [float(x) / a.steps / world for x in ctr_sum[59:61]]) if ctr_sum[59] > 0 else None,
                            "allreduce_ms_per_step": allreduce_ms / a.steps,
                            "estimator_block_bytes": int(ndoubles * 8),
@@ -461,6 +471,10 @@ def main():
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6537.6",
                              "kernel": "k_transport_persistent", "launches_per_step": 1,
                              "algorithmic_bytes_per_launch": alg_bytes / a.steps,
+                             # n_bf of the formula counted as the reference counts it (every continuum in range, exact zeros
+                             # included) instead of the live continua the kernel evaluates: comparable with earlier rounds
+                             "algorithmic_bytes_per_launch_every_continuum": alg_bytes_ref / a.steps,
+                             "frac_every_continuum": (alg_bytes_ref / (kernel_ms * 1e-3) / 1e9 / peak) if kernel_ms > 0 else 0.0,
                              "traffic_source": TRAFFIC_FILE + " (ncu dram bytes per launch, filed under the workload key; "
                                                "null when no capture of this workload and packet count is committed)",
                              "workload_key": workload_key(wname, P)},

@@ -142,6 +142,10 @@ enum {
   ARTIS_CTR_PACKET_UPDATES = 49,  /* do_packet calls */
   ARTIS_CTR_HANDOFFS = 50,        /* packets handed from one scheduler ring to another in mid-timestep */
   /* [51,61): unused since ABI 6 (were the per-kind scheduler statistics of five kinds), except: */
+  ARTIS_CTR_BF_LISTED = 51,       /* bf continua the REFERENCE's loop visits for the same opacity evaluations (every continuum with
+                                   * nu_edge <= nu <= nu_edge * last_phixs_nuovernuedge); BF_EVALUATED counts the live ones */
+  ARTIS_CTR_THIN_BEGIN_CYCLES = 52, /* of WARP_CYCLES0 + 1 (r-packet steps in non-grey cells): SM cycles up to the opacity evaluation */
+  ARTIS_CTR_THIN_KAPPA_CYCLES = 53, /* ... and inside it (coop_kappa_warm); the rest is get_event, the event and the estimators */
   ARTIS_CTR_VPKT_REQUESTS = 57,   /* VPKT_ON: interactions whose virtual packets were traced from the request list in the last transport */
   ARTIS_CTR_VPKT_RESTARTS = 58,   /* ... times the request list filled and the scheduler was launched again */
   ARTIS_CTR_DRAIN_NS_10PCT = 61,  /* ns from the transport launch until 10% / 1% / none of the packets are still active */

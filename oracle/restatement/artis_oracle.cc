@@ -39,6 +39,7 @@ void be_timer_begin() { g_t0 = std::chrono::steady_clock::now(); }
 double be_timer_end_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_t0).count(); }
 void be_run_levelpop(long long n) { for (long long i = 0; i < n; i++) artis::body_levelpop(g_ctx, i); }
 void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g_ctx, i); }
+void be_run_ff_zsum(long long n, double *out) { for (long long i = 0; i < n; i++) artis::body_ff_zsum(g_ctx, i, out); }
 size_t be_free_bytes() { return (size_t)1 << 46; }
 long long be_run_bf_live_count(long long ncells, long long *off) {
   long long run = 0;
@@ -49,11 +50,15 @@ long long be_run_bf_live_count(long long ncells, long long *off) {
   off[ncells] = run;
   return run;
 }
-void be_run_bf_live_fill(long long ncells, const long long *off, double *pair, artis::ContRec *rec) {
+void be_run_bf_live_fill(long long ncells, const long long *off, double *pair, artis::ContRec *rec, int *rank) {
+  const int nbf = g_ctx.st.nbfcontinua;
   for (long long tc = 0; tc < ncells; tc++) {
     long long at = off[tc];
-    for (int i = 0; i < g_ctx.st.nbfcontinua; i++)
+    for (int i = 0; i < nbf; i++) {
+      rank[(size_t)tc * (nbf + 1) + i] = (int)(at - off[tc]);
       if (artis::body_bf_live_test(g_ctx, (int)tc, i)) artis::body_bf_live_store(g_ctx, (int)tc, i, at++, pair, rec);
+    }
+    rank[(size_t)tc * (nbf + 1) + nbf] = (int)(at - off[tc]);
   }
 }
 void be_run_corrphoto(long long n) { for (long long i = 0; i < n; i++) artis::body_corrphoto(g_ctx, i); }
