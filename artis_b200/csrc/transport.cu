@@ -586,6 +586,28 @@ __device__ __forceinline__ void kappa_stage_init(KappaStage *ks) {
 // `nchunk`: chunks this warp has staged since the kernel began (stage = nchunk % KSTAGES, mbarrier parity from it).
 // need / nu_cmf / mgi: this lane's request; returns its bound-free sum; gc(slot, v) is called on the owner lane for every
 // ground-continuum contribution, in index order like the serial loop (rpkt.cc:1158-1166).
+// -DARTIS_KAPPA_PROFILE: where the cycles of coop_kappa_sum go (measurement builds): counters[54..56], [59], [60] and [55]...
+#ifdef ARTIS_KAPPA_PROFILE
+#define KP_BEGIN() long long kp_t = clock64(), kp_acc[6] = {0, 0, 0, 0, 0, 0}
+#define KP_ADD(i)                 \
+  do {                            \
+    const long long kp_n = clock64(); \
+    kp_acc[i] += kp_n - kp_t;     \
+    kp_t = kp_n;                  \
+  } while (0)
+#define KP_END()                                                                                           \
+  do {                                                                                                     \
+    if ((threadIdx.x & 31) == 0) {                                                                         \
+      const int kp_slot[6] = {54, 55, 56, 58, 59, 60};                                                     \
+      for (int kp_i = 0; kp_i < 6; kp_i++)                                                                 \
+        atomicAdd((unsigned long long *)&c.es.counters[kp_slot[kp_i]], (unsigned long long)kp_acc[kp_i]); \
+    }                                                                                                      \
+  } while (0)
+#else
+#define KP_BEGIN()
+#define KP_ADD(i)
+#define KP_END()
+#endif
 template <class GC>
 __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool need, const int mgi, const double nu_cmf,
                                                  artis::Tally &tl, KappaStage *ks, unsigned &nchunk, GC gc) {
@@ -594,6 +616,7 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
   const int lane = threadIdx.x & 31;
   const unsigned owners = __ballot_sync(full, need);
   if (owners == 0u) return 0.;
+  KP_BEGIN();
   // every owner prepares its own sum in parallel: the range of continua, exp(-h nu / k T_e)
   double kappa_bf = 0., my_expfac = 0.;
   int my_ilo = 0, my_i0 = 0;
@@ -645,9 +668,11 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
     iss_j++;
     if (iss_j == iss_nch) iss_next_owner();
   };
+  KP_ADD(0);  // prologue: every owner's range, exp, list pointers
   iss_next_owner();
 #pragma unroll
   for (int s2 = 0; s2 < KSTAGES; s2++) issue_one();
+  KP_ADD(3);
   unsigned rest = owners;
   while (rest != 0u) {
     const int owner = __ffs(rest) - 1;
@@ -659,7 +684,9 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
     double sum = 0.;
     for (int base = ilo; base < i0; base += KCH) {
       const int st = (int)(nchunk % KSTAGES);
+      KP_ADD(4);  // owner set-up (shuffles) and loop overhead
       mbar_wait(&ks->bar[st], (nchunk / KSTAGES) & 1u);
+      KP_ADD(1);
       nchunk++;
       double t[KCH_TILES], gcontr[KCH_TILES];
       int slot[KCH_TILES];
@@ -677,7 +704,9 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
         }
       }
       __syncwarp(full);  // every lane has its operands out of the stage: it can be refilled
+      KP_ADD(2);  // term arithmetic
       issue_one();
+      KP_ADD(3);  // copy issue
 #pragma unroll
       for (int off = 1; off < BF_TILE; off <<= 1) {  // adjacent pairs first: the tree of rpkt.cuh PairTree
 #pragma unroll
@@ -695,10 +724,13 @@ __device__ __forceinline__ double coop_kappa_sum(const artis::Ctx &c, const bool
           if (lane == owner) gc(sl, v);
         }
       }
+      KP_ADD(5);
     }
+    KP_ADD(5);  // reductions and ground-continuum contributions (of the owner's last chunk; the others fall under 4)
     sum = __shfl_sync(full, sum, 0);
     if (lane == owner) kappa_bf = sum;
   }
+  KP_END();
   return kappa_bf;
 }
 // the single-kernel variant: the thin role's own warp evaluates the sums of its lanes and leaves them in their caches

@@ -453,6 +453,9 @@ def main():
                            "mean_busy_lanes_by_kind": [round(float(ctr_sum[72 + i]) / max(float(ctr_sum[64 + i]), 1.0), 2) for i in range(8)],
                            "warp_Mcycles_by_kind": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[80:88]],
                            "rpkt_steps_and_kappa_evals_per_step": [float(ctr_sum[35]) / a.steps / world, float(ctr_sum[48]) / a.steps / world],
+                           # -DARTIS_KAPPA_PROFILE builds only: prologue, barrier wait, term arithmetic, copy issue, owner set-up, reductions
+                           "kappa_profile_Mcycles": ([round(float(ctr_sum[i]) / a.steps / world * 1e-6, 1) for i in (54, 55, 56, 58, 59, 60)]
+                                                     if ctr_sum[54] > 0 and not st.get("opt_vpkt_on") else None),
                            "thin_role_Mcycles_begin_kappa": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[52:54]],
                            "warp_Mcycles_refill_push_idle": [round(float(x) / a.steps / world * 1e-6, 1) for x in ctr_sum[88:91]],
                            "scheduler_geometry_kernels_blocks_single_big_jump": T.scheduler_geometry(),
