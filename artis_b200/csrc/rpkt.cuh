@@ -428,7 +428,11 @@ struct BfList {
 };
 ARTIS_DEV BfList bf_list(const Ctx &c, const int tc) {
   BfList l;
-  if (c.tb.bf_live_off != nullptr) {
+  if (tc < 0) {  // a cell without a table row (empty or grey: the transport never asks; the probes may)
+    l.pair = nullptr;
+    l.rec = nullptr;
+    l.n = 0;
+  } else if (c.tb.bf_live_off != nullptr) {
     const long long o = c.tb.bf_live_off[tc];
     l.pair = c.tb.bf_live_pair + 2 * o;
     l.rec = c.tb.bf_live_rec + o;
@@ -447,7 +451,10 @@ ARTIS_DEV void bf_list_range(const Ctx &c, const int tc, const double nu, int *i
   const int f0 = bf_stop_index(c, nu);
   const int flo = bf_start_index(c, nu, f0);
   *listed = f0 - flo;
-  if (c.tb.bf_live_off != nullptr) {
+  if (tc < 0) {
+    *i0 = 0;
+    *ilo = 0;
+  } else if (c.tb.bf_live_off != nullptr) {
     const int *rank = c.tb.bf_live_rank + (size_t)tc * (c.st.nbfcontinua + 1);
     *i0 = rank[f0];
     *ilo = rank[flo];
