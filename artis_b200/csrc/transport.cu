@@ -348,6 +348,13 @@ constexpr unsigned ROLES_ALL = ROLES_HEAVY | (1u << artis::KIND_MAJUMP);
 #ifndef ARTIS_HEAVY_MINBLOCKS
 #define ARTIS_HEAVY_MINBLOCKS 3
 #endif
+// ARTIS_HEAVY_MAXNREG: an explicit register cap for the big kernel instead of one derived from blocks per SM (160: two of its
+// blocks leave room for three blocks of the jump kernel; measurement builds)
+#ifdef ARTIS_HEAVY_MAXNREG
+#define ARTIS_HEAVY_BOUNDS __maxnreg__(ARTIS_HEAVY_MAXNREG)
+#else
+#define ARTIS_HEAVY_BOUNDS __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS)
+#endif
 #ifndef ARTIS_JUMP_MINBLOCKS
 #define ARTIS_JUMP_MINBLOCKS 8
 #endif
@@ -794,7 +801,7 @@ __device__ __forceinline__ bool row_arena_stop(const artis::Ctx &c, const int la
 
 // ROLES: bit mask of the kinds the warps of this kernel may take up
 template <unsigned ROLES>
-__global__ void __launch_bounds__(128, ARTIS_HEAVY_MINBLOCKS) k_transport_persistent(PktHot *hot, PktCold *cold, PersistView pv, long long max_events,
+__global__ void ARTIS_HEAVY_BOUNDS k_transport_persistent(PktHot *hot, PktCold *cold, PersistView pv, long long max_events,
                                                                        unsigned long long idle_timeout_ns) {
   using namespace artis;
   const Ctx &c = d_ctx;

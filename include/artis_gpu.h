@@ -180,7 +180,10 @@ int artis_gpu_zero_estimators(void);
 /* ---- the hot path ------------------------------------------------------------------------------------- */
 /* Drop-in for update_packets(my_rank, nts, packets) (update_packets.cc:234): H2D of the AoS packet array,
  * all passes of the transport, D2H of the packets. Postconditions as update_packets.cc:309:
- * every packet has type ESCAPE or prop_time == ts+tw. Packets come back in input order. */
+ * every packet has type ESCAPE or prop_time == ts+tw. Packets come back in input order.
+ * An ensemble that does not fit the device next to the tables is streamed through it in batches (the reference reads and
+ * writes a rank's packets in one piece, sn3d.cc:387-398; packets are independent within a timestep and the estimators keep
+ * accumulating): the batch size follows from the free device memory, ARTIS_BATCH_PACKETS sets it by hand. */
 int artis_gpu_update_packets(int my_rank, int nts, ArtisPacket *host_packets, int npkts);
 /* The same in three steps, so that a driver can keep the packets resident between timesteps
  *  and so that the device-resident rate can be measured separately from the copies. */
