@@ -1504,6 +1504,14 @@ void *be_alloc(size_t n) {
   return p;
 }
 void be_free(void *p) { cudaFree(p); }
+// artis_gpu_finalize: the buffers this backend grows on demand (the streams and events stay: a later init reuses them)
+void be_release() {
+  if (g_kcache) cudaFree(g_kcache);
+  if (g_stepstate) cudaFree(g_stepstate);
+  g_kcache = nullptr;
+  g_stepstate = nullptr;
+  g_kcache_doubles = 0;
+}
 size_t be_free_bytes() {
   size_t fr = 0, tot = 0;
   if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) {

@@ -40,6 +40,7 @@ double be_timer_end_ms() { return std::chrono::duration<double, std::milli>(std:
 void be_run_levelpop(long long n) { for (long long i = 0; i < n; i++) artis::body_levelpop(g_ctx, i); }
 void be_run_bf(long long n) { for (long long i = 0; i < n; i++) artis::body_bf(g_ctx, i); }
 void be_run_ff_zsum(long long n, double *out) { for (long long i = 0; i < n; i++) artis::body_ff_zsum(g_ctx, i, out); }
+void be_release() {}
 size_t be_free_bytes() { return (size_t)1 << 46; }
 long long be_run_bf_live_count(long long ncells, long long *off) {
   long long run = 0;
