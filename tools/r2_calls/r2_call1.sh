@@ -1,7 +1,7 @@
 #!/bin/bash
 # One gpurun call after the container was re-created: GPU parity tests, smoke, the classic bench (both arms), and the first
 # lines of the two new workloads (config 5: virtual packets, warp-cooperative ray trace against the one-lane build; config 3:
-# kilonova with 1.1e6 lines), each with its reference arm.   gpurun --timeout 2400 -- bash tools/r2_call1.sh [tag]
+# kilonova with 1.1e6 lines), each with its reference arm.   gpurun --timeout 2400 -- bash tools/r2_calls/r2_call1.sh [tag]
 TAG=${1:-call1}
 O=gpurun_out/$TAG
 mkdir -p $O
