@@ -112,7 +112,7 @@ constexpr int NRING = NKIND + 2;
 #define ARTIS_RING_STRIDE 16
 #endif
 constexpr int RING_META_STRIDE = ARTIS_RING_STRIDE;
-constexpr int RING_META_WORDS = (2 * NRING + 2) * RING_META_STRIDE;
+constexpr int RING_META_WORDS = (2 * NRING + 3) * RING_META_STRIDE;  // heads, tails, active count, start time, partner flag
 
 struct QueueView {
   const int *in;        // indices to consume

@@ -366,6 +366,7 @@ struct PersistView {
   int *n_active;             // packets that have not finished the timestep
   int n_initial;             // its value at launch
   unsigned long long *t_start;  // globaltimer at launch
+  int *partner_started;         // two-kernel scheduler: set by the jump kernel when it starts (nullptr: one kernel)
   int cap;
   unsigned long long *pend;  // [cap] macro-atom action a jump has drawn and left for the event role: (action + 1) << 32 | selidx
   double *kcache;            // [cap][kstride] continuum opacity delivered for a packet: KappaCache scalars + gamma_contr
@@ -513,6 +514,9 @@ __device__ __forceinline__ bool idle_poll(const artis::Ctx &c, const PersistView
   if (lane == 0) left = *reinterpret_cast<volatile int *>(pv.n_active);
   left = __shfl_sync(full, left, 0);
   if (left <= 0) return true;  // every packet has reached the end of the timestep
+  if (lane == 0 && c.error_flag != nullptr) left = (*reinterpret_cast<volatile int *>(c.error_flag) != 0) ? -1 : left;
+  left = __shfl_sync(full, left, 0);
+  if (left < 0) return true;   // somebody has given the timestep up
   unsigned long long now = 0ull;
   if (lane == 0) now = global_ns();
   now = __shfl_sync(full, now, 0);
@@ -521,6 +525,18 @@ __device__ __forceinline__ bool idle_poll(const artis::Ctx &c, const PersistView
   if (idle_since == 0ull || left != last_active) {
     idle_since = now;
     last_active = left;
+  }
+  // The two kernels of the pair need each other. Under a profiler, a debugger or CUDA_LAUNCH_BLOCKING the runtime runs
+  // kernels one after the other: this kernel then waits for a partner that cannot start before it ends. One second without
+  // progress and without the partner's start flag: give up with code 901; the host switches to the one-kernel scheduler and
+  // launches the unfinished packets again (engine.inc).
+  if (pv.partner_started != nullptr) {
+    int give_up = 0;
+    if (lane == 0 && now - idle_since > 1000000000ull && *reinterpret_cast<volatile int *>(pv.partner_started) == 0) {
+      if (c.error_flag) atomicCAS(c.error_flag, 0, 901);
+      give_up = 1;
+    }
+    if (__shfl_sync(full, give_up, 0) != 0) return true;
   }
   if (now - idle_since > idle_timeout_ns) {  // a lost packet would otherwise hang the device
     if (lane == 0 && c.error_flag) atomicCAS(c.error_flag, 0, 900);
@@ -1089,6 +1105,7 @@ __global__ void __launch_bounds__(128, ARTIS_JUMP_MINBLOCKS) k_transport_light(P
   const int event_cap = max_events > 0x7fffffffLL ? 0x7fffffff : (int)max_events;
   MaView v = {0, 0, 0, 0, 0};
   Rng rng = {};
+  if (blockIdx.x == 0 && threadIdx.x == 0 && pv.partner_started != nullptr) *reinterpret_cast<volatile int *>(pv.partner_started) = 1;
   unsigned long long idle_since = 0ull;
   int last_active = -1;
   int refill_skip = 0;
@@ -1630,6 +1647,7 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
   pv.n_active = reinterpret_cast<int *>(pmeta + 2 * NRING * RMS);
   pv.n_initial = n_initial;
   pv.t_start = pmeta + (2 * NRING + 1) * RMS;
+  pv.partner_started = nullptr;  // set below for the pair
   pv.cap = cap;
   pv.pend = pend;
   // opacity hand-over rows of the two-kernel scheduler (8 scalars + the ground-continuum contributions per packet)
@@ -1663,6 +1681,7 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
       w.tail = scratch + NRING * RMS;
       w.n_active = reinterpret_cast<int *>(scratch + 2 * NRING * RMS);
       w.t_start = scratch + (2 * NRING + 1) * RMS;
+      w.partner_started = nullptr;
       w.n_initial = 0;
       k_transport_persistent<ROLES_ALL><<<g_sms * g_blocks_all, 128, KAPPA_SMEM_PER_BLOCK, g_stream>>>(hot, cold, w, maxev, timeout);
       k_transport_persistent<ROLES_HEAVY><<<g_sms * g_blocks_heavy, 128, HEAVY_SMEM, g_stream>>>(hot, cold, w, maxev, timeout);
@@ -1681,6 +1700,7 @@ bool be_run_persistent(PktHot *hot, PktCold *cold, int *rings, int cap, unsigned
   // need next to none -- launched the other way round, the split chosen for the first kernel leaves no room for the
   // second one's blocks and they wait for the first kernel to drain, which it never does (each waits for the other's
   // packets). The side stream waits for what is queued on the main stream (ring setup), the main stream for the side kernel.
+  pv.partner_started = reinterpret_cast<int *>(pmeta + (2 * NRING + 2) * RMS);
   note(cudaEventRecord(g_ev_fork, g_stream), "event record");
   note(cudaStreamWaitEvent(g_stream2, g_ev_fork, 0), "stream wait");
   if (LIGHT_SMEM != 0) k_transport_light<<<g_sms * g_blocks_jump, 128, LIGHT_SMEM, g_stream2>>>(hot, pv, maxev, timeout);
